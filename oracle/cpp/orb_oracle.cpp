@@ -1,0 +1,780 @@
+// orb_oracle.cpp — CPU ORACLE (test infrastructure, NOT product code; see orb_oracle.h).
+//
+// Restates, with no OpenCV dependency, the CPU path of the reference:
+//   ORBextractor_old.cc (ctor :411-471, DivideNode :482-538, compareNodes :540-555, DistributeOctTree :557-781,
+//   ComputeKeyPointsOctTree :783-898, IC_Angle :78-105, computeOrbDescriptor :109-148, operator() :1088-1191,
+//   ComputePyramid :1331-1356) and Frame.cc:45,1227-1231 (BFMatcher NORM_HAMMING knnMatch k=2).
+// The OpenCV primitives (resize INTER_LINEAR 8U, copyMakeBorder REFLECT_101, FAST-9/16 + NMS, GaussianBlur 7x7
+// sigma 2 fixed point, fastAtan2, cvRound) are restated from OpenCV 4.x's published algorithms; OpenCV is a
+// third-party dependency of the reference (4.2.0 Android SDK, CMakeLists.txt:38-58) that is not vendored.
+// Parity: pinned against cv2 4.13.0 in this container (tests/test_oracle_vs_cv2.py, tests/golden/).
+//
+// Floating point: built with -ffp-contract=off; every expression keeps the reference's types and order.
+#include "orb_oracle.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cfloat>
+#include <cstring>
+#include <list>
+#include <thread>
+#include <utility>
+#include <vector>
+
+#include "../../orbslam3lib_b200/csrc/orb_pattern.h"
+
+namespace {
+
+// ---- OpenCV scalar helpers -------------------------------------------------------------------------------------
+inline int cvRoundD(double v) { return (int)std::lrint(v); }    // round-half-to-even (default FP environment)
+inline int cvRoundF(float v) { return (int)std::lrintf(v); }
+inline int cvFloorD(double v) { int i = (int)v; return i - (i > v); }
+inline int cvCeilD(double v) { int i = (int)v; return i + (i < v); }
+inline int reflect101(int p, int len) {
+    // cv::borderInterpolate(p, len, BORDER_REFLECT_101)
+    if ((unsigned)p < (unsigned)len) return p;
+    if (len == 1) return 0;
+    do {
+        if (p < 0) p = -p; else p = 2 * len - p - 2;
+    } while ((unsigned)p >= (unsigned)len);
+    return p;
+}
+
+const int kPatch = 31, kHalfPatch = 15, kEdge = 19;
+
+struct Timer {
+    std::chrono::high_resolution_clock::time_point t0 = std::chrono::high_resolution_clock::now();
+    double lap() {
+        auto t1 = std::chrono::high_resolution_clock::now();
+        double s = std::chrono::duration<double>(t1 - t0).count();
+        t0 = t1;
+        return s;
+    }
+};
+
+// ---- cv::resize INTER_LINEAR, CV_8UC1 --------------------------------------------------------------------------
+// imgproc/resize.cpp: coefficient setup of cv::resize + HResizeLinear<uchar,int,short,2048> +
+// VResizeLinear<uchar,int,short,FixedPtCast<int,uchar,22>>.
+void resizeLinearU8(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride) {
+    const double inv_x = (double)dw / sw, inv_y = (double)dh / sh;
+    const double scale_x = 1. / inv_x, scale_y = 1. / inv_y;
+    std::vector<int> xofs(dw), yofs(dh);
+    std::vector<short> alpha(2 * dw), beta(2 * dh);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx = (float)((dx + 0.5) * scale_x - 0.5);
+        int sx = cvFloorD(fx);
+        fx -= sx;
+        if (sx < 0) { fx = 0; sx = 0; }
+        if (sx >= sw - 1) { fx = 0; sx = sw - 1; }
+        xofs[dx] = sx;
+        alpha[2 * dx] = (short)cvRoundF((1.f - fx) * 2048);
+        alpha[2 * dx + 1] = (short)cvRoundF(fx * 2048);
+    }
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5) * scale_y - 0.5);
+        int sy = cvFloorD(fy);
+        fy -= sy;
+        yofs[dy] = sy;
+        beta[2 * dy] = (short)cvRoundF((1.f - fy) * 2048);
+        beta[2 * dy + 1] = (short)cvRoundF(fy * 2048);
+    }
+    auto clipRow = [sh](int y) { return y < 0 ? 0 : (y < sh ? y : sh - 1); };
+    std::vector<int> r0(dw), r1(dw);
+    for (int dy = 0; dy < dh; dy++) {
+        const uint8_t* s0 = src + (size_t)clipRow(yofs[dy]) * sstride;
+        const uint8_t* s1 = src + (size_t)clipRow(yofs[dy] + 1) * sstride;
+        for (int dx = 0; dx < dw; dx++) {
+            int sx = xofs[dx], sx1 = sx + 1 < sw ? sx + 1 : sx;
+            int a0 = alpha[2 * dx], a1 = alpha[2 * dx + 1];
+            r0[dx] = s0[sx] * a0 + s0[sx1] * a1;
+            r1[dx] = s1[sx] * a0 + s1[sx1] * a1;
+        }
+        int b0 = beta[2 * dy], b1 = beta[2 * dy + 1];
+        uint8_t* d = dst + (size_t)dy * dstride;
+        for (int dx = 0; dx < dw; dx++)
+            d[dx] = (uint8_t)((((b0 * (r0[dx] >> 4)) >> 16) + ((b1 * (r1[dx] >> 4)) >> 16) + 2) >> 2);
+    }
+}
+
+void borderReflect101(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride, int b) {
+    for (int y = -b; y < h + b; y++) {
+        const uint8_t* s = src + (size_t)reflect101(y, h) * sstride;
+        uint8_t* d = dst + (size_t)(y + b) * dstride;
+        for (int x = -b; x < w + b; x++) d[x + b] = s[reflect101(x, w)];
+    }
+}
+
+// ---- cv::GaussianBlur 7x7 sigma=2, CV_8U: fixed-point (Q8 kernel, ufixedpoint16/32) path of smooth.simd.hpp -----
+void gaussian7x7U8(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride) {
+    static const uint32_t k[7] = {18, 34, 48, 56, 48, 34, 18};    // getGaussianKernelBitExact(7, 2) * 256
+    std::vector<uint16_t> hbuf((size_t)w * h);
+    std::vector<int> xi(w + 6);
+    for (int x = -3; x < w + 3; x++) xi[x + 3] = reflect101(x, w);
+    for (int y = 0; y < h; y++) {
+        const uint8_t* s = src + (size_t)y * sstride;
+        uint16_t* hb = &hbuf[(size_t)y * w];
+        for (int x = 0; x < w; x++) {
+            uint32_t acc = 0;
+            for (int i = 0; i < 7; i++) acc += k[i] * s[xi[x + i]];
+            hb[x] = (uint16_t)acc;    // <= 255*256, no saturation
+        }
+    }
+    for (int y = 0; y < h; y++) {
+        const uint16_t* rows[7];
+        for (int i = 0; i < 7; i++) rows[i] = &hbuf[(size_t)reflect101(y + i - 3, h) * w];
+        uint8_t* d = dst + (size_t)y * dstride;
+        for (int x = 0; x < w; x++) {
+            uint32_t acc = 0;
+            for (int i = 0; i < 7; i++) acc += k[i] * rows[i][x];
+            d[x] = (uint8_t)((acc + 32768u) >> 16);
+        }
+    }
+}
+
+// ---- cv::FAST TYPE_9_16 with non-max suppression (features2d/fast.cpp, fast_score.cpp) -------------------------
+// Bresenham circle of radius 3, clockwise from (0,3).
+const int kRingDx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
+const int kRingDy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+
+// cornerScore<16> (fast_score.cpp): the largest threshold at which the pixel is still a FAST-9 corner, floored at
+// `threshold`.  With d[k] = v - ring[k]:  max(threshold, max_arcs min(d), -min_arcs max(d)) - 1 over the sixteen
+// 9-long circular arcs.  (OpenCV prunes arcs early; the value is the same.)
+inline int fastCornerScore(const uint8_t* p, const int* off, int threshold) {
+    int d[24];
+    const int v = p[0];
+    for (int k = 0; k < 24; k++) d[k] = v - p[off[k & 15]];
+    int best = threshold;
+    for (int k = 0; k < 16; k++) {
+        int mn = d[k], mx = d[k];
+        for (int i = 1; i < 9; i++) { mn = std::min(mn, d[k + i]); mx = std::max(mx, d[k + i]); }
+        best = std::max(best, std::max(mn, -mx));
+    }
+    return best - 1;
+}
+
+struct XYR { int x, y, r; };
+
+void fast9Nms(const uint8_t* img, int w, int h, int stride, int threshold, std::vector<XYR>& out) {
+    out.clear();
+    if (w < 7 || h < 7) return;
+    threshold = std::min(std::max(threshold, 0), 255);
+    int off[16];
+    for (int k = 0; k < 16; k++) off[k] = kRingDy[k] * stride + kRingDx[k];
+    // three rolling score rows (zero = not a corner) + corner position lists, as in FAST_t
+    std::vector<uint8_t> sbuf((size_t)3 * w, 0);
+    std::vector<int> cbuf((size_t)3 * (w + 1));
+    uint8_t* buf[3] = {&sbuf[0], &sbuf[w], &sbuf[2 * (size_t)w]};
+    int* cpbuf[3] = {&cbuf[0], &cbuf[w + 1], &cbuf[2 * (size_t)(w + 1)]};
+    for (int i = 3; i < h - 2; i++) {
+        const uint8_t* ptr = img + (size_t)i * stride + 3;
+        uint8_t* curr = buf[(i - 3) % 3];
+        int* cornerpos = cpbuf[(i - 3) % 3] + 1;
+        std::memset(curr, 0, w);
+        int ncorners = 0;
+        if (i < h - 3) {
+            for (int j = 3; j < w - 3; j++, ptr++) {
+                int v = ptr[0];
+                int lo = v - threshold, hi = v + threshold;
+                // opposite-pair rejection cascade of FAST_t: a 9-arc contains one pixel of every opposite pair,
+                // so the class (1 = darker, 2 = brighter) must survive the AND over all eight pairs.
+                auto cls = [&](int k) { int x = ptr[off[k]]; return x < lo ? 1 : (x > hi ? 2 : 0); };
+                int d = cls(0) | cls(8);
+                if (d == 0) continue;
+                d &= cls(2) | cls(10);
+                d &= cls(4) | cls(12);
+                d &= cls(6) | cls(14);
+                if (d == 0) continue;
+                d &= cls(1) | cls(9);
+                d &= cls(3) | cls(11);
+                d &= cls(5) | cls(13);
+                d &= cls(7) | cls(15);
+                bool corner = false;
+                if (d & 1) {
+                    int count = 0;
+                    for (int k = 0; k < 25; k++) {
+                        if (ptr[off[k & 15]] < lo) { if (++count > 8) { corner = true; break; } } else count = 0;
+                    }
+                }
+                if (!corner && (d & 2)) {
+                    int count = 0;
+                    for (int k = 0; k < 25; k++) {
+                        if (ptr[off[k & 15]] > hi) { if (++count > 8) { corner = true; break; } } else count = 0;
+                    }
+                }
+                if (corner) {
+                    cornerpos[ncorners++] = j;
+                    curr[j] = (uint8_t)fastCornerScore(ptr, off, threshold);
+                }
+            }
+        }
+        cornerpos[-1] = ncorners;
+        if (i == 3) continue;
+        const uint8_t* prev = buf[(i - 4 + 3) % 3];
+        const uint8_t* pprev = buf[(i - 5 + 3) % 3];
+        cornerpos = cpbuf[(i - 4 + 3) % 3] + 1;
+        ncorners = cornerpos[-1];
+        for (int k = 0; k < ncorners; k++) {
+            int j = cornerpos[k];
+            int score = prev[j];
+            if (score > prev[j + 1] && score > prev[j - 1] && score > pprev[j - 1] && score > pprev[j] &&
+                score > pprev[j + 1] && score > curr[j - 1] && score > curr[j] && score > curr[j + 1])
+                out.push_back({j, i - 1, score});
+        }
+    }
+}
+
+// ---- cv::fastAtan2 (core/mathfuncs_core: atan_f32) -------------------------------------------------------------
+float fastAtan2f(float y, float x) {
+    static const float p1 = 0.9997878412794807f * (float)(180 / 3.14159265358979323846);
+    static const float p3 = -0.3258083974640975f * (float)(180 / 3.14159265358979323846);
+    static const float p5 = 0.1555786518463281f * (float)(180 / 3.14159265358979323846);
+    static const float p7 = -0.04432655554792128f * (float)(180 / 3.14159265358979323846);
+    float ax = std::fabs(x), ay = std::fabs(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = ay / (ax + (float)DBL_EPSILON);
+        c2 = c * c;
+        a = (((p7 * c2 + p5) * c2 + p3) * c2 + p1) * c;
+    } else {
+        c = ax / (ay + (float)DBL_EPSILON);
+        c2 = c * c;
+        a = 90.f - (((p7 * c2 + p5) * c2 + p3) * c2 + p1) * c;
+    }
+    if (x < 0) a = 180.f - a;
+    if (y < 0) a = 360.f - a;
+    return a;
+}
+
+// ---- Hamming kNN (k = 2), OpenCV tie rule: equal distances keep the lower train index first ---------------------
+inline int hamming256(const uint64_t* a, const uint64_t* b) {
+    return __builtin_popcountll(a[0] ^ b[0]) + __builtin_popcountll(a[1] ^ b[1]) +
+           __builtin_popcountll(a[2] ^ b[2]) + __builtin_popcountll(a[3] ^ b[3]);
+}
+void knn2Range(const uint8_t* q, int64_t q0, int64_t q1, const uint8_t* t, int64_t nt, int32_t* idx, int32_t* dist) {
+    for (int64_t i = q0; i < q1; i++) {
+        uint64_t qa[4];
+        std::memcpy(qa, q + i * 32, 32);
+        int b1 = 1 << 30, b2 = 1 << 30;
+        int64_t i1 = -1, i2 = -1;
+        for (int64_t j = 0; j < nt; j++) {
+            uint64_t tb[4];
+            std::memcpy(tb, t + j * 32, 32);
+            int d = hamming256(qa, tb);
+            if (d < b1) { b2 = b1; i2 = i1; b1 = d; i1 = j; }
+            else if (d < b2) { b2 = d; i2 = j; }
+        }
+        idx[2 * i] = (int32_t)i1; dist[2 * i] = i1 < 0 ? -1 : b1;
+        idx[2 * i + 1] = (int32_t)i2; dist[2 * i + 1] = i2 < 0 ? -1 : b2;
+    }
+}
+
+// ---- the extractor ---------------------------------------------------------------------------------------------
+struct KeyPt {    // cv::KeyPoint
+    float x = 0, y = 0, size = 0, angle = -1, response = 0;
+    int octave = 0, class_id = -1;
+};
+struct Pt2i { int x = 0, y = 0; };
+
+struct Node {    // ExtractorNode, ORBextractor_old.h:32-44
+    std::vector<KeyPt> keys;
+    Pt2i UL, UR, BL, BR;
+    std::list<Node>::iterator lit;
+    bool noMore = false;
+    void divide(Node& n1, Node& n2, Node& n3, Node& n4) const;
+};
+
+void Node::divide(Node& n1, Node& n2, Node& n3, Node& n4) const {    // :482-538
+    const int halfX = (int)std::ceil(static_cast<float>(UR.x - UL.x) / 2);
+    const int halfY = (int)std::ceil(static_cast<float>(BR.y - UL.y) / 2);
+    n1.UL = UL;
+    n1.UR = {UL.x + halfX, UL.y};
+    n1.BL = {UL.x, UL.y + halfY};
+    n1.BR = {UL.x + halfX, UL.y + halfY};
+    n2.UL = n1.UR;
+    n2.UR = UR;
+    n2.BL = n1.BR;
+    n2.BR = {UR.x, UL.y + halfY};
+    n3.UL = n1.BL;
+    n3.UR = n1.BR;
+    n3.BL = BL;
+    n3.BR = {n1.BR.x, BL.y};
+    n4.UL = n3.UR;
+    n4.UR = n2.BR;
+    n4.BL = n3.BR;
+    n4.BR = BR;
+    for (const KeyPt& kp : keys) {
+        if (kp.x < n1.UR.x) {
+            if (kp.y < n1.BR.y) n1.keys.push_back(kp); else n3.keys.push_back(kp);
+        } else if (kp.y < n1.BR.y) n2.keys.push_back(kp);
+        else n4.keys.push_back(kp);
+    }
+    n1.noMore = n1.keys.size() == 1;
+    n2.noMore = n2.keys.size() == 1;
+    n3.noMore = n3.keys.size() == 1;
+    n4.noMore = n4.keys.size() == 1;
+}
+
+typedef std::pair<int, Node*> SizeNode;
+thread_local int64_t g_sortTies = 0;
+bool compareNodes(SizeNode& e1, SizeNode& e2) {    // :540-555
+    if (e1.first < e2.first) return true;
+    if (e1.first > e2.first) return false;
+    if (e1.second != e2.second && e1.second->UL.x == e2.second->UL.x) g_sortTies++;
+    return e1.second->UL.x < e2.second->UL.x;
+}
+
+}  // namespace
+
+struct orc_extractor {
+    int nfeatures, nlevels, iniTh, minTh;
+    double scaleFactor;    // the reference stores the float ctor argument in a double member (ORBextractor_old.h:103)
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> featuresPerLevel, umax;
+    Pt2i pattern[512];
+    // state of the last call
+    struct Level {
+        int w = 0, h = 0, pw = 0;
+        std::vector<uint8_t> padded;     // (w+38) x (h+38), ROI at (19,19) — mvImagePyramid[level]
+        std::vector<uint8_t> blurred;    // w x h, empty when the level produced no keypoint
+        std::vector<XYR> candidates;     // vToDistributeKeys, relative to (minBorderX, minBorderY)
+        std::vector<KeyPt> keypoints;    // after DistributeOctTree + border offset + angle (level coordinates)
+        const uint8_t* roi() const { return &padded[(size_t)kEdge * pw + kEdge]; }
+    };
+    std::vector<Level> levels;
+    double stage[7] = {0, 0, 0, 0, 0, 0, 0};
+    int64_t sortTies = 0;
+
+    orc_extractor(int nf, float sf, int nl, int ini, int mn);
+    void computePyramid(const uint8_t* img, int w, int h, int stride);
+    std::vector<KeyPt> distributeOctTree(const std::vector<KeyPt>& in, int minX, int maxX, int minY, int maxY, int N);
+    void computeKeyPointsOctTree();
+    int run(const uint8_t* img, int w, int h, int stride, int lap0, int lap1, orc_keypoint* kps, uint8_t* desc,
+            int cap, int* count);
+};
+
+orc_extractor::orc_extractor(int nf, float sf, int nl, int ini, int mn)
+    : nfeatures(nf), nlevels(nl), iniTh(ini), minTh(mn), scaleFactor(sf) {    // :411-471
+    scale.resize(nlevels);
+    sigma2.resize(nlevels);
+    scale[0] = 1.0f;
+    sigma2[0] = 1.0f;
+    for (int i = 1; i < nlevels; i++) {
+        scale[i] = scale[i - 1] * scaleFactor;    // float * double -> double -> float, as in the reference
+        sigma2[i] = scale[i] * scale[i];
+    }
+    invScale.resize(nlevels);
+    invSigma2.resize(nlevels);
+    for (int i = 0; i < nlevels; i++) {
+        invScale[i] = 1.0f / scale[i];
+        invSigma2[i] = 1.0f / sigma2[i];
+    }
+    featuresPerLevel.resize(nlevels);
+    float factor = 1.0f / scaleFactor;
+    float nDesired = nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nlevels));
+    int sum = 0;
+    for (int level = 0; level < nlevels - 1; level++) {
+        featuresPerLevel[level] = cvRoundF(nDesired);
+        sum += featuresPerLevel[level];
+        nDesired *= factor;
+    }
+    featuresPerLevel[nlevels - 1] = std::max(nfeatures - sum, 0);
+    for (int i = 0; i < 512; i++) {
+        pattern[i].x = ORBFE_BIT_PATTERN_31[2 * i];
+        pattern[i].y = ORBFE_BIT_PATTERN_31[2 * i + 1];
+    }
+    umax.resize(kHalfPatch + 1);
+    int v, v0, vmax = cvFloorD(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+    int vmin = cvCeilD(kHalfPatch * std::sqrt(2.f) / 2);
+    const double hp2 = kHalfPatch * kHalfPatch;
+    for (v = 0; v <= vmax; ++v) umax[v] = cvRoundD(std::sqrt(hp2 - v * v));
+    for (v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+        while (umax[v0] == umax[v0 + 1]) ++v0;
+        umax[v] = v0;
+        ++v0;
+    }
+    levels.resize(nlevels);
+}
+
+void orc_extractor::computePyramid(const uint8_t* img, int w, int h, int stride) {    // :1331-1356
+    for (int level = 0; level < nlevels; ++level) {
+        float s = invScale[level];
+        Level& L = levels[level];
+        L.w = cvRoundF((float)w * s);
+        L.h = cvRoundF((float)h * s);
+        L.pw = L.w + 2 * kEdge;
+        L.padded.assign((size_t)L.pw * (L.h + 2 * kEdge), 0);
+        L.blurred.clear();
+        L.candidates.clear();
+        L.keypoints.clear();
+        if (level != 0) {
+            const Level& P = levels[level - 1];
+            std::vector<uint8_t> tmp((size_t)L.w * L.h);
+            resizeLinearU8(P.roi(), P.w, P.h, P.pw, tmp.data(), L.w, L.h, L.w);
+            borderReflect101(tmp.data(), L.w, L.h, L.w, L.padded.data(), L.pw, kEdge);
+        } else {
+            borderReflect101(img, w, h, stride, L.padded.data(), L.pw, kEdge);
+        }
+    }
+}
+
+std::vector<KeyPt> orc_extractor::distributeOctTree(const std::vector<KeyPt>& in, int minX, int maxX, int minY,
+                                                    int maxY, int N) {    // :557-781
+    // the reference divides by nIni == 0 for images narrower than half their height (undefined behaviour); clamp.
+    const int nIni = std::max(1, (int)std::round(static_cast<float>(maxX - minX) / (maxY - minY)));
+    const float hX = static_cast<float>(maxX - minX) / nIni;
+    std::list<Node> nodes;
+    std::vector<Node*> ini(nIni);
+    for (int i = 0; i < nIni; i++) {
+        Node ni;
+        ni.UL = {(int)(hX * static_cast<float>(i)), 0};
+        ni.UR = {(int)(hX * static_cast<float>(i + 1)), 0};
+        ni.BL = {ni.UL.x, maxY - minY};
+        ni.BR = {ni.UR.x, maxY - minY};
+        nodes.push_back(ni);
+        ini[i] = &nodes.back();
+    }
+    for (const KeyPt& kp : in) ini[(int)(kp.x / hX)]->keys.push_back(kp);
+
+    auto lit = nodes.begin();
+    while (lit != nodes.end()) {
+        if (lit->keys.size() == 1) { lit->noMore = true; ++lit; }
+        else if (lit->keys.empty()) lit = nodes.erase(lit);
+        else ++lit;
+    }
+
+    bool finish = false;
+    std::vector<SizeNode> sizeAndNode;
+    sizeAndNode.reserve(nodes.size() * 4);
+
+    // children go to the FRONT of the list in the order n1..n4; those with more than one key are recorded
+    auto addChild = [&](Node& c, int* nToExpand) {
+        if (c.keys.empty()) return;
+        nodes.push_front(c);
+        if (c.keys.size() > 1) {
+            if (nToExpand) ++*nToExpand;
+            sizeAndNode.push_back(std::make_pair((int)c.keys.size(), &nodes.front()));
+            nodes.front().lit = nodes.begin();
+        }
+    };
+
+    while (!finish) {
+        int prevSize = (int)nodes.size();
+        lit = nodes.begin();
+        int nToExpand = 0;
+        sizeAndNode.clear();
+        while (lit != nodes.end()) {
+            if (lit->noMore) { ++lit; continue; }
+            Node n1, n2, n3, n4;
+            lit->divide(n1, n2, n3, n4);
+            addChild(n1, &nToExpand);
+            addChild(n2, &nToExpand);
+            addChild(n3, &nToExpand);
+            addChild(n4, &nToExpand);
+            lit = nodes.erase(lit);
+        }
+        if ((int)nodes.size() >= N || (int)nodes.size() == prevSize) {
+            finish = true;
+        } else if (((int)nodes.size() + nToExpand * 3) > N) {
+            while (!finish) {
+                prevSize = (int)nodes.size();
+                std::vector<SizeNode> prev = sizeAndNode;
+                sizeAndNode.clear();
+                std::sort(prev.begin(), prev.end(), compareNodes);    // libstdc++ introsort; ties are unordered
+                for (int j = (int)prev.size() - 1; j >= 0; j--) {
+                    Node n1, n2, n3, n4;
+                    prev[j].second->divide(n1, n2, n3, n4);
+                    addChild(n1, nullptr);
+                    addChild(n2, nullptr);
+                    addChild(n3, nullptr);
+                    addChild(n4, nullptr);
+                    nodes.erase(prev[j].second->lit);
+                    if ((int)nodes.size() >= N) break;
+                }
+                if ((int)nodes.size() >= N || (int)nodes.size() == prevSize) finish = true;
+            }
+        }
+    }
+
+    std::vector<KeyPt> result;
+    result.reserve(nfeatures);
+    for (Node& n : nodes) {
+        const KeyPt* best = &n.keys[0];
+        float maxResponse = best->response;
+        for (size_t k = 1; k < n.keys.size(); k++)
+            if (n.keys[k].response > maxResponse) { best = &n.keys[k]; maxResponse = n.keys[k].response; }
+        result.push_back(*best);
+    }
+    return result;
+}
+
+void orc_extractor::computeKeyPointsOctTree() {    // :783-898
+    const float W = 35;
+    Timer tm;
+    std::vector<XYR> cell;
+    for (int level = 0; level < nlevels; ++level) {
+        Level& L = levels[level];
+        const int minBorderX = kEdge - 3, minBorderY = minBorderX;
+        const int maxBorderX = L.w - kEdge + 3, maxBorderY = L.h - kEdge + 3;
+        std::vector<KeyPt> toDistribute;
+        toDistribute.reserve(nfeatures * 10);
+        const float width = (maxBorderX - minBorderX), height = (maxBorderY - minBorderY);
+        const int nCols = width / W, nRows = height / W;
+        const int wCell = nCols > 0 ? (int)std::ceil(width / nCols) : 0;
+        const int hCell = nRows > 0 ? (int)std::ceil(height / nRows) : 0;
+        for (int i = 0; i < nRows; i++) {
+            const float iniY = minBorderY + i * hCell;
+            float maxY = iniY + hCell + 6;
+            if (iniY >= maxBorderY - 3) continue;
+            if (maxY > maxBorderY) maxY = maxBorderY;
+            for (int j = 0; j < nCols; j++) {
+                const float iniX = minBorderX + j * wCell;
+                float maxX = iniX + wCell + 6;
+                if (iniX >= maxBorderX - 6) continue;
+                if (maxX > maxBorderX) maxX = maxBorderX;
+                const int y0 = (int)iniY, y1 = (int)maxY, x0 = (int)iniX, x1 = (int)maxX;
+                const uint8_t* sub = L.roi() + (size_t)y0 * L.pw + x0;
+                fast9Nms(sub, x1 - x0, y1 - y0, L.pw, iniTh, cell);
+                if (cell.empty()) fast9Nms(sub, x1 - x0, y1 - y0, L.pw, minTh, cell);
+                for (const XYR& c : cell) {
+                    KeyPt kp;
+                    kp.x = (float)c.x; kp.y = (float)c.y; kp.size = 7.f; kp.angle = -1; kp.response = (float)c.r;
+                    kp.x += j * wCell;
+                    kp.y += i * hCell;
+                    toDistribute.push_back(kp);
+                    L.candidates.push_back({(int)kp.x, (int)kp.y, c.r});
+                }
+            }
+        }
+        stage[1] += tm.lap();
+        g_sortTies = 0;
+        L.keypoints = (nCols > 0 && nRows > 0 && maxBorderX > minBorderX && maxBorderY > minBorderY)
+                          ? distributeOctTree(toDistribute, minBorderX, maxBorderX, minBorderY, maxBorderY,
+                                              featuresPerLevel[level])
+                          : std::vector<KeyPt>();
+        sortTies += g_sortTies;
+        const int scaledPatchSize = kPatch * scale[level];
+        for (KeyPt& kp : L.keypoints) {
+            kp.x += minBorderX;
+            kp.y += minBorderY;
+            kp.octave = level;
+            kp.size = scaledPatchSize;
+        }
+        stage[2] += tm.lap();
+    }
+    // computeOrientation -> IC_Angle (:78-105), on the unblurred level
+    for (int level = 0; level < nlevels; ++level) {
+        Level& L = levels[level];
+        const int step = L.pw;
+        for (KeyPt& kp : L.keypoints) {
+            int m_01 = 0, m_10 = 0;
+            const uint8_t* center = L.roi() + (size_t)cvRoundF(kp.y) * step + cvRoundF(kp.x);
+            for (int u = -kHalfPatch; u <= kHalfPatch; ++u) m_10 += u * center[u];
+            for (int v = 1; v <= kHalfPatch; ++v) {
+                int v_sum = 0, d = umax[v];
+                for (int u = -d; u <= d; ++u) {
+                    int val_plus = center[u + v * step], val_minus = center[u - v * step];
+                    v_sum += (val_plus - val_minus);
+                    m_10 += u * (val_plus + val_minus);
+                }
+                m_01 += v * v_sum;
+            }
+            kp.angle = fastAtan2f((float)m_01, (float)m_10);
+        }
+    }
+    stage[3] += tm.lap();
+}
+
+int orc_extractor::run(const uint8_t* img, int w, int h, int stride, int lap0, int lap1, orc_keypoint* kps,
+                       uint8_t* desc, int cap, int* count) {    // :1088-1191
+    if (!img || w <= 0 || h <= 0) { if (count) *count = 0; return -1; }
+    sortTies = 0;
+    Timer tm;
+    computePyramid(img, w, h, stride);
+    stage[0] += tm.lap();
+    computeKeyPointsOctTree();
+    tm.lap();
+
+    int nkeypoints = 0;
+    for (int level = 0; level < nlevels; ++level) nkeypoints += (int)levels[level].keypoints.size();
+    if (count) *count = nkeypoints;
+    std::vector<KeyPt> outK(nkeypoints);
+    std::vector<uint8_t> outD((size_t)nkeypoints * 32);
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    int monoIndex = 0, stereoIndex = nkeypoints - 1;
+    for (int level = 0; level < nlevels; ++level) {
+        Level& L = levels[level];
+        if (L.keypoints.empty()) continue;
+        // GaussianBlur(mvImagePyramid[level].clone(), 7x7, 2, 2, BORDER_REFLECT_101): the clone drops the frame
+        L.blurred.resize((size_t)L.w * L.h);
+        gaussian7x7U8(L.roi(), L.w, L.h, L.pw, L.blurred.data(), L.w);
+        stage[4] += tm.lap();
+        std::vector<uint8_t> d((size_t)L.keypoints.size() * 32);
+        const int step = L.w;
+        for (size_t i = 0; i < L.keypoints.size(); i++) {    // computeOrbDescriptor :109-148
+            const KeyPt& kp = L.keypoints[i];
+            float angle = (float)kp.angle * factorPI;
+            // the reference calls cos/sin on a float (cosf/sinf); evaluated here in double and rounded to float
+            // so that host libm and the CUDA math library agree (DESIGN.md "Floating point").
+            float a = (float)std::cos((double)angle), b = (float)std::sin((double)angle);
+            const uint8_t* center = &L.blurred[(size_t)cvRoundF(kp.y) * step + cvRoundF(kp.x)];
+            const Pt2i* p = pattern;
+            uint8_t* o = &d[i * 32];
+            for (int k = 0; k < 32; ++k, p += 16) {
+                int val = 0;
+                for (int bit = 0; bit < 8; bit++) {
+                    const Pt2i& p0 = p[2 * bit];
+                    const Pt2i& p1 = p[2 * bit + 1];
+                    int t0 = center[cvRoundF(p0.x * b + p0.y * a) * step + cvRoundF(p0.x * a - p0.y * b)];
+                    int t1 = center[cvRoundF(p1.x * b + p1.y * a) * step + cvRoundF(p1.x * a - p1.y * b)];
+                    val |= (t0 < t1) << bit;
+                }
+                o[k] = (uint8_t)val;
+            }
+        }
+        stage[5] += tm.lap();
+        float s = scale[level];
+        int i = 0;
+        for (KeyPt kp : L.keypoints) {
+            if (level != 0) { kp.x *= s; kp.y *= s; }
+            int dst;
+            if (kp.x >= lap0 && kp.x <= lap1) dst = stereoIndex--; else dst = monoIndex++;
+            outK[dst] = kp;
+            std::memcpy(&outD[(size_t)dst * 32], &d[(size_t)i * 32], 32);
+            i++;
+        }
+        stage[6] += tm.lap();
+    }
+    int ncopy = std::min(nkeypoints, cap);
+    for (int i = 0; i < ncopy; i++) {
+        const KeyPt& k = outK[i];
+        if (kps) kps[i] = {k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id};
+    }
+    if (desc && ncopy > 0) std::memcpy(desc, outD.data(), (size_t)ncopy * 32);
+    return monoIndex;
+}
+
+// ---- C interface -----------------------------------------------------------------------------------------------
+extern "C" {
+
+void orc_resize_linear_u8(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride) {
+    resizeLinearU8(src, sw, sh, sstride, dst, dw, dh, dstride);
+}
+void orc_border_reflect101_u8(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride, int border) {
+    borderReflect101(src, w, h, sstride, dst, dstride, border);
+}
+void orc_gaussian7x7_u8(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride) {
+    gaussian7x7U8(src, w, h, sstride, dst, dstride);
+}
+int orc_fast9_nms(const uint8_t* img, int w, int h, int stride, int threshold, int* out_xyr, int cap) {
+    std::vector<XYR> v;
+    fast9Nms(img, w, h, stride, threshold, v);
+    for (int i = 0; i < (int)v.size() && i < cap; i++) {
+        out_xyr[3 * i] = v[i].x; out_xyr[3 * i + 1] = v[i].y; out_xyr[3 * i + 2] = v[i].r;
+    }
+    return (int)v.size();
+}
+float orc_fast_atan2(float y, float x) { return fastAtan2f(y, x); }
+
+void orc_knn2_hamming(const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt, int32_t* idx, int32_t* dist,
+                      int threads) {
+    if (threads <= 1 || nq < 2 * threads) { knn2Range(q, 0, nq, t, nt, idx, dist); return; }
+    std::vector<std::thread> pool;
+    std::atomic<int64_t> next(0);
+    const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(256, nq / (threads * 4)));
+    for (int k = 0; k < threads; k++)
+        pool.emplace_back([&] {
+            for (;;) {
+                int64_t a = next.fetch_add(chunk);
+                if (a >= nq) break;
+                knn2Range(q, a, std::min(nq, a + chunk), t, nt, idx, dist);
+            }
+        });
+    for (auto& th : pool) th.join();
+}
+
+orc_extractor* orc_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th) {
+    if (nlevels < 1 || nlevels > 64 || nfeatures < 0) return nullptr;
+    return new orc_extractor(nfeatures, scale_factor, nlevels, ini_th, min_th);
+}
+void orc_extractor_destroy(orc_extractor* e) { delete e; }
+void orc_extractor_tables(const orc_extractor* e, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                          int* features_per_level, int* umax) {
+    for (int i = 0; i < e->nlevels; i++) {
+        if (scale) scale[i] = e->scale[i];
+        if (inv_scale) inv_scale[i] = e->invScale[i];
+        if (sigma2) sigma2[i] = e->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = e->invSigma2[i];
+        if (features_per_level) features_per_level[i] = e->featuresPerLevel[i];
+    }
+    if (umax) for (int i = 0; i < 16; i++) umax[i] = e->umax[i];
+}
+int orc_extract(orc_extractor* e, const uint8_t* img, int w, int h, int stride, int lap0, int lap1,
+                orc_keypoint* kps, uint8_t* desc, int cap, int* count) {
+    return e->run(img, w, h, stride, lap0, lap1, kps, desc, cap, count);
+}
+void orc_level_size(const orc_extractor* e, int level, int* w, int* h) {
+    *w = e->levels[level].w; *h = e->levels[level].h;
+}
+void orc_level_pixels(const orc_extractor* e, int level, uint8_t* dst, int dstride) {
+    const auto& L = e->levels[level];
+    for (int y = 0; y < L.h; y++) std::memcpy(dst + (size_t)y * dstride, L.roi() + (size_t)y * L.pw, L.w);
+}
+void orc_level_padded(const orc_extractor* e, int level, uint8_t* dst, int dstride) {
+    const auto& L = e->levels[level];
+    for (int y = 0; y < L.h + 2 * kEdge; y++) std::memcpy(dst + (size_t)y * dstride, &L.padded[(size_t)y * L.pw], L.pw);
+}
+void orc_level_blurred(const orc_extractor* e, int level, uint8_t* dst, int dstride) {
+    const auto& L = e->levels[level];
+    for (int y = 0; y < L.h; y++) {
+        if (L.blurred.empty()) std::memset(dst + (size_t)y * dstride, 0, L.w);
+        else std::memcpy(dst + (size_t)y * dstride, &L.blurred[(size_t)y * L.w], L.w);
+    }
+}
+int orc_level_candidates(const orc_extractor* e, int level, int* out_xyr, int cap) {
+    const auto& c = e->levels[level].candidates;
+    for (int i = 0; i < (int)c.size() && i < cap; i++) {
+        out_xyr[3 * i] = c[i].x; out_xyr[3 * i + 1] = c[i].y; out_xyr[3 * i + 2] = c[i].r;
+    }
+    return (int)c.size();
+}
+int orc_level_keypoints(const orc_extractor* e, int level, orc_keypoint* out, int cap) {
+    const auto& k = e->levels[level].keypoints;
+    for (int i = 0; i < (int)k.size() && i < cap; i++)
+        out[i] = {k[i].x, k[i].y, k[i].size, k[i].angle, k[i].response, k[i].octave, k[i].class_id};
+    return (int)k.size();
+}
+void orc_extractor_stage_seconds(const orc_extractor* e, double out[7]) {
+    for (int i = 0; i < 7; i++) out[i] = e->stage[i];
+}
+int64_t orc_extractor_sort_ties(const orc_extractor* e) { return e->sortTies; }
+
+int orc_extract_batch(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, const uint8_t* imgs,
+                      int n, int w, int h, int stride, int lap0, int lap1, orc_keypoint* kps, uint8_t* desc, int cap,
+                      int* counts, int* monos, int threads) {
+    if (threads < 1) threads = 1;
+    std::atomic<int> next(0);
+    auto work = [&] {
+        orc_extractor e(nfeatures, scale_factor, nlevels, ini_th, min_th);
+        for (;;) {
+            int i = next.fetch_add(1);
+            if (i >= n) break;
+            int cnt = 0;
+            int mono = e.run(imgs + (size_t)i * h * stride, w, h, stride, lap0, lap1,
+                             kps ? kps + (size_t)i * cap : nullptr, desc ? desc + (size_t)i * cap * 32 : nullptr, cap,
+                             &cnt);
+            if (counts) counts[i] = cnt;
+            if (monos) monos[i] = mono;
+        }
+    };
+    if (threads == 1) { work(); return 0; }
+    std::vector<std::thread> pool;
+    for (int k = 0; k < threads; k++) pool.emplace_back(work);
+    for (auto& th : pool) th.join();
+    return 0;
+}
+
+int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
+
+}  // extern "C"

@@ -1,0 +1,78 @@
+/* orb_oracle.h — C interface of the CPU ORACLE (test infrastructure, NOT product code).
+ *
+ * Dependency-free C++ restatement of the reference's CPU ORB front-end
+ * (app/src/main/cpp/src/ORBextractor_old.cc + the OpenCV 4.x primitives it calls) and of the
+ * Frame.cc brute-force Hamming matcher.  Only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs may load this library.  The product (liborbfe.so) never does.
+ *
+ * Parity status: the reference ships no golden vectors for this path ("parity unpinned" by the
+ * reference itself).  The restated primitives are pinned against the genuine OpenCV
+ * build in this container (cv2 4.13.0) by tests/test_oracle_vs_cv2.py and by the committed
+ * fixtures in tests/golden/ that oracle/gen_golden.py produced from cv2.
+ */
+#ifndef ORB_ORACLE_H
+#define ORB_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* cv::KeyPoint memory layout (7 x 4 bytes). */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orc_keypoint;
+
+/* ---- primitives (each restates one OpenCV call of the reference path) ---- */
+/* cv::resize(..., INTER_LINEAR) on CV_8UC1 (ORBextractor_old.cc:1344). */
+void orc_resize_linear_u8(const uint8_t* src, int sw, int sh, int sstride,
+                          uint8_t* dst, int dw, int dh, int dstride);
+/* cv::copyMakeBorder(..., BORDER_REFLECT_101) (ORBextractor_old.cc:1346-1352). dst is (w+2b) x (h+2b). */
+void orc_border_reflect101_u8(const uint8_t* src, int w, int h, int sstride,
+                              uint8_t* dst, int dstride, int border);
+/* cv::GaussianBlur(src, dst, Size(7,7), 2, 2, BORDER_REFLECT_101) on CV_8UC1 (ORBextractor_old.cc:1147). */
+void orc_gaussian7x7_u8(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride);
+/* cv::FAST(img, kps, threshold, true) TYPE_9_16 (ORBextractor_old.cc:828,845). out_xyr = triples
+ * (x, y, response) in OpenCV output order; returns the number found (may exceed cap; only cap are written). */
+int orc_fast9_nms(const uint8_t* img, int w, int h, int stride, int threshold, int* out_xyr, int cap);
+/* cv::fastAtan2(y, x), degrees in [0,360). */
+float orc_fast_atan2(float y, float x);
+/* cv::BFMatcher(NORM_HAMMING).knnMatch(query, train, k=2) (Frame.cc:45,1227).  idx/dist hold 2 entries per
+ * query (best, second); missing neighbours (nt < 2) are idx = -1, dist = -1.  threads <= 1 runs single-threaded. */
+void orc_knn2_hamming(const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt,
+                      int32_t* idx, int32_t* dist, int threads);
+
+/* ---- the extractor (ORBextractor_old.cc:411-471 ctor, :1088-1191 operator()) ---- */
+typedef struct orc_extractor orc_extractor;
+orc_extractor* orc_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th);
+void orc_extractor_destroy(orc_extractor*);
+/* ctor tables; out arrays hold nlevels entries (umax: 16). */
+void orc_extractor_tables(const orc_extractor*, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                          int* features_per_level, int* umax);
+/* operator()(image, mask, keypoints, descriptors, vLappingArea): returns monoIndex, or -1 for an empty image.
+ * kps/desc must hold cap entries; *count receives the true keypoint count. */
+int orc_extract(orc_extractor*, const uint8_t* img, int w, int h, int stride, int lap0, int lap1,
+                orc_keypoint* kps, uint8_t* desc, int cap, int* count);
+/* intermediates of the LAST orc_extract call on this object (for stage-by-stage parity). */
+void orc_level_size(const orc_extractor*, int level, int* w, int* h);
+void orc_level_pixels(const orc_extractor*, int level, uint8_t* dst, int dstride);          /* w x h ROI      */
+void orc_level_padded(const orc_extractor*, int level, uint8_t* dst, int dstride);          /* (w+38)x(h+38)  */
+void orc_level_blurred(const orc_extractor*, int level, uint8_t* dst, int dstride);         /* 0 if level had no kp */
+int  orc_level_candidates(const orc_extractor*, int level, int* out_xyr, int cap);          /* pre-octree, rel. to (16,16) */
+int  orc_level_keypoints(const orc_extractor*, int level, orc_keypoint* out, int cap);      /* post-octree + angle, level coords */
+/* per-stage seconds accumulated since create: pyramid, fast, octree, angle, blur, desc, pack */
+void orc_extractor_stage_seconds(const orc_extractor*, double out[7]);
+/* number of compareNodes ties (equal count and UL.x, different node) seen by std::sort in the last call */
+int64_t orc_extractor_sort_ties(const orc_extractor*);
+
+/* n images (contiguous, each h*stride bytes) over `threads` std::threads; outputs strided by cap.
+ * returns 0.  counts[i], monos[i] per image. */
+int orc_extract_batch(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th,
+                      const uint8_t* imgs, int n, int w, int h, int stride, int lap0, int lap1,
+                      orc_keypoint* kps, uint8_t* desc, int cap, int* counts, int* monos, int threads);
+
+int orc_hardware_threads(void);
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,228 @@
+"""ctypes binding of the CPU ORACLE (oracle/_build/liborb_oracle.so).
+
+Test infrastructure only: imported by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs.
+Nothing under orbslam3lib_b200/ imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ORACLE_DIR = os.path.dirname(_HERE)
+_SO = os.path.join(_ORACLE_DIR, "_build", "liborb_oracle.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+def build(force=False):
+    """Compile the oracle with g++ (oracle/Makefile). Building the checker is not using it."""
+    if force or not os.path.exists(_SO) or any(
+            os.path.getmtime(os.path.join(_ORACLE_DIR, "cpp", f)) > os.path.getmtime(_SO)
+            for f in ("orb_oracle.cpp", "orb_oracle.h")):
+        subprocess.check_call(["make", "-C", _ORACLE_DIR, "-s"] + (["-B"] if force else []))
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = C.CDLL(_SO)
+        u8p, i32p, f32p = C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_float)
+        L.orc_resize_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.orc_border_reflect101_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        L.orc_gaussian7x7_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_fast9_nms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_fast9_nms.restype = C.c_int
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_knn2_hamming.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_extractor_create.restype = C.c_void_p
+        L.orc_extractor_destroy.argtypes = [C.c_void_p]
+        L.orc_extractor_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        L.orc_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                  C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_extract.restype = C.c_int
+        L.orc_level_size.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        for name in ("orc_level_pixels", "orc_level_padded", "orc_level_blurred"):
+            getattr(L, name).argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.orc_level_candidates.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.orc_level_candidates.restype = C.c_int
+        L.orc_level_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.orc_level_keypoints.restype = C.c_int
+        L.orc_extractor_stage_seconds.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_extractor_sort_ties.argtypes = [C.c_void_p]
+        L.orc_extractor_sort_ties.restype = C.c_int64
+        L.orc_extract_batch.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                        C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                        C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_extract_batch.restype = C.c_int
+        L.orc_hardware_threads.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(img):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    assert img.ndim == 2
+    return img
+
+
+def resize_linear(img, dw, dh):
+    img = _u8(img)
+    out = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_linear_u8(_p(img), img.shape[1], img.shape[0], img.strides[0], _p(out), dw, dh, dw)
+    return out
+
+
+def border_reflect101(img, border=19):
+    img = _u8(img)
+    h, w = img.shape
+    out = np.empty((h + 2 * border, w + 2 * border), np.uint8)
+    lib().orc_border_reflect101_u8(_p(img), w, h, img.strides[0], _p(out), out.strides[0], border)
+    return out
+
+
+def gaussian7x7(img):
+    img = _u8(img)
+    out = np.empty_like(img)
+    lib().orc_gaussian7x7_u8(_p(img), img.shape[1], img.shape[0], img.strides[0], _p(out), out.strides[0])
+    return out
+
+
+def fast9_nms(img, threshold):
+    """-> int32 array (n, 3) of (x, y, response) in OpenCV order."""
+    img = _u8(img)
+    cap = max(16, img.size // 4 + 16)
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orc_fast9_nms(_p(img), img.shape[1], img.shape[0], img.strides[0], int(threshold), _p(out), cap)
+    return out[:n].copy()
+
+
+def fast_atan2(y, x):
+    return float(lib().orc_fast_atan2(float(y), float(x)))
+
+
+def knn2_hamming(q, t, threads=1):
+    """-> (idx int32 (nq,2), dist int32 (nq,2)); OpenCV BFMatcher(NORM_HAMMING).knnMatch(k=2) semantics."""
+    q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
+    t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+    idx = np.empty((q.shape[0], 2), np.int32)
+    dist = np.empty((q.shape[0], 2), np.int32)
+    lib().orc_knn2_hamming(_p(q), q.shape[0], _p(t), t.shape[0], _p(idx), _p(dist), int(threads))
+    return idx, dist
+
+
+class OracleExtractor:
+    """ORB_SLAM3::ORBextractor (ORBextractor_old.cc) restated on the CPU."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.args = (int(nfeatures), float(scale_factor), int(nlevels), int(ini_th), int(min_th))
+        self.nfeatures, self.nlevels = int(nfeatures), int(nlevels)
+        self._h = lib().orc_extractor_create(*self.args)
+        if not self._h:
+            raise ValueError("bad extractor parameters")
+        n = self.nlevels
+        self.scale = np.empty(n, np.float32)
+        self.inv_scale = np.empty(n, np.float32)
+        self.sigma2 = np.empty(n, np.float32)
+        self.inv_sigma2 = np.empty(n, np.float32)
+        self.features_per_level = np.empty(n, np.int32)
+        self.umax = np.empty(16, np.int32)
+        lib().orc_extractor_tables(self._h, _p(self.scale), _p(self.inv_scale), _p(self.sigma2), _p(self.inv_sigma2),
+                                   _p(self.features_per_level), _p(self.umax))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_extractor_destroy(self._h)
+            self._h = None
+
+    def __call__(self, img, lapping=(0, 0)):
+        """-> (mono_index, keypoints[KP_DTYPE], descriptors uint8 (n,32))"""
+        img = _u8(img)
+        cap = self.nfeatures + 4 * self.nlevels + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        cnt = C.c_int(0)
+        mono = lib().orc_extract(self._h, _p(img), img.shape[1], img.shape[0], img.strides[0], int(lapping[0]),
+                                 int(lapping[1]), _p(kps), _p(desc), cap, C.byref(cnt))
+        n = cnt.value
+        assert n <= cap
+        return mono, kps[:n].copy(), desc[:n].copy()
+
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        lib().orc_level_size(self._h, level, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def level_pixels(self, level):
+        w, h = self.level_size(level)
+        out = np.empty((h, w), np.uint8)
+        lib().orc_level_pixels(self._h, level, _p(out), w)
+        return out
+
+    def level_padded(self, level):
+        w, h = self.level_size(level)
+        out = np.empty((h + 38, w + 38), np.uint8)
+        lib().orc_level_padded(self._h, level, _p(out), w + 38)
+        return out
+
+    def level_blurred(self, level):
+        w, h = self.level_size(level)
+        out = np.empty((h, w), np.uint8)
+        lib().orc_level_blurred(self._h, level, _p(out), w)
+        return out
+
+    def level_candidates(self, level):
+        w, h = self.level_size(level)
+        cap = w * h // 4 + 64
+        out = np.empty((cap, 3), np.int32)
+        n = lib().orc_level_candidates(self._h, level, _p(out), cap)
+        return out[:n].copy()
+
+    def level_keypoints(self, level):
+        cap = self.nfeatures + 64
+        out = np.zeros(cap, KP_DTYPE)
+        n = lib().orc_level_keypoints(self._h, level, _p(out), cap)
+        return out[:n].copy()
+
+    def stage_seconds(self):
+        out = np.zeros(7, np.float64)
+        lib().orc_extractor_stage_seconds(self._h, _p(out))
+        return dict(zip(("pyramid", "fast", "octree", "angle", "blur", "desc", "pack"), out.tolist()))
+
+    def sort_ties(self):
+        return int(lib().orc_extractor_sort_ties(self._h))
+
+
+def extract_batch(imgs, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, lapping=(0, 0), threads=1,
+                  want_outputs=True):
+    """imgs uint8 (n,h,w) -> (counts, monos, kps (n,cap), desc (n,cap,32)); frames spread over std::threads."""
+    imgs = np.ascontiguousarray(imgs, np.uint8)
+    n, h, w = imgs.shape
+    cap = int(nfeatures) + 4 * int(nlevels) + 64
+    counts = np.zeros(n, np.int32)
+    monos = np.zeros(n, np.int32)
+    kps = np.zeros((n, cap), KP_DTYPE) if want_outputs else None
+    desc = np.zeros((n, cap, 32), np.uint8) if want_outputs else None
+    lib().orc_extract_batch(int(nfeatures), float(scale_factor), int(nlevels), int(ini_th), int(min_th), _p(imgs), n, w,
+                            h, w, int(lapping[0]), int(lapping[1]), _p(kps) if want_outputs else None,
+                            _p(desc) if want_outputs else None, cap, _p(counts), _p(monos), int(threads))
+    return counts, monos, kps, desc
+
+
+def hardware_threads():
+    return int(lib().orc_hardware_threads())

@@ -1,0 +1,121 @@
+"""Seeded synthetic scenes for parity tests and the benchmark.
+
+Everything derives from a splitmix64 counter hash, so a scene is a pure function of (kind, w, h, seed).
+The reference has no fixtures for this path (dsp/debug_scripts/prepare_input.py:16-17 names two PNGs that are
+not in the repo), so these scenes are the shared inputs of the oracle and of the CUDA path.
+"""
+import numpy as np
+
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def splitmix64(idx, seed):
+    """Counter-based hash: element `idx` (array of uint64) of stream `seed` -> uint64."""
+    with np.errstate(over="ignore"):
+        z = np.asarray(idx, dtype=np.uint64) + np.uint64((int(seed) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return z
+
+
+def rand_u8(n, seed, offset=0):
+    return (splitmix64(np.arange(offset, offset + n, dtype=np.uint64), seed) >> np.uint64(56)).astype(np.uint8)
+
+
+def rand_u32(n, seed, offset=0):
+    return (splitmix64(np.arange(offset, offset + n, dtype=np.uint64), seed) >> np.uint64(32)).astype(np.uint32)
+
+
+def noise(w, h, seed):
+    return rand_u8(w * h, seed).reshape(h, w)
+
+
+def _signed_noise(w, h, seed, amp):
+    r = rand_u8(w * h, seed ^ 0x5EED).reshape(h, w).astype(np.int32)
+    return r % (2 * amp + 1) - amp
+
+
+def checker(w, h, seed, period=16, amp=8):
+    yy, xx = np.mgrid[0:h, 0:w]
+    base = np.where(((xx // period) + (yy // period)) % 2 == 0, 64, 192).astype(np.int32)
+    return np.clip(base + _signed_noise(w, h, seed, amp), 0, 255).astype(np.uint8)
+
+
+def _box3(img):
+    p = np.pad(img.astype(np.int32), 1, mode="edge")
+    s = sum(p[dy:dy + img.shape[0], dx:dx + img.shape[1]] for dy in range(3) for dx in range(3))
+    return ((s + 4) // 9).astype(np.uint8)
+
+
+def _rects(w, h, seed, n, base, smooth):
+    img = np.full((h, w), base, np.uint8)
+    r = rand_u32(5 * n, seed)
+    for i in range(n):
+        x0 = int(r[5 * i] % w)
+        y0 = int(r[5 * i + 1] % h)
+        rw = 4 + int(r[5 * i + 2] % max(8, w // 6))
+        rh = 4 + int(r[5 * i + 3] % max(8, h // 6))
+        img[y0:y0 + rh, x0:x0 + rw] = r[5 * i + 4] & 0xFF
+    return _box3(img) if smooth else img
+
+
+def texture(w, h, seed):
+    """Random gray rectangles painted in seed order, then a 3x3 box filter: multi-scale corners, some empty cells."""
+    n = max(8, int(round(400.0 * (w * h) / 360960.0)))
+    return _rects(w, h, seed, n, 128, True)
+
+
+def flat_blobs(w, h, seed):
+    """Constant 128 with 20 rectangles: mostly empty FAST cells (minThFAST fallback, levels with < N candidates)."""
+    return _rects(w, h, seed, 20, 128, False)
+
+
+def stereo_right(left, seed):
+    """Right view: row y shifted left by the integer disparity d(y) = 4 + (y mod 37), edge replicated, noise +-2."""
+    h, w = left.shape
+    yy, xx = np.mgrid[0:h, 0:w]
+    src = np.clip(xx + (4 + (yy % 37)), 0, w - 1)
+    out = left[yy, src].astype(np.int32) + _signed_noise(w, h, seed ^ 0xA11CE, 2)
+    return np.clip(out, 0, 255).astype(np.uint8)
+
+
+def previous_frame(cur, seed):
+    """Previous frame of C1: the current frame shifted by (+3, +2) px, edge replicated, noise +-2."""
+    h, w = cur.shape
+    yy, xx = np.mgrid[0:h, 0:w]
+    out = cur[np.clip(yy - 2, 0, h - 1), np.clip(xx - 3, 0, w - 1)].astype(np.int32)
+    return np.clip(out + _signed_noise(w, h, seed ^ 0xB0B, 2), 0, 255).astype(np.uint8)
+
+
+SCENES = {"noise": noise, "checker": checker, "texture": texture, "flat_blobs": flat_blobs}
+
+
+def make(kind, w, h, seed):
+    return np.ascontiguousarray(SCENES[kind](w, h, seed))
+
+
+def descriptors(n, seed):
+    """n iid 256-bit descriptors, uint8 (n, 32)."""
+    return rand_u8(n * 32, seed).reshape(n, 32)
+
+
+def map_descriptors(nq, nt, seed, max_flips=40, dup_frac=0.01):
+    """C5 workload: train iid (1 % of the rows duplicated verbatim -> exact ties), query i = a train row with
+    0..max_flips random bit flips.  Returns (query, train)."""
+    train = descriptors(nt, seed)
+    ndup = int(nt * dup_frac)
+    if ndup > 0 and nt > 1:
+        src = (rand_u32(ndup, seed + 1) % np.uint32(nt)).astype(np.int64)
+        dst = (rand_u32(ndup, seed + 2) % np.uint32(nt)).astype(np.int64)
+        train[dst] = train[src]
+    pick = (rand_u32(nq, seed + 3) % np.uint32(nt)).astype(np.int64)
+    query = train[pick].copy()
+    nflip = (rand_u32(nq, seed + 4) % np.uint32(max_flips + 1)).astype(np.int64)
+    pos = (rand_u32(nq * max_flips, seed + 5) % np.uint32(256)).reshape(nq, max_flips).astype(np.int64)
+    for k in range(max_flips):
+        m = nflip > k
+        rows = np.nonzero(m)[0]
+        p = pos[rows, k]
+        query[rows, p >> 3] ^= (1 << (p & 7)).astype(np.uint8)
+    return query, train
