@@ -1,0 +1,159 @@
+/* orbfe_c.h — C ABI of liborbfe.so, the B200 (sm_100a) ORB front-end.
+ *
+ * This is the drop-in boundary.  It stands where the reference has its FastRPC stub
+ * (app/src/main/cpp/inc/orbslam3.idl:14-22, expanded by QAIC to the skel signatures at
+ * dsp/src/orbslam_dsp.cpp:866,931,567,1017) and the rpcmem / AHardwareBuffer plumbing of
+ * LynxHardwareAccelerator.cpp:26-213.  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions:
+ *   - every function returns an int status: 0 = ORBFE_OK, negative = error (never exit()s, never throws);
+ *     the text of the last error of a handle is available through orbfe_last_error().
+ *   - the caller owns every buffer; capacities are passed explicitly and the true counts are reported.
+ *   - calls on one handle are serialised by an internal mutex; distinct handles are independent
+ *     (one CUDA stream + one device workspace each).
+ *   - buffers are host memory unless the corresponding ORBFE_*_DEVICE flag says otherwise.  Pinned host
+ *     memory makes the copies asynchronous; pageable memory works but is slower.
+ *   - there is no CPU fallback: without a CUDA device every entry point fails with ORBFE_ERR_CUDA.
+ */
+#ifndef ORBFE_C_H
+#define ORBFE_C_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBFE_OK 0
+#define ORBFE_ERR_ARG (-1)      /* bad argument (null pointer, non-positive size, too many levels, ...) */
+#define ORBFE_ERR_CAPACITY (-2) /* an output capacity was too small; counts hold the true sizes */
+#define ORBFE_ERR_CUDA (-3)     /* CUDA runtime error; see orbfe_last_error() */
+#define ORBFE_ERR_NCCL (-4)     /* NCCL error in the sharded matcher */
+#define ORBFE_ERR_INTERNAL (-5) /* internal invariant violated (reported, never ignored) */
+
+#define ORBFE_MAX_LEVELS 16
+
+/* flags */
+#define ORBFE_IN_DEVICE 1u  /* input pointers are device memory of the handle's GPU */
+#define ORBFE_OUT_DEVICE 2u /* output pointers are device memory of the handle's GPU */
+
+/* cv::KeyPoint memory layout (pt.x, pt.y, size, angle, response, octave, class_id) — 28 bytes. */
+typedef struct orbfe_keypoint {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbfe_keypoint;
+
+/* Arguments of ORB_SLAM3::ORBextractor::ORBextractor (include/ORBextractor.h:38-39, ORBextractor_old.cc:411-415). */
+typedef struct orbfe_params {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;
+    int32_t ini_th_fast;
+    int32_t min_th_fast;
+} orbfe_params;
+
+typedef struct orbfe_extractor orbfe_extractor; /* opaque: params + stream + device workspace */
+typedef struct orbfe_matcher orbfe_matcher;     /* opaque: stream + device workspace */
+
+/* ---- library ---- */
+const char* orbfe_version(void);
+/* number of visible CUDA devices (0 when there is none; the library then cannot compute anything). */
+int orbfe_device_count(void);
+/* kernels launched by this library in this process so far (bench.py's gpu_launches). */
+uint64_t orbfe_kernel_launches(void);
+
+/* ---- extractor: replaces ORBextractor's ctor + LynxHardwareAccelerator ctor (LHA:26-93) ---- */
+int orbfe_extractor_create(int device, const orbfe_params* params, orbfe_extractor** out);
+int orbfe_extractor_destroy(orbfe_extractor* ex);
+const char* orbfe_last_error(const orbfe_extractor* ex);
+/* upper bound on device workspace (bytes) the extractor may hold; batches are processed in chunks that fit.
+ * Default 24 GiB. */
+int orbfe_extractor_set_workspace_limit(orbfe_extractor* ex, size_t bytes);
+/* ctor-derived tables (ORBextractor_old.cc:416-470; getters of include/ORBextractor.h:61-82).  Each array holds
+ * nlevels entries (umax: 16); null pointers are skipped. */
+int orbfe_extractor_tables(const orbfe_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                           int32_t* features_per_level, int32_t* umax);
+/* max keypoints one image can produce with these params: the size to give `cap` below. */
+int orbfe_extractor_max_keypoints(const orbfe_extractor* ex);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors, vLappingArea) (include/ORBextractor_old.h:59-61,
+ * ORBextractor_old.cc:1088-1191) over a batch of n equally sized CV_8UC1 images.
+ *   images       image i starts at images + i*image_stride bytes; rows are `stride` bytes apart
+ *   lap0,lap1    vLappingArea; keypoints with lap0 <= x <= lap1 are packed from the back ("stereo"), the others
+ *                from the front ("mono"), ORBextractor_old.cc:1171-1180
+ *   kps, desc    image i writes kps[i*cap ...] and desc[(i*cap ...)*32]; cap = per-image capacity
+ *   counts[i]    keypoints found in image i (true count, even when > cap -> ORBFE_ERR_CAPACITY)
+ *   monos[i]     the operator's return value (monoIndex); -1 for an empty image
+ */
+int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int width, int height, int stride,
+                        size_t image_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                        int32_t* counts, int32_t* monos, unsigned flags);
+/* single image convenience == ORBextractor::operator(); returns monoIndex through *mono. */
+int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int width, int height, int stride, int lap0, int lap1,
+                  orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* count, int32_t* mono);
+
+/* Stage outputs of image `index` of the LAST orbfe_extract* call on this extractor (parity tests; mvImagePyramid
+ * readers such as Frame.cc:834,924).  All destinations are host memory. */
+int orbfe_level_size(const orbfe_extractor* ex, int level, int* w, int* h);
+/* which: 0 = level pixels w x h (mvImagePyramid[level] ROI), 1 = padded (w+38) x (h+38), 2 = blurred w x h */
+int orbfe_level_read(orbfe_extractor* ex, int index, int level, int which, uint8_t* dst, int dstride);
+/* pre-octree FAST candidates of a level as (x, y, response) int32 triples relative to (minBorderX, minBorderY),
+ * in the reference's insertion order (ORBextractor_old.cc:865-870).  Returns the count (negative = error). */
+int orbfe_level_candidates(orbfe_extractor* ex, int index, int level, int32_t* out_xyr, int cap);
+/* post-octree keypoints of a level, level coordinates, with angle (ORBextractor_old.cc:879-897). */
+int orbfe_level_keypoints(orbfe_extractor* ex, int index, int level, orbfe_keypoint* out, int cap);
+/* device time (ms) of each stage of the last call, measured with CUDA events:
+ * [0] h2d, [1] pyramid, [2] fast, [3] octree, [4] blur, [5] angle+descriptors+pack, [6] d2h */
+int orbfe_extractor_stage_ms(const orbfe_extractor* ex, float out[7]);
+/* kernels launched by the last call on this extractor */
+int orbfe_extractor_last_launches(const orbfe_extractor* ex);
+
+/* ---- matcher: cv::BFMatcher(NORM_HAMMING).knnMatch(query, train, matches, 2)  (Frame.cc:45,1227) ---- */
+int orbfe_matcher_create(int device, orbfe_matcher** out);
+int orbfe_matcher_destroy(orbfe_matcher* m);
+const char* orbfe_matcher_last_error(const orbfe_matcher* m);
+/* q: nq x 32 bytes, t: nt x 32 bytes, row-major.  idx/dist: 2 entries per query row (best, second best);
+ * equal distances keep the lower train index first (OpenCV's order); missing neighbours (nt < 2) are -1. */
+int orbfe_knn2(orbfe_matcher* m, const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt, int32_t* idx,
+               int32_t* dist, unsigned flags);
+/* npairs independent problems: problem p uses rows [p*q_cap, p*q_cap + nq[p]) of q and [p*t_cap, p*t_cap + nt[p])
+ * of t, and writes idx/dist rows [p*q_cap ...).  nq/nt are host arrays unless ORBFE_IN_DEVICE (then device int32). */
+int orbfe_knn2_batch(orbfe_matcher* m, const uint8_t* q, const int32_t* nq, int q_cap, const uint8_t* t,
+                     const int32_t* nt, int t_cap, int npairs, int32_t* idx, int32_t* dist, unsigned flags);
+/* Lowe ratio test of Frame.cc:1230 on host arrays returned by orbfe_knn2: out[i] = idx[2i] if both neighbours exist
+ * and (float)dist[2i] < (float)dist[2i+1] * ratio (evaluated in double, like the reference's `distance * 0.7`),
+ * else -1.  Pure host code, no arithmetic of the hot path. */
+int orbfe_ratio_test(const int32_t* idx, const int32_t* dist, int64_t nq, double ratio, int32_t* out);
+/* device time (ms) of the kernel(s) of the last call and their launch count */
+int orbfe_matcher_last_ms(const orbfe_matcher* m, float* kernel_ms, int* launches);
+
+/* ---- wire-compatible entry points: the four skel functions of the FastRPC interface ----------------------
+ * Same names, argument order and meaning as dsp/src/orbslam_dsp.cpp:866 (open), :931 (close), :1017-1021
+ * (extractFeatures) and :567 (bfMatchStereo), so LynxHardwareAccelerator.cpp:62,116,146-150 links against
+ * liborbfe.so instead of libcdsprpc + the generated stub.  Differences, all deliberate (SURVEY.md §8a "known
+ * defects"): width/height/stride/threshold are honoured; the image is a side-by-side stereo frame (left eye =
+ * columns [0,width), right eye = columns [width, 2*width), `stride` bytes per row); extraction follows the CPU
+ * semantics of ORBextractor_old.cc with the parameters set by orbslam3_configure (default 1000,1.2,8,20,7; the
+ * `threshold` argument, when > 0, replaces iniThFAST); angles are packed as (int8 sin*64)<<8 | (int8 cos*64)&0xff
+ * (LHA:175-177); counts are the true counts (not count+1); matching is left(query) -> right(train) over the
+ * stereo parts, indices/distances as int16 like the IDL. */
+typedef uint64_t orbfe_remote_handle64;
+int orbslam3_open(const char* uri, orbfe_remote_handle64* h);
+int orbslam3_close(orbfe_remote_handle64 h);
+int orbslam3_configure(orbfe_remote_handle64 h, const orbfe_params* params);
+int orbslam3_extractFeatures(
+    orbfe_remote_handle64 h, const unsigned char* image, int imageLen, int width, int height, int stride, int threshold,
+    int vLappingAreaLeft0, int vLappingAreaLeft1, int vLappingAreaRight0, int vLappingAreaRight1, int* totalPointsLeft,
+    int* leftKeypointsX, int leftKeypointsXLen, int* leftKeypointsY, int leftKeypointsYLen, int* leftKeypointsAngle,
+    int leftKeypointsAngleLen, int* leftKeypointsLevel, int leftKeypointsLevelLen, uint8_t* leftKeypointsORB,
+    int leftKeypointsORBLen, int* totalPointsRight, int* rightKeypointsX, int rightKeypointsXLen, int* rightKeypointsY,
+    int rightKeypointsYLen, int* rightKeypointsAngle, int rightKeypointsAngleLen, int* rightKeypointsLevel,
+    int rightKeypointsLevelLen, uint8_t* rightKeypointsORB, int rightKeypointsORBLen, int* monoLeft, int* monoRight,
+    short* indices, int indicesLen, short* distances1, int distances1Len, short* distances2, int distances2Len);
+int orbslam3_bfMatchStereo(orbfe_remote_handle64 h, const unsigned char* leftDescriptors, int leftDescriptorsLen,
+                           const unsigned char* rightDescriptors, int rightDescriptorsLen, short* indices,
+                           int indicesLen, short* distances1, int distances1Len, short* distances2, int distances2Len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBFE_C_H */

@@ -1,0 +1,228 @@
+// k_describe.cu — the per-keypoint tail of ORBextractor::operator() (ORBextractor_old.cc:1088-1191):
+//   pack_kernel      output row of every keypoint: levels in order, list order inside a level, "mono" keypoints from
+//                    the front and keypoints inside vLappingArea from the back (:1161-1182); monoIndex (:1190)
+//   describe_kernel  IC_Angle (:78-105) on the unblurred level, cv::fastAtan2, computeOrbDescriptor (:109-148) on
+//                    the blurred level, cv::KeyPoint fields (:882-892, :1167-1169), one warp per keypoint
+//
+// Floating point (DESIGN.md "Floating point"): IEEE fp32 with explicit round-to-nearest intrinsics so that nvcc
+// cannot contract a*b+c into an FMA; cos/sin are evaluated in double and rounded to float, exactly like the oracle.
+// These kernels gather from L2 (749 B + 512 B of reads per keypoint) and are not HBM-bound.
+#include <cfloat>
+
+#include "orb_pattern.h"
+#include "orbfe_internal.h"
+
+namespace orbfe {
+
+__constant__ signed char c_pattern[1024];    // 256 x (x0,y0,x1,y1), ORBextractor_old.cc:151-409
+
+void upload_pattern() {
+    static bool done[64] = {false};    // __constant__ memory is per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !done[dev]) {
+        cudaMemcpyToSymbol(c_pattern, ORBFE_BIT_PATTERN_31, 1024);
+        if (dev >= 0 && dev < 64) done[dev] = true;
+    }
+}
+
+constexpr int PK_THREADS = 256;
+
+// grid (n); block PK_THREADS; dynamic shared memory: 2 * (outCap + 1) ints
+__global__ void __launch_bounds__(PK_THREADS) pack_kernel(const __grid_constant__ Geom g, const ExtractBuffers b, int lap0,
+                                                          int lap1) {
+    extern __shared__ int sh[];
+    __shared__ int lvOff[ORBFE_MAX_LEVELS + 1];
+    __shared__ int wsum[PK_THREADS / 32 + 1];
+    const int img = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int* isStereo = sh;
+    if (tid == 0) {
+        int o = 0;
+        for (int l = 0; l < g.nlevels; l++) {
+            lvOff[l] = o;
+            o += min(b.levelCount[(size_t)img * g.nlevels + l], g.lv[l].keyCap);
+        }
+        lvOff[g.nlevels] = o;
+    }
+    __syncthreads();
+    const int nk = lvOff[g.nlevels];
+    const uint32_t* keys = b.levelKeys + (size_t)img * g.keyTotal;
+    KpWork* work = b.work + (size_t)img * g.outCap;
+    const float fl0 = (float)lap0, fl1 = (float)lap1;
+
+    // serial-in-chunks scan: each thread owns a contiguous run of keypoints
+    const int per = (nk + PK_THREADS - 1) / PK_THREADS;
+    const int beg = min(tid * per, nk), end = min(beg + per, nk);
+    int level = 0;
+    while (level < g.nlevels - 1 && beg >= lvOff[level + 1]) level++;
+    int cnt = 0;
+    {
+        int lv = level;
+        for (int i = beg; i < end; i++) {
+            while (i >= lvOff[lv + 1]) lv++;
+            const uint32_t key = keys[g.lv[lv].keyBase + (i - lvOff[lv])];
+            float x = (float)((int)(key & 0xfff) + kMinBorder);
+            if (lv != 0) x = __fmul_rn(x, g.lv[lv].scale);
+            const int st = (x >= fl0 && x <= fl1) ? 1 : 0;
+            isStereo[i] = st;
+            cnt += st;
+        }
+    }
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    int wbase = 0, total = 0;
+    for (int w = 0; w < PK_THREADS / 32; w++) {
+        if (w < warp) wbase += wsum[w];
+        total += wsum[w];
+    }
+    int stereoBefore = wbase + inc - cnt;
+    {
+        int lv = level;
+        for (int i = beg; i < end; i++) {
+            while (i >= lvOff[lv + 1]) lv++;
+            const uint32_t key = keys[g.lv[lv].keyBase + (i - lvOff[lv])];
+            const int st = isStereo[i];
+            KpWork w;
+            w.x = (unsigned short)((key & 0xfff) + kMinBorder);
+            w.y = (unsigned short)(((key >> 12) & 0xfff) + kMinBorder);
+            w.level = (unsigned char)lv;
+            w.response = (unsigned char)(key >> 24);
+            w.pad = 0;
+            w.dst = st ? (nk - 1 - stereoBefore) : (i - stereoBefore);
+            stereoBefore += st;
+            work[i] = w;
+        }
+    }
+    if (tid == 0) b.result[img] = ImageResult{nk, nk - total};
+}
+
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {    // cv::fastAtan2
+    const float scale = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = __fmul_rn(0.9997878412794807f, scale), p3 = __fmul_rn(-0.3258083974640975f, scale);
+    const float p5 = __fmul_rn(0.1555786518463281f, scale), p7 = __fmul_rn(-0.04432655554792128f, scale);
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+constexpr int DS_WARPS = 8;
+
+// grid (ceil(outCap / DS_WARPS), n); block 32 * DS_WARPS
+__global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
+                                                                 orbfe_keypoint* __restrict__ kps,
+                                                                 uint8_t* __restrict__ desc, int cap) {
+    const int img = blockIdx.y, lane = threadIdx.x & 31;
+    const int k = blockIdx.x * DS_WARPS + (threadIdx.x >> 5);
+    if (k >= b.result[img].count) return;
+    const KpWork w = b.work[(size_t)img * g.outCap + k];
+    const LevelGeom& L = g.lv[w.level];
+    const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff + (size_t)(w.y + kEdge) * L.pitch + kXOff + w.x;
+
+    // ---- IC_Angle: m10 = sum u*I, m01 = sum v*I over the radius-15 disc (:78-105); lane = u + 15
+    const uint8_t* c = b.pyr + planeBase;
+    int m10 = 0, m01 = 0;
+    if (lane < 2 * kHalfPatch + 1) {
+        const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+        int colSum = 0;
+#pragma unroll 4
+        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+            if (au <= g.umax[v < 0 ? -v : v]) {
+                const int val = c[v * L.pitch + u];
+                colSum += val;
+                m01 += v * val;
+            }
+        }
+        m10 = u * colSum;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // ---- computeOrbDescriptor (:109-148); lane = output byte
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    const float rad = __fmul_rn(angle, factorPI);
+    const float ca = (float)cos((double)rad), sb = (float)sin((double)rad);
+    const uint8_t* center = b.blur + planeBase;
+    uint32_t byte = 0;
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) {
+        const int pi = (lane * 8 + bit) * 4;
+        const float x0 = (float)c_pattern[pi], y0 = (float)c_pattern[pi + 1];
+        const float x1 = (float)c_pattern[pi + 2], y1 = (float)c_pattern[pi + 3];
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
+        const int t0 = center[r0 * L.pitch + c0], t1 = center[r1 * L.pitch + c1];
+        byte |= (uint32_t)(t0 < t1) << bit;
+    }
+    // 32 bytes -> two 128-bit stores (lanes 0 and 16)
+    uint32_t v = byte | (__shfl_down_sync(0xffffffffu, byte, 1) << 8);
+    v = v | (__shfl_down_sync(0xffffffffu, v, 2) << 16);    // valid in lanes 0,4,8,...
+    const int src = (lane & 16);
+    uint4 q;
+    q.x = __shfl_sync(0xffffffffu, v, src);
+    q.y = __shfl_sync(0xffffffffu, v, src + 4);
+    q.z = __shfl_sync(0xffffffffu, v, src + 8);
+    q.w = __shfl_sync(0xffffffffu, v, src + 12);
+    if (w.dst < cap) {
+        if ((lane & 15) == 0)
+            *reinterpret_cast<uint4*>(desc + ((size_t)img * cap + w.dst) * 32 + (lane >> 4) * 16) = q;
+        // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
+        if (lane < 7) {
+            float fx = (float)w.x, fy = (float)w.y;
+            if (w.level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+            uint32_t word;
+            switch (lane) {
+                case 0: word = __float_as_uint(fx); break;
+                case 1: word = __float_as_uint(fy); break;
+                case 2: word = __float_as_uint((float)L.scaledPatch); break;
+                case 3: word = __float_as_uint(angle); break;
+                case 4: word = __float_as_uint((float)w.response); break;
+                case 5: word = (uint32_t)w.level; break;
+                default: word = 0xffffffffu; break;
+            }
+            reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + w.dst)[lane] = word;
+        }
+    }
+}
+
+int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st) {
+    const size_t smem = sizeof(int) * (size_t)(g.outCap + 1);
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && configured < smem) {
+        cudaFuncSetAttribute(pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+    }
+    pack_kernel<<<n, PK_THREADS, smem, st>>>(g, b, lap0, lap1);
+    return 1;
+}
+
+int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                    cudaStream_t st) {
+    upload_pattern();
+    describe_kernel<<<dim3((g.outCap + DS_WARPS - 1) / DS_WARPS, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
+    return 1;
+}
+
+}    // namespace orbfe

@@ -1,0 +1,1003 @@
+// orbfe_api.cu — the C ABI of liborbfe.so (include/orbfe_c.h): handles, geometry tables, workspace, staging and the
+// launch sequence of ORBextractor::operator() (ORBextractor_old.cc:1088-1191) and of the BFMatcher kNN (Frame.cc:1227).
+// Host side only; the arithmetic lives in the k_*.cu kernels.  No CPU fallback: every entry point needs a CUDA device.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "orbfe_internal.h"
+
+namespace orbfe {
+// launchers defined in the kernel files
+int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* scoreBytes);
+int fast_smem_bytes(int tileBytes, int scoreBytes);
+int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, int tileBytes,
+                int scoreBytes, uint32_t* slots, int* cellCount, cudaStream_t st);
+size_t octree_smem_bytes(int nodeCap, int keySmem);
+int launch_octree(const Geom& g, int n, const ExtractBuffers& b, int nodeCap, int keySmem, cudaStream_t st);
+struct BlurTile { short level, tx, ty, pad; };
+int blur_tile_table(const Geom& g, BlurTile* out, int cap);
+int launch_blur_tiles(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, const void* tiles, int nTiles,
+                      const int* levelCount, cudaStream_t st);
+int launch_knn2(const uint8_t* q, const int* nq, long long qCap, const uint8_t* t, const int* nt, long long tCap,
+                int npairs, long long nqSingle, long long ntSingle, long long maxNq, long long maxNt, int32_t* idx,
+                int32_t* dist, cudaStream_t st);
+
+static std::atomic<uint64_t> g_launches{0};
+
+static inline int cv_round_f(float v) { return (int)lrintf(v); }    // cvRound: round half to even
+static inline int cv_round_d(double v) { return (int)lrint(v); }
+static inline int cv_floor_d(double v) { int i = (int)v; return i - (i > v); }
+static inline int cv_ceil_d(double v) { int i = (int)v; return i + (i < v); }
+
+struct Tables {    // ORBextractor::ORBextractor, ORBextractor_old.cc:411-471
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> nfeat;
+    int umax[kHalfPatch + 1];
+};
+
+static void build_tables(const orbfe_params& p, Tables& t) {
+    const int nl = p.nlevels;
+    const double scaleFactor = p.scale_factor;    // the member is a double holding the float argument (ORBextractor.h:94)
+    t.scale.assign(nl, 1.f);
+    t.sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; i++) {
+        t.scale[i] = (float)(t.scale[i - 1] * scaleFactor);
+        t.sigma2[i] = t.scale[i] * t.scale[i];
+    }
+    t.invScale.resize(nl);
+    t.invSigma2.resize(nl);
+    for (int i = 0; i < nl; i++) {
+        t.invScale[i] = 1.0f / t.scale[i];
+        t.invSigma2[i] = 1.0f / t.sigma2[i];
+    }
+    t.nfeat.assign(nl, 0);
+    const float factor = (float)(1.0f / scaleFactor);
+    float nDesired = p.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; l++) {
+        t.nfeat[l] = cv_round_f(nDesired);
+        sum += t.nfeat[l];
+        nDesired *= factor;
+    }
+    t.nfeat[nl - 1] = std::max(p.nfeatures - sum, 0);
+    // umax (:455-470)
+    int v, v0;
+    const int vmax = cv_floor_d(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+    const int vmin = cv_ceil_d(kHalfPatch * std::sqrt(2.f) / 2);
+    const double hp2 = kHalfPatch * kHalfPatch;
+    for (v = 0; v <= kHalfPatch; v++) t.umax[v] = 0;
+    for (v = 0; v <= vmax; ++v) t.umax[v] = cv_round_d(std::sqrt(hp2 - v * v));
+    for (v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+        while (t.umax[v0] == t.umax[v0 + 1]) ++v0;
+        t.umax[v] = v0;
+        ++v0;
+    }
+}
+
+// level sizes, plane layout, FAST cell grid, octree roots and capacities for one image size
+static void build_geom(const orbfe_params& p, const Tables& t, int w, int h, Geom& g) {
+    memset(&g, 0, sizeof(g));
+    g.nlevels = p.nlevels;
+    g.width = w;
+    g.height = h;
+    g.iniTh = p.ini_th_fast;
+    g.minTh = p.min_th_fast;
+    for (int i = 0; i <= kHalfPatch; i++) g.umax[i] = t.umax[i];
+    unsigned long long off = 0;
+    int cellBase = 0, keyBase = 0, slotCap = 1, maxCW = 7, maxCH = 7;
+    for (int l = 0; l < p.nlevels; l++) {
+        LevelGeom& L = g.lv[l];
+        L.w = cv_round_f((float)w * t.invScale[l]);    // :1335
+        L.h = cv_round_f((float)h * t.invScale[l]);
+        L.w = std::max(L.w, 1);
+        L.h = std::max(L.h, 1);
+        L.pitch = (kXOff + L.w + kEdge + 63) & ~63;
+        L.planeOff = off;
+        off += ((unsigned long long)L.pitch * (L.h + 2 * kEdge) + 255) & ~255ull;
+        L.nfeat = t.nfeat[l];
+        L.scale = t.scale[l];
+        L.scaledPatch = (int)(kPatch * t.scale[l]);    // :891
+        // :791-805
+        const int minBX = kMinBorder, minBY = kMinBorder, maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
+        const float width = (float)(maxBX - minBX), height = (float)(maxBY - minBY);
+        int nCols = 0, nRows = 0;
+        if (maxBX > minBX && maxBY > minBY) {
+            nCols = (int)(width / (float)kCellW);
+            nRows = (int)(height / (float)kCellW);
+        }
+        if (nCols <= 0 || nRows <= 0) nCols = nRows = 0;
+        L.nCols = nCols;
+        L.nRows = nRows;
+        L.wCell = nCols > 0 ? (int)std::ceil(width / nCols) : 0;
+        L.hCell = nRows > 0 ? (int)std::ceil(height / nRows) : 0;
+        L.cellBase = cellBase;
+        cellBase += nCols * nRows;
+        if (nCols > 0) {
+            slotCap = std::max(slotCap, ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2));
+            maxCW = std::max(maxCW, L.wCell + 6);
+            maxCH = std::max(maxCH, L.hCell + 6);
+            // :561-563 (the reference divides by zero when width < height / 2; clamp to one root like the oracle)
+            L.nIni = std::max(1, (int)std::round(static_cast<float>(maxBX - minBX) / (maxBY - minBY)));
+            L.hX = static_cast<float>(maxBX - minBX) / L.nIni;
+        } else {
+            L.nIni = 1;
+            L.hX = 1.f;
+        }
+        L.keyCap = std::max(L.nfeat + 3, 4 * L.nIni);
+        L.keyBase = keyBase;
+        keyBase += L.keyCap;
+    }
+    g.nCells = cellBase;
+    g.slotCap = slotCap;
+    g.keyTotal = keyBase;
+    g.outCap = keyBase;
+    g.maxCellW = maxCW;
+    g.maxCellH = maxCH;
+    g.slabBytes = off;
+    for (int l = 0; l < p.nlevels; l++) g.lv[l].maxCand = g.lv[l].nCols * g.lv[l].nRows * slotCap;
+}
+
+// cv::resize(INTER_LINEAR) coefficient tables for src -> dst along one axis (imgproc/resize.cpp).
+// horizontal: the fraction is zeroed at the clamped ends; vertical: only the row indices are clamped.
+static void build_taps(int src, int dst, bool horizontal, std::vector<ResizeTap>& out) {
+    out.resize(dst);
+    const double inv = (double)dst / src, scale = 1. / inv;
+    for (int d = 0; d < dst; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = cv_floor_d(f);
+        f -= s;
+        ResizeTap tp;
+        if (horizontal) {
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= src - 1) { f = 0; s = src - 1; }
+            tp.s = (short)s;
+            tp.s1 = (short)(s + 1 < src ? s + 1 : s);
+        } else {
+            tp.s = (short)(s < 0 ? 0 : (s < src ? s : src - 1));
+            tp.s1 = (short)(s + 1 < 0 ? 0 : (s + 1 < src ? s + 1 : src - 1));
+        }
+        tp.a0 = (short)cv_round_f((1.f - f) * 2048);
+        tp.a1 = (short)cv_round_f(f * 2048);
+        out[d] = tp;
+    }
+}
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t reserve(size_t need) {
+        if (need <= bytes) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMalloc(&p, need);
+        if (e == cudaSuccess) bytes = need;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+};
+
+}    // namespace orbfe
+
+using namespace orbfe;
+
+// ---------------------------------------------------------------------------------------------------------------
+// extractor object
+// ---------------------------------------------------------------------------------------------------------------
+struct orbfe_extractor {
+    int device = 0;
+    orbfe_params params{};
+    Tables tables;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    std::mutex mu;
+    std::string err;
+    size_t wsLimit = (size_t)24 << 30;
+
+    // geometry of the current image size
+    bool haveGeom = false;
+    Geom geom{};
+    int nItems = 0, tileBytes = 0, scoreBytes = 0, nBlurTiles = 0, nodeCap = 0, keySmem = 0;
+    DevBuf dItems, dBlurTiles, dTaps;
+    const ResizeTap* xtab[ORBFE_MAX_LEVELS] = {};
+    const ResizeTap* ytab[ORBFE_MAX_LEVELS] = {};
+
+    // workspace for `chunkCap` images
+    int chunkCap = 0;
+    size_t perImageBytes = 0;
+    DevBuf dPyr, dBlur, dSlots, dCellCount, dLevelKeys, dLevelCount, dScratch, dWork, dResult, dErr;
+    DevBuf dIn, dKps, dDesc;    // staging for host inputs / outputs
+    ExtractBuffers bufs{};
+
+    // last call (stage outputs for the parity accessors)
+    int lastChunkBase = 0, lastChunkN = 0, lastCap = 0, lastLaunches = 0;
+    const orbfe_keypoint* lastKps = nullptr;    // device pointers of the last chunk's outputs
+    const uint8_t* lastDesc = nullptr;
+    float stageMs[7] = {0, 0, 0, 0, 0, 0, 0};
+};
+
+static int set_err(orbfe_extractor* ex, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ex) ex->err = buf;
+    return code;
+}
+
+#define ORBFE_CUDA(ex, call)                                                                              \
+    do {                                                                                                  \
+        cudaError_t e__ = (call);                                                                         \
+        if (e__ != cudaSuccess)                                                                           \
+            return set_err(ex, ORBFE_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+static size_t per_image_bytes(const Geom& g) {
+    size_t scratch = 0;
+    for (int l = 0; l < g.nlevels; l++) scratch += 2 * (size_t)g.lv[l].maxCand * 4;
+    return 2 * (size_t)g.slabBytes + (size_t)g.nCells * g.slotCap * 4 + (size_t)g.nCells * 4 + (size_t)g.keyTotal * 4 +
+           (size_t)g.nlevels * 4 + scratch + (size_t)g.outCap * sizeof(KpWork) + sizeof(ImageResult);
+}
+
+// (re)build everything that depends on the image size
+static int configure_geometry(orbfe_extractor* ex, int w, int h) {
+    if (ex->haveGeom && ex->geom.width == w && ex->geom.height == h) return ORBFE_OK;
+    Geom g;
+    build_geom(ex->params, ex->tables, w, h, g);
+    if (w > 4095 + 2 * kMinBorder || h > 4095 + 2 * kMinBorder)
+        return set_err(ex, ORBFE_ERR_ARG, "image %dx%d too large: candidate coordinates are packed in 12 bits", w, h);
+    // FAST work items
+    std::vector<FastItem> items;
+    int tb = 0, sb = 0;
+    const int nItems = fast_item_table(g, nullptr, 0, &tb, &sb);
+    items.resize(std::max(nItems, 1));
+    fast_item_table(g, items.data(), nItems, &tb, &sb);
+    if (fast_smem_bytes(tb, sb) > 220 * 1024)
+        return set_err(ex, ORBFE_ERR_ARG, "FAST cell strip does not fit shared memory (%d bytes)", fast_smem_bytes(tb, sb));
+    // blur tiles
+    std::vector<BlurTile> tiles;
+    const int nTiles = blur_tile_table(g, nullptr, 0);
+    tiles.resize(std::max(nTiles, 1));
+    blur_tile_table(g, tiles.data(), nTiles);
+    // octree capacities
+    int nodeCap = 256;
+    for (int l = 0; l < g.nlevels; l++) nodeCap = std::max(nodeCap, g.lv[l].keyCap + 1);
+    int keySmem = 4096;
+    while (keySmem > 0 && octree_smem_bytes(nodeCap, keySmem) > 200 * 1024) keySmem /= 2;
+    if (octree_smem_bytes(nodeCap, keySmem) > 220 * 1024)
+        return set_err(ex, ORBFE_ERR_ARG, "nfeatures too large for the shared-memory quadtree (%d nodes per level)", nodeCap);
+    // resize taps
+    std::vector<ResizeTap> all;
+    std::vector<size_t> xo(g.nlevels, 0), yo(g.nlevels, 0);
+    for (int l = 1; l < g.nlevels; l++) {
+        std::vector<ResizeTap> tx, ty;
+        build_taps(g.lv[l - 1].w, g.lv[l].w, true, tx);
+        build_taps(g.lv[l - 1].h, g.lv[l].h, false, ty);
+        xo[l] = all.size();
+        all.insert(all.end(), tx.begin(), tx.end());
+        yo[l] = all.size();
+        all.insert(all.end(), ty.begin(), ty.end());
+    }
+    if (all.empty()) all.push_back(ResizeTap{0, 0, 2048, 0});
+    ORBFE_CUDA(ex, ex->dItems.reserve(items.size() * sizeof(FastItem)));
+    ORBFE_CUDA(ex, ex->dBlurTiles.reserve(tiles.size() * sizeof(BlurTile)));
+    ORBFE_CUDA(ex, ex->dTaps.reserve(all.size() * sizeof(ResizeTap)));
+    ORBFE_CUDA(ex, cudaStreamSynchronize(ex->stream));
+    ORBFE_CUDA(ex, cudaMemcpy(ex->dItems.p, items.data(), items.size() * sizeof(FastItem), cudaMemcpyHostToDevice));
+    ORBFE_CUDA(ex, cudaMemcpy(ex->dBlurTiles.p, tiles.data(), tiles.size() * sizeof(BlurTile), cudaMemcpyHostToDevice));
+    ORBFE_CUDA(ex, cudaMemcpy(ex->dTaps.p, all.data(), all.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
+    for (int l = 0; l < ORBFE_MAX_LEVELS; l++) {
+        ex->xtab[l] = l > 0 && l < g.nlevels ? (const ResizeTap*)ex->dTaps.p + xo[l] : nullptr;
+        ex->ytab[l] = l > 0 && l < g.nlevels ? (const ResizeTap*)ex->dTaps.p + yo[l] : nullptr;
+    }
+    ex->geom = g;
+    ex->nItems = nItems;
+    ex->tileBytes = tb;
+    ex->scoreBytes = sb;
+    ex->nBlurTiles = nTiles;
+    ex->nodeCap = nodeCap;
+    ex->keySmem = keySmem;
+    ex->perImageBytes = per_image_bytes(g);
+    ex->chunkCap = 0;    // workspace must be re-laid out
+    ex->haveGeom = true;
+    ex->lastChunkN = 0;
+    return ORBFE_OK;
+}
+
+static int reserve_workspace(orbfe_extractor* ex, int chunk) {
+    if (chunk <= ex->chunkCap) return ORBFE_OK;
+    const Geom& g = ex->geom;
+    size_t scratchPer = 0;
+    for (int l = 0; l < g.nlevels; l++) scratchPer += 2 * (size_t)g.lv[l].maxCand;
+    ORBFE_CUDA(ex, cudaStreamSynchronize(ex->stream));
+    ORBFE_CUDA(ex, ex->dPyr.reserve((size_t)chunk * g.slabBytes));
+    ORBFE_CUDA(ex, ex->dBlur.reserve((size_t)chunk * g.slabBytes));
+    ORBFE_CUDA(ex, ex->dSlots.reserve(std::max<size_t>(16, (size_t)chunk * g.nCells * g.slotCap * 4)));
+    ORBFE_CUDA(ex, ex->dCellCount.reserve(std::max<size_t>(16, (size_t)chunk * g.nCells * 4)));
+    ORBFE_CUDA(ex, ex->dLevelKeys.reserve((size_t)chunk * g.keyTotal * 4));
+    ORBFE_CUDA(ex, ex->dLevelCount.reserve((size_t)chunk * g.nlevels * 4));
+    ORBFE_CUDA(ex, ex->dScratch.reserve(std::max<size_t>(16, (size_t)chunk * scratchPer * 4)));
+    ORBFE_CUDA(ex, ex->dWork.reserve((size_t)chunk * g.outCap * sizeof(KpWork)));
+    ORBFE_CUDA(ex, ex->dResult.reserve((size_t)chunk * sizeof(ImageResult)));
+    ORBFE_CUDA(ex, ex->dErr.reserve(16));
+    ORBFE_CUDA(ex, cudaMemset(ex->dErr.p, 0, 16));
+    // the blurred slab is only written inside the level ROIs; clear it once so that stage reads are deterministic
+    ORBFE_CUDA(ex, cudaMemset(ex->dBlur.p, 0, (size_t)chunk * g.slabBytes));
+    ExtractBuffers& b = ex->bufs;
+    b.pyr = (uint8_t*)ex->dPyr.p;
+    b.blur = (uint8_t*)ex->dBlur.p;
+    b.slots = (uint32_t*)ex->dSlots.p;
+    b.cellCount = (int*)ex->dCellCount.p;
+    b.levelKeys = (uint32_t*)ex->dLevelKeys.p;
+    b.levelCount = (int*)ex->dLevelCount.p;
+    b.scratch = (uint32_t*)ex->dScratch.p;
+    b.scratchPerImage = scratchPer;
+    b.work = (KpWork*)ex->dWork.p;
+    b.result = (ImageResult*)ex->dResult.p;
+    b.errFlag = (int*)ex->dErr.p;
+    ex->chunkCap = chunk;
+    return ORBFE_OK;
+}
+
+// run the kernels on `n` images already resident on the device; outputs go to device buffers dKps/dDesc (cap-strided)
+static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int stride, size_t imageStride, int lap0,
+                     int lap1, orbfe_keypoint* dKps, uint8_t* dDesc, int cap) {
+    const Geom& g = ex->geom;
+    cudaStream_t st = ex->stream;
+    int launches = 0;
+    cudaEventRecord(ex->ev[1], st);
+    launches += launch_pyramid(g, dImages, n, stride, imageStride, ex->bufs.pyr, ex->xtab, ex->ytab, st);
+    cudaEventRecord(ex->ev[2], st);
+    launches += launch_fast(g, ex->bufs.pyr, n, (const FastItem*)ex->dItems.p, ex->nItems, ex->tileBytes, ex->scoreBytes,
+                            ex->bufs.slots, ex->bufs.cellCount, st);
+    cudaEventRecord(ex->ev[3], st);
+    launches += launch_octree(g, n, ex->bufs, ex->nodeCap, ex->keySmem, st);
+    cudaEventRecord(ex->ev[4], st);
+    launches += launch_blur_tiles(g, ex->bufs.pyr, ex->bufs.blur, n, ex->dBlurTiles.p, ex->nBlurTiles, ex->bufs.levelCount, st);
+    cudaEventRecord(ex->ev[5], st);
+    launches += launch_pack(g, n, ex->bufs, lap0, lap1, st);
+    launches += launch_describe(g, n, ex->bufs, dKps, dDesc, cap, st);
+    cudaEventRecord(ex->ev[6], st);
+    ORBFE_CUDA(ex, cudaGetLastError());
+    g_launches += launches;
+    ex->lastLaunches += launches;
+    return ORBFE_OK;
+}
+
+extern "C" {
+
+const char* orbfe_version(void) { return "orbfe 0.1 (sm_100a)"; }
+
+int orbfe_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+uint64_t orbfe_kernel_launches(void) { return g_launches.load(); }
+
+int orbfe_extractor_create(int device, const orbfe_params* params, orbfe_extractor** out) {
+    if (!params || !out) return ORBFE_ERR_ARG;
+    *out = nullptr;
+    if (params->nlevels < 1 || params->nlevels > ORBFE_MAX_LEVELS || params->nfeatures < 0 ||
+        !(params->scale_factor > 1.0f) || params->ini_th_fast < 0 || params->min_th_fast < 0)
+        return ORBFE_ERR_ARG;
+    if (orbfe_device_count() <= device || device < 0) return ORBFE_ERR_CUDA;    // no device, no extractor: no CPU fallback
+    orbfe_extractor* ex = new orbfe_extractor();
+    ex->device = device;
+    ex->params = *params;
+    build_tables(*params, ex->tables);
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ex;
+        return ORBFE_ERR_CUDA;
+    }
+    for (auto& e : ex->ev) cudaEventCreate(&e);
+    *out = ex;
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_destroy(orbfe_extractor* ex) {
+    if (!ex) return ORBFE_ERR_ARG;
+    cudaSetDevice(ex->device);
+    if (ex->stream) cudaStreamSynchronize(ex->stream);
+    DevBuf* bufs[] = {&ex->dItems, &ex->dBlurTiles, &ex->dTaps, &ex->dPyr, &ex->dBlur, &ex->dSlots, &ex->dCellCount,
+                      &ex->dLevelKeys, &ex->dLevelCount, &ex->dScratch, &ex->dWork, &ex->dResult, &ex->dErr, &ex->dIn,
+                      &ex->dKps, &ex->dDesc};
+    for (DevBuf* b : bufs) b->release();
+    for (auto& e : ex->ev) if (e) cudaEventDestroy(e);
+    if (ex->stream) cudaStreamDestroy(ex->stream);
+    delete ex;
+    return ORBFE_OK;
+}
+
+const char* orbfe_last_error(const orbfe_extractor* ex) { return ex ? ex->err.c_str() : "null extractor"; }
+
+int orbfe_extractor_set_workspace_limit(orbfe_extractor* ex, size_t bytes) {
+    if (!ex || bytes == 0) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ex->mu);
+    ex->wsLimit = bytes;
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_tables(const orbfe_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                           int32_t* features_per_level, int32_t* umax) {
+    if (!ex) return ORBFE_ERR_ARG;
+    const Tables& t = ex->tables;
+    for (int i = 0; i < ex->params.nlevels; i++) {
+        if (scale) scale[i] = t.scale[i];
+        if (inv_scale) inv_scale[i] = t.invScale[i];
+        if (sigma2) sigma2[i] = t.sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = t.invSigma2[i];
+        if (features_per_level) features_per_level[i] = t.nfeat[i];
+    }
+    if (umax) for (int i = 0; i <= kHalfPatch; i++) umax[i] = t.umax[i];
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_max_keypoints(const orbfe_extractor* ex) {
+    if (!ex) return ORBFE_ERR_ARG;
+    // sum over levels of max(N_l + 3, 4 * nIni_l); nIni depends on the aspect ratio, bounded here for ratios <= 8:1
+    int total = 0;
+    for (int l = 0; l < ex->params.nlevels; l++) total += std::max(ex->tables.nfeat[l] + 3, 32);
+    return total;
+}
+
+int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int width, int height, int stride,
+                        size_t image_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                        int32_t* counts, int32_t* monos, unsigned flags) {
+    if (!ex) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ex->mu);
+    if (n < 0 || cap < 0 || (n > 0 && (!kps || !desc) && cap > 0)) return set_err(ex, ORBFE_ERR_ARG, "bad arguments");
+    if (n == 0) return ORBFE_OK;
+    if (!images || width <= 0 || height <= 0) {    // ORBextractor_old.cc:1091-1092: empty image -> -1
+        for (int i = 0; i < n; i++) {
+            if (counts && !(flags & ORBFE_OUT_DEVICE)) counts[i] = 0;
+            if (monos && !(flags & ORBFE_OUT_DEVICE)) monos[i] = -1;
+        }
+        return images ? ORBFE_OK : set_err(ex, ORBFE_ERR_ARG, "null image pointer");
+    }
+    if (stride < width || (n > 1 && image_stride < (size_t)stride * (height - 1) + width))
+        return set_err(ex, ORBFE_ERR_ARG, "stride %d / image_stride %zu too small for %dx%d", stride, image_stride, width, height);
+    ORBFE_CUDA(ex, cudaSetDevice(ex->device));
+    int rc = configure_geometry(ex, width, height);
+    if (rc != ORBFE_OK) return rc;
+    const Geom& g = ex->geom;
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    const size_t ioPer = (inDev ? 0 : (size_t)width * height) + (outDev ? 0 : (size_t)cap * 60);
+    int chunk = (int)std::min<size_t>((size_t)n, std::max<size_t>(1, ex->wsLimit / (ex->perImageBytes + ioPer)));
+    chunk = std::min(chunk, 32768);
+    rc = reserve_workspace(ex, chunk);
+    if (rc != ORBFE_OK) return rc;
+    if (!inDev) ORBFE_CUDA(ex, ex->dIn.reserve((size_t)chunk * width * height));
+    if (!outDev) {
+        ORBFE_CUDA(ex, ex->dKps.reserve(std::max<size_t>(16, (size_t)chunk * cap * sizeof(orbfe_keypoint))));
+        ORBFE_CUDA(ex, ex->dDesc.reserve(std::max<size_t>(16, (size_t)chunk * cap * 32)));
+    }
+    cudaStream_t st = ex->stream;
+    ex->lastLaunches = 0;
+    for (int i = 0; i < 7; i++) ex->stageMs[i] = 0;
+    std::vector<ImageResult> res(chunk);
+    int status = ORBFE_OK;
+    for (int base = 0; base < n; base += chunk) {
+        const int m = std::min(chunk, n - base);
+        const uint8_t* src = images + (size_t)base * image_stride;
+        const uint8_t* dImages = src;
+        int dStride = stride;
+        size_t dImageStride = image_stride;
+        cudaEventRecord(ex->ev[0], st);
+        if (!inDev) {
+            // one 2-D copy per chunk when the images are evenly spaced (rows of all images form one pitched array)
+            if (stride == width && (m == 1 || image_stride == (size_t)width * height)) {
+                ORBFE_CUDA(ex, cudaMemcpyAsync(ex->dIn.p, src, (size_t)m * width * height, cudaMemcpyHostToDevice, st));
+            } else {
+                for (int i = 0; i < m; i++)
+                    ORBFE_CUDA(ex, cudaMemcpy2DAsync((uint8_t*)ex->dIn.p + (size_t)i * width * height, width,
+                                                     src + (size_t)i * image_stride, stride, width, height,
+                                                     cudaMemcpyHostToDevice, st));
+            }
+            dImages = (const uint8_t*)ex->dIn.p;
+            dStride = width;
+            dImageStride = (size_t)width * height;
+        }
+        orbfe_keypoint* dK = outDev ? kps + (size_t)base * cap : (orbfe_keypoint*)ex->dKps.p;
+        uint8_t* dD = outDev ? desc + (size_t)base * cap * 32 : (uint8_t*)ex->dDesc.p;
+        rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap);
+        if (rc != ORBFE_OK) return rc;
+        // results
+        int errFlag = 0;
+        ORBFE_CUDA(ex, cudaMemcpyAsync(res.data(), ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
+        ORBFE_CUDA(ex, cudaMemcpyAsync(&errFlag, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
+        if (!outDev && cap > 0) {
+            ORBFE_CUDA(ex, cudaMemcpyAsync(kps + (size_t)base * cap, dK, (size_t)m * cap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
+            ORBFE_CUDA(ex, cudaMemcpyAsync(desc + (size_t)base * cap * 32, dD, (size_t)m * cap * 32, cudaMemcpyDeviceToHost, st));
+        }
+        cudaEventRecord(ex->ev[7], st);
+        ORBFE_CUDA(ex, cudaStreamSynchronize(st));
+        if (errFlag) return set_err(ex, ORBFE_ERR_INTERNAL, "quadtree capacity exceeded on the device (images %d..%d)", base, base + m - 1);
+        for (int i = 0; i < 7; i++) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, ex->ev[i], ex->ev[i + 1]) == cudaSuccess) ex->stageMs[i] += ms;
+        }
+        for (int i = 0; i < m; i++) {
+            if (res[i].count > cap) status = ORBFE_ERR_CAPACITY;
+            if (outDev) continue;
+            if (counts) counts[base + i] = res[i].count;
+            if (monos) monos[base + i] = res[i].mono;
+        }
+        if (outDev) {
+            // counts / monos are device int32 arrays: scatter the two fields with strided 2-D copies
+            if (counts) ORBFE_CUDA(ex, cudaMemcpy2DAsync(counts + base, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
+            if (monos) ORBFE_CUDA(ex, cudaMemcpy2DAsync(monos + base, 4, &ex->bufs.result[0].mono, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
+            ORBFE_CUDA(ex, cudaStreamSynchronize(st));
+        }
+        ex->lastChunkBase = base;
+        ex->lastChunkN = m;
+        ex->lastCap = cap;
+        ex->lastKps = dK;
+        ex->lastDesc = dD;
+    }
+    if (status == ORBFE_ERR_CAPACITY) return set_err(ex, status, "keypoint capacity %d too small (need <= %d)", cap, g.outCap);
+    return status;
+}
+
+int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int width, int height, int stride, int lap0, int lap1,
+                  orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* count, int32_t* mono) {
+    return orbfe_extract_batch(ex, image, 1, width, height, stride, (size_t)stride * (height > 0 ? height : 0), lap0, lap1,
+                               kps, desc, cap, count, mono, 0);
+}
+
+}    // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// stage outputs of the last call (parity tests)
+// ---------------------------------------------------------------------------------------------------------------
+static int check_index(orbfe_extractor* ex, int index, int level) {
+    if (!ex->haveGeom || ex->lastChunkN == 0) return set_err(ex, ORBFE_ERR_ARG, "no previous extraction");
+    if (level < 0 || level >= ex->geom.nlevels) return set_err(ex, ORBFE_ERR_ARG, "bad level %d", level);
+    if (index < ex->lastChunkBase || index >= ex->lastChunkBase + ex->lastChunkN)
+        return set_err(ex, ORBFE_ERR_ARG, "image %d is not in the last processed chunk [%d, %d)", index, ex->lastChunkBase,
+                       ex->lastChunkBase + ex->lastChunkN);
+    return ORBFE_OK;
+}
+
+extern "C" {
+
+int orbfe_level_size(const orbfe_extractor* ex, int level, int* w, int* h) {
+    if (!ex || !ex->haveGeom || level < 0 || level >= ex->geom.nlevels) return ORBFE_ERR_ARG;
+    if (w) *w = ex->geom.lv[level].w;
+    if (h) *h = ex->geom.lv[level].h;
+    return ORBFE_OK;
+}
+
+int orbfe_level_read(orbfe_extractor* ex, int index, int level, int which, uint8_t* dst, int dstride) {
+    if (!ex || !dst) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ex->mu);
+    int rc = check_index(ex, index, level);
+    if (rc != ORBFE_OK) return rc;
+    ORBFE_CUDA(ex, cudaSetDevice(ex->device));
+    const Geom& g = ex->geom;
+    const LevelGeom& L = g.lv[level];
+    const int i = index - ex->lastChunkBase;
+    const uint8_t* slab = (which == 2 ? ex->bufs.blur : ex->bufs.pyr) + (size_t)i * g.slabBytes + L.planeOff;
+    if (which == 1) {
+        ORBFE_CUDA(ex, cudaMemcpy2D(dst, dstride, slab + kXOff - kEdge, L.pitch, L.w + 2 * kEdge, L.h + 2 * kEdge, cudaMemcpyDeviceToHost));
+    } else if (which == 0 || which == 2) {
+        ORBFE_CUDA(ex, cudaMemcpy2D(dst, dstride, slab + (size_t)kEdge * L.pitch + kXOff, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+    } else {
+        return set_err(ex, ORBFE_ERR_ARG, "bad plane selector %d", which);
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_level_candidates(orbfe_extractor* ex, int index, int level, int32_t* out_xyr, int cap) {
+    if (!ex) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ex->mu);
+    int rc = check_index(ex, index, level);
+    if (rc != ORBFE_OK) return rc;
+    ORBFE_CUDA(ex, cudaSetDevice(ex->device));
+    const Geom& g = ex->geom;
+    const LevelGeom& L = g.lv[level];
+    const int i = index - ex->lastChunkBase, nc = L.nCols * L.nRows;
+    if (nc == 0) return 0;
+    std::vector<int> cnt(nc);
+    std::vector<uint32_t> slots((size_t)nc * g.slotCap);
+    ORBFE_CUDA(ex, cudaMemcpy(cnt.data(), ex->bufs.cellCount + (size_t)i * g.nCells + L.cellBase, nc * 4, cudaMemcpyDeviceToHost));
+    ORBFE_CUDA(ex, cudaMemcpy(slots.data(), ex->bufs.slots + ((size_t)i * g.nCells + L.cellBase) * g.slotCap, slots.size() * 4, cudaMemcpyDeviceToHost));
+    int n = 0;
+    for (int c = 0; c < nc; c++)
+        for (int k = 0; k < cnt[c]; k++) {
+            const uint32_t key = slots[(size_t)c * g.slotCap + k];
+            if (out_xyr && n < cap) {
+                out_xyr[3 * n] = key & 0xfff;
+                out_xyr[3 * n + 1] = (key >> 12) & 0xfff;
+                out_xyr[3 * n + 2] = key >> 24;
+            }
+            n++;
+        }
+    return n;
+}
+
+int orbfe_level_keypoints(orbfe_extractor* ex, int index, int level, orbfe_keypoint* out, int cap) {
+    if (!ex) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ex->mu);
+    int rc = check_index(ex, index, level);
+    if (rc != ORBFE_OK) return rc;
+    ORBFE_CUDA(ex, cudaSetDevice(ex->device));
+    const Geom& g = ex->geom;
+    const int i = index - ex->lastChunkBase;
+    std::vector<int> lc(g.nlevels);
+    ORBFE_CUDA(ex, cudaMemcpy(lc.data(), ex->bufs.levelCount + (size_t)i * g.nlevels, g.nlevels * 4, cudaMemcpyDeviceToHost));
+    int off = 0;
+    for (int l = 0; l < level; l++) off += lc[l];
+    const int n = lc[level];
+    if (n == 0) return 0;
+    std::vector<KpWork> work(n);
+    ORBFE_CUDA(ex, cudaMemcpy(work.data(), ex->bufs.work + (size_t)i * g.outCap + off, (size_t)n * sizeof(KpWork), cudaMemcpyDeviceToHost));
+    std::vector<orbfe_keypoint> all(ex->lastCap);
+    if (ex->lastCap > 0)
+        ORBFE_CUDA(ex, cudaMemcpy(all.data(), ex->lastKps + (size_t)i * ex->lastCap, (size_t)ex->lastCap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < n && k < cap; k++) {
+        orbfe_keypoint kp{};
+        kp.x = work[k].x;
+        kp.y = work[k].y;
+        kp.size = (float)g.lv[level].scaledPatch;
+        kp.angle = work[k].dst < ex->lastCap ? all[work[k].dst].angle : -1.f;
+        kp.response = work[k].response;
+        kp.octave = level;
+        kp.class_id = -1;
+        out[k] = kp;
+    }
+    return n;
+}
+
+int orbfe_extractor_stage_ms(const orbfe_extractor* ex, float out[7]) {
+    if (!ex || !out) return ORBFE_ERR_ARG;
+    for (int i = 0; i < 7; i++) out[i] = ex->stageMs[i];
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_last_launches(const orbfe_extractor* ex) { return ex ? ex->lastLaunches : ORBFE_ERR_ARG; }
+
+}    // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// matcher
+// ---------------------------------------------------------------------------------------------------------------
+struct orbfe_matcher {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[2] = {};
+    std::mutex mu;
+    std::string err;
+    DevBuf dQ, dT, dIdx, dDist, dNq, dNt;
+    float lastMs = 0;
+    int lastLaunches = 0;
+};
+
+static int set_merr(orbfe_matcher* m, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (m) m->err = buf;
+    return code;
+}
+#define ORBFE_MCUDA(m, call)                                                                               \
+    do {                                                                                                   \
+        cudaError_t e__ = (call);                                                                          \
+        if (e__ != cudaSuccess)                                                                            \
+            return set_merr(m, ORBFE_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+static int knn_common(orbfe_matcher* m, const uint8_t* q, const int32_t* nq, long long qCap, const uint8_t* t,
+                      const int32_t* nt, long long tCap, int npairs, long long nqSingle, long long ntSingle, int32_t* idx,
+                      int32_t* dist, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (npairs < 0 || qCap < 0 || tCap < 0) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (npairs == 0 || qCap == 0) return ORBFE_OK;
+    if (!q || !idx || !dist || (tCap > 0 && !t)) return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t qBytes = (size_t)npairs * qCap * 32, tBytes = (size_t)npairs * tCap * 32, oBytes = (size_t)npairs * qCap * 8;
+    const uint8_t *dq = q, *dt = t;
+    const int *dnq = nq, *dnt = nt;
+    long long maxNq = nqSingle, maxNt = ntSingle;
+    if (nq) {
+        // per-pair counts: the launch grid is sized for q_cap rows; empty tails exit at once
+        maxNq = qCap;
+        maxNt = tCap;
+    }
+    if (!inDev) {
+        ORBFE_MCUDA(m, m->dQ.reserve(std::max<size_t>(qBytes, 32)));
+        ORBFE_MCUDA(m, m->dT.reserve(std::max<size_t>(tBytes, 32)));
+        ORBFE_MCUDA(m, cudaMemcpyAsync(m->dQ.p, q, qBytes, cudaMemcpyHostToDevice, st));
+        if (tBytes) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dT.p, t, tBytes, cudaMemcpyHostToDevice, st));
+        dq = (const uint8_t*)m->dQ.p;
+        dt = (const uint8_t*)m->dT.p;
+        if (nq) {
+            ORBFE_MCUDA(m, m->dNq.reserve((size_t)npairs * 4));
+            ORBFE_MCUDA(m, m->dNt.reserve((size_t)npairs * 4));
+            ORBFE_MCUDA(m, cudaMemcpyAsync(m->dNq.p, nq, (size_t)npairs * 4, cudaMemcpyHostToDevice, st));
+            ORBFE_MCUDA(m, cudaMemcpyAsync(m->dNt.p, nt, (size_t)npairs * 4, cudaMemcpyHostToDevice, st));
+            dnq = (const int*)m->dNq.p;
+            dnt = (const int*)m->dNt.p;
+        }
+    }
+    int32_t *di = idx, *dd = dist;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dIdx.reserve(oBytes));
+        ORBFE_MCUDA(m, m->dDist.reserve(oBytes));
+        di = (int32_t*)m->dIdx.p;
+        dd = (int32_t*)m->dDist.p;
+    }
+    if (nq) {    // rows beyond nq[p] are not written by the kernel: define them
+        ORBFE_MCUDA(m, cudaMemsetAsync(di, 0xff, oBytes, st));
+        ORBFE_MCUDA(m, cudaMemsetAsync(dd, 0xff, oBytes, st));
+    }
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_knn2(dq, dnq, qCap, dt, dnt, tCap, npairs, nqSingle, ntSingle, maxNq, maxNt, di, dd, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, cudaMemcpyAsync(idx, di, oBytes, cudaMemcpyDeviceToHost, st));
+        ORBFE_MCUDA(m, cudaMemcpyAsync(dist, dd, oBytes, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+extern "C" {
+
+int orbfe_matcher_create(int device, orbfe_matcher** out) {
+    if (!out) return ORBFE_ERR_ARG;
+    *out = nullptr;
+    if (device < 0 || orbfe_device_count() <= device) return ORBFE_ERR_CUDA;
+    orbfe_matcher* m = new orbfe_matcher();
+    m->device = device;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete m;
+        return ORBFE_ERR_CUDA;
+    }
+    cudaEventCreate(&m->ev[0]);
+    cudaEventCreate(&m->ev[1]);
+    *out = m;
+    return ORBFE_OK;
+}
+
+int orbfe_matcher_destroy(orbfe_matcher* m) {
+    if (!m) return ORBFE_ERR_ARG;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    DevBuf* bufs[] = {&m->dQ, &m->dT, &m->dIdx, &m->dDist, &m->dNq, &m->dNt};
+    for (DevBuf* b : bufs) b->release();
+    cudaEventDestroy(m->ev[0]);
+    cudaEventDestroy(m->ev[1]);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+    return ORBFE_OK;
+}
+
+const char* orbfe_matcher_last_error(const orbfe_matcher* m) { return m ? m->err.c_str() : "null matcher"; }
+
+int orbfe_knn2(orbfe_matcher* m, const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt, int32_t* idx, int32_t* dist,
+               unsigned flags) {
+    if (nq < 0 || nt < 0) return ORBFE_ERR_ARG;
+    return knn_common(m, q, nullptr, nq, t, nullptr, nt, 1, nq, nt, idx, dist, flags);
+}
+
+int orbfe_knn2_batch(orbfe_matcher* m, const uint8_t* q, const int32_t* nq, int q_cap, const uint8_t* t, const int32_t* nt,
+                     int t_cap, int npairs, int32_t* idx, int32_t* dist, unsigned flags) {
+    if (!nq || !nt) return ORBFE_ERR_ARG;
+    return knn_common(m, q, nq, q_cap, t, nt, t_cap, npairs, 0, 0, idx, dist, flags);
+}
+
+int orbfe_ratio_test(const int32_t* idx, const int32_t* dist, int64_t nq, double ratio, int32_t* out) {
+    if (!idx || !dist || !out || nq < 0) return ORBFE_ERR_ARG;
+    for (int64_t i = 0; i < nq; i++) {
+        const bool ok = idx[2 * i] >= 0 && idx[2 * i + 1] >= 0 && (double)(float)dist[2 * i] < (double)(float)dist[2 * i + 1] * ratio;
+        out[i] = ok ? idx[2 * i] : -1;
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_matcher_last_ms(const orbfe_matcher* m, float* kernel_ms, int* launches) {
+    if (!m) return ORBFE_ERR_ARG;
+    if (kernel_ms) *kernel_ms = m->lastMs;
+    if (launches) *launches = m->lastLaunches;
+    return ORBFE_OK;
+}
+
+}    // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// wire-compatible entry points (orbslam3.idl:14-22; skel signatures dsp/src/orbslam_dsp.cpp:866,931,567,1017)
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+struct WireHandle {
+    orbfe_params params{1000, 1.2f, 8, 20, 7};
+    orbfe_extractor* ex = nullptr;
+    orbfe_matcher* mt = nullptr;
+    int iniThInUse = -1;
+    std::vector<uint8_t> eyes;    // de-interleaved left | right images
+    std::vector<orbfe_keypoint> kps;
+    std::vector<uint8_t> desc;
+    std::vector<int32_t> idx, dist;
+    std::mutex mu;
+};
+
+int wire_ensure_extractor(WireHandle* w, int threshold) {
+    const int ini = threshold > 0 ? threshold : w->params.ini_th_fast;
+    if (w->ex && w->iniThInUse == ini) return ORBFE_OK;
+    if (w->ex) orbfe_extractor_destroy(w->ex);
+    w->ex = nullptr;
+    orbfe_params p = w->params;
+    p.ini_th_fast = ini;
+    const int rc = orbfe_extractor_create(0, &p, &w->ex);
+    if (rc == ORBFE_OK) w->iniThInUse = ini;
+    return rc;
+}
+
+inline short sat16(int v) { return (short)(v > 32767 ? 32767 : (v < -32768 ? -32768 : v)); }
+}    // namespace
+
+extern "C" {
+
+int orbslam3_open(const char* uri, orbfe_remote_handle64* h) {
+    (void)uri;
+    if (!h) return ORBFE_ERR_ARG;
+    *h = 0;
+    if (orbfe_device_count() <= 0) return ORBFE_ERR_CUDA;
+    WireHandle* w = new WireHandle();
+    int rc = orbfe_matcher_create(0, &w->mt);
+    if (rc != ORBFE_OK) {
+        delete w;
+        return rc;
+    }
+    *h = (orbfe_remote_handle64)(uintptr_t)w;
+    return ORBFE_OK;
+}
+
+int orbslam3_close(orbfe_remote_handle64 h) {
+    WireHandle* w = (WireHandle*)(uintptr_t)h;
+    if (!w) return ORBFE_ERR_ARG;
+    if (w->ex) orbfe_extractor_destroy(w->ex);
+    if (w->mt) orbfe_matcher_destroy(w->mt);
+    delete w;
+    return ORBFE_OK;
+}
+
+int orbslam3_configure(orbfe_remote_handle64 h, const orbfe_params* params) {
+    WireHandle* w = (WireHandle*)(uintptr_t)h;
+    if (!w || !params) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(w->mu);
+    if (params->nlevels < 1 || params->nlevels > ORBFE_MAX_LEVELS || params->nfeatures < 0 || !(params->scale_factor > 1.0f))
+        return ORBFE_ERR_ARG;
+    w->params = *params;
+    if (w->ex) orbfe_extractor_destroy(w->ex);
+    w->ex = nullptr;
+    w->iniThInUse = -1;
+    return ORBFE_OK;
+}
+
+int orbslam3_bfMatchStereo(orbfe_remote_handle64 h, const unsigned char* leftDescriptors, int leftDescriptorsLen,
+                           const unsigned char* rightDescriptors, int rightDescriptorsLen, short* indices,
+                           int indicesLen, short* distances1, int distances1Len, short* distances2, int distances2Len) {
+    WireHandle* w = (WireHandle*)(uintptr_t)h;
+    if (!w || leftDescriptorsLen < 0 || rightDescriptorsLen < 0) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(w->mu);
+    const int nl = leftDescriptorsLen / 32, nr = rightDescriptorsLen / 32;
+    if (nl == 0) return ORBFE_OK;
+    if (nl > indicesLen || nl > distances1Len || nl > distances2Len) return ORBFE_ERR_CAPACITY;
+    if (nr > 32767) return ORBFE_ERR_ARG;    // int16 indices of the IDL cannot address more rows (dsp .../matcher.h:19)
+    w->idx.resize((size_t)nl * 2);
+    w->dist.resize((size_t)nl * 2);
+    const int rc = orbfe_knn2(w->mt, leftDescriptors, nl, rightDescriptors, nr, w->idx.data(), w->dist.data(), 0);
+    if (rc != ORBFE_OK) return rc;
+    for (int i = 0; i < nl; i++) {
+        indices[i] = sat16(w->idx[2 * i]);
+        distances1[i] = sat16(w->dist[2 * i]);
+        distances2[i] = sat16(w->dist[2 * i + 1]);
+    }
+    return ORBFE_OK;
+}
+
+int orbslam3_extractFeatures(
+    orbfe_remote_handle64 h, const unsigned char* image, int imageLen, int width, int height, int stride, int threshold,
+    int vLappingAreaLeft0, int vLappingAreaLeft1, int vLappingAreaRight0, int vLappingAreaRight1, int* totalPointsLeft,
+    int* leftKeypointsX, int leftKeypointsXLen, int* leftKeypointsY, int leftKeypointsYLen, int* leftKeypointsAngle,
+    int leftKeypointsAngleLen, int* leftKeypointsLevel, int leftKeypointsLevelLen, uint8_t* leftKeypointsORB,
+    int leftKeypointsORBLen, int* totalPointsRight, int* rightKeypointsX, int rightKeypointsXLen, int* rightKeypointsY,
+    int rightKeypointsYLen, int* rightKeypointsAngle, int rightKeypointsAngleLen, int* rightKeypointsLevel,
+    int rightKeypointsLevelLen, uint8_t* rightKeypointsORB, int rightKeypointsORBLen, int* monoLeft, int* monoRight,
+    short* indices, int indicesLen, short* distances1, int distances1Len, short* distances2, int distances2Len) {
+    WireHandle* w = (WireHandle*)(uintptr_t)h;
+    if (!w || !image || width <= 0 || height <= 0 || stride < 2 * width) return ORBFE_ERR_ARG;
+    if ((long long)imageLen < (long long)stride * (height - 1) + 2 * width) return ORBFE_ERR_ARG;
+    std::unique_lock<std::mutex> lk(w->mu);
+    int rc = wire_ensure_extractor(w, threshold);
+    if (rc != ORBFE_OK) return rc;
+    // de-interleave the side-by-side frame (dsp/src/orbslam_dsp_pyramid.cpp:169-199 does this on the DSP)
+    const size_t eye = (size_t)width * height;
+    w->eyes.resize(2 * eye);
+    for (int y = 0; y < height; y++) {
+        memcpy(&w->eyes[(size_t)y * width], image + (size_t)y * stride, width);
+        memcpy(&w->eyes[eye + (size_t)y * width], image + (size_t)y * stride + width, width);
+    }
+    const int cap = orbfe_extractor_max_keypoints(w->ex);
+    w->kps.resize((size_t)2 * cap);
+    w->desc.resize((size_t)2 * cap * 32);
+    int32_t counts[2] = {0, 0}, monos[2] = {0, 0};
+    // the two eyes may have different lapping areas: two calls when they differ, one batched call otherwise
+    if (vLappingAreaLeft0 == vLappingAreaRight0 && vLappingAreaLeft1 == vLappingAreaRight1) {
+        rc = orbfe_extract_batch(w->ex, w->eyes.data(), 2, width, height, width, eye, vLappingAreaLeft0, vLappingAreaLeft1,
+                                 w->kps.data(), w->desc.data(), cap, counts, monos, 0);
+    } else {
+        rc = orbfe_extract_batch(w->ex, w->eyes.data(), 1, width, height, width, eye, vLappingAreaLeft0, vLappingAreaLeft1,
+                                 w->kps.data(), w->desc.data(), cap, counts, monos, 0);
+        if (rc == ORBFE_OK)
+            rc = orbfe_extract_batch(w->ex, w->eyes.data() + eye, 1, width, height, width, eye, vLappingAreaRight0,
+                                     vLappingAreaRight1, w->kps.data() + cap, w->desc.data() + (size_t)cap * 32, cap,
+                                     counts + 1, monos + 1, 0);
+    }
+    if (rc != ORBFE_OK) return rc;
+    int* X[2] = {leftKeypointsX, rightKeypointsX};
+    int* Y[2] = {leftKeypointsY, rightKeypointsY};
+    int* A[2] = {leftKeypointsAngle, rightKeypointsAngle};
+    int* Lv[2] = {leftKeypointsLevel, rightKeypointsLevel};
+    uint8_t* D[2] = {leftKeypointsORB, rightKeypointsORB};
+    const int lens[2] = {std::min(std::min(leftKeypointsXLen, leftKeypointsYLen), std::min(std::min(leftKeypointsAngleLen, leftKeypointsLevelLen), leftKeypointsORBLen / 32)),
+                         std::min(std::min(rightKeypointsXLen, rightKeypointsYLen), std::min(std::min(rightKeypointsAngleLen, rightKeypointsLevelLen), rightKeypointsORBLen / 32))};
+    int status = ORBFE_OK;
+    for (int e = 0; e < 2; e++) {
+        if (!X[e] || !Y[e] || !A[e] || !Lv[e] || !D[e]) return ORBFE_ERR_ARG;
+        if (counts[e] > lens[e]) status = ORBFE_ERR_CAPACITY;
+        const int n = std::min(counts[e], lens[e]);
+        for (int i = 0; i < n; i++) {
+            const orbfe_keypoint& k = w->kps[(size_t)e * cap + i];
+            X[e][i] = (int)k.x;    // the wire carries integer pixel coordinates (LHA:170-171)
+            Y[e][i] = (int)k.y;
+            Lv[e][i] = k.octave;
+            const double rad = (double)k.angle * 3.14159265358979323846 / 180.0;
+            const int c8 = (int)lrint(std::cos(rad) * 64.0), s8 = (int)lrint(std::sin(rad) * 64.0);    // LHA:175-177
+            A[e][i] = ((s8 & 0xff) << 8) | (c8 & 0xff);
+        }
+        memcpy(D[e], &w->desc[(size_t)e * cap * 32], (size_t)n * 32);
+    }
+    if (totalPointsLeft) *totalPointsLeft = counts[0];
+    if (totalPointsRight) *totalPointsRight = counts[1];
+    if (monoLeft) *monoLeft = monos[0];
+    if (monoRight) *monoRight = monos[1];
+    // stereo parts: left (query) -> right (train), dsp/src/orbslam_dsp.cpp:746-800, consumed at Frame.cc:1164-1182
+    const int sl = counts[0] - monos[0], sr = counts[1] - monos[1];
+    if (indices && distances1 && distances2 && sl > 0 && monos[0] >= 0 && monos[1] >= 0) {
+        lk.unlock();
+        rc = orbslam3_bfMatchStereo(h, &w->desc[(size_t)monos[0] * 32], sl * 32, &w->desc[((size_t)cap + monos[1]) * 32],
+                                    std::max(sr, 0) * 32, indices, indicesLen, distances1, distances1Len, distances2,
+                                    distances2Len);
+        if (rc != ORBFE_OK) return rc;
+    }
+    return status;
+}
+
+}    // extern "C"

@@ -1,0 +1,114 @@
+// orbfe_internal.h — shared declarations of the liborbfe.so translation units (host + device).
+//
+// Data layout in HBM (DESIGN.md "Data layout"):
+//   pyramid slab   one per image; level l is a padded u8 plane of (h_l + 38) rows, `pitch_l` bytes per row
+//                  (multiple of 64).  The level's pixel (0,0) sits at row 19, column 32, so ROI rows start 16-byte
+//                  aligned; the REFLECT_101 frame of 19 px (ORBextractor_old.cc:1346-1352) occupies columns 13..31
+//                  and w+32..w+50.  Planes of one image are packed back to back (256-byte aligned).
+//   blurred slab   same geometry; only the w x h ROI is written (GaussianBlur output, ORBextractor_old.cc:1147).
+//   cell slots     per image, per FAST cell: `slotCap` packed candidates (x | y<<12 | response<<24, relative to
+//                  (minBorderX, minBorderY)) + one count per cell; cells are numbered level-major, row-major,
+//                  which is exactly the reference's insertion order (ORBextractor_old.cc:807-871).
+//   level keys     per image, per level: the post-octree keypoints (same packing) in std::list order + count.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/orbfe_c.h"
+
+namespace orbfe {
+
+constexpr int kEdge = 19;         // EDGE_THRESHOLD, ORBextractor_old.cc:75
+constexpr int kHalfPatch = 15;    // HALF_PATCH_SIZE, :74
+constexpr int kPatch = 31;        // PATCH_SIZE, :73
+constexpr int kXOff = 32;         // column of level pixel x = 0 inside a padded plane row
+constexpr int kMinBorder = 16;    // EDGE_THRESHOLD - 3, :791
+constexpr int kCellW = 35;        // W of ComputeKeyPointsOctTree, :787
+
+struct LevelGeom {
+    int w, h;            // level size (cvRound(cols * invScale), :1335)
+    int pitch;           // bytes per plane row
+    int nfeat;           // mnFeaturesPerLevel[l], :436-447
+    int nCols, nRows;    // FAST cell grid, :802-803
+    int wCell, hCell;    // :804-805
+    int cellBase;        // index of cell (0,0) of this level inside the image's cell array
+    int nIni;            // root nodes of DistributeOctTree, :561
+    int keyCap;          // capacity of the level's post-octree keypoint list
+    int keyBase;         // offset of that list inside the image's level-key array
+    int maxCand;         // upper bound of FAST candidates of the level (sum of cell capacities)
+    int scaledPatch;     // (int)(PATCH_SIZE * mvScaleFactor[l]), :891
+    float scale;         // mvScaleFactor[l]
+    float hX;            // (maxX - minX) / nIni, :563
+    unsigned long long planeOff;    // byte offset of the plane inside a slab
+};
+
+struct Geom {
+    int nlevels;
+    int width, height;
+    int iniTh, minTh;
+    int nCells;          // cells per image (all levels)
+    int slotCap;         // candidate capacity per cell
+    int keyTotal;        // level-key entries per image (sum of keyCap)
+    int outCap;          // == keyTotal: max keypoints per image
+    int maxCellW, maxCellH;    // largest cell sub-image (wCell + 6, hCell + 6) over the levels
+    unsigned long long slabBytes;    // bytes of one pyramid (or blurred) slab
+    LevelGeom lv[ORBFE_MAX_LEVELS];
+    int umax[kHalfPatch + 1];
+};
+
+// one FAST work item = a run of cells of one cell row (k_fast.cu)
+struct FastItem {
+    short level, row, col0, ncols;
+};
+
+// resize tables: per destination column / row (OpenCV linear resize coefficients)
+struct ResizeTap {
+    short s;         // source index (clamped)
+    short s1;        // second tap index (clamped to src - 1)
+    short a0, a1;    // weights * 2048
+};
+
+// per-image results of the pack step
+struct ImageResult {
+    int count;     // nkeypoints
+    int mono;      // monoIndex (ORBextractor_old.cc:1190)
+};
+
+// work record for the angle + descriptor kernel
+struct KpWork {
+    unsigned short x, y;    // level coordinates
+    unsigned char level, response;
+    unsigned short pad;
+    int dst;                // final row in the caller's keypoint / descriptor arrays
+};
+
+struct ExtractBuffers {
+    uint8_t* pyr;            // n slabs
+    uint8_t* blur;           // n slabs
+    uint32_t* slots;         // n * nCells * slotCap
+    int* cellCount;          // n * nCells
+    uint32_t* levelKeys;     // n * keyTotal
+    int* levelCount;         // n * nlevels
+    uint32_t* scratch;       // octree key ping-pong: n * scratchPerImage
+    unsigned long long scratchPerImage;
+    KpWork* work;            // n * outCap
+    ImageResult* result;     // n
+    int* errFlag;            // 1 int, device
+};
+
+// ---- kernel launchers (each returns the number of kernels it launched) ----
+int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size_t imageStride, uint8_t* pyr,
+                   const ResizeTap* const* xtab, const ResizeTap* const* ytab, cudaStream_t st);
+int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, uint32_t* slots,
+                int* cellCount, cudaStream_t st);
+int launch_octree(const Geom& g, int n, const ExtractBuffers& b, cudaStream_t st);
+int launch_blur(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, cudaStream_t st);
+int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st);
+int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                    cudaStream_t st);
+int launch_knn2(const uint8_t* q, const int* nq, int qCap, const uint8_t* t, const int* nt, int tCap, int npairs,
+                int64_t nqSingle, int64_t ntSingle, int32_t* idx, int32_t* dist, cudaStream_t st);
+
+size_t octree_smem_bytes(const Geom& g);
+
+}    // namespace orbfe

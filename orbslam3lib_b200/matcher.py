@@ -1,0 +1,89 @@
+"""Python mirror of the matcher call sites of the reference: cv::BFMatcher(NORM_HAMMING).knnMatch(query, train, 2)
+(Frame.cc:45,1227-1231) and LynxHardwareAccelerator::BFMatchORB (LynxHardwareAccelerator.cpp:206-213), on top of
+the C ABI (orbfe_knn2 / orbfe_knn2_batch)."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import OrbfeError, ptr
+
+
+class BFMatcher:
+    """BFMatcher(NORM_HAMMING) restricted to what the reference uses: knnMatch with k = 2 on 32-byte rows."""
+
+    def __init__(self, device=0):
+        self._h = None
+        h = C.c_void_p()
+        rc = _lib.lib().orbfe_matcher_create(int(device), C.byref(h))
+        if rc != _lib.OK:
+            raise OrbfeError(rc, "orbfe_matcher_create (no CUDA device?)")
+        self._h = h
+        self.device = int(device)
+
+    def close(self):
+        if self._h is not None:
+            _lib.lib().orbfe_matcher_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != _lib.OK:
+            raise OrbfeError(rc, _lib.lib().orbfe_matcher_last_error(self._h).decode())
+
+    def knnMatch(self, query, train, k=2):
+        """-> (idx int32 (nq, 2), dist int32 (nq, 2)); ties keep the lower train index first; missing = -1."""
+        if k != 2:
+            raise ValueError("the reference path uses k = 2 only (Frame.cc:1227)")
+        q = np.ascontiguousarray(query, np.uint8).reshape(-1, 32)
+        t = np.ascontiguousarray(train, np.uint8).reshape(-1, 32)
+        idx = np.full((q.shape[0], 2), -1, np.int32)
+        dist = np.full((q.shape[0], 2), -1, np.int32)
+        self._check(_lib.lib().orbfe_knn2(self._h, ptr(q), q.shape[0], ptr(t), t.shape[0], ptr(idx), ptr(dist), 0))
+        return idx, dist
+
+    def knn2_raw(self, q, nq, t, nt, idx, dist, flags=0):
+        """caller-owned buffers (numpy / torch host or device tensors / addresses)."""
+        self._check(_lib.lib().orbfe_knn2(self._h, ptr(q), int(nq), ptr(t), int(nt), ptr(idx), ptr(dist), int(flags)))
+
+    def knnMatchBatch(self, query, nq, train, nt):
+        """query (p, q_cap, 32), train (p, t_cap, 32), per-pair row counts nq / nt -> idx, dist (p, q_cap, 2)."""
+        q = np.ascontiguousarray(query, np.uint8)
+        t = np.ascontiguousarray(train, np.uint8)
+        p, qc, tc = q.shape[0], q.shape[1], t.shape[1]
+        nq = np.ascontiguousarray(nq, np.int32)
+        nt = np.ascontiguousarray(nt, np.int32)
+        idx = np.full((p, qc, 2), -1, np.int32)
+        dist = np.full((p, qc, 2), -1, np.int32)
+        self._check(_lib.lib().orbfe_knn2_batch(self._h, ptr(q), ptr(nq), qc, ptr(t), ptr(nt), tc, p, ptr(idx),
+                                                ptr(dist), 0))
+        return idx, dist
+
+    def knn2_batch_raw(self, q, nq, q_cap, t, nt, t_cap, npairs, idx, dist, flags=0):
+        self._check(_lib.lib().orbfe_knn2_batch(self._h, ptr(q), ptr(nq), int(q_cap), ptr(t), ptr(nt), int(t_cap),
+                                                int(npairs), ptr(idx), ptr(dist), int(flags)))
+
+    def last_ms(self):
+        ms, n = C.c_float(), C.c_int()
+        _lib.lib().orbfe_matcher_last_ms(self._h, C.byref(ms), C.byref(n))
+        return ms.value, n.value
+
+    @staticmethod
+    def ratio_test(idx, dist, ratio=0.7):
+        """Lowe ratio of Frame.cc:1230 -> int32 (nq,) best train index or -1."""
+        idx = np.ascontiguousarray(idx, np.int32)
+        dist = np.ascontiguousarray(dist, np.int32)
+        out = np.empty(idx.shape[0], np.int32)
+        _lib.lib().orbfe_ratio_test(ptr(idx), ptr(dist), idx.shape[0], float(ratio), ptr(out))
+        return out
+
+    def BFMatchORB(self, left_desc, right_desc):
+        """LynxHardwareAccelerator::BFMatchORB (LHA:206-213) as consumed at Frame.cc:1164-1182: per LEFT row the
+        best right index and the two smallest distances, uint16 like the reference vectors."""
+        idx, dist = self.knnMatch(left_desc, right_desc)
+        return idx[:, 0].astype(np.uint16), dist[:, 0].astype(np.uint16), dist[:, 1].astype(np.uint16)

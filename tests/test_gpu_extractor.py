@@ -1,0 +1,95 @@
+"""-m gpu: the CUDA extractor against the CPU oracle, stage by stage and end to end, through the C ABI.
+
+Bars (BASELINE.json north_star): bit-exact pyramid pixels, FAST responses, keypoint (x, y, octave) sets and order
+after distribution, descriptors; angles within 1e-3 degrees."""
+import numpy as np
+import pytest
+
+from orbslam3lib_b200 import ORBextractor, scenes
+
+pytestmark = pytest.mark.gpu
+
+ANGLE_TOL_DEG = 1e-3
+
+CASES = [
+    # kind, w, h, seed, nfeatures, nlevels
+    ("texture", 640, 480, 1000, 1000, 8),
+    ("texture", 752, 480, 1001, 1200, 8),
+    ("checker", 640, 480, 1002, 1000, 8),
+    ("noise", 320, 240, 1003, 500, 8),
+    ("flat_blobs", 752, 480, 1004, 1000, 8),
+    ("texture", 211, 173, 1005, 300, 5),
+    ("noise", 752, 480, 1006, 1200, 8),
+    ("texture", 1280, 720, 1007, 2000, 10),
+]
+
+
+def _compare(oracle, kind, w, h, seed, nf, nl, lap=(0, 0), stages=True):
+    img = scenes.make(kind, w, h, seed)
+    ref = oracle.OracleExtractor(nf, 1.2, nl, 20, 7)
+    mono_r, kps_r, desc_r = ref(img, lap)
+    ex = ORBextractor(nf, 1.2, nl, 20, 7)
+    mono_g, kps_g, desc_g = ex(img, lap)
+    if stages:
+        for l in range(nl):
+            assert ex.level_size(l) == ref.level_size(l), "level %d size" % l
+            np.testing.assert_array_equal(ex.level_padded(l), ref.level_padded(l), "padded pyramid level %d" % l)
+            cr, cg = ref.level_candidates(l), ex.level_candidates(l)
+            assert cg.shape == cr.shape, "level %d: %d FAST candidates, oracle %d" % (l, len(cg), len(cr))
+            np.testing.assert_array_equal(cg, cr, "FAST candidates level %d" % l)
+            kr, kg = ref.level_keypoints(l), ex.level_keypoints(l)
+            assert len(kg) == len(kr), "level %d: %d keypoints after the quadtree, oracle %d" % (l, len(kg), len(kr))
+            for f in ("x", "y", "response", "octave", "size"):
+                np.testing.assert_array_equal(kg[f], kr[f], "level %d keypoint field %s" % (l, f))
+            if len(kr):
+                np.testing.assert_array_equal(ex.level_blurred(l), ref.level_blurred(l), "blurred level %d" % l)
+                d = np.abs(kg["angle"] - kr["angle"])
+                d = np.minimum(d, 360.0 - d)
+                assert d.max() <= ANGLE_TOL_DEG, "level %d angle diff %g" % (l, d.max())
+    assert mono_g == mono_r
+    assert len(kps_g) == len(kps_r)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        np.testing.assert_array_equal(kps_g[f], kps_r[f], "keypoint field %s" % f)
+    d = np.abs(kps_g["angle"] - kps_r["angle"])
+    d = np.minimum(d, 360.0 - d)
+    assert len(d) == 0 or d.max() <= ANGLE_TOL_DEG
+    np.testing.assert_array_equal(desc_g, desc_r, "descriptors")
+    return len(kps_g), ref.sort_ties()
+
+
+@pytest.mark.parametrize("kind,w,h,seed,nf,nl", CASES)
+def test_extractor_matches_oracle(oracle, kind, w, h, seed, nf, nl):
+    n, ties = _compare(oracle, kind, w, h, seed, nf, nl)
+    assert n > 0
+
+
+def test_lapping_area_packing(oracle):
+    # ORBextractor_old.cc:1171-1180: keypoints inside vLappingArea go to the back
+    _compare(oracle, "texture", 640, 480, 1010, 1000, 8, lap=(200, 400), stages=False)
+    _compare(oracle, "texture", 640, 480, 1010, 1000, 8, lap=(0, 1000), stages=False)
+
+
+def test_batch_equals_single(oracle):
+    imgs = np.stack([scenes.make("texture", 640, 480, 2000 + i) for i in range(6)])
+    ex = ORBextractor(1000, 1.2, 8, 20, 7)
+    counts, monos, kps, desc = ex.extract_batch(imgs)
+    rc, rm, rk, rd = oracle.extract_batch(imgs, 1000, 1.2, 8, 20, 7, threads=4)
+    np.testing.assert_array_equal(counts, rc)
+    np.testing.assert_array_equal(monos, rm)
+    for i in range(len(imgs)):
+        n = counts[i]
+        for f in ("x", "y", "size", "response", "octave"):
+            np.testing.assert_array_equal(kps[i, :n][f], rk[i, :n][f])
+        np.testing.assert_array_equal(desc[i, :n], rd[i, :n])
+
+
+def test_chunked_batch(oracle):
+    # a tiny workspace limit forces several chunks; results must not depend on the chunking
+    imgs = np.stack([scenes.make("checker", 320, 240, 3000 + i) for i in range(5)])
+    ex = ORBextractor(500, 1.2, 8, 20, 7)
+    a = ex.extract_batch(imgs)
+    ex2 = ORBextractor(500, 1.2, 8, 20, 7)
+    ex2.set_workspace_limit(3 << 20)
+    b = ex2.extract_batch(imgs)
+    for x, y in zip(a, b):
+        np.testing.assert_array_equal(x, y)

@@ -1,0 +1,75 @@
+"""-m gpu: Hamming kNN (k = 2) against the CPU oracle through the C ABI: bit-exact indices and distances, ties
+broken by the lowest train index (OpenCV's order)."""
+import numpy as np
+import pytest
+
+from orbslam3lib_b200 import BFMatcher, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (7, 5), (500, 500), (1000, 1000), (1200, 1200), (300, 4099), (4096, 20000)])
+def test_knn2_matches_oracle(oracle, nq, nt):
+    q, t = scenes.map_descriptors(nq, nt, 77 + nq)
+    idx, dist = BFMatcher().knnMatch(q, t)
+    ri, rd = oracle.knn2_hamming(q, t, threads=4)
+    np.testing.assert_array_equal(idx, ri)
+    np.testing.assert_array_equal(dist, rd)
+
+
+def test_knn2_ties_lowest_index(oracle):
+    t = scenes.descriptors(2000, 5)
+    t[700] = t[5]
+    t[1500] = t[5]
+    q = t[[5, 5, 1500]].copy()
+    idx, dist = BFMatcher().knnMatch(q, t)
+    assert idx[0].tolist() == [5, 700] and dist[0].tolist() == [0, 0]
+    assert idx[2].tolist() == [5, 700]
+    # all-equal train set
+    t2 = np.repeat(t[:1], 300, axis=0)
+    idx, dist = BFMatcher().knnMatch(t[:3], t2)
+    assert (idx == np.array([0, 1])).all()
+
+
+def test_knn2_empty_and_short():
+    m = BFMatcher()
+    q = scenes.descriptors(4, 1)
+    idx, dist = m.knnMatch(q, np.zeros((0, 32), np.uint8))
+    assert (idx == -1).all() and (dist == -1).all()
+    idx, dist = m.knnMatch(q, q[:1])
+    assert (idx[:, 0] == 0).all() and (idx[:, 1] == -1).all() and (dist[:, 1] == -1).all()
+    idx, dist = m.knnMatch(np.zeros((0, 32), np.uint8), q)
+    assert idx.shape == (0, 2)
+
+
+def test_knn2_batch_matches_single(oracle):
+    p, cap = 6, 640
+    rng = np.random.default_rng(3)
+    nq = rng.integers(1, cap, p).astype(np.int32)
+    nt = rng.integers(2, cap, p).astype(np.int32)
+    nq[0], nt[0] = cap, cap
+    q = scenes.descriptors(p * cap, 11).reshape(p, cap, 32)
+    t = scenes.descriptors(p * cap, 12).reshape(p, cap, 32)
+    idx, dist = BFMatcher().knnMatchBatch(q, nq, t, nt)
+    for k in range(p):
+        ri, rd = oracle.knn2_hamming(q[k, :nq[k]], t[k, :nt[k]])
+        np.testing.assert_array_equal(idx[k, :nq[k]], ri)
+        np.testing.assert_array_equal(dist[k, :nq[k]], rd)
+        assert (idx[k, nq[k]:] == -1).all()
+
+
+def test_large_kernel_path(oracle):
+    # enough query rows for the thread-per-query kernel (>= 296 CTAs), checked on a sample of rows
+    q, t = scenes.map_descriptors(80000, 3000, 9)
+    idx, dist = BFMatcher().knnMatch(q, t)
+    sel = np.arange(0, 80000, 97)
+    ri, rd = oracle.knn2_hamming(q[sel], t, threads=4)
+    np.testing.assert_array_equal(idx[sel], ri)
+    np.testing.assert_array_equal(dist[sel], rd)
+
+
+def test_ratio_test():
+    idx = np.array([[3, 9], [4, -1], [5, 6]], np.int32)
+    dist = np.array([[10, 20], [5, -1], [70, 100]], np.int32)
+    out = BFMatcher.ratio_test(idx, dist, 0.7)
+    assert out.tolist() == [3, -1, -1]    # 10 < 14; no second neighbour; 70 < 70 is false
