@@ -72,13 +72,16 @@ __device__ __forceinline__ int fast9_score(const uint8_t* c, int tp) {
     for (int k = 0; k < 16; k++) { a[k] = min(mn[k], mn[(k + 2) & 15]); b[k] = max(mx[k], mx[(k + 2) & 15]); }
 #pragma unroll
     for (int k = 0; k < 16; k++) { mn[k] = min(a[k], a[(k + 4) & 15]); mx[k] = max(b[k], b[(k + 4) & 15]); }
-    int best = -1024;
+    // max over arcs of min(d) and min over arcs of max(d) are reduced separately and combined once: the per-arc form
+    // max(best, max(lo9, -hi9)) is miscompiled by nvcc 12.9 for sm_100a (unsigned VIMNMX on the negated operand;
+    // tools/dbg_fast_unit.cu reproduces it), and this form is also cheaper.
+    int dark = -1024, bright = 1024;
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-        const int lo9 = min(mn[k], d[(k + 8) & 15]);     // min of d[k..k+8]
-        const int hi9 = max(mx[k], d[(k + 8) & 15]);     // max of d[k..k+8]
-        best = max(best, max(lo9, -hi9));
+        dark = max(dark, min(mn[k], d[(k + 8) & 15]));       // min of d[k..k+8]
+        bright = min(bright, max(mx[k], d[(k + 8) & 15]));   // max of d[k..k+8]
     }
+    const int best = max(dark, -bright);
     return best - 1;
 }
 

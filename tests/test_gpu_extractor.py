@@ -91,5 +91,9 @@ def test_chunked_batch(oracle):
     ex2 = ORBextractor(500, 1.2, 8, 20, 7)
     ex2.set_workspace_limit(3 << 20)
     b = ex2.extract_batch(imgs)
-    for x, y in zip(a, b):
-        np.testing.assert_array_equal(x, y)
+    np.testing.assert_array_equal(a[0], b[0])
+    np.testing.assert_array_equal(a[1], b[1])
+    for i in range(len(imgs)):    # rows beyond counts[i] are unspecified
+        n = a[0][i]
+        np.testing.assert_array_equal(a[2][i, :n], b[2][i, :n])
+        np.testing.assert_array_equal(a[3][i, :n], b[3][i, :n])
