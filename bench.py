@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py — ORB front-end throughput on B200 (BASELINE.json metric: ORB frames/s + Hamming kNN Gpairs/s; %roofline).
+
+One "step" = one pass of the hot path over one batch of synthetic input.  Default workload = BASELINE.json
+configs[1] ("c2"): EuRoC-shaped 752x480 stereo pairs, 1200 features per image, 512 pairs per GPU: extraction of the
+1024 images (pyramid, per-cell FAST, quadtree, orientation, blur, rBRIEF) + left->right brute-force Hamming kNN (k=2).
+`value` is measured with the inputs resident in HBM; `e2e` goes through the same C-ABI calls with pinned HOST buffers
+(host->device and device->host copies inside the timed region).  `--impl reference` times the CPU oracle
+(oracle/cpp, the restatement of the reference's ORBextractor_old.cc + OpenCV primitives; the reference itself cannot
+be compiled here, DESIGN.md "Oracle") on the host cores on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, NFEAT, NLEVELS = 752, 480, 1200, 8
+# algorithmic bytes per 752x480 image (DESIGN.md "Roofline")
+ALGO_BYTES = {"pyramid": 1845634, "fast": 1117367, "blur": 2234734}
+
+
+def make_pairs(npairs, seed0):
+    from orbslam3lib_b200 import scenes
+    imgs = np.empty((2 * npairs, H, W), np.uint8)
+    for k in range(npairs):
+        left = scenes.make("texture", W, H, seed0 + k)
+        imgs[k] = left
+        imgs[npairs + k] = scenes.stereo_right(left, seed0 + k)
+    return imgs
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        self.proc = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag:
+                    break
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 6:
+                    continue
+                try:
+                    self.samples.append(float(f[0]))
+                    self.max_mhz = float(f[1])
+                except ValueError:
+                    continue
+                for n, v in zip(names, f[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+        except Exception:
+            pass
+
+    def stop(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_sample(npairs_sample, threads, budget_s=12.0):
+    """The CPU oracle on a bounded sample of the workload: frames/s and Gpairs/s on `threads` host threads."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+    import oracle_lib
+    oracle_lib.build()
+    imgs = make_pairs(npairs_sample, 1000)
+    t0 = time.perf_counter()
+    frames, pairs, reps = 0, 0, 0
+    while True:
+        counts, monos, kps, desc = oracle_lib.extract_batch(imgs, NFEAT, 1.2, NLEVELS, 20, 7, threads=threads)
+        for k in range(npairs_sample):
+            nq, nt = int(counts[k]), int(counts[npairs_sample + k])
+            oracle_lib.knn2_hamming(desc[k, :nq], desc[npairs_sample + k, :nt], threads=threads)
+            pairs += nq * nt
+        frames += 2 * npairs_sample
+        reps += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return frames / dt, pairs / dt * 1e-9, "%d stereo pairs 752x480 nf=1200 x %d repetitions (%.1f s)" % (npairs_sample, reps, dt)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+    import oracle_lib
+    oracle_lib.build()
+    cores = oracle_lib.hardware_threads()
+    sample = max(4, min(32, cores // 2))
+    imgs = make_pairs(sample, 1000)
+
+    def step():
+        counts, monos, kps, desc = oracle_lib.extract_batch(imgs, NFEAT, 1.2, NLEVELS, 20, 7, threads=cores)
+        p = 0
+        for k in range(sample):
+            nq, nt = int(counts[k]), int(counts[sample + k])
+            oracle_lib.knn2_hamming(desc[k, :nq], desc[sample + k, :nt], threads=cores)
+            p += nq * nt
+        return p
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    pairs = 0
+    for _ in range(args.steps):
+        pairs += step()
+    dt = time.perf_counter() - t0
+    fps = 2 * sample * args.steps / dt
+    line = {"impl": "reference", "metric": "orb_frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "c2: 752x480 stereo pairs, 1200 features, 8 levels, extraction + L->R Hamming kNN k=2",
+                       "sample_pairs_per_step": sample},
+            "knn_gpairs_per_s": pairs / dt * 1e-9,
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": "%d stereo pairs per step, all host threads (CPU oracle oracle/cpp; the reference's "
+                                       "own CPU extractor does not compile here)" % sample},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=512, help="stereo pairs per GPU per step (512 = BASELINE configs[1])")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from orbslam3lib_b200 import BFMatcher, ORBextractor, _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    P = args.pairs
+    n = 2 * P
+    imgs_np = make_pairs(P, 1000 + rank * P)    # every rank extracts its own frames: no data-path collective
+    h_imgs = torch.from_numpy(imgs_np).pin_memory()
+    d_imgs = h_imgs.to(dev)
+
+    ex = ORBextractor(NFEAT, 1.2, NLEVELS, 20, 7, device=local)
+    mt = BFMatcher(device=local)
+    stream = torch.cuda.current_stream().cuda_stream
+    ex.set_stream(stream)
+    mt.set_stream(stream)
+    cap = ex.max_keypoints
+    u8 = torch.uint8
+    d_kps = torch.zeros((n, cap, 28), dtype=u8, device=dev)
+    d_desc = torch.zeros((n, cap, 32), dtype=u8, device=dev)
+    d_counts = torch.zeros(n, dtype=torch.int32, device=dev)
+    d_monos = torch.zeros(n, dtype=torch.int32, device=dev)
+    d_idx = torch.zeros((P, cap, 2), dtype=torch.int32, device=dev)
+    d_dist = torch.zeros((P, cap, 2), dtype=torch.int32, device=dev)
+    h_kps = torch.zeros((n, cap, 28), dtype=u8).pin_memory()
+    h_desc = torch.zeros((n, cap, 32), dtype=u8).pin_memory()
+    h_counts = torch.zeros(n, dtype=torch.int32).pin_memory()
+    h_monos = torch.zeros(n, dtype=torch.int32).pin_memory()
+    h_idx = torch.zeros((P, cap, 2), dtype=torch.int32).pin_memory()
+    h_dist = torch.zeros((P, cap, 2), dtype=torch.int32).pin_memory()
+    FL = _lib.IN_DEVICE | _lib.OUT_DEVICE
+
+    def step_device():
+        ex.extract_batch_raw(d_imgs, n, W, H, d_kps, d_desc, cap, d_counts, d_monos, flags=FL)
+        st = ex.stage_ms()
+        mt.knn2_batch_raw(d_desc, d_counts, cap, d_desc[P:], d_counts[P:], cap, P, d_idx, d_dist, flags=FL)
+        st["knn"] = mt.last_ms()[0]
+        return st
+
+    def step_e2e():
+        ex.extract_batch_raw(h_imgs, n, W, H, h_kps, h_desc, cap, h_counts, h_monos, flags=0)
+        mt.knn2_batch_raw(h_desc, h_counts, cap, h_desc[P:], h_counts[P:], cap, P, h_idx, h_dist, flags=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        acc = {}
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            r = fn()
+            if r:
+                for k, v in r.items():
+                    acc[k] = acc.get(k, 0.0) + v
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, acc
+
+    for _ in range(args.warmup):
+        step_device()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = _lib.lib().orbfe_kernel_launches()
+    ms_dev, stages = timed(step_device, args.steps)
+    launches = int(_lib.lib().orbfe_kernel_launches() - l0)
+    counts = d_counts.cpu().numpy().astype(np.int64)
+    pairs_per_step = int((counts[:P] * counts[P:]).sum())
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    ms_e2e, _ = timed(step_e2e, args.steps)
+    clocks = sampler.stop()
+
+    if world > 1:
+        t = torch.tensor([float(pairs_per_step)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t)
+        pairs_all = float(t.item())
+    else:
+        pairs_all = float(pairs_per_step)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    frames = n * world * args.steps
+    fps = frames / (ms_dev * 1e-3)
+    fps_e2e = frames / (ms_e2e * 1e-3)
+    hbm_peak, peak_src, sm_mhz = peaks()
+    per = {k: v / args.steps for k, v in stages.items()}    # ms per step per stage on rank 0
+    total_stage = sum(per.values())
+    stage_report = {}
+    for k, v in per.items():
+        e = {"ms_per_step": round(v, 4), "share": round(v / total_stage, 4) if total_stage else None}
+        if k in ALGO_BYTES and v > 0:
+            gbs = ALGO_BYTES[k] * n / (v * 1e-3) * 1e-9
+            e["achieved_gbs"] = round(gbs, 1)
+            e["frac_hbm"] = round(gbs / hbm_peak, 4)
+        if k == "knn" and v > 0:
+            gp = pairs_per_step / (v * 1e-3) * 1e-9
+            e["gpairs_per_s"] = round(gp, 2)
+            # POPC pipe: 16 lanes/clk/SM measured (tools/ubench_pipes.cu), 8 POPC per pair, 148 SMs
+            e["frac_popc_pipe"] = round(gp / (148 * 2.0 * sm_mhz * 1e-3), 4)
+        stage_report[k] = e
+    hbm_stages = [k for k in ("pyramid", "fast", "blur") if per.get(k, 0) > 0]
+    dom = max(hbm_stages, key=lambda k: per[k])
+    launches_dom = NLEVELS if dom == "pyramid" else 1
+    achieved = ALGO_BYTES[dom] * n / (per[dom] * 1e-3) * 1e-9
+    line = {
+        "metric": "orb_frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "c2: EuRoC-shaped 752x480 stereo pairs, 1200 features/image, 8 levels, scale 1.2, FAST 20/7, "
+                               "%d pairs per GPU per step; extraction + left->right Hamming kNN k=2" % P,
+                   "pairs_per_gpu": P, "l2_policy": "inputs larger than L2 (%.0f MB of images per step)" % (imgs_np.nbytes / 1e6),
+                   "scene": "texture (seeded rectangles + box filter), right = row-dependent integer disparity"},
+        "knn_gpairs_per_s": pairs_all * args.steps / (ms_dev * 1e-3) * 1e-9,
+        "knn_pairs_per_step": pairs_all,
+        "keypoints_per_image": float(counts.mean()),
+        "e2e": {"value": fps_e2e, "unit": "frames/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": int(h_imgs.numel() + h_desc.numel() + 2 * h_counts.numel() * 4),
+                "d2h_bytes_per_step": int(h_kps.numel() + h_desc.numel() + 2 * n * 4 + h_idx.numel() * 4 + h_dist.numel() * 4)},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                     "launches_per_step": launches_dom,
+                     "note": "algorithmic bytes per image x images per step / CUDA-event time of the stage"},
+        "stages": stage_report,
+    }
+    if not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+        import oracle_lib
+        cores = oracle_lib.hardware_threads()
+        v, gp, sample = cpu_sample(max(4, min(32, cores // 2)), cores)
+        line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample,
+                                "knn_gpairs_per_s": gp}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -68,6 +68,10 @@ const char* orbfe_last_error(const orbfe_extractor* ex);
 /* upper bound on device workspace (bytes) the extractor may hold; batches are processed in chunks that fit.
  * Default 24 GiB. */
 int orbfe_extractor_set_workspace_limit(orbfe_extractor* ex, size_t bytes);
+/* run this extractor's copies and kernels on the caller's CUDA stream (a cudaStream_t passed as void*; e.g. the
+ * current PyTorch stream) instead of the private stream created by orbfe_extractor_create.  The caller keeps
+ * ownership of the stream.  NULL restores the private stream. */
+int orbfe_extractor_set_stream(orbfe_extractor* ex, void* cuda_stream);
 /* ctor-derived tables (ORBextractor_old.cc:416-470; getters of include/ORBextractor.h:61-82).  Each array holds
  * nlevels entries (umax: 16); null pointers are skipped. */
 int orbfe_extractor_tables(const orbfe_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
@@ -111,6 +115,7 @@ int orbfe_extractor_last_launches(const orbfe_extractor* ex);
 int orbfe_matcher_create(int device, orbfe_matcher** out);
 int orbfe_matcher_destroy(orbfe_matcher* m);
 const char* orbfe_matcher_last_error(const orbfe_matcher* m);
+int orbfe_matcher_set_stream(orbfe_matcher* m, void* cuda_stream); /* as orbfe_extractor_set_stream */
 /* q: nq x 32 bytes, t: nt x 32 bytes, row-major.  idx/dist: 2 entries per query row (best, second best);
  * equal distances keep the lower train index first (OpenCV's order); missing neighbours (nt < 2) are -1. */
 int orbfe_knn2(orbfe_matcher* m, const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt, int32_t* idx,

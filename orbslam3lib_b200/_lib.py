@@ -51,6 +51,8 @@ SYMBOLS = {
     "orbfe_extractor_create": (_i, [_i, C.POINTER(Params), C.POINTER(_vp)]),
     "orbfe_extractor_destroy": (_i, [_vp]),
     "orbfe_last_error": (C.c_char_p, [_vp]),
+    "orbfe_extractor_set_stream": (_i, [_vp, _vp]),
+    "orbfe_matcher_set_stream": (_i, [_vp, _vp]),
     "orbfe_extractor_set_workspace_limit": (_i, [_vp, _sz]),
     "orbfe_extractor_tables": (_i, [_vp] + [_vp] * 6),
     "orbfe_extractor_max_keypoints": (_i, [_vp]),

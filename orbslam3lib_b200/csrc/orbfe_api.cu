@@ -199,7 +199,8 @@ struct orbfe_extractor {
     int device = 0;
     orbfe_params params{};
     Tables tables;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;       // the stream in use
+    cudaStream_t ownStream = nullptr;    // the private stream (owned)
     cudaEvent_t ev[8] = {};
     std::mutex mu;
     std::string err;
@@ -402,10 +403,11 @@ int orbfe_extractor_create(int device, const orbfe_params* params, orbfe_extract
     ex->device = device;
     ex->params = *params;
     build_tables(*params, ex->tables);
-    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ex->ownStream, cudaStreamNonBlocking) != cudaSuccess) {
         delete ex;
         return ORBFE_ERR_CUDA;
     }
+    ex->stream = ex->ownStream;
     for (auto& e : ex->ev) cudaEventCreate(&e);
     *out = ex;
     return ORBFE_OK;
@@ -420,12 +422,21 @@ int orbfe_extractor_destroy(orbfe_extractor* ex) {
                       &ex->dKps, &ex->dDesc};
     for (DevBuf* b : bufs) b->release();
     for (auto& e : ex->ev) if (e) cudaEventDestroy(e);
-    if (ex->stream) cudaStreamDestroy(ex->stream);
+    if (ex->ownStream) cudaStreamDestroy(ex->ownStream);
     delete ex;
     return ORBFE_OK;
 }
 
 const char* orbfe_last_error(const orbfe_extractor* ex) { return ex ? ex->err.c_str() : "null extractor"; }
+
+int orbfe_extractor_set_stream(orbfe_extractor* ex, void* cuda_stream) {
+    if (!ex) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ex->mu);
+    cudaSetDevice(ex->device);
+    cudaStreamSynchronize(ex->stream);
+    ex->stream = cuda_stream ? (cudaStream_t)cuda_stream : ex->ownStream;
+    return ORBFE_OK;
+}
 
 int orbfe_extractor_set_workspace_limit(orbfe_extractor* ex, size_t bytes) {
     if (!ex || bytes == 0) return ORBFE_ERR_ARG;
@@ -680,7 +691,7 @@ int orbfe_extractor_last_launches(const orbfe_extractor* ex) { return ex ? ex->l
 // ---------------------------------------------------------------------------------------------------------------
 struct orbfe_matcher {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, ownStream = nullptr;
     cudaEvent_t ev[2] = {};
     std::mutex mu;
     std::string err;
@@ -775,10 +786,11 @@ int orbfe_matcher_create(int device, orbfe_matcher** out) {
     if (device < 0 || orbfe_device_count() <= device) return ORBFE_ERR_CUDA;
     orbfe_matcher* m = new orbfe_matcher();
     m->device = device;
-    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&m->ownStream, cudaStreamNonBlocking) != cudaSuccess) {
         delete m;
         return ORBFE_ERR_CUDA;
     }
+    m->stream = m->ownStream;
     cudaEventCreate(&m->ev[0]);
     cudaEventCreate(&m->ev[1]);
     *out = m;
@@ -793,8 +805,17 @@ int orbfe_matcher_destroy(orbfe_matcher* m) {
     for (DevBuf* b : bufs) b->release();
     cudaEventDestroy(m->ev[0]);
     cudaEventDestroy(m->ev[1]);
-    if (m->stream) cudaStreamDestroy(m->stream);
+    if (m->ownStream) cudaStreamDestroy(m->ownStream);
     delete m;
+    return ORBFE_OK;
+}
+
+int orbfe_matcher_set_stream(orbfe_matcher* m, void* cuda_stream) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    cudaSetDevice(m->device);
+    cudaStreamSynchronize(m->stream);
+    m->stream = cuda_stream ? (cudaStream_t)cuda_stream : m->ownStream;
     return ORBFE_OK;
 }
 

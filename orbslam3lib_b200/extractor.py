@@ -69,6 +69,10 @@ class ORBextractor:
         if rc != _lib.OK:
             raise OrbfeError(rc, _lib.lib().orbfe_last_error(self._h).decode())
 
+    def set_stream(self, cuda_stream):
+        """run on the caller's CUDA stream (int handle, e.g. torch.cuda.current_stream().cuda_stream); None = private."""
+        self._check(_lib.lib().orbfe_extractor_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
+
     def set_workspace_limit(self, nbytes):
         self._check(_lib.lib().orbfe_extractor_set_workspace_limit(self._h, int(nbytes)))
 

@@ -36,6 +36,9 @@ class BFMatcher:
         if rc != _lib.OK:
             raise OrbfeError(rc, _lib.lib().orbfe_matcher_last_error(self._h).decode())
 
+    def set_stream(self, cuda_stream):
+        self._check(_lib.lib().orbfe_matcher_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
+
     def knnMatch(self, query, train, k=2):
         """-> (idx int32 (nq, 2), dist int32 (nq, 2)); ties keep the lower train index first; missing = -1."""
         if k != 2:
