@@ -7,6 +7,7 @@
 // Floating point (DESIGN.md "Floating point"): IEEE fp32 with explicit round-to-nearest intrinsics so that nvcc
 // cannot contract a*b+c into an FMA; cos/sin are evaluated in double and rounded to float, exactly like the oracle.
 // These kernels gather from L2 (749 B + 512 B of reads per keypoint) and are not HBM-bound.
+#include <algorithm>
 #include <cfloat>
 
 #include "orb_pattern.h"
@@ -14,14 +15,14 @@
 
 namespace orbfe {
 
-__constant__ signed char c_pattern[1024];    // 256 x (x0,y0,x1,y1), ORBextractor_old.cc:151-409
+__device__ char4 d_pattern[256];    // 256 x (x0,y0,x1,y1), ORBextractor_old.cc:151-409 (global: loaded coalesced)
 
 void upload_pattern() {
-    static bool done[64] = {false};    // __constant__ memory is per device
+    static bool done[64] = {false};    // __device__ variables are per device
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !done[dev]) {
-        cudaMemcpyToSymbol(c_pattern, ORBFE_BIT_PATTERN_31, 1024);
+        cudaMemcpyToSymbol(d_pattern, ORBFE_BIT_PATTERN_31, 1024);
         if (dev >= 0 && dev < 64) done[dev] = true;
     }
 }
@@ -128,9 +129,17 @@ constexpr int DS_WARPS = 8;
 __global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
                                                                  orbfe_keypoint* __restrict__ kps,
                                                                  uint8_t* __restrict__ desc, int cap) {
+    // pattern in shared memory, transposed so that lane l reads test (8*l + bit) at word bit*32 + l (conflict free);
+    // (__constant__ reads would serialise: every lane needs a different address)
+    __shared__ char4 sPat[256];
+    {
+        const int t = threadIdx.x;    // blockDim.x == 256
+        sPat[(t & 7) * 32 + (t >> 3)] = d_pattern[t];
+    }
+    __syncthreads();
     const int img = blockIdx.y, lane = threadIdx.x & 31;
-    const int k = blockIdx.x * DS_WARPS + (threadIdx.x >> 5);
-    if (k >= b.result[img].count) return;
+    const int nk = b.result[img].count;
+    for (int k = blockIdx.x * DS_WARPS + (threadIdx.x >> 5); k < nk; k += gridDim.x * DS_WARPS) {
     const KpWork w = b.work[(size_t)img * g.outCap + k];
     const LevelGeom& L = g.lv[w.level];
     const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff + (size_t)(w.y + kEdge) * L.pitch + kXOff + w.x;
@@ -166,9 +175,8 @@ __global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_co
     uint32_t byte = 0;
 #pragma unroll
     for (int bit = 0; bit < 8; bit++) {
-        const int pi = (lane * 8 + bit) * 4;
-        const float x0 = (float)c_pattern[pi], y0 = (float)c_pattern[pi + 1];
-        const float x1 = (float)c_pattern[pi + 2], y1 = (float)c_pattern[pi + 3];
+        const char4 pt = sPat[bit * 32 + lane];
+        const float x0 = (float)pt.x, y0 = (float)pt.y, x1 = (float)pt.z, y1 = (float)pt.w;
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
         const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
@@ -205,6 +213,7 @@ __global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_co
             reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + w.dst)[lane] = word;
         }
     }
+    }    // keypoint loop
 }
 
 int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st) {
@@ -221,7 +230,10 @@ int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap
 int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
                     cudaStream_t st) {
     upload_pattern();
-    describe_kernel<<<dim3((g.outCap + DS_WARPS - 1) / DS_WARPS, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
+    // a few keypoints per warp so that the shared pattern load is amortised; small batches keep one keypoint per warp
+    const int full = (g.outCap + DS_WARPS - 1) / DS_WARPS;
+    const int gx = n >= 64 ? std::min(full, 24) : full;
+    describe_kernel<<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
     return 1;
 }
 

@@ -8,12 +8,13 @@
 // two cells — reproduced, not de-duplicated.
 //
 // Mapping: one CTA stages a run of up to 16 cells of one cell row (a strip of the level plane) into shared memory
-// with 16-byte coalesced loads; each warp then owns whole cells.  Per cell: (1) the 16 ring pixels of 32 positions
-// at a time are classified into a "brighter" and a "darker" 16-bit mask and a 9-run is detected with shifts/ANDs;
-// corner positions are compacted with __ballot_sync; (2) the compacted corners are scored 32 at a time (min/max
-// over the sixteen 9-arcs, computed with a log-step sliding window in registers) into a per-warp score tile;
-// (3) NMS + emission in raster order, again 32 positions at a time with __ballot_sync / __popc ranks, so the
-// output order is deterministic and equals OpenCV's.  Candidates go to the cell's fixed slot array as packed
+// with 16-byte coalesced loads; each warp then owns whole cells and works in three compaction stages, each 32
+// positions at a time with __ballot_sync / __popc ranks so that raster order is preserved:
+// (A) every tested pixel: opposite-pair rejection on ring pixels 0/8 and 4/12 (5 shared loads), survivors compacted;
+// (B) survivors: the 16 ring pixels are classified into a "brighter" and a "darker" 16-bit mask, a 9-run is detected
+//     with shifts/ANDs, corners are scored (min/max over the sixteen 9-arcs with a log-step sliding window in
+//     registers) into a per-warp score tile and compacted in place;
+// (C) corners: 3x3 NMS on the score tile + emission, so the output order is deterministic and equals OpenCV's.  Candidates go to the cell's fixed slot array as packed
 // (x | y << 12 | response << 24), coordinates relative to (minBorderX, minBorderY) as in :865-870.
 //
 // HBM-bound by design (reads P bytes per image once; the 6-px overlaps hit L1/L2); integer only.
@@ -91,7 +92,7 @@ __global__ void __launch_bounds__(32 * FAST_WARPS) fast_cells_kernel(const __gri
                                                                       const FastItem* __restrict__ items,
                                                                       uint32_t* __restrict__ slots,
                                                                       int* __restrict__ cellCount, int tileBytes,
-                                                                      int scoreBytes) {
+                                                                      int scoreBytes, int listBytes) {
     extern __shared__ __align__(16) uint8_t smem[];
     const FastItem it = items[blockIdx.x];
     const int img = blockIdx.y;
@@ -127,8 +128,8 @@ __global__ void __launch_bounds__(32 * FAST_WARPS) fast_cells_kernel(const __gri
     }
     __syncthreads();
 
-    uint8_t* score = smem + tileBytes + warp * (scoreBytes + 128);
-    unsigned short* list = reinterpret_cast<unsigned short*>(score + scoreBytes);
+    uint8_t* score = smem + tileBytes + warp * (scoreBytes + listBytes);
+    unsigned short* list = reinterpret_cast<unsigned short*>(score + scoreBytes);    // (cy << 8 | cx) entries
 
     for (int jc = warp; jc < it.ncols; jc += FAST_WARPS) {
         const int j = it.col0 + jc;
@@ -139,53 +140,68 @@ __global__ void __launch_bounds__(32 * FAST_WARPS) fast_cells_kernel(const __gri
             const int cw = maxX - iniX;
             const int tw = cw - 6, th = ch - 6;
             const int npix = tw * th;
-            const uint8_t* cell = tile + (kXOff + iniX - ax0);    // cell(0,0); rows tp apart
+            const uint8_t* cell = tile + (kXOff + iniX - ax0) + 3 * tp + 3;    // first tested pixel; rows tp apart
+            uint8_t* sc0 = score + 3 * cw + 3;                                   // its score
             uint32_t* out = slots + ((size_t)img * g.nCells + cellRowBase + j) * g.slotCap;
             const int xAdd = j * L.wCell + 3, yAdd = it.row * L.hCell + 3;
+            const int cy0 = lane / tw, cx0 = lane - cy0 * tw;
             for (int pass = 0; pass < 2; pass++) {
                 const int t = min(max(pass == 0 ? g.iniTh : g.minTh, 0), 255);
                 for (int i = lane; i < (cw * ch + 3) / 4; i += 32) reinterpret_cast<uint32_t*>(score)[i] = 0;
+                // stage A: opposite-pair rejection on every tested pixel (a 9-arc contains one pixel of each
+                // opposite pair), survivors compacted in raster order
+                int nA = 0;
+                {
+                    int cx = cx0, cy = cy0;
+                    for (int base = 0; base < npix; base += 32) {
+                        bool pass2 = false;
+                        if (base + lane < npix) {
+                            const uint8_t* c = cell + cy * tp + cx;
+                            const int v = c[0], lo = v - t, hi = v + t;
+                            const int p0 = c[3 * tp], p8 = c[-3 * tp];
+                            if ((p0 < lo) | (p0 > hi) | (p8 < lo) | (p8 > hi)) {
+                                const int p4 = c[3], p12 = c[-3];
+                                pass2 = (p4 < lo) | (p4 > hi) | (p12 < lo) | (p12 > hi);
+                            }
+                        }
+                        const uint32_t m = __ballot_sync(0xffffffffu, pass2);
+                        if (pass2) list[nA + __popc(m & ltMask)] = (unsigned short)((cy << 8) | cx);
+                        nA += __popc(m);
+                        cx += 32;
+                        while (cx >= tw) { cx -= tw; cy++; }
+                    }
+                }
                 __syncwarp();
-                int cnt = 0;
-                for (int base = 0; base < npix; base += 32) {
-                    const int p = base + lane;
+                // stage B: full FAST-9 test + score on the survivors; corners compacted in place (writes trail reads)
+                int nC = 0;
+                for (int base = 0; base < nA; base += 32) {
+                    const int i = base + lane;
                     bool corner = false;
-                    if (p < npix) {
-                        const int cy = p / tw, cx = p - cy * tw;
-                        corner = fast9_is_corner(cell + (cy + 3) * tp + cx + 3, tp, t);
+                    unsigned short e = 0;
+                    if (i < nA) {
+                        e = list[i];
+                        const int cy = e >> 8, cx = e & 0xff;
+                        const uint8_t* c = cell + cy * tp + cx;
+                        corner = fast9_is_corner(c, tp, t);
+                        if (corner) sc0[cy * cw + cx] = (uint8_t)fast9_score(c, tp);
                     }
                     const uint32_t m = __ballot_sync(0xffffffffu, corner);
-                    if (corner) list[cnt + __popc(m & ltMask)] = (unsigned short)p;
-                    cnt += __popc(m);
                     __syncwarp();
-                    if (cnt >= 32) {
-                        const int q = list[lane];
-                        const int cy = q / tw, cx = q - cy * tw;
-                        score[(cy + 3) * cw + cx + 3] = (uint8_t)fast9_score(cell + (cy + 3) * tp + cx + 3, tp);
-                        const int rest = cnt - 32;
-                        const unsigned short mv = lane < rest ? list[32 + lane] : 0;
-                        __syncwarp();
-                        if (lane < rest) list[lane] = mv;
-                        cnt = rest;
-                        __syncwarp();
-                    }
-                }
-                if (lane < cnt) {
-                    const int q = list[lane];
-                    const int cy = q / tw, cx = q - cy * tw;
-                    score[(cy + 3) * cw + cx + 3] = (uint8_t)fast9_score(cell + (cy + 3) * tp + cx + 3, tp);
+                    if (corner) list[nC + __popc(m & ltMask)] = e;
+                    nC += __popc(m);
                 }
                 __syncwarp();
-                // non-max suppression + ordered emission
+                // stage C: 3x3 non-max suppression on the corners + emission in raster order
                 total = 0;
-                for (int base = 0; base < npix; base += 32) {
-                    const int p = base + lane;
+                for (int base = 0; base < nC; base += 32) {
+                    const int i = base + lane;
                     bool keep = false;
                     int cx = 0, cy = 0, s = 0;
-                    if (p < npix) {
-                        cy = p / tw;
-                        cx = p - cy * tw;
-                        const uint8_t* sp = score + (cy + 3) * cw + cx + 3;
+                    if (i < nC) {
+                        const unsigned short e = list[i];
+                        cy = e >> 8;
+                        cx = e & 0xff;
+                        const uint8_t* sp = sc0 + cy * cw + cx;
                         s = sp[0];
                         keep = s > 0 && s > sp[-1] && s > sp[1] && s > sp[-cw - 1] && s > sp[-cw] && s > sp[-cw + 1] &&
                                s > sp[cw - 1] && s > sp[cw] && s > sp[cw + 1];
@@ -206,7 +222,7 @@ __global__ void __launch_bounds__(32 * FAST_WARPS) fast_cells_kernel(const __gri
 }
 
 // host: work items of one geometry.  Every cell row of every level is cut into runs of <= FAST_ITEM_COLS cells.
-int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* scoreBytes) {
+int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* scoreBytes, int* listBytes) {
     int n = 0, maxTile = 16, maxScore = 4;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& L = g.lv[l];
@@ -224,22 +240,23 @@ int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* 
     }
     *tileBytes = (maxTile + 15) & ~15;
     *scoreBytes = (maxScore + 15) & ~15;
+    *listBytes = (2 * maxScore + 15) & ~15;    // one u16 per tested pixel (< cell area)
     return n;
 }
 
-int fast_smem_bytes(int tileBytes, int scoreBytes) { return tileBytes + FAST_WARPS * (scoreBytes + 128); }
+int fast_smem_bytes(int tileBytes, int scoreBytes, int listBytes) { return tileBytes + FAST_WARPS * (scoreBytes + listBytes); }
 
 int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, int tileBytes,
-                int scoreBytes, uint32_t* slots, int* cellCount, cudaStream_t st) {
+                int scoreBytes, int listBytes, uint32_t* slots, int* cellCount, cudaStream_t st) {
     if (nItems <= 0) return 0;
-    const int smem = fast_smem_bytes(tileBytes, scoreBytes);
+    const int smem = fast_smem_bytes(tileBytes, scoreBytes, listBytes);
     static int configured = 0;
     if (smem > 48 * 1024 && configured < smem) {
         cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
     fast_cells_kernel<<<dim3(nItems, n), 32 * FAST_WARPS, smem, st>>>(g, pyr, items, slots, cellCount, tileBytes,
-                                                                      scoreBytes);
+                                                                      scoreBytes, listBytes);
     return 1;
 }
 

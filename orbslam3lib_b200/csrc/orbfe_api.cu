@@ -15,10 +15,10 @@
 
 namespace orbfe {
 // launchers defined in the kernel files
-int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* scoreBytes);
-int fast_smem_bytes(int tileBytes, int scoreBytes);
+int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* scoreBytes, int* listBytes);
+int fast_smem_bytes(int tileBytes, int scoreBytes, int listBytes);
 int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, int tileBytes,
-                int scoreBytes, uint32_t* slots, int* cellCount, cudaStream_t st);
+                int scoreBytes, int listBytes, uint32_t* slots, int* cellCount, cudaStream_t st);
 size_t octree_smem_bytes(int nodeCap, int keySmem);
 int launch_octree(const Geom& g, int n, const ExtractBuffers& b, int nodeCap, int keySmem, cudaStream_t st);
 struct BlurTile { short level, tx, ty, pad; };
@@ -209,7 +209,7 @@ struct orbfe_extractor {
     // geometry of the current image size
     bool haveGeom = false;
     Geom geom{};
-    int nItems = 0, tileBytes = 0, scoreBytes = 0, nBlurTiles = 0, nodeCap = 0, keySmem = 0;
+    int nItems = 0, tileBytes = 0, scoreBytes = 0, listBytes = 0, nBlurTiles = 0, nodeCap = 0, keySmem = 0;
     DevBuf dItems, dBlurTiles, dTaps;
     const ResizeTap* xtab[ORBFE_MAX_LEVELS] = {};
     const ResizeTap* ytab[ORBFE_MAX_LEVELS] = {};
@@ -261,12 +261,12 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
         return set_err(ex, ORBFE_ERR_ARG, "image %dx%d too large: candidate coordinates are packed in 12 bits", w, h);
     // FAST work items
     std::vector<FastItem> items;
-    int tb = 0, sb = 0;
-    const int nItems = fast_item_table(g, nullptr, 0, &tb, &sb);
+    int tb = 0, sb = 0, lb = 0;
+    const int nItems = fast_item_table(g, nullptr, 0, &tb, &sb, &lb);
     items.resize(std::max(nItems, 1));
-    fast_item_table(g, items.data(), nItems, &tb, &sb);
-    if (fast_smem_bytes(tb, sb) > 220 * 1024)
-        return set_err(ex, ORBFE_ERR_ARG, "FAST cell strip does not fit shared memory (%d bytes)", fast_smem_bytes(tb, sb));
+    fast_item_table(g, items.data(), nItems, &tb, &sb, &lb);
+    if (fast_smem_bytes(tb, sb, lb) > 220 * 1024 || g.maxCellW > 255 || g.maxCellH > 255)
+        return set_err(ex, ORBFE_ERR_ARG, "FAST cell strip does not fit shared memory (%d bytes)", fast_smem_bytes(tb, sb, lb));
     // blur tiles
     std::vector<BlurTile> tiles;
     const int nTiles = blur_tile_table(g, nullptr, 0);
@@ -307,6 +307,7 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
     ex->nItems = nItems;
     ex->tileBytes = tb;
     ex->scoreBytes = sb;
+    ex->listBytes = lb;
     ex->nBlurTiles = nTiles;
     ex->nodeCap = nodeCap;
     ex->keySmem = keySmem;
@@ -362,7 +363,7 @@ static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int str
     launches += launch_pyramid(g, dImages, n, stride, imageStride, ex->bufs.pyr, ex->xtab, ex->ytab, st);
     cudaEventRecord(ex->ev[2], st);
     launches += launch_fast(g, ex->bufs.pyr, n, (const FastItem*)ex->dItems.p, ex->nItems, ex->tileBytes, ex->scoreBytes,
-                            ex->bufs.slots, ex->bufs.cellCount, st);
+                            ex->listBytes, ex->bufs.slots, ex->bufs.cellCount, st);
     cudaEventRecord(ex->ev[3], st);
     launches += launch_octree(g, n, ex->bufs, ex->nodeCap, ex->keySmem, st);
     cudaEventRecord(ex->ev[4], st);
