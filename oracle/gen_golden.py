@@ -1,0 +1,136 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz from GENUINE OpenCV (cv2) + the Python restatement of the ORB-SLAM glue
+(oracle/py/cv2_oracle.py).  Test infrastructure.
+
+The reference ships no golden vectors for this path and its CPU extractor cannot be compiled here,
+so the fixtures pin the C++ oracle (and, through it, the CUDA path) against real OpenCV primitives: cv2.resize,
+cv2.copyMakeBorder, cv2.FastFeatureDetector, cv2.GaussianBlur, cv2.fastAtan2, cv2.BFMatcher.  cv2 exists only in the
+build container; the fixtures travel, this script does not need to.
+
+    python oracle/gen_golden.py          # rewrites tests/golden/
+"""
+import hashlib
+import os
+import re
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+# (name, scene, w, h, seed, nfeatures, nlevels, iniTh, minTh, lapping)
+EXTRACT_CASES = [
+    ("texture_320x240", "texture", 320, 240, 4001, 400, 6, 20, 7, (0, 0)),
+    ("checker_256x200", "checker", 256, 200, 4002, 300, 5, 20, 7, (60, 180)),
+    ("blobs_376x240", "flat_blobs", 376, 240, 4003, 500, 8, 20, 7, (0, 0)),
+    ("noise_160x120", "noise", 160, 120, 4004, 200, 4, 20, 7, (0, 1000)),
+    ("texture_640x480", "texture", 640, 480, 1000, 1000, 8, 20, 7, (0, 0)),    # BASELINE configs[0] shape
+]
+
+
+def load_pattern():
+    src = open(os.path.join(ROOT, "orbslam3lib_b200", "csrc", "orb_pattern.h")).read()
+    body = src[src.index("{") + 1:src.rindex("}")]
+    vals = [int(v) for v in re.findall(r"-?\d+", body)]
+    assert len(vals) == 1024
+    return np.array(vals, np.int8)
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def gen_extract(case):
+    import cv2
+    import cv2_oracle
+    from orbslam3lib_b200 import scenes
+    name, kind, w, h, seed, nf, nl, ini, mn, lap = case
+    img = scenes.make(kind, w, h, seed)
+    ex = cv2_oracle.Cv2Extractor(nf, 1.2, nl, ini, mn)
+    ex.set_pattern(load_pattern())
+    mono, kps, desc = ex(img, lap)
+    out = {
+        "meta": np.array([w, h, seed, nf, nl, ini, mn, lap[0], lap[1]], np.int64),
+        "scene": np.array(kind),
+        "opencv_version": np.array(cv2.__version__),
+        "image_sha256": np.array(sha(img)),
+        "mono": np.array(mono, np.int32),
+        "kps": np.array([[k[0], k[1], k[2], k[3], k[4]] for k in kps], np.float32).reshape(-1, 5),
+        "octave": np.array([k[5] for k in kps], np.int32),
+        "desc": desc,
+        "features_per_level": np.array(ex.features_per_level, np.int32),
+        "umax": np.array(ex.umax, np.int32),
+        "scale": np.array(ex.scale, np.float32),
+    }
+    for l in range(nl):
+        out["padded_sha256_%d" % l] = np.array(sha(ex.pyr_padded[l]))
+        out["level_size_%d" % l] = np.array(ex.pyr[l].shape[::-1], np.int32)
+        out["cand_%d" % l] = np.array(ex.candidates[l], np.int32).reshape(-1, 3)
+        lk = ex.level_kps[l]
+        out["lkps_%d" % l] = np.array([[k[0], k[1], k[3], k[4]] for k in lk], np.float32).reshape(-1, 4)
+        if ex.blurred[l] is not None:
+            out["blur_sha256_%d" % l] = np.array(sha(ex.blurred[l]))
+    # one small level stored verbatim so that a hash mismatch can be localised
+    out["padded_last"] = ex.pyr_padded[nl - 1]
+    np.savez_compressed(os.path.join(GOLDEN, "extract_%s.npz" % name), **out)
+    print("extract_%s: %d keypoints, mono %d" % (name, len(kps), mono))
+
+
+def gen_primitives():
+    import cv2
+    from orbslam3lib_b200 import scenes
+    out = {"opencv_version": np.array(cv2.__version__)}
+    # resize: every (src -> dst) step of a 1.2 pyramid on an awkward size + a generic pair
+    src = scenes.make("noise", 211, 173, 5001)
+    sizes = [(176, 144), (147, 120), (97, 61), (210, 172), (106, 87)]
+    out["resize_src_meta"] = np.array([211, 173, 5001], np.int64)
+    out["resize_sizes"] = np.array(sizes, np.int32)
+    for i, (dw, dh) in enumerate(sizes):
+        out["resize_%d" % i] = cv2.resize(src, (dw, dh), 0, 0, cv2.INTER_LINEAR)
+    out["border"] = cv2.copyMakeBorder(src[:40, :50].copy(), 19, 19, 19, 19, cv2.BORDER_REFLECT_101)
+    small = scenes.make("texture", 123, 77, 5002)
+    out["blur_meta"] = np.array([123, 77, 5002], np.int64)
+    out["blur"] = cv2.GaussianBlur(small, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+    out["blur_noise"] = cv2.GaussianBlur(src, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+    # FAST on cell-sized crops, both thresholds, order included
+    for kind, seed in (("noise", 5003), ("texture", 5004), ("checker", 5005)):
+        cell = scenes.make(kind, 41, 43, seed)
+        for t in (7, 20):
+            det = cv2.FastFeatureDetector_create(t, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+            kp = det.detect(cell)
+            out["fast_%s_%d" % (kind, t)] = np.array([[int(k.pt[0]), int(k.pt[1]), int(k.response)] for k in kp],
+                                                      np.int32).reshape(-1, 3)
+    out["fast_meta"] = np.array([41, 43], np.int64)
+    # fastAtan2 on moment-like inputs
+    r = scenes.rand_u32(4000, 5006).astype(np.int64)
+    ys = (r[:2000] % 200001 - 100000).astype(np.float32)
+    xs = (r[2000:] % 200001 - 100000).astype(np.float32)
+    ys[:8] = [0, 0, 1, -1, 5, -5, 0, 3]
+    xs[:8] = [0, 1, 0, 0, 5, -5, -7, 3]
+    out["atan_y"], out["atan_x"] = ys, xs
+    out["atan"] = np.array([cv2.fastAtan2(float(y), float(x)) for y, x in zip(ys, xs)], np.float32)
+    # BFMatcher kNN (ties included)
+    q, t = scenes.map_descriptors(300, 700, 5007)
+    m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, t, k=2)
+    out["knn_meta"] = np.array([300, 700, 5007], np.int64)
+    out["knn_idx"] = np.array([[d.trainIdx for d in row] for row in m], np.int32)
+    out["knn_dist"] = np.array([[int(d.distance) for d in row] for row in m], np.int32)
+    np.savez_compressed(os.path.join(GOLDEN, "primitives.npz"), **out)
+    print("primitives: ok")
+
+
+def main():
+    os.makedirs(GOLDEN, exist_ok=True)
+    gen_primitives()
+    for c in EXTRACT_CASES:
+        gen_extract(c)
+    pat = load_pattern()
+    open(os.path.join(GOLDEN, "pattern.sha256"), "w").write(hashlib.sha256(pat.tobytes()).hexdigest() + "\n")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,34 @@
+"""-m gpu: the CUDA path (through the C ABI) against the committed golden fixtures (cv2-generated, tests/golden/):
+independent of the oracle library, so a defect shared by oracle and kernels cannot hide."""
+import os
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+from orbslam3lib_b200 import BFMatcher, ORBextractor, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("path", gu.extract_fixtures(), ids=lambda p: os.path.basename(p)[8:-4])
+def test_extractor_fixture(path):
+    g = gu.load(path)
+    w, h, seed, nf, nl, ini, mn, lap0, lap1 = [int(v) for v in g["meta"]]
+    img = scenes.make(str(g["scene"]), w, h, seed)
+    ex = ORBextractor(nf, 1.2, nl, ini, mn)
+    mono, kps, desc = ex(img, (lap0, lap1))
+    np.testing.assert_array_equal(ex.features_per_level, g["features_per_level"])
+    np.testing.assert_array_equal(ex.umax, g["umax"])
+    np.testing.assert_array_equal(ex.GetScaleFactors(), g["scale"])
+    gu.check_extractor_against_fixture(ex, g, img)
+    gu.check_outputs_against_fixture(mono, kps, desc, g)
+
+
+def test_knn_fixture():
+    g = gu.load(os.path.join(gu.GOLDEN, "primitives.npz"))
+    nq, nt, seed = [int(v) for v in g["knn_meta"]]
+    q, t = scenes.map_descriptors(nq, nt, seed)
+    idx, dist = BFMatcher().knnMatch(q, t)
+    np.testing.assert_array_equal(idx, g["knn_idx"])
+    np.testing.assert_array_equal(dist, g["knn_dist"])
