@@ -6,8 +6,17 @@
 // coordinate first.  The resize arithmetic is OpenCV's 8-bit fixed-point INTER_LINEAR; the
 // per-column / per-row taps are precomputed on the host exactly as cv::resize does (orbfe_api.cu: build_taps).
 //
-// HBM-bound ((P - P_last) + (P - P_0) bytes per image).  Each thread produces 4 adjacent bytes and
-// issues one 32-bit store; source reads go through L1 (a 4-byte output group touches <= 6 source bytes per row).
+// HBM-bound by bytes ((P - P_last) + (P - P_0) bytes per image); the work is organised to spend as few
+// instructions per pixel as possible:
+//   * pad_level0_kernel: 16 bytes per thread, aligned 128-bit loads/stores in the interior, byte path on the frame;
+//   * resize_tile_kernel: one CTA = a 256 x (4*RPT) tile of the padded destination plane.  The source window is staged
+//     in shared memory with 128-bit loads, twice: as is and shifted by one byte, so that the horizontal pair
+//     (S[s], S[s+1]) of any tap is ONE aligned 16-bit shared load.  A thread owns 4 adjacent destination columns
+//     (taps in registers) and walks down its rows: horizontal pass = one IDP.2A per pixel (a0*S[s] + a1*S[s+1]),
+//     kept in registers and re-used by the next destination row when it shares the source row (ratio 1.2: 1.2
+//     horizontal passes per output row instead of 2); vertical pass in registers; one 32-bit store per 4 pixels.
+#include <algorithm>
+
 #include "orbfe_internal.h"
 
 namespace orbfe {
@@ -21,72 +30,217 @@ __device__ __forceinline__ int reflect101(int p, int len) {    // cv::borderInte
     return p;
 }
 
-// grid: (ceil(words / 64), ceil(rows / 4), n); block (64, 4)
+// range [lo, hi] of reflect101(x, len) for x in [xa, xb] (xa <= xb, |overhang| < len)
+__device__ __forceinline__ void reflect_range(int xa, int xb, int len, int& lo, int& hi) {
+    lo = len;
+    hi = -1;
+    const int ia = max(xa, 0), ib = min(xb, len - 1);
+    if (ia <= ib) { lo = ia; hi = ib; }
+    if (xa < 0) {
+        const int a = reflect101(min(xb, -1), len), b = reflect101(xa, len);
+        lo = min(lo, min(a, b));
+        hi = max(hi, max(a, b));
+    }
+    if (xb >= len) {
+        const int a = reflect101(xb, len), b = reflect101(max(xa, len), len);
+        lo = min(lo, min(a, b));
+        hi = max(hi, max(a, b));
+    }
+}
+
+// grid: (ceil(chunks / 64), ceil(rows / 4), n); block (64, 4); one 16-byte chunk of the padded plane per thread
 __global__ void __launch_bounds__(256) pad_level0_kernel(const uint8_t* __restrict__ images, int stride,
                                                          size_t imageStride, uint8_t* __restrict__ pyr,
                                                          unsigned long long slabBytes, int w, int h, int pitch) {
-    const int wx = blockIdx.x * 64 + threadIdx.x;
+    const int cx = blockIdx.x * 64 + threadIdx.x;
     const int py = blockIdx.y * 4 + threadIdx.y;
     if (py >= h + 2 * kEdge) return;
-    const int c0 = 4 * wx;
-    if (c0 + 3 < kXOff - kEdge || c0 >= kXOff + w + kEdge) return;
+    const int c0 = 16 * cx;
+    if (c0 + 15 < kXOff - kEdge || c0 >= kXOff + w + kEdge) return;
     const uint8_t* src = images + (size_t)blockIdx.z * imageStride + (size_t)reflect101(py - kEdge, h) * stride;
-    uint32_t out = 0;
-#pragma unroll
-    for (int b = 0; b < 4; b++) {
-        const int x = c0 + b - kXOff;
-        uint32_t v = 0;
-        if (x >= -kEdge && x < w + kEdge) v = __ldg(src + reflect101(x, w));
-        out |= v << (8 * b);
+    uint4* dst = reinterpret_cast<uint4*>(pyr + (size_t)blockIdx.z * slabBytes + (size_t)py * pitch + c0);
+    const int x0 = c0 - kXOff;
+    if (x0 >= 0 && x0 + 16 <= w && ((reinterpret_cast<uintptr_t>(src + x0) & 15) == 0)) {
+        *dst = __ldg(reinterpret_cast<const uint4*>(src + x0));
+        return;
     }
-    *reinterpret_cast<uint32_t*>(pyr + (size_t)blockIdx.z * slabBytes + (size_t)py * pitch + c0) = out;
+    uint32_t o[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        uint32_t out = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const int x = x0 + 4 * q + b;
+            uint32_t v = 0;
+            if (x >= -kEdge && x < w + kEdge) v = __ldg(src + reflect101(x, w));
+            out |= v << (8 * b);
+        }
+        o[q] = out;
+    }
+    *dst = make_uint4(o[0], o[1], o[2], o[3]);
 }
 
-// grid: (ceil(words / 64), ceil(rows / 4), n); block (64, 4).  src/dst point at the planes of image 0.
-__global__ void __launch_bounds__(256) resize_level_kernel(const uint8_t* __restrict__ srcPlane, int spitch,
-                                                           uint8_t* __restrict__ dstPlane, int dpitch,
-                                                           unsigned long long slabBytes, int dw, int dh,
-                                                           const ResizeTap* __restrict__ xtab,
-                                                           const ResizeTap* __restrict__ ytab) {
-    const int wx = blockIdx.x * 64 + threadIdx.x;
-    const int py = blockIdx.y * 4 + threadIdx.y;
-    if (py >= dh + 2 * kEdge) return;
-    const int c0 = 4 * wx;
-    if (c0 + 3 < kXOff - kEdge || c0 >= kXOff + dw + kEdge) return;
-    const ResizeTap yt = ytab[reflect101(py - kEdge, dh)];
-    const uint8_t* s0 = srcPlane + (size_t)blockIdx.z * slabBytes + (size_t)(yt.s + kEdge) * spitch + kXOff;
-    const uint8_t* s1 = srcPlane + (size_t)blockIdx.z * slabBytes + (size_t)(yt.s1 + kEdge) * spitch + kXOff;
-    uint32_t out = 0;
-#pragma unroll
-    for (int b = 0; b < 4; b++) {
-        const int x = c0 + b - kXOff;
-        uint32_t v = 0;
-        if (x >= -kEdge && x < dw + kEdge) {
-            const ResizeTap xt = xtab[reflect101(x, dw)];
-            const int r0 = (int)__ldg(s0 + xt.s) * xt.a0 + (int)__ldg(s0 + xt.s1) * xt.a1;
-            const int r1 = (int)__ldg(s1 + xt.s) * xt.a0 + (int)__ldg(s1 + xt.s1) * xt.a1;
-            v = (uint32_t)((((yt.a0 * (r0 >> 4)) >> 16) + ((yt.a1 * (r1 >> 4)) >> 16) + 2) >> 2) & 0xffu;
+constexpr int RS_TW = 256;    // destination columns per tile
+constexpr int RS_C0 = 12;     // first plane column covered by tile 0 (kXOff - kEdge = 13, rounded down to a word)
+
+// grid: (x tiles, y tiles, n); block 256 = 64 column groups x 4 row groups; dynamic shared memory 2 * SP * SH bytes.
+// srcPlane / dstPlane point at the planes of image 0.
+__global__ void __launch_bounds__(256) resize_tile_kernel(const uint8_t* __restrict__ srcPlane, int spitch,
+                                                          uint8_t* __restrict__ dstPlane, int dpitch,
+                                                          unsigned long long slabBytes, int dw, int dh,
+                                                          const ResizeTap* __restrict__ xtab,
+                                                          const ResizeTap* __restrict__ ytab, int SP, int SH, int rpt) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    const int tid = threadIdx.x, tx = tid & 63, ty = tid >> 6;
+    const int TH = 4 * rpt;
+    const int cb = RS_C0 + blockIdx.x * RS_TW;    // plane column of the tile's first byte
+    const int rb = blockIdx.y * TH;               // padded row of the tile's first row
+    // destination ROI coordinates covered by the tile, reflected into the image: source window
+    const int xa = max(cb - kXOff, -kEdge), xb = min(cb + RS_TW - 1 - kXOff, dw + kEdge - 1);
+    const int ya = rb - kEdge, yb = min(rb + TH - 1, dh + 2 * kEdge - 1) - kEdge;
+    if (xa > xb || ya > yb) return;
+    int xlo, xhi, ylo, yhi;
+    reflect_range(xa, xb, dw, xlo, xhi);
+    reflect_range(ya, yb, dh, ylo, yhi);
+    const int clo = xtab[xlo].s, chi = xtab[xhi].s + 1;    // source columns [clo, chi] (chi may be the first frame column)
+    const int rlo = ytab[ylo].s, rhi = ytab[yhi].s1;       // source rows [rlo, rhi]
+    const int colbase = (kXOff + clo) & ~15;
+    const int nvec = ((kXOff + chi + 1) - colbase + 15) >> 4;
+    const int nrows = rhi - rlo + 1;
+    uint8_t* sA = sm;
+    uint8_t* sB = sm + SP * SH;    // sB[j] = sA[j + 1]
+    {
+        const uint8_t* sp = srcPlane + (size_t)blockIdx.z * slabBytes + (size_t)(rlo + kEdge) * spitch + colbase;
+        for (int i = tid; i < nvec * nrows; i += 256) {
+            const int r = i / nvec, c = i - r * nvec;
+            const uint8_t* p = sp + (size_t)r * spitch + 16 * c;
+            const uint4 v = *reinterpret_cast<const uint4*>(p);
+            const uint32_t nb = (colbase + 16 * c + 16 < spitch) ? p[16] : 0u;
+            *reinterpret_cast<uint4*>(sA + r * SP + 16 * c) = v;
+            *reinterpret_cast<uint4*>(sB + r * SP + 16 * c) =
+                make_uint4(__funnelshift_r(v.x, v.y, 8), __funnelshift_r(v.y, v.z, 8), __funnelshift_r(v.z, v.w, 8),
+                           __funnelshift_r(v.w, nb, 8));
         }
-        out |= v << (8 * b);
     }
-    *reinterpret_cast<uint32_t*>(dstPlane + (size_t)blockIdx.z * slabBytes + (size_t)py * dpitch + c0) = out;
+    __syncthreads();
+    const int c = cb + 4 * tx;
+    if (c >= kXOff + dw + kEdge) return;
+    uint32_t wt[4];
+    int ad[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = c + k - kXOff;
+        const bool valid = x >= -kEdge && x < dw + kEdge;
+        const int2 raw = __ldg(reinterpret_cast<const int2*>(xtab + reflect101(valid ? x : 0, dw)));
+        const int s = (short)(raw.x & 0xffff);
+        const int off = kXOff + s - colbase;
+        ad[k] = !valid ? 0 : ((off & 1) ? (SP * SH + off - 1) : off);
+        wt[k] = valid ? (uint32_t)raw.y : 0u;    // a0 | a1 << 16
+    }
+    int idxA = -1, idxB = -1;
+    uint32_t A[4] = {0, 0, 0, 0}, B[4] = {0, 0, 0, 0};
+    const int py0 = rb + ty * rpt;
+    uint8_t* dp = dstPlane + (size_t)blockIdx.z * slabBytes + c;
+    for (int i = 0; i < rpt; i++) {
+        const int py = py0 + i;
+        if (py >= dh + 2 * kEdge) break;
+        const int2 yraw = __ldg(reinterpret_cast<const int2*>(ytab + reflect101(py - kEdge, dh)));
+        const int s0 = (short)(yraw.x & 0xffff) - rlo, s1 = (short)(yraw.x >> 16) - rlo;
+        const uint32_t b0 = (uint32_t)yraw.y & 0xffffu, b1 = (uint32_t)yraw.y >> 16;
+        if (s0 == idxB) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) A[k] = B[k];
+            idxA = idxB;
+        } else if (s0 != idxA) {
+            const uint8_t* row = sm + s0 * SP;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                A[k] = __dp2a_lo(wt[k], (uint32_t)*reinterpret_cast<const uint16_t*>(row + ad[k]), 0u) >> 4;
+            idxA = s0;
+        }
+        if (s1 == idxA) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) B[k] = A[k];
+            idxB = idxA;
+        } else if (s1 != idxB) {
+            const uint8_t* row = sm + s1 * SP;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                B[k] = __dp2a_lo(wt[k], (uint32_t)*reinterpret_cast<const uint16_t*>(row + ad[k]), 0u) >> 4;
+            idxB = s1;
+        }
+        uint32_t out = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t v = (((b0 * A[k]) >> 16) + ((b1 * B[k]) >> 16) + 2u) >> 2;
+            out |= (v & 0xffu) << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(dp + (size_t)py * dpitch) = out;
+    }
+}
+
+// host: shared-memory window (pitch SP, rows SH) needed by the tiles of one level for `rpt` rows per thread.
+// Mirrors the range computation of the kernel on the host copies of the tap tables.
+static int h_reflect101(int p, int len) {
+    if ((unsigned)p < (unsigned)len) return p;
+    if (len == 1) return 0;
+    do {
+        if (p < 0) p = -p; else p = 2 * len - p - 2;
+    } while ((unsigned)p >= (unsigned)len);
+    return p;
+}
+
+void resize_tile_dims(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int dh, int rpt, int* SP, int* SH) {
+    int sp = 16, shh = 1;
+    const int TH = 4 * rpt;
+    for (int cb = RS_C0; cb < kXOff + dw + kEdge; cb += RS_TW) {
+        const int xa = std::max(cb - kXOff, -kEdge), xb = std::min(cb + RS_TW - 1 - kXOff, dw + kEdge - 1);
+        int lo = 1 << 30, hi = -1;
+        for (int x = xa; x <= xb; x++) {
+            const int r = h_reflect101(x, dw);
+            lo = std::min(lo, r);
+            hi = std::max(hi, r);
+        }
+        const int clo = xtab[lo].s, chi = xtab[hi].s + 1;
+        const int colbase = (kXOff + clo) & ~15;
+        sp = std::max(sp, (((kXOff + chi + 1) - colbase + 15) >> 4) * 16);
+    }
+    for (int rb = 0; rb < dh + 2 * kEdge; rb += TH) {
+        const int ya = rb - kEdge, yb = std::min(rb + TH - 1, dh + 2 * kEdge - 1) - kEdge;
+        int lo = 1 << 30, hi = -1;
+        for (int y = ya; y <= yb; y++) {
+            const int r = h_reflect101(y, dh);
+            lo = std::min(lo, r);
+            hi = std::max(hi, r);
+        }
+        shh = std::max(shh, ytab[hi].s1 - ytab[lo].s + 1);
+    }
+    *SP = sp;
+    *SH = shh;
 }
 
 int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size_t imageStride, uint8_t* pyr,
-                   const ResizeTap* const* xtab, const ResizeTap* const* ytab, cudaStream_t st) {
+                   const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims, cudaStream_t st) {
     int launches = 0;
-    const dim3 block(64, 4);
+    static int configured = 0;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& L = g.lv[l];
-        const int words = (kXOff + L.w + kEdge + 3) / 4;
-        const dim3 grid((words + 63) / 64, (L.h + 2 * kEdge + 3) / 4, n);
         if (l == 0) {
-            pad_level0_kernel<<<grid, block, 0, st>>>(images, stride, imageStride, pyr + L.planeOff, g.slabBytes, L.w,
-                                                      L.h, L.pitch);
+            const int chunks = (kXOff + L.w + kEdge + 15) / 16;
+            const dim3 grid((chunks + 63) / 64, (L.h + 2 * kEdge + 3) / 4, n);
+            pad_level0_kernel<<<grid, dim3(64, 4), 0, st>>>(images, stride, imageStride, pyr + L.planeOff, g.slabBytes,
+                                                            L.w, L.h, L.pitch);
         } else {
             const LevelGeom& P = g.lv[l - 1];
-            resize_level_kernel<<<grid, block, 0, st>>>(pyr + P.planeOff, P.pitch, pyr + L.planeOff, L.pitch,
-                                                        g.slabBytes, L.w, L.h, xtab[l], ytab[l]);
+            const ResizeDims& d = dims[l];
+            const int smem = 2 * d.SP * d.SH;
+            if (smem > 48 * 1024 && configured < smem) {
+                cudaFuncSetAttribute(resize_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+                configured = smem;
+            }
+            const dim3 grid((kXOff + L.w + kEdge - RS_C0 + RS_TW - 1) / RS_TW, (L.h + 2 * kEdge + 4 * d.rpt - 1) / (4 * d.rpt), n);
+            resize_tile_kernel<<<grid, 256, smem, st>>>(pyr + P.planeOff, P.pitch, pyr + L.planeOff, L.pitch, g.slabBytes,
+                                                        L.w, L.h, xtab[l], ytab[l], d.SP, d.SH, d.rpt);
         }
         launches++;
     }

@@ -213,6 +213,7 @@ struct orbfe_extractor {
     DevBuf dItems, dBlurTiles, dTaps;
     const ResizeTap* xtab[ORBFE_MAX_LEVELS] = {};
     const ResizeTap* ytab[ORBFE_MAX_LEVELS] = {};
+    ResizeDims rsDims[2][ORBFE_MAX_LEVELS] = {};    // [0] large batches (16 rows per thread), [1] small batches (4)
 
     // workspace for `chunkCap` images
     int chunkCap = 0;
@@ -286,6 +287,17 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
         std::vector<ResizeTap> tx, ty;
         build_taps(g.lv[l - 1].w, g.lv[l].w, true, tx);
         build_taps(g.lv[l - 1].h, g.lv[l].h, false, ty);
+        for (int v = 0; v < 2; v++) {
+            ResizeDims& d = ex->rsDims[v][l];
+            d.rpt = v == 0 ? 16 : 4;
+            resize_tile_dims(tx.data(), ty.data(), g.lv[l].w, g.lv[l].h, d.rpt, &d.SP, &d.SH);
+            while (2 * d.SP * d.SH > 96 * 1024 && d.rpt > 1) {
+                d.rpt /= 2;
+                resize_tile_dims(tx.data(), ty.data(), g.lv[l].w, g.lv[l].h, d.rpt, &d.SP, &d.SH);
+            }
+            if (2 * d.SP * d.SH > 200 * 1024)
+                return set_err(ex, ORBFE_ERR_ARG, "scale factor too large for the resize tile (%d bytes of shared memory)", 2 * d.SP * d.SH);
+        }
         xo[l] = all.size();
         all.insert(all.end(), tx.begin(), tx.end());
         yo[l] = all.size();
@@ -360,7 +372,8 @@ static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int str
     cudaStream_t st = ex->stream;
     int launches = 0;
     cudaEventRecord(ex->ev[1], st);
-    launches += launch_pyramid(g, dImages, n, stride, imageStride, ex->bufs.pyr, ex->xtab, ex->ytab, st);
+    launches += launch_pyramid(g, dImages, n, stride, imageStride, ex->bufs.pyr, ex->xtab, ex->ytab,
+                               ex->rsDims[n >= 32 ? 0 : 1], st);
     cudaEventRecord(ex->ev[2], st);
     launches += launch_fast(g, ex->bufs.pyr, n, (const FastItem*)ex->dItems.p, ex->nItems, ex->tileBytes, ex->scoreBytes,
                             ex->listBytes, ex->bufs.slots, ex->bufs.cellCount, st);

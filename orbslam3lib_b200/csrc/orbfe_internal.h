@@ -68,6 +68,12 @@ struct ResizeTap {
     short a0, a1;    // weights * 2048
 };
 
+// shared-memory window of the resize tiles of one level (k_pyramid.cu)
+struct ResizeDims {
+    int SP, SH;    // pitch (multiple of 16) and rows of the staged source window
+    int rpt;       // destination rows per thread (tile height = 4 * rpt)
+};
+
 // per-image results of the pack step
 struct ImageResult {
     int count;     // nkeypoints
@@ -98,7 +104,8 @@ struct ExtractBuffers {
 
 // ---- kernel launchers (each returns the number of kernels it launched) ----
 int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size_t imageStride, uint8_t* pyr,
-                   const ResizeTap* const* xtab, const ResizeTap* const* ytab, cudaStream_t st);
+                   const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims, cudaStream_t st);
+void resize_tile_dims(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int dh, int rpt, int* SP, int* SH);
 int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, uint32_t* slots,
                 int* cellCount, cudaStream_t st);
 int launch_octree(const Geom& g, int n, const ExtractBuffers& b, cudaStream_t st);

@@ -16,6 +16,17 @@ __global__ void k(unsigned* out, unsigned seed, int iters) {
             if (MODE == 0) a[i] = __popc(a[i]) + a[i];                 // POPC + IADD, dependent per chain (8 chains)
             if (MODE == 1) a[i] = (a[i] ^ seed) & (a[i] | 0x55u + i);    // LOP3-ish
             if (MODE == 2) acc += __popc(a[i] ^ (seed + it));          // matcher inner loop shape
+            if (MODE == 3) a[i] = __dp2a_lo(a[i], seed, a[i]);                        // IDP.2A
+            if (MODE == 4) a[i] = __vimax3_s16x2(a[i], seed, a[(i + 1) & 7]);         // VIMNMX3.S16x2
+            if (MODE == 5) a[i] = __vabsdiffu4(a[i], seed + i);                        // VABSDIFF4
+            if (MODE == 6) a[i] = __byte_perm(a[i], seed, 0x2103 + i);                 // PRMT
+            if (MODE == 7) a[i] = a[i] * seed + i;                                     // IMAD
+            if (MODE == 8) a[i] = __umulhi(a[i], seed) + i;                            // IMAD.HI
+            if (MODE == 9) a[i] = (a[i] >> 3) + seed;                                  // SHF + IADD
+            if (MODE == 10) a[i] = __dp4a(a[i], seed, a[i]);                           // IDP.4A
+            if (MODE == 11) { a[i] = a[i] * seed + i; a[i] = (a[i] ^ seed) | (a[i] >> 1); }   // IMAD + SHF + LOP3 mix
+            if (MODE == 12) a[i] = __vmaxs2(a[i], seed + i);                      // VIMNMX.S16x2
+            if (MODE == 13) a[i] = max(min((int)a[i], (int)seed), i);                  // VIMNMX 32-bit x2
         }
         if (MODE == 2) a[it & 7] += acc;
     }
@@ -53,5 +64,16 @@ int main() {
     run<0>("popc(+iadd) per thread-op", p.multiProcessorCount, 8);
     run<1>("lop3 pairs", p.multiProcessorCount, 16);
     run<2>("xor+popc+add (matcher shape)", p.multiProcessorCount, 8);
+    run<3>("dp2a (IDP.2A)", p.multiProcessorCount, 8);
+    run<4>("vimax3_s16x2 (VIMNMX3)", p.multiProcessorCount, 8);
+    run<5>("vabsdiffu4", p.multiProcessorCount, 8);
+    run<6>("byte_perm (PRMT)", p.multiProcessorCount, 8);
+    run<7>("imad", p.multiProcessorCount, 8);
+    run<8>("umulhi+iadd", p.multiProcessorCount, 8);
+    run<9>("shf+iadd", p.multiProcessorCount, 8);
+    run<10>("dp4a (IDP.4A)", p.multiProcessorCount, 8);
+    run<11>("imad+lop3(shf) mix (3 instr)", p.multiProcessorCount, 8);
+    run<12>("vimax_s16x2", p.multiProcessorCount, 8);
+    run<13>("max(min()) s32 (2 instr)", p.multiProcessorCount, 8);
     return 0;
 }
