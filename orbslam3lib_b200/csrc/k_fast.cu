@@ -4,218 +4,270 @@
 // that returns nothing, again with minThFAST (:828-848).  cv::FAST semantics: FAST-9/16 on the
 // Bresenham circle of radius 3, tested on the cell sub-image minus a 3-px border, score = the largest threshold at
 // which the pixel is still a corner, minus one; 3x3 non-max suppression with strict ">" where everything outside
-// the tested region scores 0; output in raster order.  Cells overlap by 6 px and the same pixel may be reported by
-// two cells — reproduced, not de-duplicated.
+// the tested window of the cell scores 0; output in raster order.  The tested windows of adjacent cells are
+// disjoint and contiguous (a cell is wCell + 6 wide and loses 3 px on each side), so every pixel is scored once.
 //
-// Mapping: one CTA stages a run of up to 8 cells of one cell row (a strip of the level plane) into shared memory with
-// 16-byte coalesced loads.  A pixel's corner score depends only on its own neighbourhood, not on the cell asking, so
-// (1) the whole CTA scores the strip ONCE at iniThFAST: every lane tests 4 pixels packed in a 32-bit word with SWAR
-//     byte compares (opposite-pair rejection on ring pixels 0/8 and 4/12), survivors are compacted per warp with
-//     __ballot_sync, and 32 survivors at a time get the full test (16 ring pixels classified into a "brighter" and a
-//     "darker" 16-bit mask, 9-run detected with shifts/ANDs) and the score (min/max over the sixteen 9-arcs with a
-//     log-step sliding window in registers), written to a strip-wide score map in shared memory;
-// (2) one warp per cell runs the 3x3 NMS on the cell's tested window of that map (neighbours outside the window
-//     count as 0, exactly what cv::FAST sees on the sub-image) and emits in raster order with __ballot_sync /
-//     __popc ranks, so the output order is deterministic and equals OpenCV's;
-// (3) a cell that comes back empty is searched again at minThFAST on a private score tile (rare path).  Candidates go to the cell's fixed slot array as packed
-// (x | y << 12 | response << 24), coordinates relative to (minBorderX, minBorderY) as in :865-870.
-//
-// HBM-bound by design (reads P bytes per image once; the 6-px overlaps hit L1/L2); integer only.
+// Mapping: one CTA stages a run of up to FAST_ITEM_COLS cells of one cell row (a strip of the level plane) into
+// shared memory with 16-byte loads and runs up to two passes (iniThFAST for all cells, then minThFAST for the cells
+// that came back empty) of a four-phase pipeline, every phase using all threads of the CTA:
+//   A  test      a thread owns one 32-bit word column (4 px) x 8 rows: SWAR opposite-pair rejection (a 9-arc contains
+//                one pixel of each opposite ring pair, so a corner needs |p0-v|>t or |p8-v|>t, and |p4-v|>t or
+//                |p12-v|>t) on 4 pixels at a time (VABSDIFF4 + carry-free byte compares); the 32 survivor flags of the
+//                thread are compacted into a shared survivor list (warp scan of the popcounts, one shared atomic
+//                per warp);
+//   B  score     one thread per listed pixel: the 16 ring differences are packed two per register (k, k+8) and the
+//                sixteen 9-arc minima / maxima come from two levels of 3-input packed min/max (VIMNMX3.S16x2);
+//                score >= t  <=>  corner at t, so the score alone decides; scores go to a strip-wide score map;
+//   C  nms       the list is walked again: every scored pixel compares with its 8 neighbours inside its own cell's
+//                tested window and sets its bit in a keep bitmap;
+//   D  emit      one warp per cell: a lane owns a window row, counts its kept bits, a warp scan gives raster-order
+//                ranks, candidates go to the cell's slot array as packed (x | y << 12 | response << 24) relative to
+//                (minBorderX, minBorderY) as in :865-870.
+// Integer only; reads P bytes per image once (the 6-px overlaps hit L1/L2).
 #include "orbfe_internal.h"
 
 namespace orbfe {
 
-constexpr int FAST_WARPS = 8;
-constexpr int FAST_ITEM_COLS = 8;
+constexpr int FAST_THREADS = 256;
+constexpr int FAST_WARPS = FAST_THREADS / 32;
+constexpr int FAST_ITEM_COLS = 8;    // <= FAST_WARPS (phase D gives a warp to every cell)
 
-__device__ __forceinline__ bool has_run9(uint32_t m16) {    // 9 contiguous set bits in a circular 16-bit mask
-    uint32_t m = m16 | (m16 << 16);
-    uint32_t x = m & (m >> 1);
-    x &= x >> 2;
-    x &= x >> 4;     // bit k: bits k..k+7 set
-    x &= m >> 8;     // bit k: bits k..k+8 set
-    return (x & 0xffffu) != 0;
-}
+__device__ __forceinline__ uint32_t swap16(uint32_t a) { return __byte_perm(a, a, 0x1032); }
 
-// c points at the centre pixel inside the shared strip tile (pitch tp).
-__device__ __forceinline__ bool fast9_is_corner(const uint8_t* c, int tp, int t) {
-    const int v = c[0];
-    const int lo = v - t, hi = v + t;
-    // opposite-pair rejection (a 9-arc contains one pixel of every opposite pair)
-    const int p0 = c[3 * tp], p8 = c[-3 * tp];
-    if (!((p0 < lo) | (p0 > hi) | (p8 < lo) | (p8 > hi))) return false;
-    const int p4 = c[3], p12 = c[-3];
-    if (!((p4 < lo) | (p4 > hi) | (p12 < lo) | (p12 > hi))) return false;
-    uint32_t mb = 0, md = 0;
-#define ORBFE_RING(k, dx, dy)                      \
-    {                                              \
-        const int x = c[(dy) * tp + (dx)];         \
-        mb |= (uint32_t)(x > hi) << (k);           \
-        md |= (uint32_t)(x < lo) << (k);           \
-    }
-    ORBFE_RING(0, 0, 3) ORBFE_RING(1, 1, 3) ORBFE_RING(2, 2, 2) ORBFE_RING(3, 3, 1)
-    ORBFE_RING(4, 3, 0) ORBFE_RING(5, 3, -1) ORBFE_RING(6, 2, -2) ORBFE_RING(7, 1, -3)
-    ORBFE_RING(8, 0, -3) ORBFE_RING(9, -1, -3) ORBFE_RING(10, -2, -2) ORBFE_RING(11, -3, -1)
-    ORBFE_RING(12, -3, 0) ORBFE_RING(13, -3, 1) ORBFE_RING(14, -2, 2) ORBFE_RING(15, -1, 3)
-#undef ORBFE_RING
-    return has_run9(mb) || has_run9(md);
-}
-
-// cornerScore<16>: max over the sixteen 9-arcs of max(min d, -max d), d = v - ring; returns that value - 1.
+// cornerScore<16> of cv::FAST: max over the sixteen 9-arcs of max(min d, -max d), d = v - ring, minus 1.
+// c points at the centre pixel inside the shared strip tile (pitch tp).  Works on e = ring - v + 256 (biased, always
+// positive, so two values pack into the 16-bit lanes of one register without borrows): lane lo of R[k] is ring
+// position k, lane hi is position k + 8.
 __device__ __forceinline__ int fast9_score(const uint8_t* c, int tp) {
-    const int v = c[0];
-    int d[16];
-    d[0] = v - c[3 * tp];       d[1] = v - c[3 * tp + 1];    d[2] = v - c[2 * tp + 2];    d[3] = v - c[tp + 3];
-    d[4] = v - c[3];            d[5] = v - c[-tp + 3];       d[6] = v - c[-2 * tp + 2];   d[7] = v - c[-3 * tp + 1];
-    d[8] = v - c[-3 * tp];      d[9] = v - c[-3 * tp - 1];   d[10] = v - c[-2 * tp - 2];  d[11] = v - c[-tp - 3];
-    d[12] = v - c[-3];          d[13] = v - c[tp - 3];       d[14] = v - c[2 * tp - 2];   d[15] = v - c[3 * tp - 1];
-    int mn[16], mx[16], a[16], b[16];
+    const uint32_t bias = (uint32_t)(256 - (int)c[0]) * 0x10001u;
+    uint32_t R[10];
+#define ORBFE_PAIR(k, dx0, dy0, dx1, dy1) \
+    R[k] = (uint32_t)c[(dy0) * tp + (dx0)] + ((uint32_t)c[(dy1) * tp + (dx1)] << 16) + bias;
+    ORBFE_PAIR(0, 0, 3, 0, -3)
+    ORBFE_PAIR(1, 1, 3, -1, -3)
+    ORBFE_PAIR(2, 2, 2, -2, -2)
+    ORBFE_PAIR(3, 3, 1, -3, -1)
+    ORBFE_PAIR(4, 3, 0, -3, 0)
+    ORBFE_PAIR(5, 3, -1, -3, 1)
+    ORBFE_PAIR(6, 2, -2, -2, 2)
+    ORBFE_PAIR(7, 1, -3, -1, 3)
+#undef ORBFE_PAIR
+    R[8] = swap16(R[0]);
+    R[9] = swap16(R[1]);
+    uint32_t mn[14], mx[14];
 #pragma unroll
-    for (int k = 0; k < 16; k++) { mn[k] = min(d[k], d[(k + 1) & 15]); mx[k] = max(d[k], d[(k + 1) & 15]); }
-#pragma unroll
-    for (int k = 0; k < 16; k++) { a[k] = min(mn[k], mn[(k + 2) & 15]); b[k] = max(mx[k], mx[(k + 2) & 15]); }
-#pragma unroll
-    for (int k = 0; k < 16; k++) { mn[k] = min(a[k], a[(k + 4) & 15]); mx[k] = max(b[k], b[(k + 4) & 15]); }
-    // max over arcs of min(d) and min over arcs of max(d) are reduced separately and combined once: the per-arc form
-    // max(best, max(lo9, -hi9)) is miscompiled by nvcc 12.9 for sm_100a (unsigned VIMNMX on the negated operand;
-    // tools/dbg_fast_unit.cu reproduces it), and this form is also cheaper.
-    int dark = -1024, bright = 1024;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        dark = max(dark, min(mn[k], d[(k + 8) & 15]));       // min of d[k..k+8]
-        bright = min(bright, max(mx[k], d[(k + 8) & 15]));   // max of d[k..k+8]
+    for (int k = 0; k < 8; k++) {    // 3 consecutive ring positions
+        mn[k] = __vimin3_s16x2(R[k], R[k + 1], R[k + 2]);
+        mx[k] = __vimax3_s16x2(R[k], R[k + 1], R[k + 2]);
     }
-    const int best = max(dark, -bright);
-    return best - 1;
-}
-
-// bytes of x that are > t (t <= 127), as 0x80 flags: exact SWAR compare (the low 7 bits cannot carry)
-__device__ __forceinline__ uint32_t bytes_gt(uint32_t x, uint32_t k127mt) {
-    return (((x & 0x7f7f7f7fu) + k127mt) | x) & 0x80808080u;
-}
-
-// score `cnt` (<= 32) listed positions (r << 10 | col, tile coordinates) into the score map
-__device__ __forceinline__ void score_listed(const uint8_t* tile, uint8_t* smap, int tp, const unsigned short* list, int cnt,
-                                             int lane, int t) {
-    if (lane < cnt) {
-        const int e = list[lane];
-        const int off = (e >> 10) * tp + (e & 1023);
-        // corner at threshold t  <=>  the largest arc threshold (score + 1) exceeds t, so the score alone decides
-        const int sc = fast9_score(tile + off, tp);
-        if (sc >= t) smap[off] = (uint8_t)sc;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        mn[8 + k] = swap16(mn[k]);
+        mx[8 + k] = swap16(mx[k]);
     }
+    uint32_t a9[8], b9[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {    // 9 consecutive ring positions: arc k (lo) and arc k + 8 (hi)
+        a9[k] = __vimin3_s16x2(mn[k], mn[k + 3], mn[k + 6]);
+        b9[k] = __vimax3_s16x2(mx[k], mx[k + 3], mx[k + 6]);
+    }
+    // max over arcs of min(e) ; min over arcs of max(e)
+    uint32_t ma = __vimax3_s16x2(__vimax3_s16x2(a9[0], a9[1], a9[2]), __vimax3_s16x2(a9[3], a9[4], a9[5]),
+                                 __vimax3_s16x2(a9[6], a9[7], a9[7]));
+    uint32_t mb = __vimin3_s16x2(__vimin3_s16x2(b9[0], b9[1], b9[2]), __vimin3_s16x2(b9[3], b9[4], b9[5]),
+                                 __vimin3_s16x2(b9[6], b9[7], b9[7]));
+    const int maxMinE = max((int)(ma & 0xffffu), (int)(ma >> 16)) - 256;    // = -bright  (d = -e)
+    const int minMaxE = min((int)(mb & 0xffffu), (int)(mb >> 16)) - 256;    // = -dark
+    return max(maxMinE, -minMaxE) - 1;
 }
 
-// NMS + emission over the tested region (tw x th, origin `sc0`, pitch sp) of a score map, raster order.  Scores outside
-// the tested region count as 0 (cv::FAST never scores the 3-px border of the sub-image it is given).
-__device__ __forceinline__ int nms_emit(const uint8_t* sc0, int sp, int tw, int th, uint32_t* out, int slotCap, int xAdd,
-                                        int yAdd, int lane, uint32_t ltMask) {
-    int total = 0;
-    int cy = lane / tw, cx = lane - cy * tw;
-    const int npix = tw * th;
-    for (int base = 0; base < npix; base += 32) {
-        int s = 0;
-        if (base + lane < npix) s = sc0[cy * sp + cx];
-        if (__any_sync(0xffffffffu, s != 0)) {
-            bool keep = false;
-            if (s != 0) {
-                const uint8_t* q = sc0 + cy * sp + cx;
-                const bool l = cx > 0, r = cx < tw - 1, u = cy > 0, d = cy < th - 1;
-                keep = (!l || s > q[-1]) && (!r || s > q[1]) && (!u || (s > q[-sp] && (!l || s > q[-sp - 1]) && (!r || s > q[-sp + 1]))) &&
-                       (!d || (s > q[sp] && (!l || s > q[sp - 1]) && (!r || s > q[sp + 1])));
+// bytes of x that are > t (t <= 127), as 0x80 flags (other bits undefined): the low 7 bits cannot carry
+__device__ __forceinline__ uint32_t bytes_gt_raw(uint32_t x, uint32_t k127mt) { return ((x & 0x7f7f7f7fu) + k127mt) | x; }
+
+struct FastStrip {
+    uint8_t* tile;           // strip pixels, pitch tp
+    uint8_t* smap;           // strip score map, pitch tp
+    uint32_t* kbits;         // keep bitmap, kw words per tile row
+    unsigned short* list;    // survivor list: byte offsets into the tile (tile <= 64 KiB)
+    int* cnt;                // [0] list length, [1] mask of cells that came back empty
+    int tp, kw, ch;          // tile pitch, bitmap words per row, tile rows
+    int colLo, colHi;        // tested tile columns [colLo, colHi)
+    int wCell, ncols;        // cell pitch and number of cells in the strip
+};
+
+// cell (0 .. ncols-1) of a tested tile column
+__device__ __forceinline__ int strip_cell(const FastStrip& s, int col) {
+    const int rel = col - s.colLo;
+    int j = 0;
+#pragma unroll
+    for (int q = 1; q < FAST_ITEM_COLS; q++) j += (q < s.ncols && rel >= q * s.wCell) ? 1 : 0;
+    return j;
+}
+
+// phases A..C for threshold t over the cells of cellMask.  Ends with the keep bitmap complete (block synchronised).
+__device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t cellMask, bool allCells) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int wpr = s.tp >> 2;
+    const int wLo = s.colLo >> 2, nwc = ((s.colHi + 3) >> 2) - wLo;
+    const int th = s.ch - 6;
+    const int ngroups = (th + 7) >> 3;
+    const uint32_t k127mt = (uint32_t)(127 - min(t, 127)) * 0x01010101u;
+    const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(s.tile);
+
+    // ---- A: test + compaction --------------------------------------------------------------------------------
+    const int nunits = nwc * ngroups;
+    for (int u0 = 0; u0 < nunits; u0 += FAST_THREADS) {    // uniform trip count: the warp scan below needs all lanes
+        const int u = u0 + tid;
+        uint32_t acc = 0;
+        int w = 0, r0 = 0;
+        if (u < nunits) {
+            const int g = u / nwc;
+            w = wLo + (u - g * nwc);
+            r0 = 3 + 8 * g;
+            // bytes of this word column that are tested (and belong to a cell of cellMask)
+            uint32_t bm = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int col = 4 * w + j;
+                bool ok = col >= s.colLo && col < s.colHi;
+                if (ok && !allCells) ok = (cellMask >> strip_cell(s, col)) & 1u;
+                if (ok) bm |= 0x80u << (8 * j);
             }
-            const uint32_t m = __ballot_sync(0xffffffffu, keep);
-            if (keep) {
-                const int k = total + __popc(m & ltMask);
-                if (k < slotCap) out[k] = (uint32_t)(cx + xAdd) | ((uint32_t)(cy + yAdd) << 12) | ((uint32_t)s << 24);
+            if (bm != 0) {
+                const uint32_t* p = tw32 + r0 * wpr + w;
+                if (t <= 127) {
+#pragma unroll
+                    for (int i = 0; i < 8; i++) {
+                        const uint32_t c = p[i * wpr], cp = p[i * wpr - 1], cn = p[i * wpr + 1];
+                        const uint32_t up = p[(i + 3) * wpr], dn = p[(i - 3) * wpr];
+                        const uint32_t p4 = __byte_perm(c, cn, 0x6543), p12 = __byte_perm(cp, c, 0x4321);
+                        const uint32_t v = bytes_gt_raw(__vabsdiffu4(up, c), k127mt) | bytes_gt_raw(__vabsdiffu4(dn, c), k127mt);
+                        const uint32_t h = bytes_gt_raw(__vabsdiffu4(p4, c), k127mt) | bytes_gt_raw(__vabsdiffu4(p12, c), k127mt);
+                        acc = (acc >> 1) | (v & h & bm);
+                    }
+                } else {
+                    acc = bm | (bm >> 1) | (bm >> 2) | (bm >> 3) | (bm >> 4) | (bm >> 5) | (bm >> 6) | (bm >> 7);
+                }
+                // rows beyond the tested window (the last group may be partial)
+                const int nvalid = min(8, th - 8 * g);
+                acc &= ((1u << nvalid) - 1u) * 0x01010101u;
             }
-            total += __popc(m);
         }
-        cx += 32;
-        while (cx >= tw) { cx -= tw; cy++; }
+        // bit 8 j + i of acc: pixel (row r0 + i, column 4 w + j) survived
+        const int n = __popc(acc);
+        int inc = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        int base = 0;
+        if (lane == 31 && inc > 0) base = atomicAdd(&s.cnt[0], inc);
+        base = __shfl_sync(0xffffffffu, base, 31) + inc - n;
+        while (acc) {
+            const int b = __ffs(acc) - 1;
+            acc &= acc - 1;
+            s.list[base++] = (unsigned short)((r0 + (b & 7)) * s.tp + 4 * w + (b >> 3));
+        }
     }
-    return total;
+    __syncthreads();
+
+    // ---- B: score ----------------------------------------------------------------------------------------------
+    const int nlist = s.cnt[0];
+    for (int e = tid; e < nlist; e += FAST_THREADS) {
+        const int off = s.list[e];
+        const int sc = fast9_score(s.tile + off, s.tp);
+        // corner at threshold t  <=>  the largest arc threshold (score + 1) exceeds t
+        s.smap[off] = sc >= t ? (uint8_t)sc : (uint8_t)0;
+    }
+    __syncthreads();
+
+    // ---- C: non-max suppression inside the pixel's own cell window ------------------------------------------------
+    for (int e = tid; e < nlist; e += FAST_THREADS) {
+        const int off = s.list[e];
+        const uint8_t* q = s.smap + off;
+        const int sc = q[0];
+        if (sc == 0) continue;
+        const int r = off / s.tp, col = off - r * s.tp;
+        const int j = strip_cell(s, col);
+        const int x0 = s.colLo + j * s.wCell;
+        const int x1 = min(x0 + s.wCell, s.colHi);    // window columns [x0, x1)
+        const bool l = col > x0, rt = col < x1 - 1, u = r > 3, d = r < s.ch - 4;
+        const int tp = s.tp;
+        const bool keep = (!l || sc > q[-1]) && (!rt || sc > q[1]) &&
+                          (!u || (sc > q[-tp] && (!l || sc > q[-tp - 1]) && (!rt || sc > q[-tp + 1]))) &&
+                          (!d || (sc > q[tp] && (!l || sc > q[tp - 1]) && (!rt || sc > q[tp + 1])));
+        if (keep) atomicOr(&s.kbits[r * s.kw + (col >> 5)], 1u << (col & 31));
+    }
+    __syncthreads();
 }
 
-// Same as nms_emit for the strip score map, but 4 pixels (one aligned 32-bit word) per lane: almost all words are 0.
-// X0 = tile column of the first tested pixel of the cell; the tested rows start at tile row 3.
-__device__ __forceinline__ int nms_emit_words(const uint8_t* smap, int tp, int X0, int tw, int th, uint32_t* out, int slotCap,
-                                              int xAdd, int yAdd, int lane, uint32_t ltMask) {
-    const int wpr = tp >> 2, wA = X0 >> 2, nwc = ((X0 + tw + 3) >> 2) - wA;
-    const int nitems = nwc * th;
-    const uint32_t firstMask = ~((1u << (8 * (X0 & 3))) - 1u);
-    const int lastBytes = X0 + tw - 4 * (wA + nwc - 1);    // valid bytes in the last word of a row: 1..4
-    const uint32_t lastMask = lastBytes >= 4 ? 0xffffffffu : ((1u << (8 * lastBytes)) - 1u);
-    const int rStep = 32 / nwc, wStep = 32 - rStep * nwc;
-    int row = lane / nwc, w = lane - row * nwc;
+// phase D for the cells of cellMask: raster-order emission of the kept pixels of every cell window, one warp per cell.
+// Returns (to lane 0 of the warp that owns cell j) nothing; totals are written to counts[] and empty cells are
+// recorded in s.cnt[1] when markEmpty is set.
+__device__ __forceinline__ void fast_emit(const FastStrip& s, uint32_t cellMask, bool markEmpty, uint32_t* slotsRow,
+                                          int* counts, int slotCap, int col0, int xAddBase, int yAdd) {
+    const int lane = threadIdx.x & 31, j = threadIdx.x >> 5;
+    if (j >= s.ncols || !((cellMask >> j) & 1u)) return;
+    const int x0 = s.colLo + j * s.wCell;
+    const int x1 = min(x0 + s.wCell, s.colHi);
     int total = 0;
-    for (int base = 0; base < nitems; base += 32) {
-        uint32_t word = 0;
-        if (base + lane < nitems) {
-            word = reinterpret_cast<const uint32_t*>(smap)[(3 + row) * wpr + wA + w];
-            if (w == 0) word &= firstMask;
-            if (w == nwc - 1) word &= lastMask;
-        }
-        if (__any_sync(0xffffffffu, word != 0)) {
-            uint32_t keep4 = 0;
-            if (word != 0) {
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const int s = (word >> (8 * j)) & 0xff;
-                    if (s == 0) continue;
-                    const int cx = 4 * (wA + w) + j - X0, cy = row;
-                    const uint8_t* q = smap + (3 + row) * tp + X0 + cx;
-                    const bool l = cx > 0, r = cx < tw - 1, u = cy > 0, d = cy < th - 1;
-                    const bool keep = (!l || s > q[-1]) && (!r || s > q[1]) &&
-                                      (!u || (s > q[-tp] && (!l || s > q[-tp - 1]) && (!r || s > q[-tp + 1]))) &&
-                                      (!d || (s > q[tp] && (!l || s > q[tp - 1]) && (!r || s > q[tp + 1])));
-                    if (keep) keep4 |= 1u << j;
+    if (x1 > x0) {
+        const int th = s.ch - 6;
+        const int wA = x0 >> 5, wB = (x1 - 1) >> 5;
+        uint32_t* out = slotsRow + (size_t)(col0 + j) * slotCap;
+        const int xAdd = xAddBase + j * s.wCell - x0;
+        for (int rbase = 0; rbase < th; rbase += 32) {
+            const int row = rbase + lane;
+            int n = 0;
+            if (row < th) {
+                for (int wi = wA; wi <= wB; wi++) {
+                    uint32_t bits = s.kbits[(3 + row) * s.kw + wi];
+                    const int lo = max(x0 - 32 * wi, 0), hi = min(x1 - 32 * wi, 32);
+                    bits &= (hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+                    n += __popc(bits);
                 }
             }
-            if (__any_sync(0xffffffffu, keep4 != 0)) {
-                // raster order: lane-major, byte-minor.  rank = kept bytes in lower lanes + kept lower bytes of this lane
-                int lower = 0, all = 0;
+            int inc = n;
 #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const uint32_t bm = __ballot_sync(0xffffffffu, (keep4 >> j) & 1u);
-                    lower += __popc(bm & ltMask);
-                    all += __popc(bm);
-                }
-                int before = 0;
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    if ((keep4 >> j) & 1u) {
-                        const int k = total + lower + before;
-                        const int cx = 4 * (wA + w) + j - X0;
-                        const int s = (word >> (8 * j)) & 0xff;
-                        if (k < slotCap) out[k] = (uint32_t)(cx + xAdd) | ((uint32_t)(row + yAdd) << 12) | ((uint32_t)s << 24);
-                        before++;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += v;
+            }
+            int k = total + inc - n;
+            if (n > 0) {
+                for (int wi = wA; wi <= wB; wi++) {
+                    uint32_t bits = s.kbits[(3 + row) * s.kw + wi];
+                    const int lo = max(x0 - 32 * wi, 0), hi = min(x1 - 32 * wi, 32);
+                    bits &= (hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+                    while (bits) {
+                        const int col = 32 * wi + __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        const uint32_t sc = s.smap[(3 + row) * s.tp + col];
+                        if (k < slotCap) out[k] = (uint32_t)(col + xAdd) | ((uint32_t)(row + yAdd) << 12) | (sc << 24);
+                        k++;
                     }
                 }
-                total += all;
             }
+            total += __shfl_sync(0xffffffffu, inc, 31);
         }
-        row += rStep;
-        w += wStep;
-        if (w >= nwc) { w -= nwc; row++; }
+        if (markEmpty && total == 0 && lane == 0) atomicOr(&s.cnt[1], 1 << j);
     }
-    return total;
+    if (lane == 0) counts[col0 + j] = total;
 }
 
-// grid (nItems, n); block 32 * FAST_WARPS.  dynamic shared memory: strip tile | strip score map | per warp: private
-// score tile (minThFAST fallback) + 64-entry survivor list.
-__global__ void __launch_bounds__(32 * FAST_WARPS, 4) fast_cells_kernel(const __grid_constant__ Geom g,
-                                                                      const uint8_t* __restrict__ pyr,
-                                                                      const FastItem* __restrict__ items,
-                                                                      uint32_t* __restrict__ slots,
-                                                                      int* __restrict__ cellCount, int tileBytes,
-                                                                      int scoreBytes, int listBytes) {
+// grid (nItems, n); block FAST_THREADS.  dynamic shared memory: tile | score map | keep bitmap | survivor list.
+__global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_constant__ Geom g,
+                                                                  const uint8_t* __restrict__ pyr,
+                                                                  const FastItem* __restrict__ items,
+                                                                  uint32_t* __restrict__ slots,
+                                                                  int* __restrict__ cellCount, int tileBytes,
+                                                                  int kbitsBytes, int listBytes) {
     extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ int sCnt[2];
     const FastItem it = items[blockIdx.x];
     const int img = blockIdx.y;
     const LevelGeom& L = g.lv[it.level];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t ltMask = (1u << lane) - 1u;
 
     const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
     const int iniY = kMinBorder + it.row * L.hCell;
@@ -226,7 +278,7 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, 4) fast_cells_kernel(const __
 
     const bool rowSkipped = (iniY >= maxBY - 3) || ch < 7;    // :812 (and cv::FAST finds nothing in < 7 rows)
     if (rowSkipped) {
-        for (int jc = threadIdx.x; jc < it.ncols; jc += 32 * FAST_WARPS) counts[it.col0 + jc] = 0;
+        for (int jc = threadIdx.x; jc < it.ncols; jc += FAST_THREADS) counts[it.col0 + jc] = 0;
         return;
     }
     // strip columns [xs, xe) of the level, as plane columns [ax0, ax1)
@@ -234,153 +286,58 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, 4) fast_cells_kernel(const __
     const int xe = min(kMinBorder + (it.col0 + it.ncols - 1) * L.wCell + L.wCell + 6, maxBX);
     const int ax0 = (kXOff + xs) & ~15;
     const int ax1 = (kXOff + max(xe, xs) + 15) & ~15;
-    const int tp = ax1 - ax0;
-    uint8_t* tile = smem;
-    uint8_t* smap = smem + tileBytes;
-    uint8_t* pscore = smem + 2 * tileBytes + warp * (scoreBytes + listBytes);
-    unsigned short* list = reinterpret_cast<unsigned short*>(pscore + scoreBytes);
+
+    FastStrip s;
+    s.tp = ax1 - ax0;
+    s.kw = (s.tp + 31) >> 5;
+    s.ch = ch;
+    s.tile = smem;
+    s.smap = smem + tileBytes;
+    s.kbits = reinterpret_cast<uint32_t*>(smem + 2 * tileBytes);
+    s.list = reinterpret_cast<unsigned short*>(smem + 2 * tileBytes + kbitsBytes);
+    s.cnt = sCnt;
+    s.colLo = kXOff + xs - ax0 + 3;
+    s.colHi = max(kXOff + xe - ax0 - 3, s.colLo);
+    s.wCell = L.wCell;
+    s.ncols = it.ncols;
 
     {
         const uint8_t* plane = pyr + (size_t)img * g.slabBytes + L.planeOff + (size_t)(iniY + kEdge) * L.pitch + ax0;
-        const int vecPerRow = tp >> 4;
-        for (int i = threadIdx.x; i < vecPerRow * ch; i += 32 * FAST_WARPS) {
+        const int vecPerRow = s.tp >> 4;
+        for (int i = threadIdx.x; i < vecPerRow * ch; i += FAST_THREADS) {
             const int r = i / vecPerRow, c = i - r * vecPerRow;
             uint4 v = make_uint4(0, 0, 0, 0);
             if (ax0 + 16 * c + 16 <= L.pitch) v = __ldg(reinterpret_cast<const uint4*>(plane + (size_t)r * L.pitch + 16 * c));
-            *reinterpret_cast<uint4*>(tile + r * tp + 16 * c) = v;
-            *reinterpret_cast<uint4*>(smap + r * tp + 16 * c) = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4*>(s.tile + r * s.tp + 16 * c) = v;
+            *reinterpret_cast<uint4*>(s.smap + r * s.tp + 16 * c) = make_uint4(0, 0, 0, 0);
         }
+        for (int i = threadIdx.x; i < s.kw * ch; i += FAST_THREADS) s.kbits[i] = 0;
+        if (threadIdx.x < 2) sCnt[threadIdx.x] = 0;
     }
     __syncthreads();
 
-    // ---- phase 1 (whole CTA, whole strip, iniThFAST): 4 pixels per lane in one 32-bit word --------------------
-    // opposite-pair rejection: a 9-arc contains one pixel of each opposite ring pair, so a corner needs
-    // (|p0-v| > t or |p8-v| > t) and (|p4-v| > t or |p12-v| > t).  Survivors are listed per warp (64 entries), the
-    // full FAST-9 test + score runs on 32 listed pixels at a time.
-    const int tIni = min(max(g.iniTh, 0), 255);
-    {
-        const int wpr = tp >> 2;                          // words per tile row
-        const int colLo = kXOff + xs - ax0 + 3;           // tile columns of tested pixels: [colLo, colHi)
-        const int colHi = kXOff + xe - ax0 - 3;
-        const int wLo = colLo >> 2, wHi = (colHi + 3) >> 2;
-        const int nw = wHi - wLo, nitems = nw * (ch - 6);
-        const uint32_t k127mt = (uint32_t)(127 - min(tIni, 127)) * 0x01010101u;
-        int cnt = 0;
-        int r = threadIdx.x / nw, wi = threadIdx.x - r * nw;
-        const int rStep = (32 * FAST_WARPS) / nw, wStep = (32 * FAST_WARPS) - rStep * nw;
-        for (int base = warp * 32; base < nitems; base += 32 * FAST_WARPS) {
-            uint32_t m = 0;
-            const int w = wLo + wi;
-            if (base + lane < nitems) {
-                const uint32_t* row = reinterpret_cast<const uint32_t*>(tile + (r + 3) * tp);
-                const uint32_t c = row[w], cp = row[max(w - 1, 0)], cn = row[min(w + 1, wpr - 1)];
-                const uint32_t up = row[w + 3 * wpr], dn = row[w - 3 * wpr];
-                const uint32_t p4 = __byte_perm(c, cn, 0x6543), p12 = __byte_perm(cp, c, 0x4321);
-                if (tIni <= 127)
-                    m = (bytes_gt(__vabsdiffu4(up, c), k127mt) | bytes_gt(__vabsdiffu4(dn, c), k127mt)) &
-                        (bytes_gt(__vabsdiffu4(p4, c), k127mt) | bytes_gt(__vabsdiffu4(p12, c), k127mt));
-                else
-                    m = 0x80808080u;    // no cheap rejection for thresholds above 127
-                // bytes outside [colLo, colHi)
-                const int c0 = 4 * w;
-#pragma unroll
-                for (int j = 0; j < 4; j++)
-                    if (c0 + j < colLo || c0 + j >= colHi) m &= ~(0x80u << (8 * j));
-            }
-            if (__any_sync(0xffffffffu, m != 0)) {
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const bool sv = (m >> (8 * j + 7)) & 1u;
-                    const uint32_t bm = __ballot_sync(0xffffffffu, sv);
-                    if (sv) list[cnt + __popc(bm & ltMask)] = (unsigned short)(((r + 3) << 10) | (4 * w + j));
-                    cnt += __popc(bm);
-                    __syncwarp();
-                    if (cnt >= 32) {
-                        score_listed(tile, smap, tp, list, 32, lane, tIni);
-                        const int rest = cnt - 32;
-                        const unsigned short mv = lane < rest ? list[32 + lane] : 0;
-                        __syncwarp();
-                        if (lane < rest) list[lane] = mv;
-                        cnt = rest;
-                        __syncwarp();
-                    }
-                }
-            }
-            r += rStep;
-            wi += wStep;
-            if (wi >= nw) { wi -= nw; r++; }
-        }
-        score_listed(tile, smap, tp, list, cnt, lane, tIni);
-    }
-    __syncthreads();
+    uint32_t* slotsRow = slots + ((size_t)img * g.nCells + cellRowBase) * g.slotCap;
+    const int xAddBase = it.col0 * L.wCell + 3, yAdd = it.row * L.hCell + 3;
+    const uint32_t all = (1u << it.ncols) - 1u;
 
-    // ---- phase 2: one warp per cell: NMS + emission on the strip score map; minThFAST fallback for empty cells ----
-    for (int jc = warp; jc < it.ncols; jc += FAST_WARPS) {
-        const int j = it.col0 + jc;
-        const int iniX = kMinBorder + j * L.wCell;
-        int total = 0;
-        if (iniX < maxBX - 6) {    // :821
-            const int maxX = min(iniX + L.wCell + 6, maxBX);
-            const int cw = maxX - iniX;
-            const int tw = cw - 6, th = ch - 6;
-            const int off0 = 3 * tp + (kXOff + iniX - ax0) + 3;    // first tested pixel of the cell in tile coordinates
-            uint32_t* out = slots + ((size_t)img * g.nCells + cellRowBase + j) * g.slotCap;
-            const int xAdd = j * L.wCell + 3, yAdd = it.row * L.hCell + 3;
-            total = nms_emit_words(smap, tp, kXOff + iniX - ax0 + 3, tw, th, out, g.slotCap, xAdd, yAdd, lane, ltMask);
-            if (total == 0) {
-                // :845-848: nothing at iniThFAST -> the cell is searched again at minThFAST, on a private score tile
-                const int t = min(max(g.minTh, 0), 255);
-                const uint8_t* cell = tile + off0;
-                for (int i = lane; i < (tw * th + 3) / 4; i += 32) reinterpret_cast<uint32_t*>(pscore)[i] = 0;
-                __syncwarp();
-                const int npix = tw * th;
-                int cnt = 0;
-                int cy = lane / tw, cx = lane - cy * tw;
-                for (int base = 0; base < npix; base += 32) {
-                    bool sv = false;
-                    if (base + lane < npix) {
-                        const uint8_t* c = cell + cy * tp + cx;
-                        const int v = c[0], lo = v - t, hi = v + t;
-                        const int p0 = c[3 * tp], p8 = c[-3 * tp];
-                        if ((p0 < lo) | (p0 > hi) | (p8 < lo) | (p8 > hi)) {
-                            const int p4 = c[3], p12 = c[-3];
-                            sv = (p4 < lo) | (p4 > hi) | (p12 < lo) | (p12 > hi);
-                        }
-                    }
-                    const uint32_t bm = __ballot_sync(0xffffffffu, sv);
-                    if (sv) list[cnt + __popc(bm & ltMask)] = (unsigned short)((cy << 8) | cx);
-                    cnt += __popc(bm);
-                    __syncwarp();
-                    if (cnt >= 32) {
-                        const int e = list[lane];
-                        const uint8_t* c = cell + (e >> 8) * tp + (e & 0xff);
-                        if (fast9_is_corner(c, tp, t)) pscore[(e >> 8) * tw + (e & 0xff)] = (uint8_t)fast9_score(c, tp);
-                        const int rest = cnt - 32;
-                        const unsigned short mv = lane < rest ? list[32 + lane] : 0;
-                        __syncwarp();
-                        if (lane < rest) list[lane] = mv;
-                        cnt = rest;
-                        __syncwarp();
-                    }
-                    cx += 32;
-                    while (cx >= tw) { cx -= tw; cy++; }
-                }
-                if (lane < cnt) {
-                    const int e = list[lane];
-                    const uint8_t* c = cell + (e >> 8) * tp + (e & 0xff);
-                    if (fast9_is_corner(c, tp, t)) pscore[(e >> 8) * tw + (e & 0xff)] = (uint8_t)fast9_score(c, tp);
-                }
-                __syncwarp();
-                total = nms_emit(pscore, tw, tw, th, out, g.slotCap, xAdd, yAdd, lane, ltMask);
-            }
-        }
-        if (lane == 0) counts[j] = total;
-    }
+    fast_pass(s, min(max(g.iniTh, 0), 255), all, true);
+    fast_emit(s, all, true, slotsRow, counts, g.slotCap, it.col0, xAddBase, yAdd);
+    __syncthreads();
+    const uint32_t empty = (uint32_t)sCnt[1];
+    if (empty == 0) return;
+    // :845-848: nothing at iniThFAST -> those cells are searched again at minThFAST
+    __syncthreads();
+    if (threadIdx.x == 0) sCnt[0] = 0;
+    __syncthreads();
+    fast_pass(s, min(max(g.minTh, 0), 255), empty, false);
+    fast_emit(s, empty, false, slotsRow, counts, g.slotCap, it.col0, xAddBase, yAdd);
 }
 
 // host: work items of one geometry.  Every cell row of every level is cut into runs of <= FAST_ITEM_COLS cells.
-int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* scoreBytes, int* listBytes) {
-    int n = 0, maxTile = 16, maxScore = 4;
+// tileBytes: strip tile (and score map) bytes; kbitsBytes: keep bitmap; listBytes: survivor list (worst case: every
+// tested pixel survives).
+int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* kbitsBytes, int* listBytes) {
+    int n = 0, maxTile = 16, maxK = 4, maxList = 16;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& L = g.lv[l];
         for (int r = 0; r < L.nRows; r++)
@@ -391,31 +348,36 @@ int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* 
                 const int tp = ((nc * L.wCell + 6 + 15 + 15) & ~15) + 16;
                 const int ch = L.hCell + 6;
                 if (tp * ch > maxTile) maxTile = tp * ch;
+                const int kb = ((tp + 31) / 32) * 4 * ch;
+                if (kb > maxK) maxK = kb;
+                const int lb = (nc * L.wCell + 8) * L.hCell * 2;
+                if (lb > maxList) maxList = lb;
             }
-        const int sb = ((L.wCell + 6) * (L.hCell + 6) + 3) & ~3;
-        if (L.nCols > 0 && L.nRows > 0 && sb > maxScore) maxScore = sb;
     }
     *tileBytes = (maxTile + 15) & ~15;
-    *scoreBytes = (maxScore + 15) & ~15;
-    *listBytes = 128;    // 64 u16 survivor entries per warp
+    *kbitsBytes = (maxK + 15) & ~15;
+    *listBytes = (maxList + 15) & ~15;
     return n;
 }
 
-int fast_smem_bytes(int tileBytes, int scoreBytes, int listBytes) {
-    return 2 * tileBytes + FAST_WARPS * (scoreBytes + listBytes);
+int fast_smem_bytes(int tileBytes, int kbitsBytes, int listBytes) {
+    // phase A reads up to 10 tile rows past the strip (masked afterwards): they must stay inside the allocation, and
+    // list offsets are 16-bit
+    if (tileBytes > 65536) return 1 << 30;
+    return 2 * tileBytes + kbitsBytes + listBytes;
 }
 
 int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, int tileBytes,
-                int scoreBytes, int listBytes, uint32_t* slots, int* cellCount, cudaStream_t st) {
+                int kbitsBytes, int listBytes, uint32_t* slots, int* cellCount, cudaStream_t st) {
     if (nItems <= 0) return 0;
-    const int smem = fast_smem_bytes(tileBytes, scoreBytes, listBytes);
+    const int smem = fast_smem_bytes(tileBytes, kbitsBytes, listBytes);
     static int configured = 0;
     if (smem > 48 * 1024 && configured < smem) {
         cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    fast_cells_kernel<<<dim3(nItems, n), 32 * FAST_WARPS, smem, st>>>(g, pyr, items, slots, cellCount, tileBytes,
-                                                                      scoreBytes, listBytes);
+    fast_cells_kernel<<<dim3(nItems, n), FAST_THREADS, smem, st>>>(g, pyr, items, slots, cellCount, tileBytes,
+                                                                   kbitsBytes, listBytes);
     return 1;
 }
 
