@@ -90,7 +90,9 @@ struct FastStrip {
     uint32_t* kbits;         // keep bitmap, kw words per tile row
     unsigned short* list;    // survivor list: byte offsets into the tile (tile <= 64 KiB)
     int* cnt;                // [0] list length, [1] mask of cells that came back empty
-    int tp, kw, ch;          // tile pitch, bitmap words per row, tile rows
+    const uint8_t* cedge;    // per tile column: bit 0 = first column of its cell window, bit 1 = last column
+    unsigned tpMagic;        // floor(2^32 / tp) + 1: off / tp == umulhi(off, tpMagic) for off < 65536
+    int tp, kw, ch;          // tile pitch (multiple of 32), bitmap words per row (tp / 32), tile rows
     int colLo, colHi;        // tested tile columns [colLo, colHi)
     int wCell, ncols;        // cell pitch and number of cells in the strip
 };
@@ -164,10 +166,23 @@ __device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t ce
         int base = 0;
         if (lane == 31 && inc > 0) base = atomicAdd(&s.cnt[0], inc);
         base = __shfl_sync(0xffffffffu, base, 31) + inc - n;
-        while (acc) {
-            const int b = __ffs(acc) - 1;
-            acc &= acc - 1;
-            s.list[base++] = (unsigned short)((r0 + (b & 7)) * s.tp + 4 * w + (b >> 3));
+        const int o0 = r0 * s.tp + 4 * w;
+        if (__any_sync(0xffffffffu, n > 10)) {
+            // survivors cluster along edges: when some lane holds many, 32 predicated steps beat a loop whose trip
+            // count is the largest popcount of the warp
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if ((acc >> (8 * j + i)) & 1u) s.list[base++] = (unsigned short)(o0 + i * s.tp + j);
+                }
+            }
+        } else {
+            while (acc) {
+                const int b = __ffs(acc) - 1;
+                acc &= acc - 1;
+                s.list[base++] = (unsigned short)(o0 + (b & 7) * s.tp + (b >> 3));
+            }
         }
     }
     __syncthreads();
@@ -183,21 +198,22 @@ __device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t ce
     __syncthreads();
 
     // ---- C: non-max suppression inside the pixel's own cell window ------------------------------------------------
+    // Scores outside the tested rows / columns of the strip are 0 in the map, so only the borders BETWEEN the cell
+    // windows of the strip need masking (cedge: bit 0 = first column of its window, bit 1 = last column).
     for (int e = tid; e < nlist; e += FAST_THREADS) {
         const int off = s.list[e];
         const uint8_t* q = s.smap + off;
         const int sc = q[0];
         if (sc == 0) continue;
-        const int r = off / s.tp, col = off - r * s.tp;
-        const int j = strip_cell(s, col);
-        const int x0 = s.colLo + j * s.wCell;
-        const int x1 = min(x0 + s.wCell, s.colHi);    // window columns [x0, x1)
-        const bool l = col > x0, rt = col < x1 - 1, u = r > 3, d = r < s.ch - 4;
         const int tp = s.tp;
-        const bool keep = (!l || sc > q[-1]) && (!rt || sc > q[1]) &&
-                          (!u || (sc > q[-tp] && (!l || sc > q[-tp - 1]) && (!rt || sc > q[-tp + 1]))) &&
-                          (!d || (sc > q[tp] && (!l || sc > q[tp - 1]) && (!rt || sc > q[tp + 1])));
-        if (keep) atomicOr(&s.kbits[r * s.kw + (col >> 5)], 1u << (col & 31));
+        const int r = (int)__umulhi((unsigned)off, s.tpMagic);
+        const int fl = s.cedge[off - r * tp];
+        const int mc = max((int)q[-tp], (int)q[tp]);
+        int mL = max(max((int)q[-tp - 1], (int)q[-1]), (int)q[tp - 1]);
+        int mR = max(max((int)q[-tp + 1], (int)q[1]), (int)q[tp + 1]);
+        if (fl & 1) mL = 0;
+        if (fl & 2) mR = 0;
+        if (sc > max(mc, max(mL, mR))) atomicOr(&s.kbits[off >> 5], 1u << (off & 31));
     }
     __syncthreads();
 }
@@ -265,6 +281,7 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
                                                                   int kbitsBytes, int listBytes) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int sCnt[2];
+    __shared__ uint8_t sEdge[1024];
     const FastItem it = items[blockIdx.x];
     const int img = blockIdx.y;
     const LevelGeom& L = g.lv[it.level];
@@ -284,12 +301,14 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
     // strip columns [xs, xe) of the level, as plane columns [ax0, ax1)
     const int xs = kMinBorder + it.col0 * L.wCell;
     const int xe = min(kMinBorder + (it.col0 + it.ncols - 1) * L.wCell + L.wCell + 6, maxBX);
-    const int ax0 = (kXOff + xs) & ~15;
-    const int ax1 = (kXOff + max(xe, xs) + 15) & ~15;
+    const int ax0 = (kXOff + xs) & ~31;
+    const int ax1 = (kXOff + max(xe, xs) + 31) & ~31;
 
     FastStrip s;
     s.tp = ax1 - ax0;
-    s.kw = (s.tp + 31) >> 5;
+    s.kw = s.tp >> 5;
+    s.tpMagic = 0xffffffffu / (unsigned)s.tp + 1u;
+    s.cedge = sEdge;
     s.ch = ch;
     s.tile = smem;
     s.smap = smem + tileBytes;
@@ -312,6 +331,14 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
             *reinterpret_cast<uint4*>(s.smap + r * s.tp + 16 * c) = make_uint4(0, 0, 0, 0);
         }
         for (int i = threadIdx.x; i < s.kw * ch; i += FAST_THREADS) s.kbits[i] = 0;
+        for (int col = threadIdx.x; col < s.tp; col += FAST_THREADS) {
+            int fl = 0;
+            if (col >= s.colLo && col < s.colHi) {
+                const int x0 = s.colLo + strip_cell(s, col) * s.wCell;
+                fl = (col == x0 ? 1 : 0) | (col == min(x0 + s.wCell, s.colHi) - 1 ? 2 : 0);
+            }
+            sEdge[col] = (uint8_t)fl;
+        }
         if (threadIdx.x < 2) sCnt[threadIdx.x] = 0;
     }
     __syncthreads();
@@ -345,10 +372,11 @@ int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* 
                 const int nc = L.nCols - c0 < FAST_ITEM_COLS ? L.nCols - c0 : FAST_ITEM_COLS;
                 if (out && n < cap) out[n] = FastItem{(short)l, (short)r, (short)c0, (short)nc};
                 n++;
-                const int tp = ((nc * L.wCell + 6 + 15 + 15) & ~15) + 16;
+                const int tp = ((nc * L.wCell + 6 + 31 + 31) & ~31) + 32;
+                if (tp > 1024) maxTile = 1 << 28;    // sEdge[] holds 1024 columns
                 const int ch = L.hCell + 6;
                 if (tp * ch > maxTile) maxTile = tp * ch;
-                const int kb = ((tp + 31) / 32) * 4 * ch;
+                const int kb = (tp / 32) * 4 * ch;
                 if (kb > maxK) maxK = kb;
                 const int lb = (nc * L.wCell + 8) * L.hCell * 2;
                 if (lb > maxList) maxList = lb;

@@ -48,15 +48,20 @@ __device__ __forceinline__ void reflect_range(int xa, int xb, int len, int& lo, 
     }
 }
 
-// grid: (ceil(chunks / 64), ceil(rows / 4), n); block (64, 4); one 16-byte chunk of the padded plane per thread
+// grid: (ceil(chunks / 64), ceil(rows / 4), n); block (64, 4); one 16-byte chunk of the padded plane per thread.
+// The chunk index is rotated by 3 so that the chunks touching the right frame and those touching the left frame sit
+// in the same warp: only that warp takes the byte path, all the others copy 128 bits per thread.
 __global__ void __launch_bounds__(256) pad_level0_kernel(const uint8_t* __restrict__ images, int stride,
                                                          size_t imageStride, uint8_t* __restrict__ pyr,
-                                                         unsigned long long slabBytes, int w, int h, int pitch) {
-    const int cx = blockIdx.x * 64 + threadIdx.x;
+                                                         unsigned long long slabBytes, int w, int h, int pitch,
+                                                         int nchunks) {
+    const int cr = blockIdx.x * 64 + threadIdx.x;
     const int py = blockIdx.y * 4 + threadIdx.y;
-    if (py >= h + 2 * kEdge) return;
+    if (py >= h + 2 * kEdge || cr >= nchunks) return;
+    int cx = cr + nchunks - 3;
+    if (cx >= nchunks) cx -= nchunks;
+    if (cx < 0) cx = cr;    // fewer than 3 chunks
     const int c0 = 16 * cx;
-    if (c0 + 15 < kXOff - kEdge || c0 >= kXOff + w + kEdge) return;
     const uint8_t* src = images + (size_t)blockIdx.z * imageStride + (size_t)reflect101(py - kEdge, h) * stride;
     uint4* dst = reinterpret_cast<uint4*>(pyr + (size_t)blockIdx.z * slabBytes + (size_t)py * pitch + c0);
     const int x0 = c0 - kXOff;
@@ -72,7 +77,11 @@ __global__ void __launch_bounds__(256) pad_level0_kernel(const uint8_t* __restri
         for (int b = 0; b < 4; b++) {
             const int x = x0 + 4 * q + b;
             uint32_t v = 0;
-            if (x >= -kEdge && x < w + kEdge) v = __ldg(src + reflect101(x, w));
+            if (x >= -kEdge && x < w + kEdge) {
+                int xr = x < 0 ? -x : (x >= w ? 2 * w - 2 - x : x);
+                if ((unsigned)xr >= (unsigned)w) xr = reflect101(x, w);    // images narrower than the frame
+                v = __ldg(src + xr);
+            }
             out |= v << (8 * b);
         }
         o[q] = out;
@@ -229,7 +238,7 @@ int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size
             const int chunks = (kXOff + L.w + kEdge + 15) / 16;
             const dim3 grid((chunks + 63) / 64, (L.h + 2 * kEdge + 3) / 4, n);
             pad_level0_kernel<<<grid, dim3(64, 4), 0, st>>>(images, stride, imageStride, pyr + L.planeOff, g.slabBytes,
-                                                            L.w, L.h, L.pitch);
+                                                            L.w, L.h, L.pitch, chunks);
         } else {
             const LevelGeom& P = g.lv[l - 1];
             const ResizeDims& d = dims[l];
