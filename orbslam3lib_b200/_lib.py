@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "liborbfe.so")
+SO_PATH = os.environ.get("ORBFE_SO") or os.path.join(_HERE, "liborbfe.so")    # ORBFE_SO: kernel-tuning builds
 CSRC = os.path.join(_HERE, "csrc")
 
 OK, ERR_ARG, ERR_CAPACITY, ERR_CUDA, ERR_NCCL, ERR_INTERNAL = 0, -1, -2, -3, -4, -5

@@ -1,85 +1,123 @@
 // k_blur.cu — cv::GaussianBlur(level, 7x7, sigma 2, BORDER_REFLECT_101) of ORBextractor_old.cc:1146-1147.
 //
 // OpenCV's 8-bit path is fixed point and bit exact: Q8 kernel k = [18,34,48,56,48,34,18]
-// (sum 256), horizontal pass H = sum k_i * src (<= 255*256, fits u16), vertical pass V = sum k_j * H,
-// dst = (V + 32768) >> 16.  The reference blurs a clone() of the level, i.e. the image WITHOUT its 19-px frame,
-// reflecting about the true image edge; the padded pyramid plane holds exactly that reflection already (the frame
-// is the REFLECT_101 extension), so the kernel reads its 3-px halo from the plane and never branches on borders.
+// (sum 256), horizontal pass H = sum k_i * src (<= 255*256, exact in 16 bits), vertical pass V = sum k_j * H,
+// dst = (V + 32768) >> 16.  Nothing is rounded before the final shift, so the result is the exact integer 2-D
+// convolution with k (x) k and the two passes may run in either order.  The reference blurs a clone() of the level,
+// i.e. the image WITHOUT its 19-px frame, reflecting about the true image edge; the padded pyramid plane holds exactly
+// that reflection already, so the kernel reads its 3-px halo from the plane and never branches on borders.
 //
-// HBM-bound: read P + write P bytes per image.  One CTA = one 128 x 32 output tile of one level of
-// one image: 16-byte coalesced loads of the (128+32) x (32+6) source window into shared memory, horizontal pass to a
-// u16 tile in shared memory, vertical pass, one 32-bit store per 4 output pixels.
+// HBM-bound by bytes (read P + write P per image); organised for few instructions per pixel:
+//   * one WARP = one strip of <= 30 output words (120 px) x BL_ROWS rows; a lane owns one 32-bit word column (4 px)
+//     and walks down the rows with coalesced 128-byte row reads straight from global memory (no shared memory);
+//   * vertical pass first, SWAR: the word is split into even / odd bytes (two 16-bit lanes per register), a 7-row
+//     window lives in registers (fully unrolled, statically indexed), 3 adds + 4 multiply-adds per register give the
+//     Q8.8 column sums of 2 pixels at once (<= 65280: no carry between the lanes);
+//   * horizontal pass: the neighbour lanes' sums come by warp shuffle, adjacent 16-bit pairs are formed with PRMT and
+//     every output is four IDP.2A (16-bit x 8-bit dot products) accumulated on the rounding constant 32768;
+//   * lanes 0 and 31 of a strip are halo lanes (strips overlap by two words); one 32-bit store per 4 output pixels.
 #include "orbfe_internal.h"
 
 namespace orbfe {
 
-constexpr int BT_W = 128, BT_H = 32;
-constexpr int BT_SW = BT_W + 32;    // source window width (16-byte aligned halo on both sides)
-constexpr int BT_SH = BT_H + 6;
+constexpr int BL_ROWS = 32;       // output rows per warp tile
+constexpr int BL_WORDS = 30;      // output words per strip (lanes 1..30)
+constexpr int BL_WARPS = 8;
 
 struct BlurTile {
     short level, tx, ty, pad;
 };
 
-__global__ void __launch_bounds__(256) gauss7x7_kernel(const __grid_constant__ Geom g, const uint8_t* __restrict__ pyr,
-                                                       uint8_t* __restrict__ blur, const BlurTile* __restrict__ tiles,
-                                                       const int* __restrict__ levelCount) {
-    __shared__ __align__(16) uint8_t sSrc[BT_SH * BT_SW];
-    __shared__ __align__(16) uint16_t sH[BT_SH * BT_W];
-    const BlurTile t = tiles[blockIdx.x];
+__host__ __device__ inline void blur_strips(int w, int* nStrips, int* stripWords) {
+    const int words = (w + 3) >> 2;
+    const int ns = (words + BL_WORDS - 1) / BL_WORDS;
+    *nStrips = ns;
+    *stripWords = (words + ns - 1) / ns;
+}
+
+// grid (ceil(nTiles / BL_WARPS), n); block 32 * BL_WARPS; one warp per tile
+__global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_constant__ Geom g,
+                                                                 const uint8_t* __restrict__ pyr,
+                                                                 uint8_t* __restrict__ blur,
+                                                                 const BlurTile* __restrict__ tiles, int nTiles,
+                                                                 const int* __restrict__ levelCount) {
+    const int lane = threadIdx.x & 31;
+    const int ti = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
+    if (ti >= nTiles) return;
+    const BlurTile t = tiles[ti];
     const int img = blockIdx.y;
     // ORBextractor_old.cc:1140-1141: levels without keypoints are not blurred
     if (levelCount && levelCount[img * g.nlevels + t.level] == 0) return;
     const LevelGeom& L = g.lv[t.level];
-    const int x0 = t.tx * BT_W, y0 = t.ty * BT_H;
-    const uint8_t* plane = pyr + (size_t)img * g.slabBytes + L.planeOff;
+    int nStrips, sw;
+    blur_strips(L.w, &nStrips, &sw);
+    const int words = (L.w + 3) >> 2;
+    const int wfirst = t.tx * sw;                          // first output word of the strip
+    const int wlast = min(wfirst + sw, words);             // one past the last output word
+    const int wi = wfirst - 1 + lane;                      // this lane's word (level x = 4 * wi)
+    const int y0 = t.ty * BL_ROWS;
+    const int pc = kXOff + 4 * wi;                         // plane column of the word
+    const bool inPlane = pc >= 0 && pc + 4 <= L.pitch;
+    const bool outLane = lane >= 1 && wi < wlast;
+    const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff;
+    // source row y - 3 of output row y is plane row y - 3 + kEdge
+    const uint8_t* src = pyr + planeBase + (size_t)(y0 - 3 + kEdge) * L.pitch + pc;
+    uint8_t* dst = blur + planeBase + (size_t)(y0 + kEdge) * L.pitch + pc;
     const int planeRows = L.h + 2 * kEdge;
+    const int rowsLeft = L.h - y0;                         // output rows available in this tile (> 0)
 
-    // load rows y0-3 .. y0+BT_H+2, plane columns (kXOff + x0 - 16) .. +BT_SW
-    const int pc0 = kXOff + x0 - 16;
-    for (int i = threadIdx.x; i < BT_SH * (BT_SW / 16); i += 256) {
-        const int r = i / (BT_SW / 16), c = i - r * (BT_SW / 16);
-        const int pr = y0 - 3 + r + kEdge, pc = pc0 + 16 * c;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (pr < planeRows && pc + 16 <= L.pitch) v = __ldg(reinterpret_cast<const uint4*>(plane + (size_t)pr * L.pitch + pc));
-        *reinterpret_cast<uint4*>(&sSrc[r * BT_SW + 16 * c]) = v;
-    }
-    __syncthreads();
+    constexpr uint32_t K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24);    // lo: (18,34)  hi: (48,56)
+    constexpr uint32_t K2 = 48u | (34u << 8) | (0u << 16) | (18u << 24);     // lo: (48,34)  hi: (0,18)
+    constexpr uint32_t K3 = 18u;                                             // lo: (18,0)
 
-    // horizontal pass: 4 adjacent outputs per thread
-    for (int i = threadIdx.x; i < BT_SH * (BT_W / 4); i += 256) {
-        const int r = i / (BT_W / 4), xg = (i - r * (BT_W / 4)) * 4;
-        const uint8_t* s = &sSrc[r * BT_SW + 16 + xg - 3];    // s[0] = src(x - 3)
-        uint32_t p[10];
+    uint32_t E[7], O[7];    // even / odd bytes of the last 7 source rows (16-bit lanes)
 #pragma unroll
-        for (int k = 0; k < 10; k++) p[k] = s[k];
-        uint32_t o[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++)
-            o[k] = 18u * (p[k] + p[k + 6]) + 34u * (p[k + 1] + p[k + 5]) + 48u * (p[k + 2] + p[k + 4]) + 56u * p[k + 3];
-        *reinterpret_cast<uint2*>(&sH[r * BT_W + xg]) = make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
-    }
-    __syncthreads();
-
-    // vertical pass
-    uint8_t* out = blur + (size_t)img * g.slabBytes + L.planeOff;
-    for (int i = threadIdx.x; i < BT_H * (BT_W / 4); i += 256) {
-        const int r = i / (BT_W / 4), xg = (i - r * (BT_W / 4)) * 4;
-        const int x = x0 + xg, y = y0 + r;
-        if (x >= L.w || y >= L.h) continue;
-        uint32_t acc[4] = {0, 0, 0, 0};
-        const uint32_t kk[7] = {18, 34, 48, 56, 48, 34, 18};
-#pragma unroll
-        for (int j = 0; j < 7; j++) {
-            const uint2 hv = *reinterpret_cast<const uint2*>(&sH[(r + j) * BT_W + xg]);
-            acc[0] += kk[j] * (hv.x & 0xffffu);
-            acc[1] += kk[j] * (hv.x >> 16);
-            acc[2] += kk[j] * (hv.y & 0xffffu);
-            acc[3] += kk[j] * (hv.y >> 16);
+    for (int i = 0; i < BL_ROWS + 6; i++) {
+        // source row i of the tile = plane row y0 - 3 + kEdge + i
+        uint32_t wv = 0;
+        if (inPlane && (y0 - 3 + kEdge + i) < planeRows && i < rowsLeft + 6)
+            wv = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)i * L.pitch));
+        E[i % 7] = wv & 0x00ff00ffu;
+        O[i % 7] = __byte_perm(wv, 0u, 0x4341);
+        if (i >= 6) {
+            const int r = i - 6;    // output row of the tile; window rows r .. r + 6 live in slots (r + k) % 7
+            if (r < rowsLeft) {     // warp-uniform
+                const uint32_t VE = (E[r % 7] + E[(r + 6) % 7]) * 18u + (E[(r + 1) % 7] + E[(r + 5) % 7]) * 34u +
+                                    (E[(r + 2) % 7] + E[(r + 4) % 7]) * 48u + E[(r + 3) % 7] * 56u;    // (v0, v2)
+                const uint32_t VO = (O[r % 7] + O[(r + 6) % 7]) * 18u + (O[(r + 1) % 7] + O[(r + 5) % 7]) * 34u +
+                                    (O[(r + 2) % 7] + O[(r + 4) % 7]) * 48u + O[(r + 3) % 7] * 56u;    // (v1, v3)
+                const uint32_t LE = __shfl_up_sync(0xffffffffu, VE, 1), LO = __shfl_up_sync(0xffffffffu, VO, 1);      // (v-4, v-2), (v-3, v-1)
+                const uint32_t RE = __shfl_down_sync(0xffffffffu, VE, 1), RO = __shfl_down_sync(0xffffffffu, VO, 1);  // (v4, v6), (v5, v7)
+                // adjacent pairs (lo lane first)
+                const uint32_t Pm3 = __byte_perm(LO, LE, 0x7610);    // (v-3, v-2)
+                const uint32_t Pm2 = __byte_perm(LE, LO, 0x7632);    // (v-2, v-1)
+                const uint32_t Pm1 = __byte_perm(LO, VE, 0x5432);    // (v-1, v0)
+                const uint32_t P0 = __byte_perm(VE, VO, 0x5410);     // (v0, v1)
+                const uint32_t P1 = __byte_perm(VO, VE, 0x7610);     // (v1, v2)
+                const uint32_t P2 = __byte_perm(VE, VO, 0x7632);     // (v2, v3)
+                const uint32_t P3 = __byte_perm(VO, RE, 0x5432);     // (v3, v4)
+                const uint32_t P4 = __byte_perm(RE, RO, 0x5410);     // (v4, v5)
+                uint32_t o0 = __dp2a_lo(Pm3, K1, 32768u);            // v-3*18 + v-2*34
+                o0 = __dp2a_hi(Pm1, K1, o0);                         // v-1*48 + v0*56
+                o0 = __dp2a_lo(P1, K2, o0);                          // v1*48 + v2*34
+                o0 = __dp2a_hi(P2, K2, o0);                          // v3*18
+                uint32_t o1 = __dp2a_lo(Pm2, K1, 32768u);            // v-2*18 + v-1*34
+                o1 = __dp2a_hi(P0, K1, o1);                          // v0*48 + v1*56
+                o1 = __dp2a_lo(P2, K2, o1);                          // v2*48 + v3*34
+                o1 = __dp2a_lo(P4, K3, o1);                          // v4*18
+                uint32_t o2 = __dp2a_lo(Pm1, K1, 32768u);            // v-1*18 + v0*34
+                o2 = __dp2a_hi(P1, K1, o2);                          // v1*48 + v2*56
+                o2 = __dp2a_lo(P3, K2, o2);                          // v3*48 + v4*34
+                o2 = __dp2a_hi(P4, K2, o2);                          // v5*18
+                uint32_t o3 = __dp2a_lo(P0, K1, 32768u);             // v0*18 + v1*34
+                o3 = __dp2a_hi(P2, K1, o3);                          // v2*48 + v3*56
+                o3 = __dp2a_lo(P4, K2, o3);                          // v4*48 + v5*34
+                o3 = __dp2a_hi(RE, K2, o3);                          // v6*18
+                // byte 2 of every accumulator = (V + 32768) >> 16
+                const uint32_t out = __byte_perm(__byte_perm(o0, o1, 0x0062), __byte_perm(o2, o3, 0x0062), 0x5410);
+                if (outLane) *reinterpret_cast<uint32_t*>(dst + (size_t)r * L.pitch) = out;
+            }
         }
-        const uint32_t o = ((acc[0] + 32768u) >> 16) | (((acc[1] + 32768u) >> 16) << 8) |
-                           (((acc[2] + 32768u) >> 16) << 16) | (((acc[3] + 32768u) >> 16) << 24);
-        *reinterpret_cast<uint32_t*>(out + (size_t)(y + kEdge) * L.pitch + kXOff + x) = o;
     }
 }
 
@@ -87,7 +125,9 @@ __global__ void __launch_bounds__(256) gauss7x7_kernel(const __grid_constant__ G
 int blur_tile_table(const Geom& g, BlurTile* out, int cap) {
     int n = 0;
     for (int l = 0; l < g.nlevels; l++) {
-        const int tx = (g.lv[l].w + BT_W - 1) / BT_W, ty = (g.lv[l].h + BT_H - 1) / BT_H;
+        int tx, sw;
+        blur_strips(g.lv[l].w, &tx, &sw);
+        const int ty = (g.lv[l].h + BL_ROWS - 1) / BL_ROWS;
         for (int y = 0; y < ty; y++)
             for (int x = 0; x < tx; x++) {
                 if (out && n < cap) out[n] = BlurTile{(short)l, (short)x, (short)y, 0};
@@ -99,7 +139,9 @@ int blur_tile_table(const Geom& g, BlurTile* out, int cap) {
 
 int launch_blur_tiles(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, const void* tiles, int nTiles,
                       const int* levelCount, cudaStream_t st) {
-    gauss7x7_kernel<<<dim3(nTiles, n), 256, 0, st>>>(g, pyr, blur, (const BlurTile*)tiles, levelCount);
+    if (nTiles <= 0) return 0;
+    gauss7x7_kernel<<<dim3((nTiles + BL_WARPS - 1) / BL_WARPS, n), 32 * BL_WARPS, 0, st>>>(
+        g, pyr, blur, (const BlurTile*)tiles, nTiles, levelCount);
     return 1;
 }
 

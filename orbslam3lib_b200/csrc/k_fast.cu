@@ -28,9 +28,16 @@
 
 namespace orbfe {
 
-constexpr int FAST_THREADS = 256;
+#ifndef ORBFE_FAST_THREADS
+#define ORBFE_FAST_THREADS 256
+#endif
+#ifndef ORBFE_FAST_COLS
+#define ORBFE_FAST_COLS 8
+#endif
+constexpr int FAST_THREADS = ORBFE_FAST_THREADS;
 constexpr int FAST_WARPS = FAST_THREADS / 32;
-constexpr int FAST_ITEM_COLS = 8;    // <= FAST_WARPS (phase D gives a warp to every cell)
+constexpr int FAST_ITEM_COLS = ORBFE_FAST_COLS;    // <= FAST_WARPS (phase D gives a warp to every cell)
+static_assert(FAST_ITEM_COLS <= FAST_WARPS, "phase D gives a warp to every cell");
 
 __device__ __forceinline__ uint32_t swap16(uint32_t a) { return __byte_perm(a, a, 0x1032); }
 
