@@ -105,6 +105,12 @@ int orbfe_level_read(orbfe_extractor* ex, int index, int level, int which, uint8
 int orbfe_level_candidates(orbfe_extractor* ex, int index, int level, int32_t* out_xyr, int cap);
 /* post-octree keypoints of a level, level coordinates, with angle (ORBextractor_old.cc:879-897). */
 int orbfe_level_keypoints(orbfe_extractor* ex, int index, int level, orbfe_keypoint* out, int cap);
+/* Device-resident copies of the outputs of the LAST chunk of the last orbfe_extract* call (all of them when the batch
+ * fitted one chunk, which is the normal case): keypoints and descriptors strided by *cap, int32 counts per image.
+ * Valid until the next call on this extractor.  Lets the matcher consume descriptors without a host round trip:
+ * orbfe_knn2_batch(m, desc, counts, cap, desc + P*cap*32, counts + P, cap, P, idx, dist, ORBFE_IN_DEVICE). */
+int orbfe_extractor_device_outputs(orbfe_extractor* ex, const orbfe_keypoint** kps, const uint8_t** desc,
+                                   const int32_t** counts, int* n, int* cap);
 /* device time (ms) of each stage of the last call, measured with CUDA events:
  * [0] h2d, [1] pyramid, [2] fast, [3] octree, [4] blur, [5] angle+descriptors+pack, [6] d2h */
 int orbfe_extractor_stage_ms(const orbfe_extractor* ex, float out[7]);

@@ -62,6 +62,7 @@ SYMBOLS = {
     "orbfe_level_read": (_i, [_vp, _i, _i, _i, _vp, _i]),
     "orbfe_level_candidates": (_i, [_vp, _i, _i, _vp, _i]),
     "orbfe_level_keypoints": (_i, [_vp, _i, _i, _vp, _i]),
+    "orbfe_extractor_device_outputs": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "orbfe_extractor_stage_ms": (_i, [_vp, _vp]),
     "orbfe_extractor_last_launches": (_i, [_vp]),
     "orbfe_matcher_create": (_i, [_i, C.POINTER(_vp)]),

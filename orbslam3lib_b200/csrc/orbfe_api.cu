@@ -202,6 +202,8 @@ struct orbfe_extractor {
     cudaStream_t stream = nullptr;       // the stream in use
     cudaStream_t ownStream = nullptr;    // the private stream (owned)
     cudaEvent_t ev[8] = {};
+    cudaStream_t inStream = nullptr, outStream = nullptr;    // copy streams of the pipelined host path
+    std::vector<cudaEvent_t> pipeEv;                         // 2 events per sub-chunk (input landed, compute done)
     std::mutex mu;
     std::string err;
     size_t wsLimit = (size_t)24 << 30;
@@ -220,12 +222,16 @@ struct orbfe_extractor {
     size_t perImageBytes = 0;
     DevBuf dPyr, dBlur, dSlots, dCellCount, dLevelKeys, dLevelCount, dScratch, dWork, dResult, dErr;
     DevBuf dIn, dKps, dDesc;    // staging for host inputs / outputs
+    DevBuf dCounts;             // int32 keypoint counts of the last chunk (orbfe_extractor_device_outputs)
     ExtractBuffers bufs{};
 
     // last call (stage outputs for the parity accessors)
     int lastChunkBase = 0, lastChunkN = 0, lastCap = 0, lastLaunches = 0;
     const orbfe_keypoint* lastKps = nullptr;    // device pointers of the last chunk's outputs
     const uint8_t* lastDesc = nullptr;
+    int lastOutN = 0;                              // outputs of the whole last chunk (device copies)
+    const orbfe_keypoint* lastOutKps = nullptr;
+    const uint8_t* lastOutDesc = nullptr;
     float stageMs[7] = {0, 0, 0, 0, 0, 0, 0};
 };
 
@@ -367,24 +373,26 @@ static int reserve_workspace(orbfe_extractor* ex, int chunk) {
 
 // run the kernels on `n` images already resident on the device; outputs go to device buffers dKps/dDesc (cap-strided)
 static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int stride, size_t imageStride, int lap0,
-                     int lap1, orbfe_keypoint* dKps, uint8_t* dDesc, int cap) {
+                     int lap1, orbfe_keypoint* dKps, uint8_t* dDesc, int cap, ImageResult* resultDst, bool timed) {
     const Geom& g = ex->geom;
     cudaStream_t st = ex->stream;
     int launches = 0;
-    cudaEventRecord(ex->ev[1], st);
+    ExtractBuffers bufs = ex->bufs;
+    bufs.result = resultDst;
+    if (timed) cudaEventRecord(ex->ev[1], st);
     launches += launch_pyramid(g, dImages, n, stride, imageStride, ex->bufs.pyr, ex->xtab, ex->ytab,
                                ex->rsDims[n >= 32 ? 0 : 1], st);
-    cudaEventRecord(ex->ev[2], st);
+    if (timed) cudaEventRecord(ex->ev[2], st);
     launches += launch_fast(g, ex->bufs.pyr, n, (const FastItem*)ex->dItems.p, ex->nItems, ex->tileBytes, ex->scoreBytes,
                             ex->listBytes, ex->bufs.slots, ex->bufs.cellCount, st);
-    cudaEventRecord(ex->ev[3], st);
-    launches += launch_octree(g, n, ex->bufs, ex->nodeCap, ex->keySmem, st);
-    cudaEventRecord(ex->ev[4], st);
+    if (timed) cudaEventRecord(ex->ev[3], st);
+    launches += launch_octree(g, n, bufs, ex->nodeCap, ex->keySmem, st);
+    if (timed) cudaEventRecord(ex->ev[4], st);
     launches += launch_blur_tiles(g, ex->bufs.pyr, ex->bufs.blur, n, ex->dBlurTiles.p, ex->nBlurTiles, ex->bufs.levelCount, st);
-    cudaEventRecord(ex->ev[5], st);
-    launches += launch_pack(g, n, ex->bufs, lap0, lap1, st);
-    launches += launch_describe(g, n, ex->bufs, dKps, dDesc, cap, st);
-    cudaEventRecord(ex->ev[6], st);
+    if (timed) cudaEventRecord(ex->ev[5], st);
+    launches += launch_pack(g, n, bufs, lap0, lap1, st);
+    launches += launch_describe(g, n, bufs, dKps, dDesc, cap, st);
+    if (timed) cudaEventRecord(ex->ev[6], st);
     ORBFE_CUDA(ex, cudaGetLastError());
     g_launches += launches;
     ex->lastLaunches += launches;
@@ -422,6 +430,8 @@ int orbfe_extractor_create(int device, const orbfe_params* params, orbfe_extract
         return ORBFE_ERR_CUDA;
     }
     ex->stream = ex->ownStream;
+    cudaStreamCreateWithFlags(&ex->inStream, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&ex->outStream, cudaStreamNonBlocking);
     for (auto& e : ex->ev) cudaEventCreate(&e);
     *out = ex;
     return ORBFE_OK;
@@ -433,9 +443,12 @@ int orbfe_extractor_destroy(orbfe_extractor* ex) {
     if (ex->stream) cudaStreamSynchronize(ex->stream);
     DevBuf* bufs[] = {&ex->dItems, &ex->dBlurTiles, &ex->dTaps, &ex->dPyr, &ex->dBlur, &ex->dSlots, &ex->dCellCount,
                       &ex->dLevelKeys, &ex->dLevelCount, &ex->dScratch, &ex->dWork, &ex->dResult, &ex->dErr, &ex->dIn,
-                      &ex->dKps, &ex->dDesc};
+                      &ex->dKps, &ex->dDesc, &ex->dCounts};
     for (DevBuf* b : bufs) b->release();
     for (auto& e : ex->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : ex->pipeEv) cudaEventDestroy(e);
+    if (ex->inStream) cudaStreamDestroy(ex->inStream);
+    if (ex->outStream) cudaStreamDestroy(ex->outStream);
     if (ex->ownStream) cudaStreamDestroy(ex->ownStream);
     delete ex;
     return ORBFE_OK;
@@ -509,6 +522,7 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
     rc = reserve_workspace(ex, chunk);
     if (rc != ORBFE_OK) return rc;
     if (!inDev) ORBFE_CUDA(ex, ex->dIn.reserve((size_t)chunk * width * height));
+    ORBFE_CUDA(ex, ex->dCounts.reserve((size_t)chunk * 4));
     if (!outDev) {
         ORBFE_CUDA(ex, ex->dKps.reserve(std::max<size_t>(16, (size_t)chunk * cap * sizeof(orbfe_keypoint))));
         ORBFE_CUDA(ex, ex->dDesc.reserve(std::max<size_t>(16, (size_t)chunk * cap * 32)));
@@ -524,40 +538,98 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
         const uint8_t* dImages = src;
         int dStride = stride;
         size_t dImageStride = image_stride;
-        cudaEventRecord(ex->ev[0], st);
-        if (!inDev) {
-            // one 2-D copy per chunk when the images are evenly spaced (rows of all images form one pitched array)
-            if (stride == width && (m == 1 || image_stride == (size_t)width * height)) {
-                ORBFE_CUDA(ex, cudaMemcpyAsync(ex->dIn.p, src, (size_t)m * width * height, cudaMemcpyHostToDevice, st));
-            } else {
-                for (int i = 0; i < m; i++)
-                    ORBFE_CUDA(ex, cudaMemcpy2DAsync((uint8_t*)ex->dIn.p + (size_t)i * width * height, width,
-                                                     src + (size_t)i * image_stride, stride, width, height,
-                                                     cudaMemcpyHostToDevice, st));
-            }
-            dImages = (const uint8_t*)ex->dIn.p;
-            dStride = width;
-            dImageStride = (size_t)width * height;
-        }
         orbfe_keypoint* dK = outDev ? kps + (size_t)base * cap : (orbfe_keypoint*)ex->dKps.p;
         uint8_t* dD = outDev ? desc + (size_t)base * cap * 32 : (uint8_t*)ex->dDesc.p;
-        rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap);
-        if (rc != ORBFE_OK) return rc;
-        // results
         int errFlag = 0;
-        ORBFE_CUDA(ex, cudaMemcpyAsync(res.data(), ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
-        ORBFE_CUDA(ex, cudaMemcpyAsync(&errFlag, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
-        if (!outDev && cap > 0) {
-            ORBFE_CUDA(ex, cudaMemcpyAsync(kps + (size_t)base * cap, dK, (size_t)m * cap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
-            ORBFE_CUDA(ex, cudaMemcpyAsync(desc + (size_t)base * cap * 32, dD, (size_t)m * cap * 32, cudaMemcpyDeviceToHost, st));
+        const bool contiguous = stride == width && (m == 1 || image_stride == (size_t)width * height);
+        const int kSub = 128;    // images per pipeline stage
+        if (!inDev && !outDev && contiguous && m >= 2 * kSub && ex->inStream && ex->outStream) {
+            // host -> host: software pipeline over sub-chunks.  The copy-in of stage k+1 and the copy-out of stage k-1
+            // overlap the kernels of stage k (three streams, two events per stage); the workspace is re-used by
+            // every stage (the compute stream is in order), inputs / outputs / per-image results are chunk sized.
+            const int nsub = (m + kSub - 1) / kSub;
+            while ((int)ex->pipeEv.size() < 2 * nsub) {
+                cudaEvent_t e;
+                ORBFE_CUDA(ex, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                ex->pipeEv.push_back(e);
+            }
+            const size_t imgBytes = (size_t)width * height;
+            cudaEventRecord(ex->ev[0], st);
+            ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->inStream, ex->ev[0], 0));    // after the caller's earlier work
+            for (int k = 0; k < nsub; k++) {
+                const int b0 = k * kSub, mk = std::min(kSub, m - b0);
+                ORBFE_CUDA(ex, cudaMemcpyAsync((uint8_t*)ex->dIn.p + (size_t)b0 * imgBytes, src + (size_t)b0 * imgBytes,
+                                               (size_t)mk * imgBytes, cudaMemcpyHostToDevice, ex->inStream));
+                ORBFE_CUDA(ex, cudaEventRecord(ex->pipeEv[2 * k], ex->inStream));
+            }
+            for (int k = 0; k < nsub; k++) {
+                const int b0 = k * kSub, mk = std::min(kSub, m - b0);
+                ORBFE_CUDA(ex, cudaStreamWaitEvent(st, ex->pipeEv[2 * k], 0));
+                rc = run_chunk(ex, (const uint8_t*)ex->dIn.p + (size_t)b0 * imgBytes, mk, width, imgBytes, lap0, lap1,
+                               dK + (size_t)b0 * cap, dD + (size_t)b0 * cap * 32, cap, ex->bufs.result + b0, false);
+                if (rc != ORBFE_OK) return rc;
+                ORBFE_CUDA(ex, cudaEventRecord(ex->pipeEv[2 * k + 1], st));
+                if (cap > 0) {
+                    ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->outStream, ex->pipeEv[2 * k + 1], 0));
+                    ORBFE_CUDA(ex, cudaMemcpyAsync(kps + (size_t)(base + b0) * cap, dK + (size_t)b0 * cap,
+                                                   (size_t)mk * cap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, ex->outStream));
+                    ORBFE_CUDA(ex, cudaMemcpyAsync(desc + (size_t)(base + b0) * cap * 32, dD + (size_t)b0 * cap * 32,
+                                                   (size_t)mk * cap * 32, cudaMemcpyDeviceToHost, ex->outStream));
+                }
+            }
+            ORBFE_CUDA(ex, cudaMemcpyAsync(res.data(), ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
+            ORBFE_CUDA(ex, cudaMemcpyAsync(&errFlag, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
+            ORBFE_CUDA(ex, cudaMemcpy2DAsync(ex->dCounts.p, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
+            cudaEventRecord(ex->ev[7], st);
+            ORBFE_CUDA(ex, cudaStreamSynchronize(st));
+            ORBFE_CUDA(ex, cudaStreamSynchronize(ex->outStream));
+            ORBFE_CUDA(ex, cudaStreamSynchronize(ex->inStream));
+            // the workspace holds the last stage only (stage accessors: orbfe_level_read ...)
+            ex->lastChunkBase = base + (nsub - 1) * kSub;
+            ex->lastChunkN = m - (nsub - 1) * kSub;
+            ex->lastKps = dK + (size_t)(nsub - 1) * kSub * cap;
+            ex->lastDesc = dD + (size_t)(nsub - 1) * kSub * cap * 32;
+        } else {
+            cudaEventRecord(ex->ev[0], st);
+            if (!inDev) {
+                // one copy per chunk when the images are contiguous, else one 2-D copy per image
+                if (contiguous) {
+                    ORBFE_CUDA(ex, cudaMemcpyAsync(ex->dIn.p, src, (size_t)m * width * height, cudaMemcpyHostToDevice, st));
+                } else {
+                    for (int i = 0; i < m; i++)
+                        ORBFE_CUDA(ex, cudaMemcpy2DAsync((uint8_t*)ex->dIn.p + (size_t)i * width * height, width,
+                                                         src + (size_t)i * image_stride, stride, width, height,
+                                                         cudaMemcpyHostToDevice, st));
+                }
+                dImages = (const uint8_t*)ex->dIn.p;
+                dStride = width;
+                dImageStride = (size_t)width * height;
+            }
+            rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap, ex->bufs.result, true);
+            if (rc != ORBFE_OK) return rc;
+            ORBFE_CUDA(ex, cudaMemcpyAsync(res.data(), ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
+            ORBFE_CUDA(ex, cudaMemcpyAsync(&errFlag, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
+            ORBFE_CUDA(ex, cudaMemcpy2DAsync(ex->dCounts.p, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
+            if (!outDev && cap > 0) {
+                ORBFE_CUDA(ex, cudaMemcpyAsync(kps + (size_t)base * cap, dK, (size_t)m * cap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
+                ORBFE_CUDA(ex, cudaMemcpyAsync(desc + (size_t)base * cap * 32, dD, (size_t)m * cap * 32, cudaMemcpyDeviceToHost, st));
+            }
+            cudaEventRecord(ex->ev[7], st);
+            ORBFE_CUDA(ex, cudaStreamSynchronize(st));
+            for (int i = 0; i < 7; i++) {
+                float ms = 0;
+                if (cudaEventElapsedTime(&ms, ex->ev[i], ex->ev[i + 1]) == cudaSuccess) ex->stageMs[i] += ms;
+            }
+            ex->lastChunkBase = base;
+            ex->lastChunkN = m;
+            ex->lastKps = dK;
+            ex->lastDesc = dD;
         }
-        cudaEventRecord(ex->ev[7], st);
-        ORBFE_CUDA(ex, cudaStreamSynchronize(st));
+        ex->lastCap = cap;
+        ex->lastOutN = m;
+        ex->lastOutKps = dK;
+        ex->lastOutDesc = dD;
         if (errFlag) return set_err(ex, ORBFE_ERR_INTERNAL, "quadtree capacity exceeded on the device (images %d..%d)", base, base + m - 1);
-        for (int i = 0; i < 7; i++) {
-            float ms = 0;
-            if (cudaEventElapsedTime(&ms, ex->ev[i], ex->ev[i + 1]) == cudaSuccess) ex->stageMs[i] += ms;
-        }
         for (int i = 0; i < m; i++) {
             if (res[i].count > cap) status = ORBFE_ERR_CAPACITY;
             if (outDev) continue;
@@ -570,11 +642,6 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
             if (monos) ORBFE_CUDA(ex, cudaMemcpy2DAsync(monos + base, 4, &ex->bufs.result[0].mono, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
             ORBFE_CUDA(ex, cudaStreamSynchronize(st));
         }
-        ex->lastChunkBase = base;
-        ex->lastChunkN = m;
-        ex->lastCap = cap;
-        ex->lastKps = dK;
-        ex->lastDesc = dD;
     }
     if (status == ORBFE_ERR_CAPACITY) return set_err(ex, status, "keypoint capacity %d too small (need <= %d)", cap, g.outCap);
     return status;
@@ -688,6 +755,19 @@ int orbfe_level_keypoints(orbfe_extractor* ex, int index, int level, orbfe_keypo
         out[k] = kp;
     }
     return n;
+}
+
+int orbfe_extractor_device_outputs(orbfe_extractor* ex, const orbfe_keypoint** kps, const uint8_t** desc,
+                                   const int32_t** counts, int* n, int* cap) {
+    if (!ex) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ex->mu);
+    if (ex->lastOutN == 0) return set_err(ex, ORBFE_ERR_ARG, "no previous extraction");
+    if (kps) *kps = ex->lastOutKps;
+    if (desc) *desc = ex->lastOutDesc;
+    if (counts) *counts = (const int32_t*)ex->dCounts.p;
+    if (n) *n = ex->lastOutN;
+    if (cap) *cap = ex->lastCap;
+    return ORBFE_OK;
 }
 
 int orbfe_extractor_stage_ms(const orbfe_extractor* ex, float out[7]) {

@@ -145,6 +145,14 @@ class ORBextractor:
             self._check(n)
         return out[:n].copy()
 
+    def device_outputs(self):
+        """-> (kps_ptr, desc_ptr, counts_ptr, n, cap): device addresses of the outputs of the last call's last chunk."""
+        k, d, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        n, cap = C.c_int(), C.c_int()
+        self._check(_lib.lib().orbfe_extractor_device_outputs(self._h, C.byref(k), C.byref(d), C.byref(c), C.byref(n),
+                                                              C.byref(cap)))
+        return k.value, d.value, c.value, n.value, cap.value
+
     def stage_ms(self):
         out = np.zeros(7, np.float32)
         _lib.lib().orbfe_extractor_stage_ms(self._h, ptr(out))

@@ -97,3 +97,39 @@ def test_chunked_batch(oracle):
         n = a[0][i]
         np.testing.assert_array_equal(a[2][i, :n], b[2][i, :n])
         np.testing.assert_array_equal(a[3][i, :n], b[3][i, :n])
+
+
+def test_pipelined_host_batch_and_device_outputs(oracle):
+    # >= 256 host images take the pipelined path (copy-in / kernels / copy-out overlapped over 128-image stages);
+    # results must equal image-by-image extraction, and the device-resident outputs must feed the matcher
+    import ctypes as C
+    from orbslam3lib_b200 import BFMatcher, _lib
+    base = [scenes.make(k, 160, 120, 5000 + i) for i, k in enumerate(("texture", "checker", "noise", "flat_blobs", "texture"))]
+    n = 300
+    imgs = np.stack([base[i % len(base)] for i in range(n)])
+    ex = ORBextractor(200, 1.2, 4, 20, 7)
+    counts, monos, kps, desc = ex.extract_batch(imgs)
+    single = ORBextractor(200, 1.2, 4, 20, 7)
+    refs = [single(b) for b in base]
+    for i in range(n):
+        mono, rk, rd = refs[i % len(base)]
+        c = int(counts[i])
+        assert c == len(rk) and int(monos[i]) == mono
+        np.testing.assert_array_equal(kps[i, :c], rk)
+        np.testing.assert_array_equal(desc[i, :c], rd)
+    # oracle on the distinct images
+    for b, (mono, rk, rd) in zip(base, refs):
+        omono, ok, od = oracle.OracleExtractor(200, 1.2, 4, 20, 7)(b)
+        assert omono == mono
+        np.testing.assert_array_equal(rd, od)
+    _, dd, dc, dn, dcap = ex.device_outputs()
+    assert dn == n and dcap == ex.max_keypoints
+    P = n // 2
+    m = BFMatcher()
+    idx = np.full((P, dcap, 2), -1, np.int32)
+    dist = np.full((P, dcap, 2), -1, np.int32)
+    m.knn2_batch_raw(dd, dc, dcap, dd + P * dcap * 32, dc + 4 * P, dcap, P, idx, dist, flags=_lib.IN_DEVICE)
+    for p in (0, 1, 77, P - 1):
+        ri, rdist = oracle.knn2_hamming(desc[p, :counts[p]], desc[P + p, :counts[P + p]])
+        np.testing.assert_array_equal(idx[p, :counts[p]], ri)
+        np.testing.assert_array_equal(dist[p, :counts[p]], rdist)
