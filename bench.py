@@ -107,6 +107,58 @@ def cpu_sample(npairs_sample, threads, budget_s=12.0):
     return frames / dt, pairs / dt * 1e-9, "%d stereo pairs 752x480 nf=1200 x %d repetitions (%.1f s)" % (npairs_sample, reps, dt)
 
 
+def map_knn_leg(args, rank, world, local, dev, dist, matcher):
+    """BASELINE configs[4]: brute-force Hamming kNN k=2 of nq x nt 256-bit descriptors, query rows sharded over the
+    ranks, train set broadcast and results exchanged with NCCL (orbfe_knn2_sharded).  Strong scaling: the problem is
+    fixed, so the per-step time falls with N.  Device time, max over ranks."""
+    import torch
+    from orbslam3lib_b200 import ShardedMatcher, scenes, shard_range
+    nq = nt = int(args.map_rows)
+    q, t = scenes.map_descriptors(nq, nt, 9000)    # every rank derives the same seeded sets; only the root uploads t
+    b, c = shard_range(nq, world, rank)
+    d_q = torch.from_numpy(q[b:b + c].copy()).to(dev)
+    d_t = torch.from_numpy(t).to(dev) if rank == 0 else torch.zeros((nt, 32), dtype=torch.uint8, device=dev)
+    d_idx = torch.full((nq, 2), -9, dtype=torch.int32, device=dev)
+    d_dist = torch.full((nq, 2), -9, dtype=torch.int32, device=dev)
+    sm = ShardedMatcher(matcher, rank, world, local, dist)
+    times = []
+    for it in range(1 + args.map_steps):
+        if world > 1:
+            if rank != 0:
+                d_t.zero_()    # the broadcast has to deliver the train set every step
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = sm.knn2(d_q, nq, d_t, nt, d_idx, d_dist)
+        if world > 1:
+            tt = torch.tensor([ms], device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        if it > 0:
+            times.append(ms)
+    idx = d_idx.cpu().numpy()
+    dd = d_dist.cpu().numpy()
+    out = None
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+        import oracle_lib
+        sel = np.arange(0, nq, max(1, nq // 256))[:256]
+        ri, rd = oracle_lib.knn2_hamming(q[sel], t, threads=oracle_lib.hardware_threads())
+        ok = bool(np.array_equal(idx[sel], ri) and np.array_equal(dd[sel], rd))
+        ms = sum(times) / len(times)
+        _, _, sm_mhz = peaks()
+        gp = nq * nt / (ms * 1e-3) * 1e-9
+        out = {"workload": "c5: %d x %d 256-bit descriptors, k=2, query rows sharded over %d GPU(s), NCCL train "
+                           "broadcast + result exchange" % (nq, nt, world),
+               "ms_per_step": ms, "gpairs_per_s": gp, "scaling": "strong", "steps": args.map_steps,
+               "frac_popc_pipe": gp / (world * 148 * 2.0 * sm_mhz * 1e-3),
+               "checksum": int((idx.astype(np.int64) * 31 + dd).sum() & 0xFFFFFFFFFFFF),
+               "parity_sample": {"rows": int(len(sel)), "vs": "CPU oracle", "ok": ok}}
+    sm.close()
+    del d_q, d_t, d_idx, d_dist
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -155,6 +207,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pairs", type=int, default=512, help="stereo pairs per GPU per step (512 = BASELINE configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--map-rows", type=int, default=1000000, help="rows of the map-scale kNN leg (configs[4]); 0 = skip")
+    ap.add_argument("--map-steps", type=int, default=2)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -250,6 +304,7 @@ def main():
     ms_e2e, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop()
 
+    knn_map = map_knn_leg(args, rank, world, local, dev, dist, mt) if args.map_rows > 0 else None
     if world > 1:
         t = torch.tensor([float(pairs_per_step)], device=dev, dtype=torch.float64)
         dist.all_reduce(t)
@@ -305,6 +360,8 @@ def main():
                      "note": "algorithmic bytes per image x images per step / CUDA-event time of the stage"},
         "stages": stage_report,
     }
+    if knn_map:
+        line["knn_map"] = knn_map
     if not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
         import oracle_lib

@@ -137,6 +137,27 @@ int orbfe_ratio_test(const int32_t* idx, const int32_t* dist, int64_t nq, double
 /* device time (ms) of the kernel(s) of the last call and their launch count */
 int orbfe_matcher_last_ms(const orbfe_matcher* m, float* kernel_ms, int* launches);
 
+/* ---- map-scale matcher over the GPUs of one box (BASELINE configs[4]) ------------------------------
+ * One process per GPU.  Query rows are sharded: rank g owns rows [g*nq/G, (g+1)*nq/G) (orbfe_shard_range); the train
+ * set is broadcast from `root` with NCCL, every rank matches its shard against the whole train set (global train
+ * indices: the tie order of cv::BFMatcher is preserved), and the results are exchanged with NCCL so that every rank
+ * ends with all nq_total rows.  NCCL is loaded at run time (libnccl.so.2 or $ORBFE_NCCL_LIB).  This replaces nothing
+ * in the reference (its matcher is per frame, Frame.cc:1227); it is the partitioned form of the same knnMatch call. */
+int orbfe_shard_range(int64_t n, int world, int rank, int64_t* begin, int64_t* count);
+/* communicator plumbing: rank 0 calls orbfe_nccl_unique_id and ships the 128 bytes to the other ranks by any means
+ * (bench.py: torch.distributed); every rank then creates its communicator (a ncclComm_t returned as void*). */
+int orbfe_nccl_unique_id(char out[128]);
+int orbfe_nccl_comm_create(const char id[128], int rank, int world, int device, void** comm);
+int orbfe_nccl_comm_destroy(void* comm);
+const char* orbfe_nccl_last_error(void);
+/* All pointers are DEVICE memory of the matcher's GPU.  q_shard: this rank's query rows (count from
+ * orbfe_shard_range); t: nt x 32 bytes, filled on `root`, overwritten by the broadcast elsewhere; idx_all / dist_all:
+ * nq_total x 2 int32 on every rank.  world == 1 needs no communicator.  *ms_out: device time of broadcast + match +
+ * exchange on this rank (CUDA events on the matcher's stream). */
+int orbfe_knn2_sharded(orbfe_matcher* m, void* nccl_comm, int rank, int world, const uint8_t* q_shard,
+                       int64_t nq_total, uint8_t* t, int64_t nt, int root, int32_t* idx_all, int32_t* dist_all,
+                       float* ms_out);
+
 /* ---- wire-compatible entry points: the four skel functions of the FastRPC interface ----------------------
  * Same names, argument order and meaning as dsp/src/orbslam_dsp.cpp:866 (open), :931 (close), :1017-1021
  * (extractFeatures) and :567 (bfMatchStereo), so LynxHardwareAccelerator.cpp:62,116,146-150 links against

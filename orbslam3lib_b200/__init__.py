@@ -6,3 +6,4 @@ from . import scenes  # noqa: F401
 from ._lib import KP_DTYPE, OrbfeError, build  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import BFMatcher  # noqa: F401
+from .sharded import ShardedMatcher, shard_range  # noqa: F401

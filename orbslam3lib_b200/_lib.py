@@ -72,6 +72,12 @@ SYMBOLS = {
     "orbfe_knn2_batch": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _u]),
     "orbfe_ratio_test": (_i, [_vp, _vp, _i64, C.c_double, _vp]),
     "orbfe_matcher_last_ms": (_i, [_vp, _vp, _vp]),
+    "orbfe_shard_range": (_i, [_i64, _i, _i, C.POINTER(_i64), C.POINTER(_i64)]),
+    "orbfe_nccl_unique_id": (_i, [_vp]),
+    "orbfe_nccl_comm_create": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),
+    "orbfe_nccl_comm_destroy": (_i, [_vp]),
+    "orbfe_nccl_last_error": (C.c_char_p, []),
+    "orbfe_knn2_sharded": (_i, [_vp, _vp, _i, _i, _vp, _i64, _vp, _i64, _i, _vp, _vp, _vp]),
     "orbslam3_open": (_i, [C.c_char_p, C.POINTER(C.c_uint64)]),
     "orbslam3_close": (_i, [C.c_uint64]),
     "orbslam3_configure": (_i, [C.c_uint64, C.POINTER(Params)]),

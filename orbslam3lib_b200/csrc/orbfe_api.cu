@@ -872,6 +872,25 @@ static int knn_common(orbfe_matcher* m, const uint8_t* q, const int32_t* nq, lon
     return ORBFE_OK;
 }
 
+namespace orbfe {
+// used by orbfe_sharded.cu: one kNN launch on the matcher's stream with device buffers (no host synchronisation).
+// With q == nullptr it only reports the stream.
+int matcher_knn_device(orbfe_matcher* m, const uint8_t* q, long long nq, const uint8_t* t, long long nt, int32_t* idx,
+                       int32_t* dist, cudaStream_t* streamOut) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    if (streamOut) *streamOut = m->stream;
+    if (!q || nq <= 0) return ORBFE_OK;
+    const int launches = launch_knn2(q, nullptr, nq, t, nullptr, nt, 1, nq, nt, nq, nt, idx, dist, m->stream);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    return ORBFE_OK;
+}
+int matcher_fail(orbfe_matcher* m, int code, const char* msg) { return set_merr(m, code, "%s", msg); }
+}    // namespace orbfe
+
 extern "C" {
 
 int orbfe_matcher_create(int device, orbfe_matcher** out) {
