@@ -125,94 +125,104 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {    // cv::fa
 
 constexpr int DS_WARPS = 8;
 
+// cvRound of |v| < 2^22: adding 1.5 * 2^23 leaves the round-half-even integer in the mantissa (one full-rate FADD and
+// one integer subtract instead of a quarter-rate F2I)
+__device__ __forceinline__ int round_rn_magic(float v) { return __float_as_int(__fadd_rn(v, 12582912.f)) - 0x4B400000; }
+
 // grid (ceil(outCap / DS_WARPS), n); block 32 * DS_WARPS
 __global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
                                                                  orbfe_keypoint* __restrict__ kps,
                                                                  uint8_t* __restrict__ desc, int cap) {
-    // pattern in shared memory, transposed so that lane l reads test (8*l + bit) at word bit*32 + l (conflict free);
-    // (__constant__ reads would serialise: every lane needs a different address)
-    __shared__ char4 sPat[256];
+    // pattern in shared memory as floats, transposed so that lane l reads test (8*l + bit) at slot bit*32 + l
+    // (conflict-free 128-bit loads; __constant__ reads would serialise: every lane needs a different address)
+    __shared__ float4 sPat[256];
     {
         const int t = threadIdx.x;    // blockDim.x == 256
-        sPat[(t & 7) * 32 + (t >> 3)] = d_pattern[t];
+        const char4 p = d_pattern[t];
+        sPat[(t & 7) * 32 + (t >> 3)] = make_float4((float)p.x, (float)p.y, (float)p.z, (float)p.w);
     }
     __syncthreads();
     const int img = blockIdx.y, lane = threadIdx.x & 31;
     const int nk = b.result[img].count;
+    // lane = column u + 15 of the orientation patch; umax[] of the rows this lane takes part in, as a bit mask
+    const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+    uint32_t rowMask = 0;    // bit |v|: this column lies inside the disc on rows +-v
+#pragma unroll
+    for (int v = 0; v <= kHalfPatch; v++)
+        if (lane < 2 * kHalfPatch + 1 && au <= g.umax[v]) rowMask |= 1u << v;
     for (int k = blockIdx.x * DS_WARPS + (threadIdx.x >> 5); k < nk; k += gridDim.x * DS_WARPS) {
-    const KpWork w = b.work[(size_t)img * g.outCap + k];
-    const LevelGeom& L = g.lv[w.level];
-    const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff + (size_t)(w.y + kEdge) * L.pitch + kXOff + w.x;
+        const KpWork w = b.work[(size_t)img * g.outCap + k];
+        const LevelGeom& L = g.lv[w.level];
+        const int pitch = L.pitch;
+        const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff + (size_t)(w.y + kEdge) * pitch + kXOff + w.x;
 
-    // ---- IC_Angle: m10 = sum u*I, m01 = sum v*I over the radius-15 disc (:78-105); lane = u + 15
-    const uint8_t* c = b.pyr + planeBase;
-    int m10 = 0, m01 = 0;
-    if (lane < 2 * kHalfPatch + 1) {
-        const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
-        int colSum = 0;
-#pragma unroll 4
-        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-            if (au <= g.umax[v < 0 ? -v : v]) {
-                const int val = c[v * L.pitch + u];
-                colSum += val;
-                m01 += v * val;
+        // ---- IC_Angle: m10 = sum u*I, m01 = sum v*I over the radius-15 disc (:78-105)
+        const uint8_t* c = b.pyr + planeBase + u;
+        int colSum = 0, m01 = 0;
+#pragma unroll
+        for (int v = 1; v <= kHalfPatch; v++) {
+            if ((rowMask >> v) & 1u) {
+                const int lo = c[-v * pitch], hi = c[v * pitch];
+                colSum += lo + hi;
+                m01 += v * (hi - lo);
             }
         }
-        m10 = u * colSum;
-    }
+        if (rowMask & 1u) colSum += c[0];
+        int m10 = u * colSum;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-    // ---- computeOrbDescriptor (:109-148); lane = output byte
-    const float factorPI = (float)(3.14159265358979323846 / 180.f);
-    const float rad = __fmul_rn(angle, factorPI);
-    const float ca = (float)cos((double)rad), sb = (float)sin((double)rad);
-    const uint8_t* center = b.blur + planeBase;
-    uint32_t byte = 0;
-#pragma unroll
-    for (int bit = 0; bit < 8; bit++) {
-        const char4 pt = sPat[bit * 32 + lane];
-        const float x0 = (float)pt.x, y0 = (float)pt.y, x1 = (float)pt.z, y1 = (float)pt.w;
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-        const int t0 = center[r0 * L.pitch + c0], t1 = center[r1 * L.pitch + c1];
-        byte |= (uint32_t)(t0 < t1) << bit;
-    }
-    // 32 bytes -> two 128-bit stores (lanes 0 and 16)
-    uint32_t v = byte | (__shfl_down_sync(0xffffffffu, byte, 1) << 8);
-    v = v | (__shfl_down_sync(0xffffffffu, v, 2) << 16);    // valid in lanes 0,4,8,...
-    const int src = (lane & 16);
-    uint4 q;
-    q.x = __shfl_sync(0xffffffffu, v, src);
-    q.y = __shfl_sync(0xffffffffu, v, src + 4);
-    q.z = __shfl_sync(0xffffffffu, v, src + 8);
-    q.w = __shfl_sync(0xffffffffu, v, src + 12);
-    if (w.dst < cap) {
-        if ((lane & 15) == 0)
-            *reinterpret_cast<uint4*>(desc + ((size_t)img * cap + w.dst) * 32 + (lane >> 4) * 16) = q;
-        // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
-        if (lane < 7) {
-            float fx = (float)w.x, fy = (float)w.y;
-            if (w.level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
-            uint32_t word;
-            switch (lane) {
-                case 0: word = __float_as_uint(fx); break;
-                case 1: word = __float_as_uint(fy); break;
-                case 2: word = __float_as_uint((float)L.scaledPatch); break;
-                case 3: word = __float_as_uint(angle); break;
-                case 4: word = __float_as_uint((float)w.response); break;
-                case 5: word = (uint32_t)w.level; break;
-                default: word = 0xffffffffu; break;
-            }
-            reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + w.dst)[lane] = word;
+        for (int o = 16; o > 0; o >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
         }
-    }
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+        // ---- computeOrbDescriptor (:109-148); lane = output byte
+        const float factorPI = (float)(3.14159265358979323846 / 180.f);
+        const float rad = __fmul_rn(angle, factorPI);
+        double sd, cd;
+        sincos((double)rad, &sd, &cd);
+        const float ca = (float)cd, sb = (float)sd;
+        const uint8_t* center = b.blur + planeBase;
+        uint32_t byte = 0;
+#pragma unroll
+        for (int bit = 0; bit < 8; bit++) {
+            const float4 pt = sPat[bit * 32 + lane];
+            const int r0 = round_rn_magic(__fadd_rn(__fmul_rn(pt.x, sb), __fmul_rn(pt.y, ca)));
+            const int c0 = round_rn_magic(__fsub_rn(__fmul_rn(pt.x, ca), __fmul_rn(pt.y, sb)));
+            const int r1 = round_rn_magic(__fadd_rn(__fmul_rn(pt.z, sb), __fmul_rn(pt.w, ca)));
+            const int c1 = round_rn_magic(__fsub_rn(__fmul_rn(pt.z, ca), __fmul_rn(pt.w, sb)));
+            const int t0 = center[r0 * pitch + c0], t1 = center[r1 * pitch + c1];
+            byte |= (uint32_t)(t0 < t1) << bit;
+        }
+        // 32 bytes -> two 128-bit stores (lanes 0 and 16)
+        uint32_t v = byte | (__shfl_down_sync(0xffffffffu, byte, 1) << 8);
+        v = v | (__shfl_down_sync(0xffffffffu, v, 2) << 16);    // valid in lanes 0,4,8,...
+        const int src = (lane & 16);
+        uint4 q;
+        q.x = __shfl_sync(0xffffffffu, v, src);
+        q.y = __shfl_sync(0xffffffffu, v, src + 4);
+        q.z = __shfl_sync(0xffffffffu, v, src + 8);
+        q.w = __shfl_sync(0xffffffffu, v, src + 12);
+        if (w.dst < cap) {
+            if ((lane & 15) == 0)
+                *reinterpret_cast<uint4*>(desc + ((size_t)img * cap + w.dst) * 32 + (lane >> 4) * 16) = q;
+            // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
+            if (lane < 7) {
+                float fx = (float)w.x, fy = (float)w.y;
+                if (w.level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+                uint32_t word;
+                switch (lane) {
+                    case 0: word = __float_as_uint(fx); break;
+                    case 1: word = __float_as_uint(fy); break;
+                    case 2: word = __float_as_uint((float)L.scaledPatch); break;
+                    case 3: word = __float_as_uint(angle); break;
+                    case 4: word = __float_as_uint((float)w.response); break;
+                    case 5: word = (uint32_t)w.level; break;
+                    default: word = 0xffffffffu; break;
+                }
+                reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + w.dst)[lane] = word;
+            }
+        }
     }    // keypoint loop
 }
 
