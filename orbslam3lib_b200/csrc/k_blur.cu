@@ -23,6 +23,7 @@ namespace orbfe {
 constexpr int BL_ROWS = 32;       // output rows per warp tile
 constexpr int BL_WORDS = 30;      // output words per strip (lanes 1..30)
 constexpr int BL_WARPS = 8;
+constexpr int BL_PF = 8;          // source rows requested ahead of use
 
 struct BlurTile {
     short level, tx, ty, pad;
@@ -71,12 +72,22 @@ __global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_co
     constexpr uint32_t K3 = 18u;                                             // lo: (18,0)
 
     uint32_t E[7], O[7];    // even / odd bytes of the last 7 source rows (16-bit lanes)
+    uint32_t raw[BL_PF];    // loads in flight: row i + BL_PF is requested while row i is consumed
+#pragma unroll
+    for (int j = 0; j < BL_PF; j++) {
+        raw[j] = 0;
+        if (inPlane && (y0 - 3 + kEdge + j) < planeRows && j < rowsLeft + 6)
+            raw[j] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)j * L.pitch));
+    }
 #pragma unroll
     for (int i = 0; i < BL_ROWS + 6; i++) {
         // source row i of the tile = plane row y0 - 3 + kEdge + i
-        uint32_t wv = 0;
-        if (inPlane && (y0 - 3 + kEdge + i) < planeRows && i < rowsLeft + 6)
-            wv = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)i * L.pitch));
+        const uint32_t wv = raw[i % BL_PF];
+        if (i + BL_PF < BL_ROWS + 6) {
+            raw[i % BL_PF] = 0;
+            if (inPlane && (y0 - 3 + kEdge + i + BL_PF) < planeRows && i + BL_PF < rowsLeft + 6)
+                raw[i % BL_PF] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(i + BL_PF) * L.pitch));
+        }
         E[i % 7] = wv & 0x00ff00ffu;
         O[i % 7] = __byte_perm(wv, 0u, 0x4341);
         if (i >= 6) {

@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
                                                                   int kbitsBytes, int listBytes) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int sCnt[2];
-    __shared__ uint8_t sEdge[1024];
+    __shared__ __align__(4) uint8_t sEdge[1024];
     const FastItem it = items[blockIdx.x];
     const int img = blockIdx.y;
     const LevelGeom& L = g.lv[it.level];
@@ -328,25 +328,32 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
     s.ncols = it.ncols;
 
     {
+        // staging: warp w copies tile rows w, w + FAST_WARPS, ...; a lane moves one 16-byte chunk per trip
         const uint8_t* plane = pyr + (size_t)img * g.slabBytes + L.planeOff + (size_t)(iniY + kEdge) * L.pitch + ax0;
         const int vecPerRow = s.tp >> 4;
-        for (int i = threadIdx.x; i < vecPerRow * ch; i += FAST_THREADS) {
-            const int r = i / vecPerRow, c = i - r * vecPerRow;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (ax0 + 16 * c + 16 <= L.pitch) v = __ldg(reinterpret_cast<const uint4*>(plane + (size_t)r * L.pitch + 16 * c));
-            *reinterpret_cast<uint4*>(s.tile + r * s.tp + 16 * c) = v;
-            *reinterpret_cast<uint4*>(s.smap + r * s.tp + 16 * c) = make_uint4(0, 0, 0, 0);
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (int c = lane; c < vecPerRow; c += 32) {
+            const bool in = ax0 + 16 * c + 16 <= L.pitch;
+            for (int r = warp; r < ch; r += FAST_WARPS) {
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (in) v = __ldg(reinterpret_cast<const uint4*>(plane + (size_t)r * L.pitch + 16 * c));
+                *reinterpret_cast<uint4*>(s.tile + r * s.tp + 16 * c) = v;
+                *reinterpret_cast<uint4*>(s.smap + r * s.tp + 16 * c) = make_uint4(0, 0, 0, 0);
+            }
         }
         for (int i = threadIdx.x; i < s.kw * ch; i += FAST_THREADS) s.kbits[i] = 0;
-        for (int col = threadIdx.x; col < s.tp; col += FAST_THREADS) {
-            int fl = 0;
-            if (col >= s.colLo && col < s.colHi) {
-                const int x0 = s.colLo + strip_cell(s, col) * s.wCell;
-                fl = (col == x0 ? 1 : 0) | (col == min(x0 + s.wCell, s.colHi) - 1 ? 2 : 0);
-            }
-            sEdge[col] = (uint8_t)fl;
-        }
+        for (int i = threadIdx.x; i < (s.tp >> 2); i += FAST_THREADS) reinterpret_cast<uint32_t*>(sEdge)[i] = 0;
         if (threadIdx.x < 2) sCnt[threadIdx.x] = 0;
+    }
+    __syncthreads();
+    if (threadIdx.x < it.ncols) {    // first / last column of every cell window (windows are >= 1 column wide)
+        const int x0 = s.colLo + threadIdx.x * s.wCell, x1 = min(x0 + s.wCell, s.colHi);
+        if (x1 > x0) {
+            // a one-column window gets both flags: two byte stores from the same thread, no race between threads
+            // because windows are disjoint
+            sEdge[x0] = (uint8_t)(x1 - 1 == x0 ? 3 : 1);
+            if (x1 - 1 != x0) sEdge[x1 - 1] = 2;
+        }
     }
     __syncthreads();
 
