@@ -133,3 +133,46 @@ def test_pipelined_host_batch_and_device_outputs(oracle):
         ri, rdist = oracle.knn2_hamming(desc[p, :counts[p]], desc[P + p, :counts[P + p]])
         np.testing.assert_array_equal(idx[p, :counts[p]], ri)
         np.testing.assert_array_equal(dist[p, :counts[p]], rdist)
+
+
+# BASELINE.json configs as parity cases (C1 640x480 nf=1000; C3 640x480 stereo nf=500; C4 3840x2160
+# nf=5000 12 levels; C2 is covered by CASES[1] and by the benchmark scene)
+def test_config_c1_previous_frame_matching(oracle):
+    from orbslam3lib_b200 import BFMatcher
+    cur = scenes.make("texture", 640, 480, 1000)
+    prev = scenes.previous_frame(cur, 1000)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7)
+    ref = oracle.OracleExtractor(1000, 1.2, 8, 20, 7)
+    outs = []
+    for img in (cur, prev):
+        mono, kps, desc = ex(img)
+        rm, rk, rd = ref(img)
+        assert mono == rm
+        np.testing.assert_array_equal(desc, rd)
+        np.testing.assert_array_equal(kps["x"], rk["x"])
+        outs.append(desc)
+    idx, dist = BFMatcher().knnMatch(outs[0], outs[1])
+    ri, rdist = oracle.knn2_hamming(outs[0], outs[1])
+    np.testing.assert_array_equal(idx, ri)
+    np.testing.assert_array_equal(dist, rdist)
+    good = BFMatcher.ratio_test(idx, dist, 0.7)
+    assert (good >= 0).sum() > 100    # the shifted frame really matches
+
+
+def test_config_c3_stereo_500(oracle):
+    left = scenes.make("texture", 640, 480, 1003)
+    right = scenes.stereo_right(left, 1003)
+    ex = ORBextractor(500, 1.2, 8, 20, 7)
+    counts, monos, kps, desc = ex.extract_batch(np.stack([left, right]))
+    rc, rm, rk, rd = oracle.extract_batch(np.stack([left, right]), 500, 1.2, 8, 20, 7, threads=2)
+    np.testing.assert_array_equal(counts, rc)
+    for i in range(2):
+        n = counts[i]
+        np.testing.assert_array_equal(desc[i, :n], rd[i, :n])
+        for f in ("x", "y", "octave", "response"):
+            np.testing.assert_array_equal(kps[i, :n][f], rk[i, :n][f])
+
+
+def test_config_c4_4k_12_levels(oracle):
+    n, ties = _compare(oracle, "texture", 3840, 2160, 1004, 5000, 12)
+    assert n >= 5000
