@@ -159,6 +159,43 @@ def map_knn_leg(args, rank, world, local, dev, dist, matcher):
     return out
 
 
+def latency_leg(args, local):
+    """BASELINE configs[2]: Lynx-R1-style 640x480 stereo stream, 500 features per image: per-frame latency of one
+    stereo pair through the C ABI with HOST buffers (copy-in, extraction of both eyes, left->right kNN, copy-out),
+    wall clock around the blocking calls."""
+    import torch
+    from orbslam3lib_b200 import BFMatcher, ORBextractor, _lib, scenes
+    w, h, nf = 640, 480, 500
+    frames = []
+    for k in range(8):
+        left = scenes.make("texture", w, h, 3000 + k)
+        frames.append(torch.from_numpy(np.stack([left, scenes.stereo_right(left, 3000 + k)])).pin_memory())
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, device=local)
+    mt = BFMatcher(device=local)
+    cap = ex.max_keypoints
+    kps = torch.zeros((2, cap, 28), dtype=torch.uint8).pin_memory()
+    desc = torch.zeros((2, cap, 32), dtype=torch.uint8).pin_memory()
+    counts = torch.zeros(2, dtype=torch.int32).pin_memory()
+    monos = torch.zeros(2, dtype=torch.int32).pin_memory()
+    idx = torch.zeros((cap, 2), dtype=torch.int32).pin_memory()
+    dist = torch.zeros((cap, 2), dtype=torch.int32).pin_memory()
+    ts = []
+    for it in range(args.latency_iters + 20):
+        f = frames[it % len(frames)]
+        t0 = time.perf_counter()
+        ex.extract_batch_raw(f, 2, w, h, kps, desc, cap, counts, monos, flags=0)
+        _, dd, dc, _, _ = ex.device_outputs()
+        mt.knn2_batch_raw(dd, dc, cap, dd + cap * 32, dc + 4, cap, 1, idx, dist, flags=_lib.IN_DEVICE)
+        t1 = time.perf_counter()
+        if it >= 20:
+            ts.append((t1 - t0) * 1e3)
+    ts.sort()
+    return {"workload": "c3: 640x480 stereo pair, 500 features/image, host buffers, extraction + L->R kNN per call",
+            "iters": len(ts), "p50_ms": ts[len(ts) // 2], "p99_ms": ts[min(len(ts) - 1, int(len(ts) * 0.99))],
+            "mean_ms": sum(ts) / len(ts), "fps_at_p50": 1e3 / ts[len(ts) // 2],
+            "keypoints": [int(counts[0]), int(counts[1])]}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -209,6 +246,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--map-rows", type=int, default=1000000, help="rows of the map-scale kNN leg (configs[4]); 0 = skip")
     ap.add_argument("--map-steps", type=int, default=2)
+    ap.add_argument("--latency-iters", type=int, default=300, help="stereo pairs of the per-frame latency leg (configs[2]); 0 = skip")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -371,6 +409,8 @@ def main():
     }
     if knn_map:
         line["knn_map"] = knn_map
+    if args.latency_iters > 0:
+        line["latency"] = latency_leg(args, local)
     if not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
         import oracle_lib
