@@ -32,7 +32,7 @@ namespace orbfe {
 #define ORBFE_FAST_THREADS 256
 #endif
 #ifndef ORBFE_FAST_COLS
-#define ORBFE_FAST_COLS 8
+#define ORBFE_FAST_COLS 4
 #endif
 constexpr int FAST_THREADS = ORBFE_FAST_THREADS;
 constexpr int FAST_WARPS = FAST_THREADS / 32;
@@ -288,6 +288,7 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
                                                                   int kbitsBytes, int listBytes) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int sCnt[2];
+    __shared__ __align__(8) uint64_t sBar;
     __shared__ __align__(4) uint8_t sEdge[1024];
     const FastItem it = items[blockIdx.x];
     const int img = blockIdx.y;
@@ -328,19 +329,20 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
     s.ncols = it.ncols;
 
     {
-        // staging: warp w copies tile rows w, w + FAST_WARPS, ...; a lane moves one 16-byte chunk per trip
+        // staging: one TMA bulk copy (cp.async.bulk -> UBLKCP) per tile row, issued by the lanes of warp 0 and
+        // completing on an mbarrier; meanwhile every thread clears the score map, the keep bitmap and the edge table.
+        // Tile columns past the plane pitch are never copied: they lie beyond every tested pixel's ring.
         const uint8_t* plane = pyr + (size_t)img * g.slabBytes + L.planeOff + (size_t)(iniY + kEdge) * L.pitch + ax0;
-        const int vecPerRow = s.tp >> 4;
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        for (int c = lane; c < vecPerRow; c += 32) {
-            const bool in = ax0 + 16 * c + 16 <= L.pitch;
-            for (int r = warp; r < ch; r += FAST_WARPS) {
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (in) v = __ldg(reinterpret_cast<const uint4*>(plane + (size_t)r * L.pitch + 16 * c));
-                *reinterpret_cast<uint4*>(s.tile + r * s.tp + 16 * c) = v;
-                *reinterpret_cast<uint4*>(s.smap + r * s.tp + 16 * c) = make_uint4(0, 0, 0, 0);
-            }
+        const uint32_t rowBytes = (uint32_t)min(s.tp, L.pitch - ax0);
+        if (threadIdx.x == 0) mbar_init(&sBar, 1);
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            if (threadIdx.x == 0) mbar_arrive_expect_tx(&sBar, rowBytes * (uint32_t)ch);
+            __syncwarp();
+            for (int r = threadIdx.x; r < ch; r += 32) bulk_g2s(s.tile + r * s.tp, plane + (size_t)r * L.pitch, rowBytes, &sBar);
         }
+        uint4* z = reinterpret_cast<uint4*>(s.smap);
+        for (int i = threadIdx.x; i < (ch * s.tp) >> 4; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
         for (int i = threadIdx.x; i < s.kw * ch; i += FAST_THREADS) s.kbits[i] = 0;
         for (int i = threadIdx.x; i < (s.tp >> 2); i += FAST_THREADS) reinterpret_cast<uint32_t*>(sEdge)[i] = 0;
         if (threadIdx.x < 2) sCnt[threadIdx.x] = 0;
@@ -355,6 +357,7 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
             if (x1 - 1 != x0) sEdge[x1 - 1] = 2;
         }
     }
+    mbar_wait(&sBar, 0);    // the strip tile has landed
     __syncthreads();
 
     uint32_t* slotsRow = slots + ((size_t)img * g.nCells + cellRowBase) * g.slotCap;

@@ -119,3 +119,40 @@ int launch_knn2(const uint8_t* q, const int* nq, int qCap, const uint8_t* t, con
 size_t octree_smem_bytes(const Geom& g);
 
 }    // namespace orbfe
+
+#ifdef __CUDACC__
+// ---- TMA bulk copies (cp.async.bulk, SASS UBLKCP) completing on a shared-memory mbarrier ---------------------------
+// The stages that tile a level plane through shared memory (k_fast.cu, k_blur.cu, k_pyramid.cu) move whole tile rows
+// with one bulk copy each instead of per-thread 16-byte loads: no registers, no issue slots, every row of the tile in
+// flight at once.  Addresses and sizes must be multiples of 16 bytes.
+namespace orbfe {
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// one arrival that also announces `bytes` of bulk-copy traffic
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "ORBFE_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra ORBFE_DONE_%=;\n"
+        "bra ORBFE_WAIT_%=;\n"
+        "ORBFE_DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dstSmem, const void* srcGlobal, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dstSmem)),
+                 "l"(srcGlobal), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+}    // namespace orbfe
+#endif

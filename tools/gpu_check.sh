@@ -1,0 +1,20 @@
+#!/bin/bash
+# GPU-box check used during kernel work: parity tests, then the C2 bench without the slow legs.
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+B="python bench.py --no-cpu-baseline --map-rows 0 --latency-iters 0"
+$B 2>&1 | python -c "
+import sys, json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d = json.loads(l); print(d['value'], d['e2e']['value'], {k: v['ms_per_step'] for k, v in d['stages'].items()})
+"
+for so in variants/*.so; do
+  [ -f "$so" ] || continue
+  echo "== $so"
+  ORBFE_SO=$PWD/$so $B 2>&1 | python -c "
+import sys, json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d = json.loads(l); print(d['value'], d['e2e']['value'], {k: v['ms_per_step'] for k, v in d['stages'].items()})
+"
+done
