@@ -17,6 +17,7 @@
 #include <chrono>
 #include <cmath>
 #include <cfloat>
+#include <climits>
 #include <cstring>
 #include <list>
 #include <thread>
@@ -773,6 +774,140 @@ int orc_extract_batch(int nfeatures, float scale_factor, int nlevels, int ini_th
     for (int k = 0; k < threads; k++) pool.emplace_back(work);
     for (auto& th : pool) th.join();
     return 0;
+}
+
+// ---- Frame::ComputeStereoMatches (Frame.cc:827-997) --------------------------------------------------------------
+// Restated statement by statement: row table (:836-854), Hamming best-of-band with octave +-1 and the disparity
+// window (:868-910), 11x11 SAD over +-5 px on the keypoint's pyramid level (:914-949, cv::norm(IL, IR, NORM_L1) on
+// CV_8U is an exact integer sum), parabola fit (:954-962), depth (:964-979), median cut (:983-996).
+// ORBmatcher::TH_HIGH = 100, TH_LOW = 50 (ORBmatcher.cc:35-36).  Where the reference would index outside its row table
+// or take a window outside mvImagePyramid[level] (undefined behaviour / cv::Exception) the keypoint gets no match and
+// the event is counted in the return value.
+int orc_stereo_matches(const orc_extractor* eL, const orc_extractor* eR, const orc_keypoint* kl, const uint8_t* dl,
+                       int nl, const orc_keypoint* kr, const uint8_t* dr, int nr, float mb, float mbf, float* uRight,
+                       float* depth, int32_t* sad) {
+    const int TH_HIGH = 100, TH_LOW = 50;
+    int faults = 0;
+    for (int i = 0; i < nl; i++) {
+        uRight[i] = -1.0f;
+        depth[i] = -1.0f;
+        if (sad) sad[i] = -1;
+    }
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    const int nRows = eL->levels[0].h;
+    std::vector<std::vector<size_t>> vRowIndices(nRows);
+    for (int iR = 0; iR < nr; iR++) {
+        const float kpY = kr[iR].y;
+        const float r = 2.0f * eL->scale[kr[iR].octave];
+        const int maxr = (int)std::ceil(kpY + r);
+        const int minr = (int)std::floor(kpY - r);
+        for (int yi = minr; yi <= maxr; yi++) {
+            if (yi < 0 || yi >= nRows) { faults++; continue; }
+            vRowIndices[yi].push_back(iR);
+        }
+    }
+    const float minZ = mb;
+    const float minD = 0;
+    const float maxD = mbf / minZ;
+    std::vector<std::pair<int, int>> vDistIdx;
+    vDistIdx.reserve(nl);
+    for (int iL = 0; iL < nl; iL++) {
+        const orc_keypoint& kpL = kl[iL];
+        const int levelL = kpL.octave;
+        const float vL = kpL.y;
+        const float uL = kpL.x;
+        const size_t row = (size_t)vL;
+        if (row >= (size_t)nRows) { faults++; continue; }
+        const std::vector<size_t>& vCandidates = vRowIndices[row];
+        if (vCandidates.empty()) continue;
+        const float minU = uL - maxD;
+        const float maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH;
+        size_t bestIdxR = 0;
+        uint64_t a[4];
+        std::memcpy(a, dl + (size_t)iL * 32, 32);
+        for (size_t iC = 0; iC < vCandidates.size(); iC++) {
+            const size_t iR = vCandidates[iC];
+            const orc_keypoint& kpR = kr[iR];
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                uint64_t b[4];
+                std::memcpy(b, dr + iR * 32, 32);
+                const int dist = hamming256(a, b);
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestIdxR = iR;
+                }
+            }
+        }
+        if (bestDist < thOrbDist) {
+            const float uR0 = kr[bestIdxR].x;
+            const float scaleFactor = eL->invScale[kpL.octave];
+            const float scaleduL = std::round(kpL.x * scaleFactor);
+            const float scaledvL = std::round(kpL.y * scaleFactor);
+            const float scaleduR0 = std::round(uR0 * scaleFactor);
+            const int w = 5;
+            const auto& LL = eL->levels[kpL.octave];
+            const auto& LR = eR->levels[kpL.octave];
+            // IL = level.rowRange(scaledvL-w, scaledvL+w+1).colRange(scaleduL-w, scaleduL+w+1)
+            const int y0 = (int)(scaledvL - w), y1 = (int)(scaledvL + w + 1);
+            const int xl0 = (int)(scaleduL - w), xl1 = (int)(scaleduL + w + 1);
+            if (y0 < 0 || y1 > LL.h || xl0 < 0 || xl1 > LL.w) { faults++; continue; }
+            int bestSad = INT_MAX;
+            int bestincR = 0;
+            const int L = 5;
+            float vDists[2 * 5 + 1];
+            const float iniu = scaleduR0 + L - w;
+            const float endu = scaleduR0 + L + w + 1;
+            if (iniu < 0 || endu >= LR.w) continue;
+            if ((int)(scaleduR0 - L - w) < 0 || y1 > LR.h) { faults++; continue; }
+            for (int incR = -L; incR <= +L; incR++) {
+                const int xr0 = (int)(scaleduR0 + incR - w);
+                int64_t s = 0;
+                for (int y = y0; y < y1; y++) {
+                    const uint8_t* pl = LL.roi() + (size_t)y * LL.pw + xl0;
+                    const uint8_t* pr = LR.roi() + (size_t)y * LR.pw + xr0;
+                    for (int x = 0; x < 2 * w + 1; x++) s += std::abs((int)pl[x] - (int)pr[x]);
+                }
+                const float dist = (float)(double)s;
+                if (dist < bestSad) {
+                    bestSad = (int)dist;
+                    bestincR = incR;
+                }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;
+            const float dist1 = vDists[L + bestincR - 1];
+            const float dist2 = vDists[L + bestincR];
+            const float dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = eL->scale[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) {
+                    disparity = 0.01;
+                    bestuR = uL - 0.01;
+                }
+                depth[iL] = mbf / disparity;
+                uRight[iL] = bestuR;
+                if (sad) sad[iL] = bestSad;
+                vDistIdx.push_back(std::pair<int, int>(bestSad, iL));
+            }
+        }
+    }
+    if (vDistIdx.empty()) return faults;    // the reference indexes an empty vector here
+    std::sort(vDistIdx.begin(), vDistIdx.end());
+    const float median = vDistIdx[vDistIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+        if (vDistIdx[i].first < thDist) break;
+        uRight[vDistIdx[i].second] = -1;
+        depth[vDistIdx[i].second] = -1;
+    }
+    return faults;
 }
 
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }

@@ -71,6 +71,14 @@ int orc_extract_batch(int nfeatures, float scale_factor, int nlevels, int ini_th
                       const uint8_t* imgs, int n, int w, int h, int stride, int lap0, int lap1,
                       orc_keypoint* kps, uint8_t* desc, int cap, int* counts, int* monos, int threads);
 
+/* Frame::ComputeStereoMatches (Frame.cc:827-997) on the keypoints / descriptors of a rectified pair; eL / eR hold the
+ * pyramids of the LAST orc_extract of the left / right image (mvImagePyramid) and the scale tables.  uRight/depth: nl
+ * floats (-1 = no match, mvuRight / mvDepth); sad (optional): the 11x11 SAD of accepted matches before the median cut
+ * (-1 = none).  Returns the number of places where the reference would have left its arrays (0 on extractor output). */
+int orc_stereo_matches(const orc_extractor* eL, const orc_extractor* eR, const orc_keypoint* kl, const uint8_t* dl,
+                       int nl, const orc_keypoint* kr, const uint8_t* dr, int nr, float mb, float mbf, float* uRight,
+                       float* depth, int32_t* sad);
+
 int orc_hardware_threads(void);
 #ifdef __cplusplus
 }

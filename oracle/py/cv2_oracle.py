@@ -402,3 +402,101 @@ def knn2(query, train):
         for k, dm in enumerate(row):
             idx[i, k], dist[i, k] = dm.trainIdx, int(dm.distance)
     return idx, dist
+
+
+def stereo_matches_cv2(pyr_l, pyr_r, scale, inv_scale, kps_l, desc_l, kps_r, desc_r, mb, mbf):
+    """Frame::ComputeStereoMatches (Frame.cc:827-997) with the genuine cv2.norm(NORM_L1) for the window SAD and
+    numpy float32 for the reference's float arithmetic; an independent second statement that pins the C++ oracle.
+    pyr_l / pyr_r: lists of level ROIs (mvImagePyramid); kps_*: structured arrays with x, y, octave; desc_*: (n,32) u8.
+    -> (uRight f32 (n,), depth f32 (n,))"""
+    f32 = np.float32
+    th_high, th_low = 100, 50
+    n = len(kps_l)
+    u_right = np.full(n, -1.0, f32)
+    depth = np.full(n, -1.0, f32)
+    th_orb = (th_high + th_low) // 2
+    n_rows = pyr_l[0].shape[0]
+    rows = [[] for _ in range(n_rows)]
+    for ir in range(len(kps_r)):
+        y = f32(kps_r["y"][ir])
+        r = f32(2.0) * f32(scale[int(kps_r["octave"][ir])])
+        maxr = int(np.ceil(f32(y + r)))
+        minr = int(np.floor(f32(y - r)))
+        for yi in range(minr, maxr + 1):
+            rows[yi].append(ir)
+    mb, mbf = f32(mb), f32(mbf)
+    min_d = f32(0)
+    max_d = f32(mbf / mb)
+    bits_l = np.unpackbits(np.ascontiguousarray(desc_l, np.uint8).reshape(-1, 32), axis=1)
+    bits_r = np.unpackbits(np.ascontiguousarray(desc_r, np.uint8).reshape(-1, 32), axis=1)
+    dist_idx = []
+    for il in range(n):
+        level = int(kps_l["octave"][il])
+        v_l, u_l = f32(kps_l["y"][il]), f32(kps_l["x"][il])
+        cand = rows[int(v_l)]
+        if not cand:
+            continue
+        min_u, max_u = f32(u_l - max_d), f32(u_l - min_d)
+        if max_u < 0:
+            continue
+        best, best_r = th_high, 0
+        for ir in cand:
+            o = int(kps_r["octave"][ir])
+            if o < level - 1 or o > level + 1:
+                continue
+            u_r = f32(kps_r["x"][ir])
+            if min_u <= u_r <= max_u:
+                d = int(np.count_nonzero(bits_l[il] != bits_r[ir]))
+                if d < best:
+                    best, best_r = d, ir
+        if best >= th_orb:
+            continue
+        u_r0 = f32(kps_r["x"][best_r])
+        sf = f32(inv_scale[level])
+
+        def c_round(v):    # round(): half away from zero
+            v = float(v)
+            return f32(np.floor(v + 0.5) if v >= 0 else np.ceil(v - 0.5))
+        su_l, sv_l, su_r0 = c_round(f32(u_l * sf)), c_round(f32(v_l * sf)), c_round(f32(u_r0 * sf))
+        w, L = 5, 5
+        il_img = pyr_l[level][int(sv_l) - w:int(sv_l) + w + 1, int(su_l) - w:int(su_l) + w + 1]
+        assert il_img.shape == (11, 11)
+        ini_u, end_u = f32(su_r0 + L - w), f32(su_r0 + L + w + 1)
+        if ini_u < 0 or end_u >= pyr_r[level].shape[1]:
+            continue
+        best_sad, best_inc = 2 ** 31 - 1, 0
+        dists = np.zeros(2 * L + 1, f32)
+        for inc in range(-L, L + 1):
+            c0 = int(su_r0) + inc - w
+            ir_img = pyr_r[level][int(sv_l) - w:int(sv_l) + w + 1, c0:c0 + 2 * w + 1]
+            assert c0 >= 0 and ir_img.shape == (11, 11)
+            d = f32(cv2.norm(np.ascontiguousarray(il_img), np.ascontiguousarray(ir_img), cv2.NORM_L1))
+            if d < best_sad:
+                best_sad, best_inc = int(d), inc
+            dists[L + inc] = d
+        if best_inc == -L or best_inc == L:
+            continue
+        d1, d2, d3 = dists[L + best_inc - 1], dists[L + best_inc], dists[L + best_inc + 1]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            delta = f32(f32(d1 - d3) / f32(f32(2.0) * f32(f32(d1 + d3) - f32(f32(2.0) * d2))))
+        if delta < -1 or delta > 1:
+            continue
+        best_u = f32(f32(scale[level]) * f32(f32(su_r0 + f32(best_inc)) + delta))
+        disp = f32(u_l - best_u)
+        if disp >= min_d and disp < max_d:
+            if disp <= 0:
+                disp = f32(0.01)
+                best_u = f32(float(u_l) - 0.01)
+            depth[il] = f32(mbf / disp)
+            u_right[il] = best_u
+            dist_idx.append((best_sad, il))
+    if dist_idx:
+        dist_idx.sort()
+        median = f32(dist_idx[len(dist_idx) // 2][0])
+        th = f32(f32(f32(1.5) * f32(1.4)) * median)
+        for d, il in reversed(dist_idx):
+            if f32(d) < th:
+                break
+            u_right[il] = -1
+            depth[il] = -1
+    return u_right, depth

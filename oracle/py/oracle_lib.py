@@ -67,6 +67,9 @@ def lib():
                                         C.c_void_p, C.c_void_p, C.c_int]
         L.orc_extract_batch.restype = C.c_int
         L.orc_hardware_threads.restype = C.c_int
+        L.orc_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                         C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_stereo_matches.restype = C.c_int
         _lib = L
     return _lib
 
@@ -222,6 +225,22 @@ def extract_batch(imgs, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, 
                             h, w, int(lapping[0]), int(lapping[1]), _p(kps) if want_outputs else None,
                             _p(desc) if want_outputs else None, cap, _p(counts), _p(monos), int(threads))
     return counts, monos, kps, desc
+
+
+def stereo_matches(ex_left, ex_right, kps_l, desc_l, kps_r, desc_r, mb, mbf):
+    """Frame::ComputeStereoMatches (Frame.cc:827-997).  ex_left / ex_right: OracleExtractor objects whose LAST call
+    extracted the left / right image (they hold mvImagePyramid).  -> (uRight f32, depth f32, sad i32, faults)."""
+    kl = np.ascontiguousarray(kps_l, KP_DTYPE)
+    kr = np.ascontiguousarray(kps_r, KP_DTYPE)
+    dl = np.ascontiguousarray(desc_l, np.uint8).reshape(-1, 32)
+    dr = np.ascontiguousarray(desc_r, np.uint8).reshape(-1, 32)
+    n = kl.shape[0]
+    u = np.empty(n, np.float32)
+    z = np.empty(n, np.float32)
+    sad = np.empty(n, np.int32)
+    faults = lib().orc_stereo_matches(ex_left._h, ex_right._h, _p(kl), _p(dl), n, _p(kr), _p(dr), kr.shape[0], float(mb),
+                                      float(mbf), _p(u), _p(z), _p(sad))
+    return u, z, sad, int(faults)
 
 
 def hardware_threads():

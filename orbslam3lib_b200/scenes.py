@@ -80,6 +80,17 @@ def stereo_right(left, seed):
     return np.clip(out, 0, 255).astype(np.uint8)
 
 
+def stereo_right_rectified(left, seed, band=48):
+    """Right view of a rectified pair for Frame::ComputeStereoMatches (Frame.cc:827-997): the disparity is constant
+    inside horizontal bands of `band` rows, d = 4 + (7 * (y // band)) mod 37, so 11x11 windows away from the band edges
+    match exactly up to the +-2 noise; edge replicated."""
+    h, w = left.shape
+    yy, xx = np.mgrid[0:h, 0:w]
+    src = np.clip(xx + (4 + (7 * (yy // band)) % 37), 0, w - 1)
+    out = left[yy, src].astype(np.int32) + _signed_noise(w, h, seed ^ 0x5E7E0, 2)
+    return np.clip(out, 0, 255).astype(np.uint8)
+
+
 def previous_frame(cur, seed):
     """Previous frame of C1: the current frame shifted by (+3, +2) px, edge replicated, noise +-2."""
     h, w = cur.shape
