@@ -196,6 +196,68 @@ def latency_leg(args, local):
             "keypoints": [int(counts[0]), int(counts[1])]}
 
 
+def stereo_leg(args, local, dev):
+    """SURVEY.md 8(f) rank 1: the rectified-stereo front-end of Frame::Frame (two extractions) followed by
+    Frame::ComputeStereoMatches (Frame.cc:827-997) on device-resident pyramids, P pairs per step
+    (orbfe_extract_stereo_batch, images interleaved L, R).  Device time of the two stereo kernels from CUDA events
+    inside the library, whole call from torch events; the CPU oracle's orc_stereo_matches timed beside it."""
+    import torch
+    from orbslam3lib_b200 import ORBextractor, _lib, scenes
+    P = args.stereo_pairs
+    mb, mbf = 0.11, 0.11 * 435.2
+    imgs = np.empty((P, 2, H, W), np.uint8)
+    nsc = min(P, 16)
+    for k in range(nsc):
+        imgs[k, 0] = scenes.make("texture", W, H, 5000 + k)
+        imgs[k, 1] = scenes.stereo_right_rectified(imgs[k, 0], 5000 + k)
+    for k in range(nsc, P):
+        imgs[k] = imgs[k % nsc]
+    d_imgs = torch.from_numpy(imgs).to(dev)
+    ex = ORBextractor(NFEAT, 1.2, NLEVELS, 20, 7, device=local)
+    ex.set_stream(torch.cuda.current_stream().cuda_stream)
+    cap = ex.max_keypoints
+    d_kps = torch.zeros((2 * P, cap, 28), dtype=torch.uint8, device=dev)
+    d_desc = torch.zeros((2 * P, cap, 32), dtype=torch.uint8, device=dev)
+    d_counts = torch.zeros(2 * P, dtype=torch.int32, device=dev)
+    d_u = torch.zeros((P, cap), dtype=torch.float32, device=dev)
+    d_z = torch.zeros((P, cap), dtype=torch.float32, device=dev)
+    FL = _lib.IN_DEVICE | _lib.OUT_DEVICE
+    ms_st, ms_all, steps = 0.0, 0.0, 3
+    for it in range(steps + 2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        ex.extract_stereo_batch_raw(d_imgs, P, W, H, d_kps, d_desc, cap, d_counts, mb, mbf, d_u, d_z, flags=FL)
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            ms_st += ex.stereo_ms()
+            ms_all += e0.elapsed_time(e1)
+    u = d_u[:nsc].cpu().numpy()
+    counts = d_counts.cpu().numpy().reshape(P, 2)
+    out = {"workload": "Frame::ComputeStereoMatches after extraction, %d rectified 752x480 pairs per step, %d features"
+                       % (P, NFEAT), "stereo_kernels_ms_per_step": ms_st / steps, "call_ms_per_step": ms_all / steps,
+           "pairs_per_s_stereo_kernels": P / (ms_st / steps * 1e-3) if ms_st > 0 else None,
+           "pairs_per_s_call": P / (ms_all / steps * 1e-3),
+           "matches_per_pair": float((u >= 0).sum() / nsc), "keypoints_left": float(counts[:, 0].mean())}
+    # CPU oracle beside it (single thread, a few pairs), parity on those pairs
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+    import oracle_lib
+    oracle_lib.build()
+    t_cpu, ok = 0.0, True
+    for k in range(min(nsc, 4)):
+        eL, eR = (oracle_lib.OracleExtractor(NFEAT, 1.2, NLEVELS, 20, 7) for _ in range(2))
+        _, kl, dl = eL(imgs[k, 0])
+        _, kr, dr = eR(imgs[k, 1])
+        t0 = time.perf_counter()
+        ru, rz, _, _ = oracle_lib.stereo_matches(eL, eR, kl, dl, kr, dr, mb, mbf)
+        t_cpu += time.perf_counter() - t0
+        ok = ok and bool(np.array_equal(u[k, :len(kl)].view(np.uint32), ru.view(np.uint32)))
+    out["cpu_oracle_pairs_per_s_1thread"] = min(nsc, 4) / t_cpu
+    out["parity_sample"] = {"pairs": min(nsc, 4), "vs": "CPU oracle (bit-exact mvuRight)", "ok": ok}
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -247,6 +309,7 @@ def main():
     ap.add_argument("--map-rows", type=int, default=1000000, help="rows of the map-scale kNN leg (configs[4]); 0 = skip")
     ap.add_argument("--map-steps", type=int, default=2)
     ap.add_argument("--latency-iters", type=int, default=300, help="stereo pairs of the per-frame latency leg (configs[2]); 0 = skip")
+    ap.add_argument("--stereo-pairs", type=int, default=512, help="pairs per step of the ComputeStereoMatches leg; 0 = skip")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -411,6 +474,10 @@ def main():
         line["knn_map"] = knn_map
     if args.latency_iters > 0:
         line["latency"] = latency_leg(args, local)
+    if args.stereo_pairs > 0:
+        del d_kps, d_desc, d_idx, d_dist
+        torch.cuda.empty_cache()
+        line["stereo_matches"] = stereo_leg(args, local, dev)
     if not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
         import oracle_lib

@@ -95,6 +95,21 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
 int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int width, int height, int stride, int lap0, int lap1,
                   orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* count, int32_t* mono);
 
+/* Rectified stereo front-end: the two ORBextractor calls of Frame::Frame (Frame.cc:142-146, both with vLappingArea
+ * (0,0)) followed by Frame::ComputeStereoMatches (Frame.cc:827-997) for npairs pairs, with mvImagePyramid staying on
+ * the device between the two.
+ *   images        2*npairs images, interleaved: image 2p = left, 2p+1 = right of pair p (strides as orbfe_extract_batch)
+ *   kps/desc/counts   as orbfe_extract_batch, for the 2*npairs images (mvKeys / mvKeysRight, mDescriptors / ...Right)
+ *   mb, mbf       stereo baseline in metres and baseline * fx (Frame members mb, mbf): minZ = mb, maxD = mbf / mb
+ *   u_right/depth npairs x cap floats: mvuRight / mvDepth of the left keypoints of pair p at [p*cap ...), -1 = no match
+ * ORBmatcher::TH_HIGH / TH_LOW are the reference's 100 / 50 (ORBmatcher.cc:35-36). */
+int orbfe_extract_stereo_batch(orbfe_extractor* ex, const uint8_t* images, int npairs, int width, int height, int stride,
+                               size_t image_stride, orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* counts,
+                               float mb, float mbf, float* u_right, float* depth, unsigned flags);
+/* device time (ms) of the ComputeStereoMatches kernels of the last orbfe_extract_stereo_batch call (0 when the host
+ * path was pipelined over sub-chunks and the stages were not timed individually) */
+int orbfe_extractor_stereo_ms(const orbfe_extractor* ex, float* ms);
+
 /* Stage outputs of image `index` of the LAST orbfe_extract* call on this extractor (parity tests; mvImagePyramid
  * readers such as Frame.cc:834,924).  All destinations are host memory. */
 int orbfe_level_size(const orbfe_extractor* ex, int level, int* w, int* h);

@@ -123,9 +123,54 @@ def gen_primitives():
     print("primitives: ok")
 
 
+# (name, scene, w, h, seed, nfeatures, nlevels, mb, fx)
+STEREO_CASES = [
+    ("texture_376x240", "texture", 376, 240, 4101, 500, 8, 0.11, 435.2),
+    ("blobs_320x240", "flat_blobs", 320, 240, 4102, 400, 6, 0.11, 435.2),
+    ("texture_320x200_short_baseline", "texture", 320, 200, 4103, 400, 6, 0.05, 14.0),
+]
+
+
+def gen_stereo(case):
+    """Frame::ComputeStereoMatches fixture: cv2-backed extraction of both eyes + stereo_matches_cv2 (cv2.norm)."""
+    import cv2
+    import cv2_oracle
+    from orbslam3lib_b200 import scenes
+    name, kind, w, h, seed, nf, nl, mb, fx = case
+    left = scenes.make(kind, w, h, seed)
+    right = scenes.stereo_right_rectified(left, seed)
+    kp_dtype = np.dtype([("x", "<f4"), ("y", "<f4"), ("octave", "<i4")])
+    eyes = []
+    for img in (left, right):
+        ex = cv2_oracle.Cv2Extractor(nf, 1.2, nl, 20, 7)
+        ex.set_pattern(load_pattern())
+        _, kps, desc = ex(img, (0, 0))
+        ka = np.zeros(len(kps), kp_dtype)
+        ka["x"] = [k[0] for k in kps]
+        ka["y"] = [k[1] for k in kps]
+        ka["octave"] = [k[5] for k in kps]
+        eyes.append((ex, ka, desc))
+    (exl, kl, dl), (exr, kr, dr) = eyes
+    mbf = float(np.float32(mb) * np.float32(fx))
+    u, z = cv2_oracle.stereo_matches_cv2(exl.pyr, exr.pyr, exl.scale, exl.inv_scale, kl, dl, kr, dr, mb, mbf)
+    np.savez_compressed(os.path.join(GOLDEN, "stereo_%s.npz" % name),
+                        meta=np.array([w, h, seed, nf, nl], np.int64), scene=np.array(kind),
+                        mb_mbf=np.array([mb, mbf], np.float32), opencv_version=np.array(cv2.__version__),
+                        left_sha256=np.array(sha(left)), right_sha256=np.array(sha(right)),
+                        n_left=np.array(len(kl), np.int32), n_right=np.array(len(kr), np.int32),
+                        desc_left_sha256=np.array(sha(dl)), u_right=u, depth=z)
+    print("stereo_%s: %d / %d keypoints, %d matches" % (name, len(kl), len(kr), int((u >= 0).sum())))
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if "--stereo-only" in sys.argv:
+        for c in STEREO_CASES:
+            gen_stereo(c)
+        return
     gen_primitives()
+    for c in STEREO_CASES:
+        gen_stereo(c)
     for c in EXTRACT_CASES:
         gen_extract(c)
     pat = load_pattern()

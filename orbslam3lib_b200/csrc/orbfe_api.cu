@@ -25,6 +25,10 @@ struct BlurTile { short level, tx, ty, pad; };
 int blur_tile_table(const Geom& g, BlurTile* out, int cap);
 int launch_blur_tiles(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, const void* tiles, int nTiles,
                       const int* levelCount, cudaStream_t st);
+size_t stereo_smem_bytes(int cap);
+int launch_stereo(const Geom& g, const float* scale, const float* invScale, const uint8_t* pyr, const orbfe_keypoint* kps,
+                  const uint8_t* desc, const ImageResult* result, int npairs, int cap, float mb, float mbf, float* uRight,
+                  float* depth, int* sad, cudaStream_t st);
 int launch_knn2(const uint8_t* q, const int* nq, long long qCap, const uint8_t* t, const int* nt, long long tCap,
                 int npairs, long long nqSingle, long long ntSingle, long long maxNq, long long maxNt, int32_t* idx,
                 int32_t* dist, cudaStream_t st);
@@ -223,6 +227,7 @@ struct orbfe_extractor {
     DevBuf dPyr, dBlur, dSlots, dCellCount, dLevelKeys, dLevelCount, dScratch, dWork, dResult, dErr;
     DevBuf dIn, dKps, dDesc;    // staging for host inputs / outputs
     DevBuf dCounts;             // int32 keypoint counts of the last chunk (orbfe_extractor_device_outputs)
+    DevBuf dStereoU, dStereoZ, dStereoSad;    // ComputeStereoMatches outputs / SAD scratch of a chunk (pairs x cap)
     ExtractBuffers bufs{};
 
     // last call (stage outputs for the parity accessors)
@@ -233,6 +238,8 @@ struct orbfe_extractor {
     const orbfe_keypoint* lastOutKps = nullptr;
     const uint8_t* lastOutDesc = nullptr;
     float stageMs[7] = {0, 0, 0, 0, 0, 0, 0};
+    float stereoMs = 0;    // device time of the ComputeStereoMatches kernels of the last stereo call
+    cudaEvent_t evStereo[2] = {};
 };
 
 static int set_err(orbfe_extractor* ex, int code, const char* fmt, ...) {
@@ -371,9 +378,17 @@ static int reserve_workspace(orbfe_extractor* ex, int chunk) {
     return ORBFE_OK;
 }
 
+// request of orbfe_extract_stereo_batch: run Frame::ComputeStereoMatches after the extraction of every chunk
+struct StereoReq {
+    float mb, mbf;
+    float* uRight;    // npairs x cap (host, or device with ORBFE_OUT_DEVICE)
+    float* depth;
+};
+
 // run the kernels on `n` images already resident on the device; outputs go to device buffers dKps/dDesc (cap-strided)
 static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int stride, size_t imageStride, int lap0,
-                     int lap1, orbfe_keypoint* dKps, uint8_t* dDesc, int cap, ImageResult* resultDst, bool timed) {
+                     int lap1, orbfe_keypoint* dKps, uint8_t* dDesc, int cap, ImageResult* resultDst, bool timed,
+                     const StereoReq* sr = nullptr, float* dU = nullptr, float* dZ = nullptr, int* dSad = nullptr) {
     const Geom& g = ex->geom;
     cudaStream_t st = ex->stream;
     int launches = 0;
@@ -393,6 +408,12 @@ static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int str
     launches += launch_pack(g, n, bufs, lap0, lap1, st);
     launches += launch_describe(g, n, bufs, dKps, dDesc, cap, st);
     if (timed) cudaEventRecord(ex->ev[6], st);
+    if (sr) {    // Frame::ComputeStereoMatches on the pairs (2p, 2p + 1) of this chunk, pyramids still in the workspace
+        if (timed) cudaEventRecord(ex->evStereo[0], st);
+        launches += launch_stereo(g, ex->tables.scale.data(), ex->tables.invScale.data(), ex->bufs.pyr, dKps, dDesc,
+                                  resultDst, n / 2, cap, sr->mb, sr->mbf, dU, dZ, dSad, st);
+        if (timed) cudaEventRecord(ex->evStereo[1], st);
+    }
     ORBFE_CUDA(ex, cudaGetLastError());
     g_launches += launches;
     ex->lastLaunches += launches;
@@ -433,6 +454,7 @@ int orbfe_extractor_create(int device, const orbfe_params* params, orbfe_extract
     cudaStreamCreateWithFlags(&ex->inStream, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&ex->outStream, cudaStreamNonBlocking);
     for (auto& e : ex->ev) cudaEventCreate(&e);
+    for (auto& e : ex->evStereo) cudaEventCreate(&e);
     *out = ex;
     return ORBFE_OK;
 }
@@ -446,6 +468,7 @@ int orbfe_extractor_destroy(orbfe_extractor* ex) {
                       &ex->dKps, &ex->dDesc, &ex->dCounts};
     for (DevBuf* b : bufs) b->release();
     for (auto& e : ex->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : ex->evStereo) if (e) cudaEventDestroy(e);
     for (auto& e : ex->pipeEv) cudaEventDestroy(e);
     if (ex->inStream) cudaStreamDestroy(ex->inStream);
     if (ex->outStream) cudaStreamDestroy(ex->outStream);
@@ -495,11 +518,21 @@ int orbfe_extractor_max_keypoints(const orbfe_extractor* ex) {
     return total;
 }
 
-int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int width, int height, int stride,
-                        size_t image_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
-                        int32_t* counts, int32_t* monos, unsigned flags) {
+}    // extern "C"
+
+// orbfe_extract_batch, and with `sr` orbfe_extract_stereo_batch (images interleaved left, right, left, right ...)
+static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n, int width, int height, int stride,
+                              size_t image_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                              int32_t* counts, int32_t* monos, unsigned flags, const StereoReq* sr) {
     if (!ex) return ORBFE_ERR_ARG;
     std::lock_guard<std::mutex> lk(ex->mu);
+    if (sr) {
+        if (n % 2 != 0 || !sr->uRight || !sr->depth || cap <= 0 || !(sr->mb > 0))
+            return set_err(ex, ORBFE_ERR_ARG, "stereo: need an even image count, output arrays, cap > 0 and mb > 0");
+        if (cap > 65535 || stereo_smem_bytes(cap) > 200 * 1024)
+            return set_err(ex, ORBFE_ERR_ARG, "stereo: keypoint capacity %d too large for the right-keypoint table", cap);
+        ex->stereoMs = 0;
+    }
     if (n < 0 || cap < 0 || (n > 0 && (!kps || !desc) && cap > 0)) return set_err(ex, ORBFE_ERR_ARG, "bad arguments");
     if (n == 0) return ORBFE_OK;
     if (!images || width <= 0 || height <= 0) {    // ORBextractor_old.cc:1091-1092: empty image -> -1
@@ -519,6 +552,7 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
     const size_t ioPer = (inDev ? 0 : (size_t)width * height) + (outDev ? 0 : (size_t)cap * 60);
     int chunk = (int)std::min<size_t>((size_t)n, std::max<size_t>(1, ex->wsLimit / (ex->perImageBytes + ioPer)));
     chunk = std::min(chunk, 32768);
+    if (sr) chunk = std::max(2, chunk & ~1);    // pairs stay inside one chunk
     rc = reserve_workspace(ex, chunk);
     if (rc != ORBFE_OK) return rc;
     if (!inDev) ORBFE_CUDA(ex, ex->dIn.reserve((size_t)chunk * width * height));
@@ -526,6 +560,13 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
     if (!outDev) {
         ORBFE_CUDA(ex, ex->dKps.reserve(std::max<size_t>(16, (size_t)chunk * cap * sizeof(orbfe_keypoint))));
         ORBFE_CUDA(ex, ex->dDesc.reserve(std::max<size_t>(16, (size_t)chunk * cap * 32)));
+    }
+    if (sr) {
+        ORBFE_CUDA(ex, ex->dStereoSad.reserve((size_t)(chunk / 2) * cap * 4));
+        if (!outDev) {
+            ORBFE_CUDA(ex, ex->dStereoU.reserve((size_t)(chunk / 2) * cap * 4));
+            ORBFE_CUDA(ex, ex->dStereoZ.reserve((size_t)(chunk / 2) * cap * 4));
+        }
     }
     cudaStream_t st = ex->stream;
     ex->lastLaunches = 0;
@@ -540,6 +581,10 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
         size_t dImageStride = image_stride;
         orbfe_keypoint* dK = outDev ? kps + (size_t)base * cap : (orbfe_keypoint*)ex->dKps.p;
         uint8_t* dD = outDev ? desc + (size_t)base * cap * 32 : (uint8_t*)ex->dDesc.p;
+        // stereo outputs of this chunk (pair index = image index / 2)
+        float* dU = !sr ? nullptr : outDev ? sr->uRight + (size_t)(base / 2) * cap : (float*)ex->dStereoU.p;
+        float* dZ = !sr ? nullptr : outDev ? sr->depth + (size_t)(base / 2) * cap : (float*)ex->dStereoZ.p;
+        int* dSad = (int*)ex->dStereoSad.p;
         int errFlag = 0;
         const bool contiguous = stride == width && (m == 1 || image_stride == (size_t)width * height);
         const int kSub = 128;    // images per pipeline stage
@@ -566,11 +611,18 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
                 const int b0 = k * kSub, mk = std::min(kSub, m - b0);
                 ORBFE_CUDA(ex, cudaStreamWaitEvent(st, ex->pipeEv[2 * k], 0));
                 rc = run_chunk(ex, (const uint8_t*)ex->dIn.p + (size_t)b0 * imgBytes, mk, width, imgBytes, lap0, lap1,
-                               dK + (size_t)b0 * cap, dD + (size_t)b0 * cap * 32, cap, ex->bufs.result + b0, false);
+                               dK + (size_t)b0 * cap, dD + (size_t)b0 * cap * 32, cap, ex->bufs.result + b0, false, sr,
+                               sr ? dU + (size_t)(b0 / 2) * cap : nullptr, sr ? dZ + (size_t)(b0 / 2) * cap : nullptr,
+                               sr ? dSad + (size_t)(b0 / 2) * cap : nullptr);
                 if (rc != ORBFE_OK) return rc;
                 ORBFE_CUDA(ex, cudaEventRecord(ex->pipeEv[2 * k + 1], st));
                 if (cap > 0) {
                     ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->outStream, ex->pipeEv[2 * k + 1], 0));
+                    if (sr) {
+                        const size_t po = (size_t)(b0 / 2) * cap, pb = (size_t)(mk / 2) * cap * 4;
+                        ORBFE_CUDA(ex, cudaMemcpyAsync(sr->uRight + (size_t)(base / 2) * cap + po, dU + po, pb, cudaMemcpyDeviceToHost, ex->outStream));
+                        ORBFE_CUDA(ex, cudaMemcpyAsync(sr->depth + (size_t)(base / 2) * cap + po, dZ + po, pb, cudaMemcpyDeviceToHost, ex->outStream));
+                    }
                     ORBFE_CUDA(ex, cudaMemcpyAsync(kps + (size_t)(base + b0) * cap, dK + (size_t)b0 * cap,
                                                    (size_t)mk * cap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, ex->outStream));
                     ORBFE_CUDA(ex, cudaMemcpyAsync(desc + (size_t)(base + b0) * cap * 32, dD + (size_t)b0 * cap * 32,
@@ -605,8 +657,12 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
                 dStride = width;
                 dImageStride = (size_t)width * height;
             }
-            rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap, ex->bufs.result, true);
+            rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap, ex->bufs.result, true, sr, dU, dZ, dSad);
             if (rc != ORBFE_OK) return rc;
+            if (sr && !outDev) {
+                ORBFE_CUDA(ex, cudaMemcpyAsync(sr->uRight + (size_t)(base / 2) * cap, dU, (size_t)(m / 2) * cap * 4, cudaMemcpyDeviceToHost, st));
+                ORBFE_CUDA(ex, cudaMemcpyAsync(sr->depth + (size_t)(base / 2) * cap, dZ, (size_t)(m / 2) * cap * 4, cudaMemcpyDeviceToHost, st));
+            }
             ORBFE_CUDA(ex, cudaMemcpyAsync(res.data(), ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
             ORBFE_CUDA(ex, cudaMemcpyAsync(&errFlag, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
             ORBFE_CUDA(ex, cudaMemcpy2DAsync(ex->dCounts.p, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
@@ -619,6 +675,10 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
             for (int i = 0; i < 7; i++) {
                 float ms = 0;
                 if (cudaEventElapsedTime(&ms, ex->ev[i], ex->ev[i + 1]) == cudaSuccess) ex->stageMs[i] += ms;
+            }
+            if (sr) {
+                float ms = 0;
+                if (cudaEventElapsedTime(&ms, ex->evStereo[0], ex->evStereo[1]) == cudaSuccess) ex->stereoMs += ms;
             }
             ex->lastChunkBase = base;
             ex->lastChunkN = m;
@@ -645,6 +705,31 @@ int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int w
     }
     if (status == ORBFE_ERR_CAPACITY) return set_err(ex, status, "keypoint capacity %d too small (need <= %d)", cap, g.outCap);
     return status;
+}
+
+extern "C" {
+
+int orbfe_extract_batch(orbfe_extractor* ex, const uint8_t* images, int n, int width, int height, int stride,
+                        size_t image_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                        int32_t* counts, int32_t* monos, unsigned flags) {
+    return extract_batch_impl(ex, images, n, width, height, stride, image_stride, lap0, lap1, kps, desc, cap, counts, monos,
+                              flags, nullptr);
+}
+
+int orbfe_extract_stereo_batch(orbfe_extractor* ex, const uint8_t* images, int npairs, int width, int height, int stride,
+                               size_t image_stride, orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* counts,
+                               float mb, float mbf, float* u_right, float* depth, unsigned flags) {
+    if (npairs < 0 || npairs > (1 << 29)) return ex ? set_err(ex, ORBFE_ERR_ARG, "bad pair count") : ORBFE_ERR_ARG;
+    const StereoReq sr{mb, mbf, u_right, depth};
+    // Frame.cc:142-143: both extractors run with vLappingArea (0, 0)
+    return extract_batch_impl(ex, images, 2 * npairs, width, height, stride, image_stride, 0, 0, kps, desc, cap, counts,
+                              nullptr, flags, &sr);
+}
+
+int orbfe_extractor_stereo_ms(const orbfe_extractor* ex, float* ms) {
+    if (!ex || !ms) return ORBFE_ERR_ARG;
+    *ms = ex->stereoMs;
+    return ORBFE_OK;
 }
 
 int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int width, int height, int stride, int lap0, int lap1,

@@ -105,6 +105,37 @@ class ORBextractor:
                                                    int(vLappingArea[0]), int(vLappingArea[1]), ptr(kps), ptr(desc),
                                                    int(cap), ptr(counts), ptr(monos), int(flags)))
 
+    def extract_stereo_batch(self, images, mb, mbf, cap=None):
+        """Frame::Frame stereo ctor path (Frame.cc:142-146) + Frame::ComputeStereoMatches (Frame.cc:827-997).
+        images uint8 (npairs, 2, h, w): [p, 0] = left, [p, 1] = right ->
+        (counts (npairs, 2), kps (npairs, 2, cap), desc (npairs, 2, cap, 32), uRight (npairs, cap), depth (npairs, cap));
+        uRight / depth are mvuRight / mvDepth of the left keypoints (-1 = no match)."""
+        images = np.ascontiguousarray(images, np.uint8)
+        npairs, two, h, w = images.shape
+        if two != 2:
+            raise ValueError("images must be (npairs, 2, h, w)")
+        cap = self.max_keypoints if cap is None else int(cap)
+        kps = np.zeros((npairs, 2, cap), KP_DTYPE)
+        desc = np.zeros((npairs, 2, cap, 32), np.uint8)
+        counts = np.zeros((npairs, 2), np.int32)
+        u_right = np.full((npairs, cap), -1, np.float32)
+        depth = np.full((npairs, cap), -1, np.float32)
+        self._check(_lib.lib().orbfe_extract_stereo_batch(self._h, ptr(images), npairs, w, h, w, w * h, ptr(kps), ptr(desc),
+                                                          cap, ptr(counts), float(mb), float(mbf), ptr(u_right),
+                                                          ptr(depth), 0))
+        return counts, kps, desc, u_right, depth
+
+    def extract_stereo_batch_raw(self, images, npairs, w, h, kps, desc, cap, counts, mb, mbf, u_right, depth, flags=0):
+        """Thin call with caller-owned buffers (numpy arrays, torch tensors — pinned host or device — or addresses)."""
+        self._check(_lib.lib().orbfe_extract_stereo_batch(self._h, ptr(images), int(npairs), int(w), int(h), int(w),
+                                                          int(w) * int(h), ptr(kps), ptr(desc), int(cap), ptr(counts),
+                                                          float(mb), float(mbf), ptr(u_right), ptr(depth), int(flags)))
+
+    def stereo_ms(self):
+        ms = C.c_float(0)
+        _lib.lib().orbfe_extractor_stereo_ms(self._h, C.byref(ms))
+        return float(ms.value)
+
     # ---- stage outputs of the last call (parity tests; mvImagePyramid) ----
     def level_size(self, level):
         w, h = C.c_int(), C.c_int()

@@ -57,3 +57,25 @@ def check_outputs_against_fixture(mono, kps, desc, g):
     np.testing.assert_array_equal(kps["octave"], g["octave"])
     assert len(gk) == 0 or angle_diff(kps["angle"], gk[:, 3]).max() <= ANGLE_TOL_DEG
     np.testing.assert_array_equal(desc, g["desc"])
+
+
+def stereo_fixtures():
+    return sorted(glob.glob(os.path.join(GOLDEN, "stereo_*.npz")))
+
+
+def stereo_images(g):
+    """the rectified pair of a stereo_*.npz fixture, checked against the stored hashes."""
+    from orbslam3lib_b200 import scenes
+    w, h, seed, nf, nl = [int(v) for v in g["meta"]]
+    left = scenes.make(str(g["scene"]), w, h, seed)
+    right = scenes.stereo_right_rectified(left, seed)
+    assert sha(left) == str(g["left_sha256"]) and sha(right) == str(g["right_sha256"]), "scene generator drifted"
+    return left, right
+
+
+def check_stereo_against_fixture(n_left, n_right, desc_left, u_right, depth, g):
+    """mvuRight / mvDepth must equal the cv2-generated fixture bit for bit."""
+    assert (n_left, n_right) == (int(g["n_left"]), int(g["n_right"]))
+    assert sha(desc_left) == str(g["desc_left_sha256"])
+    np.testing.assert_array_equal(np.asarray(u_right, np.float32).view(np.uint32), g["u_right"].view(np.uint32))
+    np.testing.assert_array_equal(np.asarray(depth, np.float32).view(np.uint32), g["depth"].view(np.uint32))

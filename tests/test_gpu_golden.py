@@ -32,3 +32,16 @@ def test_knn_fixture():
     idx, dist = BFMatcher().knnMatch(q, t)
     np.testing.assert_array_equal(idx, g["knn_idx"])
     np.testing.assert_array_equal(dist, g["knn_dist"])
+
+
+@pytest.mark.parametrize("path", gu.stereo_fixtures(), ids=lambda p: os.path.basename(p)[7:-4])
+def test_stereo_fixture(path):
+    """Frame::ComputeStereoMatches on the GPU against the fixture made with cv2.norm + numpy float32."""
+    g = gu.load(path)
+    w, h, seed, nf, nl = [int(v) for v in g["meta"]]
+    left, right = gu.stereo_images(g)
+    mb, mbf = [float(v) for v in g["mb_mbf"]]
+    ex = ORBextractor(nf, 1.2, nl, 20, 7)
+    counts, kps, desc, u, z = ex.extract_stereo_batch(np.stack([left, right])[None], mb, mbf)
+    nL, nR = int(counts[0, 0]), int(counts[0, 1])
+    gu.check_stereo_against_fixture(nL, nR, desc[0, 0, :nL], u[0, :nL], z[0, :nL], g)

@@ -89,3 +89,20 @@ def test_pattern_table():
         body = re.sub(r"/\*.*?\*/", "", m.group(1), flags=re.S)
         body = re.sub(r"//.*", "", body)
         assert [int(v) for v in re.findall(r"-?\d+", body)] == vals
+
+
+@pytest.mark.parametrize("path", gu.stereo_fixtures(), ids=lambda p: os.path.basename(p)[7:-4])
+def test_stereo_matches_fixture(oracle, path):
+    """orc_stereo_matches (Frame::ComputeStereoMatches restated in C++) against the cv2.norm / numpy-float32 fixture."""
+    g = gu.load(path)
+    w, h, seed, nf, nl = [int(v) for v in g["meta"]]
+    left, right = gu.stereo_images(g)
+    mb, mbf = [float(v) for v in g["mb_mbf"]]
+    eL, eR = oracle.OracleExtractor(nf, 1.2, nl, 20, 7), oracle.OracleExtractor(nf, 1.2, nl, 20, 7)
+    _, kl, dl = eL(left)
+    _, kr, dr = eR(right)
+    u, z, sad, faults = oracle.stereo_matches(eL, eR, kl, dl, kr, dr, mb, mbf)
+    assert faults == 0
+    gu.check_stereo_against_fixture(len(kl), len(kr), dl, u, z, g)
+    assert int((u >= 0).sum()) > 50
+    assert ((sad >= 0) >= (u >= 0)).all()    # the median cut only removes accepted matches

@@ -113,3 +113,29 @@ def test_extractor_vs_cv2_glue(oracle, kind, w, h, seed, nf, nl, lap):
         np.testing.assert_array_equal(kps[f], rk[:, i], f)
     np.testing.assert_array_equal(kps["octave"], rk[:, 5].astype(np.int32))
     np.testing.assert_array_equal(desc, rd)
+
+
+@pytest.mark.parametrize("kind,w,h,seed,nf,rectified", [
+    ("texture", 752, 480, 7301, 1200, True),
+    ("texture", 640, 480, 7302, 1000, False),
+    ("checker", 376, 240, 7303, 500, True),
+    ("noise", 320, 240, 7304, 500, True),
+    ("flat_blobs", 752, 480, 7305, 1000, True),
+])
+def test_stereo_matches_vs_cv2(oracle, kind, w, h, seed, nf, rectified):
+    """Frame::ComputeStereoMatches: the C++ restatement against the cv2.norm(NORM_L1) + numpy-float32 restatement on
+    the oracle's own keypoints and pyramids (both eyes), bit for bit."""
+    import cv2_oracle
+    left = scenes.make(kind, w, h, seed)
+    right = scenes.stereo_right_rectified(left, seed) if rectified else scenes.stereo_right(left, seed)
+    eL, eR = oracle.OracleExtractor(nf, 1.2, 8, 20, 7), oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _, kl, dl = eL(left)
+    _, kr, dr = eR(right)
+    for mb, mbf in ((0.11, 0.11 * 435.2), (0.05, 0.05 * 20.0)):
+        u, z, sad, faults = oracle.stereo_matches(eL, eR, kl, dl, kr, dr, mb, mbf)
+        assert faults == 0
+        pl = [eL.level_pixels(l) for l in range(8)]
+        pr = [eR.level_pixels(l) for l in range(8)]
+        u2, z2 = cv2_oracle.stereo_matches_cv2(pl, pr, eL.scale, eL.inv_scale, kl, dl, kr, dr, mb, mbf)
+        np.testing.assert_array_equal(u.view(np.uint32), u2.view(np.uint32))
+        np.testing.assert_array_equal(z.view(np.uint32), z2.view(np.uint32))
