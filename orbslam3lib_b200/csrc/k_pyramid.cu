@@ -12,9 +12,8 @@
 //   * resize_tile_kernel: one CTA = a 256 x (4*RPT) tile of the padded destination plane.  The source window is staged
 //     in shared memory with 128-bit loads, twice: as is and shifted by one byte, so that the horizontal pair
 //     (S[s], S[s+1]) of any tap is ONE aligned 16-bit shared load.  A thread owns 4 adjacent destination columns
-//     (taps in registers) and walks down its rows: horizontal pass = one IDP.2A per pixel (a0*S[s] + a1*S[s+1]),
-//     kept in registers and re-used by the next destination row when it shares the source row (ratio 1.2: 1.2
-//     horizontal passes per output row instead of 2); vertical pass in registers; one 32-bit store per 4 pixels.
+//     (taps in registers) and walks down its rows: horizontal pass = one IDP.2A per pixel and source row
+//     (a0*S[s] + a1*S[s+1]); vertical pass in registers; one 32-bit store per 4 pixels.
 #include <algorithm>
 
 #include "orbfe_internal.h"
@@ -146,43 +145,28 @@ __global__ void __launch_bounds__(256) resize_tile_kernel(const uint8_t* __restr
         ad[k] = !valid ? 0 : ((off & 1) ? (SP * SH + off - 1) : off);
         wt[k] = valid ? (uint32_t)raw.y : 0u;    // a0 | a1 << 16
     }
-    int idxA = -1, idxB = -1;
-    uint32_t A[4] = {0, 0, 0, 0}, B[4] = {0, 0, 0, 0};
     const int py0 = rb + ty * rpt;
     uint8_t* dp = dstPlane + (size_t)blockIdx.z * slabBytes + c;
-    for (int i = 0; i < rpt; i++) {
-        const int py = py0 + i;
-        if (py >= dh + 2 * kEdge) break;
+    const int pyEnd = min(py0 + rpt, dh + 2 * kEdge);
+    for (int py = py0; py < pyEnd; py++) {
         const int2 yraw = __ldg(reinterpret_cast<const int2*>(ytab + reflect101(py - kEdge, dh)));
         const int s0 = (short)(yraw.x & 0xffff) - rlo, s1 = (short)(yraw.x >> 16) - rlo;
         const uint32_t b0 = (uint32_t)yraw.y & 0xffffu, b1 = (uint32_t)yraw.y >> 16;
-        if (s0 == idxB) {
+        // both horizontal passes every row: re-using the previous row's pass (1.2 instead of 2 per output row) costs
+        // more register moves and branches than the 3 instructions per pixel it saves
+        const uint8_t* row0 = sm + s0 * SP;
+        const uint8_t* row1 = sm + s1 * SP;
+        uint32_t A[4], B[4];
 #pragma unroll
-            for (int k = 0; k < 4; k++) A[k] = B[k];
-            idxA = idxB;
-        } else if (s0 != idxA) {
-            const uint8_t* row = sm + s0 * SP;
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-                A[k] = __dp2a_lo(wt[k], (uint32_t)*reinterpret_cast<const uint16_t*>(row + ad[k]), 0u) >> 4;
-            idxA = s0;
-        }
-        if (s1 == idxA) {
-#pragma unroll
-            for (int k = 0; k < 4; k++) B[k] = A[k];
-            idxB = idxA;
-        } else if (s1 != idxB) {
-            const uint8_t* row = sm + s1 * SP;
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-                B[k] = __dp2a_lo(wt[k], (uint32_t)*reinterpret_cast<const uint16_t*>(row + ad[k]), 0u) >> 4;
-            idxB = s1;
+        for (int k = 0; k < 4; k++) {
+            A[k] = __dp2a_lo(wt[k], (uint32_t)*reinterpret_cast<const uint16_t*>(row0 + ad[k]), 0u) >> 4;
+            B[k] = __dp2a_lo(wt[k], (uint32_t)*reinterpret_cast<const uint16_t*>(row1 + ad[k]), 0u) >> 4;
         }
         uint32_t out = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const uint32_t v = (((b0 * A[k]) >> 16) + ((b1 * B[k]) >> 16) + 2u) >> 2;
-            out |= (v & 0xffu) << (8 * k);
+            out |= v << (8 * k);    // v <= 255: the weights of each pass sum to 2048
         }
         *reinterpret_cast<uint32_t*>(dp + (size_t)py * dpitch) = out;
     }
