@@ -11,6 +11,8 @@
 #include <string>
 #include <vector>
 
+#include <cstdlib>
+
 #include "orbfe_internal.h"
 
 namespace orbfe {
@@ -587,7 +589,8 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
         int* dSad = (int*)ex->dStereoSad.p;
         int errFlag = 0;
         const bool contiguous = stride == width && (m == 1 || image_stride == (size_t)width * height);
-        const int kSub = 128;    // images per pipeline stage
+        static const int kSubEnv = getenv("ORBFE_PIPE_SUB") ? atoi(getenv("ORBFE_PIPE_SUB")) : 0;
+        const int kSub = kSubEnv >= 2 ? (kSubEnv & ~1) : 128;    // images per pipeline stage (even: stereo pairs stay together)
         if (!inDev && !outDev && contiguous && m >= 2 * kSub && ex->inStream && ex->outStream) {
             // host -> host: software pipeline over sub-chunks.  The copy-in of stage k+1 and the copy-out of stage k-1
             // overlap the kernels of stage k (three streams, two events per stage); the workspace is re-used by
