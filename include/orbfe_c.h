@@ -149,6 +149,37 @@ int orbfe_knn2_batch(orbfe_matcher* m, const uint8_t* q, const int32_t* nq, int 
  * and (float)dist[2i] < (float)dist[2i+1] * ratio (evaluated in double, like the reference's `distance * 0.7`),
  * else -1.  Pure host code, no arithmetic of the hot path. */
 int orbfe_ratio_test(const int32_t* idx, const int32_t* dist, int64_t nq, double ratio, int32_t* out);
+/* ---- guided matcher: the frame grid + ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints)
+ * (ORBmatcher.cc:44-143; Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea, Frame.cc:405-436, 672-751;
+ * ORBmatcher::DescriptorDistance, ORBmatcher.cc:2107-2123) for frames with Nleft == -1 (monocular, rectified stereo).
+ * A map point as that loop reads it: mTrackProjX/Y, mTrackProjXR, mTrackViewCos, mTrackDepth, mnTrackScaleLevel,
+ * GetDescriptor(); flags bit 0 = mbTrackInView, bit 1 = isBad(), bit 2 = Observations() > 0 (an assigned point then
+ * blocks its feature for the later points of the call, ORBmatcher.cc:84-86 — the order dependence is reproduced). */
+typedef struct orbfe_track_point {
+    float proj_x, proj_y, proj_xr, view_cos, track_depth;
+    int32_t level, flags;
+    uint8_t desc[32];
+} orbfe_track_point;
+/*   keys_un/desc   mvKeysUn / mDescriptors of the frame (n features)
+ *   u_right        mvuRight (n floats) or NULL for a monocular frame (no mTrackProjXR gate)
+ *   occupied       n bytes, non-zero = F.mvpMapPoints[i] is set and has Observations() > 0 before the call; or NULL
+ *   bounds         mnMinX, mnMinY, mnMaxX, mnMaxY;  scale_factors: mvScaleFactors (nlevels)
+ *   nn_ratio       ORBmatcher::mfNNratio;  th / far_points / th_far: the call's arguments
+ *   match[npts]    feature index assigned to each point (F.mvpMapPoints[match[i]] = point i) or -1
+ *   owner[n]       (optional) index of the LAST point assigned to each feature or -1;  *nmatches: the return value */
+int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc, const float* u_right,
+                               const uint8_t* occupied, int n, const float bounds[4], const float* scale_factors,
+                               int nlevels, const orbfe_track_point* pts, int npts, float th, int far_points, float th_far,
+                               float nn_ratio, int32_t* match, int32_t* owner, int32_t* nmatches);
+/* nframes independent frames, one CTA each: frame f uses features [f*cap, f*cap + n[f]) and points
+ * [f*pts_cap, f*pts_cap + npts[f]); bounds / scale_factors / thresholds are shared (host memory always).  The other
+ * arrays are host memory unless ORBFE_IN_DEVICE / ORBFE_OUT_DEVICE. */
+int orbfe_search_by_projection_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc,
+                                     const float* u_right, const uint8_t* occupied, const int32_t* n, int cap,
+                                     const float bounds[4], const float* scale_factors, int nlevels,
+                                     const orbfe_track_point* pts, const int32_t* npts, int pts_cap, int nframes, float th,
+                                     int far_points, float th_far, float nn_ratio, int32_t* match, int32_t* owner,
+                                     int32_t* nmatches, unsigned flags);
 /* device time (ms) of the kernel(s) of the last call and their launch count */
 int orbfe_matcher_last_ms(const orbfe_matcher* m, float* kernel_ms, int* launches);
 

@@ -910,6 +910,120 @@ int orc_stereo_matches(const orc_extractor* eL, const orc_extractor* eR, const o
     return faults;
 }
 
+// ---- Frame grid + ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th, bFarPoints, thFarPoints) ------------
+// Frame::AssignFeaturesToGrid (Frame.cc:405-436) with Frame::PosInGrid (:741-751), Frame::GetFeaturesInArea
+// (:672-736), ORBmatcher::RadiusByViewingCos (ORBmatcher.cc:216-222), ORBmatcher::DescriptorDistance (:2107-2123) and
+// the map-point loop of ORBmatcher.cc:44-143 for frames with Nleft == -1 (monocular / rectified stereo: the keypoints
+// are mvKeysUn and the right-image branch :145-211 is not taken).  MapPoint state enters through orc_track_point:
+// flags bit 0 = mbTrackInView, bit 1 = isBad(), bit 2 = Observations() > 0 (an assigned point then blocks its feature
+// for the later points of the same call, :84-86).
+namespace {
+const int GRID_ROWS = 48, GRID_COLS = 64;    // FRAME_GRID_ROWS / FRAME_GRID_COLS, Frame.h:46-47
+}
+
+int orc_search_by_projection(const orc_keypoint* keysUn, const uint8_t* desc, const float* uRight,
+                             const uint8_t* occupied, int n, float mnMinX, float mnMinY, float mnMaxX, float mnMaxY,
+                             const float* mvScaleFactors, const orc_track_point* pts, int npts, float th, int bFarPoints,
+                             float thFarPoints, float mfNNratio, int32_t* match, int32_t* owner) {
+    const int TH_HIGH = 100;
+    const float mfGridElementWidthInv = static_cast<float>(GRID_COLS) / (mnMaxX - mnMinX);      // Frame.cc:179-180
+    const float mfGridElementHeightInv = static_cast<float>(GRID_ROWS) / (mnMaxY - mnMinY);
+    static thread_local std::vector<size_t> mGrid[GRID_COLS][GRID_ROWS];
+    for (int i = 0; i < GRID_COLS; i++)
+        for (int j = 0; j < GRID_ROWS; j++) mGrid[i][j].clear();
+    for (int i = 0; i < n; i++) {    // AssignFeaturesToGrid
+        const orc_keypoint& kp = keysUn[i];
+        const int posX = (int)std::round((kp.x - mnMinX) * mfGridElementWidthInv);
+        const int posY = (int)std::round((kp.y - mnMinY) * mfGridElementHeightInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        mGrid[posX][posY].push_back(i);
+    }
+    // F.mvpMapPoints[idx] != NULL && Observations() > 0, and which point of this call owns the feature
+    std::vector<uint8_t> blocked(n, 0);
+    for (int i = 0; i < n; i++) {
+        blocked[i] = occupied ? occupied[i] : 0;
+        if (owner) owner[i] = -1;
+    }
+    int nmatches = 0;
+    const bool bFactor = th != 1.0;
+    std::vector<size_t> vIndices;
+    for (int iMP = 0; iMP < npts; iMP++) {
+        const orc_track_point& mp = pts[iMP];
+        match[iMP] = -1;
+        if (!(mp.flags & 1)) continue;                                  // !mbTrackInView (&& !mbTrackInViewR)
+        if (bFarPoints && mp.track_depth > thFarPoints) continue;
+        if (mp.flags & 2) continue;                                     // isBad()
+        const int nPredictedLevel = mp.level;
+        float r = mp.view_cos > 0.998 ? 2.5 : 4.0;                      // RadiusByViewingCos
+        if (bFactor) r *= th;
+        // GetFeaturesInArea(x, y, r * scale, level - 1, level)
+        const float x = mp.proj_x, y = mp.proj_y;
+        const float rr = r * mvScaleFactors[nPredictedLevel];
+        const int minLevel = nPredictedLevel - 1, maxLevel = nPredictedLevel;
+        vIndices.clear();
+        {
+            const float factorX = rr, factorY = rr;
+            const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * mfGridElementWidthInv));
+            const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * mfGridElementWidthInv));
+            const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * mfGridElementHeightInv));
+            const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * mfGridElementHeightInv));
+            if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0)) {
+                const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+                for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                    for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                        const std::vector<size_t>& vCell = mGrid[ix][iy];
+                        for (size_t j = 0; j < vCell.size(); j++) {
+                            const orc_keypoint& kpUn = keysUn[vCell[j]];
+                            if (bCheckLevels) {
+                                if (kpUn.octave < minLevel) continue;
+                                if (maxLevel >= 0)
+                                    if (kpUn.octave > maxLevel) continue;
+                            }
+                            const float distx = kpUn.x - x;
+                            const float disty = kpUn.y - y;
+                            if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) vIndices.push_back(vCell[j]);
+                        }
+                    }
+            }
+        }
+        if (vIndices.empty()) continue;
+        uint64_t a[4];
+        std::memcpy(a, mp.desc, 32);
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (size_t k = 0; k < vIndices.size(); k++) {
+            const size_t idx = vIndices[k];
+            if (blocked[idx]) continue;
+            if (uRight && uRight[idx] > 0) {
+                const float er = std::fabs(mp.proj_xr - uRight[idx]);
+                if (er > r * mvScaleFactors[nPredictedLevel]) continue;
+            }
+            uint64_t b[4];
+            std::memcpy(b, desc + idx * 32, 32);
+            const int dist = hamming256(a, b);
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestLevel2 = bestLevel;
+                bestLevel = keysUn[idx].octave;
+                bestIdx = (int)idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = keysUn[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+            if (bestLevel != bestLevel2 || bestDist <= mfNNratio * bestDist2) {
+                match[iMP] = bestIdx;                       // F.mvpMapPoints[bestIdx] = pMP
+                if (owner) owner[bestIdx] = iMP;
+                blocked[bestIdx] = (mp.flags & 4) ? 1 : 0;    // later points skip it iff pMP->Observations() > 0
+                nmatches++;
+            }
+        }
+    }
+    return nmatches;
+}
+
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

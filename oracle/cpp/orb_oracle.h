@@ -79,6 +79,22 @@ int orc_stereo_matches(const orc_extractor* eL, const orc_extractor* eR, const o
                        int nl, const orc_keypoint* kr, const uint8_t* dr, int nr, float mb, float mbf, float* uRight,
                        float* depth, int32_t* sad);
 
+/* A map point as ORBmatcher::SearchByProjection sees it (MapPoint members mTrackProjX/Y, mTrackProjXR, mTrackViewCos,
+ * mTrackDepth, mnTrackScaleLevel, GetDescriptor()); flags: 1 = mbTrackInView, 2 = isBad(), 4 = Observations() > 0. */
+typedef struct {
+    float proj_x, proj_y, proj_xr, view_cos, track_depth;
+    int32_t level, flags;
+    uint8_t desc[32];
+} orc_track_point;
+/* Frame::AssignFeaturesToGrid + GetFeaturesInArea (Frame.cc:405-436, 672-751) and ORBmatcher::SearchByProjection(F,
+ * vpMapPoints, th, bFarPoints, thFarPoints) (ORBmatcher.cc:44-143) for Nleft == -1.  keysUn/desc/uRight/occupied: the
+ * frame (uRight, occupied nullable); match[npts]: feature assigned to each point or -1; owner[n] (nullable): last
+ * point assigned to each feature or -1.  Returns nmatches. */
+int orc_search_by_projection(const orc_keypoint* keysUn, const uint8_t* desc, const float* uRight,
+                             const uint8_t* occupied, int n, float mnMinX, float mnMinY, float mnMaxX, float mnMaxY,
+                             const float* mvScaleFactors, const orc_track_point* pts, int npts, float th, int bFarPoints,
+                             float thFarPoints, float mfNNratio, int32_t* match, int32_t* owner);
+
 int orc_hardware_threads(void);
 #ifdef __cplusplus
 }

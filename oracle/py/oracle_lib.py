@@ -13,6 +13,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ORACLE_DIR = os.path.dirname(_HERE)
 _SO = os.path.join(_ORACLE_DIR, "_build", "liborb_oracle.so")
 
+TRACK_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<f4"), ("view_cos", "<f4"),
+                        ("track_depth", "<f4"), ("level", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
+assert TRACK_DTYPE.itemsize == 60
+
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
                      ("octave", "<i4"), ("class_id", "<i4")])
 assert KP_DTYPE.itemsize == 28
@@ -67,6 +71,10 @@ def lib():
                                         C.c_void_p, C.c_void_p, C.c_int]
         L.orc_extract_batch.restype = C.c_int
         L.orc_hardware_threads.restype = C.c_int
+        L.orc_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
+                                               C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int,
+                                               C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_search_by_projection.restype = C.c_int
         L.orc_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                          C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_stereo_matches.restype = C.c_int
@@ -241,6 +249,27 @@ def stereo_matches(ex_left, ex_right, kps_l, desc_l, kps_r, desc_r, mb, mbf):
     faults = lib().orc_stereo_matches(ex_left._h, ex_right._h, _p(kl), _p(dl), n, _p(kr), _p(dr), kr.shape[0], float(mb),
                                       float(mbf), _p(u), _p(z), _p(sad))
     return u, z, sad, int(faults)
+
+
+def search_by_projection(keys_un, desc, u_right, occupied, bounds, scale_factors, pts, th=1.0, far_points=False,
+                         th_far=0.0, nn_ratio=0.8):
+    """Frame grid + ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) for Nleft == -1
+    (ORBmatcher.cc:44-143).  bounds = (mnMinX, mnMinY, mnMaxX, mnMaxY); pts: TRACK_DTYPE array.
+    -> (match int32 (npts,), owner int32 (n,), nmatches)"""
+    k = np.ascontiguousarray(keys_un, KP_DTYPE)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = k.shape[0]
+    ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+    oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    p = np.ascontiguousarray(pts, TRACK_DTYPE)
+    match = np.empty(p.shape[0], np.int32)
+    owner = np.empty(n, np.int32)
+    nm = lib().orc_search_by_projection(_p(k), _p(d), None if ur is None else _p(ur), None if oc is None else _p(oc), n,
+                                        float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]), _p(sf),
+                                        _p(p), p.shape[0], float(th), int(bool(far_points)), float(th_far),
+                                        float(nn_ratio), _p(match), _p(owner))
+    return match, owner, int(nm)
 
 
 def hardware_threads():

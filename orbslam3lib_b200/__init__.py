@@ -5,5 +5,5 @@ the reference interface used by tests and bench.py.  Nothing in this package imp
 from . import scenes  # noqa: F401
 from ._lib import KP_DTYPE, OrbfeError, build  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
-from .matcher import BFMatcher  # noqa: F401
+from .matcher import BFMatcher, ORBmatcher  # noqa: F401
 from .sharded import ShardedMatcher, shard_range  # noqa: F401

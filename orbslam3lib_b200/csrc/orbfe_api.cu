@@ -28,6 +28,12 @@ int blur_tile_table(const Geom& g, BlurTile* out, int cap);
 int launch_blur_tiles(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, const void* tiles, int nTiles,
                       const int* levelCount, cudaStream_t st);
 size_t stereo_smem_bytes(int cap);
+size_t search_smem_bytes(int cap);
+int launch_search_by_projection(const float bounds[4], const float* scale, int nlevels, float th, int farPoints,
+                                float thFar, float nnRatio, const orbfe_keypoint* keys, const uint8_t* desc,
+                                const float* uRight, const uint8_t* occupied, const int* nFeat, int cap, const void* pts,
+                                const int* nPts, int ptsCap, int nframes, int* match, int* owner, int* nMatches,
+                                cudaStream_t st);
 int launch_stereo(const Geom& g, const float* scale, const float* invScale, const uint8_t* pyr, const orbfe_keypoint* kps,
                   const uint8_t* desc, const ImageResult* result, int npairs, int cap, float mb, float mbf, float* uRight,
                   float* depth, int* sad, cudaStream_t st);
@@ -878,6 +884,7 @@ struct orbfe_matcher {
     std::mutex mu;
     std::string err;
     DevBuf dQ, dT, dIdx, dDist, dNq, dNt;
+    DevBuf dS[10];    // staging of orbfe_search_by_projection_batch
     float lastMs = 0;
     int lastLaunches = 0;
 };
@@ -1004,6 +1011,7 @@ int orbfe_matcher_destroy(orbfe_matcher* m) {
     if (m->stream) cudaStreamSynchronize(m->stream);
     DevBuf* bufs[] = {&m->dQ, &m->dT, &m->dIdx, &m->dDist, &m->dNq, &m->dNt};
     for (DevBuf* b : bufs) b->release();
+    for (DevBuf& b : m->dS) b.release();
     cudaEventDestroy(m->ev[0]);
     cudaEventDestroy(m->ev[1]);
     if (m->ownStream) cudaStreamDestroy(m->ownStream);
@@ -1041,6 +1049,79 @@ int orbfe_ratio_test(const int32_t* idx, const int32_t* dist, int64_t nq, double
         out[i] = ok ? idx[2 * i] : -1;
     }
     return ORBFE_OK;
+}
+
+int orbfe_search_by_projection_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc,
+                                     const float* u_right, const uint8_t* occupied, const int32_t* n, int cap,
+                                     const float bounds[4], const float* scale_factors, int nlevels,
+                                     const orbfe_track_point* pts, const int32_t* npts, int pts_cap, int nframes, float th,
+                                     int far_points, float th_far, float nn_ratio, int32_t* match, int32_t* owner,
+                                     int32_t* nmatches, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (nframes < 0 || cap < 0 || pts_cap < 0 || nlevels < 1 || nlevels > ORBFE_MAX_LEVELS)
+        return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (nframes == 0) return ORBFE_OK;
+    if (!n || !npts || !bounds || !scale_factors || !match || (cap > 0 && (!keys_un || !desc)) || (pts_cap > 0 && !pts))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (!(bounds[2] > bounds[0]) || !(bounds[3] > bounds[1])) return set_merr(m, ORBFE_ERR_ARG, "empty image bounds");
+    if (cap > 65535 || search_smem_bytes(cap) > 200 * 1024)
+        return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large for the shared-memory frame grid", cap);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)nframes;
+    const void* dIn[6] = {keys_un, desc, u_right, occupied, n, npts};
+    const void* dPts = pts;
+    const size_t inBytes[6] = {F * cap * sizeof(orbfe_keypoint), F * cap * 32, F * cap * 4, F * cap, F * 4, F * 4};
+    if (!inDev) {
+        for (int i = 0; i < 6; i++) {
+            if (!dIn[i]) continue;
+            ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(inBytes[i], 16)));
+            if (inBytes[i]) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, dIn[i], inBytes[i], cudaMemcpyHostToDevice, st));
+            dIn[i] = m->dS[i].p;
+        }
+        ORBFE_MCUDA(m, m->dS[6].reserve(std::max<size_t>(F * pts_cap * sizeof(orbfe_track_point), 16)));
+        if (pts_cap) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[6].p, pts, F * pts_cap * sizeof(orbfe_track_point), cudaMemcpyHostToDevice, st));
+        dPts = m->dS[6].p;
+    }
+    int32_t *dMatch = match, *dOwner = owner, *dCount = nmatches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dS[7].reserve(std::max<size_t>(F * pts_cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[8].reserve(std::max<size_t>(F * cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[9].reserve(F * 4));
+        dMatch = (int32_t*)m->dS[7].p;
+        dOwner = owner ? (int32_t*)m->dS[8].p : nullptr;
+        dCount = (int32_t*)m->dS[9].p;
+    }
+    ORBFE_MCUDA(m, cudaMemsetAsync(dMatch, 0xff, F * pts_cap * 4, st));    // slots past npts[f]: -1
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_search_by_projection(bounds, scale_factors, nlevels, th, far_points, th_far, nn_ratio,
+                                                     (const orbfe_keypoint*)dIn[0], (const uint8_t*)dIn[1],
+                                                     (const float*)dIn[2], (const uint8_t*)dIn[3], (const int*)dIn[4], cap,
+                                                     dPts, (const int*)dIn[5], pts_cap, nframes, dMatch, dOwner, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        if (pts_cap) ORBFE_MCUDA(m, cudaMemcpyAsync(match, dMatch, F * pts_cap * 4, cudaMemcpyDeviceToHost, st));
+        if (owner && cap) ORBFE_MCUDA(m, cudaMemcpyAsync(owner, dOwner, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc, const float* u_right,
+                               const uint8_t* occupied, int n, const float bounds[4], const float* scale_factors,
+                               int nlevels, const orbfe_track_point* pts, int npts, float th, int far_points, float th_far,
+                               float nn_ratio, int32_t* match, int32_t* owner, int32_t* nmatches) {
+    if (n < 0 || npts < 0) return m ? set_merr(m, ORBFE_ERR_ARG, "negative count") : ORBFE_ERR_ARG;
+    const int32_t nn = n, np = npts;
+    return orbfe_search_by_projection_batch(m, keys_un, desc, u_right, occupied, &nn, n, bounds, scale_factors, nlevels,
+                                            pts, &np, npts, 1, th, far_points, th_far, nn_ratio, match, owner, nmatches, 0);
 }
 
 int orbfe_matcher_last_ms(const orbfe_matcher* m, float* kernel_ms, int* launches) {

@@ -6,7 +6,8 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import OrbfeError, ptr
+from ._lib import KP_DTYPE, OrbfeError, ptr
+from .scenes import TRACK_DTYPE
 
 
 class BFMatcher:
@@ -90,3 +91,49 @@ class BFMatcher:
         best right index and the two smallest distances, uint16 like the reference vectors."""
         idx, dist = self.knnMatch(left_desc, right_desc)
         return idx[:, 0].astype(np.uint16), dist[:, 0].astype(np.uint16), dist[:, 1].astype(np.uint16)
+
+
+class ORBmatcher:
+    """ORB_SLAM3::ORBmatcher restricted to the guided search built so far: SearchByProjection(F, vpMapPoints, th,
+    bFarPoints, thFarPoints) (ORBmatcher.cc:44-143) on frames with Nleft == -1.  A frame is passed as its arrays
+    (mvKeysUn, mDescriptors, mvuRight, image bounds, mvScaleFactors), map points as a TRACK_DTYPE array
+    (scenes.TRACK_DTYPE == orbfe_track_point)."""
+
+    TH_HIGH, TH_LOW = 100, 50
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        self._bf = BFMatcher(device)
+
+    def SearchByProjection(self, keys_un, desc, u_right, bounds, scale_factors, track_points, th=1.0, bFarPoints=False,
+                           thFarPoints=50.0, occupied=None):
+        """-> (nmatches, match int32 (npts,), owner int32 (n,)): match[i] = feature given to point i
+        (F.mvpMapPoints[match[i]] = vpMapPoints[i]) or -1; owner[j] = last point assigned to feature j or -1."""
+        k = np.ascontiguousarray(keys_un, KP_DTYPE)
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        p = np.ascontiguousarray(track_points, TRACK_DTYPE)
+        match = np.full(p.shape[0], -1, np.int32)
+        owner = np.full(k.shape[0], -1, np.int32)
+        nm = C.c_int32(0)
+        self._bf._check(_lib.lib().orbfe_search_by_projection(
+            self._bf._h, ptr(k), ptr(d), ptr(ur), ptr(oc), k.shape[0], ptr(b), ptr(sf), sf.shape[0], ptr(p), p.shape[0],
+            float(th), int(bool(bFarPoints)), float(thFarPoints), self.mfNNratio, ptr(match), ptr(owner), C.byref(nm)))
+        return int(nm.value), match, owner
+
+    def search_by_projection_batch_raw(self, keys_un, desc, u_right, occupied, n, cap, bounds, scale_factors, pts, npts,
+                                       pts_cap, nframes, th, match, owner, nmatches, bFarPoints=False, thFarPoints=50.0,
+                                       flags=0):
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        self._bf._check(_lib.lib().orbfe_search_by_projection_batch(
+            self._bf._h, ptr(keys_un), ptr(desc), ptr(u_right), ptr(occupied), ptr(n), int(cap), ptr(b), ptr(sf),
+            sf.shape[0], ptr(pts), ptr(npts), int(pts_cap), int(nframes), float(th), int(bool(bFarPoints)),
+            float(thFarPoints), self.mfNNratio, ptr(match), ptr(owner), ptr(nmatches), int(flags)))
+
+    def last_ms(self):
+        return self._bf.last_ms()

@@ -99,6 +99,47 @@ def previous_frame(cur, seed):
     return np.clip(out + _signed_noise(w, h, seed ^ 0xB0B, 2), 0, 255).astype(np.uint8)
 
 
+TRACK_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<f4"), ("view_cos", "<f4"),
+                        ("track_depth", "<f4"), ("level", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
+
+
+def track_points(kps, desc, u_right, nlevels, npts, seed, jitter=3.0, max_flips=30, dup_frac=0.15):
+    """Synthetic local-map points for ORBmatcher::SearchByProjection (ORBmatcher.cc:44-143): point i is a frame feature
+    seen again -- projected at the feature's position + uniform jitter, predicted level = octave or octave + 1,
+    descriptor = the feature's with 0..max_flips random bit flips, mTrackProjXR = the feature's uRight + jitter.  A
+    fraction of the points are duplicates of an earlier point's feature (two points competing for one feature: the
+    sequential already-matched rule decides), some are not in view, bad or far.  Deterministic in `seed`."""
+    n = len(kps)
+    pts = np.zeros(npts, TRACK_DTYPE)
+    if n == 0 or npts == 0:
+        return pts
+    r = rand_u32(npts * 8, seed).reshape(8, npts)
+    feat = (r[0] % np.uint32(n)).astype(np.int64)
+    ndup = int(npts * dup_frac)
+    if ndup > 0 and npts > 1:
+        dst = (rand_u32(ndup, seed + 1) % np.uint32(npts - 1)).astype(np.int64) + 1
+        feat[dst] = feat[dst - 1]
+    u = lambda a: (a.astype(np.float64) / 4294967296.0)    # noqa: E731
+    pts["proj_x"] = (kps["x"][feat] + (u(r[1]) * 2 - 1) * jitter).astype(np.float32)
+    pts["proj_y"] = (kps["y"][feat] + (u(r[2]) * 2 - 1) * jitter).astype(np.float32)
+    ur = u_right[feat] if u_right is not None else np.full(npts, -1.0, np.float32)
+    pts["proj_xr"] = (ur + (u(r[3]) * 2 - 1) * jitter).astype(np.float32)
+    pts["view_cos"] = (0.9975 + u(r[4]) * 0.0025).astype(np.float32)
+    pts["track_depth"] = (1.0 + u(r[5]) * 39.0).astype(np.float32)
+    pts["level"] = np.minimum(kps["octave"][feat] + (r[6] & 1).astype(np.int32), nlevels - 1)
+    sel = r[7] % np.uint32(100)
+    pts["flags"] = np.where(sel < 4, 0, 1) | np.where((sel >= 4) & (sel < 7), 2, 0) | np.where(sel < 93, 4, 0)
+    d = desc[feat].copy()
+    nflip = (rand_u32(npts, seed + 2) % np.uint32(max_flips + 1)).astype(np.int64)
+    pos = (rand_u32(npts * max_flips, seed + 3) % np.uint32(256)).reshape(npts, max_flips).astype(np.int64)
+    for k in range(max_flips):
+        rows = np.nonzero(nflip > k)[0]
+        p = pos[rows, k]
+        d[rows, p >> 3] ^= (1 << (p & 7)).astype(np.uint8)
+    pts["desc"] = d
+    return pts
+
+
 SCENES = {"noise": noise, "checker": checker, "texture": texture, "flat_blobs": flat_blobs}
 
 

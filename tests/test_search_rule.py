@@ -1,0 +1,122 @@
+"""CPU: the order-free form of the best / runner-up update of ORBmatcher::SearchByProjection (ORBmatcher.cc:80-120)
+that k_search.cu relies on, checked exhaustively-at-random against the literal sequential loop; and the C++ oracle's
+orc_search_by_projection against a literal Python restatement of the same reference lines on small frames."""
+import math
+import random
+
+import numpy as np
+
+from orbslam3lib_b200 import scenes
+
+
+def _sequential(el):
+    bd, bl, bd2, bl2, bi = 256, -1, 256, -1, -1
+    for i, (d, l) in enumerate(el):
+        if d < bd:
+            bd2, bd, bl2, bl, bi = bd, d, bl, l, i
+        elif d < bd2:
+            bl2, bd2 = l, d
+    return bd, bl, bi, bd2, bl2
+
+
+def _order_free(el):
+    keys = [(d, i) for i, (d, _) in enumerate(el)]
+    if not keys or min(keys)[0] >= 256:
+        return 256, -1, -1, 256, -1
+    m1, p1 = min(keys)
+    before = [k for k in keys if k[1] < p1]
+    after = [k for k in keys if k[1] > p1]
+    mp, ms = (min(before) if before else None), (min(after) if after else None)
+    sec = mp if mp is not None and (ms is None or mp[0] <= ms[0]) else ms
+    if sec is None or sec[0] >= 256:
+        return m1, el[p1][1], p1, 256, -1
+    return m1, el[p1][1], p1, sec[0], el[sec[1]][1]
+
+
+def test_runner_up_rule_equals_sequential_loop():
+    rng = random.Random(7)
+    for _ in range(60000):
+        n = rng.randint(0, 9)
+        el = [(rng.choice([rng.randint(0, 5), rng.randint(0, 256)]), rng.randint(0, 3)) for _ in range(n)]
+        assert _sequential(el) == _order_free(el), el
+
+
+def _py_search(keys, desc, u_right, bounds, scale, pts, th, nn_ratio):
+    """literal restatement of Frame.cc:405-436, 672-751 and ORBmatcher.cc:44-143 (Nleft == -1), numpy float32."""
+    f32 = np.float32
+    min_x, min_y, max_x, max_y = [f32(v) for v in bounds]
+    gw, gh = f32(f32(64) / f32(max_x - min_x)), f32(f32(48) / f32(max_y - min_y))
+
+    def c_round(v):
+        v = float(v)
+        return int(math.floor(v + 0.5) if v >= 0 else math.ceil(v - 0.5))
+    grid = {}
+    for i in range(len(keys)):
+        px = c_round(f32(f32(keys["x"][i] - min_x) * gw))
+        py = c_round(f32(f32(keys["y"][i] - min_y) * gh))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    bits = np.unpackbits(desc, axis=1)
+    blocked = np.zeros(len(keys), bool)
+    match = np.full(len(pts), -1, np.int32)
+    for ip in range(len(pts)):
+        mp = pts[ip]
+        if not (mp["flags"] & 1) or (mp["flags"] & 2):
+            continue
+        lvl = int(mp["level"])
+        r = f32(2.5) if float(mp["view_cos"]) > 0.998 else f32(4.0)
+        if th != 1.0:
+            r = f32(r * f32(th))
+        rr = f32(r * f32(scale[lvl]))
+        x, y = f32(mp["proj_x"]), f32(mp["proj_y"])
+        cx0 = max(0, int(math.floor(f32(f32(f32(x - min_x) - rr) * gw))))
+        cx1 = min(63, int(math.ceil(f32(f32(f32(x - min_x) + rr) * gw))))
+        cy0 = max(0, int(math.floor(f32(f32(f32(y - min_y) - rr) * gh))))
+        cy1 = min(47, int(math.ceil(f32(f32(f32(y - min_y) + rr) * gh))))
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            continue
+        cand = []
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for j in grid.get((ix, iy), []):
+                    o = int(keys["octave"][j])
+                    if o < lvl - 1 or o > lvl:
+                        continue
+                    if abs(f32(keys["x"][j] - x)) < rr and abs(f32(keys["y"][j] - y)) < rr:
+                        cand.append(j)
+        mbits = np.unpackbits(mp["desc"])
+        bd, bl, bd2, bl2, bi = 256, -1, 256, -1, -1
+        for j in cand:
+            if blocked[j]:
+                continue
+            if u_right is not None and u_right[j] > 0 and abs(f32(mp["proj_xr"] - u_right[j])) > rr:
+                continue
+            d = int(np.count_nonzero(mbits != bits[j]))
+            if d < bd:
+                bd2, bd, bl2, bl, bi = bd, d, bl, int(keys["octave"][j]), j
+            elif d < bd2:
+                bl2, bd2 = int(keys["octave"][j]), d
+        if bd <= 100:
+            lim = f32(f32(nn_ratio) * f32(bd2))
+            if bl == bl2 and f32(bd) > lim:
+                continue
+            if bl != bl2 or f32(bd) <= lim:
+                match[ip] = bi
+                blocked[bi] = bool(mp["flags"] & 4)
+    return match
+
+
+def test_oracle_search_by_projection_vs_python(oracle):
+    for seed, th in ((11, 1.0), (12, 3.0), (13, 8.0)):
+        img = scenes.make("texture", 320, 240, 6000 + seed)
+        ex = oracle.OracleExtractor(500, 1.2, 8, 20, 7)
+        _, kps, desc = ex(img)
+        u_right = np.where(scenes.rand_u32(len(kps), seed) % 3 == 0, -1.0, kps["x"] - 7.5).astype(np.float32)
+        pts = scenes.track_points(kps, desc, u_right, 8, 400, seed)
+        m, owner, nm = oracle.search_by_projection(kps, desc, u_right, None, (0, 0, 320, 240), ex.scale, pts, th=th,
+                                                   nn_ratio=0.8)
+        ref = _py_search(kps, desc, u_right, (0, 0, 320, 240), ex.scale, pts, th, 0.8)
+        np.testing.assert_array_equal(m, ref)
+        assert nm == int((m >= 0).sum()) and nm > 100
+        for j in np.unique(m[m >= 0]):
+            assert owner[j] == np.nonzero(m == j)[0].max()
