@@ -258,6 +258,69 @@ def stereo_leg(args, local, dev):
     return out
 
 
+def search_leg(args, local, dev):
+    """SURVEY.md 8(f) rank 3: frame grid + ORBmatcher::SearchByProjection (ORBmatcher.cc:44-143) for a batch of frames
+    (one CTA per frame), 2000 local-map points against ~1200 features per frame; everything resident in HBM.  The CPU
+    oracle's orc_search_by_projection is timed beside it on one thread and checked on the sampled frames."""
+    import torch
+    from orbslam3lib_b200 import ORBextractor, ORBmatcher, _lib, scenes
+    nfr, npts = args.search_frames, 2000
+    ex = ORBextractor(NFEAT, 1.2, NLEVELS, 20, 7, device=local)
+    cap = ex.max_keypoints
+    nsc = min(nfr, 8)
+    imgs = np.stack([scenes.make("texture", W, H, 7000 + k) for k in range(nsc)])
+    counts, _, kps, desc = ex.extract_batch(imgs)
+    scale = ex.GetScaleFactors()
+    K = np.zeros((nfr, cap), _lib.KP_DTYPE)
+    D = np.zeros((nfr, cap, 32), np.uint8)
+    U = np.full((nfr, cap), -1, np.float32)
+    P = np.zeros((nfr, npts), scenes.TRACK_DTYPE)
+    nn = np.zeros(nfr, np.int32)
+    for f in range(nfr):
+        k = f % nsc
+        n = int(counts[k])
+        nn[f] = n
+        K[f, :n], D[f, :n] = kps[k, :n], desc[k, :n]
+        U[f, :n] = kps[k, :n]["x"] - 9.25
+        if f < nsc:
+            P[f] = scenes.track_points(kps[k, :n], desc[k, :n], U[f, :n], NLEVELS, npts, 7100 + f, dup_frac=0.2)
+        else:
+            P[f] = P[f % nsc]
+    t = lambda a: torch.from_numpy(a.view(np.uint8).reshape(a.shape[0], -1)).to(dev)    # noqa: E731
+    dK, dD, dU, dP = t(K), t(D), torch.from_numpy(U).to(dev), t(P)
+    dn = torch.from_numpy(nn).to(dev)
+    dnp = torch.full((nfr,), npts, dtype=torch.int32, device=dev)
+    d_match = torch.zeros((nfr, npts), dtype=torch.int32, device=dev)
+    d_owner = torch.zeros((nfr, cap), dtype=torch.int32, device=dev)
+    d_cnt = torch.zeros(nfr, dtype=torch.int32, device=dev)
+    m = ORBmatcher(0.8, device=local)
+    bounds = (0.0, 0.0, float(W), float(H))
+    FL = _lib.IN_DEVICE | _lib.OUT_DEVICE
+    ms, steps = 0.0, 5
+    for it in range(steps + 2):
+        m.search_by_projection_batch_raw(dK, dD, dU, None, dn, cap, bounds, scale, dP, dnp, npts, nfr, 1.0, d_match,
+                                         d_owner, d_cnt, flags=FL)
+        if it >= 2:
+            ms += m.last_ms()[0]
+    match = d_match[:nsc].cpu().numpy()
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+    import oracle_lib
+    oracle_lib.build()
+    ok, t_cpu = True, 0.0
+    for f in range(nsc):
+        n = int(nn[f])
+        t0 = time.perf_counter()
+        rm, _, _ = oracle_lib.search_by_projection(K[f, :n], D[f, :n], U[f, :n], None, bounds, scale, P[f], th=1.0,
+                                                   nn_ratio=0.8)
+        t_cpu += time.perf_counter() - t0
+        ok = ok and bool(np.array_equal(match[f], rm))
+    return {"workload": "ORBmatcher::SearchByProjection, %d frames per step, %d map points x ~%d features per frame, th = 1"
+                        % (nfr, npts, int(nn.mean())), "kernel_ms_per_step": ms / steps,
+            "frames_per_s": nfr / (ms / steps * 1e-3), "matches_per_frame": float(d_cnt.float().mean().item()),
+            "cpu_oracle_frames_per_s_1thread": nsc / t_cpu,
+            "parity_sample": {"frames": nsc, "vs": "CPU oracle (match index per map point)", "ok": ok}}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -309,6 +372,7 @@ def main():
     ap.add_argument("--map-rows", type=int, default=1000000, help="rows of the map-scale kNN leg (configs[4]); 0 = skip")
     ap.add_argument("--map-steps", type=int, default=2)
     ap.add_argument("--latency-iters", type=int, default=300, help="stereo pairs of the per-frame latency leg (configs[2]); 0 = skip")
+    ap.add_argument("--search-frames", type=int, default=512, help="frames per step of the SearchByProjection leg; 0 = skip")
     ap.add_argument("--stereo-pairs", type=int, default=512, help="pairs per step of the ComputeStereoMatches leg; 0 = skip")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -478,6 +542,9 @@ def main():
         del d_kps, d_desc, d_idx, d_dist
         torch.cuda.empty_cache()
         line["stereo_matches"] = stereo_leg(args, local, dev)
+    if args.search_frames > 0:
+        torch.cuda.empty_cache()
+        line["search_by_projection"] = search_leg(args, local, dev)
     if not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
         import oracle_lib

@@ -22,7 +22,10 @@
 
 namespace orbfe {
 
-constexpr int SR_THREADS = 1024;
+#ifndef ORBFE_SEARCH_THREADS
+#define ORBFE_SEARCH_THREADS 256
+#endif
+constexpr int SR_THREADS = ORBFE_SEARCH_THREADS;
 constexpr int SR_WARPS = SR_THREADS / 32;
 constexpr int SR_ROWS = 48, SR_COLS = 64, SR_CELLS = SR_ROWS * SR_COLS;    // FRAME_GRID_ROWS / COLS, Frame.h:46-47
 constexpr int SR_TH_HIGH = 100;                                           // ORBmatcher::TH_HIGH
@@ -78,7 +81,7 @@ __global__ void __launch_bounds__(SR_THREADS) search_by_projection_kernel(
     __shared__ int sScan[SR_WARPS + 1];
     __shared__ int sRes[SR_WARPS];     // tentative feature of the chunk's points (-1 none)
     __shared__ int sOpen;              // bit w: point of warp w still open
-    __shared__ int sCount;
+    __shared__ int sCount, sTotal;
 
     const int f = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -129,15 +132,15 @@ __global__ void __launch_bounds__(SR_THREADS) search_by_projection_kernel(
         if (lane == 31) sScan[warp] = inc;
         __syncthreads();
         if (warp == 0) {
-            const int w = sScan[lane];
+            const int w = lane < SR_WARPS ? sScan[lane] : 0;
             int winc = w;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int v = __shfl_up_sync(0xffffffffu, winc, o);
                 if (lane >= o) winc += v;
             }
-            sScan[lane] = winc - w;
-            if (lane == 31) sScan[SR_WARPS] = winc;
+            if (lane < SR_WARPS) sScan[lane] = winc - w;
+            if (lane == 31) sTotal = winc;
         }
         __syncthreads();
         int run = sScan[warp] + inc - s;
@@ -146,7 +149,7 @@ __global__ void __launch_bounds__(SR_THREADS) search_by_projection_kernel(
             cellStart[i] = run;
             run += c;
         }
-        if (tid == SR_THREADS - 1) cellStart[SR_CELLS] = sScan[SR_WARPS];
+        if (tid == SR_THREADS - 1) cellStart[SR_CELLS] = sTotal;
     }
     __syncthreads();
     for (int i = tid; i < n; i += SR_THREADS) {
@@ -204,7 +207,7 @@ __global__ void __launch_bounds__(SR_THREADS) search_by_projection_kernel(
                 }
             }
         }
-        if (tid == 0) sOpen = npts - base >= SR_WARPS ? -1 : (int)((1u << (npts - base)) - 1u);
+        if (tid == 0) sOpen = (int)(0xffffffffu >> (32 - min(npts - base, SR_WARPS)));
         __syncthreads();
         for (;;) {
             // -- search: every open point against the current blocked set --
