@@ -24,7 +24,10 @@
 
 namespace orbfe {
 
-constexpr int OT_THREADS = 256;
+#ifndef ORBFE_OT_THREADS
+#define ORBFE_OT_THREADS 256
+#endif
+constexpr int OT_THREADS = ORBFE_OT_THREADS;
 constexpr int OT_WARPS = OT_THREADS / 32;
 
 struct __align__(16) OtNode {

@@ -297,7 +297,7 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
     // octree capacities
     int nodeCap = 256;
     for (int l = 0; l < g.nlevels; l++) nodeCap = std::max(nodeCap, g.lv[l].keyCap + 1);
-    int keySmem = 4096;
+    int keySmem = getenv("ORBFE_OT_KEYSMEM") ? atoi(getenv("ORBFE_OT_KEYSMEM")) : 2048;    // kernel tuning
     while (keySmem > 0 && octree_smem_bytes(nodeCap, keySmem) > 200 * 1024) keySmem /= 2;
     if (octree_smem_bytes(nodeCap, keySmem) > 220 * 1024)
         return set_err(ex, ORBFE_ERR_ARG, "nfeatures too large for the shared-memory quadtree (%d nodes per level)", nodeCap);
