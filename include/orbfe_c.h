@@ -180,6 +180,12 @@ int orbfe_search_by_projection_batch(orbfe_matcher* m, const orbfe_keypoint* key
                                      const orbfe_track_point* pts, const int32_t* npts, int pts_cap, int nframes, float th,
                                      int far_points, float th_far, float nn_ratio, int32_t* match, int32_t* owner,
                                      int32_t* nmatches, unsigned flags);
+/* Frame::UndistortKeyPoints (Frame.cc:763-796): mvKeysUn = mvKeys with the positions passed through
+ * cv::undistortPoints(pts, pts, K, mDistCoef, Mat(), mK) (OpenCV 4.x: 5 fixed-point iterations in double); K = (fx, fy,
+ * cx, cy) of mK, dist_coef = k1, k2, p1, p2[, k3] (ndist 4 or 5, up to OpenCV's 14); dist_coef[0] == 0 copies the
+ * keypoints (:765-769).  n keypoints of any number of frames of the same camera.  dist_coef is host memory. */
+int orbfe_undistort_keypoints(orbfe_matcher* m, const orbfe_keypoint* keys, int64_t n, float fx, float fy, float cx,
+                              float cy, const float* dist_coef, int ndist, orbfe_keypoint* keys_un, unsigned flags);
 /* device time (ms) of the kernel(s) of the last call and their launch count */
 int orbfe_matcher_last_ms(const orbfe_matcher* m, float* kernel_ms, int* launches);
 

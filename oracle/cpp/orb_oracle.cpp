@@ -1024,6 +1024,49 @@ int orc_search_by_projection(const orc_keypoint* keysUn, const uint8_t* desc, co
     return nmatches;
 }
 
+// ---- Frame::UndistortKeyPoints (Frame.cc:763-796) ------------------------------------------------------------------
+// cv::undistortPoints(mat, mat, K, mDistCoef, cv::Mat(), mK): OpenCV 4.x cvUndistortPointsInternal with the default
+// criteria TermCriteria(MAX_ITER, 5, 0.01): normalise, 5 fixed-point iterations of the radial / tangential model in
+// double, re-project with P = mK, store as float.  k = (k1, k2, p1, p2[, k3]); mDistCoef[0] == 0 copies the keypoints
+// (:765-769).  Pinned against cv2.undistortPoints in tests/test_oracle_vs_cv2.py.
+void orc_undistort_keypoints(const orc_keypoint* keys, int n, float fx, float fy, float cx, float cy, const float* dist,
+                             int ndist, orc_keypoint* keysUn) {
+    if (ndist <= 0 || dist[0] == 0.0) {
+        for (int i = 0; i < n; i++) keysUn[i] = keys[i];
+        return;
+    }
+    double k[14] = {0};
+    for (int i = 0; i < ndist && i < 14; i++) k[i] = dist[i];
+    const double dfx = fx, dfy = fy, dcx = cx, dcy = cy;
+    const double ifx = 1. / dfx, ify = 1. / dfy;
+    for (int i = 0; i < n; i++) {
+        double x = keys[i].x, y = keys[i].y;
+        const double u = x, v = y;
+        x = (x - dcx) * ifx;
+        y = (y - dcy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) {
+                x = (u - dcx) * ifx;
+                y = (v - dcy) * ify;
+                break;
+            }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = dfx * x + 0.0 * y + dcx;
+        const double yy = 0.0 * x + dfy * y + dcy;
+        const double ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        keysUn[i] = keys[i];
+        keysUn[i].x = (float)(xx * ww);
+        keysUn[i].y = (float)(yy * ww);
+    }
+}
+
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

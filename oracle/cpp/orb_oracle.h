@@ -95,6 +95,11 @@ int orc_search_by_projection(const orc_keypoint* keysUn, const uint8_t* desc, co
                              const float* mvScaleFactors, const orc_track_point* pts, int npts, float th, int bFarPoints,
                              float thFarPoints, float mfNNratio, int32_t* match, int32_t* owner);
 
+/* Frame::UndistortKeyPoints (Frame.cc:763-796): cv::undistortPoints(pts, pts, K, mDistCoef, Mat(), mK) on the keypoint
+ * positions (5 iterations in double), everything else copied.  dist: k1, k2, p1, p2[, k3]; dist[0] == 0 copies. */
+void orc_undistort_keypoints(const orc_keypoint* keys, int n, float fx, float fy, float cx, float cy, const float* dist,
+                             int ndist, orc_keypoint* keysUn);
+
 int orc_hardware_threads(void);
 #ifdef __cplusplus
 }

@@ -162,13 +162,34 @@ def gen_stereo(case):
     print("stereo_%s: %d / %d keypoints, %d matches" % (name, len(kl), len(kr), int((u >= 0).sum())))
 
 
+def gen_undistort():
+    """Frame::UndistortKeyPoints fixture: genuine cv2.undistortPoints on seeded positions, three coefficient sets."""
+    import cv2
+    from orbslam3lib_b200 import scenes
+    fx, fy, cx, cy = 458.654, 457.296, 367.215, 248.375
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+    r = scenes.rand_u32(6000, 4201).astype(np.float64) / 4294967296.0
+    pts = np.stack([(r[:3000] * 752).astype(np.float32), (r[3000:] * 480).astype(np.float32)], 1)
+    out = {"K": K, "pts": pts, "opencv_version": np.array(cv2.__version__), "seed": np.array(4201)}
+    for i, d in enumerate(([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], [-0.28, 0.07, 0.0002, 1.7e-05, 0.01],
+                           [0.9, -2.5, 0.01, -0.02])):
+        D = np.array(d, np.float32)
+        out["dist_%d" % i] = D
+        out["un_%d" % i] = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, D, None, K).reshape(-1, 2)
+    np.savez_compressed(os.path.join(GOLDEN, "undistort.npz"), **out)
+    print("undistort: ok")
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if "--undistort-only" in sys.argv:
+        return gen_undistort()
     if "--stereo-only" in sys.argv:
         for c in STEREO_CASES:
             gen_stereo(c)
         return
     gen_primitives()
+    gen_undistort()
     for c in STEREO_CASES:
         gen_stereo(c)
     for c in EXTRACT_CASES:

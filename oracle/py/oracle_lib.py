@@ -71,6 +71,8 @@ def lib():
                                         C.c_void_p, C.c_void_p, C.c_int]
         L.orc_extract_batch.restype = C.c_int
         L.orc_hardware_threads.restype = C.c_int
+        L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p,
+                                              C.c_int, C.c_void_p]
         L.orc_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                                C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int,
                                                C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
@@ -270,6 +272,15 @@ def search_by_projection(keys_un, desc, u_right, occupied, bounds, scale_factors
                                         _p(p), p.shape[0], float(th), int(bool(far_points)), float(th_far),
                                         float(nn_ratio), _p(match), _p(owner))
     return match, owner, int(nm)
+
+
+def undistort_keypoints(kps, fx, fy, cx, cy, dist):
+    """Frame::UndistortKeyPoints (Frame.cc:763-796) -> mvKeysUn."""
+    k = np.ascontiguousarray(kps, KP_DTYPE)
+    d = np.ascontiguousarray(dist, np.float32)
+    out = np.empty_like(k)
+    lib().orc_undistort_keypoints(_p(k), k.shape[0], float(fx), float(fy), float(cx), float(cy), _p(d), d.shape[0], _p(out))
+    return out
 
 
 def hardware_threads():

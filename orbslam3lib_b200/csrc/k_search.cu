@@ -367,4 +367,65 @@ int launch_search_by_projection(const float bounds[4], const float* scale, int n
     return 1;
 }
 
+// ---- Frame::UndistortKeyPoints (Frame.cc:763-796) --------------------------------------------------------------------
+// cv::undistortPoints(pts, pts, K, mDistCoef, Mat(), mK) = OpenCV 4.x cvUndistortPointsInternal with the default
+// TermCriteria(MAX_ITER, 5, 0.01): normalise with K, five fixed-point iterations of the radial / tangential model in
+// double, re-project with P = mK, round to float.  One thread per keypoint; fp64, no FMA (--fmad=false), operation
+// order as in OpenCV (the zero terms of P are kept: they are exact).
+struct UndistortParams {
+    double fx, fy, cx, cy;
+    double k[14];
+    int identity;    // mDistCoef[0] == 0: mvKeysUn = mvKeys (:765-769)
+};
+
+__global__ void __launch_bounds__(256) undistort_keypoints_kernel(const __grid_constant__ UndistortParams P,
+                                                                  const orbfe_keypoint* __restrict__ keys, int n,
+                                                                  orbfe_keypoint* __restrict__ keysUn) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    orbfe_keypoint kp = keys[i];
+    if (!P.identity) {
+        const double* k = P.k;
+        const double ifx = 1. / P.fx, ify = 1. / P.fy;
+        double x = kp.x, y = kp.y;
+        const double u = x, v = y;
+        x = (x - P.cx) * ifx;
+        y = (y - P.cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) {
+                x = (u - P.cx) * ifx;
+                y = (v - P.cy) * ify;
+                break;
+            }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = P.fx * x + 0.0 * y + P.cx;
+        const double yy = 0.0 * x + P.fy * y + P.cy;
+        const double ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        kp.x = (float)(xx * ww);
+        kp.y = (float)(yy * ww);
+    }
+    keysUn[i] = kp;
+}
+
+int launch_undistort(const orbfe_keypoint* keys, int n, float fx, float fy, float cx, float cy, const float* dist,
+                     int ndist, orbfe_keypoint* keysUn, cudaStream_t st) {
+    if (n <= 0) return 0;
+    UndistortParams P;
+    P.fx = fx;
+    P.fy = fy;
+    P.cx = cx;
+    P.cy = cy;
+    for (int i = 0; i < 14; i++) P.k[i] = i < ndist ? (double)dist[i] : 0.0;
+    P.identity = ndist <= 0 || dist[0] == 0.0;
+    undistort_keypoints_kernel<<<(n + 255) / 256, 256, 0, st>>>(P, keys, n, keysUn);
+    return 1;
+}
+
 }    // namespace orbfe

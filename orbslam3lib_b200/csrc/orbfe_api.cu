@@ -29,6 +29,8 @@ int launch_blur_tiles(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, c
                       const int* levelCount, cudaStream_t st);
 size_t stereo_smem_bytes(int cap);
 size_t search_smem_bytes(int cap);
+int launch_undistort(const orbfe_keypoint* keys, int n, float fx, float fy, float cx, float cy, const float* dist,
+                     int ndist, orbfe_keypoint* keysUn, cudaStream_t st);
 int launch_search_by_projection(const float bounds[4], const float* scale, int nlevels, float th, int farPoints,
                                 float thFar, float nnRatio, const orbfe_keypoint* keys, const uint8_t* desc,
                                 const float* uRight, const uint8_t* occupied, const int* nFeat, int cap, const void* pts,
@@ -1122,6 +1124,41 @@ int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_keypoint* keys_un, 
     const int32_t nn = n, np = npts;
     return orbfe_search_by_projection_batch(m, keys_un, desc, u_right, occupied, &nn, n, bounds, scale_factors, nlevels,
                                             pts, &np, npts, 1, th, far_points, th_far, nn_ratio, match, owner, nmatches, 0);
+}
+
+int orbfe_undistort_keypoints(orbfe_matcher* m, const orbfe_keypoint* keys, int64_t n, float fx, float fy, float cx,
+                              float cy, const float* dist_coef, int ndist, orbfe_keypoint* keys_un, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (n < 0 || n > (1ll << 30) || ndist < 0 || ndist > 14 || (ndist > 0 && !dist_coef)) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (n == 0) return ORBFE_OK;
+    if (!keys || !keys_un) return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (!(fx != 0.f) || !(fy != 0.f)) return set_merr(m, ORBFE_ERR_ARG, "zero focal length");
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t bytes = (size_t)n * sizeof(orbfe_keypoint);
+    const orbfe_keypoint* dk = keys;
+    orbfe_keypoint* du = keys_un;
+    if (!inDev) {
+        ORBFE_MCUDA(m, m->dS[0].reserve(bytes));
+        ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[0].p, keys, bytes, cudaMemcpyHostToDevice, st));
+        dk = (const orbfe_keypoint*)m->dS[0].p;
+    }
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dS[8].reserve(bytes));
+        du = (orbfe_keypoint*)m->dS[8].p;
+    }
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_undistort(dk, (int)n, fx, fy, cx, cy, dist_coef, ndist, du, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) ORBFE_MCUDA(m, cudaMemcpyAsync(keys_un, du, bytes, cudaMemcpyDeviceToHost, st));
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
 }
 
 int orbfe_matcher_last_ms(const orbfe_matcher* m, float* kernel_ms, int* launches) {

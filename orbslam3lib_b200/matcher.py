@@ -135,5 +135,17 @@ class ORBmatcher:
             sf.shape[0], ptr(pts), ptr(npts), int(pts_cap), int(nframes), float(th), int(bool(bFarPoints)),
             float(thFarPoints), self.mfNNratio, ptr(match), ptr(owner), ptr(nmatches), int(flags)))
 
+    def UndistortKeyPoints(self, keys, K, dist_coef):
+        """Frame::UndistortKeyPoints (Frame.cc:763-796): keys (KP_DTYPE), K = 3x3 mK or (fx, fy, cx, cy), mDistCoef ->
+        mvKeysUn."""
+        k = np.ascontiguousarray(keys, KP_DTYPE)
+        K = np.asarray(K, np.float32)
+        fx, fy, cx, cy = (K[0, 0], K[1, 1], K[0, 2], K[1, 2]) if K.ndim == 2 else K
+        d = np.ascontiguousarray(dist_coef, np.float32).reshape(-1)
+        out = np.empty_like(k)
+        self._bf._check(_lib.lib().orbfe_undistort_keypoints(self._bf._h, ptr(k), k.shape[0], float(fx), float(fy),
+                                                             float(cx), float(cy), ptr(d), d.shape[0], ptr(out), 0))
+        return out
+
     def last_ms(self):
         return self._bf.last_ms()

@@ -45,3 +45,24 @@ def test_stereo_fixture(path):
     counts, kps, desc, u, z = ex.extract_stereo_batch(np.stack([left, right])[None], mb, mbf)
     nL, nR = int(counts[0, 0]), int(counts[0, 1])
     gu.check_stereo_against_fixture(nL, nR, desc[0, 0, :nL], u[0, :nL], z[0, :nL], g)
+
+
+def test_undistort_fixture():
+    """Frame::UndistortKeyPoints on the GPU against the committed cv2.undistortPoints fixture, bit for bit."""
+    from orbslam3lib_b200 import ORBmatcher, _lib
+    g = gu.load(os.path.join(gu.GOLDEN, "undistort.npz"))
+    K, pts = g["K"], g["pts"]
+    kps = np.zeros(len(pts), _lib.KP_DTYPE)
+    kps["x"], kps["y"] = pts[:, 0], pts[:, 1]
+    kps["octave"], kps["angle"], kps["class_id"] = np.arange(len(pts)) % 8, 33.25, -1
+    m = ORBmatcher()
+    for i in range(3):
+        out = m.UndistortKeyPoints(kps, K, g["dist_%d" % i])
+        ref = g["un_%d" % i]
+        np.testing.assert_array_equal(out["x"].view(np.uint32), np.ascontiguousarray(ref[:, 0]).view(np.uint32))
+        np.testing.assert_array_equal(out["y"].view(np.uint32), np.ascontiguousarray(ref[:, 1]).view(np.uint32))
+        for f in ("size", "angle", "response", "octave", "class_id"):
+            np.testing.assert_array_equal(out[f], kps[f])
+    same = m.UndistortKeyPoints(kps, K, [0.0, 0.1, 0.0, 0.0])    # mDistCoef[0] == 0 -> copy
+    np.testing.assert_array_equal(same, kps)
+    assert len(m.UndistortKeyPoints(kps[:0], K, g["dist_0"])) == 0

@@ -106,3 +106,16 @@ def test_stereo_matches_fixture(oracle, path):
     gu.check_stereo_against_fixture(len(kl), len(kr), dl, u, z, g)
     assert int((u >= 0).sum()) > 50
     assert ((sad >= 0) >= (u >= 0)).all()    # the median cut only removes accepted matches
+
+
+def test_undistort_fixture(oracle):
+    """orc_undistort_keypoints against the committed cv2.undistortPoints fixture."""
+    g = gu.load(os.path.join(gu.GOLDEN, "undistort.npz"))
+    K, pts = g["K"], g["pts"]
+    kps = np.zeros(len(pts), oracle.KP_DTYPE)
+    kps["x"], kps["y"] = pts[:, 0], pts[:, 1]
+    for i in range(3):
+        out = oracle.undistort_keypoints(kps, K[0, 0], K[1, 1], K[0, 2], K[1, 2], g["dist_%d" % i])
+        ref = g["un_%d" % i]
+        np.testing.assert_array_equal(out["x"].view(np.uint32), np.ascontiguousarray(ref[:, 0]).view(np.uint32))
+        np.testing.assert_array_equal(out["y"].view(np.uint32), np.ascontiguousarray(ref[:, 1]).view(np.uint32))

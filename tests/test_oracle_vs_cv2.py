@@ -139,3 +139,29 @@ def test_stereo_matches_vs_cv2(oracle, kind, w, h, seed, nf, rectified):
         u2, z2 = cv2_oracle.stereo_matches_cv2(pl, pr, eL.scale, eL.inv_scale, kl, dl, kr, dr, mb, mbf)
         np.testing.assert_array_equal(u.view(np.uint32), u2.view(np.uint32))
         np.testing.assert_array_equal(z.view(np.uint32), z2.view(np.uint32))
+
+
+@pytest.mark.parametrize("dist", [
+    [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05],           # EuRoC cam0
+    [-0.28, 0.07, 0.0002, 1.7e-05, 0.01],                            # with k3
+    [0.9, -2.5, 0.01, -0.02],                                        # strong: icdist < 0 near the corners
+    [0.0, 0.07, 0.0002, 1.7e-05],                                    # mDistCoef[0] == 0 -> copy (Frame.cc:765-769)
+])
+def test_undistort_keypoints_vs_cv2(oracle, dist):
+    """Frame::UndistortKeyPoints: the restated cv::undistortPoints (5 iterations, double) against cv2, bit for bit."""
+    fx, fy, cx, cy = 458.654, 457.296, 367.215, 248.375
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+    D = np.array(dist, np.float32)
+    r = scenes.rand_u32(8000, 7400).astype(np.float64) / 4294967296.0
+    kps = np.zeros(4000, oracle.KP_DTYPE)
+    kps["x"], kps["y"] = (r[:4000] * 752).astype(np.float32), (r[4000:] * 480).astype(np.float32)
+    kps["octave"], kps["angle"] = np.arange(4000) % 8, 17.5
+    out = oracle.undistort_keypoints(kps, K[0, 0], K[1, 1], K[0, 2], K[1, 2], D)
+    if D[0] == 0:
+        ref = np.stack([kps["x"], kps["y"]], 1)
+    else:
+        ref = cv2.undistortPoints(np.stack([kps["x"], kps["y"]], 1).reshape(-1, 1, 2), K, D, None, K).reshape(-1, 2)
+    np.testing.assert_array_equal(out["x"].view(np.uint32), np.ascontiguousarray(ref[:, 0]).view(np.uint32))
+    np.testing.assert_array_equal(out["y"].view(np.uint32), np.ascontiguousarray(ref[:, 1]).view(np.uint32))
+    for f in ("size", "angle", "response", "octave", "class_id"):
+        np.testing.assert_array_equal(out[f], kps[f])
