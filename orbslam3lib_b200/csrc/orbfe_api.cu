@@ -217,6 +217,7 @@ struct orbfe_extractor {
     cudaStream_t ownStream = nullptr;    // the private stream (owned)
     cudaEvent_t ev[8] = {};
     cudaStream_t inStream = nullptr, outStream = nullptr;    // copy streams of the pipelined host path
+    cudaStream_t auxStream = nullptr;                        // second compute stream of the pipelined host path
     std::vector<cudaEvent_t> pipeEv;                         // 2 events per sub-chunk (input landed, compute done)
     std::mutex mu;
     std::string err;
@@ -242,6 +243,7 @@ struct orbfe_extractor {
 
     // last call (stage outputs for the parity accessors)
     int lastChunkBase = 0, lastChunkN = 0, lastCap = 0, lastLaunches = 0;
+    int lastWsOff = 0;    // workspace slot of image lastChunkBase (the pipelined path alternates two workspace halves)
     const orbfe_keypoint* lastKps = nullptr;    // device pointers of the last chunk's outputs
     const uint8_t* lastDesc = nullptr;
     int lastOutN = 0;                              // outputs of the whole last chunk (device copies)
@@ -398,30 +400,39 @@ struct StereoReq {
 // run the kernels on `n` images already resident on the device; outputs go to device buffers dKps/dDesc (cap-strided)
 static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int stride, size_t imageStride, int lap0,
                      int lap1, orbfe_keypoint* dKps, uint8_t* dDesc, int cap, ImageResult* resultDst, bool timed,
-                     const StereoReq* sr = nullptr, float* dU = nullptr, float* dZ = nullptr, int* dSad = nullptr) {
+                     const StereoReq* sr = nullptr, float* dU = nullptr, float* dZ = nullptr, int* dSad = nullptr,
+                     int wsOff = 0, cudaStream_t stOverride = nullptr) {
     const Geom& g = ex->geom;
-    cudaStream_t st = ex->stream;
+    cudaStream_t st = stOverride ? stOverride : ex->stream;
     int launches = 0;
+    // the workspace slots [wsOff, wsOff + n) of this call
     ExtractBuffers bufs = ex->bufs;
+    bufs.pyr += (size_t)wsOff * g.slabBytes;
+    bufs.blur += (size_t)wsOff * g.slabBytes;
+    bufs.slots += (size_t)wsOff * g.nCells * g.slotCap;
+    bufs.cellCount += (size_t)wsOff * g.nCells;
+    bufs.levelKeys += (size_t)wsOff * g.keyTotal;
+    bufs.levelCount += (size_t)wsOff * g.nlevels;
+    bufs.scratch += (size_t)wsOff * bufs.scratchPerImage;
+    bufs.work += (size_t)wsOff * g.outCap;
     bufs.result = resultDst;
     if (timed) cudaEventRecord(ex->ev[1], st);
-    launches += launch_pyramid(g, dImages, n, stride, imageStride, ex->bufs.pyr, ex->xtab, ex->ytab,
-                               ex->rsDims[n >= 32 ? 0 : 1], st);
+    launches += launch_pyramid(g, dImages, n, stride, imageStride, bufs.pyr, ex->xtab, ex->ytab, ex->rsDims[n >= 32 ? 0 : 1], st);
     if (timed) cudaEventRecord(ex->ev[2], st);
-    launches += launch_fast(g, ex->bufs.pyr, n, (const FastItem*)ex->dItems.p, ex->nItems, ex->tileBytes, ex->scoreBytes,
-                            ex->listBytes, ex->bufs.slots, ex->bufs.cellCount, st);
+    launches += launch_fast(g, bufs.pyr, n, (const FastItem*)ex->dItems.p, ex->nItems, ex->tileBytes, ex->scoreBytes,
+                            ex->listBytes, bufs.slots, bufs.cellCount, st);
     if (timed) cudaEventRecord(ex->ev[3], st);
     launches += launch_octree(g, n, bufs, ex->nodeCap, ex->keySmem, st);
     if (timed) cudaEventRecord(ex->ev[4], st);
-    launches += launch_blur_tiles(g, ex->bufs.pyr, ex->bufs.blur, n, ex->dBlurTiles.p, ex->nBlurTiles, ex->bufs.levelCount, st);
+    launches += launch_blur_tiles(g, bufs.pyr, bufs.blur, n, ex->dBlurTiles.p, ex->nBlurTiles, bufs.levelCount, st);
     if (timed) cudaEventRecord(ex->ev[5], st);
     launches += launch_pack(g, n, bufs, lap0, lap1, st);
     launches += launch_describe(g, n, bufs, dKps, dDesc, cap, st);
     if (timed) cudaEventRecord(ex->ev[6], st);
     if (sr) {    // Frame::ComputeStereoMatches on the pairs (2p, 2p + 1) of this chunk, pyramids still in the workspace
         if (timed) cudaEventRecord(ex->evStereo[0], st);
-        launches += launch_stereo(g, ex->tables.scale.data(), ex->tables.invScale.data(), ex->bufs.pyr, dKps, dDesc,
-                                  resultDst, n / 2, cap, sr->mb, sr->mbf, dU, dZ, dSad, st);
+        launches += launch_stereo(g, ex->tables.scale.data(), ex->tables.invScale.data(), bufs.pyr, dKps, dDesc, resultDst,
+                                  n / 2, cap, sr->mb, sr->mbf, dU, dZ, dSad, st);
         if (timed) cudaEventRecord(ex->evStereo[1], st);
     }
     ORBFE_CUDA(ex, cudaGetLastError());
@@ -463,6 +474,7 @@ int orbfe_extractor_create(int device, const orbfe_params* params, orbfe_extract
     ex->stream = ex->ownStream;
     cudaStreamCreateWithFlags(&ex->inStream, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&ex->outStream, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&ex->auxStream, cudaStreamNonBlocking);
     for (auto& e : ex->ev) cudaEventCreate(&e);
     for (auto& e : ex->evStereo) cudaEventCreate(&e);
     *out = ex;
@@ -482,6 +494,7 @@ int orbfe_extractor_destroy(orbfe_extractor* ex) {
     for (auto& e : ex->pipeEv) cudaEventDestroy(e);
     if (ex->inStream) cudaStreamDestroy(ex->inStream);
     if (ex->outStream) cudaStreamDestroy(ex->outStream);
+    if (ex->auxStream) cudaStreamDestroy(ex->auxStream);
     if (ex->ownStream) cudaStreamDestroy(ex->ownStream);
     delete ex;
     return ORBFE_OK;
@@ -603,30 +616,60 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             // host -> host: software pipeline over sub-chunks.  The copy-in of stage k+1 and the copy-out of stage k-1
             // overlap the kernels of stage k (three streams, two events per stage); the workspace is re-used by
             // every stage (the compute stream is in order), inputs / outputs / per-image results are chunk sized.
-            const int nsub = (m + kSub - 1) / kSub;
+            // stage sizes: a short first stage (its copy-in is the only one nothing overlaps), then doubling up to
+            // 2 * kSub (large stages run the kernels more efficiently), and a short last stage (its copy-out is exposed)
+            std::vector<int> sb, sm;    // first image and image count of every stage
+            {
+                static const int ramp = getenv("ORBFE_PIPE_RAMP") ? atoi(getenv("ORBFE_PIPE_RAMP")) : 1;
+                int b = 0, sz = ramp ? std::max(2, (kSub / 4) & ~1) : kSub;
+                const int tail = (kSub / 2) & ~1;
+                while (b < m) {
+                    int mk = std::min(sz, m - b);
+                    if (ramp && m - b <= sz + tail) {    // the end: [rest - tail, tail], or one stage when that is small
+                        mk = m - b > 2 * tail ? m - b - tail : m - b;
+                    }
+                    sb.push_back(b);
+                    sm.push_back(mk);
+                    b += mk;
+                    if (ramp) sz = std::min(2 * sz, 2 * kSub);
+                }
+            }
+            const int nsub = (int)sb.size();
             while ((int)ex->pipeEv.size() < 2 * nsub) {
                 cudaEvent_t e;
-                ORBFE_CUDA(ex, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                ORBFE_CUDA(ex, cudaEventCreate(&e));    // timing enabled: ORBFE_PIPE_TRACE prints the stage timeline
                 ex->pipeEv.push_back(e);
             }
             const size_t imgBytes = (size_t)width * height;
             cudaEventRecord(ex->ev[0], st);
             ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->inStream, ex->ev[0], 0));    // after the caller's earlier work
             for (int k = 0; k < nsub; k++) {
-                const int b0 = k * kSub, mk = std::min(kSub, m - b0);
+                const int b0 = sb[k], mk = sm[k];
                 ORBFE_CUDA(ex, cudaMemcpyAsync((uint8_t*)ex->dIn.p + (size_t)b0 * imgBytes, src + (size_t)b0 * imgBytes,
                                                (size_t)mk * imgBytes, cudaMemcpyHostToDevice, ex->inStream));
                 ORBFE_CUDA(ex, cudaEventRecord(ex->pipeEv[2 * k], ex->inStream));
             }
+            // two compute streams, each with its own half of the workspace: the tail of stage k (small grids, serial
+            // quadtree passes) overlaps the head of stage k + 1
+            int maxStage = 0;
+            for (int v : sm) maxStage = std::max(maxStage, v);
+            static const int dualEnv = getenv("ORBFE_PIPE_DUAL") ? atoi(getenv("ORBFE_PIPE_DUAL")) : 0;    // measured slower (12.3 vs 11.9 ms): off
+            const bool dual = dualEnv && ex->auxStream && 2 * maxStage <= ex->chunkCap;
+            if (dual) ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->auxStream, ex->ev[0], 0));
+            int lastAux = -1;
             for (int k = 0; k < nsub; k++) {
-                const int b0 = k * kSub, mk = std::min(kSub, m - b0);
-                ORBFE_CUDA(ex, cudaStreamWaitEvent(st, ex->pipeEv[2 * k], 0));
+                const int b0 = sb[k], mk = sm[k];
+                cudaStream_t cs = dual && (k & 1) ? ex->auxStream : st;
+                const int wsOff = dual && (k & 1) ? maxStage : 0;
+                if (dual && (k & 1)) lastAux = k;
+                ORBFE_CUDA(ex, cudaStreamWaitEvent(cs, ex->pipeEv[2 * k], 0));
                 rc = run_chunk(ex, (const uint8_t*)ex->dIn.p + (size_t)b0 * imgBytes, mk, width, imgBytes, lap0, lap1,
                                dK + (size_t)b0 * cap, dD + (size_t)b0 * cap * 32, cap, ex->bufs.result + b0, false, sr,
                                sr ? dU + (size_t)(b0 / 2) * cap : nullptr, sr ? dZ + (size_t)(b0 / 2) * cap : nullptr,
-                               sr ? dSad + (size_t)(b0 / 2) * cap : nullptr);
+                               sr ? dSad + (size_t)(b0 / 2) * cap : nullptr, wsOff, cs);
                 if (rc != ORBFE_OK) return rc;
-                ORBFE_CUDA(ex, cudaEventRecord(ex->pipeEv[2 * k + 1], st));
+                ORBFE_CUDA(ex, cudaEventRecord(ex->pipeEv[2 * k + 1], cs));
+                if (k == nsub - 1) ex->lastWsOff = wsOff;
                 if (cap > 0) {
                     ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->outStream, ex->pipeEv[2 * k + 1], 0));
                     if (sr) {
@@ -640,6 +683,7 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
                                                    (size_t)mk * cap * 32, cudaMemcpyDeviceToHost, ex->outStream));
                 }
             }
+            if (lastAux >= 0) ORBFE_CUDA(ex, cudaStreamWaitEvent(st, ex->pipeEv[2 * lastAux + 1], 0));    // join
             ORBFE_CUDA(ex, cudaMemcpyAsync(res.data(), ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
             ORBFE_CUDA(ex, cudaMemcpyAsync(&errFlag, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
             ORBFE_CUDA(ex, cudaMemcpy2DAsync(ex->dCounts.p, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
@@ -647,11 +691,19 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             ORBFE_CUDA(ex, cudaStreamSynchronize(st));
             ORBFE_CUDA(ex, cudaStreamSynchronize(ex->outStream));
             ORBFE_CUDA(ex, cudaStreamSynchronize(ex->inStream));
+            if (getenv("ORBFE_PIPE_TRACE")) {
+                for (int k = 0; k < nsub; k++) {
+                    float a = 0, b = 0;
+                    cudaEventElapsedTime(&a, ex->ev[0], ex->pipeEv[2 * k]);
+                    cudaEventElapsedTime(&b, ex->ev[0], ex->pipeEv[2 * k + 1]);
+                    fprintf(stderr, "[orbfe pipe] stage %d: %d images, input landed %.3f ms, kernels done %.3f ms\n", k, sm[k], a, b);
+                }
+            }
             // the workspace holds the last stage only (stage accessors: orbfe_level_read ...)
-            ex->lastChunkBase = base + (nsub - 1) * kSub;
-            ex->lastChunkN = m - (nsub - 1) * kSub;
-            ex->lastKps = dK + (size_t)(nsub - 1) * kSub * cap;
-            ex->lastDesc = dD + (size_t)(nsub - 1) * kSub * cap * 32;
+            ex->lastChunkBase = base + sb[nsub - 1];
+            ex->lastChunkN = sm[nsub - 1];
+            ex->lastKps = dK + (size_t)sb[nsub - 1] * cap;
+            ex->lastDesc = dD + (size_t)sb[nsub - 1] * cap * 32;
         } else {
             cudaEventRecord(ex->ev[0], st);
             if (!inDev) {
@@ -693,6 +745,7 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             }
             ex->lastChunkBase = base;
             ex->lastChunkN = m;
+            ex->lastWsOff = 0;
             ex->lastKps = dK;
             ex->lastDesc = dD;
         }
@@ -780,7 +833,7 @@ int orbfe_level_read(orbfe_extractor* ex, int index, int level, int which, uint8
     ORBFE_CUDA(ex, cudaSetDevice(ex->device));
     const Geom& g = ex->geom;
     const LevelGeom& L = g.lv[level];
-    const int i = index - ex->lastChunkBase;
+    const int i = index - ex->lastChunkBase + ex->lastWsOff;
     const uint8_t* slab = (which == 2 ? ex->bufs.blur : ex->bufs.pyr) + (size_t)i * g.slabBytes + L.planeOff;
     if (which == 1) {
         ORBFE_CUDA(ex, cudaMemcpy2D(dst, dstride, slab + kXOff - kEdge, L.pitch, L.w + 2 * kEdge, L.h + 2 * kEdge, cudaMemcpyDeviceToHost));
@@ -800,7 +853,7 @@ int orbfe_level_candidates(orbfe_extractor* ex, int index, int level, int32_t* o
     ORBFE_CUDA(ex, cudaSetDevice(ex->device));
     const Geom& g = ex->geom;
     const LevelGeom& L = g.lv[level];
-    const int i = index - ex->lastChunkBase, nc = L.nCols * L.nRows;
+    const int i = index - ex->lastChunkBase + ex->lastWsOff, nc = L.nCols * L.nRows;
     if (nc == 0) return 0;
     std::vector<int> cnt(nc);
     std::vector<uint32_t> slots((size_t)nc * g.slotCap);
@@ -827,7 +880,7 @@ int orbfe_level_keypoints(orbfe_extractor* ex, int index, int level, orbfe_keypo
     if (rc != ORBFE_OK) return rc;
     ORBFE_CUDA(ex, cudaSetDevice(ex->device));
     const Geom& g = ex->geom;
-    const int i = index - ex->lastChunkBase;
+    const int i = index - ex->lastChunkBase + ex->lastWsOff;
     std::vector<int> lc(g.nlevels);
     ORBFE_CUDA(ex, cudaMemcpy(lc.data(), ex->bufs.levelCount + (size_t)i * g.nlevels, g.nlevels * 4, cudaMemcpyDeviceToHost));
     int off = 0;
