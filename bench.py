@@ -258,6 +258,58 @@ def stereo_leg(args, local, dev):
     return out
 
 
+def c4_leg(args, rank, world, local, dev, dist):
+    """BASELINE configs[3]: 3840x2160 frames, 5000 features, 12 levels, a batch of frames per GPU (frames are
+    independent: every rank extracts its own batch, no data-path collective; weak scaling).  Device-resident input and
+    output, CUDA-event time of the call, max over ranks; a 4K frame is 26.8 Mpixel of pyramid (24x a C2 image)."""
+    import torch
+    from orbslam3lib_b200 import ORBextractor, _lib, scenes
+    n, w, h, nf, nl = args.c4_frames, 3840, 2160, 5000, 12
+    base = scenes.make("texture", w, h, 1004 + rank)
+    imgs = np.empty((n, h, w), np.uint8)
+    for k in range(n):
+        imgs[k] = np.roll(base, 17 * k, axis=1)    # distinct frames without regenerating the scene
+    d_imgs = torch.from_numpy(imgs).to(dev)
+    ex = ORBextractor(nf, 1.2, nl, 20, 7, device=local)
+    ex.set_stream(torch.cuda.current_stream().cuda_stream)
+    cap = ex.max_keypoints
+    d_kps = torch.zeros((n, cap, 28), dtype=torch.uint8, device=dev)
+    d_desc = torch.zeros((n, cap, 32), dtype=torch.uint8, device=dev)
+    d_counts = torch.zeros(n, dtype=torch.int32, device=dev)
+    d_monos = torch.zeros(n, dtype=torch.int32, device=dev)
+    FL = _lib.IN_DEVICE | _lib.OUT_DEVICE
+    steps, ms, stages = 3, 0.0, {}
+    for it in range(steps + 2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        ex.extract_batch_raw(d_imgs, n, w, h, d_kps, d_desc, cap, d_counts, d_monos, flags=FL)
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            ms += e0.elapsed_time(e1)
+            for k, v in ex.stage_ms().items():
+                stages[k] = stages.get(k, 0.0) + v
+    ms /= steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    hbm_peak, _, _ = peaks()
+    algo = {"pyramid": 45164255, "fast": 26804551, "blur": 53609102}    # SURVEY.md 8d, bytes per 4K frame
+    rep = {}
+    for k, v in stages.items():
+        v /= steps
+        rep[k] = {"ms_per_step": round(v, 4)}
+        if k in algo and v > 0:
+            rep[k]["frac_hbm"] = round(algo[k] * n / (v * 1e-3) * 1e-9 / hbm_peak, 4)
+    return {"workload": "c4: %d frames 3840x2160 per GPU per step, 5000 features, 12 levels, %d GPU(s)" % (n, world),
+            "ms_per_step": ms, "frames_per_s": n * world / (ms * 1e-3), "scaling": "weak",
+            "keypoints_per_frame": float(d_counts.float().mean().item()), "stages": rep}
+
+
 def search_leg(args, local, dev):
     """SURVEY.md 8(f) rank 3: frame grid + ORBmatcher::SearchByProjection (ORBmatcher.cc:44-143) for a batch of frames
     (one CTA per frame), 2000 local-map points against ~1200 features per frame; everything resident in HBM.  The CPU
@@ -372,6 +424,7 @@ def main():
     ap.add_argument("--map-rows", type=int, default=1000000, help="rows of the map-scale kNN leg (configs[4]); 0 = skip")
     ap.add_argument("--map-steps", type=int, default=2)
     ap.add_argument("--latency-iters", type=int, default=300, help="stereo pairs of the per-frame latency leg (configs[2]); 0 = skip")
+    ap.add_argument("--c4-frames", type=int, default=32, help="4K frames per GPU per step of the configs[3] leg; 0 = skip")
     ap.add_argument("--search-frames", type=int, default=512, help="frames per step of the SearchByProjection leg; 0 = skip")
     ap.add_argument("--stereo-pairs", type=int, default=512, help="pairs per step of the ComputeStereoMatches leg; 0 = skip")
     args = ap.parse_args()
@@ -470,6 +523,11 @@ def main():
     clocks = sampler.stop()
 
     knn_map = map_knn_leg(args, rank, world, local, dev, dist, mt) if args.map_rows > 0 else None
+    c4 = None
+    if args.c4_frames > 0:
+        del d_imgs
+        torch.cuda.empty_cache()
+        c4 = c4_leg(args, rank, world, local, dev, dist)
     if world > 1:
         t = torch.tensor([float(pairs_per_step)], device=dev, dtype=torch.float64)
         dist.all_reduce(t)
@@ -536,6 +594,8 @@ def main():
     }
     if knn_map:
         line["knn_map"] = knn_map
+    if c4:
+        line["c4_4k"] = c4
     if args.latency_iters > 0:
         line["latency"] = latency_leg(args, local)
     if args.stereo_pairs > 0:

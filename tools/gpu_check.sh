@@ -1,7 +1,7 @@
 #!/bin/bash
 # GPU-box check used during kernel work: parity tests, then the C2 bench without the slow legs.
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-B="python bench.py --no-cpu-baseline --map-rows 0 --latency-iters 0 --stereo-pairs 0 --search-frames 0"
+B="python bench.py --no-cpu-baseline --map-rows 0 --latency-iters 0 --stereo-pairs 0 --search-frames 0 --c4-frames 0"
 $B 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
