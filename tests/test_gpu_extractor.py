@@ -176,3 +176,51 @@ def test_config_c3_stereo_500(oracle):
 def test_config_c4_4k_12_levels(oracle):
     n, ties = _compare(oracle, "texture", 3840, 2160, 1004, 5000, 12)
     assert n >= 5000
+
+
+def test_config_c2_full_batch_properties(oracle):
+    """BASELINE configs[1] at full size: 512 stereo pairs of 752x480, 1200 features, through the host (pipelined) path
+    and through the rectified-stereo entry point.  Size-independent properties: the batch is 8 distinct pairs repeated,
+    so every output must repeat with period 8 (batch position, pipeline stage and workspace slot must not matter); the
+    8 distinct pairs equal the oracle; a checksum over all descriptors equals 64 x the checksum of one period."""
+    P, w, h, nf = 512, 752, 480, 1200
+    distinct = 8
+    imgs = np.empty((P, 2, h, w), np.uint8)
+    for k in range(distinct):
+        imgs[k, 0] = scenes.make("texture", w, h, 9100 + k)
+        imgs[k, 1] = scenes.stereo_right_rectified(imgs[k, 0], 9100 + k)
+    for p in range(distinct, P):
+        imgs[p] = imgs[p % distinct]
+    ex = ORBextractor(nf, 1.2, 8, 20, 7)
+    mb, mbf = 0.11, 0.11 * 435.2
+    counts, kps, desc, u_right, depth = ex.extract_stereo_batch(imgs, mb, mbf)
+    assert counts.shape == (P, 2) and counts.min() > 1000
+    for p in range(distinct, P):
+        q = p % distinct
+        np.testing.assert_array_equal(counts[p], counts[q])
+        for e in range(2):
+            n = int(counts[q, e])
+            np.testing.assert_array_equal(kps[p, e, :n], kps[q, e, :n])
+            np.testing.assert_array_equal(desc[p, e, :n], desc[q, e, :n])
+        np.testing.assert_array_equal(u_right[p].view(np.uint32), u_right[q].view(np.uint32))
+        np.testing.assert_array_equal(depth[p].view(np.uint32), depth[q].view(np.uint32))
+    for q in range(distinct):
+        eL, eR = oracle.OracleExtractor(nf, 1.2, 8, 20, 7), oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+        _, kl, dl = eL(imgs[q, 0])
+        _, kr, dr = eR(imgs[q, 1])
+        assert (int(counts[q, 0]), int(counts[q, 1])) == (len(kl), len(kr))
+        np.testing.assert_array_equal(desc[q, 0, :len(kl)], dl)
+        np.testing.assert_array_equal(desc[q, 1, :len(kr)], dr)
+        np.testing.assert_array_equal(kps[q, 0, :len(kl)]["x"], kl["x"])
+        u, z, _, faults = oracle.stereo_matches(eL, eR, kl, dl, kr, dr, mb, mbf)
+        assert faults == 0
+        np.testing.assert_array_equal(u_right[q, :len(kl)].view(np.uint32), u.view(np.uint32))
+        np.testing.assert_array_equal(depth[q, :len(kl)].view(np.uint32), z.view(np.uint32))
+
+    def checksum(lo, hi):
+        s = 0
+        for p in range(lo, hi):
+            for e in range(2):
+                s += int(desc[p, e, :counts[p, e]].astype(np.uint64).sum())
+        return s
+    assert checksum(0, P) == (P // distinct) * checksum(0, distinct)
