@@ -88,6 +88,51 @@ __global__ void __launch_bounds__(256) pad_level0_kernel(const uint8_t* __restri
     *dst = make_uint4(o[0], o[1], o[2], o[3]);
 }
 
+// Level 0 for 16-byte aligned sources (the normal case), split so that no warp mixes the two paths:
+//   pad_interior_kernel  one aligned 128-bit copy per thread for the chunks that lie fully inside the image columns
+//                        (rows of the top / bottom frame are reflected rows: a scalar per thread row);
+//   pad_frame_kernel     the few chunks per row that touch the left / right frame, byte path, one thread per chunk.
+// grid interior: (ceil(nInterior / 64), ceil(rows / 4), n), block (64, 4); frame: (ceil(rows * nFrame / 256), n).
+__global__ void __launch_bounds__(256) pad_interior_kernel(const uint8_t* __restrict__ images, int stride,
+                                                           size_t imageStride, uint8_t* __restrict__ pyr,
+                                                           unsigned long long slabBytes, int h, int pitch, int cFirst,
+                                                           int nInterior) {
+    const int ci = blockIdx.x * 64 + threadIdx.x;
+    const int py = blockIdx.y * 4 + threadIdx.y;
+    if (py >= h + 2 * kEdge || ci >= nInterior) return;
+    const int c0 = 16 * (cFirst + ci);
+    const uint8_t* src = images + (size_t)blockIdx.z * imageStride + (size_t)reflect101(py - kEdge, h) * stride + (c0 - kXOff);
+    *reinterpret_cast<uint4*>(pyr + (size_t)blockIdx.z * slabBytes + (size_t)py * pitch + c0) =
+        __ldg(reinterpret_cast<const uint4*>(src));
+}
+
+__global__ void __launch_bounds__(256) pad_frame_kernel(const uint8_t* __restrict__ images, int stride, size_t imageStride,
+                                                        uint8_t* __restrict__ pyr, unsigned long long slabBytes, int w,
+                                                        int h, int pitch, int cFirst, int nInterior, int nchunks) {
+    const int nFrame = nchunks - nInterior;
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    const int py = t / nFrame;
+    if (py >= h + 2 * kEdge) return;
+    int cx = t - py * nFrame;                    // frame chunks: [0, cFirst) then [cFirst + nInterior, nchunks)
+    if (cx >= cFirst) cx += nInterior;
+    const int c0 = 16 * cx, x0 = c0 - kXOff;
+    const uint8_t* src = images + (size_t)blockIdx.y * imageStride + (size_t)reflect101(py - kEdge, h) * stride;
+    uint32_t o[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        uint32_t out = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const int x = x0 + 4 * q + b;
+            uint32_t v = 0;
+            if (x >= -kEdge && x < w + kEdge) v = __ldg(src + reflect101(x, w));
+            out |= v << (8 * b);
+        }
+        o[q] = out;
+    }
+    *reinterpret_cast<uint4*>(pyr + (size_t)blockIdx.y * slabBytes + (size_t)py * pitch + c0) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
 constexpr int RS_TW = 256;    // destination columns per tile
 constexpr int RS_C0 = 12;     // first plane column covered by tile 0 (kXOff - kEdge = 13, rounded down to a word)
 
@@ -220,9 +265,21 @@ int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size
         const LevelGeom& L = g.lv[l];
         if (l == 0) {
             const int chunks = (kXOff + L.w + kEdge + 15) / 16;
-            const dim3 grid((chunks + 63) / 64, (L.h + 2 * kEdge + 3) / 4, n);
-            pad_level0_kernel<<<grid, dim3(64, 4), 0, st>>>(images, stride, imageStride, pyr + L.planeOff, g.slabBytes,
-                                                            L.w, L.h, L.pitch, chunks);
+            const int rows = L.h + 2 * kEdge;
+            const int cFirst = kXOff / 16, nInterior = L.w / 16;    // chunks [cFirst, cFirst + nInterior) are pure image
+            const bool aligned = stride % 16 == 0 && imageStride % 16 == 0 && (reinterpret_cast<uintptr_t>(images) & 15) == 0;
+            if (aligned && nInterior > 0) {
+                pad_interior_kernel<<<dim3((nInterior + 63) / 64, (rows + 3) / 4, n), dim3(64, 4), 0, st>>>(
+                    images, stride, imageStride, pyr + L.planeOff, g.slabBytes, L.h, L.pitch, cFirst, nInterior);
+                const int nFrame = chunks - nInterior;
+                pad_frame_kernel<<<dim3((rows * nFrame + 255) / 256, n), 256, 0, st>>>(
+                    images, stride, imageStride, pyr + L.planeOff, g.slabBytes, L.w, L.h, L.pitch, cFirst, nInterior, chunks);
+                launches++;
+            } else {
+                const dim3 grid((chunks + 63) / 64, (rows + 3) / 4, n);
+                pad_level0_kernel<<<grid, dim3(64, 4), 0, st>>>(images, stride, imageStride, pyr + L.planeOff, g.slabBytes,
+                                                                L.w, L.h, L.pitch, chunks);
+            }
         } else {
             const LevelGeom& P = g.lv[l - 1];
             const ResizeDims& d = dims[l];
