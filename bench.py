@@ -561,13 +561,17 @@ def main():
     dom = max(hbm_stages, key=lambda k: per[k])
     launches_dom = NLEVELS if dom == "pyramid" else 1
     achieved = ALGO_BYTES[dom] * n / (per[dom] * 1e-3) * 1e-9
-    traffic, traffic_src = None, None
+    traffic, traffic_src, issue_pct = None, None, None
     tp = os.path.join(ROOT, "profiles", "kernel_traffic.json")
     if os.path.exists(tp):    # dram bytes per image from the committed ncu --set full capture (not measured in this run)
-        tj = json.load(open(tp))["dram_bytes_per_image"]
+        tall = json.load(open(tp))
+        tj = tall["dram_bytes_per_image"]
         ks = {"pyramid": ["pad_level0_kernel", "resize_tile_kernel"], "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"]}[dom]
         if all(k in tj for k in ks):
             traffic = sum(tj[k] for k in ks) * n / launches_dom
+            ip = tall.get("issue_active_pct", {})
+            if all(k in ip for k in ks):
+                issue_pct = max(ip[k] for k in ks)
             traffic_src = "profiles/kernel_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum per image x %d images / %d launches)" % (n, launches_dom)
     line = {
         "metric": "orb_frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -589,6 +593,7 @@ def main():
                      "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes_per_launch": ALGO_BYTES[dom] * n / launches_dom, "peak_source": peak_src,
                      "launches_per_step": launches_dom,
+                     "issue_active_pct_ncu": issue_pct,    # committed ncu capture: why the kernel sits below the HBM roof
                      "note": "algorithmic bytes per image x images per step / CUDA-event time of the stage"},
         "stages": stage_report,
     }
