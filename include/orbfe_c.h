@@ -180,6 +180,28 @@ int orbfe_search_by_projection_batch(orbfe_matcher* m, const orbfe_keypoint* key
                                      const orbfe_track_point* pts, const int32_t* npts, int pts_cap, int nframes, float th,
                                      int far_points, float th_far, float nn_ratio, int32_t* match, int32_t* owner,
                                      int32_t* nmatches, unsigned flags);
+/* The same call for stereo-camera frames (Nleft != -1, the Lynx fisheye rig): both branches of ORBmatcher.cc:44-214.
+ * A map point also carries its right-camera projection (mTrackProjXR/YR, mTrackViewCosR, mnTrackScaleLevelR, -1 = none);
+ * flags bit 3 = mbTrackInViewR. */
+typedef struct orbfe_track_point_stereo {
+    float proj_x, proj_y, proj_xr, proj_yr, view_cos, view_cos_r, track_depth;
+    int32_t level, level_r, flags;
+    uint8_t desc[32];
+} orbfe_track_point_stereo;
+/* Frame f: the n[f] features at [f*cap ...) are mvKeys (the first nleft[f]) followed by mvKeysRight, desc / occupied
+ * likewise (= rows of mDescriptors / slots of F.mvpMapPoints); left_to_right[f*cap + i] = mvLeftToRightMatch[i]
+ * (i < nleft[f]), right_to_left[f*cap + j] = mvRightToLeftMatch[j] (j < n[f] - nleft[f]), -1 = no partner.
+ * match_left / match_right[f*pts_cap + i]: feature found for point i by the left / right search (right: index into the
+ * right features) or -1; owner[f*cap + slot]: last point assigned to that slot of mvpMapPoints or -1; nmatches[f]: the
+ * return value.  bounds / scale_factors are host memory; the rest follows ORBFE_IN_DEVICE / ORBFE_OUT_DEVICE. */
+int orbfe_search_by_projection_stereo_batch(orbfe_matcher* m, const orbfe_keypoint* keys, const uint8_t* desc,
+                                            const uint8_t* occupied, const int32_t* n, const int32_t* nleft,
+                                            const int32_t* left_to_right, const int32_t* right_to_left, int cap,
+                                            const float bounds[4], const float* scale_factors, int nlevels,
+                                            const orbfe_track_point_stereo* pts, const int32_t* npts, int pts_cap,
+                                            int nframes, float th, int far_points, float th_far, float nn_ratio,
+                                            int32_t* match_left, int32_t* match_right, int32_t* owner, int32_t* nmatches,
+                                            unsigned flags);
 /* Frame::UndistortKeyPoints (Frame.cc:763-796): mvKeysUn = mvKeys with the positions passed through
  * cv::undistortPoints(pts, pts, K, mDistCoef, Mat(), mK) (OpenCV 4.x: 5 fixed-point iterations in double); K = (fx, fy,
  * cx, cy) of mK, dist_coef = k1, k2, p1, p2[, k3] (ndist 4 or 5, up to OpenCV's 14); dist_coef[0] == 0 copies the

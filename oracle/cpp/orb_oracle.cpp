@@ -1067,6 +1067,164 @@ void orc_undistort_keypoints(const orc_keypoint* keys, int n, float fx, float fy
     }
 }
 
+// ---- the same loop for stereo-camera frames (Nleft != -1: the Lynx fisheye rig), ORBmatcher.cc:44-214 -------------------
+// keys / desc / occupied hold the N = Nleft + Nright features, left first (mvKeys, then mvKeysRight; mDescriptors rows;
+// F.mvpMapPoints slots).  Left search on mGrid (:59-143, no mvuRight gate since Nleft != -1), its partner assignment
+// through mvLeftToRightMatch (:130-134); a ratio rejection there skips the right search (:126-127 `continue`); right
+// search on mGridRight with mTrackProjXR/YR, mnTrackScaleLevelR, mTrackViewCosR — the radius is NOT scaled by th there
+// (:148-151) — and the partner assignment through mvRightToLeftMatch (:198-202).
+int orc_search_by_projection_stereo(const orc_keypoint* keys, const uint8_t* desc, const uint8_t* occupied, int n,
+                                    int nleft, const int32_t* leftToRight, const int32_t* rightToLeft, float mnMinX,
+                                    float mnMinY, float mnMaxX, float mnMaxY, const float* mvScaleFactors,
+                                    const orc_track_point_stereo* pts, int npts, float th, int bFarPoints,
+                                    float thFarPoints, float mfNNratio, int32_t* matchL, int32_t* matchR, int32_t* owner) {
+    const int TH_HIGH = 100;
+    const float gwInv = static_cast<float>(GRID_COLS) / (mnMaxX - mnMinX);
+    const float ghInv = static_cast<float>(GRID_ROWS) / (mnMaxY - mnMinY);
+    static thread_local std::vector<size_t> mGrid[GRID_COLS][GRID_ROWS], mGridRight[GRID_COLS][GRID_ROWS];
+    for (int i = 0; i < GRID_COLS; i++)
+        for (int j = 0; j < GRID_ROWS; j++) {
+            mGrid[i][j].clear();
+            mGridRight[i][j].clear();
+        }
+    for (int i = 0; i < n; i++) {    // AssignFeaturesToGrid, Nleft != -1 (Frame.cc:420-434)
+        const orc_keypoint& kp = keys[i];
+        const int posX = (int)std::round((kp.x - mnMinX) * gwInv);
+        const int posY = (int)std::round((kp.y - mnMinY) * ghInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        if (i < nleft) mGrid[posX][posY].push_back(i);
+        else mGridRight[posX][posY].push_back(i - nleft);
+    }
+    std::vector<uint8_t> blocked(n, 0);
+    for (int i = 0; i < n; i++) {
+        blocked[i] = occupied ? occupied[i] : 0;
+        if (owner) owner[i] = -1;
+    }
+    auto assign = [&](int slot, int iMP, bool obs) {    // F.mvpMapPoints[slot] = pMP
+        if (owner) owner[slot] = iMP;
+        blocked[slot] = obs ? 1 : 0;
+    };
+    auto area = [&](float x, float y, float r, int minLevel, int maxLevel, bool bRight, std::vector<size_t>& out) {
+        out.clear();
+        const float factorX = r, factorY = r;
+        const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * gwInv));
+        if (nMinCellX >= GRID_COLS) return;
+        const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * gwInv));
+        if (nMaxCellX < 0) return;
+        const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * ghInv));
+        if (nMinCellY >= GRID_ROWS) return;
+        const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * ghInv));
+        if (nMaxCellY < 0) return;
+        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+        for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+            for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                const std::vector<size_t>& vCell = (!bRight) ? mGrid[ix][iy] : mGridRight[ix][iy];
+                for (size_t j = 0; j < vCell.size(); j++) {
+                    const orc_keypoint& kpUn = (!bRight) ? keys[vCell[j]] : keys[nleft + vCell[j]];
+                    if (bCheckLevels) {
+                        if (kpUn.octave < minLevel) continue;
+                        if (maxLevel >= 0)
+                            if (kpUn.octave > maxLevel) continue;
+                    }
+                    const float distx = kpUn.x - x;
+                    const float disty = kpUn.y - y;
+                    if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) out.push_back(vCell[j]);
+                }
+            }
+    };
+    int nmatches = 0;
+    const bool bFactor = th != 1.0;
+    std::vector<size_t> vIndices;
+    for (int iMP = 0; iMP < npts; iMP++) {
+        const orc_track_point_stereo& mp = pts[iMP];
+        matchL[iMP] = -1;
+        matchR[iMP] = -1;
+        const bool inView = mp.flags & 1, inViewR = mp.flags & 8, obs = mp.flags & 4;
+        if (!inView && !inViewR) continue;
+        if (bFarPoints && mp.track_depth > thFarPoints) continue;
+        if (mp.flags & 2) continue;
+        uint64_t a[4];
+        std::memcpy(a, mp.desc, 32);
+        bool skipRight = false;
+        if (inView) {
+            const int nPredictedLevel = mp.level;
+            float r = mp.view_cos > 0.998 ? 2.5 : 4.0;
+            if (bFactor) r *= th;
+            area(mp.proj_x, mp.proj_y, r * mvScaleFactors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel, false, vIndices);
+            if (!vIndices.empty()) {
+                int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+                for (size_t k = 0; k < vIndices.size(); k++) {
+                    const size_t idx = vIndices[k];
+                    if (blocked[idx]) continue;
+                    uint64_t b[4];
+                    std::memcpy(b, desc + idx * 32, 32);
+                    const int dist = hamming256(a, b);
+                    if (dist < bestDist) {
+                        bestDist2 = bestDist;
+                        bestDist = dist;
+                        bestLevel2 = bestLevel;
+                        bestLevel = keys[idx].octave;
+                        bestIdx = (int)idx;
+                    } else if (dist < bestDist2) {
+                        bestLevel2 = keys[idx].octave;
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist <= TH_HIGH) {
+                    if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) skipRight = true;    // `continue`
+                    else if (bestLevel != bestLevel2 || bestDist <= mfNNratio * bestDist2) {
+                        matchL[iMP] = bestIdx;
+                        assign(bestIdx, iMP, obs);
+                        if (leftToRight[bestIdx] != -1) {
+                            assign(leftToRight[bestIdx] + nleft, iMP, obs);
+                            nmatches++;
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+        }
+        if (skipRight) continue;
+        if (inViewR) {
+            const int nPredictedLevel = mp.level_r;
+            if (nPredictedLevel != -1) {
+                float r = mp.view_cos_r > 0.998 ? 2.5 : 4.0;
+                area(mp.proj_xr, mp.proj_yr, r * mvScaleFactors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel, true, vIndices);
+                if (vIndices.empty()) continue;
+                int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+                for (size_t k = 0; k < vIndices.size(); k++) {
+                    const size_t idx = vIndices[k];
+                    if (blocked[idx + nleft]) continue;
+                    uint64_t b[4];
+                    std::memcpy(b, desc + (idx + nleft) * 32, 32);
+                    const int dist = hamming256(a, b);
+                    if (dist < bestDist) {
+                        bestDist2 = bestDist;
+                        bestDist = dist;
+                        bestLevel2 = bestLevel;
+                        bestLevel = keys[nleft + idx].octave;
+                        bestIdx = (int)idx;
+                    } else if (dist < bestDist2) {
+                        bestLevel2 = keys[nleft + idx].octave;
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist <= TH_HIGH) {
+                    if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+                    if (rightToLeft[bestIdx] != -1) {
+                        assign(rightToLeft[bestIdx], iMP, obs);
+                        nmatches++;
+                    }
+                    matchR[iMP] = bestIdx;
+                    assign(bestIdx + nleft, iMP, obs);
+                    nmatches++;
+                }
+            }
+        }
+    }
+    return nmatches;
+}
+
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

@@ -100,6 +100,23 @@ int orc_search_by_projection(const orc_keypoint* keysUn, const uint8_t* desc, co
 void orc_undistort_keypoints(const orc_keypoint* keys, int n, float fx, float fy, float cx, float cy, const float* dist,
                              int ndist, orc_keypoint* keysUn);
 
+/* Stereo-camera frames (Nleft != -1): the map point also carries its right-camera projection (mTrackProjXR/YR,
+ * mTrackViewCosR, mnTrackScaleLevelR); flags bit 3 = mbTrackInViewR. */
+typedef struct {
+    float proj_x, proj_y, proj_xr, proj_yr, view_cos, view_cos_r, track_depth;
+    int32_t level, level_r, flags;
+    uint8_t desc[32];
+} orc_track_point_stereo;
+/* ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) for Nleft != -1 (ORBmatcher.cc:44-214).
+ * keys/desc/occupied: N features, the nleft left ones first; leftToRight[nleft] / rightToLeft[n - nleft]:
+ * mvLeftToRightMatch / mvRightToLeftMatch (-1 = none).  matchL / matchR[npts]: feature found by the left / right
+ * search (right: index into the right features) or -1; owner[n]: last point assigned to every slot of mvpMapPoints. */
+int orc_search_by_projection_stereo(const orc_keypoint* keys, const uint8_t* desc, const uint8_t* occupied, int n,
+                                    int nleft, const int32_t* leftToRight, const int32_t* rightToLeft, float mnMinX,
+                                    float mnMinY, float mnMaxX, float mnMaxY, const float* mvScaleFactors,
+                                    const orc_track_point_stereo* pts, int npts, float th, int bFarPoints,
+                                    float thFarPoints, float mfNNratio, int32_t* matchL, int32_t* matchR, int32_t* owner);
+
 int orc_hardware_threads(void);
 #ifdef __cplusplus
 }

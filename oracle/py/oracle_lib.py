@@ -17,6 +17,11 @@ TRACK_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<f4")
                         ("track_depth", "<f4"), ("level", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
 assert TRACK_DTYPE.itemsize == 60
 
+TRACK_STEREO_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<f4"), ("proj_yr", "<f4"),
+                               ("view_cos", "<f4"), ("view_cos_r", "<f4"), ("track_depth", "<f4"), ("level", "<i4"),
+                               ("level_r", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
+assert TRACK_STEREO_DTYPE.itemsize == 72
+
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
                      ("octave", "<i4"), ("class_id", "<i4")])
 assert KP_DTYPE.itemsize == 28
@@ -71,6 +76,11 @@ def lib():
                                         C.c_void_p, C.c_void_p, C.c_int]
         L.orc_extract_batch.restype = C.c_int
         L.orc_hardware_threads.restype = C.c_int
+        L.orc_search_by_projection_stereo.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                                      C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p,
+                                                      C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float,
+                                                      C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_search_by_projection_stereo.restype = C.c_int
         L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p,
                                               C.c_int, C.c_void_p]
         L.orc_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
@@ -272,6 +282,31 @@ def search_by_projection(keys_un, desc, u_right, occupied, bounds, scale_factors
                                         _p(p), p.shape[0], float(th), int(bool(far_points)), float(th_far),
                                         float(nn_ratio), _p(match), _p(owner))
     return match, owner, int(nm)
+
+
+def search_by_projection_stereo(keys, desc, occupied, nleft, left_to_right, right_to_left, bounds, scale_factors, pts,
+                                th=1.0, far_points=False, th_far=0.0, nn_ratio=0.8):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, ...) for stereo-camera frames (Nleft != -1, ORBmatcher.cc:44-214).
+    keys / desc: the N features, left ones first; pts: TRACK_STEREO_DTYPE.
+    -> (match_left (npts,), match_right (npts,), owner (N,), nmatches)"""
+    k = np.ascontiguousarray(keys, KP_DTYPE)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = k.shape[0]
+    oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    ltr = np.ascontiguousarray(left_to_right, np.int32)
+    rtl = np.ascontiguousarray(right_to_left, np.int32)
+    assert ltr.shape[0] == nleft and rtl.shape[0] == n - nleft
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    p = np.ascontiguousarray(pts, TRACK_STEREO_DTYPE)
+    ml = np.empty(p.shape[0], np.int32)
+    mr = np.empty(p.shape[0], np.int32)
+    owner = np.empty(n, np.int32)
+    nm = lib().orc_search_by_projection_stereo(_p(k), _p(d), None if oc is None else _p(oc), n, int(nleft), _p(ltr),
+                                               _p(rtl), float(bounds[0]), float(bounds[1]), float(bounds[2]),
+                                               float(bounds[3]), _p(sf), _p(p), p.shape[0], float(th),
+                                               int(bool(far_points)), float(th_far), float(nn_ratio), _p(ml), _p(mr),
+                                               _p(owner))
+    return ml, mr, owner, int(nm)
 
 
 def undistort_keypoints(kps, fx, fy, cx, cy, dist):

@@ -75,6 +75,9 @@ SYMBOLS = {
     "orbfe_knn2_batch": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _u]),
     "orbfe_ratio_test": (_i, [_vp, _vp, _i64, C.c_double, _vp]),
     "orbfe_matcher_last_ms": (_i, [_vp, _vp, _vp]),
+    "orbfe_search_by_projection_stereo_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp,
+                                                     _i, _i, C.c_float, _i, C.c_float, C.c_float, _vp, _vp, _vp, _vp,
+                                                     _u]),
     "orbfe_undistort_keypoints": (_i, [_vp, _vp, _i64, C.c_float, C.c_float, C.c_float, C.c_float, _vp, _i, _vp, _u]),
     "orbfe_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, C.c_float, _i, C.c_float,
                                         C.c_float, _vp, _vp, _vp]),

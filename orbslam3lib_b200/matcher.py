@@ -7,7 +7,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import KP_DTYPE, OrbfeError, ptr
-from .scenes import TRACK_DTYPE
+from .scenes import TRACK_DTYPE, TRACK_STEREO_DTYPE
 
 
 class BFMatcher:
@@ -134,6 +134,31 @@ class ORBmatcher:
             self._bf._h, ptr(keys_un), ptr(desc), ptr(u_right), ptr(occupied), ptr(n), int(cap), ptr(b), ptr(sf),
             sf.shape[0], ptr(pts), ptr(npts), int(pts_cap), int(nframes), float(th), int(bool(bFarPoints)),
             float(thFarPoints), self.mfNNratio, ptr(match), ptr(owner), ptr(nmatches), int(flags)))
+
+    def SearchByProjectionStereo(self, keys, desc, nleft, left_to_right, right_to_left, bounds, scale_factors,
+                                 track_points, th=1.0, bFarPoints=False, thFarPoints=50.0, occupied=None):
+        """The same call on a stereo-camera frame (Nleft != -1, ORBmatcher.cc:44-214): keys / desc = mvKeys followed by
+        mvKeysRight, track_points: TRACK_STEREO_DTYPE -> (nmatches, match_left, match_right, owner (N,))."""
+        k = np.ascontiguousarray(keys, KP_DTYPE)
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = k.shape[0]
+        oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        ltr = np.full(max(n, 1), -1, np.int32)
+        rtl = np.full(max(n, 1), -1, np.int32)
+        ltr[:nleft] = left_to_right
+        rtl[:n - nleft] = right_to_left
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        p = np.ascontiguousarray(track_points, TRACK_STEREO_DTYPE)
+        ml = np.full(p.shape[0], -1, np.int32)
+        mr = np.full(p.shape[0], -1, np.int32)
+        owner = np.full(n, -1, np.int32)
+        nn, nl, npp, nm = (np.array([v], np.int32) for v in (n, nleft, p.shape[0], 0))
+        self._bf._check(_lib.lib().orbfe_search_by_projection_stereo_batch(
+            self._bf._h, ptr(k), ptr(d), ptr(oc), ptr(nn), ptr(nl), ptr(ltr), ptr(rtl), n, ptr(b), ptr(sf), sf.shape[0],
+            ptr(p), ptr(npp), p.shape[0], 1, float(th), int(bool(bFarPoints)), float(thFarPoints), self.mfNNratio, ptr(ml),
+            ptr(mr), ptr(owner), ptr(nm), 0))
+        return int(nm[0]), ml, mr, owner
 
     def UndistortKeyPoints(self, keys, K, dist_coef):
         """Frame::UndistortKeyPoints (Frame.cc:763-796): keys (KP_DTYPE), K = 3x3 mK or (fx, fy, cx, cy), mDistCoef ->

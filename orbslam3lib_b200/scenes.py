@@ -140,6 +140,75 @@ def track_points(kps, desc, u_right, nlevels, npts, seed, jitter=3.0, max_flips=
     return pts
 
 
+TRACK_STEREO_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<f4"), ("proj_yr", "<f4"),
+                               ("view_cos", "<f4"), ("view_cos_r", "<f4"), ("track_depth", "<f4"), ("level", "<i4"),
+                               ("level_r", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
+
+
+def stereo_camera_frame(kps_l, desc_l, kps_r, desc_r, seed, max_dist=60):
+    """A stereo-camera frame (Nleft != -1) for SearchByProjection: features = left then right, and a consistent pair of
+    mvLeftToRightMatch / mvRightToLeftMatch tables (mutual nearest descriptors below max_dist; -1 elsewhere).
+    -> (keys (N,), desc (N, 32), nleft, left_to_right, right_to_left)"""
+    nl, nr = len(kps_l), len(kps_r)
+    keys = np.concatenate([kps_l, kps_r])
+    desc = np.concatenate([desc_l, desc_r])
+    ltr = np.full(nl, -1, np.int32)
+    rtl = np.full(nr, -1, np.int32)
+    if nl and nr:
+        bl = np.unpackbits(desc_l, axis=1).astype(np.int16)
+        br = np.unpackbits(desc_r, axis=1).astype(np.int16)
+        dist = bl.sum(1)[:, None] + br.sum(1)[None, :] - 2 * (bl @ br.T)
+        best_r = dist.argmin(1)
+        best_l = dist.argmin(0)
+        for i in range(nl):
+            j = int(best_r[i])
+            if best_l[j] == i and dist[i, j] < max_dist:
+                ltr[i], rtl[j] = j, i
+    return keys, desc, nl, ltr, rtl
+
+
+def track_points_stereo(keys, desc, nleft, ltr, nlevels, npts, seed, jitter=3.0, max_flips=30, dup_frac=0.2):
+    """Local-map points for the stereo-camera branch: point i re-observes left feature f (projection = its position +
+    jitter, level = octave or + 1) and, in the right camera, f's stereo partner when it has one (else the left position
+    shifted by 12 px); flags: bit 0 in view left, bit 3 in view right, bit 1 bad, bit 2 has observations."""
+    pts = np.zeros(npts, TRACK_STEREO_DTYPE)
+    if nleft == 0 or npts == 0:
+        return pts
+    r = rand_u32(npts * 10, seed).reshape(10, npts)
+    feat = (r[0] % np.uint32(nleft)).astype(np.int64)
+    ndup = int(npts * dup_frac)
+    if ndup > 0 and npts > 1:
+        dst = (rand_u32(ndup, seed + 1) % np.uint32(npts - 1)).astype(np.int64) + 1
+        feat[dst] = feat[dst - 1]
+    u = lambda a: (a.astype(np.float64) / 4294967296.0)    # noqa: E731
+    part = ltr[feat]
+    has = part >= 0
+    pr = np.where(has, part + nleft, feat)
+    pts["proj_x"] = (keys["x"][feat] + (u(r[1]) * 2 - 1) * jitter).astype(np.float32)
+    pts["proj_y"] = (keys["y"][feat] + (u(r[2]) * 2 - 1) * jitter).astype(np.float32)
+    pts["proj_xr"] = (keys["x"][pr] - np.where(has, 0.0, 12.0) + (u(r[3]) * 2 - 1) * jitter).astype(np.float32)
+    pts["proj_yr"] = (keys["y"][pr] + (u(r[8]) * 2 - 1) * jitter).astype(np.float32)
+    pts["view_cos"] = (0.9975 + u(r[4]) * 0.0025).astype(np.float32)
+    pts["view_cos_r"] = (0.9975 + u(r[9]) * 0.0025).astype(np.float32)
+    pts["track_depth"] = (1.0 + u(r[5]) * 39.0).astype(np.float32)
+    pts["level"] = np.minimum(keys["octave"][feat] + (r[6] & 1).astype(np.int32), nlevels - 1)
+    lr = np.minimum(keys["octave"][pr] + ((r[6] >> 1) & 1).astype(np.int32), nlevels - 1)
+    sel = r[7] % np.uint32(100)
+    pts["level_r"] = np.where(sel % 17 == 0, -1, lr)
+    in_l = np.where(sel % 11 == 0, 0, 1)
+    in_r = np.where(sel % 7 == 0, 0, 8)
+    pts["flags"] = in_l | in_r | np.where((sel >= 4) & (sel < 7), 2, 0) | np.where(sel < 93, 4, 0)
+    d = desc[feat].copy()
+    nflip = (rand_u32(npts, seed + 2) % np.uint32(max_flips + 1)).astype(np.int64)
+    pos = (rand_u32(npts * max_flips, seed + 3) % np.uint32(256)).reshape(npts, max_flips).astype(np.int64)
+    for k in range(max_flips):
+        rows = np.nonzero(nflip > k)[0]
+        p = pos[rows, k]
+        d[rows, p >> 3] ^= (1 << (p & 7)).astype(np.uint8)
+    pts["desc"] = d
+    return pts
+
+
 SCENES = {"noise": noise, "checker": checker, "texture": texture, "flat_blobs": flat_blobs}
 
 

@@ -106,3 +106,72 @@ def test_search_batch_device_and_edges(oracle):
         np.testing.assert_array_equal(match[f, :npp[f]], singles[f][1])
         assert (match[f, npp[f]:] == -1).all()
         np.testing.assert_array_equal(owner[f, :nn[f]], singles[f][2])
+
+
+def _stereo_frame(oracle, kind, w, h, seed, nf):
+    left = scenes.make(kind, w, h, seed)
+    right = scenes.stereo_right_rectified(left, seed)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _, kl, dl = ex(left)
+    _, kr, dr = ex(right)
+    return scenes.stereo_camera_frame(kl, dl, kr, dr, seed) + (ex.scale,)
+
+
+@pytest.mark.parametrize("kind,w,h,seed,nf,npts,th,ratio", [
+    ("texture", 752, 480, 8100, 1200, 2500, 1.0, 0.8),
+    ("texture", 640, 480, 8101, 1000, 2000, 3.0, 0.8),
+    ("texture", 640, 400, 8102, 1000, 1500, 10.0, 0.9),
+    ("checker", 640, 480, 8103, 1000, 2000, 1.0, 0.6),
+    ("noise", 320, 240, 8104, 500, 800, 2.0, 0.8),
+])
+def test_search_by_projection_stereo_camera_matches_oracle(oracle, kind, w, h, seed, nf, npts, th, ratio):
+    """Nleft != -1 (ORBmatcher.cc:44-214): left and right searches, partner assignments, the continue past the right
+    search, slots freed by points without observations."""
+    keys, desc, nleft, ltr, rtl, scale = _stereo_frame(oracle, kind, w, h, seed, nf)
+    pts = scenes.track_points_stereo(keys, desc, nleft, ltr, 8, npts, seed, dup_frac=0.3)
+    occupied = (scenes.rand_u32(len(keys), seed + 9) % 8 == 0).astype(np.uint8)
+    bounds = (0.0, 0.0, float(w), float(h))
+    rl, rr, ro, rn = oracle.search_by_projection_stereo(keys, desc, occupied, nleft, ltr, rtl, bounds, scale, pts, th=th,
+                                                        nn_ratio=ratio)
+    n, ml, mr, owner = ORBmatcher(ratio).SearchByProjectionStereo(keys, desc, nleft, ltr, rtl, bounds, scale, pts, th=th,
+                                                                  occupied=occupied)
+    np.testing.assert_array_equal(ml, rl)
+    np.testing.assert_array_equal(mr, rr)
+    np.testing.assert_array_equal(owner, ro)
+    assert n == rn
+    if kind == "texture":
+        assert (ml >= 0).sum() > npts // 5 and (mr >= 0).sum() > 20
+
+
+def test_search_stereo_camera_contended(oracle):
+    """16 copies of every point, one in five without observations: conflicts in every round, slots freed and retaken."""
+    keys, desc, nleft, ltr, rtl, scale = _stereo_frame(oracle, "texture", 320, 240, 8120, 400)
+    base = scenes.track_points_stereo(keys, desc, nleft, ltr, 8, 40, 8120, dup_frac=0.0)
+    pts = np.repeat(base, 16)
+    pts["flags"] = np.where(np.arange(len(pts)) % 5 == 0, 9, 13)
+    bounds = (0.0, 0.0, 320.0, 240.0)
+    rl, rr, ro, rn = oracle.search_by_projection_stereo(keys, desc, None, nleft, ltr, rtl, bounds, scale, pts, th=4.0,
+                                                        nn_ratio=0.9)
+    n, ml, mr, owner = ORBmatcher(0.9).SearchByProjectionStereo(keys, desc, nleft, ltr, rtl, bounds, scale, pts, th=4.0)
+    np.testing.assert_array_equal(ml, rl)
+    np.testing.assert_array_equal(mr, rr)
+    np.testing.assert_array_equal(owner, ro)
+    assert n == rn
+
+
+def test_search_stereo_camera_edges(oracle):
+    keys, desc, nleft, ltr, rtl, scale = _stereo_frame(oracle, "texture", 320, 240, 8130, 300)
+    m = ORBmatcher(0.8)
+    n, ml, mr, owner = m.SearchByProjectionStereo(keys, desc, nleft, ltr, rtl, (0, 0, 320, 240), scale,
+                                                  np.zeros(0, scenes.TRACK_STEREO_DTYPE))
+    assert n == 0 and len(ml) == 0 and (owner == -1).all()
+    # no right features at all (Nleft == N): the right search finds nothing, the left one still works
+    pts = scenes.track_points_stereo(keys[:nleft], desc[:nleft], nleft, np.full(nleft, -1, np.int32), 8, 300, 5)
+    none_r = np.zeros(0, np.int32)
+    rl, rr, ro, rn = oracle.search_by_projection_stereo(keys[:nleft], desc[:nleft], None, nleft, np.full(nleft, -1, np.int32),
+                                                        none_r, (0, 0, 320, 240), scale, pts, th=2.0, nn_ratio=0.8)
+    n, ml, mr, owner = m.SearchByProjectionStereo(keys[:nleft], desc[:nleft], nleft, np.full(nleft, -1, np.int32), none_r,
+                                                  (0, 0, 320, 240), scale, pts, th=2.0)
+    np.testing.assert_array_equal(ml, rl)
+    assert (mr == -1).all() and (rr == -1).all() and n == rn
+    np.testing.assert_array_equal(owner, ro)

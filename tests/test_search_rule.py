@@ -120,3 +120,125 @@ def test_oracle_search_by_projection_vs_python(oracle):
         assert nm == int((m >= 0).sum()) and nm > 100
         for j in np.unique(m[m >= 0]):
             assert owner[j] == np.nonzero(m == j)[0].max()
+
+
+def _py_search_stereo(keys, desc, nleft, ltr, rtl, bounds, scale, pts, th, nn_ratio):
+    """literal restatement of ORBmatcher.cc:44-214 for Nleft != -1 (both branches), numpy float32."""
+    f32 = np.float32
+    min_x, min_y, max_x, max_y = [f32(v) for v in bounds]
+    gw, gh = f32(f32(64) / f32(max_x - min_x)), f32(f32(48) / f32(max_y - min_y))
+
+    def c_round(v):
+        v = float(v)
+        return int(math.floor(v + 0.5) if v >= 0 else math.ceil(v - 0.5))
+    grid, grid_r = {}, {}
+    for i in range(len(keys)):
+        px = c_round(f32(f32(keys["x"][i] - min_x) * gw))
+        py = c_round(f32(f32(keys["y"][i] - min_y) * gh))
+        if 0 <= px < 64 and 0 <= py < 48:
+            if i < nleft:
+                grid.setdefault((px, py), []).append(i)
+            else:
+                grid_r.setdefault((px, py), []).append(i - nleft)
+    bits = np.unpackbits(desc, axis=1)
+    blocked = np.zeros(len(keys), bool)
+    ml = np.full(len(pts), -1, np.int32)
+    mr = np.full(len(pts), -1, np.int32)
+    nmatches = 0
+
+    def area(x, y, rr, lvl, right):
+        cx0 = max(0, int(math.floor(f32(f32(f32(x - min_x) - rr) * gw))))
+        cx1 = min(63, int(math.ceil(f32(f32(f32(x - min_x) + rr) * gw))))
+        cy0 = max(0, int(math.floor(f32(f32(f32(y - min_y) - rr) * gh))))
+        cy1 = min(47, int(math.ceil(f32(f32(f32(y - min_y) + rr) * gh))))
+        out = []
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            return out
+        g, off = (grid_r, nleft) if right else (grid, 0)
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for j in g.get((ix, iy), []):
+                    o = int(keys["octave"][off + j])
+                    if o < lvl - 1 or o > lvl:
+                        continue
+                    if abs(f32(keys["x"][off + j] - x)) < rr and abs(f32(keys["y"][off + j] - y)) < rr:
+                        out.append(j)
+        return out
+
+    def best_of(cand, off, mbits):
+        bd, bl, bd2, bl2, bi = 256, -1, 256, -1, -1
+        for j in cand:
+            if blocked[off + j]:
+                continue
+            d = int(np.count_nonzero(mbits != bits[off + j]))
+            if d < bd:
+                bd2, bd, bl2, bl, bi = bd, d, bl, int(keys["octave"][off + j]), j
+            elif d < bd2:
+                bl2, bd2 = int(keys["octave"][off + j]), d
+        return bd, bl, bd2, bl2, bi
+    for ip in range(len(pts)):
+        mp = pts[ip]
+        fl = int(mp["flags"])
+        if not (fl & 1) and not (fl & 8):
+            continue
+        if fl & 2:
+            continue
+        obs = bool(fl & 4)
+        mbits = np.unpackbits(mp["desc"])
+        skip_right = False
+        if fl & 1:
+            lvl = int(mp["level"])
+            r = f32(2.5) if float(mp["view_cos"]) > 0.998 else f32(4.0)
+            if th != 1.0:
+                r = f32(r * f32(th))
+            cand = area(f32(mp["proj_x"]), f32(mp["proj_y"]), f32(r * f32(scale[lvl])), lvl, False)
+            if cand:
+                bd, bl, bd2, bl2, bi = best_of(cand, 0, mbits)
+                if bd <= 100:
+                    lim = f32(f32(nn_ratio) * f32(bd2))
+                    if bl == bl2 and f32(bd) > lim:
+                        skip_right = True
+                    elif bl != bl2 or f32(bd) <= lim:
+                        ml[ip] = bi
+                        blocked[bi] = obs
+                        if ltr[bi] != -1:
+                            blocked[ltr[bi] + nleft] = obs
+                            nmatches += 1
+                        nmatches += 1
+        if skip_right:
+            continue
+        if fl & 8:
+            lvl = int(mp["level_r"])
+            if lvl != -1:
+                r = f32(2.5) if float(mp["view_cos_r"]) > 0.998 else f32(4.0)
+                cand = area(f32(mp["proj_xr"]), f32(mp["proj_yr"]), f32(r * f32(scale[lvl])), lvl, True)
+                if not cand:
+                    continue
+                bd, bl, bd2, bl2, bi = best_of(cand, nleft, mbits)
+                if bd <= 100:
+                    if bl == bl2 and f32(bd) > f32(f32(nn_ratio) * f32(bd2)):
+                        continue
+                    if rtl[bi] != -1:
+                        blocked[rtl[bi]] = obs
+                        nmatches += 1
+                    mr[ip] = bi
+                    blocked[bi + nleft] = obs
+                    nmatches += 1
+    return ml, mr, nmatches
+
+
+def test_oracle_search_by_projection_stereo_vs_python(oracle):
+    for seed, th in ((21, 1.0), (22, 4.0)):
+        left = scenes.make("texture", 320, 240, 6100 + seed)
+        right = scenes.stereo_right_rectified(left, 6100 + seed)
+        ex = oracle.OracleExtractor(400, 1.2, 8, 20, 7)
+        _, kl, dl = ex(left)
+        _, kr, dr = ex(right)
+        keys, desc, nleft, ltr, rtl = scenes.stereo_camera_frame(kl, dl, kr, dr, seed)
+        pts = scenes.track_points_stereo(keys, desc, nleft, ltr, 8, 500, seed)
+        ml, mr, owner, nm = oracle.search_by_projection_stereo(keys, desc, None, nleft, ltr, rtl, (0, 0, 320, 240), ex.scale,
+                                                               pts, th=th, nn_ratio=0.8)
+        rl, rr, rn = _py_search_stereo(keys, desc, nleft, ltr, rtl, (0, 0, 320, 240), ex.scale, pts, th, 0.8)
+        np.testing.assert_array_equal(ml, rl)
+        np.testing.assert_array_equal(mr, rr)
+        assert nm == rn and (ml >= 0).sum() > 100 and (mr >= 0).sum() > 20
