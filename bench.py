@@ -355,6 +355,7 @@ def search_leg(args, local, dev):
         if it >= 2:
             ms += m.last_ms()[0]
     match = d_match[:nsc].cpu().numpy()
+    mpf = float(d_cnt.float().mean().item())
     sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
     import oracle_lib
     oracle_lib.build()
@@ -366,11 +367,49 @@ def search_leg(args, local, dev):
                                                    nn_ratio=0.8)
         t_cpu += time.perf_counter() - t0
         ok = ok and bool(np.array_equal(match[f], rm))
+    # ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764): frame k-1 -> frame k, window 100, ratio 0.9
+    prev_imgs = np.stack([scenes.previous_frame(imgs[k], 7000 + k) for k in range(nsc)])
+    pcounts, _, pkps, pdesc = ex.extract_batch(prev_imgs)
+    K1 = np.zeros((nfr, cap), _lib.KP_DTYPE)
+    D1 = np.zeros((nfr, cap, 32), np.uint8)
+    PM = np.zeros((nfr, cap, 2), np.float32)
+    n1 = np.zeros(nfr, np.int32)
+    for f in range(nfr):
+        k = f % nsc
+        n = int(pcounts[k])
+        n1[f] = n
+        K1[f, :n], D1[f, :n] = pkps[k, :n], pdesc[k, :n]
+        PM[f, :n, 0], PM[f, :n, 1] = pkps[k, :n]["x"], pkps[k, :n]["y"]
+    dK1, dD1, dn1 = t(K1), t(D1), torch.from_numpy(n1).to(dev)
+    dPM0 = torch.from_numpy(PM).to(dev)
+    d_m12 = torch.zeros((nfr, cap), dtype=torch.int32, device=dev)
+    mi = ORBmatcher(0.9, True, device=local)
+    ms_i = 0.0
+    for it in range(steps + 2):
+        dPM = dPM0.clone()
+        mi.search_for_initialization_batch_raw(dK1, dD1, dn1, dK, dD, dn, cap, nfr, bounds, 100, dPM, d_m12, d_cnt, flags=FL)
+        if it >= 2:
+            ms_i += mi.last_ms()[0]
+    m12 = d_m12[:nsc].cpu().numpy()
+    ok_i, t_cpu_i = True, 0.0
+    for f in range(nsc):
+        a, b = int(n1[f]), int(nn[f])
+        t0 = time.perf_counter()
+        rm, _, _ = oracle_lib.search_for_initialization(K1[f, :a], D1[f, :a], K[f, :b], D[f, :b], bounds, PM[f, :a], 100, 0.9,
+                                                        True)
+        t_cpu_i += time.perf_counter() - t0
+        ok_i = ok_i and bool(np.array_equal(m12[f, :a], rm))
+    init = {"workload": "ORBmatcher::SearchForInitialization, %d frame pairs per step, ~%d level-0 keypoints x window 100"
+                        % (nfr, int((pkps[0, :int(pcounts[0])]["octave"] == 0).sum())),
+            "kernel_ms_per_step": ms_i / steps, "pairs_per_s": nfr / (ms_i / steps * 1e-3),
+            "matches_per_pair": float(d_cnt.float().mean().item()), "cpu_oracle_pairs_per_s_1thread": nsc / t_cpu_i,
+            "parity_sample": {"pairs": nsc, "vs": "CPU oracle (vnMatches12)", "ok": ok_i}}
     return {"workload": "ORBmatcher::SearchByProjection, %d frames per step, %d map points x ~%d features per frame, th = 1"
                         % (nfr, npts, int(nn.mean())), "kernel_ms_per_step": ms / steps,
-            "frames_per_s": nfr / (ms / steps * 1e-3), "matches_per_frame": float(d_cnt.float().mean().item()),
+            "frames_per_s": nfr / (ms / steps * 1e-3), "matches_per_frame": mpf,
             "cpu_oracle_frames_per_s_1thread": nsc / t_cpu,
-            "parity_sample": {"frames": nsc, "vs": "CPU oracle (match index per map point)", "ok": ok}}
+            "parity_sample": {"frames": nsc, "vs": "CPU oracle (match index per map point)", "ok": ok},
+            "initialization": init}
 
 
 def run_reference(args):

@@ -202,6 +202,18 @@ int orbfe_search_by_projection_stereo_batch(orbfe_matcher* m, const orbfe_keypoi
                                             int nframes, float th, int far_points, float th_far, float nn_ratio,
                                             int32_t* match_left, int32_t* match_right, int32_t* owner, int32_t* nmatches,
                                             unsigned flags);
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764, with
+ * ComputeThreeMaxima :2061-2102) for monocular frames, nframes independent (F1, F2) pairs, one CTA each.  Pair f:
+ * keys1 / desc1 [f*cap, f*cap + n1[f]) = F1.mvKeysUn / mDescriptors, keys2 / desc2 / n2 likewise for F2; bounds =
+ * F2's mnMinX, mnMinY, mnMaxX, mnMaxY (host memory).  prev_matched[f*cap + i] = vbPrevMatched[i] as (x, y), read as the
+ * window centres and updated in place for the matched keypoints (:759-761); it follows ORBFE_IN_DEVICE.
+ * matches12[f*cap + i] = vnMatches12[i] (index into F2 or -1; all cap slots are written); nmatches[f] = the return
+ * value.  nn_ratio = mfNNratio, check_orientation = mbCheckOrientation (the constructor's arguments). */
+int orbfe_search_for_initialization_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1,
+                                          const int32_t* n1, const orbfe_keypoint* keys2, const uint8_t* desc2,
+                                          const int32_t* n2, int cap, int nframes, const float bounds[4], int window_size,
+                                          float nn_ratio, int check_orientation, float* prev_matched, int32_t* matches12,
+                                          int32_t* nmatches, unsigned flags);
 /* Frame::UndistortKeyPoints (Frame.cc:763-796): mvKeysUn = mvKeys with the positions passed through
  * cv::undistortPoints(pts, pts, K, mDistCoef, Mat(), mK) (OpenCV 4.x: 5 fixed-point iterations in double); K = (fx, fy,
  * cx, cy) of mK, dist_coef = k1, k2, p1, p2[, k3] (ndist 4 or 5, up to OpenCV's 14); dist_coef[0] == 0 copies the

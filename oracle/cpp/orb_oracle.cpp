@@ -1225,6 +1225,153 @@ int orc_search_by_projection_stereo(const orc_keypoint* keys, const uint8_t* des
     return nmatches;
 }
 
+// ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764) + ComputeThreeMaxima (:2061-2102) ----------------------
+// F1 / F2 are monocular frames (Nleft == -1); the grid is F2's.  vMatchedDistance / vnMatches21 make the loop order
+// dependent (a later keypoint steals a match only with a strictly smaller distance, and matched candidates with a
+// distance <= the current one are invisible to the best / second-best bookkeeping).  HISTO_LENGTH = 30, TH_LOW = 50.
+int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, const orc_keypoint* keys2,
+                                  const uint8_t* desc2, int n2, float mnMinX, float mnMinY, float mnMaxX, float mnMaxY,
+                                  float* prevMatchedXY, int windowSize, float mfNNratio, int checkOrientation,
+                                  int32_t* vnMatches12) {
+    const int TH_LOW = 50, HISTO_LENGTH = 30;
+    const float gwInv = static_cast<float>(GRID_COLS) / (mnMaxX - mnMinX);
+    const float ghInv = static_cast<float>(GRID_ROWS) / (mnMaxY - mnMinY);
+    static thread_local std::vector<size_t> mGrid[GRID_COLS][GRID_ROWS];
+    for (int i = 0; i < GRID_COLS; i++)
+        for (int j = 0; j < GRID_ROWS; j++) mGrid[i][j].clear();
+    for (int i = 0; i < n2; i++) {
+        const int posX = (int)std::round((keys2[i].x - mnMinX) * gwInv);
+        const int posY = (int)std::round((keys2[i].y - mnMinY) * ghInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        mGrid[posX][posY].push_back(i);
+    }
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) vnMatches12[i] = -1;
+    std::vector<int> rotHist[30];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> vMatchedDistance(n2, INT_MAX);
+    std::vector<int> vnMatches21(n2, -1);
+    std::vector<size_t> vIndices2;
+    for (int i1 = 0; i1 < n1; i1++) {
+        const orc_keypoint kp1 = keys1[i1];
+        const int level1 = kp1.octave;
+        if (level1 > 0) continue;
+        // F2.GetFeaturesInArea(vbPrevMatched[i1].x, vbPrevMatched[i1].y, windowSize, level1, level1)
+        vIndices2.clear();
+        {
+            const float x = prevMatchedXY[2 * i1], y = prevMatchedXY[2 * i1 + 1];
+            const float factorX = windowSize, factorY = windowSize;
+            const int minLevel = level1, maxLevel = level1;
+            const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * gwInv));
+            const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * gwInv));
+            const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * ghInv));
+            const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * ghInv));
+            if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0)) {
+                const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+                for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                    for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                        const std::vector<size_t>& vCell = mGrid[ix][iy];
+                        for (size_t j = 0; j < vCell.size(); j++) {
+                            const orc_keypoint& kpUn = keys2[vCell[j]];
+                            if (bCheckLevels) {
+                                if (kpUn.octave < minLevel) continue;
+                                if (maxLevel >= 0)
+                                    if (kpUn.octave > maxLevel) continue;
+                            }
+                            const float distx = kpUn.x - x;
+                            const float disty = kpUn.y - y;
+                            if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) vIndices2.push_back(vCell[j]);
+                        }
+                    }
+            }
+        }
+        if (vIndices2.empty()) continue;
+        uint64_t a[4];
+        std::memcpy(a, desc1 + (size_t)i1 * 32, 32);
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (size_t k = 0; k < vIndices2.size(); k++) {
+            const size_t i2 = vIndices2[k];
+            uint64_t b[4];
+            std::memcpy(b, desc2 + i2 * 32, 32);
+            const int dist = hamming256(a, b);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestIdx2 = (int)i2;
+            } else if (dist < bestDist2) {
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * mfNNratio) {
+                if (vnMatches21[bestIdx2] >= 0) {
+                    vnMatches12[vnMatches21[bestIdx2]] = -1;
+                    nmatches--;
+                }
+                vnMatches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOrientation) {
+                    float rot = keys1[i1].angle - keys2[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        {    // ComputeThreeMaxima
+            int max1 = 0, max2 = 0, max3 = 0;
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                const int sz = (int)rotHist[i].size();
+                if (sz > max1) {
+                    max3 = max2;
+                    max2 = max1;
+                    max1 = sz;
+                    ind3 = ind2;
+                    ind2 = ind1;
+                    ind1 = i;
+                } else if (sz > max2) {
+                    max3 = max2;
+                    max2 = sz;
+                    ind3 = ind2;
+                    ind2 = i;
+                } else if (sz > max3) {
+                    max3 = sz;
+                    ind3 = i;
+                }
+            }
+            if (max2 < 0.1f * (float)max1) {
+                ind2 = -1;
+                ind3 = -1;
+            } else if (max3 < 0.1f * (float)max1) {
+                ind3 = -1;
+            }
+        }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                const int idx1 = rotHist[i][j];
+                if (vnMatches12[idx1] >= 0) {
+                    vnMatches12[idx1] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)
+        if (vnMatches12[i1] >= 0) {
+            prevMatchedXY[2 * i1] = keys2[vnMatches12[i1]].x;
+            prevMatchedXY[2 * i1 + 1] = keys2[vnMatches12[i1]].y;
+        }
+    return nmatches;
+}
+
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

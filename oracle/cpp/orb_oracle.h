@@ -117,6 +117,13 @@ int orc_search_by_projection_stereo(const orc_keypoint* keys, const uint8_t* des
                                     const orc_track_point_stereo* pts, int npts, float th, int bFarPoints,
                                     float thFarPoints, float mfNNratio, int32_t* matchL, int32_t* matchR, int32_t* owner);
 
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) for
+ * monocular frames.  prevMatchedXY: n1 (x, y) pairs, updated in place (:759-761); vnMatches12: n1 ints. Returns nmatches. */
+int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, const orc_keypoint* keys2,
+                                  const uint8_t* desc2, int n2, float mnMinX, float mnMinY, float mnMaxX, float mnMaxY,
+                                  float* prevMatchedXY, int windowSize, float mfNNratio, int checkOrientation,
+                                  int32_t* vnMatches12);
+
 int orc_hardware_threads(void);
 #ifdef __cplusplus
 }

@@ -76,6 +76,10 @@ def lib():
                                         C.c_void_p, C.c_void_p, C.c_int]
         L.orc_extract_batch.restype = C.c_int
         L.orc_hardware_threads.restype = C.c_int
+        L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                                    C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int,
+                                                    C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_for_initialization.restype = C.c_int
         L.orc_search_by_projection_stereo.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
                                                       C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p,
                                                       C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float,
@@ -307,6 +311,22 @@ def search_by_projection_stereo(keys, desc, occupied, nleft, left_to_right, righ
                                                int(bool(far_points)), float(th_far), float(nn_ratio), _p(ml), _p(mr),
                                                _p(owner))
     return ml, mr, owner, int(nm)
+
+
+def search_for_initialization(keys1, desc1, keys2, desc2, bounds, prev_matched, window_size=100, nn_ratio=0.9,
+                              check_orientation=True):
+    """ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764).  prev_matched: (n1, 2) float32 (vbPrevMatched).
+    -> (vnMatches12 int32 (n1,), updated prev_matched (n1, 2), nmatches)"""
+    k1 = np.ascontiguousarray(keys1, KP_DTYPE)
+    k2 = np.ascontiguousarray(keys2, KP_DTYPE)
+    d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    pm = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+    m12 = np.empty(k1.shape[0], np.int32)
+    nm = lib().orc_search_for_initialization(_p(k1), _p(d1), k1.shape[0], _p(k2), _p(d2), k2.shape[0], float(bounds[0]),
+                                             float(bounds[1]), float(bounds[2]), float(bounds[3]), _p(pm),
+                                             int(window_size), float(nn_ratio), int(bool(check_orientation)), _p(m12))
+    return m12, pm, int(nm)
 
 
 def undistort_keypoints(kps, fx, fy, cx, cy, dist):

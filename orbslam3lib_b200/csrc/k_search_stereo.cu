@@ -446,4 +446,295 @@ int launch_search_by_projection_stereo(const float bounds[4], const float* scale
     return 1;
 }
 
+// ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764) + ComputeThreeMaxima (:2061-2102) ----------------------
+// Monocular initialisation: every level-0 keypoint of F1 searches F2's grid in a square of windowSize around
+// vbPrevMatched[i1] (levels 0..0), keeps the best and the second-best DISTANCE, accepts with bestDist <= TH_LOW and
+// bestDist < bestDist2 * mfNNratio, and a later keypoint steals a feature of F2 only with a strictly smaller distance
+// (vMatchedDistance: candidates whose recorded distance is <= the current one are invisible, :690-691).  That state makes
+// the loop order dependent; it is handled like the map-point loop above: one CTA per frame pair, one warp per keypoint,
+// chunks searched against the current state, the longest prefix whose windows were not touched by an earlier commit of the
+// same round is committed, the rest searches again.  best = min (dist, cell, index) is the first minimum in visiting
+// order; bestDist2 is the second smallest distance with multiplicity, which is order free.
+// The rotation histogram counts every accepted match, also the ones stolen later (rotHist keeps their i1, :724-733);
+// bins are 0..12 only because factor = 1/HISTO_LENGTH (the reference's own arithmetic, reproduced).
+constexpr int SI_TH_LOW = 50, SI_HISTO = 30;
+
+__device__ __forceinline__ int ss_block_exclusive_scan(int s, int* sScan, int* sTotal) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    __syncthreads();    // sScan may still be read from an earlier use
+    if (lane == 31) sScan[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const int w = lane < SS_WARPS ? sScan[lane] : 0;
+        int winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += v;
+        }
+        if (lane < SS_WARPS) sScan[lane] = winc - w;
+        if (lane == 31) *sTotal = winc;
+    }
+    __syncthreads();
+    return sScan[warp] + inc - s;
+}
+
+// grid: nframes; block SS_THREADS; dynamic shared memory: search_init_smem_bytes(cap)
+__global__ void __launch_bounds__(SS_THREADS) search_for_initialization_kernel(
+    const __grid_constant__ StereoSearchParams P, float windowSize, int checkOrientation,
+    const orbfe_keypoint* __restrict__ keys1All, const uint8_t* __restrict__ desc1All, const int* __restrict__ n1All,
+    const orbfe_keypoint* __restrict__ keys2All, const uint8_t* __restrict__ desc2All, const int* __restrict__ n2All,
+    float2* __restrict__ prevAll, int* __restrict__ match12All, int* __restrict__ nMatches) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    int* cellStart = reinterpret_cast<int*>(smem);                                   // SS_CELLS + 1
+    int* cellFill = cellStart + SS_CELLS + 1;                                        // SS_CELLS
+    int* hist = cellFill + SS_CELLS;                                                 // 32
+    unsigned short* items = reinterpret_cast<unsigned short*>(hist + 32);            // cap
+    unsigned short* mdist = items + P.cap;                                           // vMatchedDistance (0xffff = INT_MAX)
+    unsigned short* m21 = mdist + P.cap;                                             // vnMatches21 (0xffff = -1)
+    unsigned short* list0 = m21 + P.cap;                                             // level-0 keypoints of F1, ascending
+    uint8_t* binOf = reinterpret_cast<uint8_t*>(list0 + P.cap);                      // rotHist bin of i1 (0xff = none)
+    __shared__ int sScan[SS_WARPS + 1];
+    __shared__ int sRes[SS_WARPS], sDist[SS_WARPS];
+    __shared__ int sOpen, sCount, sTotal;
+    __shared__ int sInd[3];
+
+    const int f = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n1 = min(n1All[f], P.cap), n2 = min(n2All[f], P.cap);
+    const orbfe_keypoint* keys1 = keys1All + (size_t)f * P.cap;
+    const orbfe_keypoint* keys2 = keys2All + (size_t)f * P.cap;
+    const uint8_t* desc1 = desc1All + (size_t)f * P.cap * 32;
+    const uint8_t* desc2 = desc2All + (size_t)f * P.cap * 32;
+    float2* prev = prevAll + (size_t)f * P.cap;
+    int* match12 = match12All + (size_t)f * P.cap;
+    const float gwInv = (float)SS_COLS / (P.maxX - P.minX);
+    const float ghInv = (float)SS_ROWS / (P.maxY - P.minY);
+
+    ss_build_grid(keys2, 0, n2, P, gwInv, ghInv, cellStart, cellFill, items, sScan, &sTotal);
+    for (int i = tid; i < P.cap; i += SS_THREADS) {
+        mdist[i] = 0xffffu;
+        m21[i] = 0xffffu;
+        binOf[i] = 0xffu;
+        match12[i] = -1;
+    }
+    if (tid < 32) hist[tid] = 0;
+    if (tid == 0) sCount = 0;
+    // level-0 keypoints of F1 in ascending index (:663-667)
+    int n0;
+    {
+        const int per = (n1 + SS_THREADS - 1) / SS_THREADS;
+        const int b = min(tid * per, n1), e = min(b + per, n1);
+        int s = 0;
+        for (int i = b; i < e; i++) s += keys1[i].octave <= 0;
+        int at = ss_block_exclusive_scan(s, sScan, &sTotal);
+        for (int i = b; i < e; i++)
+            if (keys1[i].octave <= 0) list0[at++] = (unsigned short)i;
+        n0 = sTotal;
+    }
+    __syncthreads();
+
+    constexpr unsigned long long NONE = 0x7fffffffull << 32;
+    for (int base = 0; base < n0; base += SS_WARPS) {
+        const bool have = base + warp < n0;
+        const int i1 = have ? list0[base + warp] : 0;
+        SWindow w;
+        w.cx0 = 1;
+        w.cx1 = 0;
+        uint32_t md[8];
+        if (have) {
+            const float2 c = prev[i1];
+            ss_window(w, P, gwInv, ghInv, c.x, c.y, windowSize, 0);
+            w.minLevel = 0;    // GetFeaturesInArea(x, y, windowSize, level1, level1), level1 == 0
+            const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(desc1 + (size_t)i1 * 32));
+            const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(desc1 + (size_t)i1 * 32) + 1);
+            md[0] = a0.x; md[1] = a0.y; md[2] = a0.z; md[3] = a0.w;
+            md[4] = a1.x; md[5] = a1.y; md[6] = a1.z; md[7] = a1.w;
+        }
+        if (tid == 0) sOpen = (int)(0xffffffffu >> (32 - min(n0 - base, SS_WARPS)));
+        __syncthreads();
+        for (;;) {
+            if (have && ((sOpen >> warp) & 1)) {
+                unsigned long long k1 = NONE;
+                int d2 = 0x7fffffff;
+                if (w.cx0 <= w.cx1) {
+                    const int ncy = w.cy1 - w.cy0 + 1;
+                    const int ncell = (w.cx1 - w.cx0 + 1) * ncy;
+                    for (int c = lane; c < ncell; c += 32) {
+                        const int cell = (w.cx0 + c / ncy) * SS_ROWS + w.cy0 + c % ncy;
+                        for (int t = cellStart[cell]; t < cellStart[cell + 1]; t++) {
+                            const int idx = items[t];
+                            if (!ss_inside(w, keys2[idx])) continue;
+                            const uint4 b0 = __ldg(reinterpret_cast<const uint4*>(desc2 + (size_t)idx * 32));
+                            const uint4 b1 = __ldg(reinterpret_cast<const uint4*>(desc2 + (size_t)idx * 32) + 1);
+                            const int d = __popc(md[0] ^ b0.x) + __popc(md[1] ^ b0.y) + __popc(md[2] ^ b0.z) +
+                                          __popc(md[3] ^ b0.w) + __popc(md[4] ^ b1.x) + __popc(md[5] ^ b1.y) +
+                                          __popc(md[6] ^ b1.z) + __popc(md[7] ^ b1.w);
+                            if ((int)mdist[idx] <= d) continue;    // vMatchedDistance[i2] <= dist (:690-691)
+                            const unsigned long long key = ((unsigned long long)d << 32) | ((uint32_t)cell << 16) | (uint32_t)idx;
+                            if (key < k1) {
+                                d2 = (int)(k1 >> 32);    // the old best is the new runner-up (it was <= d2)
+                                k1 = key;
+                            } else {
+                                d2 = min(d2, d);
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const unsigned long long ok = __shfl_xor_sync(0xffffffffu, k1, o);
+                    const int od = __shfl_xor_sync(0xffffffffu, d2, o);
+                    const unsigned long long loser = ok > k1 ? ok : k1;
+                    d2 = min(min(d2, od), (int)(loser >> 32));
+                    k1 = ok < k1 ? ok : k1;
+                }
+                const int bestDist = (int)(k1 >> 32);
+                int res = -1;
+                if (bestDist <= SI_TH_LOW && (float)bestDist < (float)d2 * P.nnRatio) res = (int)(k1 & 0xffffu);
+                if (lane == 0) {
+                    sRes[warp] = res;
+                    sDist[warp] = bestDist;
+                }
+            }
+            __syncthreads();
+            if (warp == 0) {
+                const int open = sOpen;
+                const bool mine = lane < SS_WARPS && ((open >> lane) & 1);
+                SWindow lw;
+                lw.x = lw.y = 0.f;
+                lw.rr = windowSize;
+                lw.minLevel = 0;
+                lw.maxLevel = 0;
+                int myRes = -1, my1 = 0;
+                if (mine) {
+                    my1 = list0[base + lane];
+                    const float2 c = prev[my1];
+                    lw.x = c.x;
+                    lw.y = c.y;
+                    myRes = sRes[lane];
+                }
+                bool valid = true;
+                for (int i = 0; i < SS_WARPS - 1; i++) {
+                    const int fi = __shfl_sync(0xffffffffu, myRes, i);
+                    if (i < lane && fi >= 0 && mine && ss_inside(lw, keys2[fi])) valid = false;
+                }
+                const unsigned bad = __ballot_sync(0xffffffffu, mine && !valid);
+                const int firstBad = bad ? __ffs(bad) - 1 : 32;
+                const bool commit = mine && lane < firstBad;
+                if (commit && myRes >= 0) {
+                    const int old = m21[myRes];
+                    if (old != 0xffff) match12[old] = -1;    // :705-709
+                    match12[my1] = myRes;
+                    m21[myRes] = (unsigned short)my1;
+                    mdist[myRes] = (unsigned short)sDist[lane];
+                    if (checkOrientation) {
+                        float rot = keys1[my1].angle - keys2[myRes].angle;
+                        if (rot < 0.0f) rot += 360.0f;
+                        int bin = (int)roundf(rot * (1.0f / SI_HISTO));
+                        if (bin == SI_HISTO) bin = 0;
+                        bin = min(max(bin, 0), SI_HISTO - 1);
+                        binOf[my1] = (uint8_t)bin;
+                        atomicAdd(&hist[bin], 1);
+                    }
+                }
+                const unsigned done = __ballot_sync(0xffffffffu, commit);
+                if (lane == 0) sOpen = open & ~(int)done;
+            }
+            __syncthreads();
+            if (sOpen == 0) break;
+            __syncthreads();
+        }
+        __syncthreads();
+    }
+
+    if (checkOrientation) {
+        if (tid == 0) {    // ComputeThreeMaxima
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int i = 0; i < SI_HISTO; i++) {
+                const int s = hist[i];
+                if (s > max1) {
+                    max3 = max2; max2 = max1; max1 = s;
+                    ind3 = ind2; ind2 = ind1; ind1 = i;
+                } else if (s > max2) {
+                    max3 = max2; max2 = s;
+                    ind3 = ind2; ind2 = i;
+                } else if (s > max3) {
+                    max3 = s;
+                    ind3 = i;
+                }
+            }
+            if ((float)max2 < 0.1f * (float)max1) {
+                ind2 = -1;
+                ind3 = -1;
+            } else if ((float)max3 < 0.1f * (float)max1) {
+                ind3 = -1;
+            }
+            sInd[0] = ind1;
+            sInd[1] = ind2;
+            sInd[2] = ind3;
+        }
+        __syncthreads();
+        for (int t = tid; t < n0; t += SS_THREADS) {
+            const int i1 = list0[t];
+            const int bin = binOf[i1];
+            if (bin == 0xff || bin == sInd[0] || bin == sInd[1] || bin == sInd[2]) continue;
+            if (match12[i1] >= 0) match12[i1] = -1;    // :740-747
+        }
+        __syncthreads();
+    }
+    int cnt = 0;
+    for (int t = tid; t < n0; t += SS_THREADS) {    // :759-761
+        const int i1 = list0[t];
+        const int m = match12[i1];
+        if (m >= 0) {
+            prev[i1] = make_float2(keys2[m].x, keys2[m].y);
+            cnt++;
+        }
+    }
+    if (cnt) atomicAdd(&sCount, cnt);
+    __syncthreads();
+    if (tid == 0 && nMatches) nMatches[f] = sCount;
+}
+
+size_t search_init_smem_bytes(int cap) {
+    return (size_t)(2 * SS_CELLS + 1 + 32) * 4 + (size_t)cap * 9 + 16;
+}
+
+int launch_search_for_initialization(const float bounds[4], int windowSize, float nnRatio, int checkOrientation,
+                                     const orbfe_keypoint* keys1, const uint8_t* desc1, const int* n1,
+                                     const orbfe_keypoint* keys2, const uint8_t* desc2, const int* n2, int cap, int nframes,
+                                     float* prevMatched, int* match12, int* nMatches, cudaStream_t st) {
+    if (nframes <= 0) return 0;
+    StereoSearchParams P;
+    P.minX = bounds[0];
+    P.minY = bounds[1];
+    P.maxX = bounds[2];
+    P.maxY = bounds[3];
+    for (int l = 0; l < ORBFE_MAX_LEVELS; l++) P.scale[l] = 1.0f;
+    P.th = 1.0f;
+    P.thFar = 0.f;
+    P.nnRatio = nnRatio;
+    P.farPoints = 0;
+    P.cap = cap;
+    P.ptsCap = cap;
+    const size_t smem = search_init_smem_bytes(cap);
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && configured < smem) {
+        cudaFuncSetAttribute(search_for_initialization_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+    }
+    search_for_initialization_kernel<<<nframes, SS_THREADS, smem, st>>>(P, (float)windowSize, checkOrientation, keys1, desc1,
+                                                                        n1, keys2, desc2, n2,
+                                                                        reinterpret_cast<float2*>(prevMatched), match12,
+                                                                        nMatches);
+    return 1;
+}
+
 }    // namespace orbfe

@@ -35,6 +35,11 @@ int launch_search_by_projection_stereo(const float bounds[4], const float* scale
                                        const uint8_t* occupied, const int* nFeat, const int* nLeft, const int* ltr,
                                        const int* rtl, int cap, const void* pts, const int* nPts, int ptsCap, int nframes,
                                        int* matchL, int* matchR, int* owner, int* nMatches, cudaStream_t st);
+size_t search_init_smem_bytes(int cap);
+int launch_search_for_initialization(const float bounds[4], int windowSize, float nnRatio, int checkOrientation,
+                                     const orbfe_keypoint* keys1, const uint8_t* desc1, const int* n1,
+                                     const orbfe_keypoint* keys2, const uint8_t* desc2, const int* n2, int cap, int nframes,
+                                     float* prevMatched, int* match12, int* nMatches, cudaStream_t st);
 int launch_undistort(const orbfe_keypoint* keys, int n, float fx, float fy, float cx, float cy, const float* dist,
                      int ndist, orbfe_keypoint* keysUn, cudaStream_t st);
 int launch_search_by_projection(const float bounds[4], const float* scale, int nlevels, float th, int farPoints,
@@ -1250,6 +1255,70 @@ int orbfe_search_by_projection_stereo_batch(orbfe_matcher* m, const orbfe_keypoi
             ORBFE_MCUDA(m, cudaMemcpyAsync(match_right, dMR, F * pts_cap * 4, cudaMemcpyDeviceToHost, st));
         }
         if (owner && cap) ORBFE_MCUDA(m, cudaMemcpyAsync(owner, dOwner, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_search_for_initialization_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1,
+                                          const int32_t* n1, const orbfe_keypoint* keys2, const uint8_t* desc2,
+                                          const int32_t* n2, int cap, int nframes, const float bounds[4], int window_size,
+                                          float nn_ratio, int check_orientation, float* prev_matched, int32_t* matches12,
+                                          int32_t* nmatches, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (nframes < 0 || cap < 0 || window_size < 0) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (nframes == 0) return ORBFE_OK;
+    if (!n1 || !n2 || !bounds || (cap > 0 && (!keys1 || !desc1 || !keys2 || !desc2 || !prev_matched || !matches12)))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (!(bounds[2] > bounds[0]) || !(bounds[3] > bounds[1])) return set_merr(m, ORBFE_ERR_ARG, "empty image bounds");
+    if (cap >= 65535 || search_init_smem_bytes(cap) > 200 * 1024)
+        return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large for the shared-memory frame grid", cap);
+    if (cap == 0) {
+        if (nmatches && !(flags & ORBFE_OUT_DEVICE))
+            for (int f = 0; f < nframes; f++) nmatches[f] = 0;
+        return ORBFE_OK;
+    }
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)nframes;
+    const void* dIn[6] = {keys1, desc1, n1, keys2, desc2, n2};
+    const size_t inBytes[6] = {F * cap * sizeof(orbfe_keypoint), F * cap * 32, F * 4, F * cap * sizeof(orbfe_keypoint), F * cap * 32, F * 4};
+    if (!inDev)
+        for (int i = 0; i < 6; i++) {
+            ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(inBytes[i], 16)));
+            ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, dIn[i], inBytes[i], cudaMemcpyHostToDevice, st));
+            dIn[i] = m->dS[i].p;
+        }
+    // vbPrevMatched is read and written: it is an input when deciding where it lives
+    float* dPrev = prev_matched;
+    if (!inDev) {
+        ORBFE_MCUDA(m, m->dS[6].reserve(F * cap * 8));
+        ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[6].p, prev_matched, F * cap * 8, cudaMemcpyHostToDevice, st));
+        dPrev = (float*)m->dS[6].p;
+    }
+    int32_t *dM = matches12, *dCount = nmatches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dS[9].reserve(F * cap * 4));
+        ORBFE_MCUDA(m, m->dS[12].reserve(F * 4));
+        dM = (int32_t*)m->dS[9].p;
+        dCount = (int32_t*)m->dS[12].p;
+    }
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_search_for_initialization(
+        bounds, window_size, nn_ratio, check_orientation, (const orbfe_keypoint*)dIn[0], (const uint8_t*)dIn[1],
+        (const int*)dIn[2], (const orbfe_keypoint*)dIn[3], (const uint8_t*)dIn[4], (const int*)dIn[5], cap, nframes, dPrev,
+        dM, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!inDev) ORBFE_MCUDA(m, cudaMemcpyAsync(prev_matched, dPrev, F * cap * 8, cudaMemcpyDeviceToHost, st));
+    if (!outDev) {
+        ORBFE_MCUDA(m, cudaMemcpyAsync(matches12, dM, F * cap * 4, cudaMemcpyDeviceToHost, st));
         if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
     }
     ORBFE_MCUDA(m, cudaStreamSynchronize(st));

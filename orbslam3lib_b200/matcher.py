@@ -160,6 +160,34 @@ class ORBmatcher:
             ptr(mr), ptr(owner), ptr(nm), 0))
         return int(nm[0]), ml, mr, owner
 
+    def SearchForInitialization(self, keys1_un, desc1, keys2_un, desc2, bounds, vbPrevMatched, windowSize=10):
+        """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) on
+        monocular frames given as arrays; bounds = F2's image bounds.  vbPrevMatched: (n1, 2) float32.
+        -> (nmatches, vnMatches12 int32 (n1,), updated vbPrevMatched (n1, 2))"""
+        k1 = np.ascontiguousarray(keys1_un, KP_DTYPE)
+        k2 = np.ascontiguousarray(keys2_un, KP_DTYPE)
+        n1, n2 = k1.shape[0], k2.shape[0]
+        cap = max(n1, n2, 1)
+        K = np.zeros((2, cap), KP_DTYPE)
+        D = np.zeros((2, cap, 32), np.uint8)
+        K[0, :n1], K[1, :n2] = k1, k2
+        D[0, :n1] = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        D[1, :n2] = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        pm = np.zeros((cap, 2), np.float32)
+        pm[:n1] = np.asarray(vbPrevMatched, np.float32).reshape(-1, 2)
+        m12 = np.full(cap, -1, np.int32)
+        nn1, nn2, nm = (np.array([v], np.int32) for v in (n1, n2, 0))
+        self.search_for_initialization_batch_raw(K[0], D[0], nn1, K[1], D[1], nn2, cap, 1, bounds, windowSize, pm, m12, nm)
+        return int(nm[0]), m12[:n1], pm[:n1]
+
+    def search_for_initialization_batch_raw(self, keys1, desc1, n1, keys2, desc2, n2, cap, nframes, bounds, windowSize,
+                                            prev_matched, matches12, nmatches, flags=0):
+        b = np.ascontiguousarray(bounds, np.float32)
+        self._bf._check(_lib.lib().orbfe_search_for_initialization_batch(
+            self._bf._h, ptr(keys1), ptr(desc1), ptr(n1), ptr(keys2), ptr(desc2), ptr(n2), int(cap), int(nframes), ptr(b),
+            int(windowSize), self.mfNNratio, int(self.mbCheckOrientation), ptr(prev_matched), ptr(matches12), ptr(nmatches),
+            int(flags)))
+
     def UndistortKeyPoints(self, keys, K, dist_coef):
         """Frame::UndistortKeyPoints (Frame.cc:763-796): keys (KP_DTYPE), K = 3x3 mK or (fx, fy, cx, cy), mDistCoef ->
         mvKeysUn."""

@@ -242,3 +242,116 @@ def test_oracle_search_by_projection_stereo_vs_python(oracle):
         np.testing.assert_array_equal(ml, rl)
         np.testing.assert_array_equal(mr, rr)
         assert nm == rn and (ml >= 0).sum() > 100 and (mr >= 0).sum() > 20
+
+
+def _py_search_init(k1, d1, k2, d2, bounds, prev, window, nn_ratio, check_ori):
+    """literal restatement of ORBmatcher.cc:649-764 + ComputeThreeMaxima (:2061-2102), numpy float32."""
+    f32 = np.float32
+    min_x, min_y, max_x, max_y = [f32(v) for v in bounds]
+    gw, gh = f32(f32(64) / f32(max_x - min_x)), f32(f32(48) / f32(max_y - min_y))
+
+    def c_round(v):
+        v = float(v)
+        return int(math.floor(v + 0.5) if v >= 0 else math.ceil(v - 0.5))
+    grid = {}
+    for i in range(len(k2)):
+        px = c_round(f32(f32(k2["x"][i] - min_x) * gw))
+        py = c_round(f32(f32(k2["y"][i] - min_y) * gh))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    b1, b2 = np.unpackbits(d1, axis=1), np.unpackbits(d2, axis=1)
+    prev = np.array(prev, np.float32).copy()
+    m12 = np.full(len(k1), -1, np.int32)
+    m21 = np.full(len(k2), -1, np.int32)
+    mdist = np.full(len(k2), 2**31 - 1, np.int64)
+    hist = [[] for _ in range(30)]
+    factor = f32(1.0) / f32(30)
+    r = f32(window)
+    nmatches = 0
+    for i1 in range(len(k1)):
+        if k1["octave"][i1] > 0:
+            continue
+        x, y = prev[i1]
+        cx0 = max(0, int(math.floor(f32(f32(f32(x - min_x) - r) * gw))))
+        cx1 = min(63, int(math.ceil(f32(f32(f32(x - min_x) + r) * gw))))
+        cy0 = max(0, int(math.floor(f32(f32(f32(y - min_y) - r) * gh))))
+        cy1 = min(47, int(math.ceil(f32(f32(f32(y - min_y) + r) * gh))))
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            continue
+        cand = []
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for j in grid.get((ix, iy), []):
+                    if k2["octave"][j] != 0:
+                        continue
+                    if abs(f32(k2["x"][j] - x)) < r and abs(f32(k2["y"][j] - y)) < r:
+                        cand.append(j)
+        if not cand:
+            continue
+        bd, bd2, bi = 2**31 - 1, 2**31 - 1, -1
+        for j in cand:
+            d = int(np.count_nonzero(b1[i1] != b2[j]))
+            if mdist[j] <= d:
+                continue
+            if d < bd:
+                bd2, bd, bi = bd, d, j
+            elif d < bd2:
+                bd2 = d
+        if bd <= 50 and f32(bd) < f32(f32(bd2) * f32(nn_ratio)):
+            if m21[bi] >= 0:
+                m12[m21[bi]] = -1
+                nmatches -= 1
+            m12[i1], m21[bi], mdist[bi] = bi, i1, bd
+            nmatches += 1
+            if check_ori:
+                rot = f32(k1["angle"][i1] - k2["angle"][bi])
+                if rot < 0:
+                    rot = f32(rot + f32(360))
+                b = c_round(f32(rot * factor))
+                hist[0 if b == 30 else b].append(i1)
+    if check_ori:
+        mx = [0, 0, 0]
+        ind = [-1, -1, -1]
+        for i in range(30):
+            s = len(hist[i])
+            if s > mx[0]:
+                mx, ind = [s, mx[0], mx[1]], [i, ind[0], ind[1]]
+            elif s > mx[1]:
+                mx, ind = [mx[0], s, mx[1]], [ind[0], i, ind[1]]
+            elif s > mx[2]:
+                mx[2], ind[2] = s, i
+        if mx[1] < f32(0.1) * f32(mx[0]):
+            ind[1] = ind[2] = -1
+        elif mx[2] < f32(0.1) * f32(mx[0]):
+            ind[2] = -1
+        for i in range(30):
+            if i in ind:
+                continue
+            for i1 in hist[i]:
+                if m12[i1] >= 0:
+                    m12[i1] = -1
+                    nmatches -= 1
+    for i1 in range(len(k1)):
+        if m12[i1] >= 0:
+            prev[i1] = (k2["x"][m12[i1]], k2["y"][m12[i1]])
+    return m12, prev, nmatches
+
+
+def test_oracle_search_for_initialization_vs_python(oracle):
+    cases = [("texture", 320, 240, 7100, 100, 0.9, True), ("texture", 320, 240, 7101, 30, 0.9, False),
+             ("checker", 320, 240, 7102, 100, 0.95, True), ("texture", 320, 240, 7103, 10, 0.9, True)]
+    total = 0
+    for kind, w, h, seed, window, ratio, ori in cases:
+        cur = scenes.make(kind, w, h, seed)
+        prv = scenes.previous_frame(cur, seed)
+        ex = oracle.OracleExtractor(1000, 1.2, 8, 20, 7)
+        _, k1, d1 = ex(prv)
+        _, k2, d2 = ex(cur)
+        pm = np.stack([k1["x"], k1["y"]], 1)
+        m12, pm2, nm = oracle.search_for_initialization(k1, d1, k2, d2, (0, 0, w, h), pm, window, ratio, ori)
+        rm12, rpm, rnm = _py_search_init(k1, d1, k2, d2, (0, 0, w, h), pm, window, ratio, ori)
+        np.testing.assert_array_equal(m12, rm12)
+        np.testing.assert_array_equal(pm2, rpm)
+        assert nm == rnm == int((m12 >= 0).sum())
+        total += nm
+    assert total > 150
