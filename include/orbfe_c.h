@@ -214,6 +214,33 @@ int orbfe_search_for_initialization_batch(orbfe_matcher* m, const orbfe_keypoint
                                           const int32_t* n2, int cap, int nframes, const float bounds[4], int window_size,
                                           float nn_ratio, int check_orientation, float* prev_matched, int32_t* matches12,
                                           int32_t* nmatches, unsigned flags);
+/* The half of Frame::ComputeStereoFishEyeMatches that follows BFMatchORB (Frame.cc:1164-1204) with
+ * KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:300-363: unproject both keypoints, parallax gate, 4x4 DLT, depth
+ * signs, chi-square reprojection gates), nframes stereo-camera frames per call.
+ *   rig            the two KannalaBrandt8 cameras and Frame::mRlr / mtlr / mvLevelSigma2 (host memory)
+ *   keys_left / keys_right [f*cap ...)   mvKeys / mvKeysRight; n_left / n_right [f] = Nleft / Nright;
+ *   mono_left / mono_right [f]           monoLeft / monoRight (NULL = 0): the stereo-area keypoints come after them
+ *   knn_idx / knn_dist [f*knn_cap*2 ...) the k = 2 result of orbfe_knn2_batch (== BFMatchORB's indices / dist1 / dist2)
+ *                  with the stereo-area LEFT descriptors as queries and the stereo-area RIGHT ones as train rows
+ *   left_to_right / right_to_left / depth [f*cap ...)   mvLeftToRightMatch / mvRightToLeftMatch / mvDepth (-1 = none)
+ *   points3d [f*cap*3 ...)               mvStereo3Dpoints (x, y, z; 0 where there is no match)
+ *   status (optional) [f*cap ...)        1 matched, 0 not tried, -1 .. -5 = TriangulateMatches' return, -6 depth <= 1e-4
+ *   nmatches [f]                         nMatches
+ * Float arithmetic as the reference; the 4x4 null vector is solved in double (Jacobi) instead of Eigen's float
+ * JacobiSVD: results agree with the reference build to its own float noise (<= 1e-3 relative on mvDepth). */
+typedef struct orbfe_fisheye_rig {
+    float cam1[8], cam2[8]; /* KannalaBrandt8::mvParameters (fx, fy, cx, cy, k0..k3) of mpCamera / mpCamera2 */
+    float Rlr[9], tlr[3];   /* mRlr row-major, mtlr (Frame.cc:1115-1116) */
+    float precision;        /* KannalaBrandt8::precision, 1e-6 */
+    int32_t nlevels;
+    float level_sigma2[ORBFE_MAX_LEVELS]; /* mvLevelSigma2 */
+} orbfe_fisheye_rig;
+int orbfe_stereo_fisheye_matches_batch(orbfe_matcher* m, const orbfe_keypoint* keys_left, const orbfe_keypoint* keys_right,
+                                       const int32_t* n_left, const int32_t* n_right, const int32_t* mono_left,
+                                       const int32_t* mono_right, int cap, const int32_t* knn_idx, const int32_t* knn_dist,
+                                       int knn_cap, int nframes, const orbfe_fisheye_rig* rig, int32_t* left_to_right,
+                                       int32_t* right_to_left, float* depth, float* points3d, int32_t* status,
+                                       int32_t* nmatches, unsigned flags);
 /* Frame::UndistortKeyPoints (Frame.cc:763-796): mvKeysUn = mvKeys with the positions passed through
  * cv::undistortPoints(pts, pts, K, mDistCoef, Mat(), mK) (OpenCV 4.x: 5 fixed-point iterations in double); K = (fx, fy,
  * cx, cy) of mK, dist_coef = k1, k2, p1, p2[, k3] (ndist 4 or 5, up to OpenCV's 14); dist_coef[0] == 0 copies the

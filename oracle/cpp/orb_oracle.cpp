@@ -1372,6 +1372,208 @@ int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc
     return nmatches;
 }
 
+// ---- Frame::ComputeStereoFishEyeMatches, the part after BFMatchORB (Frame.cc:1164-1204) with
+//      KannalaBrandt8::unproject / project(Vector3f) / Triangulate / TriangulateMatches (KannalaBrandt8.cpp:60-79,
+//      107-136, 300-363, 380-392).  Everything is float as in the reference, except the 4x4 SVD: the reference calls
+//      Eigen::JacobiSVD<Matrix4f> (Eigen 3.4.0, vendored under Thirdparty/); here the right singular vector of the
+//      smallest singular value comes from a one-sided Jacobi SVD in double on the same float matrix, which is at least
+//      as accurate — parity with the Eigen build is by tolerance (tests/golden/fisheye_*.npz, made with the real Eigen).
+static void kb_unproject(const float* prm, float precision, float px, float py, float out[3]) {
+    const float pwx = (px - prm[2]) / prm[0], pwy = (py - prm[3]) / prm[1];
+    float scale = 1.f;
+    float theta_d = sqrtf(pwx * pwx + pwy * pwy);
+    theta_d = fminf(fmaxf(-(float)(3.1415926535897932384626433832795 / 2.f), theta_d), (float)(3.1415926535897932384626433832795 / 2.f));
+    if (theta_d > 1e-8) {
+        float theta = theta_d;
+        for (int j = 0; j < 10; j++) {
+            const float theta2 = theta * theta, theta4 = theta2 * theta2, theta6 = theta4 * theta2, theta8 = theta4 * theta4;
+            const float k0_theta2 = prm[4] * theta2, k1_theta4 = prm[5] * theta4;
+            const float k2_theta6 = prm[6] * theta6, k3_theta8 = prm[7] * theta8;
+            const float theta_fix = (theta * (1 + k0_theta2 + k1_theta4 + k2_theta6 + k3_theta8) - theta_d) /
+                                    (1 + 3 * k0_theta2 + 5 * k1_theta4 + 7 * k2_theta6 + 9 * k3_theta8);
+            theta = theta - theta_fix;
+            if (fabsf(theta_fix) < precision) break;
+        }
+        scale = std::tan(theta) / theta_d;
+    }
+    out[0] = pwx * scale;
+    out[1] = pwy * scale;
+    out[2] = 1.f;
+}
+
+static void kb_project(const float* prm, const float v[3], float uv[2]) {
+    const float x2_plus_y2 = v[0] * v[0] + v[1] * v[1];
+    const float theta = atan2f(sqrtf(x2_plus_y2), v[2]);
+    const float psi = atan2f(v[1], v[0]);
+    const float theta2 = theta * theta;
+    const float theta3 = theta * theta2;
+    const float theta5 = theta3 * theta2;
+    const float theta7 = theta5 * theta2;
+    const float theta9 = theta7 * theta2;
+    const float r = theta + prm[4] * theta3 + prm[5] * theta5 + prm[6] * theta7 + prm[7] * theta9;
+    uv[0] = prm[0] * r * std::cos(psi) + prm[2];
+    uv[1] = prm[1] * r * std::sin(psi) + prm[3];
+}
+
+// right singular vector of the smallest singular value of a 4x4 matrix: one-sided (Hestenes) Jacobi, double
+static orc_null_vector4_fn g_nullVectorHook = nullptr;
+void orc_set_null_vector4_hook(orc_null_vector4_fn fn) { g_nullVectorHook = fn; }
+
+static void null_vector4(const float Af[4][4], double v[4]) {
+    if (g_nullVectorHook) {    // oracle/ref_eigen: the real Eigen::JacobiSVD<Matrix4f>, used to make the golden fixtures
+        float vf[4];
+        g_nullVectorHook(&Af[0][0], vf);
+        for (int i = 0; i < 4; i++) v[i] = vf[i];
+        return;
+    }
+    double U[4][4], V[4][4];
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++) {
+            U[i][j] = Af[i][j];
+            V[i][j] = i == j ? 1.0 : 0.0;
+        }
+    for (int sweep = 0; sweep < 30; sweep++) {
+        bool rotated = false;
+        for (int p = 0; p < 3; p++)
+            for (int q = p + 1; q < 4; q++) {
+                double alpha = 0, beta = 0, gamma = 0;
+                for (int i = 0; i < 4; i++) {
+                    alpha += U[i][p] * U[i][p];
+                    beta += U[i][q] * U[i][q];
+                    gamma += U[i][p] * U[i][q];
+                }
+                if (gamma == 0.0 || std::fabs(gamma) <= 1e-15 * std::sqrt(alpha * beta)) continue;
+                rotated = true;
+                const double zeta = (beta - alpha) / (2.0 * gamma);
+                const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
+                const double c = 1.0 / std::sqrt(1.0 + t * t), sn = c * t;
+                for (int i = 0; i < 4; i++) {
+                    const double up = U[i][p], uq = U[i][q];
+                    U[i][p] = c * up - sn * uq;
+                    U[i][q] = sn * up + c * uq;
+                    const double vp = V[i][p], vq = V[i][q];
+                    V[i][p] = c * vp - sn * vq;
+                    V[i][q] = sn * vp + c * vq;
+                }
+            }
+        if (!rotated) break;
+    }
+    int best = 0;
+    double bestN = 1e300;
+    for (int j = 0; j < 4; j++) {
+        double nrm = 0;
+        for (int i = 0; i < 4; i++) nrm += U[i][j] * U[i][j];
+        if (nrm < bestN) {
+            bestN = nrm;
+            best = j;
+        }
+    }
+    for (int i = 0; i < 4; i++) v[i] = V[i][best];
+}
+
+// KannalaBrandt8::TriangulateMatches (:300-363); R12 row-major.  Returns z1 or the negative reason.
+static float kb_triangulate_matches(const orc_fisheye_rig* g, float x1, float y1, float x2, float y2, float sigmaLevel,
+                                    float unc, float p3D[3], float* slack) {
+    *slack = 1e30f;    // smallest distance of a tested quantity from its threshold (relative for the chi-square gates)
+    auto note = [&](double d) { if (std::fabs(d) < *slack) *slack = (float)std::fabs(d); };
+    float r1[3], r2[3], r21[3];
+    kb_unproject(g->cam1, g->precision, x1, y1, r1);
+    kb_unproject(g->cam2, g->precision, x2, y2, r2);
+    const float* R = g->Rlr;
+    for (int i = 0; i < 3; i++) r21[i] = R[3 * i] * r2[0] + R[3 * i + 1] * r2[1] + R[3 * i + 2] * r2[2];
+    const float dot = r1[0] * r21[0] + r1[1] * r21[1] + r1[2] * r21[2];
+    const float n1 = std::sqrt(r1[0] * r1[0] + r1[1] * r1[1] + r1[2] * r1[2]);
+    const float n2 = std::sqrt(r21[0] * r21[0] + r21[1] * r21[1] + r21[2] * r21[2]);
+    const float cosParallaxRays = dot / (n1 * n2);
+    note(cosParallaxRays - 0.99998);
+    if (cosParallaxRays > 0.99998) return -1;
+    // Tcw1 = [I | 0], Tcw2 = [R21 | -R21 * t12], R21 = R12^T
+    float T2[3][4];
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) T2[i][j] = R[3 * j + i];
+        T2[i][3] = -(R[i] * g->tlr[0] + R[3 + i] * g->tlr[1] + R[6 + i] * g->tlr[2]);
+    }
+    float A[4][4];
+    const float T1[3][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}};
+    for (int j = 0; j < 4; j++) {
+        A[0][j] = r1[0] * T1[2][j] - T1[0][j];
+        A[1][j] = r1[1] * T1[2][j] - T1[1][j];
+        A[2][j] = r2[0] * T2[2][j] - T2[0][j];
+        A[3][j] = r2[1] * T2[2][j] - T2[1][j];
+    }
+    double v[4];
+    null_vector4(A, v);
+    float x3D[3];
+    if (g_nullVectorHook) {    // float division as x3Dh.head(3) / x3Dh(3)
+        for (int i = 0; i < 3; i++) x3D[i] = (float)v[i] / (float)v[3];
+    } else {
+        for (int i = 0; i < 3; i++) x3D[i] = (float)(v[i] / v[3]);
+    }
+    const float z1 = x3D[2];
+    note(z1);
+    if (!(z1 > 0)) return -2;    // z1 <= 0, and a NaN from a zero w counts as no point
+    const float z2 = T2[2][0] * x3D[0] + T2[2][1] * x3D[1] + T2[2][2] * x3D[2] + T2[2][3];
+    note(z2);
+    if (z2 <= 0) return -3;
+    float uv1[2];
+    kb_project(g->cam1, x3D, uv1);
+    const float errX1 = uv1[0] - x1, errY1 = uv1[1] - y1;
+    note((errX1 * errX1 + errY1 * errY1) / (5.991 * 8 * sigmaLevel) - 1.0);
+    if ((errX1 * errX1 + errY1 * errY1) > 5.991 * 8 * sigmaLevel) return -4;
+    float x3D2[3];
+    for (int i = 0; i < 3; i++) x3D2[i] = T2[i][0] * x3D[0] + T2[i][1] * x3D[1] + T2[i][2] * x3D[2] + T2[i][3];
+    float uv2[2];
+    kb_project(g->cam2, x3D2, uv2);
+    const float errX2 = uv2[0] - x2, errY2 = uv2[1] - y2;
+    note((errX2 * errX2 + errY2 * errY2) / (5.991 * 8 * unc) - 1.0);
+    if ((errX2 * errX2 + errY2 * errY2) > 5.991 * 8 * unc) return -5;
+    p3D[0] = x3D[0];
+    p3D[1] = x3D[1];
+    p3D[2] = x3D[2];
+    return z1;
+}
+
+int orc_stereo_fisheye_matches(const orc_keypoint* keysL, int nL, int monoL, const orc_keypoint* keysR, int nR, int monoR,
+                               const int32_t* knnIdx, const int32_t* knnDist, const orc_fisheye_rig* rig,
+                               int32_t* leftToRight, int32_t* rightToLeft, float* depth, float* p3d, int32_t* status, float* slack) {
+    for (int i = 0; i < nL; i++) {
+        if (slack) slack[i] = 1e30f;
+        leftToRight[i] = -1;
+        depth[i] = -1.0f;
+        p3d[3 * i] = p3d[3 * i + 1] = p3d[3 * i + 2] = 0.f;
+        if (status) status[i] = 0;
+    }
+    for (int i = 0; i < nR; i++) rightToLeft[i] = -1;
+    int nMatches = 0;
+    const int max_distance = 70;
+    for (int i = 0; i < nL - monoL; i++) {
+        const int d1 = knnDist[2 * i];
+        if (d1 == 0) continue;    // "Bugged point" (:1171-1175); d1 < 0 = no neighbour at all
+        if (d1 > 0 && d1 < max_distance) {
+            const int leftPos = i, rightPos = knnIdx[2 * i];
+            if (rightPos + monoR >= nR || rightPos < 0) continue;
+            const orc_keypoint& kl = keysL[leftPos + monoL];
+            const orc_keypoint& kr = keysR[rightPos + monoR];
+            const float sigma1 = rig->levelSigma2[kl.octave], sigma2 = rig->levelSigma2[kr.octave];
+            float p[3] = {0, 0, 0};
+            float sl;
+            const float dep = kb_triangulate_matches(rig, kl.x, kl.y, kr.x, kr.y, sigma1, sigma2, p, &sl);
+            if (slack) slack[leftPos + monoL] = sl;
+            if (status) status[leftPos + monoL] = dep > 0.0001f ? 1 : (dep < 0 ? (int)dep : -6);
+            if (dep > 0.0001f) {
+                leftToRight[leftPos + monoL] = rightPos + monoR;
+                rightToLeft[rightPos + monoR] = leftPos + monoL;
+                p3d[3 * (leftPos + monoL)] = p[0];
+                p3d[3 * (leftPos + monoL) + 1] = p[1];
+                p3d[3 * (leftPos + monoL) + 2] = p[2];
+                depth[leftPos + monoL] = dep;
+                nMatches++;
+            }
+        }
+    }
+    return nMatches;
+}
+
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

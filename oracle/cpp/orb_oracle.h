@@ -124,6 +124,27 @@ int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc
                                   float* prevMatchedXY, int windowSize, float mfNNratio, int checkOrientation,
                                   int32_t* vnMatches12);
 
+/* Frame::ComputeStereoFishEyeMatches after BFMatchORB (Frame.cc:1164-1204) + KannalaBrandt8::TriangulateMatches
+ * (KannalaBrandt8.cpp:300-363).  knnIdx / knnDist: k = 2 rows for the nL - monoL stereo-area left keypoints (best right
+ * index relative to monoR, distances).  status (optional, per left keypoint): 1 matched, 0 not tried, -1 .. -5 the
+ * negative return of TriangulateMatches, -6 depth <= 0.0001.  slack (optional): how close the closest gate was to
+ * flipping (absolute for cos / depths, relative for the chi-square gates) — lets a tolerance test tell a real
+ * disagreement from a decision on the edge. */
+typedef struct orc_fisheye_rig {
+    float cam1[8], cam2[8]; /* KannalaBrandt8::mvParameters fx fy cx cy k0..k3 of mpCamera / mpCamera2 */
+    float Rlr[9], tlr[3];   /* mRlr (row-major), mtlr */
+    float precision;        /* KannalaBrandt8::precision (1e-6) */
+    int32_t nlevels;
+    float levelSigma2[16];  /* mvLevelSigma2 */
+} orc_fisheye_rig;
+/* test hook: replace the restated 4x4 null-vector solve (row-major A -> v) by an external one (oracle/ref_eigen) */
+typedef void (*orc_null_vector4_fn)(const float* A, float* v);
+void orc_set_null_vector4_hook(orc_null_vector4_fn fn);
+int orc_stereo_fisheye_matches(const orc_keypoint* keysL, int nL, int monoL, const orc_keypoint* keysR, int nR, int monoR,
+                               const int32_t* knnIdx, const int32_t* knnDist, const orc_fisheye_rig* rig,
+                               int32_t* leftToRight, int32_t* rightToLeft, float* depth, float* p3d, int32_t* status,
+                               float* slack);
+
 int orc_hardware_threads(void);
 #ifdef __cplusplus
 }

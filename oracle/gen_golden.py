@@ -180,8 +180,37 @@ def gen_undistort():
     print("undistort: ok")
 
 
+def gen_fisheye():
+    """Frame::ComputeStereoFishEyeMatches / KannalaBrandt8::TriangulateMatches fixtures: the oracle's float restatement
+    with the 4x4 null vector solved by the REAL Eigen::JacobiSVD<Matrix4f> of the reference's vendored Eigen 3.4.0
+    (oracle/ref_eigen -> oracle/_ref/libeigen_svd.so; `make -C oracle ref`, needs /root/reference)."""
+    import subprocess
+    from orbslam3lib_b200 import scenes
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+    import oracle_lib
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "ref"])
+    if not oracle_lib.use_eigen_svd(True):
+        raise SystemExit("fisheye: oracle/_ref/libeigen_svd.so missing (no /root/reference here)")
+    try:
+        for name, w, h, seed, nf, ml, mr, base in (("a", 640, 400, 4301, 1500, 120, 80, 0.11),
+                                                   ("b", 752, 480, 4302, 1000, 0, 0, 0.064)):
+            img = scenes.make("texture", w, h, seed)
+            _, kl, _ = oracle_lib.OracleExtractor(nf, 1.2, 8, 20, 7)(img)
+            rig = scenes.fisheye_rig(w, h, base, seed)
+            kr, idx, dist = scenes.fisheye_stereo_case(kl, rig, seed, ml, mr)
+            ltr, rtl, depth, p3d, status, n, slack = oracle_lib.stereo_fisheye_matches(kl, ml, kr, mr, idx, dist, rig)
+            np.savez_compressed(os.path.join(GOLDEN, "fisheye_%s.npz" % name), keys_left=kl, keys_right=kr, knn_idx=idx,
+                                knn_dist=dist, rig=rig, mono=np.array([ml, mr]), ltr=ltr, rtl=rtl, depth=depth, p3d=p3d,
+                                status=status, nmatches=np.array(n), slack=slack, eigen_version=np.array("3.4.0"))
+            print("fisheye_%s: %d matches of %d rows" % (name, n, len(idx)))
+    finally:
+        oracle_lib.use_eigen_svd(False)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if "--fisheye-only" in sys.argv:
+        return gen_fisheye()
     if "--undistort-only" in sys.argv:
         return gen_undistort()
     if "--stereo-only" in sys.argv:
@@ -190,6 +219,7 @@ def main():
         return
     gen_primitives()
     gen_undistort()
+    gen_fisheye()
     for c in STEREO_CASES:
         gen_stereo(c)
     for c in EXTRACT_CASES:

@@ -329,6 +329,50 @@ def search_for_initialization(keys1, desc1, keys2, desc2, bounds, prev_matched, 
     return m12, pm, int(nm)
 
 
+FISHEYE_RIG_DTYPE = np.dtype([("cam1", "<f4", 8), ("cam2", "<f4", 8), ("Rlr", "<f4", 9), ("tlr", "<f4", 3),
+                              ("precision", "<f4"), ("nlevels", "<i4"), ("level_sigma2", "<f4", 16)])
+_EIGEN_HOOK = None
+
+
+def use_eigen_svd(on=True):
+    """Route the 4x4 null-vector solve of the fisheye oracle through the reference's vendored Eigen 3.4.0
+    (oracle/_ref/libeigen_svd.so, `make -C oracle ref`; exists only where /root/reference does).  Fixture generation
+    and the restatement-vs-Eigen test use it; returns False when the helper is not built."""
+    global _EIGEN_HOOK
+    L = lib()
+    L.orc_set_null_vector4_hook.argtypes = [C.c_void_p]
+    if not on:
+        L.orc_set_null_vector4_hook(None)
+        return True
+    so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_ref", "libeigen_svd.so")
+    if not os.path.exists(so):
+        return False
+    if _EIGEN_HOOK is None:
+        _EIGEN_HOOK = C.CDLL(so)
+    L.orc_set_null_vector4_hook(C.cast(_EIGEN_HOOK.ref_null_vector4, C.c_void_p))
+    return True
+
+
+def stereo_fisheye_matches(keys_left, mono_left, keys_right, mono_right, knn_idx, knn_dist, rig):
+    """Frame::ComputeStereoFishEyeMatches after BFMatchORB (Frame.cc:1164-1204).
+    -> (mvLeftToRightMatch, mvRightToLeftMatch, mvDepth, mvStereo3Dpoints (nL, 3), status, nMatches, slack)"""
+    kl = np.ascontiguousarray(keys_left, KP_DTYPE)
+    kr = np.ascontiguousarray(keys_right, KP_DTYPE)
+    ki = np.ascontiguousarray(knn_idx, np.int32)
+    kd = np.ascontiguousarray(knn_dist, np.int32)
+    rg = np.ascontiguousarray(rig, FISHEYE_RIG_DTYPE)
+    nl, nr = kl.shape[0], kr.shape[0]
+    ltr, rtl = np.empty(nl, np.int32), np.empty(nr, np.int32)
+    depth, p3d, status = np.empty(nl, np.float32), np.empty((nl, 3), np.float32), np.empty(nl, np.int32)
+    slack = np.empty(nl, np.float32)
+    L = lib()
+    L.orc_stereo_fisheye_matches.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9
+    L.orc_stereo_fisheye_matches.restype = C.c_int
+    n = L.orc_stereo_fisheye_matches(_p(kl), nl, int(mono_left), _p(kr), nr, int(mono_right), _p(ki), _p(kd), _p(rg),
+                                     _p(ltr), _p(rtl), _p(depth), _p(p3d), _p(status), _p(slack))
+    return ltr, rtl, depth, p3d, status, int(n), slack
+
+
 def undistort_keypoints(kps, fx, fy, cx, cy, dist):
     """Frame::UndistortKeyPoints (Frame.cc:763-796) -> mvKeysUn."""
     k = np.ascontiguousarray(kps, KP_DTYPE)

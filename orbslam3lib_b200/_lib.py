@@ -80,6 +80,8 @@ SYMBOLS = {
                                                      _u]),
     "orbfe_search_for_initialization_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, C.c_float, _i, _vp,
                                                    _vp, _vp, _u]),
+    "orbfe_stereo_fisheye_matches_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp,
+                                                _vp, _vp, _vp, _u]),
     "orbfe_undistort_keypoints": (_i, [_vp, _vp, _i64, C.c_float, C.c_float, C.c_float, C.c_float, _vp, _i, _vp, _u]),
     "orbfe_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, C.c_float, _i, C.c_float,
                                         C.c_float, _vp, _vp, _vp]),

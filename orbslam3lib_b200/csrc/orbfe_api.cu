@@ -35,6 +35,10 @@ int launch_search_by_projection_stereo(const float bounds[4], const float* scale
                                        const uint8_t* occupied, const int* nFeat, const int* nLeft, const int* ltr,
                                        const int* rtl, int cap, const void* pts, const int* nPts, int ptsCap, int nframes,
                                        int* matchL, int* matchR, int* owner, int* nMatches, cudaStream_t st);
+int launch_fisheye_matches(const void* rig, int cap, int knnCap, int nframes, const orbfe_keypoint* keysL,
+                           const orbfe_keypoint* keysR, const int* nL, const int* nR, const int* monoL, const int* monoR,
+                           const int* knnIdx, const int* knnDist, int* ltr, int* rtl, float* depth, float* p3d, int* status,
+                           int* nMatches, cudaStream_t st);
 size_t search_init_smem_bytes(int cap);
 int launch_search_for_initialization(const float bounds[4], int windowSize, float nnRatio, int checkOrientation,
                                      const orbfe_keypoint* keys1, const uint8_t* desc1, const int* n1,
@@ -1320,6 +1324,70 @@ int orbfe_search_for_initialization_batch(orbfe_matcher* m, const orbfe_keypoint
     if (!outDev) {
         ORBFE_MCUDA(m, cudaMemcpyAsync(matches12, dM, F * cap * 4, cudaMemcpyDeviceToHost, st));
         if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_stereo_fisheye_matches_batch(orbfe_matcher* m, const orbfe_keypoint* keys_left, const orbfe_keypoint* keys_right,
+                                       const int32_t* n_left, const int32_t* n_right, const int32_t* mono_left,
+                                       const int32_t* mono_right, int cap, const int32_t* knn_idx, const int32_t* knn_dist,
+                                       int knn_cap, int nframes, const orbfe_fisheye_rig* rig, int32_t* left_to_right,
+                                       int32_t* right_to_left, float* depth, float* points3d, int32_t* status,
+                                       int32_t* nmatches, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (nframes < 0 || cap < 0 || knn_cap < 0) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (nframes == 0) return ORBFE_OK;
+    if (!rig || !n_left || !n_right || !nmatches ||
+        (cap > 0 && (!keys_left || !keys_right || !left_to_right || !right_to_left || !depth || !points3d)) ||
+        (cap > 0 && knn_cap > 0 && (!knn_idx || !knn_dist)))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (rig->nlevels < 1 || rig->nlevels > ORBFE_MAX_LEVELS) return set_merr(m, ORBFE_ERR_ARG, "bad rig.nlevels");
+    for (int i = 0; i < 2; i++)
+        if (rig->cam1[i] == 0.f || rig->cam2[i] == 0.f) return set_merr(m, ORBFE_ERR_ARG, "zero focal length");
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    if (cap == 0) {
+        if (!outDev)
+            for (int f = 0; f < nframes; f++) nmatches[f] = 0;
+        return ORBFE_OK;
+    }
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)nframes;
+    const void* dIn[8] = {keys_left, keys_right, n_left, n_right, mono_left, mono_right, knn_idx, knn_dist};
+    const size_t inBytes[8] = {F * cap * sizeof(orbfe_keypoint), F * cap * sizeof(orbfe_keypoint), F * 4, F * 4, F * 4, F * 4,
+                               F * knn_cap * 8, F * knn_cap * 8};
+    if (!inDev)
+        for (int i = 0; i < 8; i++) {
+            if (!dIn[i]) continue;
+            ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(inBytes[i], 16)));
+            if (inBytes[i]) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, dIn[i], inBytes[i], cudaMemcpyHostToDevice, st));
+            dIn[i] = m->dS[i].p;
+        }
+    void* dOut[6] = {left_to_right, right_to_left, depth, points3d, status, nmatches};
+    const size_t outBytes[6] = {F * cap * 4, F * cap * 4, F * cap * 4, F * cap * 12, F * cap * 4, F * 4};
+    if (!outDev)
+        for (int i = 0; i < 6; i++) {
+            if (!dOut[i]) continue;
+            ORBFE_MCUDA(m, m->dS[8 + i].reserve(outBytes[i]));
+            dOut[i] = m->dS[8 + i].p;
+        }
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_fisheye_matches(rig, cap, knn_cap, nframes, (const orbfe_keypoint*)dIn[0],
+                                                (const orbfe_keypoint*)dIn[1], (const int*)dIn[2], (const int*)dIn[3],
+                                                (const int*)dIn[4], (const int*)dIn[5], (const int*)dIn[6], (const int*)dIn[7],
+                                                (int*)dOut[0], (int*)dOut[1], (float*)dOut[2], (float*)dOut[3], (int*)dOut[4],
+                                                (int*)dOut[5], st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        void* hOut[6] = {left_to_right, right_to_left, depth, points3d, status, nmatches};
+        for (int i = 0; i < 6; i++)
+            if (hOut[i]) ORBFE_MCUDA(m, cudaMemcpyAsync(hOut[i], dOut[i], outBytes[i], cudaMemcpyDeviceToHost, st));
     }
     ORBFE_MCUDA(m, cudaStreamSynchronize(st));
     cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);

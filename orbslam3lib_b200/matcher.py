@@ -188,6 +188,34 @@ class ORBmatcher:
             int(windowSize), self.mfNNratio, int(self.mbCheckOrientation), ptr(prev_matched), ptr(matches12), ptr(nmatches),
             int(flags)))
 
+    def ComputeStereoFishEyeMatches(self, keys_left, mono_left, keys_right, mono_right, knn_idx, knn_dist, rig):
+        """Frame::ComputeStereoFishEyeMatches after BFMatchORB (Frame.cc:1164-1204): knn_idx / knn_dist = knnMatch of the
+        stereo-area left descriptors against the stereo-area right ones; rig: scenes.FISHEYE_RIG_DTYPE.
+        -> (nMatches, mvLeftToRightMatch, mvRightToLeftMatch, mvDepth, mvStereo3Dpoints (Nleft, 3), status)"""
+        kl = np.ascontiguousarray(keys_left, KP_DTYPE)
+        kr = np.ascontiguousarray(keys_right, KP_DTYPE)
+        nl, nr = kl.shape[0], kr.shape[0]
+        cap = max(nl, nr, 1)
+        K = np.zeros((2, cap), KP_DTYPE)
+        K[0, :nl], K[1, :nr] = kl, kr
+        ki = np.ascontiguousarray(knn_idx, np.int32).reshape(-1, 2)
+        kd = np.ascontiguousarray(knn_dist, np.int32).reshape(-1, 2)
+        a = [np.array([v], np.int32) for v in (nl, nr, mono_left, mono_right, 0)]
+        ltr, rtl, st = (np.empty(cap, np.int32) for _ in range(3))
+        depth, p3d = np.empty(cap, np.float32), np.empty((cap, 3), np.float32)
+        self.stereo_fisheye_matches_batch_raw(K[0], K[1], a[0], a[1], a[2], a[3], cap, ki, kd, ki.shape[0], 1, rig, ltr, rtl,
+                                              depth, p3d, st, a[4])
+        return int(a[4][0]), ltr[:nl], rtl[:nr], depth[:nl], p3d[:nl], st[:nl]
+
+    def stereo_fisheye_matches_batch_raw(self, keys_left, keys_right, n_left, n_right, mono_left, mono_right, cap, knn_idx,
+                                         knn_dist, knn_cap, nframes, rig, ltr, rtl, depth, p3d, status, nmatches, flags=0):
+        from .scenes import FISHEYE_RIG_DTYPE
+        rg = np.ascontiguousarray(rig, FISHEYE_RIG_DTYPE)
+        self._bf._check(_lib.lib().orbfe_stereo_fisheye_matches_batch(
+            self._bf._h, ptr(keys_left), ptr(keys_right), ptr(n_left), ptr(n_right), ptr(mono_left), ptr(mono_right),
+            int(cap), ptr(knn_idx), ptr(knn_dist), int(knn_cap), int(nframes), ptr(rg), ptr(ltr), ptr(rtl), ptr(depth),
+            ptr(p3d), ptr(status), ptr(nmatches), int(flags)))
+
     def UndistortKeyPoints(self, keys, K, dist_coef):
         """Frame::UndistortKeyPoints (Frame.cc:763-796): keys (KP_DTYPE), K = 3x3 mK or (fx, fy, cx, cy), mDistCoef ->
         mvKeysUn."""

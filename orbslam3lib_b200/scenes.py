@@ -209,6 +209,97 @@ def track_points_stereo(keys, desc, nleft, ltr, nlevels, npts, seed, jitter=3.0,
     return pts
 
 
+# == orbfe_fisheye_rig / orc_fisheye_rig
+FISHEYE_RIG_DTYPE = np.dtype([("cam1", "<f4", 8), ("cam2", "<f4", 8), ("Rlr", "<f4", 9), ("tlr", "<f4", 3),
+                              ("precision", "<f4"), ("nlevels", "<i4"), ("level_sigma2", "<f4", 16)])
+assert FISHEYE_RIG_DTYPE.itemsize == 184
+
+
+def fisheye_rig(w=640, h=400, baseline=0.11, seed=0, nlevels=8, scale=1.2):
+    """a Kannala-Brandt stereo rig like the Lynx / TUM-VI ones: ~190 px focal length, small relative rotation."""
+    r = rand_u32(16, seed ^ 0xF15E).astype(np.float64) / 2.0**32 - 0.5
+    rig = np.zeros((), FISHEYE_RIG_DTYPE)
+    for cam, o in (("cam1", 0), ("cam2", 4)):
+        rig[cam] = (190.9 + 4 * r[o], 190.2 + 4 * r[o + 1], w / 2 + 6 * r[o + 2], h / 2 + 6 * r[o + 3],
+                    0.0034, 0.0007, -0.0020, 0.0002)
+    ax = 0.02 * r[8:11]                                   # Rodrigues vector of Rlr
+    th = float(np.linalg.norm(ax))
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]]) / max(th, 1e-12)
+    R = np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * (K @ K)
+    rig["Rlr"] = R.reshape(-1)
+    rig["tlr"] = (baseline, 0.004 * r[11], 0.004 * r[12])
+    rig["precision"] = 1e-6
+    rig["nlevels"] = nlevels
+    rig["level_sigma2"][:nlevels] = (np.float32(scale) ** np.arange(nlevels, dtype=np.float32)) ** 2
+    return rig
+
+
+def _kb_unproject64(prm, x, y):
+    px, py = (x - prm[2]) / prm[0], (y - prm[3]) / prm[1]
+    td = np.minimum(np.sqrt(px * px + py * py), np.pi / 2)
+    th = td.copy()
+    for _ in range(12):
+        t2 = th * th
+        f = th * (1 + prm[4] * t2 + prm[5] * t2**2 + prm[6] * t2**3 + prm[7] * t2**4) - td
+        df = 1 + 3 * prm[4] * t2 + 5 * prm[5] * t2**2 + 7 * prm[6] * t2**3 + 9 * prm[7] * t2**4
+        th = th - f / df
+    sc = np.where(td > 1e-8, np.tan(th) / np.maximum(td, 1e-12), 1.0)
+    return np.stack([px * sc, py * sc, np.ones_like(px)], 1)
+
+
+def _kb_project64(prm, X):
+    th = np.arctan2(np.sqrt(X[:, 0]**2 + X[:, 1]**2), X[:, 2])
+    psi = np.arctan2(X[:, 1], X[:, 0])
+    r = th + prm[4] * th**3 + prm[5] * th**5 + prm[6] * th**7 + prm[7] * th**9
+    return np.stack([prm[0] * r * np.cos(psi) + prm[2], prm[1] * r * np.sin(psi) + prm[3]], 1)
+
+
+def fisheye_stereo_case(kps_left, rig, seed, mono_left=0, mono_right=0, n_right=None):
+    """Right keypoints and a BFMatchORB result for a left keypoint set seen by `rig`: every stereo-area left keypoint
+    gets a depth (0.3 m .. 60 m, a few at infinity = no parallax), is re-projected into camera 2 with 0 .. 4 px of noise
+    (some fail the chi-square gate), a few partners are behind the camera or shared by two left keypoints, and the
+    descriptor distances cover 0 ("bugged point"), < 70 and >= 70.  -> (kps_right, knn_idx (ns, 2), knn_dist (ns, 2))"""
+    from ._lib import KP_DTYPE
+    nl = len(kps_left)
+    ns = nl - mono_left
+    n_right = ns + mono_right if n_right is None else n_right
+    nsr = n_right - mono_right
+    u = rand_u32(8 * max(ns, 1), seed ^ 0xF1E).reshape(8, -1).astype(np.float64) / 2.0**32
+    kl = kps_left[mono_left:]
+    c1, c2 = rig["cam1"].astype(np.float64), rig["cam2"].astype(np.float64)
+    R12, t12 = rig["Rlr"].astype(np.float64).reshape(3, 3), rig["tlr"].astype(np.float64)
+    ray = _kb_unproject64(c1, kl["x"].astype(np.float64), kl["y"].astype(np.float64))
+    z = 0.3 * (200.0 ** u[0])                               # log-uniform 0.3 .. 60 m
+    z = np.where(u[1] < 0.05, 1e5, z)                       # no parallax
+    z = np.where((u[1] >= 0.05) & (u[1] < 0.08), -z, z)     # behind camera 1: lands anywhere
+    X1 = ray * z[:, None]
+    X2 = (X1 - t12) @ R12                                   # R21 * (X1 - t12), R21 = R12^T
+    uv = _kb_project64(c2, X2)
+    amp = np.where(u[2] < 0.7, 0.4, 4.0)                    # most matches are sub-pixel accurate
+    uv = uv + amp[:, None] * (np.stack([u[3], u[4]], 1) - 0.5) * 2
+    kr = np.zeros(n_right, KP_DTYPE)
+    kr["x"][:mono_right] = 5.0
+    kr["y"][:mono_right] = 5.0
+    idx = np.full((ns, 2), -1, np.int32)
+    dist = np.full((ns, 2), -1, np.int32)
+    if nsr > 0 and ns > 0:
+        perm = (rand_u32(ns, seed ^ 0xBEEF) % np.uint32(nsr)).astype(np.int64)     # collisions: shared right partners
+        first = np.full(nsr, -1, np.int64)
+        for i in range(ns - 1, -1, -1):
+            first[perm[i]] = i                              # the right keypoint sits where its FIRST left partner projects
+        has = first >= 0
+        kr["x"][mono_right:][has] = uv[first[has], 0].astype(np.float32)
+        kr["y"][mono_right:][has] = uv[first[has], 1].astype(np.float32)
+        kr["octave"][mono_right:] = (rand_u32(nsr, seed ^ 0x0C7) % 8).astype(np.int32)
+        idx[:, 0] = perm
+        idx[:, 1] = (perm + 1) % nsr
+        d = (u[5] * 90).astype(np.int32) + 1
+        d = np.where(u[6] < 0.02, 0, d)                     # bugged points
+        dist[:, 0] = d
+        dist[:, 1] = d + (u[7] * 40).astype(np.int32)
+    return kr, idx, dist
+
+
 SCENES = {"noise": noise, "checker": checker, "texture": texture, "flat_blobs": flat_blobs}
 
 
