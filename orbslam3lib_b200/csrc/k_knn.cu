@@ -11,6 +11,8 @@
 // The small-problem variant (knn2_warp_kernel) gives a warp to every query and spreads the train rows over the
 // lanes, finishing with a warp-shuffle top-2 merge: per-frame stereo matching (500..1200 rows) would otherwise
 // occupy only a handful of CTAs.
+#include <cstdlib>
+
 #include "orbfe_internal.h"
 
 namespace orbfe {
@@ -104,6 +106,191 @@ __global__ void __launch_bounds__(KNN_THREADS) knn2_kernel(const uint8_t* __rest
     }
 }
 
+// ---- tensor-core variant -------------------------------------------------------------------------------------------
+// All-pairs Hamming is a binary GEMM: hamming(a, b) = |a| + sum_k b_k * (1 - 2 a_k).  knn2_kernel is bound by the POPC
+// pipe (8 POPC per pair: ~0.55 Tpairs/s on a B200); here the sums run on the tensor cores as int8 IMMA (mma.sync
+// m16n8k32 s8 with A' = 1 - 2a in {+1, -1} and B = b in {0, 1}: sm_100a has no native 1-bit MMA — ptxas emulates b1 with
+// the same IMMA — and exact integer accumulation is wanted, so not fp8).  The accumulator is hamming - |a| directly.
+// The k order of a dot product is free as long as both operands use the same one, so bits are expanded to bytes with a
+// shift and a mask, never transposed: thread (g, tg) of a warp owns words 2tg, 2tg+1 of "its" row, and k-step s takes
+// (word >> s) & 0x01010101.
+//   * CTA = 8 warps x 32 query rows; the expanded A' fragments (2 m16 tiles x 8 k-steps x 4 registers) stay in
+//     registers for the whole kernel;
+//   * train rows are expanded ONCE per CTA while they are staged into shared memory (double buffered), already in
+//     fragment order: [n8 tile][register quad][lane] x 16 B, so both the staging STS.128 and the four LDS.128 that
+//     fetch the B fragments of an n8 tile are contiguous per warp; 16 IMMAs per n8 tile and warp;
+//   * epilogue on the accumulator fragment: key = acc << S | j orders by (distance, train index) for a fixed row (|a|
+//     is a per-row constant, added at the end), top-2 by min/max as in knn2_kernel, merged across the four lanes of a
+//     quad by shuffles: 1 IMAD (fma pipe) + 2.5 min/max per pair instead of 8 XOR + 8 POPC + 7 ADD + 4.
+constexpr int KM_THREADS = 256;
+constexpr int KM_ROWS = 256;     // query rows per CTA
+constexpr int KM_TILE = 128;     // train rows per shared-memory tile (32 KB expanded)
+constexpr int KM_S = 22;         // index bits of a key; hamming - |a| is in [-256, 256]
+constexpr int KM_EMPTY = 0x7fffffff;
+constexpr int KM_SMEM = 2 * KM_TILE * 256;
+
+__device__ __forceinline__ void top2_update_s(int& b1, int& b2, int k) {
+    b2 = min(b2, max(b1, k));
+    b1 = min(b1, k);
+}
+
+__device__ __forceinline__ void imma_16832(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void merge_super_s(int& d1, int& i1, int& d2, int& i2, int b, int na, long long base) {
+    if (b == KM_EMPTY) return;
+    const int d = (b >> KM_S) + na;
+    const int i = (int)(base + (long long)(b & ((1 << KM_S) - 1)));
+    if (i1 < 0 || d < d1) { d2 = d1; i2 = i1; d1 = d; i1 = i; }
+    else if (i2 < 0 || d < d2) { d2 = d; i2 = i; }
+}
+
+// grid (ceil(maxNq / KM_ROWS), npairs); dynamic shared memory KM_SMEM
+__global__ void __launch_bounds__(KM_THREADS, 2) knn2_mma_kernel(const uint8_t* __restrict__ q, const int* __restrict__ nqArr,
+                                                                 long long qCap, const uint8_t* __restrict__ t,
+                                                                 const int* __restrict__ ntArr, long long tCap,
+                                                                 long long nqSingle, long long ntSingle,
+                                                                 int32_t* __restrict__ idx, int32_t* __restrict__ dist) {
+    extern __shared__ __align__(16) uint8_t kmSmem[];
+    uint4* expB = reinterpret_cast<uint4*>(kmSmem);    // [2][KM_TILE / 8][4][32] uint4
+    const int pair = blockIdx.y;
+    const long long nq = nqArr ? nqArr[pair] : nqSingle;
+    const long long nt = ntArr ? ntArr[pair] : ntSingle;
+    if ((long long)blockIdx.x * KM_ROWS >= nq) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, tg = lane & 3;
+    const long long rowBase = (long long)blockIdx.x * KM_ROWS + warp * 32;
+    const uint2* tp = reinterpret_cast<const uint2*>(t + (long long)pair * tCap * 32);
+    constexpr uint32_t M = 0x01010101u;
+
+    // A' fragments: rows rowBase + mt * 16 + g + 8 * h, words 2tg and 2tg + 1; bytes +1 (bit clear) / -1 (bit set)
+    uint32_t A[2][8][4];
+    int na[4];
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const long long row = rowBase + mt * 16 + g + 8 * h;
+            uint2 w = make_uint2(0u, 0u);
+            if (row < nq) w = __ldg(reinterpret_cast<const uint2*>(q + ((long long)pair * qCap + row) * 32) + tg);
+            int pc = __popc(w.x) + __popc(w.y);
+            pc += __shfl_xor_sync(0xffffffffu, pc, 1);
+            pc += __shfl_xor_sync(0xffffffffu, pc, 2);
+            na[mt * 2 + h] = pc;
+#pragma unroll
+            for (int s = 0; s < 8; s++) {
+                A[mt][s][h] = (((w.x >> s) & M) * 0xffu) | M;
+                A[mt][s][2 + h] = (((w.y >> s) & M) * 0xffu) | M;
+            }
+        }
+
+    int d1[4], i1[4], d2[4], i2[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) d1[r] = i1[r] = d2[r] = i2[r] = -1;
+
+    for (long long sb = 0; sb < nt; sb += (1ll << KM_S)) {
+        const int ns = (int)min(nt - sb, 1ll << KM_S);
+        int b1[4], b2[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) b1[r] = b2[r] = KM_EMPTY;
+        const int ntiles = (ns + KM_TILE - 1) / KM_TILE;
+        // a tile is 512 (row, tg) items of 8 bytes: thread t stages items t and t + 256; item e = row * 4 + tg is lane
+        // (row & 7) * 4 + tg of n8 tile row >> 3, i.e. fragment slot e
+        auto fetch = [&](int j0, uint2 (&v)[2]) {
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                const int e = tid + u * KM_THREADS;
+                v[u] = make_uint2(0u, 0u);
+                if (j0 + (e >> 2) < ns) v[u] = __ldg(tp + (sb + j0) * 4 + e);
+            }
+        };
+        auto stage = [&](int buf, const uint2 (&v)[2]) {
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                const int e = tid + u * KM_THREADS;
+                uint4* dst = expB + buf * (KM_TILE * 16) + (e >> 5) * 128 + (e & 31);
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    dst[k * 32] = make_uint4((v[u].x >> (2 * k)) & M, (v[u].y >> (2 * k)) & M, (v[u].x >> (2 * k + 1)) & M,
+                                             (v[u].y >> (2 * k + 1)) & M);
+            }
+        };
+        uint2 nx[2];
+        fetch(0, nx);
+        stage(0, nx);
+        __syncthreads();
+        for (int ti = 0; ti < ntiles; ti++) {
+            const int cur = ti & 1;
+            const int j0 = ti * KM_TILE;
+            const bool haveNext = ti + 1 < ntiles;
+            if (haveNext) fetch(j0 + KM_TILE, nx);
+            const uint4* fb = expB + cur * (KM_TILE * 16) + lane;
+            const int rows = min(KM_TILE, ns - j0);
+            const int full = rows >> 3;    // n8 tiles without padded columns
+            auto n8tile = [&](int n8, bool guard) {
+                const uint4 f0 = fb[n8 * 128], f1 = fb[n8 * 128 + 32], f2 = fb[n8 * 128 + 64], f3 = fb[n8 * 128 + 96];
+                int acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+                imma_16832(acc[0], A[0][0], f0.x, f0.y);
+                imma_16832(acc[1], A[1][0], f0.x, f0.y);
+                imma_16832(acc[0], A[0][1], f0.z, f0.w);
+                imma_16832(acc[1], A[1][1], f0.z, f0.w);
+                imma_16832(acc[0], A[0][2], f1.x, f1.y);
+                imma_16832(acc[1], A[1][2], f1.x, f1.y);
+                imma_16832(acc[0], A[0][3], f1.z, f1.w);
+                imma_16832(acc[1], A[1][3], f1.z, f1.w);
+                imma_16832(acc[0], A[0][4], f2.x, f2.y);
+                imma_16832(acc[1], A[1][4], f2.x, f2.y);
+                imma_16832(acc[0], A[0][5], f2.z, f2.w);
+                imma_16832(acc[1], A[1][5], f2.z, f2.w);
+                imma_16832(acc[0], A[0][6], f3.x, f3.y);
+                imma_16832(acc[1], A[1][6], f3.x, f3.y);
+                imma_16832(acc[0], A[0][7], f3.z, f3.w);
+                imma_16832(acc[1], A[1][7], f3.z, f3.w);
+                const int jc = j0 + n8 * 8 + 2 * tg;    // this thread's columns: jc, jc + 1
+                const bool ok0 = !guard || jc < ns, ok1 = !guard || jc + 1 < ns;
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    const int k0 = acc[mt][0] * (1 << KM_S) + jc, k1 = acc[mt][1] * (1 << KM_S) + (jc + 1);
+                    const int k2 = acc[mt][2] * (1 << KM_S) + jc, k3 = acc[mt][3] * (1 << KM_S) + (jc + 1);
+                    top2_update_s(b1[mt * 2], b2[mt * 2], ok0 ? k0 : KM_EMPTY);
+                    top2_update_s(b1[mt * 2], b2[mt * 2], ok1 ? k1 : KM_EMPTY);
+                    top2_update_s(b1[mt * 2 + 1], b2[mt * 2 + 1], ok0 ? k2 : KM_EMPTY);
+                    top2_update_s(b1[mt * 2 + 1], b2[mt * 2 + 1], ok1 ? k3 : KM_EMPTY);
+                }
+            };
+#pragma unroll 2
+            for (int n8 = 0; n8 < full; n8++) n8tile(n8, false);
+            if (rows & 7) n8tile(full, true);
+            if (haveNext) stage(cur ^ 1, nx);
+            __syncthreads();
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+#pragma unroll
+            for (int o = 1; o <= 2; o <<= 1) {
+                const int o1 = __shfl_xor_sync(0xffffffffu, b1[r], o), o2 = __shfl_xor_sync(0xffffffffu, b2[r], o);
+                b2[r] = min(max(b1[r], o1), min(b2[r], o2));
+                b1[r] = min(b1[r], o1);
+            }
+            merge_super_s(d1[r], i1[r], d2[r], i2[r], b1[r], na[r], sb);
+            merge_super_s(d1[r], i1[r], d2[r], i2[r], b2[r], na[r], sb);
+        }
+    }
+    if (tg == 0) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const long long row = rowBase + (r >> 1) * 16 + g + 8 * (r & 1);
+            if (row < nq) {
+                const long long o = ((long long)pair * qCap + row) * 2;
+                *reinterpret_cast<int2*>(idx + o) = make_int2(i1[r], i2[r]);
+                *reinterpret_cast<int2*>(dist + o) = make_int2(d1[r], d2[r]);
+            }
+        }
+    }
+}
+
 // small problems: one warp per query, train rows strided over the lanes, warp-shuffle top-2 merge.
 // grid (ceil(maxNq / 8), npairs); block 256.  nt < 2^23 per pair (the host dispatches).
 __global__ void __launch_bounds__(KNN_THREADS) knn2_warp_kernel(const uint8_t* __restrict__ q,
@@ -145,6 +332,15 @@ __global__ void __launch_bounds__(KNN_THREADS) knn2_warp_kernel(const uint8_t* _
     }
 }
 
+// ORBFE_KNN_MMA=0 selects the POPC kernel (A/B measurements); default: tensor cores
+static bool knn_use_mma() {
+    static const int v = [] {
+        const char* e = getenv("ORBFE_KNN_MMA");
+        return e ? atoi(e) : 1;
+    }();
+    return v != 0;
+}
+
 int launch_knn2(const uint8_t* q, const int* nq, long long qCap, const uint8_t* t, const int* nt, long long tCap,
                 int npairs, long long nqSingle, long long ntSingle, long long maxNq, long long maxNt, int32_t* idx,
                 int32_t* dist, cudaStream_t st) {
@@ -154,6 +350,16 @@ int launch_knn2(const uint8_t* q, const int* nq, long long qCap, const uint8_t* 
     if (ctasBig < 296 && maxNt < (1ll << KNN_SUPER_BITS)) {
         const dim3 grid((unsigned)((maxNq + 7) / 8), npairs);
         knn2_warp_kernel<<<grid, KNN_THREADS, 0, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist);
+    } else if (knn_use_mma()) {
+        const dim3 grid((unsigned)((maxNq + KM_ROWS - 1) / KM_ROWS), npairs);
+        static unsigned long long configured = 0;    // one bit per device: the attribute is per context
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (!((configured >> (dev & 63)) & 1ull)) {
+            cudaFuncSetAttribute(knn2_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KM_SMEM);
+            configured |= 1ull << (dev & 63);
+        }
+        knn2_mma_kernel<<<grid, KM_THREADS, KM_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist);
     } else {
         const dim3 grid((unsigned)((maxNq + KNN_THREADS - 1) / KNN_THREADS), npairs);
         knn2_kernel<<<grid, KNN_THREADS, 0, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist);

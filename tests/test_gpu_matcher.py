@@ -73,3 +73,36 @@ def test_ratio_test():
     dist = np.array([[10, 20], [5, -1], [70, 100]], np.int32)
     out = BFMatcher.ratio_test(idx, dist, 0.7)
     assert out.tolist() == [3, -1, -1]    # 10 < 14; no second neighbour; 70 < 70 is false
+
+
+def test_tensor_core_path_ties_and_ragged(oracle):
+    """the IMMA kernel (taken from 296 CTAs up): duplicate and all-equal train rows (ties -> lowest index, also across
+    the lanes of a quad and across shared-memory tiles), train counts that are no multiple of 8 or 256, partial query
+    tiles, all-zero and all-one descriptors (|a| = 0 / 256)."""
+    p, cap = 320, 300
+    rng = np.random.default_rng(17)
+    nq = rng.integers(1, cap + 1, p).astype(np.int32)
+    nt = rng.integers(1, cap + 1, p).astype(np.int32)
+    nq[:4], nt[:4] = (cap, 257, 1, 255), (cap, 263, 2, 1)
+    q = scenes.descriptors(p * cap, 21).reshape(p, cap, 32)
+    t = scenes.descriptors(p * cap, 22).reshape(p, cap, 32)
+    t[0, 100:200] = t[0, 7]                 # a run of identical train rows
+    q[0, :50] = t[0, 7]
+    t[1, :] = t[1, 0]                       # all-equal train set
+    q[5, 0], q[5, 1] = 0, 255
+    t[5, 3], t[5, 4] = 0, 255
+    idx, dist = BFMatcher().knnMatchBatch(q, nq, t, nt)
+    for k in list(range(8)) + list(range(8, p, 13)):
+        ri, rd = oracle.knn2_hamming(q[k, :nq[k]], t[k, :nt[k]])
+        np.testing.assert_array_equal(idx[k, :nq[k]], ri)
+        np.testing.assert_array_equal(dist[k, :nq[k]], rd)
+    assert idx[0, 0].tolist() == [7, 100] and dist[0, 0].tolist() == [0, 0]
+
+
+def test_tensor_core_path_large_single(oracle):
+    q, t = scenes.map_descriptors(100001, 5003, 31, dup_frac=0.05)
+    idx, dist = BFMatcher().knnMatch(q, t)
+    sel = np.concatenate([np.arange(0, 100001, 211), np.arange(99990, 100001)])
+    ri, rd = oracle.knn2_hamming(q[sel], t, threads=4)
+    np.testing.assert_array_equal(idx[sel], ri)
+    np.testing.assert_array_equal(dist[sel], rd)
