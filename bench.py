@@ -45,6 +45,20 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
 
 
+# mma.sync m16n8k32 s8 (IMMA.16832) issue-bound peak measured on this pool's B200 with tools/ubench/mma_probe.cu:
+# 1133 Tops/s = 2.21 Tpairs/s of 256-bit descriptors.  (tcgen05 int8 would be ~4x that; the kernel uses mma.sync.)
+IMMA_PEAK_TOPS = 1133.0
+
+
+def knn_roofline(gpairs, world):
+    """kNN kernels are tensor-bound: 512 int8 multiply-adds-as-ops per descriptor pair."""
+    tops = gpairs * 1e9 * 512 * 1e-12
+    return {"bound": "tensor", "achieved": round(tops, 1), "peak": IMMA_PEAK_TOPS * world, "unit": "Tops/s (int8 IMMA)",
+            "frac": round(tops / (IMMA_PEAK_TOPS * world), 4),
+            "peak_source": "measured: mma.sync m16n8k32 s8 issue peak, tools/ubench/mma_probe.cu (1 GPU)",
+            "popc_kernel_ceiling_gpairs": round(world * 148 * 2.0 * 1.92, 1)}
+
+
 class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
@@ -150,7 +164,7 @@ def map_knn_leg(args, rank, world, local, dev, dist, matcher):
         out = {"workload": "c5: %d x %d 256-bit descriptors, k=2, query rows sharded over %d GPU(s), NCCL train "
                            "broadcast + result exchange" % (nq, nt, world),
                "ms_per_step": ms, "gpairs_per_s": gp, "scaling": "strong", "steps": args.map_steps,
-               "frac_popc_pipe": gp / (world * 148 * 2.0 * sm_mhz * 1e-3),
+               "roofline": knn_roofline(gp, world),
                "checksum": int((idx.astype(np.int64) * 31 + dd).sum() & 0xFFFFFFFFFFFF),
                "parity_sample": {"rows": int(len(sel)), "vs": "CPU oracle", "ok": ok}}
     sm.close()
@@ -593,8 +607,7 @@ def main():
         if k == "knn" and v > 0:
             gp = pairs_per_step / (v * 1e-3) * 1e-9
             e["gpairs_per_s"] = round(gp, 2)
-            # POPC pipe: 16 lanes/clk/SM measured (tools/ubench_pipes.cu), 8 POPC per pair, 148 SMs
-            e["frac_popc_pipe"] = round(gp / (148 * 2.0 * sm_mhz * 1e-3), 4)
+            e["roofline"] = knn_roofline(gp, 1)
         stage_report[k] = e
     hbm_stages = [k for k in ("pyramid", "fast", "blur") if per.get(k, 0) > 0]
     dom = max(hbm_stages, key=lambda k: per[k])
@@ -605,7 +618,10 @@ def main():
     if os.path.exists(tp):    # dram bytes per image from the committed ncu --set full capture (not measured in this run)
         tall = json.load(open(tp))
         tj = tall["dram_bytes_per_image"]
-        ks = {"pyramid": ["pad_level0_kernel", "resize_tile_kernel"], "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"]}[dom]
+        pad = ["pad_interior_kernel", "pad_frame_kernel"] if "pad_interior_kernel" in tj else ["pad_level0_kernel"]
+        if dom == "pyramid":
+            launches_dom = NLEVELS - 1 + len(pad)
+        ks = {"pyramid": pad + ["resize_tile_kernel"], "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"]}[dom]
         if all(k in tj for k in ks):
             traffic = sum(tj[k] for k in ks) * n / launches_dom
             ip = tall.get("issue_active_pct", {})

@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(KM_THREADS, 2) knn2_mma_kernel(const uint8_t* 
             const uint4* fb = expB + cur * (KM_TILE * 16) + lane;
             const int rows = min(KM_TILE, ns - j0);
             const int full = rows >> 3;    // n8 tiles without padded columns
-            auto n8tile = [&](int n8, bool guard) {
+            auto n8tile = [&](int n8, bool guard, bool filter) {
                 const uint4 f0 = fb[n8 * 128], f1 = fb[n8 * 128 + 32], f2 = fb[n8 * 128 + 64], f3 = fb[n8 * 128 + 96];
                 int acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
                 imma_16832(acc[0], A[0][0], f0.x, f0.y);
@@ -250,19 +250,35 @@ __global__ void __launch_bounds__(KM_THREADS, 2) knn2_mma_kernel(const uint8_t* 
                 imma_16832(acc[1], A[1][7], f3.z, f3.w);
                 const int jc = j0 + n8 * 8 + 2 * tg;    // this thread's columns: jc, jc + 1
                 const bool ok0 = !guard || jc < ns, ok1 = !guard || jc + 1 < ns;
+                int k[2][4];
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++) {
-                    const int k0 = acc[mt][0] * (1 << KM_S) + jc, k1 = acc[mt][1] * (1 << KM_S) + (jc + 1);
-                    const int k2 = acc[mt][2] * (1 << KM_S) + jc, k3 = acc[mt][3] * (1 << KM_S) + (jc + 1);
-                    top2_update_s(b1[mt * 2], b2[mt * 2], ok0 ? k0 : KM_EMPTY);
-                    top2_update_s(b1[mt * 2], b2[mt * 2], ok1 ? k1 : KM_EMPTY);
-                    top2_update_s(b1[mt * 2 + 1], b2[mt * 2 + 1], ok0 ? k2 : KM_EMPTY);
-                    top2_update_s(b1[mt * 2 + 1], b2[mt * 2 + 1], ok1 ? k3 : KM_EMPTY);
+                    k[mt][0] = ok0 ? acc[mt][0] * (1 << KM_S) + jc : KM_EMPTY;
+                    k[mt][1] = ok1 ? acc[mt][1] * (1 << KM_S) + (jc + 1) : KM_EMPTY;
+                    k[mt][2] = ok0 ? acc[mt][2] * (1 << KM_S) + jc : KM_EMPTY;
+                    k[mt][3] = ok1 ? acc[mt][3] * (1 << KM_S) + (jc + 1) : KM_EMPTY;
+                }
+                // long train sets: after the first few hundred columns a new candidate rarely enters a row's top 2, so
+                // test before updating (the branch is almost never taken; keys are unique, so "<" loses nothing)
+                if (filter && !(min(k[0][0], k[0][1]) < b2[0] || min(k[0][2], k[0][3]) < b2[1] ||
+                                min(k[1][0], k[1][1]) < b2[2] || min(k[1][2], k[1][3]) < b2[3]))
+                    return;
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    top2_update_s(b1[mt * 2], b2[mt * 2], k[mt][0]);
+                    top2_update_s(b1[mt * 2], b2[mt * 2], k[mt][1]);
+                    top2_update_s(b1[mt * 2 + 1], b2[mt * 2 + 1], k[mt][2]);
+                    top2_update_s(b1[mt * 2 + 1], b2[mt * 2 + 1], k[mt][3]);
                 }
             };
+            if (j0 >= 4096) {
 #pragma unroll 2
-            for (int n8 = 0; n8 < full; n8++) n8tile(n8, false);
-            if (rows & 7) n8tile(full, true);
+                for (int n8 = 0; n8 < full; n8++) n8tile(n8, false, true);
+            } else {
+#pragma unroll 2
+                for (int n8 = 0; n8 < full; n8++) n8tile(n8, false, false);
+            }
+            if (rows & 7) n8tile(full, true, false);
             if (haveNext) stage(cur ^ 1, nx);
             __syncthreads();
         }

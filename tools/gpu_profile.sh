@@ -9,7 +9,7 @@ python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_referenc
 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err
 B="python bench.py --pairs 128 --steps 1 --warmup 1 --no-cpu-baseline --map-rows 0 --latency-iters 0 --stereo-pairs 16 --search-frames 16 --c4-frames 0"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_ncu_launches.csv $B > $O/ncu_launches.log 2>&1
-ncu --set full --import-source on --clock-control none --launch-skip 14 --launch-count 14 -o $O/${TAG}_full -f $B > $O/ncu_full.log 2>&1
+ncu --set full --import-source on --clock-control none --launch-skip 15 --launch-count 15 -o $O/${TAG}_full -f $B > $O/ncu_full.log 2>&1
 ncu --set full --import-source on --clock-control none -k regex:stereo --launch-skip 2 --launch-count 2 -o $O/${TAG}_stereo -f $B > $O/ncu_stereo.log 2>&1
 ncu -i $O/${TAG}_full.ncu-rep --page raw --csv > $O/${TAG}_full_raw.csv 2>/dev/null
 ncu -i $O/${TAG}_stereo.ncu-rep --page raw --csv > $O/${TAG}_stereo_raw.csv 2>/dev/null
