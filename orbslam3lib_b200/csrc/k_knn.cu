@@ -348,6 +348,19 @@ __global__ void __launch_bounds__(KNN_THREADS) knn2_warp_kernel(const uint8_t* _
     }
 }
 
+int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_t* t, const int* nt, long long tCap,
+                   int npairs, long long nqSingle, long long ntSingle, long long maxNq, int32_t* idx, int32_t* dist,
+                   cudaStream_t st);
+
+// the tcgen05 kernel (k_knn_tc.cu) is the default from 296 CTAs up; ORBFE_KNN_TC=0 falls back to the mma.sync kernel
+static bool knn_use_tc() {
+    static const int v = [] {
+        const char* e = getenv("ORBFE_KNN_TC");
+        return e ? atoi(e) : 1;
+    }();
+    return v != 0;
+}
+
 // ORBFE_KNN_MMA=0 selects the POPC kernel (A/B measurements); default: tensor cores
 static bool knn_use_mma() {
     static const int v = [] {
@@ -366,6 +379,8 @@ int launch_knn2(const uint8_t* q, const int* nq, long long qCap, const uint8_t* 
     if (ctasBig < 296 && maxNt < (1ll << KNN_SUPER_BITS)) {
         const dim3 grid((unsigned)((maxNq + 7) / 8), npairs);
         knn2_warp_kernel<<<grid, KNN_THREADS, 0, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist);
+    } else if (knn_use_tc()) {
+        return launch_knn2_tc(q, nq, qCap, t, nt, tCap, npairs, nqSingle, ntSingle, maxNq, idx, dist, st);
     } else if (knn_use_mma()) {
         const dim3 grid((unsigned)((maxNq + KM_ROWS - 1) / KM_ROWS), npairs);
         static unsigned long long configured = 0;    // one bit per device: the attribute is per context

@@ -1,0 +1,240 @@
+// k_knn_tc.cu — Hamming kNN (k = 2) on the 5th-generation tensor cores: tcgen05.mma kind::i8 with the accumulators in
+// tensor memory.  Same arithmetic as knn2_mma_kernel (k_knn.cu): hamming(a, b) - |a| = sum_k b_k * (1 - 2 a_k) with
+// A' = 1 - 2a in {+1, -1} and B = b in {0, 1} as int8, exact in s32.
+//
+//   * CTA = 128 query rows (UMMA M = 128: accumulator row i = TMEM lane i) x tiles of KT_N train rows (UMMA N);
+//     K = 256 = 8 instructions of K = 32.  Operands live in shared memory in the canonical K-major, no-swizzle layout:
+//     core matrix = 8 rows x 16 bytes (128 contiguous bytes), SBO = 128 B between 8-row groups, LBO = rows / 8 * 128 B
+//     between the two 16-byte K chunks of an instruction.  The k order of a dot product is free as long as A and B
+//     agree, so a 16-byte chunk is simply four registers (word >> n) & 0x01010101 — bits are never transposed.
+//   * the query tile is expanded once; every train tile is expanded by all threads from packed global rows (32 B per
+//     row) straight into the canonical layout with conflict-free STS.128, made visible to the async proxy
+//     (fence.proxy.async), then one thread issues the 8 MMAs and a tcgen05.commit onto an mbarrier;
+//   * epilogue: warp w reads its 32 TMEM lanes with tcgen05.ld.32x32b.x32 (thread = query row, 32 train columns per
+//     load), turns each accumulator into key = acc << S | column and keeps the two smallest per row in registers
+//     (distance first, train index second = OpenCV's tie order); stored keys are re-based by -32 per chunk so the column
+//     constants stay compile-time;
+//   * no warp specialisation: phases of the 2-3 co-resident CTAs of an SM overlap each other (expansion and epilogue on
+//     the ALU pipes of one CTA under the MMAs of another); the next tile's packed rows are prefetched into registers
+//     before the wait.
+#include <cstdlib>
+
+#include "orbfe_internal.h"
+
+namespace orbfe {
+
+#ifndef ORBFE_KT_N
+#define ORBFE_KT_N 128
+#endif
+constexpr int KT_M = 128;
+constexpr int KT_N = ORBFE_KT_N;    // train rows per tile = TMEM columns
+constexpr int KT_THREADS = 128;
+constexpr int KT_S = 22;
+constexpr int KT_EMPTY = 0x7fffffff;
+constexpr int KT_RPT = KT_N / KT_THREADS;    // train rows expanded per thread and tile
+static_assert(KT_N % 128 == 0 && KT_N <= 256, "tile = 1 or 2 rows per thread");
+constexpr int KT_SMEM = KT_M * 256 + KT_N * 256 + 64;
+constexpr uint32_t KT_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(KT_N >> 3) << 17) | ((uint32_t)(KT_M >> 4) << 24);
+
+// K-major, SWIZZLE_NONE shared-memory matrix descriptor (version 1 = sm_100)
+__device__ __forceinline__ uint64_t kt_desc(uint32_t saddr, uint32_t lboBytes, uint32_t sboBytes) {
+    return (uint64_t)((saddr >> 4) & 0x3fffu) | ((uint64_t)((lboBytes >> 4) & 0x3fffu) << 16) |
+           ((uint64_t)((sboBytes >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+
+__device__ __forceinline__ void kt_mma_i8(uint32_t dTmem, uint64_t aDesc, uint64_t bDesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(dTmem),
+        "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__device__ __forceinline__ void kt_ld32(uint32_t taddr, int (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];\n"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// expand one packed 256-bit row into its 16 chunks of the canonical layout; `rows` = rows of the operand tile
+template <bool SIGNED_A>
+__device__ __forceinline__ void kt_expand_row(uint8_t* base, int rows, int r, const uint4& lo, const uint4& hi) {
+    constexpr uint32_t M = 0x01010101u;
+    const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    uint8_t* rowp = base + (r >> 3) * 128 + (r & 7) * 16;
+    const int chunkStride = (rows >> 3) * 128;
+#pragma unroll
+    for (int q = 0; q < 16; q++) {
+        const int p = q & 3, j = q >> 2;
+        uint32_t x0 = (w[2 * p] >> (2 * j)) & M, x1 = (w[2 * p] >> (2 * j + 1)) & M;
+        uint32_t x2 = (w[2 * p + 1] >> (2 * j)) & M, x3 = (w[2 * p + 1] >> (2 * j + 1)) & M;
+        if (SIGNED_A) {
+            x0 = (x0 * 0xffu) | M;
+            x1 = (x1 * 0xffu) | M;
+            x2 = (x2 * 0xffu) | M;
+            x3 = (x3 * 0xffu) | M;
+        }
+        *reinterpret_cast<uint4*>(rowp + q * chunkStride) = make_uint4(x0, x1, x2, x3);
+    }
+}
+
+// grid (ceil(maxNq / KT_M), npairs); block KT_THREADS; dynamic shared memory KT_SMEM
+__global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __restrict__ q, const int* __restrict__ nqArr,
+                                                            long long qCap, const uint8_t* __restrict__ t,
+                                                            const int* __restrict__ ntArr, long long tCap,
+                                                            long long nqSingle, long long ntSingle,
+                                                            int32_t* __restrict__ idx, int32_t* __restrict__ dist) {
+    extern __shared__ __align__(128) uint8_t ktSmem[];
+    uint8_t* sA = ktSmem;
+    uint8_t* sB = ktSmem + KT_M * 256;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(ktSmem + KT_M * 256 + KT_N * 256);
+    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(bar + 1);
+
+    const int pair = blockIdx.y;
+    const long long nq = nqArr ? nqArr[pair] : nqSingle;
+    const long long nt = ntArr ? ntArr[pair] : ntSingle;
+    if ((long long)blockIdx.x * KT_M >= nq) return;    // uniform: before any allocation
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const long long row = (long long)blockIdx.x * KT_M + tid;
+    const uint4* tp = reinterpret_cast<const uint4*>(t + (long long)pair * tCap * 32);
+
+    if (tid == 0) mbar_init(bar, 1);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmemSlot)), "n"(KT_N)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // the query tile, +1 / -1
+    int na = 0;
+    {
+        uint4 lo = make_uint4(0u, 0u, 0u, 0u), hi = lo;
+        if (row < nq) {
+            const uint4* qp = reinterpret_cast<const uint4*>(q + ((long long)pair * qCap + row) * 32);
+            lo = __ldg(qp);
+            hi = __ldg(qp + 1);
+        }
+        na = __popc(lo.x) + __popc(lo.y) + __popc(lo.z) + __popc(lo.w) + __popc(hi.x) + __popc(hi.y) + __popc(hi.z) + __popc(hi.w);
+        kt_expand_row<true>(sA, KT_M, tid, lo, hi);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = *tmemSlot;
+    const uint32_t aBase = smem_u32(sA), bBase = smem_u32(sB);
+
+    int d1 = -1, i1 = -1, d2 = -1, i2 = -1;
+    uint32_t phase = 0;
+    for (long long sb = 0; sb < nt; sb += (1ll << (KT_S - 1))) {
+        const int ns = (int)min(nt - sb, 1ll << (KT_S - 1));
+        int b1 = KT_EMPTY, b2 = KT_EMPTY;    // keys relative to the current chunk: (acc << S) + (column - chunk base)
+        const int ntiles = (ns + KT_N - 1) / KT_N;
+        uint4 nx[KT_RPT][2];
+        auto fetch = [&](int j0) {
+#pragma unroll
+            for (int u = 0; u < KT_RPT; u++) {
+                const int r = j0 + u * KT_THREADS + tid;
+                nx[u][0] = nx[u][1] = make_uint4(0u, 0u, 0u, 0u);
+                if (r < ns) {
+                    nx[u][0] = __ldg(tp + (sb + r) * 2);
+                    nx[u][1] = __ldg(tp + (sb + r) * 2 + 1);
+                }
+            }
+        };
+        fetch(0);
+        for (int ti = 0; ti < ntiles; ti++) {
+            const int j0 = ti * KT_N;
+            // B tile -> shared memory (the previous tile's MMAs have completed: every thread waited on the barrier)
+#pragma unroll
+            for (int u = 0; u < KT_RPT; u++) kt_expand_row<false>(sB, KT_N, u * KT_THREADS + tid, nx[u][0], nx[u][1]);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");    // orders the previous tile's tcgen05.ld
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                for (int s = 0; s < 8; s++) {
+                    const uint64_t ad = kt_desc(aBase + 2 * s * (KT_M >> 3) * 128, (KT_M >> 3) * 128, 128);
+                    const uint64_t bd = kt_desc(bBase + 2 * s * (KT_N >> 3) * 128, (KT_N >> 3) * 128, 128);
+                    kt_mma_i8(tmem, ad, bd, KT_IDESC, s > 0);
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                             : "memory");
+            }
+            if (ti + 1 < ntiles) fetch(j0 + KT_N);
+            mbar_wait(bar, phase);
+            phase ^= 1;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const bool guard = j0 + KT_N > ns;
+#pragma unroll 1
+            for (int c = 0; c < KT_N; c += 32) {
+                int v[32];
+                kt_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, v);
+                if (guard) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) {
+                        const int k = j0 + c + i < ns ? v[i] * (1 << KT_S) + i : KT_EMPTY;
+                        b2 = min(b2, max(b1, k));
+                        b1 = min(b1, k);
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) {
+                        const int k = v[i] * (1 << KT_S) + i;
+                        b2 = min(b2, max(b1, k));
+                        b1 = min(b1, k);
+                    }
+                }
+                b1 -= 32;    // re-base to the next chunk (EMPTY drifts by < 2^21 per super block: still above any real key)
+                b2 -= 32;
+            }
+        }
+        // decode: key = d * 2^S + (index - base), |index - base| < 2^(S-1); base = columns processed so far
+        const long long base = sb + (long long)ntiles * KT_N;
+        auto merge = [&](int b) {
+            if (b > (400 << KT_S)) return;    // empty
+            const int d = (b + (1 << (KT_S - 1))) >> KT_S;
+            const int i = (int)(base + (b - d * (1 << KT_S)));
+            const int dd = d + na;
+            if (i1 < 0 || dd < d1) { d2 = d1; i2 = i1; d1 = dd; i1 = i; }
+            else if (i2 < 0 || dd < d2) { d2 = dd; i2 = i; }
+        };
+        merge(b1);
+        merge(b2);
+    }
+    if (row < nq) {
+        const long long o = ((long long)pair * qCap + row) * 2;
+        *reinterpret_cast<int2*>(idx + o) = make_int2(i1, i2);
+        *reinterpret_cast<int2*>(dist + o) = make_int2(d1, d2);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(KT_N) : "memory");
+}
+
+int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_t* t, const int* nt, long long tCap,
+                   int npairs, long long nqSingle, long long ntSingle, long long maxNq, int32_t* idx, int32_t* dist,
+                   cudaStream_t st) {
+    static unsigned long long configured = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!((configured >> (dev & 63)) & 1ull)) {
+        cudaFuncSetAttribute(knn2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KT_SMEM);
+        configured |= 1ull << (dev & 63);
+    }
+    const dim3 grid((unsigned)((maxNq + KT_M - 1) / KT_M), npairs);
+    knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist);
+    return 1;
+}
+
+}    // namespace orbfe
