@@ -8,3 +8,13 @@ for l in sys.stdin:
     if l.startswith('{'):
         d = json.loads(l); print(d['value'], d['e2e']['value'], {k: round(v['ms_per_step'], 3) for k, v in d['stages'].items()}); m = d.get('knn_map') or {}; print('map', m.get('ms_per_step'), m.get('gpairs_per_s'), m.get('parity_sample'))
 "
+for so in variants/*.so; do
+  [ -f "$so" ] || continue
+  echo "== $so"
+  ORBFE_SO=$PWD/$so timeout 600 python bench.py --no-cpu-baseline --latency-iters 0 --stereo-pairs 0 --search-frames 0 --c4-frames 0 2>&1 | python -c "
+import sys, json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d = json.loads(l); print(d['value'], d['e2e']['value'], {k: round(v['ms_per_step'], 3) for k, v in d['stages'].items()}); m = d.get('knn_map') or {}; print('map', m.get('ms_per_step'), m.get('gpairs_per_s'), m.get('parity_sample'))
+"
+done
