@@ -106,3 +106,52 @@ def test_tensor_core_path_large_single(oracle):
     ri, rd = oracle.knn2_hamming(q[sel], t, threads=4)
     np.testing.assert_array_equal(idx[sel], ri)
     np.testing.assert_array_equal(dist[sel], rd)
+
+
+@pytest.mark.parametrize("env", [{"ORBFE_KNN_TC": "0"}, {"ORBFE_KNN_TC": "0", "ORBFE_KNN_MMA": "0"}])
+def test_alternative_kernels_still_agree(env):
+    """the mma.sync IMMA kernel and the POPC kernel stay selectable for A/B measurements: same answers as the default
+    tcgen05 kernel on a ragged batch with ties (the selection is read once per process, hence the subprocess)."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import numpy as np, sys\n"
+        "from orbslam3lib_b200 import BFMatcher, scenes\n"
+        "p, cap = 320, 300\n"
+        "rng = np.random.default_rng(5)\n"
+        "nq = rng.integers(1, cap + 1, p).astype(np.int32); nt = rng.integers(1, cap + 1, p).astype(np.int32)\n"
+        "q = scenes.descriptors(p * cap, 41).reshape(p, cap, 32); t = scenes.descriptors(p * cap, 42).reshape(p, cap, 32)\n"
+        "t[0, 100:200] = t[0, 7]; q[0, :50] = t[0, 7]\n"
+        "idx, dist = BFMatcher().knnMatchBatch(q, nq, t, nt)\n"
+        "sys.stdout.write('%d %d' % (int((idx.astype(np.int64) * 31 + dist).sum()), int(idx[0, 0, 1])))\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for e in ({}, env):
+        full = dict(os.environ, **e)
+        for k in ("ORBFE_KNN_TC", "ORBFE_KNN_MMA"):
+            if k not in e:
+                full.pop(k, None)
+        outs.append(subprocess.run([sys.executable, "-c", code], cwd=root, env=full, capture_output=True, text=True,
+                                   timeout=300))
+    assert outs[0].returncode == 0 and outs[1].returncode == 0, outs[1].stderr[-400:]
+    assert outs[0].stdout == outs[1].stdout and outs[0].stdout.split()[1] == "100"
+
+
+def test_tensor_core_path_super_blocks(oracle):
+    """more than 2^21 train rows: keys are re-based per super block; a tie that straddles the boundary keeps the lower
+    train index first."""
+    nt = (1 << 21) + 1500
+    q = scenes.descriptors(80000, 51)
+    t = scenes.descriptors(nt, 52)
+    t[(1 << 21) - 1] = q[3]          # last row of super block 0
+    t[(1 << 21) + 7] = q[3]          # and a copy in super block 1
+    t[(1 << 21) + 9] = q[11]
+    t[5] = q[11]
+    idx, dist = BFMatcher().knnMatch(q, t)
+    assert idx[3].tolist() == [(1 << 21) - 1, (1 << 21) + 7] and dist[3].tolist() == [0, 0]
+    assert idx[11].tolist() == [5, (1 << 21) + 9] and dist[11].tolist() == [0, 0]
+    sel = np.arange(0, 80000, 1250)
+    ri, rd = oracle.knn2_hamming(q[sel], t, threads=8)
+    np.testing.assert_array_equal(idx[sel], ri)
+    np.testing.assert_array_equal(dist[sel], rd)
