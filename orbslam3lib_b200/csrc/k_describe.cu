@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_co
 int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st) {
     const size_t smem = sizeof(int) * (size_t)(g.outCap + 1);
     static size_t configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
+    if (smem > 32 * 1024 && configured < smem) {
         cudaFuncSetAttribute(pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }

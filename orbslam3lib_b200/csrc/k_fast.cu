@@ -32,10 +32,13 @@ namespace orbfe {
 #define ORBFE_FAST_THREADS 256
 #endif
 #ifndef ORBFE_FAST_COLS
-#define ORBFE_FAST_COLS 4
+#define ORBFE_FAST_COLS 5
 #endif
 constexpr int FAST_THREADS = ORBFE_FAST_THREADS;
 constexpr int FAST_WARPS = FAST_THREADS / 32;
+#ifndef ORBFE_FAST_MINB
+#define ORBFE_FAST_MINB 5    // CTAs per SM the register allocation must allow (<= 51 registers at 256 threads)
+#endif
 constexpr int FAST_ITEM_COLS = ORBFE_FAST_COLS;    // <= FAST_WARPS (phase D gives a warp to every cell)
 static_assert(FAST_ITEM_COLS <= FAST_WARPS, "phase D gives a warp to every cell");
 
@@ -102,6 +105,7 @@ struct FastStrip {
     int tp, kw, ch;          // tile pitch (multiple of 32), bitmap words per row (tp / 32), tile rows
     int colLo, colHi;        // tested tile columns [colLo, colHi)
     int wCell, ncols;        // cell pitch and number of cells in the strip
+    int rpu;                 // rows per phase-A unit (4..8)
 };
 
 // cell (0 .. ncols-1) of a tested tile column
@@ -119,7 +123,8 @@ __device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t ce
     const int wpr = s.tp >> 2;
     const int wLo = s.colLo >> 2, nwc = ((s.colHi + 3) >> 2) - wLo;
     const int th = s.ch - 6;
-    const int ngroups = (th + 7) >> 3;
+    const int R = s.rpu;    // rows per unit: the host picks 4..8 so that the units fill the CTA's threads
+    const int ngroups = (th + R - 1) / R;
     const uint32_t k127mt = (uint32_t)(127 - min(t, 127)) * 0x01010101u;
     const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(s.tile);
 
@@ -132,7 +137,7 @@ __device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t ce
         if (u < nunits) {
             const int g = u / nwc;
             w = wLo + (u - g * nwc);
-            r0 = 3 + 8 * g;
+            r0 = 3 + R * g;
             // bytes of this word column that are tested (and belong to a cell of cellMask)
             uint32_t bm = 0;
 #pragma unroll
@@ -147,18 +152,21 @@ __device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t ce
                 if (t <= 127) {
 #pragma unroll
                     for (int i = 0; i < 8; i++) {
-                        const uint32_t c = p[i * wpr], cp = p[i * wpr - 1], cn = p[i * wpr + 1];
-                        const uint32_t up = p[(i + 3) * wpr], dn = p[(i - 3) * wpr];
-                        const uint32_t p4 = __byte_perm(c, cn, 0x6543), p12 = __byte_perm(cp, c, 0x4321);
-                        const uint32_t v = bytes_gt_raw(__vabsdiffu4(up, c), k127mt) | bytes_gt_raw(__vabsdiffu4(dn, c), k127mt);
-                        const uint32_t h = bytes_gt_raw(__vabsdiffu4(p4, c), k127mt) | bytes_gt_raw(__vabsdiffu4(p12, c), k127mt);
-                        acc = (acc >> 1) | (v & h & bm);
+                        if (i < 4 || i < R) {    // CTA-uniform
+                            const uint32_t c = p[i * wpr], cp = p[i * wpr - 1], cn = p[i * wpr + 1];
+                            const uint32_t up = p[(i + 3) * wpr], dn = p[(i - 3) * wpr];
+                            const uint32_t p4 = __byte_perm(c, cn, 0x6543), p12 = __byte_perm(cp, c, 0x4321);
+                            const uint32_t v = bytes_gt_raw(__vabsdiffu4(up, c), k127mt) | bytes_gt_raw(__vabsdiffu4(dn, c), k127mt);
+                            const uint32_t h = bytes_gt_raw(__vabsdiffu4(p4, c), k127mt) | bytes_gt_raw(__vabsdiffu4(p12, c), k127mt);
+                            acc = (acc >> 1) | (v & h & bm);
+                        }
                     }
+                    acc >>= 8 - R;    // row i of the unit -> bit i of its byte (flags never cross a byte: R <= 8 shifts)
                 } else {
                     acc = bm | (bm >> 1) | (bm >> 2) | (bm >> 3) | (bm >> 4) | (bm >> 5) | (bm >> 6) | (bm >> 7);
                 }
                 // rows beyond the tested window (the last group may be partial)
-                const int nvalid = min(8, th - 8 * g);
+                const int nvalid = min(R, th - R * g);
                 acc &= ((1u << nvalid) - 1u) * 0x01010101u;
             }
         }
@@ -174,21 +182,23 @@ __device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t ce
         if (lane == 31 && inc > 0) base = atomicAdd(&s.cnt[0], inc);
         base = __shfl_sync(0xffffffffu, base, 31) + inc - n;
         const int o0 = r0 * s.tp + 4 * w;
-        if (__any_sync(0xffffffffu, n > 10)) {
-            // survivors cluster along edges: when some lane holds many, 32 predicated steps beat a loop whose trip
-            // count is the largest popcount of the warp
+        unsigned short* lp = s.list + base;
+        if (__any_sync(0xffffffffu, n > 14)) {
+            // survivors cluster along edges: when some lane holds many, 32 predicated steps (a predicated store and a
+            // predicated pointer bump each) beat a loop whose trip count is the largest popcount of the warp
 #pragma unroll
             for (int i = 0; i < 8; i++) {
+                const int oi = o0 + i * s.tp;
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    if ((acc >> (8 * j + i)) & 1u) s.list[base++] = (unsigned short)(o0 + i * s.tp + j);
+                    if ((acc >> (8 * j + i)) & 1u) *lp++ = (unsigned short)(oi + j);
                 }
             }
         } else {
             while (acc) {
                 const int b = __ffs(acc) - 1;
                 acc &= acc - 1;
-                s.list[base++] = (unsigned short)(o0 + (b & 7) * s.tp + (b >> 3));
+                *lp++ = (unsigned short)(o0 + (b & 7) * s.tp + (b >> 3));
             }
         }
     }
@@ -226,8 +236,10 @@ __device__ __forceinline__ void fast_pass(const FastStrip& s, int t, uint32_t ce
 }
 
 // phase D for the cells of cellMask: raster-order emission of the kept pixels of every cell window, one warp per cell.
-// Returns (to lane 0 of the warp that owns cell j) nothing; totals are written to counts[] and empty cells are
-// recorded in s.cnt[1] when markEmpty is set.
+// A window is at most wCell <= 97 columns wide, i.e. it spans at most four words of a keep-bitmap row: the four column
+// masks are built once per warp.  A lane owns rows (lane, lane + 32) of a block of 64 window rows; both counts travel
+// through ONE warp scan packed in 16-bit fields (<= 32 x 97 per field).  Totals are written to counts[]; empty cells
+// are recorded in s.cnt[1] when markEmpty is set.
 __device__ __forceinline__ void fast_emit(const FastStrip& s, uint32_t cellMask, bool markEmpty, uint32_t* slotsRow,
                                           int* counts, int slotCap, int col0, int xAddBase, int yAdd) {
     const int lane = threadIdx.x & 31, j = threadIdx.x >> 5;
@@ -237,42 +249,57 @@ __device__ __forceinline__ void fast_emit(const FastStrip& s, uint32_t cellMask,
     int total = 0;
     if (x1 > x0) {
         const int th = s.ch - 6;
-        const int wA = x0 >> 5, wB = (x1 - 1) >> 5;
+        const int wA = x0 >> 5, nw = ((x1 - 1) >> 5) - wA + 1;    // nw <= 4
+        uint32_t m[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int lo = max(x0 - 32 * (wA + q), 0), hi = min(x1 - 32 * (wA + q), 32);
+            m[q] = (q < nw && hi > lo) ? ((hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u)) : 0u;
+        }
         uint32_t* out = slotsRow + (size_t)(col0 + j) * slotCap;
         const int xAdd = xAddBase + j * s.wCell - x0;
-        for (int rbase = 0; rbase < th; rbase += 32) {
-            const int row = rbase + lane;
-            int n = 0;
-            if (row < th) {
-                for (int wi = wA; wi <= wB; wi++) {
-                    uint32_t bits = s.kbits[(3 + row) * s.kw + wi];
-                    const int lo = max(x0 - 32 * wi, 0), hi = min(x1 - 32 * wi, 32);
-                    bits &= (hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
-                    n += __popc(bits);
+        for (int rbase = 0; rbase < th; rbase += 64) {
+            const int rowA = rbase + lane, rowB = rowA + 32;
+            const uint32_t* kA = s.kbits + (3 + rowA) * s.kw + wA;
+            const uint32_t* kB = kA + 32 * s.kw;
+            uint32_t n2 = 0;    // kept pixels of rowA | rowB << 16
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (q < nw) {
+                    if (rowA < th) n2 += (uint32_t)__popc(kA[q] & m[q]);
+                    if (rowB < th) n2 += (uint32_t)__popc(kB[q] & m[q]) << 16;
                 }
             }
-            int inc = n;
+            uint32_t inc = n2;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, inc, o);
+                const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
                 if (lane >= o) inc += v;
             }
-            int k = total + inc - n;
-            if (n > 0) {
-                for (int wi = wA; wi <= wB; wi++) {
-                    uint32_t bits = s.kbits[(3 + row) * s.kw + wi];
-                    const int lo = max(x0 - 32 * wi, 0), hi = min(x1 - 32 * wi, 32);
-                    bits &= (hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
-                    while (bits) {
-                        const int col = 32 * wi + __ffs(bits) - 1;
-                        bits &= bits - 1;
-                        const uint32_t sc = s.smap[(3 + row) * s.tp + col];
-                        if (k < slotCap) out[k] = (uint32_t)(col + xAdd) | ((uint32_t)(row + yAdd) << 12) | (sc << 24);
-                        k++;
+            const uint32_t tot2 = __shfl_sync(0xffffffffu, inc, 31);
+            const int totA = (int)(tot2 & 0xffffu), totB = (int)(tot2 >> 16);
+            if (n2 != 0) {
+#pragma unroll
+                for (int half = 0; half < 2; half++) {
+                    const int n = half ? (int)(n2 >> 16) : (int)(n2 & 0xffffu);
+                    if (n == 0) continue;
+                    const int row = half ? rowB : rowA;
+                    int k = total + (half ? totA + (int)(inc >> 16) : (int)(inc & 0xffffu)) - n;
+                    const uint32_t* kr = half ? kB : kA;
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        uint32_t bits = q < nw ? kr[q] & m[q] : 0u;
+                        while (bits) {
+                            const int col = 32 * (wA + q) + __ffs(bits) - 1;
+                            bits &= bits - 1;
+                            const uint32_t sc = s.smap[(3 + row) * s.tp + col];
+                            if (k < slotCap) out[k] = (uint32_t)(col + xAdd) | ((uint32_t)(row + yAdd) << 12) | (sc << 24);
+                            k++;
+                        }
                     }
                 }
             }
-            total += __shfl_sync(0xffffffffu, inc, 31);
+            total += totA + totB;
         }
         if (markEmpty && total == 0 && lane == 0) atomicOr(&s.cnt[1], 1 << j);
     }
@@ -280,7 +307,10 @@ __device__ __forceinline__ void fast_emit(const FastStrip& s, uint32_t cellMask,
 }
 
 // grid (nItems, n); block FAST_THREADS.  dynamic shared memory: tile | score map | keep bitmap | survivor list.
-__global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_constant__ Geom g,
+// (A persistent variant of this kernel -- resident CTAs walking the (image, item) units with the next unit's tile
+// prefetched by TMA into a second buffer -- was measured 35 % SLOWER (3.85 vs 2.80 ms per 1024 images): the block
+// scheduler's staggered CTA starts interleave the phases of the CTAs sharing an SM better than lock-stepped loops.)
+__global__ void __launch_bounds__(FAST_THREADS, ORBFE_FAST_MINB) fast_cells_kernel(const __grid_constant__ Geom g,
                                                                   const uint8_t* __restrict__ pyr,
                                                                   const FastItem* __restrict__ items,
                                                                   uint32_t* __restrict__ slots,
@@ -290,32 +320,22 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
     __shared__ int sCnt[2];
     __shared__ __align__(8) uint64_t sBar;
     __shared__ __align__(4) uint8_t sEdge[1024];
-    const FastItem it = items[blockIdx.x];
+    const FastItem it = items[blockIdx.x];    // geometry-only quantities come precomputed from the host
     const int img = blockIdx.y;
     const LevelGeom& L = g.lv[it.level];
-
-    const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
-    const int iniY = kMinBorder + it.row * L.hCell;
-    const int maxY = min(iniY + L.hCell + 6, maxBY);
-    const int ch = maxY - iniY;
-    const int cellRowBase = L.cellBase + it.row * L.nCols;
+    const int ch = it.ch;
+    const int cellRowBase = it.cellRowBase;
     int* counts = cellCount + (size_t)img * g.nCells + cellRowBase;
 
-    const bool rowSkipped = (iniY >= maxBY - 3) || ch < 7;    // :812 (and cv::FAST finds nothing in < 7 rows)
-    if (rowSkipped) {
+    if (ch == 0) {    // :812 (and cv::FAST finds nothing in < 7 rows)
         for (int jc = threadIdx.x; jc < it.ncols; jc += FAST_THREADS) counts[it.col0 + jc] = 0;
         return;
     }
-    // strip columns [xs, xe) of the level, as plane columns [ax0, ax1)
-    const int xs = kMinBorder + it.col0 * L.wCell;
-    const int xe = min(kMinBorder + (it.col0 + it.ncols - 1) * L.wCell + L.wCell + 6, maxBX);
-    const int ax0 = (kXOff + xs) & ~31;
-    const int ax1 = (kXOff + max(xe, xs) + 31) & ~31;
 
     FastStrip s;
-    s.tp = ax1 - ax0;
+    s.tp = it.tp;
     s.kw = s.tp >> 5;
-    s.tpMagic = 0xffffffffu / (unsigned)s.tp + 1u;
+    s.tpMagic = it.tpMagic;
     s.cedge = sEdge;
     s.ch = ch;
     s.tile = smem;
@@ -323,17 +343,19 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
     s.kbits = reinterpret_cast<uint32_t*>(smem + 2 * tileBytes);
     s.list = reinterpret_cast<unsigned short*>(smem + 2 * tileBytes + kbitsBytes);
     s.cnt = sCnt;
-    s.colLo = kXOff + xs - ax0 + 3;
-    s.colHi = max(kXOff + xe - ax0 - 3, s.colLo);
-    s.wCell = L.wCell;
+    s.colLo = it.colLo;
+    s.colHi = it.colHi;
+    s.wCell = it.wCell;
     s.ncols = it.ncols;
+    s.rpu = it.rpu;
 
     {
         // staging: one TMA bulk copy (cp.async.bulk -> UBLKCP) per tile row, issued by the lanes of warp 0 and
-        // completing on an mbarrier; meanwhile every thread clears the score map, the keep bitmap and the edge table.
+        // completing on an mbarrier; meanwhile every thread clears the score map + keep bitmap (contiguous: one
+        // 16-byte loop over both allocations) and the edge table.
         // Tile columns past the plane pitch are never copied: they lie beyond every tested pixel's ring.
-        const uint8_t* plane = pyr + (size_t)img * g.slabBytes + L.planeOff + (size_t)(iniY + kEdge) * L.pitch + ax0;
-        const uint32_t rowBytes = (uint32_t)min(s.tp, L.pitch - ax0);
+        const uint8_t* plane = pyr + (size_t)img * g.slabBytes + L.planeOff + it.tileOff;
+        const uint32_t rowBytes = it.rowBytes;
         if (threadIdx.x == 0) mbar_init(&sBar, 1);
         __syncthreads();
         if (threadIdx.x < 32) {
@@ -342,8 +364,7 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
             for (int r = threadIdx.x; r < ch; r += 32) bulk_g2s(s.tile + r * s.tp, plane + (size_t)r * L.pitch, rowBytes, &sBar);
         }
         uint4* z = reinterpret_cast<uint4*>(s.smap);
-        for (int i = threadIdx.x; i < (ch * s.tp) >> 4; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
-        for (int i = threadIdx.x; i < s.kw * ch; i += FAST_THREADS) s.kbits[i] = 0;
+        for (int i = threadIdx.x; i < (tileBytes + kbitsBytes) >> 4; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
         for (int i = threadIdx.x; i < (s.tp >> 2); i += FAST_THREADS) reinterpret_cast<uint32_t*>(sEdge)[i] = 0;
         if (threadIdx.x < 2) sCnt[threadIdx.x] = 0;
     }
@@ -361,7 +382,7 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
     __syncthreads();
 
     uint32_t* slotsRow = slots + ((size_t)img * g.nCells + cellRowBase) * g.slotCap;
-    const int xAddBase = it.col0 * L.wCell + 3, yAdd = it.row * L.hCell + 3;
+    const int xAddBase = it.xAddBase, yAdd = it.yAdd;
     const uint32_t all = (1u << it.ncols) - 1u;
 
     fast_pass(s, min(max(g.iniTh, 0), 255), all, true);
@@ -377,23 +398,64 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_cells_kernel(const __grid_c
     fast_emit(s, empty, false, slotsRow, counts, g.slotCap, it.col0, xAddBase, yAdd);
 }
 
-// host: work items of one geometry.  Every cell row of every level is cut into runs of <= FAST_ITEM_COLS cells.
+// host: work items of one geometry.  Every cell row of every level is cut into runs of <= FAST_ITEM_COLS cells, and
+// everything the kernel needs that depends only on the geometry is worked out here.
 // tileBytes: strip tile (and score map) bytes; kbitsBytes: keep bitmap; listBytes: survivor list (worst case: every
 // tested pixel survives).
 int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* kbitsBytes, int* listBytes) {
     int n = 0, maxTile = 16, maxK = 4, maxList = 16;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& L = g.lv[l];
+        const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
+        if (L.wCell > 97) maxTile = 1 << 28;    // phase D: a cell window spans at most four bitmap words
         for (int r = 0; r < L.nRows; r++)
             for (int c0 = 0; c0 < L.nCols; c0 += FAST_ITEM_COLS) {
                 const int nc = L.nCols - c0 < FAST_ITEM_COLS ? L.nCols - c0 : FAST_ITEM_COLS;
-                if (out && n < cap) out[n] = FastItem{(short)l, (short)r, (short)c0, (short)nc};
+                const int tpMax = ((nc * L.wCell + 6 + 31 + 31) & ~31) + 32;
+                if (out && n < cap) {
+                    FastItem it{};
+                    it.level = (short)l; it.row = (short)r; it.col0 = (short)c0; it.ncols = (short)nc;
+                    const int iniY = kMinBorder + r * L.hCell;
+                    const int maxY = iniY + L.hCell + 6 < maxBY ? iniY + L.hCell + 6 : maxBY;
+                    int ch = maxY - iniY;
+                    if (iniY >= maxBY - 3 || ch < 7) ch = 0;    // ORBextractor_old.cc:812
+                    // strip columns [xs, xe) of the level, as plane columns [ax0, ax1)
+                    const int xs = kMinBorder + c0 * L.wCell;
+                    int xe = kMinBorder + (c0 + nc - 1) * L.wCell + L.wCell + 6;
+                    if (xe > maxBX) xe = maxBX;
+                    const int ax0 = (kXOff + xs) & ~31;
+                    const int ax1 = (kXOff + (xe > xs ? xe : xs) + 31) & ~31;
+                    const int tp = ax1 - ax0 > 32 ? ax1 - ax0 : 32;
+                    it.ch = (short)ch;
+                    it.tp = (short)tp;
+                    it.colLo = (short)(kXOff + xs - ax0 + 3);
+                    const int hi = kXOff + xe - ax0 - 3;
+                    it.colHi = (short)(hi > it.colLo ? hi : it.colLo);
+                    it.wCell = (short)L.wCell;
+                    it.xAddBase = (short)(c0 * L.wCell + 3);
+                    it.yAdd = (short)(r * L.hCell + 3);
+                    it.tpMagic = 0xffffffffu / (unsigned)tp + 1u;
+                    it.tileOff = (unsigned)((iniY + kEdge) * L.pitch + ax0);
+                    it.rowBytes = (unsigned)(tp < L.pitch - ax0 ? tp : L.pitch - ax0);
+                    it.cellRowBase = L.cellBase + r * L.nCols;
+                    // rows per phase-A unit: a unit is one 4-px word column x R rows and costs ~R; the units are dealt
+                    // to FAST_THREADS threads in rounds, so pick the R with the fewest rounds x R (ties: larger R)
+                    const int th = ch - 6, nwc = ((it.colHi + 3) >> 2) - (it.colLo >> 2);
+                    int bestR = 8, bestCost = 1 << 30;
+                    for (int R = 8; R >= 4 && th > 0; R--) {
+                        const int units = nwc * ((th + R - 1) / R);
+                        const int cost = ((units + FAST_THREADS - 1) / FAST_THREADS) * (R + 2);    // +2: per-unit overhead
+                        if (cost < bestCost) { bestCost = cost; bestR = R; }
+                    }
+                    it.rpu = (short)bestR;
+                    if (tp > tpMax || tp > 1024) maxTile = 1 << 28;
+                    out[n] = it;
+                }
                 n++;
-                const int tp = ((nc * L.wCell + 6 + 31 + 31) & ~31) + 32;
-                if (tp > 1024) maxTile = 1 << 28;    // sEdge[] holds 1024 columns
-                const int ch = L.hCell + 6;
-                if (tp * ch > maxTile) maxTile = tp * ch;
-                const int kb = (tp / 32) * 4 * ch;
+                if (tpMax > 1024) maxTile = 1 << 28;    // sEdge[] holds 1024 columns
+                const int chMax = L.hCell + 6;
+                if (tpMax * chMax > maxTile) maxTile = tpMax * chMax;
+                const int kb = (tpMax / 32) * 4 * chMax;
                 if (kb > maxK) maxK = kb;
                 const int lb = (nc * L.wCell + 8) * L.hCell * 2;
                 if (lb > maxList) maxList = lb;
@@ -417,7 +479,8 @@ int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items,
     if (nItems <= 0) return 0;
     const int smem = fast_smem_bytes(tileBytes, kbitsBytes, listBytes);
     static int configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
+    // the 48 KiB default limit counts static + dynamic shared memory: opt in early (static usage here is <= 16 KiB)
+    if (smem > 32 * 1024 && configured < smem) {
         cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }

@@ -544,7 +544,7 @@ size_t octree_smem_bytes(int nodeCap, int keySmem) { return octree_node_bytes(no
 int launch_octree(const Geom& g, int n, const ExtractBuffers& b, int nodeCap, int keySmem, cudaStream_t st) {
     const size_t smem = octree_smem_bytes(nodeCap, keySmem);
     static size_t configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
+    if (smem > 32 * 1024 && configured < smem) {
         cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }

@@ -284,7 +284,7 @@ int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size
             const LevelGeom& P = g.lv[l - 1];
             const ResizeDims& d = dims[l];
             const int smem = 2 * d.SP * d.SH;
-            if (smem > 48 * 1024 && configured < smem) {
+            if (smem > 32 * 1024 && configured < smem) {
                 cudaFuncSetAttribute(resize_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
                 configured = smem;
             }

@@ -358,7 +358,7 @@ int launch_search_by_projection(const float bounds[4], const float* scale, int n
     P.ptsCap = ptsCap;
     const size_t smem = search_smem_bytes(cap);
     static size_t configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
+    if (smem > 32 * 1024 && configured < smem) {
         cudaFuncSetAttribute(search_by_projection_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }

@@ -437,7 +437,7 @@ int launch_search_by_projection_stereo(const float bounds[4], const float* scale
     P.ptsCap = ptsCap;
     const size_t smem = search_stereo_smem_bytes(cap);
     static size_t configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
+    if (smem > 32 * 1024 && configured < smem) {
         cudaFuncSetAttribute(search_by_projection_stereo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }
@@ -726,7 +726,7 @@ int launch_search_for_initialization(const float bounds[4], int windowSize, floa
     P.ptsCap = cap;
     const size_t smem = search_init_smem_bytes(cap);
     static size_t configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
+    if (smem > 32 * 1024 && configured < smem) {
         cudaFuncSetAttribute(search_for_initialization_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }

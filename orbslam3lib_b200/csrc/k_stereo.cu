@@ -270,7 +270,7 @@ int launch_stereo(const Geom& g, const float* scale, const float* invScale, cons
     }
     const size_t smem = stereo_smem_bytes(cap);
     static size_t configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
+    if (smem > 32 * 1024 && configured < smem) {
         cudaFuncSetAttribute(stereo_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }

@@ -56,10 +56,22 @@ struct Geom {
     int umax[kHalfPatch + 1];
 };
 
-// one FAST work item = a run of cells of one cell row (k_fast.cu)
-struct FastItem {
+// one FAST work item = a run of cells of one cell row (k_fast.cu).  Everything that depends only on the geometry is
+// worked out once on the host (fast_item_table), so a CTA starts with three 16-byte loads instead of ~130 scalar
+// instructions per thread.
+struct alignas(16) FastItem {
     short level, row, col0, ncols;
+    short ch, tp;             // tile rows (0: the cell row is skipped, ORBextractor_old.cc:812) and tile pitch
+    short colLo, colHi;       // tested tile columns [colLo, colHi)
+    short wCell, rpu;         // cell pitch; rows per phase-A unit (4..8), chosen to fill the CTA's threads
+    short xAddBase, yAdd;     // candidate coordinates relative to (minBorderX, minBorderY): col0 * wCell + 3, row * hCell + 3
+    unsigned tpMagic;         // floor(2^32 / tp) + 1
+    unsigned tileOff;         // byte offset of the tile's first byte inside the level plane
+    unsigned rowBytes;        // bytes per bulk-copied tile row
+    int cellRowBase;          // index of the cell row's first cell inside the image's cell array
+    int pad[2];
 };
+static_assert(sizeof(FastItem) == 48, "FastItem is loaded as three 16-byte words");
 
 // resize tables: per destination column / row (OpenCV linear resize coefficients)
 struct ResizeTap {
