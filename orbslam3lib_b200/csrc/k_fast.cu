@@ -8,11 +8,14 @@
 // disjoint and contiguous (a cell is wCell + 6 wide and loses 3 px on each side), so every pixel is scored once.
 //
 // Mapping: one CTA stages a run of up to FAST_ITEM_COLS cells of one cell row (a strip of the level plane) into
-// shared memory with 16-byte loads and runs up to two passes (iniThFAST for all cells, then minThFAST for the cells
-// that came back empty) of a four-phase pipeline, every phase using all threads of the CTA:
-//   A  test      a thread owns one 32-bit word column (4 px) x 8 rows: SWAR opposite-pair rejection (a 9-arc contains
+// shared memory with TMA bulk copies (one per tile row) and runs up to two passes (iniThFAST for all cells, then
+// minThFAST for the cells that came back empty) of a four-phase pipeline, every phase using all threads of the CTA.
+// Everything that depends only on the geometry (tile pitch, tested columns, offsets, rows per unit) comes precomputed
+// in the 48-byte work item (fast_item_table).
+//   A  test      a thread owns one 32-bit word column (4 px) x R rows (R = 4..8, picked per item so that the units
+//                fill the CTA's threads): SWAR opposite-pair rejection (a 9-arc contains
 //                one pixel of each opposite ring pair, so a corner needs |p0-v|>t or |p8-v|>t, and |p4-v|>t or
-//                |p12-v|>t) on 4 pixels at a time (VABSDIFF4 + carry-free byte compares); the 32 survivor flags of the
+//                |p12-v|>t) on 4 pixels at a time (VABSDIFF4 + carry-free byte compares); the survivor flags of the
 //                thread are compacted into a shared survivor list (warp scan of the popcounts, one shared atomic
 //                per warp);
 //   B  score     one thread per listed pixel: the 16 ring differences are packed two per register (k, k+8) and the
@@ -20,8 +23,9 @@
 //                score >= t  <=>  corner at t, so the score alone decides; scores go to a strip-wide score map;
 //   C  nms       the list is walked again: every scored pixel compares with its 8 neighbours inside its own cell's
 //                tested window and sets its bit in a keep bitmap;
-//   D  emit      one warp per cell: a lane owns a window row, counts its kept bits, a warp scan gives raster-order
-//                ranks, candidates go to the cell's slot array as packed (x | y << 12 | response << 24) relative to
+//   D  emit      one warp per cell: the window's column masks (<= 4 bitmap words) are built once, a lane owns window
+//                rows (lane, lane + 32), both counts go through one packed warp scan for the raster-order ranks,
+//                candidates go to the cell's slot array as packed (x | y << 12 | response << 24) relative to
 //                (minBorderX, minBorderY) as in :865-870.
 // Integer only; reads P bytes per image once (the 6-px overlaps hit L1/L2).
 #include "orbfe_internal.h"

@@ -16,7 +16,12 @@
 //     constants stay compile-time;
 //   * no warp specialisation: phases of the 2-3 co-resident CTAs of an SM overlap each other (expansion and epilogue on
 //     the ALU pipes of one CTA under the MMAs of another); the next tile's packed rows are prefetched into registers
-//     before the wait.
+//     before the wait;
+//   * wave quantisation: one (query tile) CTA per 128 rows means a 125k-row shard (1M rows over 8 GPUs) is 977 CTAs =
+//     2.2 waves of the 444 resident CTAs -> 27 % of the last wave idle.  For a single large problem the launcher can
+//     cut the TRAIN set into `nseg` segments (grid.z): CTA (tile, z) keeps the top 2 of its segment, writes them to a
+//     scratch array, and the last CTA of a tile to finish (atomic ticket) merges the nseg partial results in segment
+//     order -- strict "<" keeps the lowest train index on ties, as OpenCV does.
 #include <cstdlib>
 
 #include "orbfe_internal.h"
@@ -93,7 +98,9 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
                                                             long long qCap, const uint8_t* __restrict__ t,
                                                             const int* __restrict__ ntArr, long long tCap,
                                                             long long nqSingle, long long ntSingle,
-                                                            int32_t* __restrict__ idx, int32_t* __restrict__ dist) {
+                                                            int32_t* __restrict__ idx, int32_t* __restrict__ dist,
+                                                            long long segLen, int4* __restrict__ partial,
+                                                            unsigned* __restrict__ ticket) {
     extern __shared__ __align__(128) uint8_t ktSmem[];
     uint8_t* sA = ktSmem;
     uint8_t* sB = ktSmem + KT_M * 256;
@@ -135,8 +142,11 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
 
     int d1 = -1, i1 = -1, d2 = -1, i2 = -1;
     uint32_t phase = 0;
-    for (long long sb = 0; sb < nt; sb += (1ll << (KT_S - 1))) {
-        const int ns = (int)min(nt - sb, 1ll << (KT_S - 1));
+    // train rows of this CTA: everything, or segment blockIdx.z of gridDim.z (segLen is a multiple of KT_N)
+    const long long tBeg = gridDim.z > 1 ? min(nt, (long long)blockIdx.z * segLen) : 0;
+    const long long tEnd = gridDim.z > 1 ? min(nt, tBeg + segLen) : nt;
+    for (long long sb = tBeg; sb < tEnd; sb += (1ll << (KT_S - 1))) {
+        const int ns = (int)min(tEnd - sb, 1ll << (KT_S - 1));
         int b1 = KT_EMPTY, b2 = KT_EMPTY;    // keys relative to the current chunk: (acc << S) + (column - chunk base)
         const int ntiles = (ns + KT_N - 1) / KT_N;
         uint4 nx[KT_RPT][2];
@@ -223,7 +233,32 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
         merge(b1);
         merge(b2);
     }
-    if (row < nq) {
+    if (gridDim.z > 1) {
+        // partial top 2 of this segment -> scratch; the last CTA of the tile merges all segments in train order
+        const long long rowsPad = (long long)gridDim.x * KT_M;
+        partial[(long long)blockIdx.z * rowsPad + row] = make_int4(i1, i2, d1, d2);
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) *tmemSlot = atomicAdd(&ticket[blockIdx.x], 1u);    // tmemSlot is free: `tmem` holds the address
+        __syncthreads();
+        const bool last = *tmemSlot == gridDim.z - 1;
+        if (last) {
+            __threadfence();
+            i1 = i2 = d1 = d2 = -1;
+            for (int z = 0; z < (int)gridDim.z; z++) {
+                const int4 pz = __ldcg(&partial[(long long)z * rowsPad + row]);
+                if (pz.x >= 0 && (i1 < 0 || pz.z < d1)) { d2 = d1; i2 = i1; d1 = pz.z; i1 = pz.x; }
+                else if (pz.x >= 0 && (i2 < 0 || pz.z < d2)) { d2 = pz.z; i2 = pz.x; }
+                if (pz.y >= 0 && (i2 < 0 || pz.w < d2)) { d2 = pz.w; i2 = pz.y; }
+            }
+            if (tid == 0) ticket[blockIdx.x] = 0;    // ready for the next launch
+        }
+        if (last && row < nq) {
+            const long long o = ((long long)pair * qCap + row) * 2;
+            *reinterpret_cast<int2*>(idx + o) = make_int2(i1, i2);
+            *reinterpret_cast<int2*>(dist + o) = make_int2(d1, d2);
+        }
+    } else if (row < nq) {
         const long long o = ((long long)pair * qCap + row) * 2;
         *reinterpret_cast<int2*>(idx + o) = make_int2(i1, i2);
         *reinterpret_cast<int2*>(dist + o) = make_int2(d1, d2);
@@ -233,18 +268,62 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(KT_N) : "memory");
 }
 
+// train segments for one large problem: the smallest count (<= 8) whose CTA total fills the resident-CTA waves to
+// >= 95 %, else the best; segments stay >= 16k rows.  ORBFE_KNN_SEGS=n forces n (tests).
+static int kt_pick_segments(long long tiles, long long nt, int resident) {
+    if (const char* e = getenv("ORBFE_KNN_SEGS")) {
+        const int v = atoi(e);
+        if (v >= 1) return (int)(v < 64 ? v : 64);
+    }
+    int best = 1;
+    double bestEff = 0;
+    for (int sgs = 1; sgs <= 8; sgs++) {
+        if (sgs > 1 && nt / sgs < 16384) break;
+        const long long ctas = tiles * sgs, waves = (ctas + resident - 1) / resident;
+        const double eff = (double)ctas / (double)(waves * resident);
+        if (eff > bestEff + 1e-9) { bestEff = eff; best = sgs; }
+        if (eff >= 0.95) break;
+    }
+    return best;
+}
+
 int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_t* t, const int* nt, long long tCap,
                    int npairs, long long nqSingle, long long ntSingle, long long maxNq, int32_t* idx, int32_t* dist,
                    cudaStream_t st) {
     static unsigned long long configured = 0;
+    static int resident = 0;
     int dev = 0;
     cudaGetDevice(&dev);
     if (!((configured >> (dev & 63)) & 1ull)) {
         cudaFuncSetAttribute(knn2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KT_SMEM);
         configured |= 1ull << (dev & 63);
     }
-    const dim3 grid((unsigned)((maxNq + KT_M - 1) / KT_M), npairs);
-    knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist);
+    if (resident == 0) {
+        int sms = 0, perSm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, knn2_tc_kernel, KT_THREADS, KT_SMEM);
+        resident = sms * (perSm > 0 ? perSm : 1);
+    }
+    const long long tiles = (maxNq + KT_M - 1) / KT_M;
+    int nseg = 1;
+    if (npairs == 1 && !nq && !nt) nseg = kt_pick_segments(tiles, ntSingle, resident);
+    if (nseg <= 1) {
+        const dim3 grid((unsigned)tiles, npairs);
+        knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist, 0, nullptr,
+                                                          nullptr);
+        return 1;
+    }
+    // stream-ordered scratch: partial results [nseg][tiles * 128] + one ticket per tile
+    const long long segLen = (((ntSingle + nseg - 1) / nseg) + KT_N - 1) / KT_N * KT_N;
+    const size_t partialBytes = (size_t)nseg * tiles * KT_M * sizeof(int4), ticketBytes = (size_t)tiles * sizeof(unsigned);
+    uint8_t* scratch = nullptr;
+    if (cudaMallocAsync(&scratch, partialBytes + ticketBytes, st) != cudaSuccess) return 0;
+    cudaMemsetAsync(scratch + partialBytes, 0, ticketBytes, st);
+    const dim3 grid((unsigned)tiles, 1, nseg);
+    knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist, segLen,
+                                                      reinterpret_cast<int4*>(scratch),
+                                                      reinterpret_cast<unsigned*>(scratch + partialBytes));
+    cudaFreeAsync(scratch, st);
     return 1;
 }
 

@@ -155,3 +155,40 @@ def test_tensor_core_path_super_blocks(oracle):
     ri, rd = oracle.knn2_hamming(q[sel], t, threads=8)
     np.testing.assert_array_equal(idx[sel], ri)
     np.testing.assert_array_equal(dist[sel], rd)
+
+
+def test_tensor_core_path_train_segments(oracle):
+    """one large problem on few query tiles: the launcher cuts the train set into segments (grid.z) to fill the last
+    wave of CTAs and the last CTA of a tile merges the partial top 2 in segment order.  Forced here with
+    ORBFE_KNN_SEGS (read per call); ties that straddle a segment boundary keep the lower train index first."""
+    import os
+    nq, nt = 80000, 40001          # >= 296 x 256 query rows: the tcgen05 path
+    q = scenes.descriptors(nq, 61)
+    t = scenes.descriptors(nt, 62)
+    seg3 = ((nt + 2) // 3 + 127) // 128 * 128          # segment length for 3 segments
+    t[seg3 - 1] = q[5]
+    t[seg3] = q[5]                                     # exact copies on both sides of the first boundary
+    t[2 * seg3 + 5] = q[9]
+    t[17] = q[9]
+    t[nt - 1] = q[77]                                  # best match in the last (short) segment
+    old = os.environ.get("ORBFE_KNN_SEGS")
+    try:
+        os.environ["ORBFE_KNN_SEGS"] = "1"
+        base_i, base_d = BFMatcher().knnMatch(q, t)
+        for segs in (3, 8, 64):
+            os.environ["ORBFE_KNN_SEGS"] = str(segs)
+            idx, dist = BFMatcher().knnMatch(q, t)
+            np.testing.assert_array_equal(idx, base_i)
+            np.testing.assert_array_equal(dist, base_d)
+    finally:
+        if old is None:
+            os.environ.pop("ORBFE_KNN_SEGS", None)
+        else:
+            os.environ["ORBFE_KNN_SEGS"] = old
+    assert base_i[5].tolist() == [seg3 - 1, seg3] and base_d[5].tolist() == [0, 0]
+    assert base_i[9].tolist() == [17, 2 * seg3 + 5] and base_d[9].tolist() == [0, 0]
+    assert base_i[77, 0] == nt - 1 and base_d[77, 0] == 0
+    sel = np.arange(0, nq, 937)
+    ri, rd = oracle.knn2_hamming(q[sel], t, threads=8)
+    np.testing.assert_array_equal(base_i[sel], ri)
+    np.testing.assert_array_equal(base_d[sel], rd)
