@@ -307,17 +307,20 @@ int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_
     const long long tiles = (maxNq + KT_M - 1) / KT_M;
     int nseg = 1;
     if (npairs == 1 && !nq && !nt) nseg = kt_pick_segments(tiles, ntSingle, resident);
+    // stream-ordered scratch for the segmented launch: partial results [nseg][tiles * 128] + one ticket per tile
+    const long long segLen = (((ntSingle + (nseg > 1 ? nseg : 1) - 1) / (nseg > 1 ? nseg : 1)) + KT_N - 1) / KT_N * KT_N;
+    const size_t partialBytes = (size_t)nseg * tiles * KT_M * sizeof(int4), ticketBytes = (size_t)tiles * sizeof(unsigned);
+    uint8_t* scratch = nullptr;
+    if (nseg > 1 && cudaMallocAsync(&scratch, partialBytes + ticketBytes, st) != cudaSuccess) {
+        cudaGetLastError();    // no memory pool / no memory: the unsegmented launch needs no scratch
+        nseg = 1;
+    }
     if (nseg <= 1) {
         const dim3 grid((unsigned)tiles, npairs);
         knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist, 0, nullptr,
                                                           nullptr);
         return 1;
     }
-    // stream-ordered scratch: partial results [nseg][tiles * 128] + one ticket per tile
-    const long long segLen = (((ntSingle + nseg - 1) / nseg) + KT_N - 1) / KT_N * KT_N;
-    const size_t partialBytes = (size_t)nseg * tiles * KT_M * sizeof(int4), ticketBytes = (size_t)tiles * sizeof(unsigned);
-    uint8_t* scratch = nullptr;
-    if (cudaMallocAsync(&scratch, partialBytes + ticketBytes, st) != cudaSuccess) return 0;
     cudaMemsetAsync(scratch + partialBytes, 0, ticketBytes, st);
     const dim3 grid((unsigned)tiles, 1, nseg);
     knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist, segLen,
