@@ -28,6 +28,11 @@
 //                candidates go to the cell's slot array as packed (x | y << 12 | response << 24) relative to
 //                (minBorderX, minBorderY) as in :865-870.
 // Integer only; reads P bytes per image once (the 6-px overlaps hit L1/L2).
+#include <cuda.h>
+
+#include <cstdlib>
+#include <cstring>
+
 #include "orbfe_internal.h"
 
 namespace orbfe {
@@ -319,8 +324,9 @@ __global__ void __launch_bounds__(FAST_THREADS, ORBFE_FAST_MINB) fast_cells_kern
                                                                   const FastItem* __restrict__ items,
                                                                   uint32_t* __restrict__ slots,
                                                                   int* __restrict__ cellCount, int tileBytes,
-                                                                  int kbitsBytes, int listBytes) {
-    extern __shared__ __align__(16) uint8_t smem[];
+                                                                  int kbitsBytes, int listBytes,
+                                                                  const __grid_constant__ FastMaps maps, int useMaps) {
+    extern __shared__ __align__(128) uint8_t smem[];
     __shared__ int sCnt[2];
     __shared__ __align__(8) uint64_t sBar;
     __shared__ __align__(4) uint8_t sEdge[1024];
@@ -337,9 +343,9 @@ __global__ void __launch_bounds__(FAST_THREADS, ORBFE_FAST_MINB) fast_cells_kern
     }
 
     FastStrip s;
-    s.tp = it.tp;
+    s.tp = useMaps ? it.boxW : it.tp;    // tensor-map path: the tile has the level's box pitch
     s.kw = s.tp >> 5;
-    s.tpMagic = it.tpMagic;
+    s.tpMagic = useMaps ? it.boxMagic : it.tpMagic;
     s.cedge = sEdge;
     s.ch = ch;
     s.tile = smem;
@@ -362,7 +368,15 @@ __global__ void __launch_bounds__(FAST_THREADS, ORBFE_FAST_MINB) fast_cells_kern
         const uint32_t rowBytes = it.rowBytes;
         if (threadIdx.x == 0) mbar_init(&sBar, 1);
         __syncthreads();
-        if (threadIdx.x < 32) {
+        if (useMaps) {
+            // ONE tiled TMA load per strip (box = boxW x boxH x 1 image of the level's tensor map) instead of one bulk
+            // copy per tile row: the TMA unit serves ~1 operation instead of ~44 per tile
+            if (threadIdx.x == 0) {
+                const int y0 = (int)(it.tileOff / (unsigned)L.pitch), x0 = (int)(it.tileOff - (unsigned)y0 * (unsigned)L.pitch);
+                mbar_arrive_expect_tx(&sBar, (uint32_t)it.boxW * (uint32_t)it.boxH);
+                tma_load_3d(s.tile, &maps.m[it.level], x0, y0, img, &sBar);
+            }
+        } else if (threadIdx.x < 32) {
             if (threadIdx.x == 0) mbar_arrive_expect_tx(&sBar, rowBytes * (uint32_t)ch);
             __syncwarp();
             for (int r = threadIdx.x; r < ch; r += 32) bulk_g2s(s.tile + r * s.tp, plane + (size_t)r * L.pitch, rowBytes, &sBar);
@@ -412,9 +426,26 @@ int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* 
         const LevelGeom& L = g.lv[l];
         const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
         if (L.wCell > 97) maxTile = 1 << 28;    // phase D: a cell window spans at most four bitmap words
+        // strip width of the level: a TMA box is at most 256 elements wide
+        int cols = FAST_ITEM_COLS;
+        while (cols > 1 && ((cols * L.wCell + 6 + 31 + 31) & ~31) + 32 > 256) cols--;
+        // the level's box: widest strip x tallest cell row (multiple of 32 columns)
+        int boxW = 32;
+        const int boxH = L.hCell + 6;
+        for (int c0 = 0; c0 < L.nCols; c0 += cols) {
+            const int nc = L.nCols - c0 < cols ? L.nCols - c0 : cols;
+            const int xs = kMinBorder + c0 * L.wCell;
+            int xe = kMinBorder + (c0 + nc - 1) * L.wCell + L.wCell + 6;
+            if (xe > maxBX) xe = maxBX;
+            const int tp = ((kXOff + (xe > xs ? xe : xs) + 31) & ~31) - ((kXOff + xs) & ~31);
+            if (tp > boxW) boxW = tp;
+        }
+        if (boxW > 256 || boxH > 256) maxTile = 1 << 28;
+        if (boxW * boxH > maxTile) maxTile = boxW * boxH;
+        if ((boxW / 32) * 4 * boxH > maxK) maxK = (boxW / 32) * 4 * boxH;
         for (int r = 0; r < L.nRows; r++)
-            for (int c0 = 0; c0 < L.nCols; c0 += FAST_ITEM_COLS) {
-                const int nc = L.nCols - c0 < FAST_ITEM_COLS ? L.nCols - c0 : FAST_ITEM_COLS;
+            for (int c0 = 0; c0 < L.nCols; c0 += cols) {
+                const int nc = L.nCols - c0 < cols ? L.nCols - c0 : cols;
                 const int tpMax = ((nc * L.wCell + 6 + 31 + 31) & ~31) + 32;
                 if (out && n < cap) {
                     FastItem it{};
@@ -442,6 +473,9 @@ int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* 
                     it.tileOff = (unsigned)((iniY + kEdge) * L.pitch + ax0);
                     it.rowBytes = (unsigned)(tp < L.pitch - ax0 ? tp : L.pitch - ax0);
                     it.cellRowBase = L.cellBase + r * L.nCols;
+                    it.boxW = (short)boxW;
+                    it.boxH = (short)boxH;
+                    it.boxMagic = 0xffffffffu / (unsigned)boxW + 1u;
                     // rows per phase-A unit: a unit is one 4-px word column x R rows and costs ~R; the units are dealt
                     // to FAST_THREADS threads in rounds, so pick the R with the fewest rounds x R (ties: larger R)
                     const int th = ch - 6, nwc = ((it.colHi + 3) >> 2) - (it.colLo >> 2);
@@ -478,9 +512,68 @@ int fast_smem_bytes(int tileBytes, int kbitsBytes, int listBytes) {
     return 2 * tileBytes + kbitsBytes + listBytes;
 }
 
+// ---- tensor maps ------------------------------------------------------------------------------------------------------
+// One CUtensorMap per level over the pyramid slabs of a launch: u8, dims {pitch, plane rows, n images}, strides
+// {pitch, slabBytes}, box {boxW, boxH, 1} (the level's box of fast_item_table), no swizzle, zero fill.  The driver entry
+// point comes from cudaGetDriverEntryPoint, so liborbfe.so does not link libcuda.  ORBFE_FAST_TMAP=0 keeps the
+// per-row bulk copies (A/B measurements); so does any failure to encode.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn fast_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        const char* e = getenv("ORBFE_FAST_TMAP");
+        if (e && atoi(e) == 0) return (EncodeTiledFn) nullptr;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return (EncodeTiledFn) nullptr;
+        }
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+static bool fast_encode_maps(const Geom& g, const uint8_t* pyr, int n, FastMaps* out) {
+    EncodeTiledFn enc = fast_encode_fn();
+    if (!enc) return false;
+    static_assert(sizeof(CUtensorMap) == 128, "FastMaps holds 128-byte tensor maps");
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& L = g.lv[l];
+        const int maxBX = L.w - kMinBorder;
+        int cols = FAST_ITEM_COLS;
+        while (cols > 1 && ((cols * L.wCell + 6 + 31 + 31) & ~31) + 32 > 256) cols--;
+        int boxW = 32;
+        for (int c0 = 0; c0 < L.nCols; c0 += cols) {    // same box as fast_item_table
+            const int nc = L.nCols - c0 < cols ? L.nCols - c0 : cols;
+            const int xs = kMinBorder + c0 * L.wCell;
+            int xe = kMinBorder + (c0 + nc - 1) * L.wCell + L.wCell + 6;
+            if (xe > maxBX) xe = maxBX;
+            const int tp = ((kXOff + (xe > xs ? xe : xs) + 31) & ~31) - ((kXOff + xs) & ~31);
+            if (tp > boxW) boxW = tp;
+        }
+        const int boxH = L.hCell + 6;
+        if (boxW > 256 || boxH > 256 || (L.pitch & 15) || (g.slabBytes & 15) || (L.planeOff & 15)) return false;
+        const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.h + 2 * kEdge), (cuuint64_t)n};
+        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)g.slabBytes};
+        const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1u};
+        const cuuint32_t estr[3] = {1u, 1u, 1u};
+        CUtensorMap tm;
+        const CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(pyr) + L.planeOff, dims, strides, box,
+                               estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return false;
+        memcpy(out->m[l], &tm, 128);
+    }
+    return true;
+}
+
 int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, int tileBytes,
                 int kbitsBytes, int listBytes, uint32_t* slots, int* cellCount, cudaStream_t st) {
-    if (nItems <= 0) return 0;
+    if (nItems <= 0 || n <= 0) return 0;
     const int smem = fast_smem_bytes(tileBytes, kbitsBytes, listBytes);
     static int configured = 0;
     // the 48 KiB default limit counts static + dynamic shared memory: opt in early (static usage here is <= 16 KiB)
@@ -488,8 +581,26 @@ int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items,
         cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    fast_cells_kernel<<<dim3(nItems, n), FAST_THREADS, smem, st>>>(g, pyr, items, slots, cellCount, tileBytes,
-                                                                   kbitsBytes, listBytes);
+    // tensor maps of this launch, cached per thread on (slab pointer, image count, geometry)
+    struct MapCache {
+        const uint8_t* pyr = nullptr;
+        int n = 0, w = 0, h = 0, nlevels = 0, ok = 0;
+        unsigned long long slab = 0;
+        FastMaps maps;
+    };
+    static thread_local MapCache mc;
+    if (mc.pyr != pyr || mc.n != n || mc.w != g.width || mc.h != g.height || mc.nlevels != g.nlevels || mc.slab != g.slabBytes) {
+        mc.pyr = pyr;
+        mc.n = n;
+        mc.w = g.width;
+        mc.h = g.height;
+        mc.nlevels = g.nlevels;
+        mc.slab = g.slabBytes;
+        memset(&mc.maps, 0, sizeof(mc.maps));
+        mc.ok = fast_encode_maps(g, pyr, n, &mc.maps) ? 1 : 0;
+    }
+    fast_cells_kernel<<<dim3(nItems, n), FAST_THREADS, smem, st>>>(g, pyr, items, slots, cellCount, tileBytes, kbitsBytes,
+                                                                   listBytes, mc.maps, mc.ok);
     return 1;
 }
 

@@ -69,7 +69,14 @@ struct alignas(16) FastItem {
     unsigned tileOff;         // byte offset of the tile's first byte inside the level plane
     unsigned rowBytes;        // bytes per bulk-copied tile row
     int cellRowBase;          // index of the cell row's first cell inside the image's cell array
-    int pad[2];
+    unsigned boxMagic;        // floor(2^32 / boxW) + 1
+    short boxW, boxH;         // tensor-map path: the level's TMA box (tile pitch and rows), same for all its items
+};
+
+// one CUtensorMap (128 bytes, 64-byte aligned) per pyramid level: u8 tensor {pitch, plane rows, images} over the
+// pyramid slabs of one launch (k_fast.cu: fast_encode_maps); passed to the kernel as a __grid_constant__ parameter
+struct alignas(64) FastMaps {
+    unsigned char m[ORBFE_MAX_LEVELS][128];
 };
 static_assert(sizeof(FastItem) == 48, "FastItem is loaded as three 16-byte words");
 
@@ -158,6 +165,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "ORBFE_DONE_%=:\n"
         "}\n" ::"r"(smem_u32(bar)),
         "r"(parity)
+        : "memory");
+}
+// one tiled TMA load (cp.async.bulk.tensor, SASS UTMALDG) of a 3-D box at (x, y, z); out-of-bounds elements are
+// zero-filled and still counted: the transaction size is always the full box
+__device__ __forceinline__ void tma_load_3d(void* dstSmem, const void* tmap, int x, int y, int z, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+            smem_u32(dstSmem)),
+        "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
         : "memory");
 }
 __device__ __forceinline__ void bulk_g2s(void* dstSmem, const void* srcGlobal, uint32_t bytes, uint64_t* bar) {
