@@ -8,7 +8,8 @@
 // disjoint and contiguous (a cell is wCell + 6 wide and loses 3 px on each side), so every pixel is scored once.
 //
 // Mapping: one CTA stages a run of up to FAST_ITEM_COLS cells of one cell row (a strip of the level plane) into
-// shared memory with TMA bulk copies (one per tile row) and runs up to two passes (iniThFAST for all cells, then
+// shared memory with ONE tiled TMA load (cp.async.bulk.tensor.3d on the level's CUtensorMap; fallback: one bulk copy
+// per tile row) and runs up to two passes (iniThFAST for all cells, then
 // minThFAST for the cells that came back empty) of a four-phase pipeline, every phase using all threads of the CTA.
 // Everything that depends only on the geometry (tile pitch, tested columns, offsets, rows per unit) comes precomputed
 // in the 48-byte work item (fast_item_table).
@@ -360,7 +361,7 @@ __global__ void __launch_bounds__(FAST_THREADS, ORBFE_FAST_MINB) fast_cells_kern
     s.rpu = it.rpu;
 
     {
-        // staging: one TMA bulk copy (cp.async.bulk -> UBLKCP) per tile row, issued by the lanes of warp 0 and
+        // staging: one tiled TMA load of the strip's box (or one bulk copy per tile row, issued by the lanes of warp 0),
         // completing on an mbarrier; meanwhile every thread clears the score map + keep bitmap (contiguous: one
         // 16-byte loop over both allocations) and the edge table.
         // Tile columns past the plane pitch are never copied: they lie beyond every tested pixel's ring.
