@@ -417,6 +417,19 @@ __global__ void __launch_bounds__(FAST_THREADS, ORBFE_FAST_MINB) fast_cells_kern
     fast_emit(s, empty, false, slotsRow, counts, g.slotCap, it.col0, xAddBase, yAdd);
 }
 
+// strip width (cells) of a level: at most FAST_ITEM_COLS; a TMA box is at most 256 elements wide; and the tile of a
+// level with tall cells (small levels have few, tall cell rows) must not dictate the shared-memory allocation of every
+// level -- its strips are narrowed until the tile fits ORBFE_FAST_TILE_BUDGET bytes
+#ifndef ORBFE_FAST_TILE_BUDGET
+#define ORBFE_FAST_TILE_BUDGET 12288
+#endif
+static int fast_level_cols(const LevelGeom& L) {
+    int cols = FAST_ITEM_COLS;
+    auto tpMax = [&](int c) { return ((c * L.wCell + 6 + 31 + 31) & ~31) + 32; };
+    while (cols > 1 && (tpMax(cols) > 256 || tpMax(cols) * (L.hCell + 6) > ORBFE_FAST_TILE_BUDGET)) cols--;
+    return cols;
+}
+
 // host: work items of one geometry.  Every cell row of every level is cut into runs of <= FAST_ITEM_COLS cells, and
 // everything the kernel needs that depends only on the geometry is worked out here.
 // tileBytes: strip tile (and score map) bytes; kbitsBytes: keep bitmap; listBytes: survivor list (worst case: every
@@ -428,8 +441,7 @@ int fast_item_table(const Geom& g, FastItem* out, int cap, int* tileBytes, int* 
         const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
         if (L.wCell > 97) maxTile = 1 << 28;    // phase D: a cell window spans at most four bitmap words
         // strip width of the level: a TMA box is at most 256 elements wide
-        int cols = FAST_ITEM_COLS;
-        while (cols > 1 && ((cols * L.wCell + 6 + 31 + 31) & ~31) + 32 > 256) cols--;
+        const int cols = fast_level_cols(L);
         // the level's box: widest strip x tallest cell row (multiple of 32 columns)
         int boxW = 32;
         const int boxH = L.hCell + 6;
@@ -545,8 +557,7 @@ static bool fast_encode_maps(const Geom& g, const uint8_t* pyr, int n, FastMaps*
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& L = g.lv[l];
         const int maxBX = L.w - kMinBorder;
-        int cols = FAST_ITEM_COLS;
-        while (cols > 1 && ((cols * L.wCell + 6 + 31 + 31) & ~31) + 32 > 256) cols--;
+        const int cols = fast_level_cols(L);
         int boxW = 32;
         for (int c0 = 0; c0 < L.nCols; c0 += cols) {    // same box as fast_item_table
             const int nc = L.nCols - c0 < cols ? L.nCols - c0 : cols;
