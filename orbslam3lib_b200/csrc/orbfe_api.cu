@@ -330,6 +330,9 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
         for (int v = 0; v < 2; v++) {
             ResizeDims& d = ex->rsDims[v][l];
             d.rpt = v == 0 ? 16 : 4;
+            if (v == 0)
+                if (const char* e = getenv("ORBFE_RESIZE_RPT"))    // rows per thread of the large-batch resize tiles (A/B)
+                    if (atoi(e) >= 1 && atoi(e) <= 64) d.rpt = atoi(e);
             resize_tile_dims(tx.data(), ty.data(), g.lv[l].w, g.lv[l].h, d.rpt, &d.SP, &d.SH);
             while (2 * d.SP * d.SH > 96 * 1024 && d.rpt > 1) {
                 d.rpt /= 2;
