@@ -751,6 +751,24 @@ void orc_extractor_stage_seconds(const orc_extractor* e, double out[7]) {
 }
 int64_t orc_extractor_sort_ties(const orc_extractor* e) { return e->sortTies; }
 
+int orc_distribute_octtree(orc_extractor* e, const orc_keypoint* keys, int n, int minX, int maxX, int minY, int maxY,
+                           int N, orc_keypoint* out, int cap, int64_t* ties) {
+    std::vector<KeyPt> in((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        in[i].x = keys[i].x; in[i].y = keys[i].y; in[i].size = keys[i].size; in[i].angle = keys[i].angle;
+        in[i].response = keys[i].response; in[i].octave = keys[i].octave; in[i].class_id = keys[i].class_id;
+    }
+    g_sortTies = 0;
+    std::vector<KeyPt> r = e->distributeOctTree(in, minX, maxX, minY, maxY, N);
+    if (ties) *ties = g_sortTies;
+    const int m = (int)r.size();
+    for (int i = 0; i < m && i < cap; ++i) {
+        out[i].x = r[i].x; out[i].y = r[i].y; out[i].size = r[i].size; out[i].angle = r[i].angle;
+        out[i].response = r[i].response; out[i].octave = r[i].octave; out[i].class_id = r[i].class_id;
+    }
+    return m;
+}
+
 int orc_extract_batch(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, const uint8_t* imgs,
                       int n, int w, int h, int stride, int lap0, int lap1, orc_keypoint* kps, uint8_t* desc, int cap,
                       int* counts, int* monos, int threads) {

@@ -5,10 +5,14 @@
  * Frame.cc brute-force Hamming matcher.  Only tests/, __graft_entry__.smoke() and bench.py's
  * cpu_baseline / --impl reference legs may load this library.  The product (liborbfe.so) never does.
  *
- * Parity status: the reference ships no golden vectors for this path ("parity unpinned" by the
- * reference itself).  The restated primitives are pinned against the genuine OpenCV
- * build in this container (cv2 4.13.0) by tests/test_oracle_vs_cv2.py and by the committed
- * fixtures in tests/golden/ that oracle/gen_golden.py produced from cv2.
+ * Parity status: PINNED.  The reference ships no golden vectors for this path, so the
+ * oracle is pinned against the reference itself run here: tests/test_oracle_ref.py compares it bit
+ * for bit with oracle/_ref/libext_old.so, the reference's own ORBextractor_old.cc compiled from
+ * /root/reference (oracle/ref_ext/make_ref_ext.py).  The restated OpenCV primitives are pinned
+ * against the genuine OpenCV build in this container (cv2 4.13.0) by tests/test_oracle_vs_cv2.py
+ * and tests/golden/primitives.npz.  Matcher-side call sites (ORBmatcher.cc / Frame.cc) cannot be
+ * compiled here (g2o / DBoW2 / Sophus member types); they are pinned by literal Python
+ * restatements (tests/test_search_rule.py) and by cv2.BFMatcher / cv2.norm / cv2.undistortPoints.
  */
 #ifndef ORB_ORACLE_H
 #define ORB_ORACLE_H
@@ -64,6 +68,10 @@ int  orc_level_keypoints(const orc_extractor*, int level, orc_keypoint* out, int
 void orc_extractor_stage_seconds(const orc_extractor*, double out[7]);
 /* number of compareNodes ties (equal count and UL.x, different node) seen by std::sort in the last call */
 int64_t orc_extractor_sort_ties(const orc_extractor*);
+/* ORBextractor::DistributeOctTree (ORBextractor_old.cc:557-781) alone, on caller-made keys (tests: stress inputs against
+ * the reference build oracle/_ref/libext_old.so).  *ties (nullable) = compareNodes ties seen by std::sort. */
+int orc_distribute_octtree(orc_extractor*, const orc_keypoint* keys, int n, int minX, int maxX, int minY, int maxY,
+                           int N, orc_keypoint* out, int cap, int64_t* ties);
 
 /* n images (contiguous, each h*stride bytes) over `threads` std::threads; outputs strided by cap.
  * returns 0.  counts[i], monos[i] per image. */

@@ -1,11 +1,15 @@
 #!/usr/bin/env python
-"""Generate tests/golden/*.npz from GENUINE OpenCV (cv2) + the Python restatement of the ORB-SLAM glue
-(oracle/py/cv2_oracle.py).  Test infrastructure.
+"""Generate tests/golden/*.npz.  Test infrastructure.
 
-The reference ships no golden vectors for this path and its CPU extractor cannot be compiled here,
-so the fixtures pin the C++ oracle (and, through it, the CUDA path) against real OpenCV primitives: cv2.resize,
-cv2.copyMakeBorder, cv2.FastFeatureDetector, cv2.GaussianBlur, cv2.fastAtan2, cv2.BFMatcher.  cv2 exists only in the
-build container; the fixtures travel, this script does not need to.
+The reference ships no golden vectors for this path, so the fixtures are outputs of the reference
+itself run here, and of the genuine OpenCV it depends on:
+  * extract_*.npz   the reference's own ORBextractor_old.cc, compiled from /root/reference into
+                    oracle/_ref/libext_old.so (oracle/ref_ext/make_ref_ext.py), cross-checked at generation time
+                    against cv2 primitives + the Python statement of the glue (oracle/py/cv2_oracle.py);
+  * primitives / stereo / undistort   genuine cv2.resize, copyMakeBorder, FastFeatureDetector, GaussianBlur,
+                    fastAtan2, BFMatcher, norm, undistortPoints;
+  * fisheye_*.npz   the reference's vendored Eigen 3.4.0 (oracle/_ref/libeigen_svd.so).
+cv2 and /root/reference exist only in the build container; the fixtures travel, this script does not need to.
 
     python oracle/gen_golden.py          # rewrites tests/golden/
 """
@@ -45,39 +49,63 @@ def sha(a):
 
 
 def gen_extract(case):
+    """extract_*.npz: outputs of the REFERENCE'S OWN extractor (oracle/_ref/libext_old.so = ORBextractor_old.cc compiled
+    from /root/reference, `make -C oracle ref_ext`) — tables, padded pyramid, per-level keypoints after the quadtree,
+    final keypoints / descriptors / monoIndex.  The same image goes through the cv2-backed Python statement
+    (genuine cv2 primitives + restated glue); generation FAILS unless the two agree bit for bit, so every fixture is
+    pinned from both sides: reference glue over cv2-pinned primitives == restated glue over real cv2 primitives.
+    The two intermediates the reference does not keep (FAST candidates before the quadtree, blurred planes) come from
+    the cv2 side."""
     import cv2
     import cv2_oracle
+    import ref_ext_lib
     from orbslam3lib_b200 import scenes
     name, kind, w, h, seed, nf, nl, ini, mn, lap = case
     img = scenes.make(kind, w, h, seed)
+    if not ref_ext_lib.available():
+        raise SystemExit("extract fixtures need oracle/_ref/libext_old.so (make -C oracle ref_ext; needs /root/reference)")
+    ref = ref_ext_lib.RefExtractor(nf, 1.2, nl, ini, mn)
+    mono, rk, desc = ref(img, lap)
     ex = cv2_oracle.Cv2Extractor(nf, 1.2, nl, ini, mn)
     ex.set_pattern(load_pattern())
-    mono, kps, desc = ex(img, lap)
+    mono_c, kps_c, desc_c = ex(img, lap)
+    kc = np.array([[k[0], k[1], k[2], k[3], k[4]] for k in kps_c], np.float32).reshape(-1, 5)
+    rk5 = np.stack([rk["x"], rk["y"], rk["size"], rk["angle"], rk["response"]], 1)
+    assert mono == mono_c and np.array_equal(rk5, kc) and np.array_equal(desc, desc_c), "reference build != cv2 statement"
+    assert np.array_equal(rk["octave"], np.array([k[5] for k in kps_c], np.int32))
+    assert np.array_equal(ref.features_per_level, ex.features_per_level) and np.array_equal(ref.umax, ex.umax)
     out = {
         "meta": np.array([w, h, seed, nf, nl, ini, mn, lap[0], lap[1]], np.int64),
         "scene": np.array(kind),
+        "source": np.array("oracle/_ref (ORBextractor_old.cc compiled from /root/reference, g++ libstdc++); "
+                           "cross-checked bit for bit against cv2 " + cv2.__version__ + " + oracle/py/cv2_oracle.py"),
         "opencv_version": np.array(cv2.__version__),
         "image_sha256": np.array(sha(img)),
         "mono": np.array(mono, np.int32),
-        "kps": np.array([[k[0], k[1], k[2], k[3], k[4]] for k in kps], np.float32).reshape(-1, 5),
-        "octave": np.array([k[5] for k in kps], np.int32),
+        "kps": rk5,
+        "octave": rk["octave"].astype(np.int32),
         "desc": desc,
-        "features_per_level": np.array(ex.features_per_level, np.int32),
-        "umax": np.array(ex.umax, np.int32),
-        "scale": np.array(ex.scale, np.float32),
+        "features_per_level": ref.features_per_level.astype(np.int32),
+        "umax": ref.umax.astype(np.int32),
+        "scale": ref.scale.astype(np.float32),
     }
     for l in range(nl):
-        out["padded_sha256_%d" % l] = np.array(sha(ex.pyr_padded[l]))
-        out["level_size_%d" % l] = np.array(ex.pyr[l].shape[::-1], np.int32)
+        padded = ref.level_padded(l)
+        assert np.array_equal(padded, ex.pyr_padded[l]), "ComputePyramid level %d" % l
+        out["padded_sha256_%d" % l] = np.array(sha(padded))
+        out["level_size_%d" % l] = np.array(ref.level_size(l), np.int32)
         out["cand_%d" % l] = np.array(ex.candidates[l], np.int32).reshape(-1, 3)
-        lk = ex.level_kps[l]
-        out["lkps_%d" % l] = np.array([[k[0], k[1], k[3], k[4]] for k in lk], np.float32).reshape(-1, 4)
+        lk = ref.level_keypoints(l)
+        lc = np.array([[k[0], k[1], k[3], k[4]] for k in ex.level_kps[l]], np.float32).reshape(-1, 4)
+        lr = np.stack([lk["x"], lk["y"], lk["angle"], lk["response"]], 1).astype(np.float32).reshape(-1, 4)
+        assert np.array_equal(lr, lc), "level %d keypoints after the quadtree" % l
+        out["lkps_%d" % l] = lr
         if ex.blurred[l] is not None:
             out["blur_sha256_%d" % l] = np.array(sha(ex.blurred[l]))
     # one small level stored verbatim so that a hash mismatch can be localised
-    out["padded_last"] = ex.pyr_padded[nl - 1]
+    out["padded_last"] = ref.level_padded(nl - 1)
     np.savez_compressed(os.path.join(GOLDEN, "extract_%s.npz" % name), **out)
-    print("extract_%s: %d keypoints, mono %d" % (name, len(kps), mono))
+    print("extract_%s: %d keypoints, mono %d (reference build == cv2 statement)" % (name, len(rk), mono))
 
 
 def gen_primitives():
@@ -209,6 +237,10 @@ def gen_fisheye():
 
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if "--extract-only" in sys.argv:
+        for c in EXTRACT_CASES:
+            gen_extract(c)
+        return
     if "--fisheye-only" in sys.argv:
         return gen_fisheye()
     if "--undistort-only" in sys.argv:

@@ -71,6 +71,8 @@ def lib():
         L.orc_extractor_stage_seconds.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_extractor_sort_ties.argtypes = [C.c_void_p]
         L.orc_extractor_sort_ties.restype = C.c_int64
+        L.orc_distribute_octtree.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_distribute_octtree.restype = C.c_int
         L.orc_extract_batch.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                         C.c_void_p, C.c_void_p, C.c_int]
@@ -233,6 +235,15 @@ class OracleExtractor:
 
     def sort_ties(self):
         return int(lib().orc_extractor_sort_ties(self._h))
+
+    def distribute(self, keys, min_x, max_x, min_y, max_y, n_wanted):
+        """ORBextractor::DistributeOctTree on caller-made keys -> (kept keys, compareNodes ties seen by std::sort)."""
+        k = np.ascontiguousarray(keys, KP_DTYPE)
+        out = np.zeros(max(len(k), 1), KP_DTYPE)
+        ties = C.c_int64(0)
+        n = lib().orc_distribute_octtree(self._h, _p(k), len(k), int(min_x), int(max_x), int(min_y), int(max_y),
+                                         int(n_wanted), _p(out), len(out), C.byref(ties))
+        return out[:n].copy(), int(ties.value)
 
 
 def extract_batch(imgs, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, lapping=(0, 0), threads=1,

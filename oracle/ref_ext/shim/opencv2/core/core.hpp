@@ -1,0 +1,2 @@
+// stands in for <opencv2/core/core.hpp> when the reference extractor is compiled by oracle/ref_ext/make_ref_ext.py (test infrastructure)
+#include "cv_shim.h"
