@@ -148,7 +148,7 @@ public:
         }
         for (int e = 0; e < 2; e++) {
             K[e]->resize(counts[e]);
-            if (counts[e] > 0) std::memcpy(K[e]->data(), kps.data() + (size_t)e * mCap, (size_t)counts[e] * sizeof(orbfe_keypoint));
+            if (counts[e] > 0) std::memcpy((void*)K[e]->data(), kps.data() + (size_t)e * mCap, (size_t)counts[e] * sizeof(orbfe_keypoint));
             D[e]->create(counts[e], 32, CV_8U);
             if (counts[e] > 0) std::memcpy(D[e]->data, mDescScratch.data() + (size_t)e * mCap * 32, (size_t)counts[e] * 32);
             *monoOut[e] = monos[e];

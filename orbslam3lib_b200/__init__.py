@@ -7,3 +7,4 @@ from ._lib import KP_DTYPE, OrbfeError, build  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import BFMatcher, ORBmatcher  # noqa: F401
 from .sharded import ShardedMatcher, shard_range  # noqa: F401
+from .wire import LynxHardwareAccelerator  # noqa: F401

@@ -17,12 +17,16 @@ namespace orbfe {
 
 __device__ char4 d_pattern[256];    // 256 x (x0,y0,x1,y1), ORBextractor_old.cc:151-409 (global: loaded coalesced)
 
-void upload_pattern() {
-    static bool done[64] = {false};    // __device__ variables are per device
+// __device__ variables are per device.  The copy is issued on the launch stream `st` (a cudaStreamNonBlocking stream
+// does not order against the legacy default stream), so the first describe_kernel of a device cannot overtake it.
+void upload_pattern(cudaStream_t st) {
+    static std::mutex mu;
+    static bool done[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(mu);
     if (dev < 0 || dev >= 64 || !done[dev]) {
-        cudaMemcpyToSymbol(d_pattern, ORBFE_BIT_PATTERN_31, 1024);
+        cudaMemcpyToSymbolAsync(d_pattern, ORBFE_BIT_PATTERN_31, 1024, 0, cudaMemcpyHostToDevice, st);
         if (dev >= 0 && dev < 64) done[dev] = true;
     }
 }
@@ -228,18 +232,15 @@ __global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_co
 
 int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st) {
     const size_t smem = sizeof(int) * (size_t)(g.outCap + 1);
-    static size_t configured = 0;
-    if (smem > 32 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, pack_kernel, smem);
     pack_kernel<<<n, PK_THREADS, smem, st>>>(g, b, lap0, lap1);
     return 1;
 }
 
 int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
                     cudaStream_t st) {
-    upload_pattern();
+    upload_pattern(st);
     // a few keypoints per warp so that the shared pattern load is amortised; small batches keep one keypoint per warp
     const int full = (g.outCap + DS_WARPS - 1) / DS_WARPS;
     const int gx = n >= 64 ? std::min(full, 24) : full;

@@ -587,12 +587,8 @@ int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items,
                 int kbitsBytes, int listBytes, uint32_t* slots, int* cellCount, cudaStream_t st) {
     if (nItems <= 0 || n <= 0) return 0;
     const int smem = fast_smem_bytes(tileBytes, kbitsBytes, listBytes);
-    static int configured = 0;
-    // the 48 KiB default limit counts static + dynamic shared memory: opt in early (static usage here is <= 16 KiB)
-    if (smem > 32 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = smem;
-    }
+    static SmemOptIn optIn;    // static usage here is <= 16 KiB
+    smem_opt_in(optIn, fast_cells_kernel, (size_t)smem);
     // tensor maps of this launch, cached per thread on (slab pointer, image count, geometry)
     struct MapCache {
         const uint8_t* pyr = nullptr;

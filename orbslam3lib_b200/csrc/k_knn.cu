@@ -383,13 +383,8 @@ int launch_knn2(const uint8_t* q, const int* nq, long long qCap, const uint8_t* 
         return launch_knn2_tc(q, nq, qCap, t, nt, tCap, npairs, nqSingle, ntSingle, maxNq, idx, dist, st);
     } else if (knn_use_mma()) {
         const dim3 grid((unsigned)((maxNq + KM_ROWS - 1) / KM_ROWS), npairs);
-        static unsigned long long configured = 0;    // one bit per device: the attribute is per context
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (!((configured >> (dev & 63)) & 1ull)) {
-            cudaFuncSetAttribute(knn2_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KM_SMEM);
-            configured |= 1ull << (dev & 63);
-        }
+        static SmemOptIn optIn;
+        smem_opt_in(optIn, knn2_mma_kernel, (size_t)KM_SMEM);
         knn2_mma_kernel<<<grid, KM_THREADS, KM_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist);
     } else {
         const dim3 grid((unsigned)((maxNq + KNN_THREADS - 1) / KNN_THREADS), npairs);

@@ -271,10 +271,12 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
 // train segments for one large problem: the smallest count (<= 8) whose CTA total fills the resident-CTA waves to
 // >= 95 %, else the best; segments stay >= 16k rows.  ORBFE_KNN_SEGS=n forces n (tests).
 static int kt_pick_segments(long long tiles, long long nt, int resident) {
-    if (const char* e = getenv("ORBFE_KNN_SEGS")) {
-        const int v = atoi(e);
-        if (v >= 1) return (int)(v < 64 ? v : 64);
-    }
+    static const int forced = [] {    // read once: the environment is not re-scanned per launch
+        const char* e = getenv("ORBFE_KNN_SEGS");
+        const int v = e ? atoi(e) : 0;
+        return v >= 1 ? (v < 64 ? v : 64) : 0;
+    }();
+    if (forced) return forced;
     int best = 1;
     double bestEff = 0;
     for (int sgs = 1; sgs <= 8; sgs++) {
@@ -290,20 +292,20 @@ static int kt_pick_segments(long long tiles, long long nt, int resident) {
 int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_t* t, const int* nt, long long tCap,
                    int npairs, long long nqSingle, long long ntSingle, long long maxNq, int32_t* idx, int32_t* dist,
                    cudaStream_t st) {
-    static unsigned long long configured = 0;
-    static int resident = 0;
+    // per-device launch state (matcher handles on distinct devices / threads are independent: orbfe_c.h)
+    static SmemOptIn optIn;
+    static std::once_flag residentOnce[64];
+    static int residentOf[64];
+    smem_opt_in(optIn, knn2_tc_kernel, (size_t)KT_SMEM);
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!((configured >> (dev & 63)) & 1ull)) {
-        cudaFuncSetAttribute(knn2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KT_SMEM);
-        configured |= 1ull << (dev & 63);
-    }
-    if (resident == 0) {
+    std::call_once(residentOnce[dev & 63], [dev] {
         int sms = 0, perSm = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, knn2_tc_kernel, KT_THREADS, KT_SMEM);
-        resident = sms * (perSm > 0 ? perSm : 1);
-    }
+        residentOf[dev & 63] = sms * (perSm > 0 ? perSm : 1);
+    });
+    const int resident = residentOf[dev & 63];
     const long long tiles = (maxNq + KT_M - 1) / KT_M;
     int nseg = 1;
     if (npairs == 1 && !nq && !nt) nseg = kt_pick_segments(tiles, ntSingle, resident);

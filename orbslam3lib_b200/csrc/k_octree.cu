@@ -543,11 +543,8 @@ size_t octree_smem_bytes(int nodeCap, int keySmem) { return octree_node_bytes(no
 
 int launch_octree(const Geom& g, int n, const ExtractBuffers& b, int nodeCap, int keySmem, cudaStream_t st) {
     const size_t smem = octree_smem_bytes(nodeCap, keySmem);
-    static size_t configured = 0;
-    if (smem > 32 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, octree_kernel, smem);
     octree_kernel<<<dim3(g.nlevels, n), OT_THREADS, smem, st>>>(g, b, nodeCap, keySmem);
     return 1;
 }

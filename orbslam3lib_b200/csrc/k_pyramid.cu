@@ -260,7 +260,7 @@ void resize_tile_dims(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int 
 int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size_t imageStride, uint8_t* pyr,
                    const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims, cudaStream_t st) {
     int launches = 0;
-    static int configured = 0;
+    static SmemOptIn optIn;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& L = g.lv[l];
         if (l == 0) {
@@ -284,10 +284,7 @@ int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size
             const LevelGeom& P = g.lv[l - 1];
             const ResizeDims& d = dims[l];
             const int smem = 2 * d.SP * d.SH;
-            if (smem > 32 * 1024 && configured < smem) {
-                cudaFuncSetAttribute(resize_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-                configured = smem;
-            }
+            smem_opt_in(optIn, resize_tile_kernel, (size_t)smem);
             const dim3 grid((kXOff + L.w + kEdge - RS_C0 + RS_TW - 1) / RS_TW, (L.h + 2 * kEdge + 4 * d.rpt - 1) / (4 * d.rpt), n);
             resize_tile_kernel<<<grid, 256, smem, st>>>(pyr + P.planeOff, P.pitch, pyr + L.planeOff, L.pitch, g.slabBytes,
                                                         L.w, L.h, xtab[l], ytab[l], d.SP, d.SH, d.rpt);

@@ -357,11 +357,8 @@ int launch_search_by_projection(const float bounds[4], const float* scale, int n
     P.cap = cap;
     P.ptsCap = ptsCap;
     const size_t smem = search_smem_bytes(cap);
-    static size_t configured = 0;
-    if (smem > 32 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(search_by_projection_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, search_by_projection_kernel, smem);
     search_by_projection_kernel<<<nframes, SR_THREADS, smem, st>>>(P, keys, desc, uRight, occupied, nFeat,
                                                                   (const TrackPoint*)pts, nPts, match, owner, nMatches);
     return 1;

@@ -436,11 +436,8 @@ int launch_search_by_projection_stereo(const float bounds[4], const float* scale
     P.cap = cap;
     P.ptsCap = ptsCap;
     const size_t smem = search_stereo_smem_bytes(cap);
-    static size_t configured = 0;
-    if (smem > 32 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(search_by_projection_stereo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, search_by_projection_stereo_kernel, smem);
     search_by_projection_stereo_kernel<<<nframes, SS_THREADS, smem, st>>>(
         P, keys, desc, occupied, nFeat, nLeft, ltr, rtl, (const TrackPointStereo*)pts, nPts, matchL, matchR, owner, nMatches);
     return 1;
@@ -725,11 +722,8 @@ int launch_search_for_initialization(const float bounds[4], int windowSize, floa
     P.cap = cap;
     P.ptsCap = cap;
     const size_t smem = search_init_smem_bytes(cap);
-    static size_t configured = 0;
-    if (smem > 32 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(search_for_initialization_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, search_for_initialization_kernel, smem);
     search_for_initialization_kernel<<<nframes, SS_THREADS, smem, st>>>(P, (float)windowSize, checkOrientation, keys1, desc1,
                                                                         n1, keys2, desc2, n2,
                                                                         reinterpret_cast<float2*>(prevMatched), match12,

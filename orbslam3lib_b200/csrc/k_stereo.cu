@@ -269,11 +269,8 @@ int launch_stereo(const Geom& g, const float* scale, const float* invScale, cons
         tb.invScale[l] = l < g.nlevels ? invScale[l] : 1.0f;
     }
     const size_t smem = stereo_smem_bytes(cap);
-    static size_t configured = 0;
-    if (smem > 32 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(stereo_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, stereo_match_kernel, smem);
     const dim3 grid((cap + ST_LEFT_PER_CTA - 1) / ST_LEFT_PER_CTA, npairs);
     stereo_match_kernel<<<grid, ST_THREADS, smem, st>>>(g, tb, pyr, kps, desc, result, cap, mb, mbf, uRight, depth, sad);
     stereo_median_kernel<<<npairs, ST_THREADS, 0, st>>>(result, cap, uRight, depth, sad);

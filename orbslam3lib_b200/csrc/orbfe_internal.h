@@ -14,6 +14,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "../../include/orbfe_c.h"
 
 namespace orbfe {
@@ -121,30 +123,42 @@ struct ExtractBuffers {
     int* errFlag;            // 1 int, device
 };
 
-// ---- kernel launchers (each returns the number of kernels it launched) ----
+// ---- kernel launchers (each returns the number of kernels it launched).  The ones whose argument lists carry
+// per-stage tables (FAST items, blur tiles, octree capacities, kNN) are declared next to their only caller in
+// orbfe_api.cu. ----
 int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size_t imageStride, uint8_t* pyr,
                    const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims, cudaStream_t st);
 void resize_tile_dims(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int dh, int rpt, int* SP, int* SH);
-int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items, int nItems, uint32_t* slots,
-                int* cellCount, cudaStream_t st);
-int launch_octree(const Geom& g, int n, const ExtractBuffers& b, cudaStream_t st);
-int launch_blur(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, cudaStream_t st);
 int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st);
 int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
                     cudaStream_t st);
-int launch_knn2(const uint8_t* q, const int* nq, int qCap, const uint8_t* t, const int* nt, int tCap, int npairs,
-                int64_t nqSingle, int64_t ntSingle, int32_t* idx, int32_t* dist, cudaStream_t st);
 
-size_t octree_smem_bytes(const Geom& g);
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of the (kernel, device) pair: one of these per kernel
+// remembers, per device, the largest dynamic shared-memory size this process has opted the kernel into.  Handles on
+// different devices (and different threads) share it, hence the lock.
+struct SmemOptIn {
+    std::mutex mu;
+    int have[64] = {0};
+};
 
 }    // namespace orbfe
 
 #ifdef __CUDACC__
 // ---- TMA bulk copies (cp.async.bulk, SASS UBLKCP) completing on a shared-memory mbarrier ---------------------------
-// The stages that tile a level plane through shared memory (k_fast.cu, k_blur.cu, k_pyramid.cu) move whole tile rows
-// with one bulk copy each instead of per-thread 16-byte loads: no registers, no issue slots, every row of the tile in
-// flight at once.  Addresses and sizes must be multiples of 16 bytes.
+// Users today: k_fast.cu (strip tiles: one tiled load each, or one bulk copy per row with ORBFE_FAST_TMAP=0).
+// Bulk-copy addresses and sizes must be multiples of 16 bytes.
 namespace orbfe {
+template <typename Kernel>
+inline void smem_opt_in(SmemOptIn& s, Kernel kernel, size_t bytes) {
+    if (bytes <= 32 * 1024) return;    // the 48 KiB default limit counts static + dynamic: opt in early
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 63;
+    std::lock_guard<std::mutex> lk(s.mu);
+    if (s.have[dev] >= (int)bytes) return;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess)
+        s.have[dev] = (int)bytes;
+}
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int arrivals) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
