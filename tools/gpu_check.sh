@@ -1,20 +1,12 @@
 #!/bin/bash
-# GPU-box check used during kernel work: parity tests, then the C2 bench without the slow legs.
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+# GPU-box check used during kernel work: parity tests, then the C2 bench without the slow legs (both FAST kernels).
+python -m pytest tests -m gpu -x -q 2>&1 | tail -15
 B="python bench.py --no-cpu-baseline --map-rows 0 --latency-iters 0 --stereo-pairs 0 --search-frames 0 --c4-frames 0"
-$B 2>&1 | python -c "
+show() { python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):
         d = json.loads(l); print(d['value'], d['e2e']['value'], {k: v['ms_per_step'] for k, v in d['stages'].items()})
-"
-for so in variants/*.so; do
-  [ -f "$so" ] || continue
-  echo "== $so"
-  ORBFE_SO=$PWD/$so $B 2>&1 | python -c "
-import sys, json
-for l in sys.stdin:
-    if l.startswith('{'):
-        d = json.loads(l); print(d['value'], d['e2e']['value'], {k: v['ms_per_step'] for k, v in d['stages'].items()})
-"
-done
+"; }
+$B 2>&1 | show
+for v in "$@"; do echo "== $v"; env $v $B 2>&1 | show; done
