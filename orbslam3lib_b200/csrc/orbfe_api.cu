@@ -645,18 +645,31 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             // 2 * kSub (large stages run the kernels more efficiently), and a short last stage (its copy-out is exposed)
             std::vector<int> sb, sm;    // first image and image count of every stage
             {
-                static const int ramp = getenv("ORBFE_PIPE_RAMP") ? atoi(getenv("ORBFE_PIPE_RAMP")) : 1;
-                int b = 0, sz = ramp ? std::max(2, (kSub / 4) & ~1) : kSub;
-                const int tail = (kSub / 2) & ~1;
+                // The copy-in (PCIe, ~6.5 us per 752x480 image) and the kernels (~7.3 us per image + ~0.2 ms per
+                // stage) run at nearly the same rate, so a stage may only be a little larger than the one before it
+                // or its input lands after the previous stage's kernels have finished: s(k+1) = 1.1 s(k) + 32
+                // (ORBFE_PIPE_SCHED="first,grow%,add,max,tail" overrides; the r1 schedule was 32,200,0,256,64).
+                static const std::vector<int> sc = [] {
+                    std::vector<int> v = {24, 110, 32, 384, 32};
+                    if (const char* e = getenv("ORBFE_PIPE_SCHED")) {
+                        int a[5];
+                        if (sscanf(e, "%d,%d,%d,%d,%d", a, a + 1, a + 2, a + 3, a + 4) == 5 && a[0] >= 2 && a[1] >= 100 && a[3] >= a[0])
+                            v.assign(a, a + 5);
+                    }
+                    return v;
+                }();
+                const int scale = std::max(1, kSub / 128);    // ORBFE_PIPE_SUB keeps scaling the whole schedule
+                int b = 0, sz = std::max(2, (sc[0] * scale) & ~1);
+                const int tail = (sc[4] * scale) & ~1;
                 while (b < m) {
                     int mk = std::min(sz, m - b);
-                    if (ramp && m - b <= sz + tail) {    // the end: [rest - tail, tail], or one stage when that is small
-                        mk = m - b > 2 * tail ? m - b - tail : m - b;
-                    }
+                    if (m - b <= sz + tail) mk = m - b > 2 * tail ? m - b - tail : m - b;    // the end: [rest - tail, tail]
+                    mk = std::max(2, mk & ~1);
+                    mk = std::min(mk, m - b);
                     sb.push_back(b);
                     sm.push_back(mk);
                     b += mk;
-                    if (ramp) sz = std::min(2 * sz, 2 * kSub);
+                    sz = std::min((int)(((long long)sz * sc[1]) / 100 + sc[2] * scale) & ~1, sc[3] * scale);
                 }
             }
             const int nsub = (int)sb.size();
