@@ -6,8 +6,9 @@ configs[1] ("c2"): EuRoC-shaped 752x480 stereo pairs, 1200 features per image, 5
 1024 images (pyramid, per-cell FAST, quadtree, orientation, blur, rBRIEF) + left->right brute-force Hamming kNN (k=2).
 `value` is measured with the inputs resident in HBM; `e2e` goes through the same C-ABI calls with pinned HOST buffers
 (host->device and device->host copies inside the timed region).  `--impl reference` times the CPU oracle
-(oracle/cpp, the restatement of the reference's ORBextractor_old.cc + OpenCV primitives; the reference itself cannot
-be compiled here, DESIGN.md "Oracle") on the host cores on a bounded sample of the same workload.
+(oracle/cpp, the restatement of the reference's ORBextractor_old.cc + OpenCV primitives, pinned bit for bit against the
+reference's own compiled extractor oracle/_ref/libext_old.so) on the host cores on a bounded sample of the
+same workload; the reference build itself is timed beside it single-threaded (`cpu_baseline.c1_single_frame_1thread`).
 """
 import argparse
 import json
@@ -50,6 +51,7 @@ def peaks():
 # twice the operations per instruction at the same instruction rate); fallback 2 x 2250 nominal.  The legacy mma.sync
 # IMMA issue peak measured with tools/ubench/mma_probe.cu (1133 Tops/s) is the ceiling of the ORBFE_KNN_TC=0 kernel.
 IMMA_SYNC_PEAK_TOPS = 1133.0
+MAP_1GPU_MS = 179.8    # 1M x 1M kNN on one B200 (SCALE_r01.json, N=1): the denominator of knn_map_summary.speedup
 
 
 def int8_peak():
@@ -131,6 +133,95 @@ def cpu_sample(npairs_sample, threads, budget_s=12.0):
             break
     dt = time.perf_counter() - t0
     return frames / dt, pairs / dt * 1e-9, "%d stereo pairs 752x480 nf=1200 x %d repetitions (%.1f s)" % (npairs_sample, reps, dt)
+
+
+def cpu_extra(cores):
+    """The CPU legs BASELINE.md §2 / north_star name beside the multi-threaded C2 number (bounded: ~15 s in total):
+    C1 single frame on one thread with the per-stage split (the log points of ORBextractor_old.cc:1107,1113,1149,1156,
+    1187 = the oracle's stage timers) and the same frame through the reference's own compiled extractor (oracle/_ref)
+    when that library travelled with the snapshot; C3 stereo pair on 2 threads, p50 / p99; the matcher on 1 thread and on
+    all cores at the C2 shape and on a 4096-query sample of the C5 shape; a cv2.BFMatcher cross-check where cv2 imports."""
+    import oracle_lib
+    from orbslam3lib_b200 import scenes
+    out = {}
+    # C1: 640x480, nf=1000, 8 levels, one thread
+    img = scenes.make("texture", 640, 480, 1000)
+    ex = oracle_lib.OracleExtractor(1000, 1.2, 8, 20, 7)
+    ex(img)
+    s0 = ex.stage_seconds()
+    t0 = time.perf_counter()
+    reps = 10
+    for _ in range(reps):
+        _, k1, d1 = ex(img)
+    dt = (time.perf_counter() - t0) / reps
+    s1 = ex.stage_seconds()
+    out["c1_single_frame_1thread"] = {
+        "workload": "c1: 640x480, nf=1000, 8 levels, ORBextractor::operator() on one thread (CPU oracle)",
+        "ms_per_frame": dt * 1e3, "keypoints": int(len(k1)),
+        "stage_ms": {k: (s1[k] - s0[k]) / reps * 1e3 for k in s1}}
+    try:
+        import ref_ext_lib
+        if ref_ext_lib.available():
+            rex = ref_ext_lib.RefExtractor(1000, 1.2, 8, 20, 7)
+            rex(img)
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                _, rk, rd = rex(img)
+            out["c1_single_frame_1thread"]["reference_build_ms_per_frame"] = (time.perf_counter() - t0) / reps * 1e3
+            out["c1_single_frame_1thread"]["reference_build"] = ("oracle/_ref/libext_old.so = the reference's own "
+                                                                 "ORBextractor_old.cc (g++ -O2) over the oracle's primitives")
+            out["c1_single_frame_1thread"]["reference_build_equals_oracle"] = bool(
+                np.array_equal(rk, k1) and np.array_equal(rd, d1))
+    except Exception as e:    # the reference build is optional on the GPU box
+        out["c1_single_frame_1thread"]["reference_build"] = "unavailable: %s" % e
+    # matcher against the previous frame (configs[0]): k=2 on one thread
+    _, k0, d0 = ex(scenes.previous_frame(img, 1000))
+    t0 = time.perf_counter()
+    for _ in range(20):
+        oracle_lib.knn2_hamming(d1, d0, threads=1)
+    out["c1_single_frame_1thread"]["knn_prev_frame_ms"] = (time.perf_counter() - t0) / 20 * 1e3
+    # C3: 640x480 stereo pair, nf=500, two threads (one per eye, as Frame.cc:142-145 does)
+    left = scenes.make("texture", 640, 480, 3000)
+    pair = np.stack([left, scenes.stereo_right(left, 3000)])
+    ts = []
+    for it in range(40):
+        t0 = time.perf_counter()
+        counts, _, _, desc = oracle_lib.extract_batch(pair, 500, 1.2, 8, 20, 7, threads=2)
+        oracle_lib.knn2_hamming(desc[0, :counts[0]], desc[1, :counts[1]], threads=1)
+        if it >= 5:
+            ts.append((time.perf_counter() - t0) * 1e3)
+    ts.sort()
+    out["c3_stereo_pair_2threads"] = {"workload": "c3: 640x480 stereo pair, nf=500, extraction on 2 threads + L->R kNN",
+                                      "p50_ms": ts[len(ts) // 2], "p99_ms": ts[-1], "iters": len(ts)}
+    # matcher: C2 shape (1200 x 1200) on one thread and on all cores; C5 shape on a 4096-query sample
+    q, t = scenes.map_descriptors(1200, 1200, 9100)
+    knn = {}
+    for name, th in (("1thread", 1), ("%dthreads" % cores, cores)):
+        t0 = time.perf_counter()
+        reps = 20 if th == 1 else 100
+        for _ in range(reps):
+            oracle_lib.knn2_hamming(q, t, threads=th)
+        knn["c2_shape_gpairs_per_s_" + name] = 1200 * 1200 * reps / (time.perf_counter() - t0) * 1e-9
+    q5, t5 = scenes.map_descriptors(4096, 1000000, 9000)
+    t0 = time.perf_counter()
+    i5, d5 = oracle_lib.knn2_hamming(q5, t5, threads=cores)
+    dt5 = time.perf_counter() - t0
+    knn["c5_sample"] = {"workload": "4096 query rows x 1M train rows (a sample of configs[4]), %d threads" % cores,
+                        "seconds": dt5, "gpairs_per_s": 4096 * 1e6 / dt5 * 1e-9}
+    try:
+        import cv2
+        # cv2.BFMatcher refuses train sets of 2^18 rows or more (IMGIDX_ONE): cross-check on the first 262143 rows
+        nt = 262143
+        m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q5[:64], t5[:nt], k=2)
+        ci = np.array([[d.trainIdx for d in row] for row in m], np.int32)
+        cd = np.array([[int(d.distance) for d in row] for row in m], np.int32)
+        oi, od = oracle_lib.knn2_hamming(q5[:64], t5[:nt], threads=cores)
+        knn["cv2_bfmatcher_crosscheck"] = {"rows": 64, "train_rows": nt, "cv2": cv2.__version__,
+                                           "equal": bool(np.array_equal(ci, oi) and np.array_equal(cd, od))}
+    except ImportError:
+        knn["cv2_bfmatcher_crosscheck"] = "cv2 not importable on this box (checked in the build container: tests/test_oracle_vs_cv2.py)"
+    out["knn"] = knn
+    return out
 
 
 def map_knn_leg(args, rank, world, local, dev, dist, matcher):
@@ -472,9 +563,11 @@ def run_reference(args):
                        "sample_pairs_per_step": sample},
             "knn_gpairs_per_s": pairs / dt * 1e-9,
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                             "sample": "%d stereo pairs per step, all host threads (CPU oracle oracle/cpp; the reference's "
-                                       "own CPU extractor does not compile here)" % sample},
+                             "sample": "%d stereo pairs per step, all host threads (CPU oracle oracle/cpp = the reference's "
+                                       "ORBextractor_old.cc restated with a multi-threaded batch entry; bit-identical to the "
+                                       "reference's own build oracle/_ref, which has no batch entry)" % sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    line["cpu_baseline"].update(cpu_extra(cores))    # single-frame / 2-thread / matcher legs + the reference's own build
     print(json.dumps(line))
 
 
@@ -487,7 +580,8 @@ def main():
     ap.add_argument("--pairs", type=int, default=512, help="stereo pairs per GPU per step (512 = BASELINE configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--map-rows", type=int, default=1000000, help="rows of the map-scale kNN leg (configs[4]); 0 = skip")
-    ap.add_argument("--map-steps", type=int, default=2)
+    ap.add_argument("--map-steps", type=int, default=10)
+    ap.add_argument("--no-nf1000", dest="nf1000", action="store_false", help="skip the 1000-feature leg")
     ap.add_argument("--latency-iters", type=int, default=300, help="stereo pairs of the per-frame latency leg (configs[2]); 0 = skip")
     ap.add_argument("--c4-frames", type=int, default=32, help="4K frames per GPU per step of the configs[3] leg; 0 = skip")
     ap.add_argument("--search-frames", type=int, default=512, help="frames per step of the SearchByProjection leg; 0 = skip")
@@ -587,6 +681,24 @@ def main():
     ms_e2e, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop()
 
+    # the configuration the metric string names (1000 features) beside c2 (1200): same images, device-resident
+    nf1000 = None
+    if args.nf1000:
+        ex2 = ORBextractor(1000, 1.2, NLEVELS, 20, 7, device=local)
+        ex2.set_stream(stream)
+        cap2 = ex2.max_keypoints
+
+        def step_1000():
+            ex2.extract_batch_raw(d_imgs, n, W, H, d_kps, d_desc, cap2, d_counts, d_monos, flags=FL)
+            dd = d_desc.view(-1)    # rows are cap2 apart in this leg
+            mt.knn2_batch_raw(dd, d_counts, cap2, dd[P * cap2 * 32:], d_counts[P:], cap2, P, d_idx, d_dist, flags=FL)
+        for _ in range(2):
+            step_1000()
+        ms_1000, _ = timed(step_1000, args.steps)
+        nf1000 = {"workload": "752x480, 1000 features/image, 8 levels: extraction + L->R kNN, %d pairs per GPU per step" % P,
+                  "ms_per_step": ms_1000 / args.steps, "frames_per_s": n * world * args.steps / (ms_1000 * 1e-3),
+                  "keypoints_per_image": float(d_counts.float().mean().item())}
+        del ex2
     knn_map = map_knn_leg(args, rank, world, local, dev, dist, mt) if args.map_rows > 0 else None
     c4 = None
     if args.c4_frames > 0:
@@ -621,6 +733,38 @@ def main():
             e["gpairs_per_s"] = round(gp, 2)
             e["roofline"] = knn_roofline(gp, 1)
         stage_report[k] = e
+    # pipe roofline: warp instructions per image and pipe from the committed ncu capture (profiles/kernel_traffic.json,
+    # a property of kernel + input) x images / the CUDA-event time of THIS run, against the pipe's issue rate measured
+    # in this process (orbfe_ubench_pipe)
+    tp0 = os.path.join(ROOT, "profiles", "kernel_traffic.json")
+    wi = json.load(open(tp0)).get("warp_inst_per_image", {}) if os.path.exists(tp0) else {}
+    pipe_peak = {}
+    for name, code in (("alu", 0), ("fmaheavy", 1)):
+        import ctypes
+        v = ctypes.c_double(0)
+        if _lib.lib().orbfe_ubench_pipe(local, code, ctypes.byref(v)) == 0:
+            pipe_peak[name] = v.value
+    stage_kernels = {"pyramid": ["pad_interior_kernel", "pad_frame_kernel", "pad_level0_kernel", "resize_tile_kernel"],
+                     "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"], "octree": ["octree_kernel"],
+                     "describe": ["pack_kernel", "describe_kernel"]}
+    for k, ks in stage_kernels.items():
+        if k not in stage_report or per.get(k, 0) <= 0:
+            continue
+        best = None
+        for pipe, peak in pipe_peak.items():
+            cnt = sum(wi.get(kn, {}).get(pipe, 0.0) for kn in ks)
+            if cnt <= 0:
+                continue
+            ach = cnt * n / (per[k] * 1e-3)
+            e = {"pipe": pipe, "peak": peak, "achieved": ach, "frac": round(ach / peak, 4), "unit": "warp instructions/s",
+                 "peak_source": "orbfe_ubench_pipe in this process", "count_source": "profiles/kernel_traffic.json warp_inst_per_image"}
+            if best is None or e["frac"] > best["frac"]:
+                best = e
+        if best:
+            tot = sum(wi.get(kn, {}).get("all", 0.0) for kn in ks)
+            if tot > 0:
+                best["issue_frac"] = round(tot * n / (per[k] * 1e-3) / (4 * 148 * sm_mhz * 1e6), 4)    # 4 schedulers x 148 SMs
+            stage_report[k]["pipe_roofline"] = best
     hbm_stages = [k for k in ("pyramid", "fast", "blur") if per.get(k, 0) > 0]
     dom = max(hbm_stages, key=lambda k: per[k])
     launches_dom = NLEVELS if dom == "pyramid" else 1
@@ -664,6 +808,8 @@ def main():
                      "note": "algorithmic bytes per image x images per step / CUDA-event time of the stage"},
         "stages": stage_report,
     }
+    if nf1000:
+        line["c2_nf1000"] = nf1000
     if knn_map:
         line["knn_map"] = knn_map
     if c4:
@@ -684,6 +830,13 @@ def main():
         v, gp, sample = cpu_sample(max(4, min(32, cores // 2)), cores)
         line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample,
                                 "knn_gpairs_per_s": gp}
+        line["cpu_baseline"].update(cpu_extra(cores))
+    if knn_map:    # last key: survives a tail of the line
+        line["knn_map_summary"] = {"n_gpus": world, "ms": round(knn_map["ms_per_step"], 3),
+                                   "gpairs": round(knn_map["gpairs_per_s"], 1), "steps": knn_map["steps"],
+                                   "speedup_vs_1gpu_ms": round(MAP_1GPU_MS / knn_map["ms_per_step"], 3),
+                                   "ref_1gpu_ms": MAP_1GPU_MS, "comm_ms": knn_map.get("comm_ms"),
+                                   "kernel_ms": knn_map.get("kernel_ms"), "checksum": knn_map["checksum"]}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -271,6 +271,14 @@ int orbfe_knn2_sharded(orbfe_matcher* m, void* nccl_comm, int rank, int world, c
                        int64_t nq_total, uint8_t* t, int64_t nt, int root, int32_t* idx_all, int32_t* dist_all,
                        float* ms_out);
 
+/* ---- measurement aid (bench.py "pipe_roofline") --------------------------------------------------------------
+ * Measured issue rate, in warp instructions per second over the whole GPU, of one integer pipe of `device`:
+ * ORBFE_PIPE_ALU (VABSDIFF4 chains; LOP3 / IADD3 / SHF / PRMT / VIMNMX issue on the same pipe) or ORBFE_PIPE_FMAHEAVY
+ * (IDP.2A chains; IMAD / IDP.4A issue on the same pipe).  Replaces nothing in the reference. */
+#define ORBFE_PIPE_ALU 0
+#define ORBFE_PIPE_FMAHEAVY 1
+int orbfe_ubench_pipe(int device, int pipe, double* warp_inst_per_s);
+
 /* ---- wire-compatible entry points: the four skel functions of the FastRPC interface ----------------------
  * Same names, argument order and meaning as dsp/src/orbslam_dsp.cpp:866 (open), :931 (close), :1017-1021
  * (extractFeatures) and :567 (bfMatchStereo), so LynxHardwareAccelerator.cpp:62,116,146-150 links against

@@ -192,3 +192,31 @@ def test_tensor_core_path_train_segments(oracle):
     ri, rd = oracle.knn2_hamming(q[sel], t, threads=8)
     np.testing.assert_array_equal(base_i[sel], ri)
     np.testing.assert_array_equal(base_d[sel], rd)
+
+
+def test_knn2_c5_shape_sample(oracle):
+    """BASELINE configs[4] / SURVEY §8(d): the map-scale problem at its full size, 1M query x 1M train 256-bit
+    descriptors, k = 2.  All 1M result rows come from the tcgen05 kernel; a 4096-row sample (every 244th row, plus the
+    first and last 128 so that both ends of the shard are covered) is compared with the CPU oracle bit for bit, and a
+    64-row subsample with cv2.BFMatcher where cv2 imports (it refuses 2^18 or more train rows, so on a 262143-row train
+    prefix).  Size-independent properties on ALL rows: best <= second, indices in range and distinct, distances <= 256."""
+    nq = nt = 1000000
+    q, t = scenes.map_descriptors(nq, nt, 9000)
+    idx, dist = BFMatcher().knnMatch(q, t)
+    assert idx.shape == (nq, 2)
+    assert (dist[:, 0] <= dist[:, 1]).all() and (dist >= 0).all() and (dist <= 256).all()
+    assert (idx >= 0).all() and (idx < nt).all() and (idx[:, 0] != idx[:, 1]).all()
+    sel = np.unique(np.concatenate([np.arange(130, nq, 260)[:3840], np.arange(128), np.arange(nq - 128, nq)]))
+    assert len(sel) == 4096
+    ri, rd = oracle.knn2_hamming(q[sel], t, threads=oracle.hardware_threads())
+    np.testing.assert_array_equal(idx[sel], ri)
+    np.testing.assert_array_equal(dist[sel], rd)
+    try:
+        import cv2
+    except ImportError:
+        return
+    ntc = 262143
+    gi, gd = BFMatcher().knnMatch(q[sel[:64]], t[:ntc])
+    m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q[sel[:64]], t[:ntc], k=2)
+    np.testing.assert_array_equal(gi, np.array([[d.trainIdx for d in row] for row in m], np.int32))
+    np.testing.assert_array_equal(gd, np.array([[int(d.distance) for d in row] for row in m], np.int32))

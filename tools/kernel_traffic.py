@@ -1,9 +1,11 @@
 #!/usr/bin/env python
 """Rebuild profiles/kernel_traffic.json from `ncu -i X.ncu-rep --page raw --csv` output.
 
-usage: python tools/kernel_traffic.py raw.csv images_per_launch TAG > profiles/kernel_traffic.json
+usage: python tools/kernel_traffic.py raw.csv images_per_launch TAG [pipes.csv] > profiles/kernel_traffic.json
 Per kernel name: DRAM bytes (read + write) summed over its launches / images, and the time-weighted issue-active
 percentage; bench.py reads the first for `roofline.traffic` and the second for `roofline.issue_active_pct_ncu`.
+pipes.csv (optional) = the `ncu --metrics sm__inst_executed_pipe_*.sum,smsp__inst_executed.sum --csv` launch list of
+the same command: warp instructions per image and per pipe, the numerators of bench.py's `pipe_roofline`.
 """
 import csv
 import json
@@ -44,6 +46,21 @@ def main():
         "issue_note": "smsp__issue_active.avg.pct_of_peak_sustained_active of the same capture (time-weighted over the "
                       "launches of a stage): the extraction kernels are bound by integer pipes / phase structure, not DRAM",
     }
+    if len(sys.argv) > 4:
+        pipes = {}
+        for r in csv.reader(open(sys.argv[4])):
+            if len(r) < 15 or r[0] == "ID":
+                continue
+            name = re.sub(r"\(.*", "", r[4]).split("::")[-1].strip()
+            m = r[12].replace("sm__inst_executed_pipe_", "").replace("smsp__inst_executed", "all").replace(".sum", "")
+            if m.startswith("gpu__"):
+                continue
+            pipes.setdefault(name, {})
+            pipes[name][m] = pipes[name].get(m, 0.0) + num(r[14])
+        out["warp_inst_per_image"] = {k: {m: round(v / images, 1) for m, v in d.items()} for k, d in pipes.items()
+                                      if k in traffic}
+        out["warp_inst_note"] = ("sm__inst_executed_pipe_{alu,fma,fmaheavy,lsu,xu}.sum and smsp__inst_executed.sum of the "
+                                 "same command, summed over the launches of a kernel / images")
     json.dump(out, sys.stdout, indent=1)
     sys.stdout.write("\n")
 
