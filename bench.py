@@ -238,7 +238,7 @@ def map_knn_leg(args, rank, world, local, dev, dist, matcher):
     d_idx = torch.full((nq, 2), -9, dtype=torch.int32, device=dev)
     d_dist = torch.full((nq, 2), -9, dtype=torch.int32, device=dev)
     sm = ShardedMatcher(matcher, rank, world, local, dist)
-    times = []
+    times, parts = [], {"kernel_ms": 0.0, "bcast_ms": 0.0, "gather_ms": 0.0}
     for it in range(1 + args.map_steps):
         if world > 1:
             if rank != 0:
@@ -252,6 +252,9 @@ def map_knn_leg(args, rank, world, local, dev, dist, matcher):
             ms = float(tt.item())
         if it > 0:
             times.append(ms)
+            for k, v in sm.last_times().items():
+                if k in parts:
+                    parts[k] += v / args.map_steps    # this rank's split of the step
     idx = d_idx.cpu().numpy()
     dd = d_dist.cpu().numpy()
     out = None
@@ -267,6 +270,11 @@ def map_knn_leg(args, rank, world, local, dev, dist, matcher):
         out = {"workload": "c5: %d x %d 256-bit descriptors, k=2, query rows sharded over %d GPU(s), NCCL train "
                            "broadcast + result exchange" % (nq, nt, world),
                "ms_per_step": ms, "gpairs_per_s": gp, "scaling": "strong", "steps": args.map_steps,
+               "kernel_ms": round(parts["kernel_ms"], 3), "comm_ms": round(ms - parts["kernel_ms"], 3),
+               "bcast_ms_own_stream": round(parts["bcast_ms"], 3), "gather_ms": round(parts["gather_ms"], 3),
+               "split_note": "rank 0: kernel_ms = the kNN launches, comm_ms = max-over-ranks step - kernel_ms (exposed "
+                             "communication + waiting for the slowest rank); the train broadcast runs on its own stream "
+                             "under the kernels",
                "roofline": knn_roofline(gp, world),
                "checksum": int((idx.astype(np.int64) * 31 + dd).sum() & 0xFFFFFFFFFFFF),
                "parity_sample": {"rows": int(len(sel)), "vs": "CPU oracle", "ok": ok}}

@@ -270,6 +270,10 @@ const char* orbfe_nccl_last_error(void);
 int orbfe_knn2_sharded(orbfe_matcher* m, void* nccl_comm, int rank, int world, const uint8_t* q_shard,
                        int64_t nq_total, uint8_t* t, int64_t nt, int root, int32_t* idx_all, int32_t* dist_all,
                        float* ms_out);
+/* device times (ms) of the last orbfe_knn2_sharded on this matcher: [0] whole call, [1] the kNN launches, [2] the train
+ * broadcast as seen on its own stream (it overlaps the launches: pieces of the train set are matched as they land),
+ * [3] the result exchange (pack + ncclAllGather + unpack).  [0] - [1] is the exposed communication. */
+int orbfe_knn2_sharded_times(orbfe_matcher* m, float out[4]);
 
 /* ---- measurement aid (bench.py "pipe_roofline") --------------------------------------------------------------
  * Measured issue rate, in warp instructions per second over the whole GPU, of one integer pipe of `device`:

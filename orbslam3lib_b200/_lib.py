@@ -93,6 +93,7 @@ SYMBOLS = {
     "orbfe_nccl_comm_destroy": (_i, [_vp]),
     "orbfe_nccl_last_error": (C.c_char_p, []),
     "orbfe_knn2_sharded": (_i, [_vp, _vp, _i, _i, _vp, _i64, _vp, _i64, _i, _vp, _vp, _vp]),
+    "orbfe_knn2_sharded_times": (_i, [_vp, _vp]),
     "orbfe_ubench_pipe": (_i, [_i, _i, C.POINTER(C.c_double)]),
     "orbslam3_open": (_i, [C.c_char_p, C.POINTER(C.c_uint64)]),
     "orbslam3_close": (_i, [C.c_uint64]),

@@ -361,6 +361,8 @@ static bool knn_use_tc() {
     return v != 0;
 }
 
+bool knn_tc_enabled() { return knn_use_tc(); }
+
 // ORBFE_KNN_MMA=0 selects the POPC kernel (A/B measurements); default: tensor cores
 static bool knn_use_mma() {
     static const int v = [] {

@@ -22,7 +22,9 @@
 //     cut the TRAIN set into `nseg` segments (grid.z): CTA (tile, z) keeps the top 2 of its segment, writes them to a
 //     scratch array, and the last CTA of a tile to finish (atomic ticket) merges the nseg partial results in segment
 //     order -- strict "<" keeps the lowest train index on ties, as OpenCV does.
+#include <algorithm>
 #include <cstdlib>
+#include <mutex>
 
 #include "orbfe_internal.h"
 
@@ -100,7 +102,7 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
                                                             long long nqSingle, long long ntSingle,
                                                             int32_t* __restrict__ idx, int32_t* __restrict__ dist,
                                                             long long segLen, int4* __restrict__ partial,
-                                                            unsigned* __restrict__ ticket) {
+                                                            unsigned* __restrict__ ticket, int zBase, int zTotal) {
     extern __shared__ __align__(128) uint8_t ktSmem[];
     uint8_t* sA = ktSmem;
     uint8_t* sB = ktSmem + KT_M * 256;
@@ -142,9 +144,12 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
 
     int d1 = -1, i1 = -1, d2 = -1, i2 = -1;
     uint32_t phase = 0;
-    // train rows of this CTA: everything, or segment blockIdx.z of gridDim.z (segLen is a multiple of KT_N)
-    const long long tBeg = gridDim.z > 1 ? min(nt, (long long)blockIdx.z * segLen) : 0;
-    const long long tEnd = gridDim.z > 1 ? min(nt, tBeg + segLen) : nt;
+    // train rows of this CTA: everything, or segment zg of zTotal (segLen is a multiple of KT_N).  The segments of one
+    // problem may be spread over several launches (zBase = first segment of this launch): the sharded matcher starts
+    // the segments of a train chunk as soon as that chunk has arrived (orbfe_sharded.cu)
+    const int zg = zBase + (int)blockIdx.z;
+    const long long tBeg = zTotal > 1 ? min(nt, (long long)zg * segLen) : 0;
+    const long long tEnd = zTotal > 1 ? min(nt, tBeg + segLen) : nt;
     for (long long sb = tBeg; sb < tEnd; sb += (1ll << (KT_S - 1))) {
         const int ns = (int)min(tEnd - sb, 1ll << (KT_S - 1));
         int b1 = KT_EMPTY, b2 = KT_EMPTY;    // keys relative to the current chunk: (acc << S) + (column - chunk base)
@@ -233,19 +238,20 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
         merge(b1);
         merge(b2);
     }
-    if (gridDim.z > 1) {
-        // partial top 2 of this segment -> scratch; the last CTA of the tile merges all segments in train order
+    if (zTotal > 1) {
+        // partial top 2 of this segment -> scratch; the last CTA of the tile (over all launches) merges all segments in
+        // train order
         const long long rowsPad = (long long)gridDim.x * KT_M;
-        partial[(long long)blockIdx.z * rowsPad + row] = make_int4(i1, i2, d1, d2);
+        partial[(long long)zg * rowsPad + row] = make_int4(i1, i2, d1, d2);
         __threadfence();
         __syncthreads();
         if (tid == 0) *tmemSlot = atomicAdd(&ticket[blockIdx.x], 1u);    // tmemSlot is free: `tmem` holds the address
         __syncthreads();
-        const bool last = *tmemSlot == gridDim.z - 1;
+        const bool last = *tmemSlot == (unsigned)(zTotal - 1);
         if (last) {
             __threadfence();
             i1 = i2 = d1 = d2 = -1;
-            for (int z = 0; z < (int)gridDim.z; z++) {
+            for (int z = 0; z < zTotal; z++) {
                 const int4 pz = __ldcg(&partial[(long long)z * rowsPad + row]);
                 if (pz.x >= 0 && (i1 < 0 || pz.z < d1)) { d2 = d1; i2 = i1; d1 = pz.z; i1 = pz.x; }
                 else if (pz.x >= 0 && (i2 < 0 || pz.z < d2)) { d2 = pz.z; i2 = pz.x; }
@@ -320,15 +326,76 @@ int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_
     if (nseg <= 1) {
         const dim3 grid((unsigned)tiles, npairs);
         knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist, 0, nullptr,
-                                                          nullptr);
+                                                          nullptr, 0, 1);
         return 1;
     }
     cudaMemsetAsync(scratch + partialBytes, 0, ticketBytes, st);
     const dim3 grid((unsigned)tiles, 1, nseg);
     knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx, dist, segLen,
                                                       reinterpret_cast<int4*>(scratch),
-                                                      reinterpret_cast<unsigned*>(scratch + partialBytes));
+                                                      reinterpret_cast<unsigned*>(scratch + partialBytes), 0, nseg);
     cudaFreeAsync(scratch, st);
+    return 1;
+}
+
+// ---- multi-launch form (orbfe_sharded.cu) -----------------------------------------------------------------------------
+// One nq x nt problem whose train set arrives in `chunks` pieces.  plan: segments per chunk (the smallest count <= 8
+// whose CTA total fills the resident-CTA waves of ONE launch to >= 95 %, else the best), the segment length (a multiple
+// of KT_N) and the scratch bytes (partial results of every segment + one ticket per query tile; tickets must be zero
+// before the first launch and are zero again after the last).  Chunk c = segments [c spc, (c + 1) spc) = train rows
+// [c spc segLen, (c + 1) spc segLen).
+static int kt_resident_ctas() {
+    static std::once_flag once[64];
+    static int resident[64];
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, knn2_tc_kernel, (size_t)KT_SMEM);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::call_once(once[dev & 63], [dev] {
+        int sms = 0, perSm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, knn2_tc_kernel, KT_THREADS, KT_SMEM);
+        resident[dev & 63] = sms * (perSm > 0 ? perSm : 1);
+    });
+    return resident[dev & 63];
+}
+
+void knn2_tc_plan(long long nq, long long nt, int chunks, int* segsPerChunk, long long* segLen, int* zTotal,
+                  size_t* scratchBytes) {
+    const long long tiles = (nq + KT_M - 1) / KT_M;
+    const int resident = kt_resident_ctas();
+    int best = 1;
+    double bestEff = 0;
+    for (int sgs = 1; sgs <= 8; sgs++) {
+        if (sgs > 1 && nt / ((long long)chunks * sgs) < 4096) break;
+        const long long ctas = tiles * sgs, waves = (ctas + resident - 1) / resident;
+        const double eff = (double)ctas / (double)(waves * resident);
+        if (eff > bestEff + 1e-9) { bestEff = eff; best = sgs; }
+        if (eff >= 0.95) break;
+    }
+    const long long want = (long long)chunks * best;
+    long long sl = ((nt + want - 1) / want + KT_N - 1) / KT_N * KT_N;
+    if (sl < KT_N) sl = KT_N;
+    *segsPerChunk = best;
+    *segLen = sl;
+    *zTotal = (int)std::max<long long>(1, (nt + sl - 1) / sl);
+    *scratchBytes = (size_t)(*zTotal) * tiles * KT_M * sizeof(int4) + (size_t)tiles * sizeof(unsigned);
+}
+
+// launches the segments [zBase, zBase + zCount) of the plan; scratch = [zTotal x planRows/128 x 128 int4][tickets], laid
+// out for the planRows the plan was made with (nq <= planRows: a rank may own fewer rows than the largest shard)
+int launch_knn2_tc_segments(const uint8_t* q, long long nq, long long planRows, const uint8_t* t, long long nt, int32_t* idx,
+                            int32_t* dist, long long segLen, int zBase, int zCount, int zTotal, uint8_t* scratch,
+                            cudaStream_t st) {
+    if (nq <= 0 || zCount <= 0) return 0;
+    kt_resident_ctas();    // shared-memory opt-in of this device
+    const long long tiles = (nq + KT_M - 1) / KT_M;
+    const size_t partialBytes = (size_t)zTotal * ((planRows + KT_M - 1) / KT_M) * KT_M * sizeof(int4);
+    const dim3 grid((unsigned)tiles, 1, (unsigned)zCount);
+    // zTotal == 1 would take the kernel's direct-store path, which needs no scratch
+    knn2_tc_kernel<<<grid, KT_THREADS, KT_SMEM, st>>>(q, nullptr, nq, t, nullptr, nt, nq, nt, idx, dist, segLen,
+                                                      reinterpret_cast<int4*>(scratch),
+                                                      reinterpret_cast<unsigned*>(scratch + partialBytes), zBase, zTotal);
     return 1;
 }
 

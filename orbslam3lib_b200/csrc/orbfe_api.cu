@@ -980,6 +980,8 @@ struct orbfe_matcher {
     DevBuf dS[14];    // staging of the orbfe_search_by_projection* calls
     float lastMs = 0;
     int lastLaunches = 0;
+    void* aux = nullptr;               // state of the sharded matcher (orbfe_sharded.cu), freed by auxFree at destroy
+    void (*auxFree)(void*) = nullptr;
 };
 
 static int set_merr(orbfe_matcher* m, int code, const char* fmt, ...) {
@@ -1077,6 +1079,15 @@ int matcher_knn_device(orbfe_matcher* m, const uint8_t* q, long long nq, const u
     return ORBFE_OK;
 }
 int matcher_fail(orbfe_matcher* m, int code, const char* msg) { return set_merr(m, code, "%s", msg); }
+void** matcher_aux(orbfe_matcher* m, void (***freeFn)(void*)) {
+    *freeFn = &m->auxFree;
+    return &m->aux;
+}
+int matcher_device(const orbfe_matcher* m) { return m->device; }
+void matcher_count_launches(orbfe_matcher* m, int launches) {
+    g_launches += launches;
+    m->lastLaunches = launches;
+}
 }    // namespace orbfe
 
 extern "C" {
@@ -1105,6 +1116,7 @@ int orbfe_matcher_destroy(orbfe_matcher* m) {
     DevBuf* bufs[] = {&m->dQ, &m->dT, &m->dIdx, &m->dDist, &m->dNq, &m->dNt};
     for (DevBuf* b : bufs) b->release();
     for (DevBuf& b : m->dS) b.release();
+    if (m->aux && m->auxFree) m->auxFree(m->aux);
     cudaEventDestroy(m->ev[0]);
     cudaEventDestroy(m->ev[1]);
     if (m->ownStream) cudaStreamDestroy(m->ownStream);

@@ -61,3 +61,9 @@ class ShardedMatcher:
         if rc != _lib.OK:
             raise OrbfeError(rc, _lib.lib().orbfe_matcher_last_error(self.m._h).decode())
         return ms.value
+
+    def last_times(self):
+        """device ms of the last knn2: whole call, kNN launches, train broadcast (own stream), result exchange."""
+        out = (C.c_float * 4)()
+        _lib.lib().orbfe_knn2_sharded_times(self.m._h, out)
+        return {"total_ms": out[0], "kernel_ms": out[1], "bcast_ms": out[2], "gather_ms": out[3]}
