@@ -529,12 +529,46 @@ def search_leg(args, local, dev):
             "kernel_ms_per_step": ms_i / steps, "pairs_per_s": nfr / (ms_i / steps * 1e-3),
             "matches_per_pair": float(d_cnt.float().mean().item()), "cpu_oracle_pairs_per_s_1thread": nsc / t_cpu_i,
             "parity_sample": {"pairs": nsc, "vs": "CPU oracle (vnMatches12)", "ok": ok_i}}
+    # ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1683-1921): the per-frame tracking
+    # call, 1200 last-frame points per frame, th = 7 (Tracking::TrackWithMotionModel, stereo), rotation histogram on
+    nfp = 1200
+    FP = np.zeros((nfr, nfp), scenes.FRAME_POINT_DTYPE)
+    for f in range(nfr):
+        k = f % nsc
+        n = int(counts[k])
+        FP[f] = scenes.frame_points(kps[k, :n], desc[k, :n], n, None, U[f, :n], NLEVELS, nfp, 7200 + f) if f < nsc else FP[f % nsc]
+    dFP = t(FP)
+    dnfp = torch.full((nfr,), nfp, dtype=torch.int32, device=dev)
+    d_ml = torch.zeros((nfr, nfp), dtype=torch.int32, device=dev)
+    d_mr = torch.zeros((nfr, nfp), dtype=torch.int32, device=dev)
+    mf = ORBmatcher(0.9, True, device=local)
+    ms_f = 0.0
+    for it in range(steps + 2):
+        mf.search_frame_batch_raw(dK, dD, dU, None, dn, None, None, cap, bounds, scale, 47.9, dFP, dnfp, nfp, nfr, 7.0, d_ml,
+                                  d_mr, d_owner, d_cnt, flags=FL)
+        if it >= 2:
+            ms_f += mf.last_ms()[0]
+    mlf = d_ml[:nsc].cpu().numpy()
+    mpf_f = float(d_cnt.float().mean().item())
+    ok_f, t_cpu_f = True, 0.0
+    for f in range(nsc):
+        n = int(nn[f])
+        t0 = time.perf_counter()
+        rl, _, _, _ = oracle_lib.search_by_projection_frame(K[f, :n], D[f, :n], U[f, :n], None, n, bounds, scale, 47.9, FP[f],
+                                                            th=7.0)
+        t_cpu_f += time.perf_counter() - t0
+        ok_f = ok_f and bool(np.array_equal(mlf[f], rl))
+    frame = {"workload": "ORBmatcher::SearchByProjection(CurrentFrame, LastFrame), %d frames per step, %d last-frame points x "
+                         "~%d features, th = 7, rotation check" % (nfr, nfp, int(nn.mean())),
+             "kernel_ms_per_step": ms_f / steps, "frames_per_s": nfr / (ms_f / steps * 1e-3), "matches_per_frame": mpf_f,
+             "cpu_oracle_frames_per_s_1thread": nsc / t_cpu_f,
+             "parity_sample": {"frames": nsc, "vs": "CPU oracle (slot per point after the rotation check)", "ok": ok_f}}
     return {"workload": "ORBmatcher::SearchByProjection, %d frames per step, %d map points x ~%d features per frame, th = 1"
                         % (nfr, npts, int(nn.mean())), "kernel_ms_per_step": ms / steps,
             "frames_per_s": nfr / (ms / steps * 1e-3), "matches_per_frame": mpf,
             "cpu_oracle_frames_per_s_1thread": nsc / t_cpu,
             "parity_sample": {"frames": nsc, "vs": "CPU oracle (match index per map point)", "ok": ok},
-            "initialization": init}
+            "initialization": init, "frame_to_frame": frame}
 
 
 def run_reference(args):

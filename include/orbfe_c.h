@@ -202,6 +202,48 @@ int orbfe_search_by_projection_stereo_batch(orbfe_matcher* m, const orbfe_keypoi
                                             int nframes, float th, int far_points, float th_far, float nn_ratio,
                                             int32_t* match_left, int32_t* match_right, int32_t* owner, int32_t* nmatches,
                                             unsigned flags);
+/* ---- the per-frame tracking matcher: ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th,
+ * bMono) with SearchByProjectionThread and the rotation histogram (ORBmatcher.cc:1683-1921), and
+ * ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1923-2059), both with
+ * ComputeThreeMaxima (:2061-2102).  The pose algebra stays with the caller (Sophus / the camera model): a MapPoint of the
+ * last frame (of the key frame) arrives as
+ *   u, v      CurrentFrame.mpCamera->project(Tcw * x3Dw)                       (:1735, :1949)
+ *   ur, vr    mpCamera->project(GetRelativePoseTrl() * x3Dc), stereo-camera frames only (:1833-1834)
+ *   invz      1 / x3Dc(2) (:1730); the mvuRight gate uses u - mbf * invz (:1786)
+ *   angle     angle of the source keypoint: kpLF.angle (:1813-1819) / pKF->mvKeysUn[i].angle (:2011)
+ *   level     nLastOctave (:1744-1746) / nPredictedLevel = pMP->PredictScale(dist3D, &CurrentFrame) (:1972)
+ *   flags     bit 0: the point reaches the search (frame form: pMP && !mvbOutlier[i] && invzc >= 0; key-frame form: pMP &&
+ *             !isBad() && !sAlreadyFound.count(pMP) && minDistance <= dist3D <= maxDistance); bit 2: Observations() > 0
+ *   desc      pMP->GetDescriptor()
+ * The image-bounds tests (:1737-1740), the window th * mvScaleFactors[level], the level range by direction, the grid
+ * search, TH_HIGH / ORBdist, the rotation histogram and the removal of the losing bins run on the device. */
+typedef struct orbfe_frame_point {
+    float u, v, ur, vr, invz, angle;
+    int32_t level, flags;
+    uint8_t desc[32];
+} orbfe_frame_point;
+/* Frame f of the batch: n[f] slots at [f*cap ...), left features first; nleft == NULL or nleft[f] == n[f] is Nleft == -1
+ * (keys = mvKeysUn, u_right = mvuRight (nullable) gates the candidates), nleft[f] < n[f] a stereo-camera frame (keys =
+ * mvKeys then mvKeysRight; the right search runs on mGridRight).  occupied[slot] = CurrentFrame.mvpMapPoints[slot] &&
+ * ->Observations() > 0 (nullable).  dir[f] (nullable = 0): 1 = bForward, 2 = bBackward (:1698-1699, from tlc(2) and mb).
+ * match_left / match_right[f*pts_cap + i]: slot chosen for point i by the left / right search (right: relative to nleft;
+ * match_right may be NULL when nleft is) or -1, AFTER the rotation check; owner[f*cap + slot] = the point that holds
+ * CurrentFrame.mvpMapPoints[slot] at return (-1 = NULL); nmatches[f] = the return value. */
+int orbfe_search_by_projection_frame_batch(orbfe_matcher* m, const orbfe_keypoint* keys, const uint8_t* desc,
+                                           const float* u_right, const uint8_t* occupied, const int32_t* n,
+                                           const int32_t* nleft, const int32_t* dir, int cap, const float bounds[4],
+                                           const float* scale_factors, int nlevels, float mbf, const orbfe_frame_point* pts,
+                                           const int32_t* npts, int pts_cap, int nframes, float th, int check_orientation,
+                                           int32_t* match_left, int32_t* match_right, int32_t* owner, int32_t* nmatches,
+                                           unsigned flags);
+/* The key-frame form (relocalisation, Tracking.cc): Nleft == -1 frames; occupied[slot] = CurrentFrame.mvpMapPoints[slot]
+ * != NULL; every accepted match takes its slot; levels nPredictedLevel +- 1; accepted at <= orb_dist. */
+int orbfe_search_by_projection_keyframe_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc,
+                                              const uint8_t* occupied, const int32_t* n, int cap, const float bounds[4],
+                                              const float* scale_factors, int nlevels, const orbfe_frame_point* pts,
+                                              const int32_t* npts, int pts_cap, int nframes, float th, int orb_dist,
+                                              int check_orientation, int32_t* match, int32_t* owner, int32_t* nmatches,
+                                              unsigned flags);
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764, with
  * ComputeThreeMaxima :2061-2102) for monocular frames, nframes independent (F1, F2) pairs, one CTA each.  Pair f:
  * keys1 / desc1 [f*cap, f*cap + n1[f]) = F1.mvKeysUn / mDescriptors, keys2 / desc2 / n2 likewise for F2; bounds =

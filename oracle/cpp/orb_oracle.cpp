@@ -1243,6 +1243,313 @@ int orc_search_by_projection_stereo(const orc_keypoint* keys, const uint8_t* des
     return nmatches;
 }
 
+// ---- ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono) (ORBmatcher.cc:1683-1921) ----
+// and ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1923-2059), with
+// ComputeThreeMaxima (:2061-2102).  The pose algebra (Tcw * x3Dw, mpCamera->project, PredictScale, the distance gates of
+// the KeyFrame form) stays with the caller: a point arrives as its projection(s), 1 / z, level, source-keypoint angle,
+// descriptor and flags (bit 0: the point reaches the search, bit 2: pMP->Observations() > 0).
+namespace {
+struct FrameGrids {
+    std::vector<size_t> mGrid[GRID_COLS][GRID_ROWS], mGridRight[GRID_COLS][GRID_ROWS];
+};
+void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3) {    // :2061-2102
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = (int)histo[i].size();
+        if (s > max1) {
+            max3 = max2; max2 = max1; max1 = s;
+            ind3 = ind2; ind2 = ind1; ind1 = i;
+        } else if (s > max2) {
+            max3 = max2; max2 = s;
+            ind3 = ind2; ind2 = i;
+        } else if (s > max3) {
+            max3 = s;
+            ind3 = i;
+        }
+    }
+    if (max2 < 0.1f * (float)max1) {
+        ind2 = -1;
+        ind3 = -1;
+    } else if (max3 < 0.1f * (float)max1) {
+        ind3 = -1;
+    }
+}
+}    // namespace
+
+int orc_search_by_projection_frame(const orc_keypoint* keys, const uint8_t* desc, const float* uRight,
+                                   const uint8_t* occupied, int n, int nleft, float mnMinX, float mnMinY, float mnMaxX,
+                                   float mnMaxY, const float* mvScaleFactors, float mbf, const orc_frame_point* pts,
+                                   int npts, float th, int dir, int checkOrientation, int32_t* matchL, int32_t* matchR,
+                                   int32_t* owner) {
+    const int TH_HIGH = 100, HISTO_LENGTH = 30;
+    const bool stereoCam = nleft != n;    // Nleft != -1: left and right features share the slot array, left first
+    const float gwInv = static_cast<float>(GRID_COLS) / (mnMaxX - mnMinX);
+    const float ghInv = static_cast<float>(GRID_ROWS) / (mnMaxY - mnMinY);
+    static thread_local FrameGrids G;
+    for (int i = 0; i < GRID_COLS; i++)
+        for (int j = 0; j < GRID_ROWS; j++) {
+            G.mGrid[i][j].clear();
+            G.mGridRight[i][j].clear();
+        }
+    for (int i = 0; i < n; i++) {    // AssignFeaturesToGrid (Frame.cc:405-436)
+        const orc_keypoint& kp = keys[i];
+        const int posX = (int)std::round((kp.x - mnMinX) * gwInv);
+        const int posY = (int)std::round((kp.y - mnMinY) * ghInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        if (i < nleft) G.mGrid[posX][posY].push_back(i);
+        else G.mGridRight[posX][posY].push_back(i - nleft);
+    }
+    std::vector<uint8_t> blocked(n, 0);    // CurrentFrame.mvpMapPoints[i2] && ->Observations() > 0
+    for (int i = 0; i < n; i++) {
+        blocked[i] = occupied ? occupied[i] : 0;
+        owner[i] = -1;
+    }
+    auto area = [&](float x, float y, float r, int minLevel, int maxLevel, bool bRight, std::vector<size_t>& out) {
+        out.clear();    // Frame::GetFeaturesInArea (Frame.cc:672-736)
+        const float factorX = r, factorY = r;
+        const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * gwInv));
+        if (nMinCellX >= GRID_COLS) return;
+        const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * gwInv));
+        if (nMaxCellX < 0) return;
+        const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * ghInv));
+        if (nMinCellY >= GRID_ROWS) return;
+        const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * ghInv));
+        if (nMaxCellY < 0) return;
+        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+        for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+            for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                const std::vector<size_t>& vCell = (!bRight) ? G.mGrid[ix][iy] : G.mGridRight[ix][iy];
+                for (size_t j = 0; j < vCell.size(); j++) {
+                    const orc_keypoint& kpUn = (!bRight) ? keys[vCell[j]] : keys[nleft + vCell[j]];
+                    if (bCheckLevels) {
+                        if (kpUn.octave < minLevel) continue;
+                        if (maxLevel >= 0)
+                            if (kpUn.octave > maxLevel) continue;
+                    }
+                    const float distx = kpUn.x - x;
+                    const float disty = kpUn.y - y;
+                    if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) out.push_back(vCell[j]);
+                }
+            }
+    };
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    const bool bForward = dir == 1, bBackward = dir == 2;
+    int nmatches = 0;
+    std::vector<size_t> vIndices2;
+    std::vector<std::pair<int, int>> entryPoint[HISTO_LENGTH];    // (point, 0 left / 1 right) of every histogram entry
+    for (int i = 0; i < npts; i++) {
+        matchL[i] = -1;
+        matchR[i] = -1;
+        const orc_frame_point& p = pts[i];
+        if (!(p.flags & 1)) continue;    // pMP, !mvbOutlier[i], invzc >= 0
+        const float invzc = p.invz;
+        const float u = p.u, v = p.v;
+        if (u < mnMinX || u > mnMaxX) continue;
+        if (v < mnMinY || v > mnMaxY) continue;
+        const int nLastOctave = p.level;
+        float radius = th * mvScaleFactors[nLastOctave];
+        if (bForward) area(u, v, radius, nLastOctave, -1, false, vIndices2);
+        else if (bBackward) area(u, v, radius, 0, nLastOctave, false, vIndices2);
+        else area(u, v, radius, nLastOctave - 1, nLastOctave + 1, false, vIndices2);
+        if (vIndices2.empty()) continue;
+        uint64_t a[4];
+        std::memcpy(a, p.desc, 32);
+        const bool obs = p.flags & 4;
+        {
+            int bestDist = 256, bestIdx2 = -1;
+            for (size_t k = 0; k < vIndices2.size(); k++) {
+                const size_t i2 = vIndices2[k];
+                if (blocked[i2]) continue;
+                if (!stereoCam && uRight && uRight[i2] > 0) {
+                    const float ur = u - mbf * invzc;
+                    const float er = std::fabs(ur - uRight[i2]);
+                    if (er > radius) continue;
+                }
+                uint64_t b[4];
+                std::memcpy(b, desc + i2 * 32, 32);
+                const int dist = hamming256(a, b);
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestIdx2 = (int)i2;
+                }
+            }
+            if (bestDist <= TH_HIGH) {
+                owner[bestIdx2] = i;    // CurrentFrame.mvpMapPoints[bestIdx2] = pMP
+                blocked[bestIdx2] = obs ? 1 : 0;
+                matchL[i] = bestIdx2;
+                nmatches++;
+                if (checkOrientation) {
+                    float rot = p.angle - keys[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(bestIdx2);
+                    entryPoint[bin].push_back({i, 0});
+                }
+            }
+        }
+        if (stereoCam) {
+            const float ur = p.ur, vr = p.vr;
+            radius = th * mvScaleFactors[nLastOctave];
+            if (bForward) area(ur, vr, radius, nLastOctave, -1, true, vIndices2);
+            else if (bBackward) area(ur, vr, radius, 0, nLastOctave, true, vIndices2);
+            else area(ur, vr, radius, nLastOctave - 1, nLastOctave + 1, true, vIndices2);
+            int bestDist = 256, bestIdx2 = -1;
+            for (size_t k = 0; k < vIndices2.size(); k++) {
+                const size_t i2 = vIndices2[k];
+                if (blocked[i2 + nleft]) continue;
+                uint64_t b[4];
+                std::memcpy(b, desc + (i2 + nleft) * 32, 32);
+                const int dist = hamming256(a, b);
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestIdx2 = (int)i2;
+                }
+            }
+            if (bestDist <= TH_HIGH) {
+                owner[bestIdx2 + nleft] = i;
+                blocked[bestIdx2 + nleft] = obs ? 1 : 0;
+                matchR[i] = bestIdx2;
+                nmatches++;
+                if (checkOrientation) {
+                    float rot = p.angle - keys[nleft + bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(bestIdx2 + nleft);
+                    entryPoint[bin].push_back({i, 1});
+                }
+            }
+        }
+    }
+    if (checkOrientation) {    // :1697-1715
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i != ind1 && i != ind2 && i != ind3) {
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    owner[rotHist[i][j]] = -1;    // CurrentFrame.mvpMapPoints[...] = NULL
+                    nmatches--;
+                    (entryPoint[i][j].second ? matchR : matchL)[entryPoint[i][j].first] = -1;
+                }
+            }
+        }
+    }
+    return nmatches;
+}
+
+int orc_search_by_projection_keyframe(const orc_keypoint* keysUn, const uint8_t* desc, const uint8_t* occupied, int n,
+                                      float mnMinX, float mnMinY, float mnMaxX, float mnMaxY, const float* mvScaleFactors,
+                                      const orc_frame_point* pts, int npts, float th, int ORBdist, int checkOrientation,
+                                      int32_t* match, int32_t* owner) {
+    const int HISTO_LENGTH = 30;
+    const float gwInv = static_cast<float>(GRID_COLS) / (mnMaxX - mnMinX);
+    const float ghInv = static_cast<float>(GRID_ROWS) / (mnMaxY - mnMinY);
+    static thread_local FrameGrids G;
+    for (int i = 0; i < GRID_COLS; i++)
+        for (int j = 0; j < GRID_ROWS; j++) G.mGrid[i][j].clear();
+    for (int i = 0; i < n; i++) {
+        const orc_keypoint& kp = keysUn[i];
+        const int posX = (int)std::round((kp.x - mnMinX) * gwInv);
+        const int posY = (int)std::round((kp.y - mnMinY) * ghInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        G.mGrid[posX][posY].push_back(i);
+    }
+    std::vector<uint8_t> taken(n, 0);    // CurrentFrame.mvpMapPoints[i2] != NULL
+    for (int i = 0; i < n; i++) {
+        taken[i] = occupied ? occupied[i] : 0;
+        owner[i] = -1;
+    }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<int> entryPoint[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nmatches = 0;
+    std::vector<size_t> vIndices2;
+    for (int i = 0; i < npts; i++) {
+        match[i] = -1;
+        const orc_frame_point& p = pts[i];
+        if (!(p.flags & 1)) continue;    // pMP && !isBad() && !sAlreadyFound.count(pMP) && dist3D inside [min, max]
+        const float u = p.u, v = p.v;
+        if (u < mnMinX || u > mnMaxX) continue;
+        if (v < mnMinY || v > mnMaxY) continue;
+        const int nPredictedLevel = p.level;
+        const float radius = th * mvScaleFactors[nPredictedLevel];
+        // GetFeaturesInArea(uv(0), uv(1), radius, nPredictedLevel - 1, nPredictedLevel + 1)
+        vIndices2.clear();
+        {
+            const float factorX = radius, factorY = radius;
+            const int minLevel = nPredictedLevel - 1, maxLevel = nPredictedLevel + 1;
+            const int nMinCellX = std::max(0, (int)std::floor((u - mnMinX - factorX) * gwInv));
+            const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((u - mnMinX + factorX) * gwInv));
+            const int nMinCellY = std::max(0, (int)std::floor((v - mnMinY - factorY) * ghInv));
+            const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((v - mnMinY + factorY) * ghInv));
+            if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0)) {
+                const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+                for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                    for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                        const std::vector<size_t>& vCell = G.mGrid[ix][iy];
+                        for (size_t j = 0; j < vCell.size(); j++) {
+                            const orc_keypoint& kpUn = keysUn[vCell[j]];
+                            if (bCheckLevels) {
+                                if (kpUn.octave < minLevel) continue;
+                                if (maxLevel >= 0)
+                                    if (kpUn.octave > maxLevel) continue;
+                            }
+                            const float distx = kpUn.x - u;
+                            const float disty = kpUn.y - v;
+                            if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) vIndices2.push_back(vCell[j]);
+                        }
+                    }
+            }
+        }
+        if (vIndices2.empty()) continue;
+        uint64_t a[4];
+        std::memcpy(a, p.desc, 32);
+        int bestDist = 256, bestIdx2 = -1;
+        for (size_t k = 0; k < vIndices2.size(); k++) {
+            const size_t i2 = vIndices2[k];
+            if (taken[i2]) continue;
+            uint64_t b[4];
+            std::memcpy(b, desc + i2 * 32, 32);
+            const int dist = hamming256(a, b);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx2 = (int)i2;
+            }
+        }
+        if (bestDist <= ORBdist) {
+            owner[bestIdx2] = i;
+            taken[bestIdx2] = 1;
+            match[i] = bestIdx2;
+            nmatches++;
+            if (checkOrientation) {
+                float rot = p.angle - keysUn[bestIdx2].angle;
+                if (rot < 0.0 || rot > 360.0) rot = std::fmod(rot, 360.0f);    // "REWRITTEN BUGGY PART" :2014-2018
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+                entryPoint[bin].push_back(i);
+            }
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i != ind1 && i != ind2 && i != ind3) {
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    owner[rotHist[i][j]] = -1;
+                    nmatches--;
+                    match[entryPoint[i][j]] = -1;
+                }
+            }
+        }
+    }
+    return nmatches;
+}
+
 // ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764) + ComputeThreeMaxima (:2061-2102) ----------------------
 // F1 / F2 are monocular frames (Nleft == -1); the grid is F2's.  vMatchedDistance / vnMatches21 make the loop order
 // dependent (a later keypoint steals a match only with a strictly smaller distance, and matched candidates with a

@@ -125,6 +125,34 @@ int orc_search_by_projection_stereo(const orc_keypoint* keys, const uint8_t* des
                                     const orc_track_point_stereo* pts, int npts, float th, int bFarPoints,
                                     float thFarPoints, float mfNNratio, int32_t* matchL, int32_t* matchR, int32_t* owner);
 
+/* A MapPoint of LastFrame / of a KeyFrame as the frame-to-frame searches see it: its projection into the current left
+ * camera (u, v) and, for stereo-camera frames, into the right one (ur, vr); 1 / z in the current camera; the octave of
+ * its keypoint in the last frame (or the predicted level for the KeyFrame form); the angle of that keypoint; flags: bit 0
+ * the point reaches the search (all of the reference's `continue`s that need the pose are taken by the caller), bit 2
+ * pMP->Observations() > 0. */
+typedef struct {
+    float u, v, ur, vr, invz, angle;
+    int32_t level, flags;
+    uint8_t desc[32];
+} orc_frame_point;
+/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) incl. SearchByProjectionThread and the rotation
+ * histogram (ORBmatcher.cc:1683-1921).  keys / desc / occupied: the n slots of CurrentFrame, left first; nleft == n is
+ * Nleft == -1 (keys = mvKeysUn, uRight = mvuRight applies), nleft < n a stereo-camera frame (keys = mvKeys then
+ * mvKeysRight, uRight ignored).  dir: 0, 1 = bForward, 2 = bBackward.  matchL / matchR[npts]: slot chosen by the left /
+ * right search (right: relative to nleft) or -1, after the rotation check; owner[n] = CurrentFrame.mvpMapPoints as point
+ * indices (-1 = NULL).  Returns nmatches. */
+int orc_search_by_projection_frame(const orc_keypoint* keys, const uint8_t* desc, const float* uRight,
+                                   const uint8_t* occupied, int n, int nleft, float mnMinX, float mnMinY, float mnMaxX,
+                                   float mnMaxY, const float* mvScaleFactors, float mbf, const orc_frame_point* pts,
+                                   int npts, float th, int dir, int checkOrientation, int32_t* matchL, int32_t* matchR,
+                                   int32_t* owner);
+/* ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (ORBmatcher.cc:1923-2059), Nleft == -1.
+ * occupied[i] = CurrentFrame.mvpMapPoints[i] != NULL. */
+int orc_search_by_projection_keyframe(const orc_keypoint* keysUn, const uint8_t* desc, const uint8_t* occupied, int n,
+                                      float mnMinX, float mnMinY, float mnMaxX, float mnMaxY, const float* mvScaleFactors,
+                                      const orc_frame_point* pts, int npts, float th, int ORBdist, int checkOrientation,
+                                      int32_t* match, int32_t* owner);
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) for
  * monocular frames.  prevMatchedXY: n1 (x, y) pairs, updated in place (:759-761); vnMatches12: n1 ints. Returns nmatches. */
 int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, const orc_keypoint* keys2,

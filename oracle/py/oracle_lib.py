@@ -340,6 +340,57 @@ def search_for_initialization(keys1, desc1, keys2, desc2, bounds, prev_matched, 
     return m12, pm, int(nm)
 
 
+FRAME_POINT_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("vr", "<f4"), ("invz", "<f4"), ("angle", "<f4"),
+                              ("level", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
+assert FRAME_POINT_DTYPE.itemsize == 64
+
+
+def search_by_projection_frame(keys, desc, u_right, occupied, nleft, bounds, scale_factors, mbf, pts, th=15.0, direction=0,
+                               check_orientation=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1683-1921).  keys / desc: the N
+    slots of the current frame, left first (nleft == N: Nleft == -1).  -> (matchL, matchR, owner, nmatches)"""
+    k = np.ascontiguousarray(keys, KP_DTYPE)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = k.shape[0]
+    ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+    oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    p = np.ascontiguousarray(pts, FRAME_POINT_DTYPE)
+    ml, mr, owner = np.empty(p.shape[0], np.int32), np.empty(p.shape[0], np.int32), np.empty(max(n, 1), np.int32)
+    L = lib()
+    L.orc_search_by_projection_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                                 C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_float, C.c_void_p, C.c_int,
+                                                 C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.orc_search_by_projection_frame.restype = C.c_int
+    nm = L.orc_search_by_projection_frame(_p(k), _p(d), None if ur is None else _p(ur), None if oc is None else _p(oc), n,
+                                          int(nleft), float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]),
+                                          _p(sf), float(mbf), _p(p), p.shape[0], float(th), int(direction),
+                                          int(bool(check_orientation)), _p(ml), _p(mr), _p(owner))
+    return ml, mr, owner[:n], int(nm)
+
+
+def search_by_projection_keyframe(keys_un, desc, occupied, bounds, scale_factors, pts, th=10.0, orb_dist=100,
+                                  check_orientation=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (ORBmatcher.cc:1923-2059).
+    -> (match, owner, nmatches)"""
+    k = np.ascontiguousarray(keys_un, KP_DTYPE)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = k.shape[0]
+    oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    p = np.ascontiguousarray(pts, FRAME_POINT_DTYPE)
+    m, owner = np.empty(p.shape[0], np.int32), np.empty(max(n, 1), np.int32)
+    L = lib()
+    L.orc_search_by_projection_keyframe.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float,
+                                                    C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
+                                                    C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    L.orc_search_by_projection_keyframe.restype = C.c_int
+    nm = L.orc_search_by_projection_keyframe(_p(k), _p(d), None if oc is None else _p(oc), n, float(bounds[0]),
+                                             float(bounds[1]), float(bounds[2]), float(bounds[3]), _p(sf), _p(p), p.shape[0],
+                                             float(th), int(orb_dist), int(bool(check_orientation)), _p(m), _p(owner))
+    return m, owner[:n], int(nm)
+
+
 FISHEYE_RIG_DTYPE = np.dtype([("cam1", "<f4", 8), ("cam2", "<f4", 8), ("Rlr", "<f4", 9), ("tlr", "<f4", 3),
                               ("precision", "<f4"), ("nlevels", "<i4"), ("level_sigma2", "<f4", 16)])
 _EIGEN_HOOK = None

@@ -78,6 +78,10 @@ SYMBOLS = {
     "orbfe_search_by_projection_stereo_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp,
                                                      _i, _i, C.c_float, _i, C.c_float, C.c_float, _vp, _vp, _vp, _vp,
                                                      _u]),
+    "orbfe_search_by_projection_frame_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, C.c_float, _vp,
+                                                    _vp, _i, _i, C.c_float, _i, _vp, _vp, _vp, _vp, _u]),
+    "orbfe_search_by_projection_keyframe_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _i, C.c_float,
+                                                       _i, _i, _vp, _vp, _vp, _u]),
     "orbfe_search_for_initialization_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, C.c_float, _i, _vp,
                                                    _vp, _vp, _u]),
     "orbfe_stereo_fisheye_matches_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp,

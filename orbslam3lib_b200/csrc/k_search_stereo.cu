@@ -22,6 +22,7 @@ constexpr int SS_THREADS = 256;
 constexpr int SS_WARPS = SS_THREADS / 32;
 constexpr int SS_ROWS = 48, SS_COLS = 64, SS_CELLS = SS_ROWS * SS_COLS;
 constexpr int SS_TH_HIGH = 100;
+constexpr int SI_HISTO_LEN = 30;    // HISTO_LENGTH, ORBmatcher.cc:38
 
 struct StereoSearchParams {
     float minX, minY, maxX, maxY;
@@ -440,6 +441,356 @@ int launch_search_by_projection_stereo(const float bounds[4], const float* scale
     smem_opt_in(optIn, search_by_projection_stereo_kernel, smem);
     search_by_projection_stereo_kernel<<<nframes, SS_THREADS, smem, st>>>(
         P, keys, desc, occupied, nFeat, nLeft, ltr, rtl, (const TrackPointStereo*)pts, nPts, matchL, matchR, owner, nMatches);
+    return 1;
+}
+
+// ---- ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1683-1921) and ----------------------
+// ---- ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (:1923-2059) ----------------------------
+// The per-frame tracking matcher: every MapPoint of the last frame (of a key frame) is projected into the current frame
+// by the caller and searched in a window of th * scale[octave] on the frame grid; levels by motion direction (bForward:
+// octave and above, bBackward: 0..octave, else octave +- 1); the first minimum in visiting order wins, accepted at
+// <= TH_HIGH (<= ORBdist); stereo-camera frames repeat the search on mGridRight around the right-camera projection, but
+// only when the left window held a feature at all (:1769-1770 `continue`); mono / rectified frames gate on mvuRight
+// (:1785-1790).  A slot taken by a point with Observations() > 0 (KeyFrame form: by any point) is invisible to the later
+// points: same optimistic chunk + ordered prefix commit as above.  Rotation histogram: one entry per accepted search
+// (bins 0..12 only, because factor = 1 / HISTO_LENGTH multiplies degrees: reproduced), ComputeThreeMaxima, and every entry
+// of a losing bin clears its slot and takes one off nmatches (:1697-1715) even when another point holds the slot too.
+struct FramePoint {    // == orbfe_frame_point
+    float u, v, ur, vr, invz, angle;
+    int level, flags;
+    uint32_t desc[8];
+};
+static_assert(sizeof(FramePoint) == 64, "orbfe_frame_point layout");
+
+struct FrameSearchParams {
+    StereoSearchParams g;    // bounds, scale, th, cap, ptsCap
+    float mbf;
+    int keyframe, distTh, checkOrientation;
+};
+
+// best = min (distance, cell, index) over the features of window w that are neither taken nor gated out; *any = the
+// window holds a feature at all (vIndices2 is not empty).  Warp-uniform results.
+__device__ __forceinline__ unsigned long long sf_search(const SWindow& w, const int* cellStart, const unsigned short* items,
+                                                        const orbfe_keypoint* keys, const uint8_t* desc, int first,
+                                                        const uint32_t* blocked, const uint32_t (&md)[8],
+                                                        const float* uRight, float urProj, float radius, bool* any) {
+    constexpr unsigned long long NONE = 256ull << 32;
+    unsigned long long k1 = NONE;
+    bool seen = false;
+    if (w.cx0 <= w.cx1) {
+        const int lane = threadIdx.x & 31;
+        const int ncy = w.cy1 - w.cy0 + 1;
+        const int ncell = (w.cx1 - w.cx0 + 1) * ncy;
+        for (int c = lane; c < ncell; c += 32) {
+            const int cell = (w.cx0 + c / ncy) * SS_ROWS + w.cy0 + c % ncy;
+            for (int t = cellStart[cell]; t < cellStart[cell + 1]; t++) {
+                const int idx = items[t];
+                if (!ss_inside(w, keys[first + idx])) continue;
+                seen = true;
+                const int slot = first + idx;
+                if ((blocked[slot >> 5] >> (slot & 31)) & 1u) continue;
+                if (uRight) {
+                    const float ur = uRight[slot];
+                    if (ur > 0) {
+                        const float er = fabsf(urProj - ur);
+                        if (er > radius) continue;
+                    }
+                }
+                const uint4 b0 = __ldg(reinterpret_cast<const uint4*>(desc + (size_t)slot * 32));
+                const uint4 b1 = __ldg(reinterpret_cast<const uint4*>(desc + (size_t)slot * 32) + 1);
+                const int d = __popc(md[0] ^ b0.x) + __popc(md[1] ^ b0.y) + __popc(md[2] ^ b0.z) + __popc(md[3] ^ b0.w) +
+                              __popc(md[4] ^ b1.x) + __popc(md[5] ^ b1.y) + __popc(md[6] ^ b1.z) + __popc(md[7] ^ b1.w);
+                const unsigned long long key = ((unsigned long long)d << 32) | ((uint32_t)cell << 16) | (uint32_t)idx;
+                k1 = key < k1 ? key : k1;
+            }
+        }
+    }
+    *any = __any_sync(0xffffffffu, seen);
+    return ss_min_u64(k1);
+}
+
+__device__ __forceinline__ void sf_levels(SWindow& w, int level, int dir, int keyframe) {
+    if (!keyframe && dir == 1) {
+        w.minLevel = level;
+        w.maxLevel = -1;
+    } else if (!keyframe && dir == 2) {
+        w.minLevel = 0;
+        w.maxLevel = level;
+    } else {
+        w.minLevel = level - 1;
+        w.maxLevel = level + 1;
+    }
+}
+
+__device__ __forceinline__ int sf_bin(float angleSrc, float angleCur, int keyframe) {
+    float rot = angleSrc - angleCur;
+    if (keyframe && (rot < 0.0f || rot > 360.0f)) rot = fmodf(rot, 360.0f);    // :2014-2018
+    if (rot < 0.0f) rot += 360.0f;
+    int bin = (int)roundf(rot * (1.0f / SI_HISTO_LEN));
+    if (bin == SI_HISTO_LEN) bin = 0;
+    return min(max(bin, 0), SI_HISTO_LEN - 1);
+}
+
+// grid: nframes; block SS_THREADS; dynamic shared memory: search_frame_smem_bytes(cap, ptsCap)
+__global__ void __launch_bounds__(SS_THREADS) search_frame_kernel(
+    const __grid_constant__ FrameSearchParams Q, const orbfe_keypoint* __restrict__ keysAll,
+    const uint8_t* __restrict__ descAll, const float* __restrict__ uRightAll, const uint8_t* __restrict__ occupiedAll,
+    const int* __restrict__ nFeat, const int* __restrict__ nLeftArr, const int* __restrict__ dirArr,
+    const FramePoint* __restrict__ ptsAll, const int* __restrict__ nPts, int* __restrict__ matchLAll,
+    int* __restrict__ matchRAll, int* __restrict__ ownerAll, int* __restrict__ nMatches) {
+    const StereoSearchParams& P = Q.g;
+    extern __shared__ __align__(16) uint8_t smem[];
+    int* cellStartL = reinterpret_cast<int*>(smem);
+    int* cellStartR = cellStartL + SS_CELLS + 1;
+    int* cellFill = cellStartR + SS_CELLS + 1;
+    int* hist = cellFill + SS_CELLS;    // 32
+    uint32_t* blocked = reinterpret_cast<uint32_t*>(hist + 32);
+    unsigned short* itemsL = reinterpret_cast<unsigned short*>(blocked + ((P.cap + 31) >> 5));
+    unsigned short* itemsR = itemsL + P.cap;
+    uint8_t* binL = reinterpret_cast<uint8_t*>(itemsR + P.cap);    // histogram bin of point i's left / right entry, 0xff none
+    uint8_t* binR = binL + P.ptsCap;
+    __shared__ int sScan[SS_WARPS + 1];
+    __shared__ int sTotal, sOpen, sCount;
+    __shared__ int sResL[SS_WARPS], sResR[SS_WARPS], sBin[SS_WARPS][2];
+    __shared__ int sInd[3];
+
+    const int f = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = min(nFeat[f], P.cap);
+    const int nleft = nLeftArr ? min(max(nLeftArr[f], 0), n) : n;
+    const bool stereoCam = nleft != n;    // Nleft != -1
+    const int dir = dirArr ? dirArr[f] : 0;
+    const int npts = min(nPts[f], P.ptsCap);
+    const orbfe_keypoint* keys = keysAll + (size_t)f * P.cap;
+    const uint8_t* desc = descAll + (size_t)f * P.cap * 32;
+    const float* uRight = (uRightAll && !stereoCam && !Q.keyframe) ? uRightAll + (size_t)f * P.cap : nullptr;
+    const uint8_t* occupied = occupiedAll ? occupiedAll + (size_t)f * P.cap : nullptr;
+    const FramePoint* pts = ptsAll + (size_t)f * P.ptsCap;
+    int* matchL = matchLAll + (size_t)f * P.ptsCap;
+    int* matchR = matchRAll ? matchRAll + (size_t)f * P.ptsCap : nullptr;
+    int* owner = ownerAll + (size_t)f * P.cap;
+    const float gwInv = (float)SS_COLS / (P.maxX - P.minX);
+    const float ghInv = (float)SS_ROWS / (P.maxY - P.minY);
+
+    for (int i = tid; i < (P.cap + 31) >> 5; i += SS_THREADS) blocked[i] = 0;
+    for (int i = tid; i < npts; i += SS_THREADS) {
+        binL[i] = 0xffu;
+        binR[i] = 0xffu;
+    }
+    if (tid < 32) hist[tid] = 0;
+    if (tid == 0) sCount = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += SS_THREADS) {
+        if (occupied && occupied[i]) atomicOr(&blocked[i >> 5], 1u << (i & 31));
+        owner[i] = -1;
+    }
+    ss_build_grid(keys, 0, nleft, P, gwInv, ghInv, cellStartL, cellFill, itemsL, sScan, &sTotal);
+    ss_build_grid(keys, nleft, n - nleft, P, gwInv, ghInv, cellStartR, cellFill, itemsR, sScan, &sTotal);
+
+    auto eligible_of = [&](const FramePoint& q) {
+        return (q.flags & 1) && q.level >= 0 && q.level < ORBFE_MAX_LEVELS && !(q.u < P.minX || q.u > P.maxX) &&
+               !(q.v < P.minY || q.v > P.maxY);
+    };
+    for (int base = 0; base < npts; base += SS_WARPS) {
+        const int iP = base + warp;
+        const bool have = iP < npts;
+        FramePoint mp;
+        bool eligible = false;
+        if (have) {
+            mp = pts[iP];
+            eligible = eligible_of(mp);
+        }
+        if (tid == 0) sOpen = (int)(0xffffffffu >> (32 - min(npts - base, SS_WARPS)));
+        __syncthreads();
+        for (;;) {
+            if (have && ((sOpen >> warp) & 1)) {
+                int resL = -1, resR = -1, bL = 0xff, bR = 0xff;
+                if (eligible) {
+                    const float radius = P.th * P.scale[mp.level];
+                    SWindow w;
+                    ss_window(w, P, gwInv, ghInv, mp.u, mp.v, radius, mp.level);
+                    sf_levels(w, mp.level, dir, Q.keyframe);
+                    const float urProj = mp.u - Q.mbf * mp.invz;    // :1786 (no FMA: --fmad=false)
+                    bool any;
+                    const unsigned long long k1 = sf_search(w, cellStartL, itemsL, keys, desc, 0, blocked, mp.desc, uRight, urProj, radius, &any);
+                    if (any) {    // :1769-1770 an empty window skips the right camera too
+                        if ((int)(k1 >> 32) <= Q.distTh) {
+                            resL = (int)(k1 & 0xffffu);
+                            if (Q.checkOrientation) bL = sf_bin(mp.angle, keys[resL].angle, Q.keyframe);
+                        }
+                        if (stereoCam && !Q.keyframe) {
+                            SWindow wr;
+                            ss_window(wr, P, gwInv, ghInv, mp.ur, mp.vr, radius, mp.level);
+                            sf_levels(wr, mp.level, dir, 0);
+                            bool anyR;
+                            const unsigned long long k2 = sf_search(wr, cellStartR, itemsR, keys, desc, nleft, blocked, mp.desc, nullptr, 0.f, radius, &anyR);
+                            if ((int)(k2 >> 32) <= Q.distTh) {
+                                resR = (int)(k2 & 0xffffu);
+                                if (Q.checkOrientation) bR = sf_bin(mp.angle, keys[nleft + resR].angle, 0);
+                            }
+                        }
+                    }
+                }
+                if (lane == 0) {
+                    sResL[warp] = resL;
+                    sResR[warp] = resR;
+                    sBin[warp][0] = bL;
+                    sBin[warp][1] = bR;
+                }
+            }
+            __syncthreads();
+            if (warp == 0) {
+                const int open = sOpen;
+                const bool mine = lane < SS_WARPS && ((open >> lane) & 1);
+                SWindow wl, wr;
+                wl.cx0 = wr.cx0 = 1;
+                wl.cx1 = wr.cx1 = 0;
+                bool el = false, blocks = false;
+                if (mine) {
+                    const FramePoint q = pts[base + lane];
+                    el = eligible_of(q);
+                    blocks = Q.keyframe || (q.flags & 4);
+                    if (el) {
+                        const float radius = P.th * P.scale[q.level];
+                        ss_window(wl, P, gwInv, ghInv, q.u, q.v, radius, q.level);
+                        sf_levels(wl, q.level, dir, Q.keyframe);
+                        ss_window(wr, P, gwInv, ghInv, q.ur, q.vr, radius, q.level);
+                        sf_levels(wr, q.level, dir, 0);
+                    }
+                }
+                // slots this point will make invisible to the later ones
+                const int takeL = (mine && blocks) ? sResL[lane] : -1;
+                const int takeR = (mine && blocks && sResR[lane] >= 0) ? sResR[lane] + nleft : -1;
+                bool valid = true;
+                for (int i = 0; i < SS_WARPS - 1; i++) {
+                    const int tl = __shfl_sync(0xffffffffu, takeL, i), tr = __shfl_sync(0xffffffffu, takeR, i);
+                    if (i < lane && mine && el) {
+                        if (tl >= 0 && ss_inside(wl, keys[tl])) valid = false;    // conservative: ignores the other gates
+                        if (tr >= 0 && stereoCam && ss_inside(wr, keys[tr])) valid = false;
+                    }
+                }
+                const unsigned bad = __ballot_sync(0xffffffffu, mine && !valid);
+                const int firstBad = bad ? __ffs(bad) - 1 : 32;
+                const bool commit = mine && lane < firstBad;
+                unsigned todo = __ballot_sync(0xffffffffu, commit);
+                const unsigned done = todo;
+                while (todo) {    // in point order: the last assignment of a slot wins (mvpMapPoints[slot] = pMP)
+                    const int i = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    if (lane == i) {
+                        const int rl = sResL[i], rr = sResR[i];
+                        matchL[base + i] = rl;
+                        if (matchR) matchR[base + i] = rr;
+                        if (rl >= 0) {
+                            owner[rl] = base + i;
+                            if (blocks) blocked[rl >> 5] |= 1u << (rl & 31);
+                            sCount++;
+                            if (sBin[i][0] != 0xff) {
+                                binL[base + i] = (uint8_t)sBin[i][0];
+                                hist[sBin[i][0]]++;
+                            }
+                        }
+                        if (rr >= 0) {
+                            const int s = rr + nleft;
+                            owner[s] = base + i;
+                            if (blocks) blocked[s >> 5] |= 1u << (s & 31);
+                            sCount++;
+                            if (sBin[i][1] != 0xff) {
+                                binR[base + i] = (uint8_t)sBin[i][1];
+                                hist[sBin[i][1]]++;
+                            }
+                        }
+                    }
+                    __syncwarp();
+                }
+                if (lane == 0) sOpen = open & ~(int)done;
+            }
+            __syncthreads();
+            if (sOpen == 0) break;
+            __syncthreads();
+        }
+        __syncthreads();
+    }
+    if (Q.checkOrientation) {
+        if (tid == 0) {    // ComputeThreeMaxima (:2061-2102)
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int i = 0; i < SI_HISTO_LEN; i++) {
+                const int sz = hist[i];
+                if (sz > max1) {
+                    max3 = max2; max2 = max1; max1 = sz;
+                    ind3 = ind2; ind2 = ind1; ind1 = i;
+                } else if (sz > max2) {
+                    max3 = max2; max2 = sz;
+                    ind3 = ind2; ind2 = i;
+                } else if (sz > max3) {
+                    max3 = sz;
+                    ind3 = i;
+                }
+            }
+            if ((float)max2 < 0.1f * (float)max1) {
+                ind2 = -1;
+                ind3 = -1;
+            } else if ((float)max3 < 0.1f * (float)max1) {
+                ind3 = -1;
+            }
+            sInd[0] = ind1;
+            sInd[1] = ind2;
+            sInd[2] = ind3;
+        }
+        __syncthreads();    // every owner[] write of the loop is done: the removals below win
+        int removed = 0;
+        for (int i = tid; i < npts; i += SS_THREADS) {
+            const int bl = binL[i], br = binR[i];
+            if (bl != 0xff && bl != sInd[0] && bl != sInd[1] && bl != sInd[2]) {
+                owner[matchL[i]] = -1;
+                matchL[i] = -1;
+                removed++;
+            }
+            if (br != 0xff && br != sInd[0] && br != sInd[1] && br != sInd[2]) {
+                owner[matchR[i] + nleft] = -1;
+                matchR[i] = -1;
+                removed++;
+            }
+        }
+        if (removed) atomicSub(&sCount, removed);
+        __syncthreads();
+    }
+    if (tid == 0 && nMatches) nMatches[f] = sCount;
+}
+
+size_t search_frame_smem_bytes(int cap, int ptsCap) {
+    return (size_t)(3 * SS_CELLS + 2 + 32) * 4 + (size_t)((cap + 31) / 32) * 4 + (size_t)cap * 4 + (size_t)ptsCap * 2 + 16;
+}
+
+// keyframe = 0: SearchByProjection(CurrentFrame, LastFrame, th, bMono); 1: SearchByProjection(CurrentFrame, pKF, ...)
+int launch_search_frame(const float bounds[4], const float* scale, int nlevels, float th, float mbf, int keyframe, int distTh,
+                        int checkOrientation, const orbfe_keypoint* keys, const uint8_t* desc, const float* uRight,
+                        const uint8_t* occupied, const int* nFeat, const int* nLeft, const int* dir, int cap,
+                        const void* pts, const int* nPts, int ptsCap, int nframes, int* matchL, int* matchR, int* owner,
+                        int* nMatches, cudaStream_t st) {
+    if (nframes <= 0) return 0;
+    FrameSearchParams Q;
+    StereoSearchParams& P = Q.g;
+    P.minX = bounds[0];
+    P.minY = bounds[1];
+    P.maxX = bounds[2];
+    P.maxY = bounds[3];
+    for (int l = 0; l < ORBFE_MAX_LEVELS; l++) P.scale[l] = l < nlevels ? scale[l] : 1.0f;
+    P.th = th;
+    P.thFar = 0.f;
+    P.nnRatio = 0.f;
+    P.farPoints = 0;
+    P.cap = cap;
+    P.ptsCap = ptsCap;
+    Q.mbf = mbf;
+    Q.keyframe = keyframe;
+    Q.distTh = distTh;
+    Q.checkOrientation = checkOrientation;
+    const size_t smem = search_frame_smem_bytes(cap, ptsCap);
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, search_frame_kernel, smem);
+    search_frame_kernel<<<nframes, SS_THREADS, smem, st>>>(Q, keys, desc, uRight, occupied, nFeat, nLeft, dir,
+                                                          (const FramePoint*)pts, nPts, matchL, matchR, owner, nMatches);
     return 1;
 }
 

@@ -30,6 +30,12 @@ int launch_blur_tiles(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, c
 size_t stereo_smem_bytes(int cap);
 size_t search_smem_bytes(int cap);
 size_t search_stereo_smem_bytes(int cap);
+size_t search_frame_smem_bytes(int cap, int ptsCap);
+int launch_search_frame(const float bounds[4], const float* scale, int nlevels, float th, float mbf, int keyframe, int distTh,
+                        int checkOrientation, const orbfe_keypoint* keys, const uint8_t* desc, const float* uRight,
+                        const uint8_t* occupied, const int* nFeat, const int* nLeft, const int* dir, int cap,
+                        const void* pts, const int* nPts, int ptsCap, int nframes, int* matchL, int* matchR, int* owner,
+                        int* nMatches, cudaStream_t st);
 int launch_search_by_projection_stereo(const float bounds[4], const float* scale, int nlevels, float th, int farPoints,
                                        float thFar, float nnRatio, const orbfe_keypoint* keys, const uint8_t* desc,
                                        const uint8_t* occupied, const int* nFeat, const int* nLeft, const int* ltr,
@@ -1299,6 +1305,101 @@ int orbfe_search_by_projection_stereo_batch(orbfe_matcher* m, const orbfe_keypoi
     ORBFE_MCUDA(m, cudaStreamSynchronize(st));
     cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
     return ORBFE_OK;
+}
+
+// shared body of the two frame-to-frame searches (k_search_stereo.cu: search_frame_kernel)
+static int search_frame_common(orbfe_matcher* m, int keyframe, const orbfe_keypoint* keys, const uint8_t* desc,
+                               const float* u_right, const uint8_t* occupied, const int32_t* n, const int32_t* nleft,
+                               const int32_t* dir, int cap, const float bounds[4], const float* scale_factors, int nlevels,
+                               float mbf, const orbfe_frame_point* pts, const int32_t* npts, int pts_cap, int nframes,
+                               float th, int dist_th, int check_orientation, int32_t* match_left, int32_t* match_right,
+                               int32_t* owner, int32_t* nmatches, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (nframes < 0 || cap < 0 || pts_cap < 0 || nlevels < 1 || nlevels > ORBFE_MAX_LEVELS)
+        return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (nframes == 0) return ORBFE_OK;
+    if (!n || !npts || !bounds || !scale_factors || !match_left || !owner || (nleft && !match_right) ||
+        (cap > 0 && (!keys || !desc)) || (pts_cap > 0 && !pts))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (!(bounds[2] > bounds[0]) || !(bounds[3] > bounds[1])) return set_merr(m, ORBFE_ERR_ARG, "empty image bounds");
+    if (cap > 65535 || search_frame_smem_bytes(cap, pts_cap) > 200 * 1024)
+        return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d / point capacity %d too large for the shared-memory frame grids", cap, pts_cap);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)nframes;
+    const void* dIn[8] = {keys, desc, occupied, n, nleft, u_right, dir, npts};
+    const size_t inBytes[8] = {F * cap * sizeof(orbfe_keypoint), F * cap * 32, F * cap, F * 4, F * 4, F * cap * 4, F * 4, F * 4};
+    const void* dPts = pts;
+    if (!inDev) {
+        for (int i = 0; i < 8; i++) {
+            if (!dIn[i]) continue;
+            ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(inBytes[i], 16)));
+            if (inBytes[i]) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, dIn[i], inBytes[i], cudaMemcpyHostToDevice, st));
+            dIn[i] = m->dS[i].p;
+        }
+        ORBFE_MCUDA(m, m->dS[8].reserve(std::max<size_t>(F * pts_cap * sizeof(orbfe_frame_point), 16)));
+        if (pts_cap) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[8].p, pts, F * pts_cap * sizeof(orbfe_frame_point), cudaMemcpyHostToDevice, st));
+        dPts = m->dS[8].p;
+    }
+    int32_t *dML = match_left, *dMR = match_right, *dOwner = owner, *dCount = nmatches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dS[9].reserve(std::max<size_t>(F * pts_cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[10].reserve(std::max<size_t>(F * pts_cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[11].reserve(std::max<size_t>(F * cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[12].reserve(F * 4));
+        dML = (int32_t*)m->dS[9].p;
+        dMR = match_right ? (int32_t*)m->dS[10].p : nullptr;
+        dOwner = (int32_t*)m->dS[11].p;
+        dCount = (int32_t*)m->dS[12].p;
+    }
+    ORBFE_MCUDA(m, cudaMemsetAsync(dML, 0xff, F * pts_cap * 4, st));
+    if (dMR) ORBFE_MCUDA(m, cudaMemsetAsync(dMR, 0xff, F * pts_cap * 4, st));
+    ORBFE_MCUDA(m, cudaMemsetAsync(dOwner, 0xff, F * cap * 4, st));
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_search_frame(bounds, scale_factors, nlevels, th, mbf, keyframe, dist_th, check_orientation,
+                                             (const orbfe_keypoint*)dIn[0], (const uint8_t*)dIn[1], (const float*)dIn[5],
+                                             (const uint8_t*)dIn[2], (const int*)dIn[3], (const int*)dIn[4], (const int*)dIn[6],
+                                             cap, dPts, (const int*)dIn[7], pts_cap, nframes, dML, dMR, dOwner, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        if (pts_cap) {
+            ORBFE_MCUDA(m, cudaMemcpyAsync(match_left, dML, F * pts_cap * 4, cudaMemcpyDeviceToHost, st));
+            if (match_right) ORBFE_MCUDA(m, cudaMemcpyAsync(match_right, dMR, F * pts_cap * 4, cudaMemcpyDeviceToHost, st));
+        }
+        if (cap) ORBFE_MCUDA(m, cudaMemcpyAsync(owner, dOwner, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_projection_frame_batch(orbfe_matcher* m, const orbfe_keypoint* keys, const uint8_t* desc,
+                                           const float* u_right, const uint8_t* occupied, const int32_t* n,
+                                           const int32_t* nleft, const int32_t* dir, int cap, const float bounds[4],
+                                           const float* scale_factors, int nlevels, float mbf, const orbfe_frame_point* pts,
+                                           const int32_t* npts, int pts_cap, int nframes, float th, int check_orientation,
+                                           int32_t* match_left, int32_t* match_right, int32_t* owner, int32_t* nmatches,
+                                           unsigned flags) {
+    return search_frame_common(m, 0, keys, desc, u_right, occupied, n, nleft, dir, cap, bounds, scale_factors, nlevels, mbf,
+                               pts, npts, pts_cap, nframes, th, 100 /* TH_HIGH, ORBmatcher.cc:35 */, check_orientation,
+                               match_left, match_right, owner, nmatches, flags);
+}
+
+int orbfe_search_by_projection_keyframe_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc,
+                                              const uint8_t* occupied, const int32_t* n, int cap, const float bounds[4],
+                                              const float* scale_factors, int nlevels, const orbfe_frame_point* pts,
+                                              const int32_t* npts, int pts_cap, int nframes, float th, int orb_dist,
+                                              int check_orientation, int32_t* match, int32_t* owner, int32_t* nmatches,
+                                              unsigned flags) {
+    return search_frame_common(m, 1, keys_un, desc, nullptr, occupied, n, nullptr, nullptr, cap, bounds, scale_factors,
+                               nlevels, 0.f, pts, npts, pts_cap, nframes, th, orb_dist, check_orientation, match, nullptr,
+                               owner, nmatches, flags);
 }
 
 int orbfe_search_for_initialization_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1,

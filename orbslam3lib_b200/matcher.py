@@ -160,6 +160,53 @@ class ORBmatcher:
             ptr(mr), ptr(owner), ptr(nm), 0))
         return int(nm[0]), ml, mr, owner
 
+    def SearchByProjectionFrame(self, keys, desc, nleft, bounds, scale_factors, frame_points, th, mbf=0.0, u_right=None,
+                                occupied=None, direction=0):
+        """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1683-1921), the per-frame
+        tracking call.  keys / desc: the N slots of CurrentFrame, left first (nleft == N: Nleft == -1, keys = mvKeysUn,
+        u_right = mvuRight); frame_points: scenes.FRAME_POINT_DTYPE (the MapPoints of LastFrame projected by the caller);
+        direction: 0, 1 = bForward, 2 = bBackward.  -> (nmatches, match_left, match_right, owner (N,))"""
+        from .scenes import FRAME_POINT_DTYPE
+        k = np.ascontiguousarray(keys, KP_DTYPE)
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = k.shape[0]
+        ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        p = np.ascontiguousarray(frame_points, FRAME_POINT_DTYPE)
+        ml, mr = np.full(p.shape[0], -1, np.int32), np.full(p.shape[0], -1, np.int32)
+        owner = np.full(max(n, 1), -1, np.int32)
+        nn, nl, npp, nm, dr = (np.array([v], np.int32) for v in (n, nleft, p.shape[0], 0, direction))
+        self.search_frame_batch_raw(k, d, ur, oc, nn, nl, dr, n, bounds, scale_factors, mbf, p, npp, p.shape[0], 1, th, ml, mr,
+                                    owner, nm)
+        return int(nm[0]), ml, mr, owner[:n]
+
+    def search_frame_batch_raw(self, keys, desc, u_right, occupied, n, nleft, direction, cap, bounds, scale_factors, mbf, pts,
+                               npts, pts_cap, nframes, th, match_left, match_right, owner, nmatches, flags=0):
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        self._bf._check(_lib.lib().orbfe_search_by_projection_frame_batch(
+            self._bf._h, ptr(keys), ptr(desc), ptr(u_right), ptr(occupied), ptr(n), ptr(nleft), ptr(direction), int(cap),
+            ptr(b), ptr(sf), sf.shape[0], float(mbf), ptr(pts), ptr(npts), int(pts_cap), int(nframes), float(th),
+            int(self.mbCheckOrientation), ptr(match_left), ptr(match_right), ptr(owner), ptr(nmatches), int(flags)))
+
+    def SearchByProjectionKeyFrame(self, keys_un, desc, bounds, scale_factors, frame_points, th, ORBdist, occupied=None):
+        """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (ORBmatcher.cc:1923-2059).
+        occupied[i] = CurrentFrame.mvpMapPoints[i] != NULL.  -> (nmatches, match, owner)"""
+        from .scenes import FRAME_POINT_DTYPE
+        k = np.ascontiguousarray(keys_un, KP_DTYPE)
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = k.shape[0]
+        oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        p = np.ascontiguousarray(frame_points, FRAME_POINT_DTYPE)
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        m, owner = np.full(p.shape[0], -1, np.int32), np.full(max(n, 1), -1, np.int32)
+        nn, npp, nm = (np.array([v], np.int32) for v in (n, p.shape[0], 0))
+        self._bf._check(_lib.lib().orbfe_search_by_projection_keyframe_batch(
+            self._bf._h, ptr(k), ptr(d), ptr(oc), ptr(nn), n, ptr(b), ptr(sf), sf.shape[0], ptr(p), ptr(npp), p.shape[0], 1,
+            float(th), int(ORBdist), int(self.mbCheckOrientation), ptr(m), ptr(owner), ptr(nm), 0))
+        return int(nm[0]), m, owner[:n]
+
     def SearchForInitialization(self, keys1_un, desc1, keys2_un, desc2, bounds, vbPrevMatched, windowSize=10):
         """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) on
         monocular frames given as arrays; bounds = F2's image bounds.  vbPrevMatched: (n1, 2) float32.

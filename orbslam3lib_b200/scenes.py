@@ -209,6 +209,65 @@ def track_points_stereo(keys, desc, nleft, ltr, nlevels, npts, seed, jitter=3.0,
     return pts
 
 
+# == orbfe_frame_point / orc_frame_point
+FRAME_POINT_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("vr", "<f4"), ("invz", "<f4"), ("angle", "<f4"),
+                              ("level", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
+assert FRAME_POINT_DTYPE.itemsize == 64
+
+
+def frame_points(keys, desc, nleft, ltr, u_right, nlevels, npts, seed, jitter=4.0, max_flips=40, dup_frac=0.2, mbf=47.9,
+                 rot_deg=7.0, outlier_rot_frac=0.12):
+    """MapPoints of the LAST frame as ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) sees them
+    (ORBmatcher.cc:1722-1917), synthesised from the CURRENT frame's features: point i re-observes left feature f --
+    projection = its position + jitter, right-camera projection = f's stereo partner when there is one, level = f's
+    octave -1 / 0 / +1, angle = f's angle + a common in-plane rotation (a fraction gets a random angle: the rotation
+    histogram has losers), descriptor = f's with 0..max_flips bit flips, 1/z consistent with f's mvuRight when it has
+    one (so the mvuRight gate passes for most and fails for some).  Duplicates compete for one feature; some points
+    have no observations (they do not block), some do not reach the search, some project outside the image."""
+    pts = np.zeros(npts, FRAME_POINT_DTYPE)
+    if nleft == 0 or npts == 0:
+        return pts
+    r = rand_u32(npts * 12, seed).reshape(12, npts)
+    feat = (r[0] % np.uint32(nleft)).astype(np.int64)
+    ndup = int(npts * dup_frac)
+    if ndup > 0 and npts > 1:
+        dst = (rand_u32(ndup, seed + 1) % np.uint32(npts - 1)).astype(np.int64) + 1
+        feat[dst] = feat[dst - 1]
+    u = lambda a: (a.astype(np.float64) / 4294967296.0)    # noqa: E731
+    pts["u"] = (keys["x"][feat] + (u(r[1]) * 2 - 1) * jitter).astype(np.float32)
+    pts["v"] = (keys["y"][feat] + (u(r[2]) * 2 - 1) * jitter).astype(np.float32)
+    if ltr is not None:
+        part = ltr[feat]
+        has = part >= 0
+        pr = np.where(has, part + nleft, feat)
+        pts["ur"] = (keys["x"][pr] - np.where(has, 0.0, 12.0) + (u(r[3]) * 2 - 1) * jitter).astype(np.float32)
+        pts["vr"] = (keys["y"][pr] + (u(r[4]) * 2 - 1) * jitter).astype(np.float32)
+    disp = np.full(npts, 8.0)
+    if u_right is not None:
+        ur = u_right[feat]
+        disp = np.where(ur > 0, keys["x"][feat] - ur, 8.0)
+    # u - mbf * invz ~ mvuRight +- a few pixels; every 9th point is far off (gated out)
+    off = (u(r[5]) * 2 - 1) * 2.0 + np.where(r[6] % np.uint32(9) == 0, 40.0, 0.0)
+    pts["invz"] = np.maximum((disp + off) / mbf, 1e-3).astype(np.float32)
+    ang = keys["angle"][feat].astype(np.float64) + rot_deg + (u(r[7]) * 2 - 1) * 3.0
+    ang = np.where(u(r[8]) < outlier_rot_frac, u(r[9]) * 360.0, ang)
+    pts["angle"] = np.mod(ang, 360.0).astype(np.float32)
+    pts["level"] = np.clip(keys["octave"][feat] + (r[10] % np.uint32(3)).astype(np.int32) - 1, 0, nlevels - 1)
+    sel = r[11] % np.uint32(100)
+    pts["flags"] = np.where(sel < 5, 0, 1) | np.where(sel < 85, 4, 0)
+    edge = sel == 50    # a few projections outside the image bounds
+    pts["u"] = np.where(edge, -3.0, pts["u"]).astype(np.float32)
+    d = desc[feat].copy()
+    nflip = (rand_u32(npts, seed + 2) % np.uint32(max_flips + 1)).astype(np.int64)
+    pos = (rand_u32(npts * max_flips, seed + 3) % np.uint32(256)).reshape(npts, max_flips).astype(np.int64)
+    for k in range(max_flips):
+        rows = np.nonzero(nflip > k)[0]
+        q = pos[rows, k]
+        d[rows, q >> 3] ^= (1 << (q & 7)).astype(np.uint8)
+    pts["desc"] = d
+    return pts
+
+
 # == orbfe_fisheye_rig / orc_fisheye_rig
 FISHEYE_RIG_DTYPE = np.dtype([("cam1", "<f4", 8), ("cam2", "<f4", 8), ("Rlr", "<f4", 9), ("tlr", "<f4", 3),
                               ("precision", "<f4"), ("nlevels", "<i4"), ("level_sigma2", "<f4", 16)])

@@ -355,3 +355,189 @@ def test_oracle_search_for_initialization_vs_python(oracle):
         assert nm == rnm == int((m12 >= 0).sum())
         total += nm
     assert total > 150
+
+
+def _py_search_frame(keys, desc, u_right, occupied, nleft, bounds, scale, mbf, pts, th, direction, check_ori, keyframe=False,
+                     orb_dist=100):
+    """literal restatement of ORBmatcher.cc:1683-1921 (LastFrame form) / :1923-2059 (KeyFrame form) with Frame.cc:405-436,
+    672-751 and ComputeThreeMaxima :2061-2102, numpy float32.  Returns (mvpMapPoints as point indices, nmatches)."""
+    f32 = np.float32
+    n = len(keys)
+    min_x, min_y, max_x, max_y = [f32(v) for v in bounds]
+    gw, gh = f32(f32(64) / f32(max_x - min_x)), f32(f32(48) / f32(max_y - min_y))
+
+    def c_round(v):
+        v = float(v)
+        return int(math.floor(v + 0.5) if v >= 0 else math.ceil(v - 0.5))
+    grids = ({}, {})
+    for i in range(n):
+        px = c_round(f32(f32(keys["x"][i] - min_x) * gw))
+        py = c_round(f32(f32(keys["y"][i] - min_y) * gh))
+        if 0 <= px < 64 and 0 <= py < 48:
+            if i < nleft:
+                grids[0].setdefault((px, py), []).append(i)
+            else:
+                grids[1].setdefault((px, py), []).append(i - nleft)
+
+    def area(x, y, r, min_level, max_level, right):
+        out = []
+        cx0 = max(0, int(math.floor(f32(f32(f32(x - min_x) - r) * gw))))
+        cx1 = min(63, int(math.ceil(f32(f32(f32(x - min_x) + r) * gw))))
+        cy0 = max(0, int(math.floor(f32(f32(f32(y - min_y) - r) * gh))))
+        cy1 = min(47, int(math.ceil(f32(f32(f32(y - min_y) + r) * gh))))
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            return out
+        check = min_level > 0 or max_level >= 0
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for j in grids[1 if right else 0].get((ix, iy), []):
+                    k = keys[nleft + j] if right else keys[j]
+                    if check:
+                        if k["octave"] < min_level:
+                            continue
+                        if max_level >= 0 and k["octave"] > max_level:
+                            continue
+                    if abs(f32(k["x"] - x)) < r and abs(f32(k["y"] - y)) < r:
+                        out.append(j)
+        return out
+    bits = np.unpackbits(desc, axis=1)
+    blocked = np.zeros(n, bool) if occupied is None else np.asarray(occupied).astype(bool).copy()
+    mvp = np.full(n, -1, np.int64)
+    rot_hist = [[] for _ in range(30)]
+    factor = f32(1.0) / f32(30)
+    nmatches = 0
+    stereo_cam = nleft != n
+
+    def levels(o):
+        if keyframe:
+            return o - 1, o + 1
+        return (o, -1) if direction == 1 else ((0, o) if direction == 2 else (o - 1, o + 1))
+
+    def push(angle_src, slot):
+        rot = f32(f32(angle_src) - f32(keys["angle"][slot]))
+        if keyframe and (rot < 0.0 or rot > 360.0):
+            rot = f32(math.fmod(float(rot), 360.0))
+        if rot < 0.0:
+            rot = f32(rot + f32(360.0))
+        b = c_round(f32(rot * factor))
+        if b == 30:
+            b = 0
+        rot_hist[b].append(slot)
+    for ip in range(len(pts)):
+        p = pts[ip]
+        if not (p["flags"] & 1):
+            continue
+        u, v = f32(p["u"]), f32(p["v"])
+        if u < min_x or u > max_x or v < min_y or v > max_y:
+            continue
+        o = int(p["level"])
+        radius = f32(f32(th) * f32(scale[o]))
+        lo, hi = levels(o)
+        cand = area(u, v, radius, lo, hi, False)
+        if not cand:
+            continue
+        mbits = np.unpackbits(p["desc"])
+        blocks = True if keyframe else bool(p["flags"] & 4)
+        bd, bi = 256, -1
+        for j in cand:
+            if blocked[j]:
+                continue
+            if not keyframe and not stereo_cam and u_right is not None and u_right[j] > 0:
+                ur = f32(u - f32(f32(mbf) * f32(p["invz"])))
+                if abs(f32(ur - u_right[j])) > radius:
+                    continue
+            d = int(np.count_nonzero(mbits != bits[j]))
+            if d < bd:
+                bd, bi = d, j
+        if bd <= (orb_dist if keyframe else 100):
+            mvp[bi] = ip
+            blocked[bi] = blocks
+            nmatches += 1
+            if check_ori:
+                push(p["angle"], bi)
+        if stereo_cam and not keyframe:
+            cand = area(f32(p["ur"]), f32(p["vr"]), radius, lo, hi, True)
+            bd, bi = 256, -1
+            for j in cand:
+                if blocked[j + nleft]:
+                    continue
+                d = int(np.count_nonzero(mbits != bits[j + nleft]))
+                if d < bd:
+                    bd, bi = d, j
+            if bd <= 100:
+                mvp[bi + nleft] = ip
+                blocked[bi + nleft] = blocks
+                nmatches += 1
+                if check_ori:
+                    push(p["angle"], bi + nleft)
+    if check_ori:
+        m1 = m2 = m3 = 0
+        i1 = i2 = i3 = -1
+        for i in range(30):
+            s = len(rot_hist[i])
+            if s > m1:
+                m3, m2, m1, i3, i2, i1 = m2, m1, s, i2, i1, i
+            elif s > m2:
+                m3, m2, i3, i2 = m2, s, i2, i
+            elif s > m3:
+                m3, i3 = s, i
+        if m2 < f32(0.1) * f32(m1):
+            i2 = i3 = -1
+        elif m3 < f32(0.1) * f32(m1):
+            i3 = -1
+        for i in range(30):
+            if i not in (i1, i2, i3):
+                for slot in rot_hist[i]:
+                    mvp[slot] = -1
+                    nmatches -= 1
+    return mvp, nmatches
+
+
+def test_oracle_search_by_projection_frame_vs_python(oracle):
+    """mono / rectified frames (mvuRight gate, all three level modes) and stereo-camera frames (right search)."""
+    for seed, th, direction in ((21, 7.0, 0), (22, 15.0, 1), (23, 15.0, 2), (24, 4.0, 0)):
+        img = scenes.make("texture", 320, 240, 6100 + seed)
+        ex = oracle.OracleExtractor(500, 1.2, 8, 20, 7)
+        _, kps, desc = ex(img)
+        n = len(kps)
+        u_right = np.where(scenes.rand_u32(n, seed) % 3 == 0, -1.0, kps["x"] - 7.5).astype(np.float32)
+        occupied = (scenes.rand_u32(n, seed + 5) % 12 == 0).astype(np.uint8)
+        pts = scenes.frame_points(kps, desc, n, None, u_right, 8, 350, seed)
+        ml, mr, owner, nm = oracle.search_by_projection_frame(kps, desc, u_right, occupied, n, (0, 0, 320, 240), ex.scale, 47.9,
+                                                              pts, th=th, direction=direction)
+        ref_owner, ref_nm = _py_search_frame(kps, desc, u_right, occupied, n, (0, 0, 320, 240), ex.scale, 47.9, pts, th,
+                                             direction, True)
+        np.testing.assert_array_equal(owner, ref_owner)
+        assert nm == ref_nm and nm > 60 and (mr == -1).all()
+    # stereo-camera frame: left features then right features
+    imgl = scenes.make("texture", 320, 240, 6130)
+    imgr = scenes.stereo_right(imgl, 6130)
+    ex = oracle.OracleExtractor(400, 1.2, 8, 20, 7)
+    _, kl, dl = ex(imgl)
+    _, kr, dr = ex(imgr)
+    keys, desc, nleft, ltr, rtl = scenes.stereo_camera_frame(kl, dl, kr, dr, 6130)
+    for seed, th, direction, ori in ((31, 7.0, 0, True), (32, 12.0, 1, True), (33, 7.0, 0, False)):
+        pts = scenes.frame_points(keys, desc, nleft, ltr, None, 8, 400, seed)
+        ml, mr, owner, nm = oracle.search_by_projection_frame(keys, desc, None, None, nleft, (0, 0, 320, 240), ex.scale, 0.0, pts,
+                                                              th=th, direction=direction, check_orientation=ori)
+        ref_owner, ref_nm = _py_search_frame(keys, desc, None, None, nleft, (0, 0, 320, 240), ex.scale, 0.0, pts, th, direction,
+                                             ori)
+        np.testing.assert_array_equal(owner, ref_owner)
+        assert nm == ref_nm and (mr >= 0).sum() > 20
+
+
+def test_oracle_search_by_projection_keyframe_vs_python(oracle):
+    for seed, th, dist in ((41, 10.0, 100), (42, 3.0, 64)):
+        img = scenes.make("texture", 320, 240, 6200 + seed)
+        ex = oracle.OracleExtractor(500, 1.2, 8, 20, 7)
+        _, kps, desc = ex(img)
+        n = len(kps)
+        occupied = (scenes.rand_u32(n, seed + 5) % 6 == 0).astype(np.uint8)
+        pts = scenes.frame_points(kps, desc, n, None, None, 8, 350, seed)
+        m, owner, nm = oracle.search_by_projection_keyframe(kps, desc, occupied, (0, 0, 320, 240), ex.scale, pts, th=th,
+                                                            orb_dist=dist)
+        ref_owner, ref_nm = _py_search_frame(kps, desc, None, occupied, n, (0, 0, 320, 240), ex.scale, 0.0, pts, th, 0, True,
+                                             keyframe=True, orb_dist=dist)
+        np.testing.assert_array_equal(owner, ref_owner)
+        assert nm == ref_nm and nm > 40
+        assert (owner[occupied.astype(bool)] == -1).all()    # taken slots are never reassigned
