@@ -448,7 +448,7 @@ static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int str
     bufs.work += (size_t)wsOff * g.outCap;
     bufs.result = resultDst;
     if (timed) cudaEventRecord(ex->ev[1], st);
-    launches += launch_pyramid(g, dImages, n, stride, imageStride, bufs.pyr, ex->xtab, ex->ytab, ex->rsDims[n >= 32 ? 0 : 1], st);
+    launches += launch_pyramid(g, dImages, n, stride, imageStride, bufs.pyr, ex->xtab, ex->ytab, ex->rsDims[n >= 32 ? 0 : 1], ex->rsDims[1], st);
     if (timed) cudaEventRecord(ex->ev[2], st);
     launches += launch_fast(g, bufs.pyr, n, (const FastItem*)ex->dItems.p, ex->nItems, ex->tileBytes, ex->scoreBytes,
                             ex->listBytes, bufs.slots, bufs.cellCount, st);

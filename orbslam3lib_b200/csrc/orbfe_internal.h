@@ -127,7 +127,8 @@ struct ExtractBuffers {
 // per-stage tables (FAST items, blur tiles, octree capacities, kNN) are declared next to their only caller in
 // orbfe_api.cu. ----
 int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size_t imageStride, uint8_t* pyr,
-                   const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims, cudaStream_t st);
+                   const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims,
+                   const ResizeDims* rows16, cudaStream_t st);
 void resize_tile_dims(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int dh, int rpt, int* SP, int* SH);
 int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st);
 int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
