@@ -274,8 +274,8 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(KT_N) : "memory");
 }
 
-// train segments for one large problem: the smallest count (<= 8) whose CTA total fills the resident-CTA waves to
-// >= 95 %, else the best; segments stay >= 16k rows.  ORBFE_KNN_SEGS=n forces n (tests).
+// train segments for one large problem: the smallest count (<= 16) whose CTA total fills the resident-CTA waves to
+// >= 98.5 %, else the best; segments stay >= 8k rows.  ORBFE_KNN_SEGS=n forces n (tests).
 static int kt_pick_segments(long long tiles, long long nt, int resident) {
     static const int forced = [] {    // read once: the environment is not re-scanned per launch
         const char* e = getenv("ORBFE_KNN_SEGS");
@@ -285,12 +285,12 @@ static int kt_pick_segments(long long tiles, long long nt, int resident) {
     if (forced) return forced;
     int best = 1;
     double bestEff = 0;
-    for (int sgs = 1; sgs <= 8; sgs++) {
-        if (sgs > 1 && nt / sgs < 16384) break;
+    for (int sgs = 1; sgs <= 16; sgs++) {    // a CTA's prologue (query tile) is ~0.1 % of a >= 8k-row segment: more segments are free
+        if (sgs > 1 && nt / sgs < 8192) break;
         const long long ctas = tiles * sgs, waves = (ctas + resident - 1) / resident;
         const double eff = (double)ctas / (double)(waves * resident);
         if (eff > bestEff + 1e-9) { bestEff = eff; best = sgs; }
-        if (eff >= 0.95) break;
+        if (eff >= 0.985) break;
     }
     return best;
 }
@@ -339,8 +339,8 @@ int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_
 }
 
 // ---- multi-launch form (orbfe_sharded.cu) -----------------------------------------------------------------------------
-// One nq x nt problem whose train set arrives in `chunks` pieces.  plan: segments per chunk (the smallest count <= 8
-// whose CTA total fills the resident-CTA waves of ONE launch to >= 95 %, else the best), the segment length (a multiple
+// One nq x nt problem whose train set arrives in `chunks` pieces.  plan: segments per chunk (the smallest count <= 16
+// whose CTA total fills the resident-CTA waves of ONE launch to >= 98.5 %, else the best), the segment length (a multiple
 // of KT_N) and the scratch bytes (partial results of every segment + one ticket per query tile; tickets must be zero
 // before the first launch and are zero again after the last).  Chunk c = segments [c spc, (c + 1) spc) = train rows
 // [c spc segLen, (c + 1) spc segLen).
@@ -366,12 +366,12 @@ void knn2_tc_plan(long long nq, long long nt, int chunks, int* segsPerChunk, lon
     const int resident = kt_resident_ctas();
     int best = 1;
     double bestEff = 0;
-    for (int sgs = 1; sgs <= 8; sgs++) {
+    for (int sgs = 1; sgs <= 16; sgs++) {
         if (sgs > 1 && nt / ((long long)chunks * sgs) < 4096) break;
         const long long ctas = tiles * sgs, waves = (ctas + resident - 1) / resident;
         const double eff = (double)ctas / (double)(waves * resident);
         if (eff > bestEff + 1e-9) { bestEff = eff; best = sgs; }
-        if (eff >= 0.95) break;
+        if (eff >= 0.985) break;
     }
     const long long want = (long long)chunks * best;
     long long sl = ((nt + want - 1) / want + KT_N - 1) / KT_N * KT_N;
