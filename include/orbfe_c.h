@@ -106,6 +106,16 @@ int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int width, int heig
 int orbfe_extract_stereo_batch(orbfe_extractor* ex, const uint8_t* images, int npairs, int width, int height, int stride,
                                size_t image_stride, orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* counts,
                                float mb, float mbf, float* u_right, float* depth, unsigned flags);
+/* The batched form of the Lynx wire call (orbslam3_extractFeatures: extraction of both eyes AND the left -> right matcher
+ * in one round trip, dsp/src/orbslam_dsp.cpp:1017-1021): npairs stereo pairs, images interleaved L0, R0, L1, R1, ...;
+ * ORBextractor::operator() on all 2 npairs images (vLappingArea = lap0, lap1) and, per pair, cv::BFMatcher(NORM_HAMMING)
+ * .knnMatch(left descriptors, right descriptors, k = 2) (Frame.cc:45,1227) on the descriptors while they are still in
+ * HBM.  kps / desc / counts / monos as orbfe_extract_batch (2 npairs images); knn_idx / knn_dist: [npairs][cap][2]
+ * (best, second; -1 past the left count or when the right image has fewer than two keypoints).  With host buffers the copies
+ * of stage k - 1 / k + 1 run under the kernels of stage k, the matches included. */
+int orbfe_extract_match_batch(orbfe_extractor* ex, const uint8_t* images, int npairs, int width, int height, int stride,
+                              size_t image_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                              int32_t* counts, int32_t* monos, int32_t* knn_idx, int32_t* knn_dist, unsigned flags);
 /* device time (ms) of the ComputeStereoMatches kernels of the last orbfe_extract_stereo_batch call (0 when the host
  * path was pipelined over sub-chunks and the stages were not timed individually) */
 int orbfe_extractor_stereo_ms(const orbfe_extractor* ex, float* ms);

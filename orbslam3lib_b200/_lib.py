@@ -60,6 +60,7 @@ SYMBOLS = {
     "orbfe_extract": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp]),
     "orbfe_extract_stereo_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _sz, _vp, _vp, _i, _vp, C.c_float, C.c_float, _vp,
                                         _vp, _u]),
+    "orbfe_extract_match_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _sz, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _u]),
     "orbfe_extractor_stereo_ms": (_i, [_vp, _vp]),
     "orbfe_level_size": (_i, [_vp, _i, _vp, _vp]),
     "orbfe_level_read": (_i, [_vp, _i, _i, _i, _vp, _i]),

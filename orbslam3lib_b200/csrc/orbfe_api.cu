@@ -260,6 +260,7 @@ struct orbfe_extractor {
     DevBuf dIn, dKps, dDesc;    // staging for host inputs / outputs
     DevBuf dCounts;             // int32 keypoint counts of the last chunk (orbfe_extractor_device_outputs)
     DevBuf dStereoU, dStereoZ, dStereoSad;    // ComputeStereoMatches outputs / SAD scratch of a chunk (pairs x cap)
+    DevBuf dKnnScratch, dPairCnt;             // orbfe_extract_match_batch: strided kNN results + per-pair counts
     ExtractBuffers bufs{};
 
     // last call (stage outputs for the parity accessors)
@@ -423,16 +424,18 @@ static int reserve_workspace(orbfe_extractor* ex, int chunk) {
 
 // request of orbfe_extract_stereo_batch: run Frame::ComputeStereoMatches after the extraction of every chunk
 struct StereoReq {
-    float mb, mbf;
+    float mb, mbf;    // mb > 0: Frame::ComputeStereoMatches on every pair
     float* uRight;    // npairs x cap (host, or device with ORBFE_OUT_DEVICE)
     float* depth;
+    int32_t* knnIdx = nullptr;    // non-null: left -> right Hamming kNN (k = 2) of every pair, npairs x cap x 2
+    int32_t* knnDist = nullptr;
 };
 
 // run the kernels on `n` images already resident on the device; outputs go to device buffers dKps/dDesc (cap-strided)
 static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int stride, size_t imageStride, int lap0,
                      int lap1, orbfe_keypoint* dKps, uint8_t* dDesc, int cap, ImageResult* resultDst, bool timed,
                      const StereoReq* sr = nullptr, float* dU = nullptr, float* dZ = nullptr, int* dSad = nullptr,
-                     int wsOff = 0, cudaStream_t stOverride = nullptr) {
+                     int wsOff = 0, cudaStream_t stOverride = nullptr, int32_t* dKnn = nullptr, int* dPairCnt = nullptr) {
     const Geom& g = ex->geom;
     cudaStream_t st = stOverride ? stOverride : ex->stream;
     int launches = 0;
@@ -460,7 +463,17 @@ static int run_chunk(orbfe_extractor* ex, const uint8_t* dImages, int n, int str
     launches += launch_pack(g, n, bufs, lap0, lap1, st);
     launches += launch_describe(g, n, bufs, dKps, dDesc, cap, st);
     if (timed) cudaEventRecord(ex->ev[6], st);
-    if (sr) {    // Frame::ComputeStereoMatches on the pairs (2p, 2p + 1) of this chunk, pyramids still in the workspace
+    if (sr && dKnn) {
+        // left -> right kNN of the pairs (2p, 2p + 1): rows of pair p start 2 * cap rows apart in dDesc, so the batched
+        // matcher runs with a row stride of 2 cap (its output has the same stride: [pair][2 cap][2], idx then dist)
+        const int np = n / 2;
+        ORBFE_CUDA(ex, cudaMemsetAsync(dKnn, 0xff, (size_t)np * 8 * cap * 4, st));    // rows past a pair's count: -1
+        ORBFE_CUDA(ex, cudaMemcpy2DAsync(dPairCnt, 4, &resultDst[0].count, 2 * sizeof(ImageResult), 4, np, cudaMemcpyDeviceToDevice, st));
+        ORBFE_CUDA(ex, cudaMemcpy2DAsync(dPairCnt + np, 4, &resultDst[1].count, 2 * sizeof(ImageResult), 4, np, cudaMemcpyDeviceToDevice, st));
+        launches += launch_knn2(dDesc, dPairCnt, 2ll * cap, dDesc + (size_t)cap * 32, dPairCnt + np, 2ll * cap, np, 0, 0, cap, cap,
+                                dKnn, dKnn + (size_t)np * 2 * cap * 2, st);
+    }
+    if (sr && sr->mb > 0) {    // Frame::ComputeStereoMatches on the pairs (2p, 2p + 1) of this chunk, pyramids still in the workspace
         if (timed) cudaEventRecord(ex->evStereo[0], st);
         launches += launch_stereo(g, ex->tables.scale.data(), ex->tables.invScale.data(), bufs.pyr, dKps, dDesc, resultDst,
                                   n / 2, cap, sr->mb, sr->mbf, dU, dZ, dSad, st);
@@ -581,9 +594,11 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
     if (!ex) return ORBFE_ERR_ARG;
     std::lock_guard<std::mutex> lk(ex->mu);
     if (sr) {
-        if (n % 2 != 0 || !sr->uRight || !sr->depth || cap <= 0 || !(sr->mb > 0))
-            return set_err(ex, ORBFE_ERR_ARG, "stereo: need an even image count, output arrays, cap > 0 and mb > 0");
-        if (cap > 65535 || stereo_smem_bytes(cap) > 200 * 1024)
+        const bool wantStereo = sr->mb > 0 || sr->uRight || sr->depth, wantKnn = sr->knnIdx || sr->knnDist;
+        if (n % 2 != 0 || cap <= 0 || (wantStereo && (!sr->uRight || !sr->depth || !(sr->mb > 0))) ||
+            (wantKnn && (!sr->knnIdx || !sr->knnDist)) || (!wantStereo && !wantKnn))
+            return set_err(ex, ORBFE_ERR_ARG, "pairs: need an even image count, cap > 0, and complete output arrays (stereo: mb > 0)");
+        if (wantStereo && (cap > 65535 || stereo_smem_bytes(cap) > 200 * 1024))
             return set_err(ex, ORBFE_ERR_ARG, "stereo: keypoint capacity %d too large for the right-keypoint table", cap);
         ex->stereoMs = 0;
     }
@@ -615,7 +630,12 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
         ORBFE_CUDA(ex, ex->dKps.reserve(std::max<size_t>(16, (size_t)chunk * cap * sizeof(orbfe_keypoint))));
         ORBFE_CUDA(ex, ex->dDesc.reserve(std::max<size_t>(16, (size_t)chunk * cap * 32)));
     }
-    if (sr) {
+    const bool wantStereo = sr && sr->mb > 0, wantKnn = sr && sr->knnIdx;
+    if (wantKnn) {    // [pair][2 cap][2] x (idx, dist) + the per-pair counts
+        ORBFE_CUDA(ex, ex->dKnnScratch.reserve((size_t)(chunk / 2) * 2 * cap * 2 * 4 * 2));
+        ORBFE_CUDA(ex, ex->dPairCnt.reserve((size_t)chunk * 4));
+    }
+    if (wantStereo) {
         ORBFE_CUDA(ex, ex->dStereoSad.reserve((size_t)(chunk / 2) * cap * 4));
         if (!outDev) {
             ORBFE_CUDA(ex, ex->dStereoU.reserve((size_t)(chunk / 2) * cap * 4));
@@ -636,8 +656,21 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
         orbfe_keypoint* dK = outDev ? kps + (size_t)base * cap : (orbfe_keypoint*)ex->dKps.p;
         uint8_t* dD = outDev ? desc + (size_t)base * cap * 32 : (uint8_t*)ex->dDesc.p;
         // stereo outputs of this chunk (pair index = image index / 2)
-        float* dU = !sr ? nullptr : outDev ? sr->uRight + (size_t)(base / 2) * cap : (float*)ex->dStereoU.p;
-        float* dZ = !sr ? nullptr : outDev ? sr->depth + (size_t)(base / 2) * cap : (float*)ex->dStereoZ.p;
+        float* dU = !wantStereo ? nullptr : outDev ? sr->uRight + (size_t)(base / 2) * cap : (float*)ex->dStereoU.p;
+        float* dZ = !wantStereo ? nullptr : outDev ? sr->depth + (size_t)(base / 2) * cap : (float*)ex->dStereoZ.p;
+        int32_t* dKnnAll = wantKnn ? (int32_t*)ex->dKnnScratch.p : nullptr;
+        int* dPairCntAll = wantKnn ? (int*)ex->dPairCnt.p : nullptr;
+        // kNN results of `np` pairs starting at chunk pair p0: the matcher wrote [np][2 cap][2] idx, then the same for dist,
+        // at dKnnAll + p0 * 8 cap; the caller gets packed [pair][cap][2] arrays (strided 2-D copies, any direction)
+        auto knn_out = [&](int p0, int np, cudaStream_t cs) -> cudaError_t {
+            const cudaMemcpyKind kind = outDev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+            const int32_t* sIdx = dKnnAll + (size_t)p0 * 8 * cap;
+            const int32_t* sDist = sIdx + (size_t)np * 4 * cap;
+            const size_t row = (size_t)cap * 8, dstOff = ((size_t)(base / 2) + p0) * cap * 2;
+            cudaError_t e = cudaMemcpy2DAsync(sr->knnIdx + dstOff, row, sIdx, 2 * row, row, np, kind, cs);
+            if (e != cudaSuccess) return e;
+            return cudaMemcpy2DAsync(sr->knnDist + dstOff, row, sDist, 2 * row, row, np, kind, cs);
+        };
         int* dSad = (int*)ex->dStereoSad.p;
         int errFlag = 0;
         const bool contiguous = stride == width && (m == 1 || image_stride == (size_t)width * height);
@@ -651,12 +684,15 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             // 2 * kSub (large stages run the kernels more efficiently), and a short last stage (its copy-out is exposed)
             std::vector<int> sb, sm;    // first image and image count of every stage
             {
-                // The copy-in (PCIe, ~6.5 us per 752x480 image) and the kernels (~7.3 us per image + ~0.2 ms per
-                // stage) run at nearly the same rate, so a stage may only be a little larger than the one before it
-                // or its input lands after the previous stage's kernels have finished: s(k+1) = 1.1 s(k) + 32
-                // (ORBFE_PIPE_SCHED="first,grow%,add,max,tail" overrides; the r1 schedule was 32,200,0,256,64).
+                // The copy-in (PCIe, ~6.5 us per 752x480 image) and the kernels (~7 us per image + ~0.2 ms per stage:
+                // one wave of the serial quadtree CTAs) run at nearly the same rate.  Stages of 32, 48, 72, 108 and then
+                // 128 images alternate between two compute streams with their own workspace halves, so the thin tail of
+                // stage k (quadtree, descriptors) overlaps the wide head of stage k + 1 (pyramid, FAST).  Measured on
+                // 1024 images 752x480 (ms per call, tools/e2e_sched.py): 9.30 with this schedule on two streams, 9.98 on
+                // one stream with s(k+1) = 1.1 s(k) + 32, 10.2 with the r1 schedule (32,200,0,256,64 on one stream).
+                // ORBFE_PIPE_SCHED="first,grow%,add,max,tail" and ORBFE_PIPE_DUAL=0 override.
                 static const std::vector<int> sc = [] {
-                    std::vector<int> v = {24, 110, 32, 384, 32};
+                    std::vector<int> v = {32, 150, 0, 128, 64};
                     if (const char* e = getenv("ORBFE_PIPE_SCHED")) {
                         int a[5];
                         if (sscanf(e, "%d,%d,%d,%d,%d", a, a + 1, a + 2, a + 3, a + 4) == 5 && a[0] >= 2 && a[1] >= 100 && a[3] >= a[0])
@@ -697,7 +733,7 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             // quadtree passes) overlaps the head of stage k + 1
             int maxStage = 0;
             for (int v : sm) maxStage = std::max(maxStage, v);
-            static const int dualEnv = getenv("ORBFE_PIPE_DUAL") ? atoi(getenv("ORBFE_PIPE_DUAL")) : 0;    // measured slower (12.3 vs 11.9 ms): off
+            static const int dualEnv = getenv("ORBFE_PIPE_DUAL") ? atoi(getenv("ORBFE_PIPE_DUAL")) : 1;
             const bool dual = dualEnv && ex->auxStream && 2 * maxStage <= ex->chunkCap;
             if (dual) ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->auxStream, ex->ev[0], 0));
             int lastAux = -1;
@@ -709,14 +745,16 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
                 ORBFE_CUDA(ex, cudaStreamWaitEvent(cs, ex->pipeEv[2 * k], 0));
                 rc = run_chunk(ex, (const uint8_t*)ex->dIn.p + (size_t)b0 * imgBytes, mk, width, imgBytes, lap0, lap1,
                                dK + (size_t)b0 * cap, dD + (size_t)b0 * cap * 32, cap, ex->bufs.result + b0, false, sr,
-                               sr ? dU + (size_t)(b0 / 2) * cap : nullptr, sr ? dZ + (size_t)(b0 / 2) * cap : nullptr,
-                               sr ? dSad + (size_t)(b0 / 2) * cap : nullptr, wsOff, cs);
+                               wantStereo ? dU + (size_t)(b0 / 2) * cap : nullptr, wantStereo ? dZ + (size_t)(b0 / 2) * cap : nullptr,
+                               wantStereo ? dSad + (size_t)(b0 / 2) * cap : nullptr, wsOff, cs,
+                               wantKnn ? dKnnAll + (size_t)(b0 / 2) * 8 * cap : nullptr, wantKnn ? dPairCntAll + b0 : nullptr);
                 if (rc != ORBFE_OK) return rc;
                 ORBFE_CUDA(ex, cudaEventRecord(ex->pipeEv[2 * k + 1], cs));
                 if (k == nsub - 1) ex->lastWsOff = wsOff;
                 if (cap > 0) {
                     ORBFE_CUDA(ex, cudaStreamWaitEvent(ex->outStream, ex->pipeEv[2 * k + 1], 0));
-                    if (sr) {
+                    if (wantKnn) ORBFE_CUDA(ex, knn_out(b0 / 2, mk / 2, ex->outStream));
+                    if (wantStereo) {
                         const size_t po = (size_t)(b0 / 2) * cap, pb = (size_t)(mk / 2) * cap * 4;
                         ORBFE_CUDA(ex, cudaMemcpyAsync(sr->uRight + (size_t)(base / 2) * cap + po, dU + po, pb, cudaMemcpyDeviceToHost, ex->outStream));
                         ORBFE_CUDA(ex, cudaMemcpyAsync(sr->depth + (size_t)(base / 2) * cap + po, dZ + po, pb, cudaMemcpyDeviceToHost, ex->outStream));
@@ -764,9 +802,11 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
                 dStride = width;
                 dImageStride = (size_t)width * height;
             }
-            rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap, ex->bufs.result, true, sr, dU, dZ, dSad);
+            rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap, ex->bufs.result, true, sr, dU, dZ, dSad, 0,
+                           nullptr, dKnnAll, dPairCntAll);
             if (rc != ORBFE_OK) return rc;
-            if (sr && !outDev) {
+            if (wantKnn) ORBFE_CUDA(ex, knn_out(0, m / 2, st));
+            if (wantStereo && !outDev) {
                 ORBFE_CUDA(ex, cudaMemcpyAsync(sr->uRight + (size_t)(base / 2) * cap, dU, (size_t)(m / 2) * cap * 4, cudaMemcpyDeviceToHost, st));
                 ORBFE_CUDA(ex, cudaMemcpyAsync(sr->depth + (size_t)(base / 2) * cap, dZ, (size_t)(m / 2) * cap * 4, cudaMemcpyDeviceToHost, st));
             }
@@ -783,7 +823,7 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
                 float ms = 0;
                 if (cudaEventElapsedTime(&ms, ex->ev[i], ex->ev[i + 1]) == cudaSuccess) ex->stageMs[i] += ms;
             }
-            if (sr) {
+            if (wantStereo) {
                 float ms = 0;
                 if (cudaEventElapsedTime(&ms, ex->evStereo[0], ex->evStereo[1]) == cudaSuccess) ex->stereoMs += ms;
             }
@@ -828,10 +868,23 @@ int orbfe_extract_stereo_batch(orbfe_extractor* ex, const uint8_t* images, int n
                                size_t image_stride, orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* counts,
                                float mb, float mbf, float* u_right, float* depth, unsigned flags) {
     if (npairs < 0 || npairs > (1 << 29)) return ex ? set_err(ex, ORBFE_ERR_ARG, "bad pair count") : ORBFE_ERR_ARG;
-    const StereoReq sr{mb, mbf, u_right, depth};
+    StereoReq sr{mb, mbf, u_right, depth};
+    if (!(mb > 0) || !u_right || !depth) return ex ? set_err(ex, ORBFE_ERR_ARG, "stereo: need output arrays and mb > 0") : ORBFE_ERR_ARG;
     // Frame.cc:142-143: both extractors run with vLappingArea (0, 0)
     return extract_batch_impl(ex, images, 2 * npairs, width, height, stride, image_stride, 0, 0, kps, desc, cap, counts,
                               nullptr, flags, &sr);
+}
+
+int orbfe_extract_match_batch(orbfe_extractor* ex, const uint8_t* images, int npairs, int width, int height, int stride,
+                              size_t image_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                              int32_t* counts, int32_t* monos, int32_t* knn_idx, int32_t* knn_dist, unsigned flags) {
+    if (npairs < 0 || npairs > (1 << 29)) return ex ? set_err(ex, ORBFE_ERR_ARG, "bad pair count") : ORBFE_ERR_ARG;
+    if (!knn_idx || !knn_dist) return ex ? set_err(ex, ORBFE_ERR_ARG, "match: need knn_idx and knn_dist") : ORBFE_ERR_ARG;
+    StereoReq sr{0.f, 0.f, nullptr, nullptr};
+    sr.knnIdx = knn_idx;
+    sr.knnDist = knn_dist;
+    return extract_batch_impl(ex, images, 2 * npairs, width, height, stride, image_stride, lap0, lap1, kps, desc, cap, counts,
+                              monos, flags, &sr);
 }
 
 int orbfe_extractor_stereo_ms(const orbfe_extractor* ex, float* ms) {

@@ -131,6 +131,27 @@ class ORBextractor:
                                                           int(w) * int(h), ptr(kps), ptr(desc), int(cap), ptr(counts),
                                                           float(mb), float(mbf), ptr(u_right), ptr(depth), int(flags)))
 
+    def extract_match_batch(self, pairs, lapping=(0, 0)):
+        """pairs uint8 (npairs, 2, h, w) -> (counts (npairs, 2), monos (npairs, 2), kps (npairs, 2, cap), desc (npairs, 2, cap,
+        32), knn_idx (npairs, cap, 2), knn_dist (npairs, cap, 2)): extraction of both eyes + left -> right kNN per pair in
+        one call (orbfe_extract_match_batch)."""
+        pairs = np.ascontiguousarray(pairs, np.uint8)
+        P, two, h, w = pairs.shape
+        assert two == 2
+        cap = self.max_keypoints
+        kps = np.zeros((P, 2, cap), KP_DTYPE)
+        desc = np.zeros((P, 2, cap, 32), np.uint8)
+        counts, monos = np.zeros((P, 2), np.int32), np.zeros((P, 2), np.int32)
+        idx, dist = np.full((P, cap, 2), -1, np.int32), np.full((P, cap, 2), -1, np.int32)
+        self.extract_match_batch_raw(pairs, P, w, h, kps, desc, cap, counts, monos, idx, dist, lapping=lapping)
+        return counts, monos, kps, desc, idx, dist
+
+    def extract_match_batch_raw(self, images, npairs, w, h, kps, desc, cap, counts, monos, knn_idx, knn_dist, lapping=(0, 0),
+                                flags=0):
+        self._check(_lib.lib().orbfe_extract_match_batch(self._h, ptr(images), int(npairs), int(w), int(h), int(w),
+                                                         int(w) * int(h), int(lapping[0]), int(lapping[1]), ptr(kps), ptr(desc),
+                                                         int(cap), ptr(counts), ptr(monos), ptr(knn_idx), ptr(knn_dist), int(flags)))
+
     def stereo_ms(self):
         ms = C.c_float(0)
         _lib.lib().orbfe_extractor_stereo_ms(self._h, C.byref(ms))

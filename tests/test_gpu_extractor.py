@@ -224,3 +224,41 @@ def test_config_c2_full_batch_properties(oracle):
                 s += int(desc[p, e, :counts[p, e]].astype(np.uint64).sum())
         return s
     assert checksum(0, P) == (P // distinct) * checksum(0, distinct)
+
+
+@pytest.mark.parametrize("npairs,lap", [(3, (0, 0)), (70, (100, 500)), (300, (0, 0))])
+def test_extract_match_batch(oracle, npairs, lap):
+    """orbfe_extract_match_batch: extraction of both eyes + left -> right kNN per pair in one call, through the chunked
+    (3 pairs), and the pipelined two-stream host path (70 / 300 pairs); every pair against the oracle's extraction and kNN."""
+    from orbslam3lib_b200 import scenes
+    w, h, nf = (752, 480, 1200) if npairs <= 70 else (320, 240, 400)
+    base = [scenes.make("texture", w, h, 9600 + k) for k in range(min(npairs, 6))]
+    pairs = np.stack([np.stack([base[k % len(base)], scenes.stereo_right(base[k % len(base)], 9600 + k % len(base))])
+                      for k in range(npairs)])
+    pairs[-1, 1] = 0    # a right image without any keypoint: every match of that pair is -1
+    ex = ORBextractor(nf, 1.2, 8, 20, 7)
+    counts, monos, kps, desc, idx, dist = ex.extract_match_batch(pairs, lapping=lap)
+    cap = ex.max_keypoints
+    refs = {}
+    for p in list(range(min(npairs, len(base)))) + [npairs - 1]:
+        out = []
+        for e in range(2):
+            key = (p % len(base), e) if p != npairs - 1 or e == 0 else ("blank", 1)
+            if key not in refs:
+                refs[key] = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)(pairs[p, e], lap)
+            out.append(refs[key])
+        for e, (mono, rk, rd) in enumerate(out):
+            n = int(counts[p, e])
+            assert n == len(rk) and int(monos[p, e]) == mono
+            np.testing.assert_array_equal(desc[p, e, :n], rd)
+            np.testing.assert_array_equal(kps[p, e, :n]["x"], rk["x"])
+        nl, nr = len(out[0][1]), len(out[1][1])
+        ri, rdist = oracle.knn2_hamming(out[0][2], out[1][2]) if nl else (np.zeros((0, 2), np.int32),) * 2
+        np.testing.assert_array_equal(idx[p, :nl], ri)
+        np.testing.assert_array_equal(dist[p, :nl], rdist)
+        assert (idx[p, nl:] == -1).all() and (dist[p, nl:] == -1).all()
+    assert (idx[npairs - 1] == -1).all()
+    # every other pair repeats one of the checked ones
+    for p in range(len(base), npairs - 1):
+        q = p % len(base)
+        assert np.array_equal(counts[p], counts[q]) and np.array_equal(idx[p], idx[q]) and np.array_equal(dist[p], dist[q])
