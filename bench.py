@@ -677,9 +677,15 @@ def main():
         st["knn"] = mt.last_ms()[0]
         return st
 
+    # e2e: ONE call of the public C ABI per step, host buffers in and out (orbfe_extract_match_batch = the batched form of
+    # the Lynx wire call: both eyes + the left -> right matcher per pair; images interleaved L0, R0, L1, R1, ...)
+    h_pairs = torch.from_numpy(np.ascontiguousarray(np.stack([imgs_np[:P], imgs_np[P:]], 1))).pin_memory()
+
     def step_e2e():
-        # host images in, host keypoints / descriptors / matches out; the matcher reads the descriptors the extractor
-        # left in HBM (orbfe_extractor_device_outputs) instead of uploading them again
+        ex.extract_match_batch_raw(h_pairs, P, W, H, h_kps, h_desc, cap, h_counts, h_monos, h_idx, h_dist)
+
+    def step_e2e_two_calls():
+        # the r1 form: extraction, then the matcher on the descriptors the extractor left in HBM
         ex.extract_batch_raw(h_imgs, n, W, H, h_kps, h_desc, cap, h_counts, h_monos, flags=0)
         _, dd, dc, dn, dcap = ex.device_outputs()
         assert dn == n and dcap == cap
@@ -722,6 +728,13 @@ def main():
         step_e2e()
     ms_e2e, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop()
+    # after the timer: the fused call returns what the two-call form returns (pair p = images p and P + p there)
+    e2e_idx, e2e_cnt = h_idx.numpy().copy(), h_counts.numpy().reshape(P, 2).copy()
+    step_e2e_two_calls()
+    torch.cuda.synchronize()
+    ms_two, _ = timed(step_e2e_two_calls, max(2, args.steps // 2))
+    e2e_same = bool(np.array_equal(e2e_idx, h_idx.numpy()) and np.array_equal(e2e_cnt[:, 0], h_counts.numpy()[:P]) and
+                    np.array_equal(e2e_cnt[:, 1], h_counts.numpy()[P:]))
 
     # the configuration the metric string names (1000 features) beside c2 (1200): same images, device-resident
     nf1000 = None
@@ -786,7 +799,8 @@ def main():
         v = ctypes.c_double(0)
         if _lib.lib().orbfe_ubench_pipe(local, code, ctypes.byref(v)) == 0:
             pipe_peak[name] = v.value
-    stage_kernels = {"pyramid": ["pad_interior_kernel", "pad_frame_kernel", "pad_level0_kernel", "resize_tile_kernel"],
+    stage_kernels = {"pyramid": ["pad_interior_kernel", "pad_frame_kernel", "pad_level0_kernel", "resize_rows_kernel",
+                                 "resize_tile_kernel"],
                      "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"], "octree": ["octree_kernel"],
                      "describe": ["pack_kernel", "describe_kernel"]}
     for k, ks in stage_kernels.items():
@@ -819,7 +833,8 @@ def main():
         pad = ["pad_interior_kernel", "pad_frame_kernel"] if "pad_interior_kernel" in tj else ["pad_level0_kernel"]
         if dom == "pyramid":
             launches_dom = NLEVELS - 1 + len(pad)
-        ks = {"pyramid": pad + ["resize_tile_kernel"], "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"]}[dom]
+        rs = ["resize_rows_kernel"] if "resize_rows_kernel" in tj else ["resize_tile_kernel"]
+        ks = {"pyramid": pad + rs, "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"]}[dom]
         if all(k in tj for k in ks):
             traffic = sum(tj[k] for k in ks) * n / launches_dom
             ip = tall.get("issue_active_pct", {})
@@ -838,6 +853,8 @@ def main():
         "knn_pairs_per_step": pairs_all,
         "keypoints_per_image": float(counts.mean()),
         "e2e": {"value": fps_e2e, "unit": "frames/s", "ms_per_step": ms_e2e / args.steps,
+                "call": "orbfe_extract_match_batch (one call: host images in; keypoints, descriptors, counts and k=2 matches out)",
+                "two_call_ms_per_step": ms_two / max(2, args.steps // 2), "equals_two_call_form": e2e_same,
                 "h2d_bytes_per_step": int(h_imgs.numel()),
                 "d2h_bytes_per_step": int(h_kps.numel() + h_desc.numel() + 2 * n * 4 + h_idx.numel() * 4 + h_dist.numel() * 4)},
         "gpu_launches": launches,
