@@ -230,6 +230,26 @@ using namespace orbfe;
 // ---------------------------------------------------------------------------------------------------------------
 // extractor object
 // ---------------------------------------------------------------------------------------------------------------
+// a captured small-batch call: every pointer / size the graph bakes in
+struct GraphKey {
+    const void* p[14];
+    int i[6];
+    float f[2];
+};
+struct GraphEntry {
+    GraphKey key;
+    cudaGraphExec_t exec;
+};
+static bool host_pinned(const void* p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
 struct orbfe_extractor {
     int device = 0;
     orbfe_params params{};
@@ -261,6 +281,9 @@ struct orbfe_extractor {
     DevBuf dCounts;             // int32 keypoint counts of the last chunk (orbfe_extractor_device_outputs)
     DevBuf dStereoU, dStereoZ, dStereoSad;    // ComputeStereoMatches outputs / SAD scratch of a chunk (pairs x cap)
     DevBuf dKnnScratch, dPairCnt;             // orbfe_extract_match_batch: strided kNN results + per-pair counts
+    std::vector<GraphEntry> graphs;           // CUDA graphs of small host -> host calls, keyed on every baked-in pointer
+    void* hPinned = nullptr;                  // pinned landing zone of the per-image results of a replayed graph
+    int graphLaunchesPerCall = 0;
     ExtractBuffers bufs{};
 
     // last call (stage outputs for the parity accessors)
@@ -531,8 +554,12 @@ int orbfe_extractor_destroy(orbfe_extractor* ex) {
     if (ex->stream) cudaStreamSynchronize(ex->stream);
     DevBuf* bufs[] = {&ex->dItems, &ex->dBlurTiles, &ex->dTaps, &ex->dPyr, &ex->dBlur, &ex->dSlots, &ex->dCellCount,
                       &ex->dLevelKeys, &ex->dLevelCount, &ex->dScratch, &ex->dWork, &ex->dResult, &ex->dErr, &ex->dIn,
-                      &ex->dKps, &ex->dDesc, &ex->dCounts};
+                      &ex->dKps, &ex->dDesc, &ex->dCounts, &ex->dStereoU, &ex->dStereoZ, &ex->dStereoSad, &ex->dKnnScratch,
+                      &ex->dPairCnt};
     for (DevBuf* b : bufs) b->release();
+    for (GraphEntry& g : ex->graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (ex->hPinned) cudaFreeHost(ex->hPinned);
     for (auto& e : ex->ev) if (e) cudaEventDestroy(e);
     for (auto& e : ex->evStereo) if (e) cudaEventDestroy(e);
     for (auto& e : ex->pipeEv) cudaEventDestroy(e);
@@ -787,7 +814,9 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             ex->lastKps = dK + (size_t)sb[nsub - 1] * cap;
             ex->lastDesc = dD + (size_t)sb[nsub - 1] * cap * 32;
         } else {
-            cudaEventRecord(ex->ev[0], st);
+            // everything this chunk puts on the stream, as a function: it is either issued directly (timed per stage) or
+            // captured once into a CUDA graph and replayed (small host -> host calls, see below)
+            auto enqueue = [&](bool timed, ImageResult* resHost, int* errHost) -> int {
             if (!inDev) {
                 // one copy per chunk when the images are contiguous, else one 2-D copy per image
                 if (contiguous) {
@@ -802,7 +831,7 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
                 dStride = width;
                 dImageStride = (size_t)width * height;
             }
-            rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap, ex->bufs.result, true, sr, dU, dZ, dSad, 0,
+            rc = run_chunk(ex, dImages, m, dStride, dImageStride, lap0, lap1, dK, dD, cap, ex->bufs.result, timed, sr, dU, dZ, dSad, 0,
                            nullptr, dKnnAll, dPairCntAll);
             if (rc != ORBFE_OK) return rc;
             if (wantKnn) ORBFE_CUDA(ex, knn_out(0, m / 2, st));
@@ -810,13 +839,77 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
                 ORBFE_CUDA(ex, cudaMemcpyAsync(sr->uRight + (size_t)(base / 2) * cap, dU, (size_t)(m / 2) * cap * 4, cudaMemcpyDeviceToHost, st));
                 ORBFE_CUDA(ex, cudaMemcpyAsync(sr->depth + (size_t)(base / 2) * cap, dZ, (size_t)(m / 2) * cap * 4, cudaMemcpyDeviceToHost, st));
             }
-            ORBFE_CUDA(ex, cudaMemcpyAsync(res.data(), ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
-            ORBFE_CUDA(ex, cudaMemcpyAsync(&errFlag, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
+            ORBFE_CUDA(ex, cudaMemcpyAsync(resHost, ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
+            ORBFE_CUDA(ex, cudaMemcpyAsync(errHost, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
             ORBFE_CUDA(ex, cudaMemcpy2DAsync(ex->dCounts.p, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
             if (!outDev && cap > 0) {
                 ORBFE_CUDA(ex, cudaMemcpyAsync(kps + (size_t)base * cap, dK, (size_t)m * cap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
                 ORBFE_CUDA(ex, cudaMemcpyAsync(desc + (size_t)base * cap * 32, dD, (size_t)m * cap * 32, cudaMemcpyDeviceToHost, st));
             }
+                return ORBFE_OK;
+            };
+            // Small-batch path (BASELINE configs[2]: one stereo pair per call at 90 FPS): the ~18 dependent launches and
+            // copies of a call are captured into a CUDA graph the second time a call with the same buffers and geometry
+            // is seen, and replayed from then on (one cudaGraphLaunch instead of ~18 stream operations; the graph is keyed
+            // on every pointer it bakes in, so a ring of pinned frame buffers gets one graph per slot).  Host buffers must
+            // be pinned (pageable copies cannot be captured); ORBFE_GRAPH=0 turns it off.
+            bool viaGraph = false;
+            static const bool graphsOn = [] { const char* e = getenv("ORBFE_GRAPH"); return !e || atoi(e) != 0; }();
+            if (graphsOn && !inDev && !outDev && contiguous && m == n && m <= 16 && cap > 0 && host_pinned(src) && host_pinned(kps) &&
+                host_pinned(desc) && (!wantKnn || (host_pinned(sr->knnIdx) && host_pinned(sr->knnDist))) &&
+                (!wantStereo || (host_pinned(sr->uRight) && host_pinned(sr->depth)))) {
+                GraphKey key{};
+                key.p[0] = src; key.p[1] = kps; key.p[2] = desc; key.p[3] = ex->dIn.p; key.p[4] = ex->dKps.p; key.p[5] = ex->dDesc.p;
+                key.p[6] = ex->bufs.pyr; key.p[7] = ex->bufs.result; key.p[8] = sr ? (const void*)sr->knnIdx : nullptr;
+                key.p[9] = sr ? (const void*)sr->knnDist : nullptr; key.p[10] = sr ? (const void*)sr->uRight : nullptr;
+                key.p[11] = sr ? (const void*)sr->depth : nullptr; key.p[12] = st; key.p[13] = ex->dKnnScratch.p;
+                key.i[0] = m; key.i[1] = width; key.i[2] = height; key.i[3] = lap0; key.i[4] = lap1; key.i[5] = cap;
+                key.f[0] = sr ? sr->mb : 0.f; key.f[1] = sr ? sr->mbf : 0.f;
+                if (!ex->hPinned) ORBFE_CUDA(ex, cudaHostAlloc(&ex->hPinned, 16 * sizeof(ImageResult) + 16, cudaHostAllocDefault));
+                ImageResult* hRes = (ImageResult*)ex->hPinned;
+                int* hErr = (int*)(hRes + 16);
+                GraphEntry* ge = nullptr;
+                for (GraphEntry& e : ex->graphs)
+                    if (memcmp(&e.key, &key, sizeof(key)) == 0) ge = &e;
+                if (!ge) {    // first sighting: run directly (this also does the one-time uploads), remember the key
+                    if (ex->graphs.size() >= 32) {
+                        if (ex->graphs.front().exec) cudaGraphExecDestroy(ex->graphs.front().exec);
+                        ex->graphs.erase(ex->graphs.begin());
+                    }
+                    ex->graphs.push_back(GraphEntry{key, nullptr});
+                } else {
+                    if (!ge->exec) {
+                        cudaGraph_t gr = nullptr;
+                        ORBFE_CUDA(ex, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                        const int erc = enqueue(false, hRes, hErr);
+                        const cudaError_t ce = cudaStreamEndCapture(st, &gr);
+                        if (erc != ORBFE_OK || ce != cudaSuccess || !gr) {
+                            if (gr) cudaGraphDestroy(gr);
+                            cudaGetLastError();
+                            return erc != ORBFE_OK ? erc : set_err(ex, ORBFE_ERR_CUDA, "CUDA graph capture failed: %s", cudaGetErrorString(ce));
+                        }
+                        const cudaError_t ie = cudaGraphInstantiate(&ge->exec, gr, 0);
+                        cudaGraphDestroy(gr);
+                        if (ie != cudaSuccess) {
+                            ge->exec = nullptr;
+                            return set_err(ex, ORBFE_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ie));
+                        }
+                    }
+                    ORBFE_CUDA(ex, cudaGraphLaunch(ge->exec, st));
+                    ORBFE_CUDA(ex, cudaStreamSynchronize(st));
+                    for (int i = 0; i < m; i++) res[i] = hRes[i];
+                    errFlag = *hErr;
+                    viaGraph = true;
+                    ex->lastLaunches += ex->graphLaunchesPerCall;
+                    g_launches += ex->graphLaunchesPerCall;
+                }
+            }
+            if (!viaGraph) {
+            cudaEventRecord(ex->ev[0], st);
+            const int l0 = ex->lastLaunches;
+            rc = enqueue(true, res.data(), &errFlag);
+            if (rc != ORBFE_OK) return rc;
+            ex->graphLaunchesPerCall = ex->lastLaunches - l0;
             cudaEventRecord(ex->ev[7], st);
             ORBFE_CUDA(ex, cudaStreamSynchronize(st));
             for (int i = 0; i < 7; i++) {
@@ -827,6 +920,7 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
                 float ms = 0;
                 if (cudaEventElapsedTime(&ms, ex->evStereo[0], ex->evStereo[1]) == cudaSuccess) ex->stereoMs += ms;
             }
+            }    // !viaGraph
             ex->lastChunkBase = base;
             ex->lastChunkN = m;
             ex->lastWsOff = 0;

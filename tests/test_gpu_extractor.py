@@ -5,6 +5,7 @@ after distribution, descriptors; angles within 1e-3 degrees."""
 import numpy as np
 import pytest
 
+from orbslam3lib_b200 import KP_DTYPE as KP
 from orbslam3lib_b200 import ORBextractor, scenes
 
 pytestmark = pytest.mark.gpu
@@ -262,3 +263,44 @@ def test_extract_match_batch(oracle, npairs, lap):
     for p in range(len(base), npairs - 1):
         q = p % len(base)
         assert np.array_equal(counts[p], counts[q]) and np.array_equal(idx[p], idx[q]) and np.array_equal(dist[p], dist[q])
+
+
+def test_small_batch_cuda_graph_path(oracle):
+    """BASELINE configs[2] shape: one 640x480 stereo pair per call, 500 features, PINNED host buffers.  The second call with
+    the same buffers captures the call into a CUDA graph, later calls replay it; every call must return the oracle's
+    keypoints, descriptors and matches, also when the images in the (same) buffer change and when a ring of buffers is
+    used (one graph per slot)."""
+    import torch
+    from orbslam3lib_b200 import scenes
+    w, h, nf = 640, 480, 500
+    ex = ORBextractor(nf, 1.2, 8, 20, 7)
+    cap = ex.max_keypoints
+    ring = [torch.zeros((2, h, w), dtype=torch.uint8).pin_memory() for _ in range(3)]
+    kps = torch.zeros((2, cap, 28), dtype=torch.uint8).pin_memory()
+    desc = torch.zeros((2, cap, 32), dtype=torch.uint8).pin_memory()
+    counts = torch.zeros(2, dtype=torch.int32).pin_memory()
+    monos = torch.zeros(2, dtype=torch.int32).pin_memory()
+    idx = torch.zeros((1, cap, 2), dtype=torch.int32).pin_memory()
+    dist = torch.zeros((1, cap, 2), dtype=torch.int32).pin_memory()
+    ref = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+    launches = []
+    for it in range(9):
+        left = scenes.make("texture" if it % 4 else "checker", w, h, 9700 + it)
+        pair = np.stack([left, scenes.stereo_right(left, 9700 + it)])
+        buf = ring[it % 3]
+        buf.copy_(torch.from_numpy(pair))
+        ex.extract_match_batch_raw(buf, 1, w, h, kps, desc, cap, counts, monos, idx, dist, lapping=(0, 0))
+        launches.append(ex.last_launches())
+        exp = [ref(pair[e]) for e in range(2)]
+        k = kps.numpy().view(KP).reshape(2, cap)
+        for e in range(2):
+            mono, rk, rd = exp[e]
+            n = int(counts[e])
+            assert n == len(rk) and int(monos[e]) == mono, (it, e)
+            np.testing.assert_array_equal(desc.numpy()[e, :n], rd)
+            np.testing.assert_array_equal(k[e, :n]["x"], rk["x"])
+            np.testing.assert_array_equal(k[e, :n]["octave"], rk["octave"])
+        ri, rdist = oracle.knn2_hamming(exp[0][2], exp[1][2])
+        np.testing.assert_array_equal(idx.numpy()[0, :len(ri)], ri)
+        np.testing.assert_array_equal(dist.numpy()[0, :len(ri)], rdist)
+    assert min(launches) > 10    # replayed graphs still report the kernels they launch
