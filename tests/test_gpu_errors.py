@@ -79,3 +79,25 @@ def test_bad_constructor_arguments():
     for args in ((-1, 1.2, 8, 20, 7), (500, 1.2, 0, 20, 7), (500, 1.2, 17, 20, 7), (500, 0.9, 8, 20, 7)):
         with pytest.raises((OrbfeError, ValueError)):
             ORBextractor(*args)
+
+
+@pytest.mark.gpu
+def test_two_devices_in_one_process(oracle):
+    """The opt-in for > 48 KiB of dynamic shared memory is a per-device property: extractors and matchers on
+    device 0 AND device 1 of one process, with the configuration whose kernels need the opt-in (nfeatures = 5000: ~87 KiB
+    quadtree; batch of 32: 96 KiB resize tiles).  Needs two GPUs."""
+    from orbslam3lib_b200 import BFMatcher, ORBextractor, _lib, scenes
+    if _lib.lib().orbfe_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    img = scenes.make("texture", 640, 480, 9900)
+    batch = np.stack([img] * 32)
+    ref = oracle.OracleExtractor(5000, 1.2, 8, 20, 7)
+    _, rk, rd = ref(img)
+    for dev in (0, 1, 0):
+        ex = ORBextractor(5000, 1.2, 8, 20, 7, device=dev)
+        counts, monos, kps, desc = ex.extract_batch(batch)
+        assert int(counts[31]) == len(rk)
+        np.testing.assert_array_equal(desc[31, :len(rk)], rd)
+        idx, dist = BFMatcher(device=dev).knnMatch(rd, rd[::-1].copy())
+        ri, rdist = oracle.knn2_hamming(rd, rd[::-1].copy())
+        np.testing.assert_array_equal(idx, ri)
