@@ -212,6 +212,22 @@ int orbfe_search_by_projection_stereo_batch(orbfe_matcher* m, const orbfe_keypoi
                                             int nframes, float th, int far_points, float th_far, float nn_ratio,
                                             int32_t* match_left, int32_t* match_right, int32_t* owner, int32_t* nmatches,
                                             unsigned flags);
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches) (ORBmatcher.cc:224-425), the matcher
+ * of Tracking::TrackReferenceKeyFrame (Tracking.cc:2788) and of relocalisation (Tracking.cc:3709); npairs (key frame, frame)
+ * pairs per call.  The DBoW2::FeatureVector of each side (std::map<NodeId, vector<unsigned>>, computed by the vocabulary on
+ * the CPU: out of scope) is passed as CSR: *_node_ids[pair*node_cap + j] ascending, *_node_start[pair*(node_cap+1) + j] the
+ * offset of node j's features inside *_idx[pair*cap ...] (feature indices in the node's vector order), *_nnodes[pair].
+ * Key frame: desc_kf rows = pKF->mDescriptors, valid_kf[i] = vpMapPointsKF[i] && !isBad(), angle_kf[i] = angle of the keypoint
+ * :330-333 picks (mvKeysUn, or mvKeys / mvKeysRight with two cameras).  Frame: desc_f rows = F.mDescriptors (n_f[pair] of them),
+ * angle_f[slot] = angle of F.mvKeys[slot] or F.mvKeysRight[slot - Nleft] (:337-340, :367-370), nleft_f[pair] = F.Nleft (NULL
+ * or -1: monocular).  matches[pair*cap + i] = index of the key-frame feature whose MapPoint is vpMapPointMatches[i], -1 =
+ * NULL, after the rotation check; nmatches[pair] = the return value.  TH_LOW = 50 (ORBmatcher.cc:36). */
+int orbfe_search_by_bow_batch(orbfe_matcher* m, const uint8_t* desc_kf, const float* angle_kf, const uint8_t* valid_kf,
+                              const int32_t* kf_node_ids, const int32_t* kf_node_start, const int32_t* kf_idx,
+                              const int32_t* kf_nnodes, const uint8_t* desc_f, const float* angle_f, const int32_t* n_f,
+                              const int32_t* nleft_f, const int32_t* f_node_ids, const int32_t* f_node_start,
+                              const int32_t* f_idx, const int32_t* f_nnodes, int cap, int node_cap, int npairs,
+                              float nn_ratio, int check_orientation, int32_t* matches, int32_t* nmatches, unsigned flags);
 /* ---- the per-frame tracking matcher: ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th,
  * bMono) with SearchByProjectionThread and the rotation histogram (ORBmatcher.cc:1683-1921), and
  * ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1923-2059), both with

@@ -1550,6 +1550,108 @@ int orc_search_by_projection_keyframe(const orc_keypoint* keysUn, const uint8_t*
     return nmatches;
 }
 
+// ---- ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches) (ORBmatcher.cc:224-425) ------
+// DBoW2::FeatureVector = std::map<NodeId, vector<unsigned>>: passed as CSR (node ids ascending, start[nnodes + 1], feature
+// indices in each node's vector order).  validKF[i] = pMP && !pMP->isBad() of vpMapPointsKF[i]; angleKF / angleF: the
+// angle of the keypoint the reference picks for that feature (:330-345).  matches[i] = KF feature whose MapPoint ends in
+// vpMapPointMatches[i], -1 = NULL.  The right-camera branch sits INSIDE `if (bestDist1 <= TH_LOW)` and its ratio test is
+// `|| true` (:355-357): both reproduced.
+int orc_search_by_bow(const uint8_t* descKF, const float* angleKF, const uint8_t* validKF, int nKF, const int32_t* kfNodeIds,
+                      const int32_t* kfNodeStart, const int32_t* kfIdx, int kfNodes, const uint8_t* descF,
+                      const float* angleF, int nF, int nleftF, const int32_t* fNodeIds, const int32_t* fNodeStart,
+                      const int32_t* fIdx, int fNodes, float mfNNratio, int checkOrientation, int32_t* matches) {
+    const int TH_LOW = 50, HISTO_LENGTH = 30;
+    (void)nKF;
+    for (int i = 0; i < nF; i++) matches[i] = -1;    // vpMapPointMatches = vector<MapPoint*>(F.N, NULL)
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int KFit = 0, Fit = 0;
+    while (KFit != kfNodes && Fit != fNodes) {
+        if (kfNodeIds[KFit] == fNodeIds[Fit]) {
+            for (int iKF = kfNodeStart[KFit]; iKF < kfNodeStart[KFit + 1]; iKF++) {
+                const unsigned int realIdxKF = (unsigned)kfIdx[iKF];
+                if (!validKF[realIdxKF]) continue;    // !pMP || pMP->isBad()
+                uint64_t a[4];
+                std::memcpy(a, descKF + (size_t)realIdxKF * 32, 32);
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
+                for (int iF = fNodeStart[Fit]; iF < fNodeStart[Fit + 1]; iF++) {
+                    const unsigned int realIdxF = (unsigned)fIdx[iF];
+                    if (matches[realIdxF] >= 0) continue;    // vpMapPointMatches[realIdxF]
+                    uint64_t b[4];
+                    std::memcpy(b, descF + (size_t)realIdxF * 32, 32);
+                    const int dist = hamming256(a, b);
+                    if (nleftF == -1) {
+                        if (dist < bestDist1) {
+                            bestDist2 = bestDist1;
+                            bestDist1 = dist;
+                            bestIdxF = (int)realIdxF;
+                        } else if (dist < bestDist2) {
+                            bestDist2 = dist;
+                        }
+                    } else {
+                        if (int(realIdxF) < nleftF && dist < bestDist1) {
+                            bestDist2 = bestDist1;
+                            bestDist1 = dist;
+                            bestIdxF = (int)realIdxF;
+                        } else if (int(realIdxF) < nleftF && dist < bestDist2) {
+                            bestDist2 = dist;
+                        }
+                        if (int(realIdxF) >= nleftF && dist < bestDist1R) {
+                            bestDist2R = bestDist1R;
+                            bestDist1R = dist;
+                            bestIdxFR = (int)realIdxF;
+                        } else if (int(realIdxF) >= nleftF && dist < bestDist2R) {
+                            bestDist2R = dist;
+                        }
+                    }
+                }
+                auto push = [&](int idxF) {
+                    if (!checkOrientation) return;
+                    float rot = angleKF[realIdxKF] - angleF[idxF];
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(idxF);
+                };
+                if (bestDist1 <= TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        matches[bestIdxF] = (int)realIdxKF;
+                        push(bestIdxF);
+                        nmatches++;
+                    }
+                    if (bestDist1R <= TH_LOW) {
+                        if (static_cast<float>(bestDist1R) < mfNNratio * static_cast<float>(bestDist2R) || true) {
+                            matches[bestIdxFR] = (int)realIdxKF;
+                            push(bestIdxFR);
+                            nmatches++;
+                        }
+                    }
+                }
+            }
+            KFit++;
+            Fit++;
+        } else if (kfNodeIds[KFit] < fNodeIds[Fit]) {
+            KFit = (int)(std::lower_bound(kfNodeIds, kfNodeIds + kfNodes, fNodeIds[Fit]) - kfNodeIds);
+        } else {
+            Fit = (int)(std::lower_bound(fNodeIds, fNodeIds + fNodes, kfNodeIds[KFit]) - fNodeIds);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                matches[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 // ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764) + ComputeThreeMaxima (:2061-2102) ----------------------
 // F1 / F2 are monocular frames (Nleft == -1); the grid is F2's.  vMatchedDistance / vnMatches21 make the loop order
 // dependent (a later keypoint steals a match only with a strictly smaller distance, and matched candidates with a

@@ -153,6 +153,15 @@ int orc_search_by_projection_keyframe(const orc_keypoint* keysUn, const uint8_t*
                                       const orc_frame_point* pts, int npts, float th, int ORBdist, int checkOrientation,
                                       int32_t* match, int32_t* owner);
 
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vpMapPointMatches) (ORBmatcher.cc:224-425).  The DBoW2 feature vectors
+ * arrive as CSR (node ids ascending, start[nnodes + 1], feature indices in vector order); validKF[i] = the key frame's map
+ * point i exists and is not bad; angle*: angle of the keypoint the reference reads for that feature; nleftF = F.Nleft
+ * (-1: monocular).  matches[nF]: key-frame feature whose MapPoint lands in vpMapPointMatches[i] or -1.  Returns nmatches. */
+int orc_search_by_bow(const uint8_t* descKF, const float* angleKF, const uint8_t* validKF, int nKF, const int32_t* kfNodeIds,
+                      const int32_t* kfNodeStart, const int32_t* kfIdx, int kfNodes, const uint8_t* descF,
+                      const float* angleF, int nF, int nleftF, const int32_t* fNodeIds, const int32_t* fNodeStart,
+                      const int32_t* fIdx, int fNodes, float mfNNratio, int checkOrientation, int32_t* matches);
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) for
  * monocular frames.  prevMatchedXY: n1 (x, y) pairs, updated in place (:759-761); vnMatches12: n1 ints. Returns nmatches. */
 int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, const orc_keypoint* keys2,

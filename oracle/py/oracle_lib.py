@@ -391,6 +391,27 @@ def search_by_projection_keyframe(keys_un, desc, occupied, bounds, scale_factors
     return m, owner[:n], int(nm)
 
 
+def search_by_bow(desc_kf, angle_kf, valid_kf, fv_kf, desc_f, angle_f, nleft_f, fv_f, nn_ratio=0.7, check_orientation=True):
+    """ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches) (ORBmatcher.cc:224-425); fv_* = (node_ids, start, idx) CSR.
+    -> (matches int32 (nF,), nmatches)"""
+    dk = np.ascontiguousarray(desc_kf, np.uint8).reshape(-1, 32)
+    df = np.ascontiguousarray(desc_f, np.uint8).reshape(-1, 32)
+    ak, af = np.ascontiguousarray(angle_kf, np.float32), np.ascontiguousarray(angle_f, np.float32)
+    vk = np.ascontiguousarray(valid_kf, np.uint8)
+    a = [np.ascontiguousarray(x, np.int32) for x in fv_kf]
+    b = [np.ascontiguousarray(x, np.int32) for x in fv_f]
+    m = np.empty(max(len(df), 1), np.int32)
+    L = lib()
+    L.orc_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                    C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                    C.c_float, C.c_int, C.c_void_p]
+    L.orc_search_by_bow.restype = C.c_int
+    nm = L.orc_search_by_bow(_p(dk), _p(ak), _p(vk), len(dk), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]), _p(df), _p(af), len(df),
+                             int(nleft_f), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), float(nn_ratio),
+                             int(bool(check_orientation)), _p(m))
+    return m[:len(df)].copy(), int(nm)
+
+
 FISHEYE_RIG_DTYPE = np.dtype([("cam1", "<f4", 8), ("cam2", "<f4", 8), ("Rlr", "<f4", 9), ("tlr", "<f4", 3),
                               ("precision", "<f4"), ("nlevels", "<i4"), ("level_sigma2", "<f4", 16)])
 _EIGEN_HOOK = None

@@ -79,6 +79,7 @@ SYMBOLS = {
     "orbfe_search_by_projection_stereo_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp,
                                                      _i, _i, C.c_float, _i, C.c_float, C.c_float, _vp, _vp, _vp, _vp,
                                                      _u]),
+    "orbfe_search_by_bow_batch": (_i, [_vp] * 16 + [_i, _i, _i, C.c_float, _i, _vp, _vp, _u]),
     "orbfe_search_by_projection_frame_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, C.c_float, _vp,
                                                     _vp, _i, _i, C.c_float, _i, _vp, _vp, _vp, _vp, _u]),
     "orbfe_search_by_projection_keyframe_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _i, C.c_float,

@@ -30,6 +30,12 @@ int launch_blur_tiles(const Geom& g, const uint8_t* pyr, uint8_t* blur, int n, c
 size_t stereo_smem_bytes(int cap);
 size_t search_smem_bytes(int cap);
 size_t search_stereo_smem_bytes(int cap);
+size_t search_bow_smem_bytes(int cap);
+int launch_search_bow(const uint8_t* descKF, const float* angleKF, const uint8_t* validKF, const int* kfIds, const int* kfStart,
+                      const int* kfIdx, const int* kfNodes, const uint8_t* descF, const float* angleF, const int* nF,
+                      const int* nleftF, const int* fIds, const int* fStart, const int* fIdx, const int* fNodes, int cap,
+                      int nodeCap, int npairs, float nnRatio, int checkOrientation, int* matches, int* nMatches,
+                      cudaStream_t st);
 size_t search_frame_smem_bytes(int cap, int ptsCap);
 int launch_search_frame(const float bounds[4], const float* scale, int nlevels, float th, float mbf, int keyframe, int distTh,
                         int checkOrientation, const orbfe_keypoint* keys, const uint8_t* desc, const float* uRight,
@@ -1447,6 +1453,73 @@ int orbfe_search_by_projection_stereo_batch(orbfe_matcher* m, const orbfe_keypoi
             ORBFE_MCUDA(m, cudaMemcpyAsync(match_right, dMR, F * pts_cap * 4, cudaMemcpyDeviceToHost, st));
         }
         if (owner && cap) ORBFE_MCUDA(m, cudaMemcpyAsync(owner, dOwner, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_bow_batch(orbfe_matcher* m, const uint8_t* desc_kf, const float* angle_kf, const uint8_t* valid_kf,
+                              const int32_t* kf_node_ids, const int32_t* kf_node_start, const int32_t* kf_idx,
+                              const int32_t* kf_nnodes, const uint8_t* desc_f, const float* angle_f, const int32_t* n_f,
+                              const int32_t* nleft_f, const int32_t* f_node_ids, const int32_t* f_node_start,
+                              const int32_t* f_idx, const int32_t* f_nnodes, int cap, int node_cap, int npairs,
+                              float nn_ratio, int check_orientation, int32_t* matches, int32_t* nmatches, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (npairs < 0 || cap < 0 || node_cap < 0) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (npairs == 0) return ORBFE_OK;
+    if (!kf_nnodes || !f_nnodes || !n_f || !matches || (cap > 0 && (!desc_kf || !angle_kf || !valid_kf || !kf_idx || !desc_f ||
+                                                                      !angle_f || !f_idx)) ||
+        (node_cap > 0 && (!kf_node_ids || !f_node_ids)) || !kf_node_start || !f_node_start)
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (cap > 65535 || search_bow_smem_bytes(cap) > 200 * 1024) return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large", cap);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)npairs;
+    const void* dIn[13] = {desc_kf, angle_kf, valid_kf, kf_node_ids, kf_node_start, kf_idx, kf_nnodes,
+                           desc_f,  angle_f,  n_f,      f_node_ids,  f_node_start,  f_idx};
+    const size_t inBytes[13] = {F * cap * 32, F * cap * 4, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4,
+                                F * cap * 32, F * cap * 4, F * 4,   F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4};
+    const void* dNleft = nleft_f;
+    const void* dFn = f_nnodes;
+    // 14 staging slots exist (dS[0..13]); the two small count arrays share slot 13
+    if (!inDev) {
+        for (int i = 0; i < 13; i++) {
+            ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(inBytes[i], 16)));
+            if (inBytes[i]) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, dIn[i], inBytes[i], cudaMemcpyHostToDevice, st));
+            dIn[i] = m->dS[i].p;
+        }
+        ORBFE_MCUDA(m, m->dS[13].reserve(std::max<size_t>(F * 8, 16)));
+        ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[13].p, f_nnodes, F * 4, cudaMemcpyHostToDevice, st));
+        dFn = m->dS[13].p;
+        if (nleft_f) {
+            ORBFE_MCUDA(m, cudaMemcpyAsync((char*)m->dS[13].p + F * 4, nleft_f, F * 4, cudaMemcpyHostToDevice, st));
+            dNleft = (char*)m->dS[13].p + F * 4;
+        }
+    }
+    int32_t *dM = matches, *dCount = nmatches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dIdx.reserve(std::max<size_t>(F * cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dDist.reserve(std::max<size_t>(F * 4, 16)));
+        dM = (int32_t*)m->dIdx.p;
+        dCount = (int32_t*)m->dDist.p;
+    }
+    ORBFE_MCUDA(m, cudaMemsetAsync(dM, 0xff, F * cap * 4, st));
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_search_bow((const uint8_t*)dIn[0], (const float*)dIn[1], (const uint8_t*)dIn[2], (const int*)dIn[3],
+                                           (const int*)dIn[4], (const int*)dIn[5], (const int*)dIn[6], (const uint8_t*)dIn[7],
+                                           (const float*)dIn[8], (const int*)dIn[9], (const int*)dNleft, (const int*)dIn[10],
+                                           (const int*)dIn[11], (const int*)dIn[12], (const int*)dFn, cap, node_cap, npairs,
+                                           nn_ratio, check_orientation, dM, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        if (cap) ORBFE_MCUDA(m, cudaMemcpyAsync(matches, dM, F * cap * 4, cudaMemcpyDeviceToHost, st));
         if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
     }
     ORBFE_MCUDA(m, cudaStreamSynchronize(st));

@@ -207,6 +207,36 @@ class ORBmatcher:
             float(th), int(ORBdist), int(self.mbCheckOrientation), ptr(m), ptr(owner), ptr(nm), 0))
         return int(nm[0]), m, owner[:n]
 
+    def SearchByBoW(self, desc_kf, angle_kf, valid_kf, fv_kf, desc_f, angle_f, fv_f, nleft_f=-1):
+        """ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vpMapPointMatches) (ORBmatcher.cc:224-425).  fv_* = the DBoW2
+        feature vector as CSR (node_ids, start, idx); valid_kf[i] = the key frame's MapPoint i exists and is not bad.
+        -> (nmatches, matches int32 (nF,): key-frame feature behind vpMapPointMatches[i] or -1)"""
+        dk = np.ascontiguousarray(desc_kf, np.uint8).reshape(-1, 32)
+        df = np.ascontiguousarray(desc_f, np.uint8).reshape(-1, 32)
+        nk, nf = len(dk), len(df)
+        cap = max(nk, nf, 1)
+        ncap = max(len(fv_kf[0]), len(fv_f[0]), 1)
+
+        def pad(a, n, dt, fill=0):
+            out = np.full((n,) + np.asarray(a).shape[1:], fill, dt)
+            out[:len(a)] = a
+            return out
+        args = [pad(dk, cap, np.uint8), pad(angle_kf, cap, np.float32), pad(valid_kf, cap, np.uint8),
+                pad(fv_kf[0], ncap, np.int32), pad(fv_kf[1], ncap + 1, np.int32), pad(fv_kf[2], cap, np.int32),
+                np.array([len(fv_kf[0])], np.int32), pad(df, cap, np.uint8), pad(angle_f, cap, np.float32),
+                np.array([nf], np.int32), np.array([nleft_f], np.int32), pad(fv_f[0], ncap, np.int32),
+                pad(fv_f[1], ncap + 1, np.int32), pad(fv_f[2], cap, np.int32), np.array([len(fv_f[0])], np.int32)]
+        m, nm = np.full(cap, -1, np.int32), np.zeros(1, np.int32)
+        self.search_by_bow_batch_raw(*args, cap, ncap, 1, m, nm)
+        return int(nm[0]), m[:nf]
+
+    def search_by_bow_batch_raw(self, desc_kf, angle_kf, valid_kf, kf_ids, kf_start, kf_idx, kf_nnodes, desc_f, angle_f, n_f,
+                                nleft_f, f_ids, f_start, f_idx, f_nnodes, cap, node_cap, npairs, matches, nmatches, flags=0):
+        self._bf._check(_lib.lib().orbfe_search_by_bow_batch(
+            self._bf._h, ptr(desc_kf), ptr(angle_kf), ptr(valid_kf), ptr(kf_ids), ptr(kf_start), ptr(kf_idx), ptr(kf_nnodes),
+            ptr(desc_f), ptr(angle_f), ptr(n_f), ptr(nleft_f), ptr(f_ids), ptr(f_start), ptr(f_idx), ptr(f_nnodes), int(cap),
+            int(node_cap), int(npairs), self.mfNNratio, int(self.mbCheckOrientation), ptr(matches), ptr(nmatches), int(flags)))
+
     def SearchForInitialization(self, keys1_un, desc1, keys2_un, desc2, bounds, vbPrevMatched, windowSize=10):
         """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) on
         monocular frames given as arrays; bounds = F2's image bounds.  vbPrevMatched: (n1, 2) float32.

@@ -268,6 +268,21 @@ def frame_points(keys, desc, nleft, ltr, u_right, nlevels, npts, seed, jitter=4.
     return pts
 
 
+def feature_vector(desc, nnodes=96, order_seed=0):
+    """A stand-in for DBoW2's FeatureVector (vocabulary node at levelsup 4 -> indices of the features under it): the node
+    of a descriptor is a function of a few of its bits, so re-observed descriptors with a few flipped bits mostly stay in
+    their node.  Returned as CSR: (node_ids ascending int32, start int32 (len + 1), idx int32) with the features of a node
+    in ascending index order (DBoW2 appends them in feature order)."""
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    node = ((d[:, 0].astype(np.int64) >> 2) * 7 + (d[:, 13].astype(np.int64) >> 5) + order_seed) % nnodes
+    ids = np.unique(node)
+    order = np.argsort(node, kind="stable")
+    counts = np.array([(node == i).sum() for i in ids], np.int64)
+    start = np.zeros(len(ids) + 1, np.int32)
+    start[1:] = np.cumsum(counts)
+    return ids.astype(np.int32), start, order.astype(np.int32)
+
+
 # == orbfe_fisheye_rig / orc_fisheye_rig
 FISHEYE_RIG_DTYPE = np.dtype([("cam1", "<f4", 8), ("cam2", "<f4", 8), ("Rlr", "<f4", 9), ("tlr", "<f4", 3),
                               ("precision", "<f4"), ("nlevels", "<i4"), ("level_sigma2", "<f4", 16)])

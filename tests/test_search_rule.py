@@ -541,3 +541,105 @@ def test_oracle_search_by_projection_keyframe_vs_python(oracle):
         np.testing.assert_array_equal(owner, ref_owner)
         assert nm == ref_nm and nm > 40
         assert (owner[occupied.astype(bool)] == -1).all()    # taken slots are never reassigned
+
+
+def _py_search_bow(dk, ak, vk, fvk, df, af, nleft, fvf, ratio, check_ori):
+    """literal restatement of ORBmatcher.cc:224-425 with std::map feature vectors as dicts."""
+    f32 = np.float32
+    kf = {int(i): [int(x) for x in fvk[2][fvk[1][j]:fvk[1][j + 1]]] for j, i in enumerate(fvk[0])}
+    fr = {int(i): [int(x) for x in fvf[2][fvf[1][j]:fvf[1][j + 1]]] for j, i in enumerate(fvf[0])}
+    bk, bf = np.unpackbits(dk, axis=1), np.unpackbits(df, axis=1)
+    vp = np.full(len(df), -1, np.int64)
+    hist = [[] for _ in range(30)]
+    nm = 0
+
+    def c_round(v):
+        v = float(v)
+        return int(math.floor(v + 0.5) if v >= 0 else math.ceil(v - 0.5))
+
+    def push(ikf, slot):
+        rot = f32(f32(ak[ikf]) - f32(af[slot]))
+        if rot < 0.0:
+            rot = f32(rot + f32(360.0))
+        b = c_round(f32(rot * (f32(1.0) / f32(30))))
+        hist[0 if b == 30 else b].append(slot)
+    for node in sorted(set(kf) & set(fr)):
+        for ikf in kf[node]:
+            if not vk[ikf]:
+                continue
+            b1, i1, b2, b1r, i1r, b2r = 256, -1, 256, 256, -1, 256
+            for jf in fr[node]:
+                if vp[jf] >= 0:
+                    continue
+                d = int(np.count_nonzero(bk[ikf] != bf[jf]))
+                if nleft == -1 or jf < nleft:
+                    if d < b1:
+                        b2, b1, i1 = b1, d, jf
+                    elif d < b2:
+                        b2 = d
+                else:
+                    if d < b1r:
+                        b2r, b1r, i1r = b1r, d, jf
+                    elif d < b2r:
+                        b2r = d
+            if b1 <= 50:
+                if f32(b1) < f32(f32(ratio) * f32(b2)):
+                    vp[i1] = ikf
+                    if check_ori:
+                        push(ikf, i1)
+                    nm += 1
+                if b1r <= 50:
+                    vp[i1r] = ikf
+                    if check_ori:
+                        push(ikf, i1r)
+                    nm += 1
+    if check_ori:
+        m1 = m2 = m3 = 0
+        i1 = i2 = i3 = -1
+        for i in range(30):
+            s = len(hist[i])
+            if s > m1:
+                m3, m2, m1, i3, i2, i1 = m2, m1, s, i2, i1, i
+            elif s > m2:
+                m3, m2, i3, i2 = m2, s, i2, i
+            elif s > m3:
+                m3, i3 = s, i
+        if m2 < f32(0.1) * f32(m1):
+            i2 = i3 = -1
+        elif m3 < f32(0.1) * f32(m1):
+            i3 = -1
+        for i in range(30):
+            if i not in (i1, i2, i3):
+                for slot in hist[i]:
+                    vp[slot] = -1
+                    nm -= 1
+    return vp, nm
+
+
+def bow_case(oracle, seed, w=320, h=240, nf=500, stereo=False):
+    """key frame = the previous frame, frame = the current one (two extractions); for stereo the frame's slots are the left
+    features followed by the right ones."""
+    cur = scenes.make("texture", w, h, seed)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _, kk, dk = ex(scenes.previous_frame(cur, seed))
+    _, kf, df = ex(cur)
+    nleft = -1
+    if stereo:
+        _, kr, dr = ex(scenes.previous_frame(scenes.previous_frame(cur, seed), seed + 11))    # a view close to the key frame's
+        nleft = len(kf)
+        kf, df = np.concatenate([kf, kr]), np.concatenate([df, dr])
+    vk = (scenes.rand_u32(len(kk), seed + 3) % 8 != 0).astype(np.uint8)
+    ak = np.where(scenes.rand_u32(len(kk), seed + 4) % 9 == 0, (kk["angle"] + 97.0) % 360.0, kk["angle"]).astype(np.float32)
+    return dk, ak, vk, scenes.feature_vector(dk), df, kf["angle"].astype(np.float32), nleft, scenes.feature_vector(df)
+
+
+def test_oracle_search_by_bow_vs_python(oracle):
+    for seed, stereo, ratio, ori in ((6301, False, 0.7, True), (6302, False, 0.9, True), (6303, True, 0.7, True),
+                                     (6304, True, 0.9, False)):
+        dk, ak, vk, fvk, df, af, nleft, fvf = bow_case(oracle, seed, stereo=stereo)
+        m, nm = oracle.search_by_bow(dk, ak, vk, fvk, df, af, nleft, fvf, ratio, ori)
+        ref, rnm = _py_search_bow(dk, ak, vk, fvk, df, af, nleft, fvf, ratio, ori)
+        np.testing.assert_array_equal(m, ref)
+        assert nm == rnm and nm > 40
+        if stereo:
+            assert (m[nleft:] >= 0).sum() > 10    # right-camera slots matched through the `|| true` branch
