@@ -270,6 +270,49 @@ int orbfe_search_by_projection_keyframe_batch(orbfe_matcher* m, const orbfe_keyp
                                               const int32_t* npts, int pts_cap, int nframes, float th, int orb_dist,
                                               int check_orientation, int32_t* match, int32_t* owner, int32_t* nmatches,
                                               unsigned flags);
+/* ---- MapPoints projected into a KEY FRAME (loop closing, map merging, local mapping).  One inner loop, five callers:
+ * KeyFrame::GetFeaturesInArea (KeyFrame.cc:706-750: the 64 x 48 grid copied from the Frame, cells ix outer / iy inner, no
+ * level filter), features of level nPredictedLevel - 1 or nPredictedLevel, the first minimum of DescriptorDistance.  A point
+ * is an orbfe_frame_point: u, v = pKF->mpCamera->project(Tcw * p3Dw) (or fx * x + cx by hand, :1527-1528), invz = 1 / z,
+ * level = pMP->PredictScale(dist, pKF), desc = pMP->GetDescriptor(), flags bit 0 = the point passed every gate that needs
+ * the map or the pose (pMP, !isBad(), not already found / not in the key frame, z >= 0, minDistance <= dist <= maxDistance,
+ * PO.dot(Pn) >= 0.5 * dist where the caller has one); KeyFrame::IsInImage (x >= mnMinX && x < mnMaxX ..., :752-755) runs on
+ * the device.  ur, vr, angle are not read.
+ *
+ * ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (ORBmatcher.cc:428-533) and its twin that
+ * also fills vpMatchedKF (:535-647): occupied[slot] = vpMatched[slot] != NULL before the call (nullable); an accepted point
+ * (bestDist <= TH_LOW * ratioHamming, required < 256) takes its slot and later points skip it (order dependence
+ * reproduced).  match[f*pts_cap + i] = bestIdx of point i or -1; owner[f*cap + slot] (nullable) = the point now in
+ * vpMatched[slot] or -1 (a slot that was occupied before the call stays -1); nmatches[f] = the return value. */
+int orbfe_search_by_projection_sim3_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc,
+                                          const uint8_t* occupied, const int32_t* n, int cap, const float bounds[4],
+                                          const float* scale_factors, int nlevels, const orbfe_frame_point* pts,
+                                          const int32_t* npts, int pts_cap, int nframes, float th, float ratio_hamming,
+                                          int32_t* match, int32_t* owner, int32_t* nmatches, unsigned flags);
+/* ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) (ORBmatcher.cc:1155-1345; check_reprojection = 1: the chi-square gate of
+ * :1274-1299 with u_right = mvuRight (nullable = all -1), inv_level_sigma2 = mvInvLevelSigma2, bf = mbf, and the
+ * point's ur = u - bf * invz computed on the device) and ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
+ * (:1347-1462; check_reprojection = 0).  keys = mvKeysUn (Nleft == -1), or mvKeys / mvKeysRight with their descriptor rows
+ * for the left / bRight call of a stereo-camera key frame (add NLeft to the returned index for bRight, :1302).  The search
+ * does not depend on the map mutations of the loop, so every point is independent: best_idx[f*pts_cap + i] = bestIdx when
+ * bestDist <= TH_LOW else -1, best_dist likewise (nullable); the caller applies Replace / AddObservation / AddMapPoint in
+ * point order (:1316-1337, :1443-1457).  ncandidates[f] = number of points with a match = nFused when no point turns bad
+ * inside the loop. */
+int orbfe_fuse_batch(orbfe_matcher* m, const orbfe_keypoint* keys, const uint8_t* desc, const float* u_right, const int32_t* n,
+                     int cap, const float bounds[4], const float* scale_factors, const float* inv_level_sigma2, int nlevels,
+                     float bf, const orbfe_frame_point* pts, const int32_t* npts, int pts_cap, int nframes, float th,
+                     int check_reprojection, int32_t* best_idx, int32_t* best_dist, int32_t* ncandidates, unsigned flags);
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, S12, th) (ORBmatcher.cc:1464-1681).  pts1[f*cap + i1] = the MapPoint of
+ * feature i1 of KF1 projected into KF2 with S21 (flags bit 0 = pMP && !vbAlreadyMatched1[i1] && !isBad() && z >= 0 &&
+ * distance range), pts2[f*cap + i2] the reverse with S12; bounds1 / bounds2 = the image bounds of KF1 / KF2.  Both searches
+ * accept at <= TH_HIGH = 100; matches12[f*cap + i1] = idx2 when vnMatch1[i1] == idx2 and vnMatch2[idx2] == i1 (:1666-1679:
+ * vpMatches12[i1] = vpMapPoints2[idx2]), else -1; nfound[f] = the return value.  match1 / match2 (nullable) receive
+ * vnMatch1 / vnMatch2. */
+int orbfe_search_by_sim3_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un1, const uint8_t* desc1, const int32_t* n1,
+                               const orbfe_keypoint* keys_un2, const uint8_t* desc2, const int32_t* n2, int cap,
+                               const float bounds1[4], const float bounds2[4], const float* scale_factors, int nlevels,
+                               const orbfe_frame_point* pts1, const orbfe_frame_point* pts2, int nframes, float th,
+                               int32_t* matches12, int32_t* match1, int32_t* match2, int32_t* nfound, unsigned flags);
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764, with
  * ComputeThreeMaxima :2061-2102) for monocular frames, nframes independent (F1, F2) pairs, one CTA each.  Pair f:
  * keys1 / desc1 [f*cap, f*cap + n1[f]) = F1.mvKeysUn / mDescriptors, keys2 / desc2 / n2 likewise for F2; bounds =

@@ -1550,6 +1550,228 @@ int orc_search_by_projection_keyframe(const orc_keypoint* keysUn, const uint8_t*
     return nmatches;
 }
 
+// ---- MapPoints projected into a key frame ---------------------------------------------------------------------------------
+// KeyFrame keeps the Frame's grid (KeyFrame.cc ctor: mGrid copied cell by cell from F.mGrid), so it is rebuilt here with
+// Frame::AssignFeaturesToGrid's rule.  KeyFrame::GetFeaturesInArea (KeyFrame.cc:706-750): no level filter, cells ix outer /
+// iy inner, |dx| < r && |dy| < r.  KeyFrame::IsInImage (:752-755).
+namespace {
+struct KFGrid {
+    std::vector<size_t> mGrid[GRID_COLS][GRID_ROWS];
+    float mnMinX, mnMinY, mnMaxX, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+    const orc_keypoint* keys;
+    void build(const orc_keypoint* k, int n, float minX, float minY, float maxX, float maxY) {
+        keys = k;
+        mnMinX = minX; mnMinY = minY; mnMaxX = maxX; mnMaxY = maxY;
+        mfGridElementWidthInv = static_cast<float>(GRID_COLS) / (mnMaxX - mnMinX);
+        mfGridElementHeightInv = static_cast<float>(GRID_ROWS) / (mnMaxY - mnMinY);
+        for (int i = 0; i < GRID_COLS; i++)
+            for (int j = 0; j < GRID_ROWS; j++) mGrid[i][j].clear();
+        for (int i = 0; i < n; i++) {
+            const int posX = (int)std::round((k[i].x - mnMinX) * mfGridElementWidthInv);
+            const int posY = (int)std::round((k[i].y - mnMinY) * mfGridElementHeightInv);
+            if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+            mGrid[posX][posY].push_back(i);
+        }
+    }
+    bool IsInImage(const float& x, const float& y) const { return (x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY); }
+    void GetFeaturesInArea(const float& x, const float& y, const float& r, std::vector<size_t>& vIndices) const {
+        vIndices.clear();
+        float factorX = r;
+        float factorY = r;
+        const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * mfGridElementWidthInv));
+        if (nMinCellX >= GRID_COLS) return;
+        const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * mfGridElementWidthInv));
+        if (nMaxCellX < 0) return;
+        const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * mfGridElementHeightInv));
+        if (nMinCellY >= GRID_ROWS) return;
+        const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * mfGridElementHeightInv));
+        if (nMaxCellY < 0) return;
+        for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+            for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                const std::vector<size_t>& vCell = mGrid[ix][iy];
+                for (size_t j = 0, jend = vCell.size(); j < jend; j++) {
+                    const orc_keypoint& kpUn = keys[vCell[j]];
+                    const float distx = kpUn.x - x;
+                    const float disty = kpUn.y - y;
+                    if (std::fabs(distx) < r && std::fabs(disty) < r) vIndices.push_back(vCell[j]);
+                }
+            }
+    }
+};
+int desc_distance(const uint8_t* a, const uint8_t* b) {
+    uint64_t x[4], y[4];
+    std::memcpy(x, a, 32);
+    std::memcpy(y, b, 32);
+    return hamming256(x, y);
+}
+}    // namespace
+
+int orc_search_by_projection_sim3(const orc_keypoint* keysUn, const uint8_t* desc, const uint8_t* occupied, int n, float mnMinX,
+                                  float mnMinY, float mnMaxX, float mnMaxY, const float* mvScaleFactors,
+                                  const orc_frame_point* pts, int npts, float th, float ratioHamming, int32_t* match,
+                                  int32_t* owner) {
+    const int TH_LOW = 50;
+    static thread_local KFGrid G;
+    G.build(keysUn, n, mnMinX, mnMinY, mnMaxX, mnMaxY);
+    std::vector<uint8_t> vpMatched(n, 0);
+    for (int i = 0; i < n; i++) {
+        vpMatched[i] = occupied ? (occupied[i] != 0) : 0;
+        if (owner) owner[i] = -1;
+    }
+    int nmatches = 0;
+    std::vector<size_t> vIndices;
+    for (int iMP = 0; iMP < npts; iMP++) {
+        match[iMP] = -1;
+        const orc_frame_point& p = pts[iMP];
+        if (!(p.flags & 1)) continue;    // isBad, spAlreadyFound, depth, distance range and viewing angle: the caller's
+        if (!G.IsInImage(p.u, p.v)) continue;
+        const int nPredictedLevel = p.level;
+        const float radius = th * mvScaleFactors[nPredictedLevel];
+        G.GetFeaturesInArea(p.u, p.v, radius, vIndices);
+        if (vIndices.empty()) continue;
+        int bestDist = 256;
+        int bestIdx = -1;
+        for (std::vector<size_t>::const_iterator vit = vIndices.begin(), vend = vIndices.end(); vit != vend; vit++) {
+            const size_t idx = *vit;
+            if (vpMatched[idx]) continue;
+            const int& kpLevel = keysUn[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int dist = desc_distance(p.desc, desc + idx * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx = (int)idx;
+            }
+        }
+        if (bestDist <= TH_LOW * ratioHamming) {
+            vpMatched[bestIdx] = 1;
+            if (owner) owner[bestIdx] = iMP;
+            match[iMP] = bestIdx;
+            nmatches++;
+        }
+    }
+    return nmatches;
+}
+
+int orc_fuse(const orc_keypoint* keys, const uint8_t* desc, const float* uRight, int n, float mnMinX, float mnMinY, float mnMaxX,
+             float mnMaxY, const float* mvScaleFactors, const float* mvInvLevelSigma2, float bf, const orc_frame_point* pts,
+             int npts, float th, int checkReprojection, int32_t* bestIdxOut, int32_t* bestDistOut) {
+    const int TH_LOW = 50;
+    static thread_local KFGrid G;
+    G.build(keys, n, mnMinX, mnMinY, mnMaxX, mnMaxY);
+    int nFused = 0;
+    std::vector<size_t> vIndices;
+    for (int i = 0; i < npts; i++) {
+        bestIdxOut[i] = -1;
+        if (bestDistOut) bestDistOut[i] = -1;
+        const orc_frame_point& p = pts[i];
+        if (!(p.flags & 1)) continue;
+        const float invz = p.invz;
+        const float uv0 = p.u, uv1 = p.v;
+        if (!G.IsInImage(uv0, uv1)) continue;
+        const float ur = uv0 - bf * invz;
+        const int nPredictedLevel = p.level;
+        const float radius = th * mvScaleFactors[nPredictedLevel];
+        G.GetFeaturesInArea(uv0, uv1, radius, vIndices);
+        if (vIndices.empty()) continue;
+        int bestDist = 256;
+        int bestIdx = -1;
+        for (std::vector<size_t>::const_iterator vit = vIndices.begin(), vend = vIndices.end(); vit != vend; vit++) {
+            size_t idx = *vit;
+            const orc_keypoint& kp = keys[idx];
+            const int& kpLevel = kp.octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            if (checkReprojection) {
+                const float mvuRight = uRight ? uRight[idx] : -1.0f;
+                if (mvuRight >= 0) {
+                    const float& kpx = kp.x;
+                    const float& kpy = kp.y;
+                    const float& kpr = mvuRight;
+                    const float ex = uv0 - kpx;
+                    const float ey = uv1 - kpy;
+                    const float er = ur - kpr;
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * mvInvLevelSigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float& kpx = kp.x;
+                    const float& kpy = kp.y;
+                    const float ex = uv0 - kpx;
+                    const float ey = uv1 - kpy;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * mvInvLevelSigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = desc_distance(p.desc, desc + idx * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx = (int)idx;
+            }
+        }
+        if (bestDist <= TH_LOW) {
+            bestIdxOut[i] = bestIdx;
+            if (bestDistOut) bestDistOut[i] = bestDist;
+            nFused++;
+        }
+    }
+    return nFused;
+}
+
+int orc_search_by_sim3(const orc_keypoint* keysUn1, const uint8_t* desc1, int n1, const orc_keypoint* keysUn2,
+                       const uint8_t* desc2, int n2, const float* bounds1, const float* bounds2, const float* mvScaleFactors,
+                       const orc_frame_point* pts1, const orc_frame_point* pts2, float th, int32_t* matches12,
+                       int32_t* vnMatch1Out, int32_t* vnMatch2Out) {
+    const int TH_HIGH = 100;
+    static thread_local KFGrid G1, G2;
+    G1.build(keysUn1, n1, bounds1[0], bounds1[1], bounds1[2], bounds1[3]);
+    G2.build(keysUn2, n2, bounds2[0], bounds2[1], bounds2[2], bounds2[3]);
+    std::vector<int> vnMatch1(n1, -1);
+    std::vector<int> vnMatch2(n2, -1);
+    std::vector<size_t> vIndices;
+    // one direction of :1504-1583 / :1585-1664
+    auto search = [&](const KFGrid& G, const orc_keypoint* keys, const uint8_t* desc, const orc_frame_point* pts, int npts,
+                      std::vector<int>& vnMatch) {
+        for (int i = 0; i < npts; i++) {
+            const orc_frame_point& p = pts[i];
+            if (!(p.flags & 1)) continue;
+            const float u = p.u, v = p.v;
+            if (!G.IsInImage(u, v)) continue;
+            const int nPredictedLevel = p.level;
+            const float radius = th * mvScaleFactors[nPredictedLevel];
+            G.GetFeaturesInArea(u, v, radius, vIndices);
+            if (vIndices.empty()) continue;
+            int bestDist = INT_MAX;
+            int bestIdx = -1;
+            for (std::vector<size_t>::const_iterator vit = vIndices.begin(), vend = vIndices.end(); vit != vend; vit++) {
+                const size_t idx = *vit;
+                const orc_keypoint& kp = keys[idx];
+                if (kp.octave < nPredictedLevel - 1 || kp.octave > nPredictedLevel) continue;
+                const int dist = desc_distance(p.desc, desc + idx * 32);
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestIdx = (int)idx;
+                }
+            }
+            if (bestDist <= TH_HIGH) vnMatch[i] = bestIdx;
+        }
+    };
+    search(G2, keysUn2, desc2, pts1, n1, vnMatch1);
+    search(G1, keysUn1, desc1, pts2, n2, vnMatch2);
+    int nFound = 0;
+    for (int i1 = 0; i1 < n1; i1++) {
+        matches12[i1] = -1;
+        int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) {
+                matches12[i1] = idx2;
+                nFound++;
+            }
+        }
+    }
+    if (vnMatch1Out) std::copy(vnMatch1.begin(), vnMatch1.end(), vnMatch1Out);
+    if (vnMatch2Out) std::copy(vnMatch2.begin(), vnMatch2.end(), vnMatch2Out);
+    return nFound;
+}
+
 // ---- ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches) (ORBmatcher.cc:224-425) ------
 // DBoW2::FeatureVector = std::map<NodeId, vector<unsigned>>: passed as CSR (node ids ascending, start[nnodes + 1], feature
 // indices in each node's vector order).  validKF[i] = pMP && !pMP->isBad() of vpMapPointsKF[i]; angleKF / angleF: the

@@ -153,6 +153,30 @@ int orc_search_by_projection_keyframe(const orc_keypoint* keysUn, const uint8_t*
                                       const orc_frame_point* pts, int npts, float th, int ORBdist, int checkOrientation,
                                       int32_t* match, int32_t* owner);
 
+/* ---- MapPoints projected into a key frame.  KeyFrame::GetFeaturesInArea (KeyFrame.cc:706-750) + KeyFrame::IsInImage (:752-755).
+ * A point = orc_frame_point (u, v, invz, level = nPredictedLevel, flags bit 0 = it reaches the projection, desc).
+ * ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (ORBmatcher.cc:428-533; :535-647 is the same
+ * loop).  occupied[i] = vpMatched[i] != NULL before the call; match[npts]; owner[n] = point placed in vpMatched[i] by this call
+ * or -1.  Returns nmatches. */
+int orc_search_by_projection_sim3(const orc_keypoint* keysUn, const uint8_t* desc, const uint8_t* occupied, int n, float mnMinX,
+                                  float mnMinY, float mnMaxX, float mnMaxY, const float* mvScaleFactors,
+                                  const orc_frame_point* pts, int npts, float th, float ratioHamming, int32_t* match,
+                                  int32_t* owner);
+/* The search of ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) (ORBmatcher.cc:1155-1345, checkReprojection = 1) and of
+ * ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1347-1462, checkReprojection = 0) without the map mutations:
+ * bestIdx[i] = the feature the loop body reaches `if(bestDist<=TH_LOW)` with, else -1; bestDist likewise.  uRight = mvuRight
+ * (NULL = all -1).  Returns the number of points with a match. */
+int orc_fuse(const orc_keypoint* keys, const uint8_t* desc, const float* uRight, int n, float mnMinX, float mnMinY, float mnMaxX,
+             float mnMaxY, const float* mvScaleFactors, const float* mvInvLevelSigma2, float bf, const orc_frame_point* pts,
+             int npts, float th, int checkReprojection, int32_t* bestIdx, int32_t* bestDist);
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, S12, th) (ORBmatcher.cc:1464-1681): pts1[n1] = KF1's MapPoints in KF2,
+ * pts2[n2] = KF2's in KF1; bounds1 / bounds2 = mnMinX, mnMinY, mnMaxX, mnMaxY of KF1 / KF2.  matches12[n1] = idx2 or -1;
+ * vnMatch1[n1] / vnMatch2[n2] nullable.  Returns nFound. */
+int orc_search_by_sim3(const orc_keypoint* keysUn1, const uint8_t* desc1, int n1, const orc_keypoint* keysUn2,
+                       const uint8_t* desc2, int n2, const float* bounds1, const float* bounds2, const float* mvScaleFactors,
+                       const orc_frame_point* pts1, const orc_frame_point* pts2, float th, int32_t* matches12,
+                       int32_t* vnMatch1, int32_t* vnMatch2);
+
 /* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vpMapPointMatches) (ORBmatcher.cc:224-425).  The DBoW2 feature vectors
  * arrive as CSR (node ids ascending, start[nnodes + 1], feature indices in vector order); validKF[i] = the key frame's map
  * point i exists and is not bad; angle*: angle of the keypoint the reference reads for that feature; nleftF = F.Nleft

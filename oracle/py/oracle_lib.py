@@ -391,6 +391,67 @@ def search_by_projection_keyframe(keys_un, desc, occupied, bounds, scale_factors
     return m, owner[:n], int(nm)
 
 
+def search_by_projection_sim3(keys_un, desc, occupied, bounds, scale_factors, pts, th=10.0, ratio_hamming=1.0):
+    """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (ORBmatcher.cc:428-533, :535-647).
+    -> (match, owner, nmatches)"""
+    k = np.ascontiguousarray(keys_un, KP_DTYPE)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = k.shape[0]
+    oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    p = np.ascontiguousarray(pts, FRAME_POINT_DTYPE)
+    m, owner = np.empty(max(p.shape[0], 1), np.int32), np.empty(max(n, 1), np.int32)
+    L = lib()
+    L.orc_search_by_projection_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float,
+                                                C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p,
+                                                C.c_void_p]
+    L.orc_search_by_projection_sim3.restype = C.c_int
+    nm = L.orc_search_by_projection_sim3(_p(k), _p(d), None if oc is None else _p(oc), n, float(bounds[0]), float(bounds[1]),
+                                         float(bounds[2]), float(bounds[3]), _p(sf), _p(p), p.shape[0], float(th),
+                                         float(ratio_hamming), _p(m), _p(owner))
+    return m[:p.shape[0]], owner[:n], int(nm)
+
+
+def fuse(keys, desc, u_right, bounds, scale_factors, inv_level_sigma2, bf, pts, th=3.0, check_reprojection=True):
+    """The search of ORBmatcher::Fuse (ORBmatcher.cc:1155-1345 / :1347-1462).  -> (best_idx, best_dist, count)"""
+    k = np.ascontiguousarray(keys, KP_DTYPE)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = k.shape[0]
+    ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    iv = np.ascontiguousarray(inv_level_sigma2, np.float32)
+    p = np.ascontiguousarray(pts, FRAME_POINT_DTYPE)
+    bi, bd = np.empty(max(p.shape[0], 1), np.int32), np.empty(max(p.shape[0], 1), np.int32)
+    L = lib()
+    L.orc_fuse.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p,
+                           C.c_void_p, C.c_float, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+    L.orc_fuse.restype = C.c_int
+    nf = L.orc_fuse(_p(k), _p(d), None if ur is None else _p(ur), n, float(bounds[0]), float(bounds[1]), float(bounds[2]),
+                    float(bounds[3]), _p(sf), _p(iv), float(bf), _p(p), p.shape[0], float(th), int(bool(check_reprojection)),
+                    _p(bi), _p(bd))
+    return bi[:p.shape[0]], bd[:p.shape[0]], int(nf)
+
+
+def search_by_sim3(keys_un1, desc1, keys_un2, desc2, bounds1, bounds2, scale_factors, pts1, pts2, th=7.5):
+    """ORBmatcher::SearchBySim3 (ORBmatcher.cc:1464-1681).  -> (matches12, vnMatch1, vnMatch2, nFound)"""
+    k1, k2 = np.ascontiguousarray(keys_un1, KP_DTYPE), np.ascontiguousarray(keys_un2, KP_DTYPE)
+    d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    n1, n2 = k1.shape[0], k2.shape[0]
+    b1, b2 = np.ascontiguousarray(bounds1, np.float32), np.ascontiguousarray(bounds2, np.float32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    p1, p2 = np.ascontiguousarray(pts1, FRAME_POINT_DTYPE), np.ascontiguousarray(pts2, FRAME_POINT_DTYPE)
+    assert p1.shape[0] == n1 and p2.shape[0] == n2
+    m12, v1, v2 = np.empty(max(n1, 1), np.int32), np.empty(max(n1, 1), np.int32), np.empty(max(n2, 1), np.int32)
+    L = lib()
+    L.orc_search_by_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.orc_search_by_sim3.restype = C.c_int
+    nf = L.orc_search_by_sim3(_p(k1), _p(d1), n1, _p(k2), _p(d2), n2, _p(b1), _p(b2), _p(sf), _p(p1), _p(p2), float(th),
+                              _p(m12), _p(v1), _p(v2))
+    return m12[:n1], v1[:n1], v2[:n2], int(nf)
+
+
 def search_by_bow(desc_kf, angle_kf, valid_kf, fv_kf, desc_f, angle_f, nleft_f, fv_f, nn_ratio=0.7, check_orientation=True):
     """ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches) (ORBmatcher.cc:224-425); fv_* = (node_ids, start, idx) CSR.
     -> (matches int32 (nF,), nmatches)"""

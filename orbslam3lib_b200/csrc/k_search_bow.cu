@@ -40,6 +40,33 @@ __device__ __forceinline__ void sb_merge(unsigned& k1, int& d2) {
     }
 }
 
+// ComputeThreeMaxima (ORBmatcher.cc:2061-2102) on the bin counts
+__device__ void sb_three_maxima(const int* hist, int* ind) {
+    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+    for (int i = 0; i < SB_HISTO; i++) {
+        const int sz = hist[i];
+        if (sz > max1) {
+            max3 = max2; max2 = max1; max1 = sz;
+            ind3 = ind2; ind2 = ind1; ind1 = i;
+        } else if (sz > max2) {
+            max3 = max2; max2 = sz;
+            ind3 = ind2; ind2 = i;
+        } else if (sz > max3) {
+            max3 = sz;
+            ind3 = i;
+        }
+    }
+    if ((float)max2 < 0.1f * (float)max1) {
+        ind2 = -1;
+        ind3 = -1;
+    } else if ((float)max3 < 0.1f * (float)max1) {
+        ind3 = -1;
+    }
+    ind[0] = ind1;
+    ind[1] = ind2;
+    ind[2] = ind3;
+}
+
 // grid: npairs; block SB_THREADS; dynamic shared memory: cap bytes (histogram bin per frame slot)
 __global__ void __launch_bounds__(SB_THREADS) search_bow_kernel(
     const __grid_constant__ BowParams P, const uint8_t* __restrict__ descKFAll, const float* __restrict__ angleKFAll,
@@ -143,34 +170,258 @@ __global__ void __launch_bounds__(SB_THREADS) search_bow_kernel(
     }
     __syncthreads();
     if (P.checkOrientation) {
-        if (tid == 0) {    // ComputeThreeMaxima (ORBmatcher.cc:2061-2102)
-            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
-            for (int i = 0; i < SB_HISTO; i++) {
-                const int sz = hist[i];
-                if (sz > max1) {
-                    max3 = max2; max2 = max1; max1 = sz;
-                    ind3 = ind2; ind2 = ind1; ind1 = i;
-                } else if (sz > max2) {
-                    max3 = max2; max2 = sz;
-                    ind3 = ind2; ind2 = i;
-                } else if (sz > max3) {
-                    max3 = sz;
-                    ind3 = i;
-                }
-            }
-            if ((float)max2 < 0.1f * (float)max1) {
-                ind2 = -1;
-                ind3 = -1;
-            } else if ((float)max3 < 0.1f * (float)max1) {
-                ind3 = -1;
-            }
-            sInd[0] = ind1;
-            sInd[1] = ind2;
-            sInd[2] = ind3;
-        }
+        if (tid == 0) sb_three_maxima(hist, sInd);
         __syncthreads();
         int removed = 0;
         for (int i = tid; i < n; i += SB_THREADS) {
+            const int b = binOf[i];
+            if (b != 0xff && b != sInd[0] && b != sInd[1] && b != sInd[2]) {
+                matches[i] = -1;
+                removed++;
+            }
+        }
+        if (removed) atomicSub(&sCount, removed);
+        __syncthreads();
+    }
+    if (tid == 0 && nMatches) nMatches[f] = sCount;
+}
+
+// ---- ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (ORBmatcher.cc:766-906) --------
+// Loop detection / relocalisation between key frames.  Same node merge; inside a common node every KF1 feature with a good
+// MapPoint looks at the KF2 features of the node that have a good MapPoint and are not in vbMatched2; best / second-best
+// distance, accepted with bestDist1 < TH_LOW (strict) and the ratio test; the accepted KF2 feature enters vbMatched2.  The
+// histogram stores idx1, the losing bins clear vpMatches12[idx1].  validN[i] = MapPoint i exists, is not bad, and (stereo-
+// camera key frames) i < mvKeysUn.size() (:802-804, :821-823).
+// grid: npairs; block SB_THREADS; dynamic shared memory: 2 * cap bytes (bin per KF1 feature, vbMatched2)
+__global__ void __launch_bounds__(SB_THREADS) search_bow_kf_kernel(
+    const __grid_constant__ BowParams P, const uint8_t* __restrict__ desc1All, const float* __restrict__ angle1All,
+    const uint8_t* __restrict__ valid1All, const int* __restrict__ ids1All, const int* __restrict__ start1All,
+    const int* __restrict__ idx1All, const int* __restrict__ nodes1, const uint8_t* __restrict__ desc2All,
+    const float* __restrict__ angle2All, const uint8_t* __restrict__ valid2All, const int* __restrict__ ids2All,
+    const int* __restrict__ start2All, const int* __restrict__ idx2All, const int* __restrict__ nodes2,
+    int* __restrict__ matchesAll, int* __restrict__ nMatches) {
+    extern __shared__ __align__(16) uint8_t binOf[];    // cap entries, 0xff = no histogram entry
+    volatile uint8_t* matched2 = binOf + ((P.cap + 15) & ~15);
+    __shared__ int hist[32];
+    __shared__ int sCount, sInd[3];
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint8_t* desc1 = desc1All + (size_t)f * P.cap * 32;
+    const float* angle1 = angle1All + (size_t)f * P.cap;
+    const uint8_t* valid1 = valid1All + (size_t)f * P.cap;
+    const int* ids1 = ids1All + (size_t)f * P.nodeCap;
+    const int* start1 = start1All + (size_t)f * (P.nodeCap + 1);
+    const int* idx1 = idx1All + (size_t)f * P.cap;
+    const uint8_t* desc2 = desc2All + (size_t)f * P.cap * 32;
+    const float* angle2 = angle2All + (size_t)f * P.cap;
+    const uint8_t* valid2 = valid2All + (size_t)f * P.cap;
+    const int* ids2 = ids2All + (size_t)f * P.nodeCap;
+    const int* start2 = start2All + (size_t)f * (P.nodeCap + 1);
+    const int* idx2 = idx2All + (size_t)f * P.cap;
+    int* matches = matchesAll + (size_t)f * P.cap;
+    const int nk = min(nodes1[f], P.nodeCap), nfn = min(nodes2[f], P.nodeCap);
+
+    for (int i = tid; i < P.cap; i += SB_THREADS) {
+        binOf[i] = 0xffu;
+        matched2[i] = 0;
+        matches[i] = -1;    // vpMatches12 = vector<MapPoint*>(vpMapPoints1.size(), NULL)
+    }
+    if (tid < 32) hist[tid] = 0;
+    if (tid == 0) sCount = 0;
+    __syncthreads();
+
+    for (int jn = warp; jn < nk; jn += SB_WARPS) {
+        const int id = ids1[jn];
+        int lo = 0, hi = nfn;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (ids2[mid] < id) lo = mid + 1; else hi = mid;
+        }
+        if (lo >= nfn || ids2[lo] != id) continue;
+        const int fs = start2[lo], fe = start2[lo + 1];
+        for (int i1 = start1[jn]; i1 < start1[jn + 1]; i1++) {
+            const int r1 = idx1[i1];
+            if (r1 < 0 || r1 >= P.cap || !valid1[r1]) continue;
+            const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(desc1 + (size_t)r1 * 32));
+            const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(desc1 + (size_t)r1 * 32) + 1);
+            constexpr unsigned NONE = 256u << 16;
+            unsigned k1 = NONE;
+            int d2 = 256;
+            for (int t = fs + lane; t < fe; t += 32) {
+                const int r2 = idx2[t];
+                if (r2 < 0 || r2 >= P.cap || matched2[r2] || !valid2[r2]) continue;
+                const uint4 b0 = __ldg(reinterpret_cast<const uint4*>(desc2 + (size_t)r2 * 32));
+                const uint4 b1 = __ldg(reinterpret_cast<const uint4*>(desc2 + (size_t)r2 * 32) + 1);
+                const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                              __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+                const unsigned key = ((unsigned)d << 16) | (unsigned)(t - fs);
+                if (key < k1) { d2 = (int)(k1 >> 16); k1 = key; } else d2 = min(d2, d);
+            }
+            sb_merge(k1, d2);
+            const int bestDist1 = (int)(k1 >> 16);
+            if (lane == 0 && bestDist1 < SB_TH_LOW && (float)bestDist1 < P.nnRatio * (float)d2) {
+                const int best2 = idx2[fs + (int)(k1 & 0xffffu)];
+                matches[r1] = best2;
+                matched2[best2] = 1;
+                if (P.checkOrientation) {
+                    float rot = angle1[r1] - angle2[best2];
+                    if (rot < 0.0f) rot += 360.0f;
+                    int bin = (int)roundf(rot * (1.0f / SB_HISTO));
+                    if (bin == SB_HISTO) bin = 0;
+                    bin = min(max(bin, 0), SB_HISTO - 1);
+                    binOf[r1] = (uint8_t)bin;
+                    atomicAdd(&hist[bin], 1);
+                }
+                atomicAdd(&sCount, 1);
+            }
+            __syncwarp();    // the next KF1 feature of the node sees vbMatched2
+        }
+    }
+    __syncthreads();
+    if (P.checkOrientation) {
+        if (tid == 0) sb_three_maxima(hist, sInd);
+        __syncthreads();
+        int removed = 0;
+        for (int i = tid; i < P.cap; i += SB_THREADS) {
+            const int b = binOf[i];
+            if (b != 0xff && b != sInd[0] && b != sInd[1] && b != sInd[2]) {
+                matches[i] = -1;
+                removed++;
+            }
+        }
+        if (removed) atomicSub(&sCount, removed);
+        __syncthreads();
+    }
+    if (tid == 0 && nMatches) nMatches[f] = sCount;
+}
+
+// ---- ORBmatcher::SearchForTriangulation(pKF1, pKF2, vMatchedPairs, bOnlyStereo, bCoarse) (ORBmatcher.cc:908-1153) -----------
+// Local mapping: matches between the features of two key frames that have NO MapPoint yet.  Node merge as above; inside a
+// common node a KF1 feature looks at the KF2 features of the node, keeps dist <= TH_LOW && dist <= bestDist (the LAST of
+// equal minima wins), skips features too close to the epipole (:1000-1008, only when neither side has a stereo measurement)
+// and applies the epipolar constraint unless bCoarse (:1044; Pinhole::epipolarConstrain, Pinhole.cpp:102-124, with F12 from
+// the caller).  vbMatched2 is never set in the reference, so the KF1 features are independent.  Rotation histogram on idx1.
+// freeN[i] = feature i has no MapPoint (and, with bOnlyStereo, has a stereo measurement); stereoN[i] = !mpCamera2 && mvuRight[i] >= 0.
+struct TriParams {
+    int cap, nodeCap;
+    int coarse, checkOrientation;
+    float scale[ORBFE_MAX_LEVELS], sigma2[ORBFE_MAX_LEVELS];
+};
+
+__device__ __forceinline__ unsigned sb_min_u32(unsigned v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// grid: npairs; block SB_THREADS; dynamic shared memory: cap bytes (bin per KF1 feature)
+__global__ void __launch_bounds__(SB_THREADS) search_triangulation_kernel(
+    const __grid_constant__ TriParams P, const orbfe_keypoint* __restrict__ keys1All, const uint8_t* __restrict__ desc1All,
+    const uint8_t* __restrict__ free1All, const uint8_t* __restrict__ stereo1All, const int* __restrict__ ids1All,
+    const int* __restrict__ start1All, const int* __restrict__ idx1All, const int* __restrict__ nodes1,
+    const orbfe_keypoint* __restrict__ keys2All, const uint8_t* __restrict__ desc2All, const uint8_t* __restrict__ free2All,
+    const uint8_t* __restrict__ stereo2All, const int* __restrict__ ids2All, const int* __restrict__ start2All,
+    const int* __restrict__ idx2All, const int* __restrict__ nodes2, const float* __restrict__ F12All,
+    const float* __restrict__ epAll, int* __restrict__ matchesAll, int* __restrict__ nMatches) {
+    extern __shared__ __align__(16) uint8_t binOf[];
+    __shared__ int hist[32];
+    __shared__ int sCount, sInd[3];
+    __shared__ float sF[9], sEp[2];
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const orbfe_keypoint* keys1 = keys1All + (size_t)f * P.cap;
+    const uint8_t* desc1 = desc1All + (size_t)f * P.cap * 32;
+    const uint8_t* free1 = free1All + (size_t)f * P.cap;
+    const uint8_t* stereo1 = stereo1All ? stereo1All + (size_t)f * P.cap : nullptr;
+    const int* ids1 = ids1All + (size_t)f * P.nodeCap;
+    const int* start1 = start1All + (size_t)f * (P.nodeCap + 1);
+    const int* idx1 = idx1All + (size_t)f * P.cap;
+    const orbfe_keypoint* keys2 = keys2All + (size_t)f * P.cap;
+    const uint8_t* desc2 = desc2All + (size_t)f * P.cap * 32;
+    const uint8_t* free2 = free2All + (size_t)f * P.cap;
+    const uint8_t* stereo2 = stereo2All ? stereo2All + (size_t)f * P.cap : nullptr;
+    const int* ids2 = ids2All + (size_t)f * P.nodeCap;
+    const int* start2 = start2All + (size_t)f * (P.nodeCap + 1);
+    const int* idx2 = idx2All + (size_t)f * P.cap;
+    int* matches = matchesAll + (size_t)f * P.cap;
+    const int nk = min(nodes1[f], P.nodeCap), nfn = min(nodes2[f], P.nodeCap);
+
+    for (int i = tid; i < P.cap; i += SB_THREADS) {
+        binOf[i] = 0xffu;
+        matches[i] = -1;    // vMatches12(pKF1->N, -1)
+    }
+    if (tid < 32) hist[tid] = 0;
+    if (tid < 9) sF[tid] = F12All ? F12All[(size_t)f * 9 + tid] : 0.f;
+    if (tid < 2) sEp[tid] = epAll ? epAll[(size_t)f * 2 + tid] : 0.f;
+    if (tid == 0) sCount = 0;
+    __syncthreads();
+
+    for (int jn = warp; jn < nk; jn += SB_WARPS) {
+        const int id = ids1[jn];
+        int lo = 0, hi = nfn;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (ids2[mid] < id) lo = mid + 1; else hi = mid;
+        }
+        if (lo >= nfn || ids2[lo] != id) continue;
+        const int fs = start2[lo], fe = start2[lo + 1];
+        for (int i1 = start1[jn]; i1 < start1[jn + 1]; i1++) {
+            const int r1 = idx1[i1];
+            if (r1 < 0 || r1 >= P.cap || !free1[r1]) continue;
+            const bool bStereo1 = stereo1 && stereo1[r1];
+            const orbfe_keypoint kp1 = keys1[r1];
+            // epipolar line in the second image l = x1' F12 = [a b c] (Pinhole.cpp:110-112)
+            const float a = kp1.x * sF[0] + kp1.y * sF[3] + sF[6];
+            const float b = kp1.x * sF[1] + kp1.y * sF[4] + sF[7];
+            const float c = kp1.x * sF[2] + kp1.y * sF[5] + sF[8];
+            const float den = a * a + b * b;
+            const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(desc1 + (size_t)r1 * 32));
+            const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(desc1 + (size_t)r1 * 32) + 1);
+            unsigned best = 0xffffffffu;    // (dist << 16) | (0xffff - position): smallest distance, LAST position
+            for (int t = fs + lane; t < fe; t += 32) {
+                const int r2 = idx2[t];
+                if (r2 < 0 || r2 >= P.cap || !free2[r2]) continue;
+                const uint4 b0 = __ldg(reinterpret_cast<const uint4*>(desc2 + (size_t)r2 * 32));
+                const uint4 b1 = __ldg(reinterpret_cast<const uint4*>(desc2 + (size_t)r2 * 32) + 1);
+                const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                              __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+                if (d > SB_TH_LOW) continue;
+                const orbfe_keypoint kp2 = keys2[r2];
+                const int o2 = min(max(kp2.octave, 0), ORBFE_MAX_LEVELS - 1);
+                const bool bStereo2 = stereo2 && stereo2[r2];
+                if (!bStereo1 && !bStereo2) {
+                    const float distex = sEp[0] - kp2.x, distey = sEp[1] - kp2.y;
+                    if (distex * distex + distey * distey < 100.0f * P.scale[o2]) continue;
+                }
+                if (!P.coarse) {
+                    if (den == 0) continue;
+                    const float num = a * kp2.x + b * kp2.y + c;
+                    const float dsqr = num * num / den;
+                    if (!((double)dsqr < 3.84 * (double)P.sigma2[o2])) continue;
+                }
+                best = min(best, ((unsigned)d << 16) | (0xffffu - (unsigned)(t - fs)));
+            }
+            best = sb_min_u32(best);
+            if (lane == 0 && best != 0xffffffffu) {
+                const int best2 = idx2[fs + (int)(0xffffu - (best & 0xffffu))];
+                matches[r1] = best2;
+                if (P.checkOrientation) {
+                    float rot = kp1.angle - keys2[best2].angle;
+                    if (rot < 0.0f) rot += 360.0f;
+                    int bin = (int)roundf(rot * (1.0f / SB_HISTO));
+                    if (bin == SB_HISTO) bin = 0;
+                    bin = min(max(bin, 0), SB_HISTO - 1);
+                    binOf[r1] = (uint8_t)bin;
+                    atomicAdd(&hist[bin], 1);
+                }
+                atomicAdd(&sCount, 1);
+            }
+        }
+    }
+    __syncthreads();
+    if (P.checkOrientation) {
+        if (tid == 0) sb_three_maxima(hist, sInd);
+        __syncthreads();
+        int removed = 0;
+        for (int i = tid; i < P.cap; i += SB_THREADS) {
             const int b = binOf[i];
             if (b != 0xff && b != sInd[0] && b != sInd[1] && b != sInd[2]) {
                 matches[i] = -1;
@@ -201,6 +452,49 @@ int launch_search_bow(const uint8_t* descKF, const float* angleKF, const uint8_t
     smem_opt_in(optIn, search_bow_kernel, smem);
     search_bow_kernel<<<npairs, SB_THREADS, smem, st>>>(P, descKF, angleKF, validKF, kfIds, kfStart, kfIdx, kfNodes, descF, angleF,
                                                         nF, nleftF, fIds, fStart, fIdx, fNodes, matches, nMatches);
+    return 1;
+}
+
+int launch_search_bow_kf(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, const int* ids1, const int* start1,
+                         const int* idx1, const int* nodes1, const uint8_t* desc2, const float* angle2, const uint8_t* valid2,
+                         const int* ids2, const int* start2, const int* idx2, const int* nodes2, int cap, int nodeCap, int npairs,
+                         float nnRatio, int checkOrientation, int* matches, int* nMatches, cudaStream_t st) {
+    if (npairs <= 0) return 0;
+    BowParams P;
+    P.cap = cap;
+    P.nodeCap = nodeCap;
+    P.nnRatio = nnRatio;
+    P.checkOrientation = checkOrientation;
+    const size_t smem = 2 * search_bow_smem_bytes(cap);
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, search_bow_kf_kernel, smem);
+    search_bow_kf_kernel<<<npairs, SB_THREADS, smem, st>>>(P, desc1, angle1, valid1, ids1, start1, idx1, nodes1, desc2, angle2,
+                                                          valid2, ids2, start2, idx2, nodes2, matches, nMatches);
+    return 1;
+}
+
+int launch_search_triangulation(const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1, const uint8_t* stereo1,
+                                const int* ids1, const int* start1, const int* idx1, const int* nodes1,
+                                const orbfe_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
+                                const int* ids2, const int* start2, const int* idx2, const int* nodes2, const float* F12,
+                                const float* ep, const float* scale, const float* sigma2, int nlevels, int cap, int nodeCap,
+                                int npairs, int coarse, int checkOrientation, int* matches, int* nMatches, cudaStream_t st) {
+    if (npairs <= 0) return 0;
+    TriParams P;
+    P.cap = cap;
+    P.nodeCap = nodeCap;
+    P.coarse = coarse;
+    P.checkOrientation = checkOrientation;
+    for (int l = 0; l < ORBFE_MAX_LEVELS; l++) {
+        P.scale[l] = l < nlevels ? scale[l] : 1.0f;
+        P.sigma2[l] = l < nlevels ? sigma2[l] : 1.0f;
+    }
+    const size_t smem = search_bow_smem_bytes(cap);
+    static SmemOptIn optIn;
+    smem_opt_in(optIn, search_triangulation_kernel, smem);
+    search_triangulation_kernel<<<npairs, SB_THREADS, smem, st>>>(P, keys1, desc1, free1, stereo1, ids1, start1, idx1, nodes1, keys2,
+                                                                 desc2, free2, stereo2, ids2, start2, idx2, nodes2, F12, ep,
+                                                                 matches, nMatches);
     return 1;
 }
 

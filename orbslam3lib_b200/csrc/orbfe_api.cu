@@ -36,6 +36,13 @@ int launch_search_bow(const uint8_t* descKF, const float* angleKF, const uint8_t
                       const int* nleftF, const int* fIds, const int* fStart, const int* fIdx, const int* fNodes, int cap,
                       int nodeCap, int npairs, float nnRatio, int checkOrientation, int* matches, int* nMatches,
                       cudaStream_t st);
+size_t search_kf_smem_bytes(int cap);
+int launch_search_kf(const float bounds[4], const float* scale, const float* invSigma2, int nlevels, float th, float distTh,
+                     float bf, int blocks, int chi2, const orbfe_keypoint* keys, const uint8_t* desc, const float* uRight,
+                     const uint8_t* occupied, const int* nFeat, int cap, const void* pts, const int* nPts, int ptsCap,
+                     int nframes, int* match, int* dist, int* owner, int* nMatches, cudaStream_t st);
+int launch_sim3_agree(const int* m1, const int* m2, const int* n1, const int* n2, int cap, int nframes, int* out, int* nFound,
+                      cudaStream_t st);
 size_t search_frame_smem_bytes(int cap, int ptsCap);
 int launch_search_frame(const float bounds[4], const float* scale, int nlevels, float th, float mbf, int keyframe, int distTh,
                         int checkOrientation, const orbfe_keypoint* keys, const uint8_t* desc, const float* uRight,
@@ -1620,6 +1627,166 @@ int orbfe_search_by_projection_keyframe_batch(orbfe_matcher* m, const orbfe_keyp
     return search_frame_common(m, 1, keys_un, desc, nullptr, occupied, n, nullptr, nullptr, cap, bounds, scale_factors,
                                nlevels, 0.f, pts, npts, pts_cap, nframes, th, orb_dist, check_orientation, match, nullptr,
                                owner, nmatches, flags);
+}
+
+// shared body of the key-frame point searches (k_search_kf.cu: search_kf_kernel)
+static int search_kf_common(orbfe_matcher* m, int blocks, int chi2, const orbfe_keypoint* keys, const uint8_t* desc,
+                            const float* u_right, const uint8_t* occupied, const int32_t* n, int cap, const float bounds[4],
+                            const float* scale_factors, const float* inv_level_sigma2, int nlevels, float bf,
+                            const orbfe_frame_point* pts, const int32_t* npts, int pts_cap, int nframes, float th,
+                            float dist_th, int32_t* match, int32_t* dist, int32_t* owner, int32_t* nmatches, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (nframes < 0 || cap < 0 || pts_cap < 0 || nlevels < 1 || nlevels > ORBFE_MAX_LEVELS)
+        return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (nframes == 0) return ORBFE_OK;
+    if (!n || !npts || !bounds || !scale_factors || (chi2 && !inv_level_sigma2) || (cap > 0 && (!keys || !desc)) ||
+        (pts_cap > 0 && (!pts || !match)))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (!(bounds[2] > bounds[0]) || !(bounds[3] > bounds[1])) return set_merr(m, ORBFE_ERR_ARG, "empty image bounds");
+    if (!(dist_th < 256.f)) return set_merr(m, ORBFE_ERR_ARG, "distance threshold must be below 256");
+    if (cap > 65535 || search_kf_smem_bytes(cap) > 200 * 1024)
+        return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large for the shared-memory frame grid", cap);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)nframes;
+    const void* dIn[7] = {keys, desc, occupied, n, u_right, npts, pts};
+    const size_t inBytes[7] = {F * cap * sizeof(orbfe_keypoint), F * cap * 32, F * cap, F * 4, F * cap * 4, F * 4,
+                               F * pts_cap * sizeof(orbfe_frame_point)};
+    if (!inDev)
+        for (int i = 0; i < 7; i++) {
+            if (!dIn[i]) continue;
+            ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(inBytes[i], 16)));
+            if (inBytes[i]) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, dIn[i], inBytes[i], cudaMemcpyHostToDevice, st));
+            dIn[i] = m->dS[i].p;
+        }
+    int32_t *dM = match, *dD = dist, *dOwner = owner, *dCount = nmatches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dS[9].reserve(std::max<size_t>(F * pts_cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[10].reserve(std::max<size_t>(F * pts_cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[11].reserve(std::max<size_t>(F * cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dS[12].reserve(F * 4));
+        dM = (int32_t*)m->dS[9].p;
+        dD = dist ? (int32_t*)m->dS[10].p : nullptr;
+        dOwner = owner ? (int32_t*)m->dS[11].p : nullptr;
+        dCount = (int32_t*)m->dS[12].p;
+    }
+    if (pts_cap) ORBFE_MCUDA(m, cudaMemsetAsync(dM, 0xff, F * pts_cap * 4, st));
+    if (dD && pts_cap) ORBFE_MCUDA(m, cudaMemsetAsync(dD, 0xff, F * pts_cap * 4, st));
+    if (dOwner && cap) ORBFE_MCUDA(m, cudaMemsetAsync(dOwner, 0xff, F * cap * 4, st));
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_search_kf(bounds, scale_factors, inv_level_sigma2, nlevels, th, dist_th, bf, blocks, chi2,
+                                          (const orbfe_keypoint*)dIn[0], (const uint8_t*)dIn[1], (const float*)dIn[4],
+                                          (const uint8_t*)dIn[2], (const int*)dIn[3], cap, dIn[6], (const int*)dIn[5], pts_cap,
+                                          nframes, dM, dD, dOwner, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        if (pts_cap) {
+            ORBFE_MCUDA(m, cudaMemcpyAsync(match, dM, F * pts_cap * 4, cudaMemcpyDeviceToHost, st));
+            if (dist) ORBFE_MCUDA(m, cudaMemcpyAsync(dist, dD, F * pts_cap * 4, cudaMemcpyDeviceToHost, st));
+        }
+        if (owner && cap) ORBFE_MCUDA(m, cudaMemcpyAsync(owner, dOwner, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_projection_sim3_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un, const uint8_t* desc,
+                                          const uint8_t* occupied, const int32_t* n, int cap, const float bounds[4],
+                                          const float* scale_factors, int nlevels, const orbfe_frame_point* pts,
+                                          const int32_t* npts, int pts_cap, int nframes, float th, float ratio_hamming,
+                                          int32_t* match, int32_t* owner, int32_t* nmatches, unsigned flags) {
+    return search_kf_common(m, 1, 0, keys_un, desc, nullptr, occupied, n, cap, bounds, scale_factors, nullptr, nlevels, 0.f, pts,
+                            npts, pts_cap, nframes, th, 50.f /* TH_LOW, ORBmatcher.cc:36 */ * ratio_hamming, match, nullptr,
+                            owner, nmatches, flags);
+}
+
+int orbfe_fuse_batch(orbfe_matcher* m, const orbfe_keypoint* keys, const uint8_t* desc, const float* u_right, const int32_t* n,
+                     int cap, const float bounds[4], const float* scale_factors, const float* inv_level_sigma2, int nlevels,
+                     float bf, const orbfe_frame_point* pts, const int32_t* npts, int pts_cap, int nframes, float th,
+                     int check_reprojection, int32_t* best_idx, int32_t* best_dist, int32_t* ncandidates, unsigned flags) {
+    return search_kf_common(m, 0, check_reprojection ? 1 : 0, keys, desc, u_right, nullptr, n, cap, bounds, scale_factors,
+                            inv_level_sigma2, nlevels, bf, pts, npts, pts_cap, nframes, th, 50.f /* TH_LOW */, best_idx,
+                            best_dist, nullptr, ncandidates, flags);
+}
+
+int orbfe_search_by_sim3_batch(orbfe_matcher* m, const orbfe_keypoint* keys_un1, const uint8_t* desc1, const int32_t* n1,
+                               const orbfe_keypoint* keys_un2, const uint8_t* desc2, const int32_t* n2, int cap,
+                               const float bounds1[4], const float bounds2[4], const float* scale_factors, int nlevels,
+                               const orbfe_frame_point* pts1, const orbfe_frame_point* pts2, int nframes, float th,
+                               int32_t* matches12, int32_t* match1, int32_t* match2, int32_t* nfound, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (nframes < 0 || cap < 0 || nlevels < 1 || nlevels > ORBFE_MAX_LEVELS) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (nframes == 0) return ORBFE_OK;
+    if (!n1 || !n2 || !bounds1 || !bounds2 || !scale_factors ||
+        (cap > 0 && (!keys_un1 || !desc1 || !keys_un2 || !desc2 || !pts1 || !pts2 || !matches12)))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (!(bounds1[2] > bounds1[0]) || !(bounds1[3] > bounds1[1]) || !(bounds2[2] > bounds2[0]) || !(bounds2[3] > bounds2[1]))
+        return set_merr(m, ORBFE_ERR_ARG, "empty image bounds");
+    if (cap > 65535 || search_kf_smem_bytes(cap) > 200 * 1024)
+        return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large for the shared-memory frame grid", cap);
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    if (cap == 0) {
+        if (nfound && !outDev)
+            for (int f = 0; f < nframes; f++) nfound[f] = 0;
+        return ORBFE_OK;
+    }
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)nframes;
+    const void* dIn[8] = {keys_un1, desc1, n1, keys_un2, desc2, n2, pts1, pts2};
+    const size_t inBytes[8] = {F * cap * sizeof(orbfe_keypoint), F * cap * 32, F * 4, F * cap * sizeof(orbfe_keypoint),
+                               F * cap * 32, F * 4, F * cap * sizeof(orbfe_frame_point), F * cap * sizeof(orbfe_frame_point)};
+    if (!inDev)
+        for (int i = 0; i < 8; i++) {
+            ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(inBytes[i], 16)));
+            ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, dIn[i], inBytes[i], cudaMemcpyHostToDevice, st));
+            dIn[i] = m->dS[i].p;
+        }
+    ORBFE_MCUDA(m, m->dS[8].reserve(F * cap * 4));
+    ORBFE_MCUDA(m, m->dS[9].reserve(F * cap * 4));
+    int32_t* dM1 = (int32_t*)m->dS[8].p;    // vnMatch1 / vnMatch2
+    int32_t* dM2 = (int32_t*)m->dS[9].p;
+    int32_t *dOut = matches12, *dCount = nfound;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dS[10].reserve(F * cap * 4));
+        ORBFE_MCUDA(m, m->dS[12].reserve(F * 4));
+        dOut = (int32_t*)m->dS[10].p;
+        dCount = (int32_t*)m->dS[12].p;
+    }
+    ORBFE_MCUDA(m, cudaMemsetAsync(dM1, 0xff, F * cap * 4, st));
+    ORBFE_MCUDA(m, cudaMemsetAsync(dM2, 0xff, F * cap * 4, st));
+    cudaEventRecord(m->ev[0], st);
+    int launches = 0;
+    // KF1's points into KF2 (:1504-1583), then KF2's points into KF1 (:1585-1664); TH_HIGH = 100
+    launches += launch_search_kf(bounds2, scale_factors, nullptr, nlevels, th, 100.f, 0.f, 0, 0, (const orbfe_keypoint*)dIn[3],
+                                 (const uint8_t*)dIn[4], nullptr, nullptr, (const int*)dIn[5], cap, dIn[6], (const int*)dIn[2],
+                                 cap, nframes, dM1, nullptr, nullptr, nullptr, st);
+    launches += launch_search_kf(bounds1, scale_factors, nullptr, nlevels, th, 100.f, 0.f, 0, 0, (const orbfe_keypoint*)dIn[0],
+                                 (const uint8_t*)dIn[1], nullptr, nullptr, (const int*)dIn[2], cap, dIn[7], (const int*)dIn[5],
+                                 cap, nframes, dM2, nullptr, nullptr, nullptr, st);
+    launches += launch_sim3_agree(dM1, dM2, (const int*)dIn[2], (const int*)dIn[5], cap, nframes, dOut, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    const cudaMemcpyKind kind = outDev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    if (match1) ORBFE_MCUDA(m, cudaMemcpyAsync(match1, dM1, F * cap * 4, kind, st));
+    if (match2) ORBFE_MCUDA(m, cudaMemcpyAsync(match2, dM2, F * cap * 4, kind, st));
+    if (!outDev) {
+        ORBFE_MCUDA(m, cudaMemcpyAsync(matches12, dOut, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nfound) ORBFE_MCUDA(m, cudaMemcpyAsync(nfound, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
 }
 
 int orbfe_search_for_initialization_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1,

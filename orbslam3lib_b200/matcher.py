@@ -207,6 +207,96 @@ class ORBmatcher:
             float(th), int(ORBdist), int(self.mbCheckOrientation), ptr(m), ptr(owner), ptr(nm), 0))
         return int(nm[0]), m, owner[:n]
 
+    def SearchByProjectionSim3(self, keys_un, desc, bounds, scale_factors, frame_points, th, ratioHamming=1.0, occupied=None):
+        """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (ORBmatcher.cc:428-533; :535-647 fills
+        vpMatchedKF from the same result).  occupied[i] = vpMatched[i] != NULL.  -> (nmatches, match, owner)"""
+        from .scenes import FRAME_POINT_DTYPE
+        k = np.ascontiguousarray(keys_un, KP_DTYPE)
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = k.shape[0]
+        oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        p = np.ascontiguousarray(frame_points, FRAME_POINT_DTYPE)
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        m, owner = np.full(max(p.shape[0], 1), -1, np.int32), np.full(max(n, 1), -1, np.int32)
+        nn, npp, nm = (np.array([v], np.int32) for v in (n, p.shape[0], 0))
+        self._bf._check(_lib.lib().orbfe_search_by_projection_sim3_batch(
+            self._bf._h, ptr(k), ptr(d), ptr(oc), ptr(nn), n, ptr(b), ptr(sf), sf.shape[0], ptr(p), ptr(npp), p.shape[0], 1,
+            float(th), float(ratioHamming), ptr(m), ptr(owner), ptr(nm), 0))
+        return int(nm[0]), m[:p.shape[0]], owner[:n]
+
+    def Fuse(self, keys, desc, bounds, scale_factors, inv_level_sigma2, frame_points, th=3.0, u_right=None, bf=0.0,
+             check_reprojection=True):
+        """The search of ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) (ORBmatcher.cc:1155-1345; check_reprojection=True) or of
+        ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1347-1462; False).  The caller applies the map mutations
+        in point order.  -> (count, best_idx, best_dist)"""
+        from .scenes import FRAME_POINT_DTYPE
+        k = np.ascontiguousarray(keys, KP_DTYPE)
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = k.shape[0]
+        ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        p = np.ascontiguousarray(frame_points, FRAME_POINT_DTYPE)
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        iv = np.ascontiguousarray(inv_level_sigma2, np.float32)
+        bi, bd = np.full(max(p.shape[0], 1), -1, np.int32), np.full(max(p.shape[0], 1), -1, np.int32)
+        nn, npp, nm = (np.array([v], np.int32) for v in (n, p.shape[0], 0))
+        self._bf._check(_lib.lib().orbfe_fuse_batch(
+            self._bf._h, ptr(k), ptr(d), ptr(ur), ptr(nn), n, ptr(b), ptr(sf), ptr(iv), sf.shape[0], float(bf), ptr(p), ptr(npp),
+            p.shape[0], 1, float(th), int(bool(check_reprojection)), ptr(bi), ptr(bd), ptr(nm), 0))
+        return int(nm[0]), bi[:p.shape[0]], bd[:p.shape[0]]
+
+    def SearchBySim3(self, keys_un1, desc1, keys_un2, desc2, bounds1, bounds2, scale_factors, frame_points1, frame_points2, th):
+        """ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, S12, th) (ORBmatcher.cc:1464-1681).  frame_points1[i1] = KF1's
+        MapPoint i1 projected into KF2, frame_points2[i2] the reverse.  -> (nFound, matches12, vnMatch1, vnMatch2)"""
+        from .scenes import FRAME_POINT_DTYPE
+        k1, k2 = np.ascontiguousarray(keys_un1, KP_DTYPE), np.ascontiguousarray(keys_un2, KP_DTYPE)
+        n1, n2 = k1.shape[0], k2.shape[0]
+        cap = max(n1, n2, 1)
+        K = np.zeros((2, cap), KP_DTYPE)
+        D = np.zeros((2, cap, 32), np.uint8)
+        P = np.zeros((2, cap), FRAME_POINT_DTYPE)
+        K[0, :n1], K[1, :n2] = k1, k2
+        D[0, :n1] = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        D[1, :n2] = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        P[0, :n1], P[1, :n2] = frame_points1, frame_points2
+        b1, b2 = np.ascontiguousarray(bounds1, np.float32), np.ascontiguousarray(bounds2, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        m12, v1, v2 = (np.full(cap, -1, np.int32) for _ in range(3))
+        nn1, nn2, nf = (np.array([v], np.int32) for v in (n1, n2, 0))
+        self._bf._check(_lib.lib().orbfe_search_by_sim3_batch(
+            self._bf._h, ptr(K[0]), ptr(D[0]), ptr(nn1), ptr(K[1]), ptr(D[1]), ptr(nn2), cap, ptr(b1), ptr(b2), ptr(sf),
+            sf.shape[0], ptr(P[0]), ptr(P[1]), 1, float(th), ptr(m12), ptr(v1), ptr(v2), ptr(nf), 0))
+        return int(nf[0]), m12[:n1], v1[:n1], v2[:n2]
+
+    def search_sim3_projection_batch_raw(self, keys_un, desc, occupied, n, cap, bounds, scale_factors, pts, npts, pts_cap, nframes,
+                                         th, ratio_hamming, match, owner, nmatches, flags=0):
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        self._bf._check(_lib.lib().orbfe_search_by_projection_sim3_batch(
+            self._bf._h, ptr(keys_un), ptr(desc), ptr(occupied), ptr(n), int(cap), ptr(b), ptr(sf), sf.shape[0], ptr(pts),
+            ptr(npts), int(pts_cap), int(nframes), float(th), float(ratio_hamming), ptr(match), ptr(owner), ptr(nmatches),
+            int(flags)))
+
+    def fuse_batch_raw(self, keys, desc, u_right, n, cap, bounds, scale_factors, inv_level_sigma2, bf, pts, npts, pts_cap, nframes,
+                       th, check_reprojection, best_idx, best_dist, ncandidates, flags=0):
+        b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        iv = np.ascontiguousarray(inv_level_sigma2, np.float32)
+        self._bf._check(_lib.lib().orbfe_fuse_batch(
+            self._bf._h, ptr(keys), ptr(desc), ptr(u_right), ptr(n), int(cap), ptr(b), ptr(sf), ptr(iv), sf.shape[0], float(bf),
+            ptr(pts), ptr(npts), int(pts_cap), int(nframes), float(th), int(bool(check_reprojection)), ptr(best_idx),
+            ptr(best_dist), ptr(ncandidates), int(flags)))
+
+    def search_by_sim3_batch_raw(self, keys1, desc1, n1, keys2, desc2, n2, cap, bounds1, bounds2, scale_factors, pts1, pts2,
+                                 nframes, th, matches12, match1, match2, nfound, flags=0):
+        b1, b2 = np.ascontiguousarray(bounds1, np.float32), np.ascontiguousarray(bounds2, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        self._bf._check(_lib.lib().orbfe_search_by_sim3_batch(
+            self._bf._h, ptr(keys1), ptr(desc1), ptr(n1), ptr(keys2), ptr(desc2), ptr(n2), int(cap), ptr(b1), ptr(b2), ptr(sf),
+            sf.shape[0], ptr(pts1), ptr(pts2), int(nframes), float(th), ptr(matches12), ptr(match1), ptr(match2), ptr(nfound),
+            int(flags)))
+
     def SearchByBoW(self, desc_kf, angle_kf, valid_kf, fv_kf, desc_f, angle_f, fv_f, nleft_f=-1):
         """ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vpMapPointMatches) (ORBmatcher.cc:224-425).  fv_* = the DBoW2
         feature vector as CSR (node_ids, start, idx); valid_kf[i] = the key frame's MapPoint i exists and is not bad.

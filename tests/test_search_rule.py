@@ -643,3 +643,225 @@ def test_oracle_search_by_bow_vs_python(oracle):
         assert nm == rnm and nm > 40
         if stereo:
             assert (m[nleft:] >= 0).sum() > 10    # right-camera slots matched through the `|| true` branch
+
+
+# ---- MapPoints projected into a key frame: ORBmatcher.cc:428-647 (Sim3 projection), :1155-1462 (Fuse), :1464-1681 (SearchBySim3)
+class _PyKeyFrame:
+    """KeyFrame grid (the Frame's, Frame.cc:405-436), KeyFrame::GetFeaturesInArea (KeyFrame.cc:706-750) and IsInImage
+    (:752-755) in numpy float32."""
+
+    def __init__(self, keys, bounds):
+        f32 = np.float32
+        self.keys = keys
+        self.min_x, self.min_y, self.max_x, self.max_y = [f32(v) for v in bounds]
+        self.gw = f32(f32(64) / f32(self.max_x - self.min_x))
+        self.gh = f32(f32(48) / f32(self.max_y - self.min_y))
+        self.grid = {}
+        for i in range(len(keys)):
+            px = self._round(f32(f32(keys["x"][i] - self.min_x) * self.gw))
+            py = self._round(f32(f32(keys["y"][i] - self.min_y) * self.gh))
+            if 0 <= px < 64 and 0 <= py < 48:
+                self.grid.setdefault((px, py), []).append(i)
+
+    @staticmethod
+    def _round(v):
+        v = float(v)
+        return int(math.floor(v + 0.5) if v >= 0 else math.ceil(v - 0.5))
+
+    def is_in_image(self, x, y):
+        return x >= self.min_x and x < self.max_x and y >= self.min_y and y < self.max_y
+
+    def features_in_area(self, x, y, r):
+        f32 = np.float32
+        out = []
+        cx0 = max(0, int(math.floor(f32(f32(f32(x - self.min_x) - r) * self.gw))))
+        if cx0 >= 64:
+            return out
+        cx1 = min(63, int(math.ceil(f32(f32(f32(x - self.min_x) + r) * self.gw))))
+        if cx1 < 0:
+            return out
+        cy0 = max(0, int(math.floor(f32(f32(f32(y - self.min_y) - r) * self.gh))))
+        if cy0 >= 48:
+            return out
+        cy1 = min(47, int(math.ceil(f32(f32(f32(y - self.min_y) + r) * self.gh))))
+        if cy1 < 0:
+            return out
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for j in self.grid.get((ix, iy), []):
+                    k = self.keys[j]
+                    if abs(f32(k["x"] - x)) < r and abs(f32(k["y"] - y)) < r:
+                        out.append(j)
+        return out
+
+
+def _py_kf_best(kf, bits, p, th, scale, skip=None, gate=None):
+    """the candidate loop shared by :488-509, :1259-1312, :1423-1440, :1552-1575: (bestDist, bestIdx) or None when the point
+    does not reach it."""
+    f32 = np.float32
+    if not (p["flags"] & 1):
+        return None
+    u, v = f32(p["u"]), f32(p["v"])
+    if not kf.is_in_image(u, v):
+        return None
+    lvl = int(p["level"])
+    radius = f32(f32(th) * f32(scale[lvl]))
+    cand = kf.features_in_area(u, v, radius)
+    if not cand:
+        return None
+    pb = np.unpackbits(p["desc"])
+    best_dist, best_idx = 256, -1
+    for idx in cand:
+        if skip is not None and skip[idx]:
+            continue
+        o = int(kf.keys["octave"][idx])
+        if o < lvl - 1 or o > lvl:
+            continue
+        if gate is not None and not gate(idx, o):
+            continue
+        d = int((pb != bits[idx]).sum())
+        if d < best_dist:
+            best_dist, best_idx = d, idx
+    return best_dist, best_idx
+
+
+def _py_search_sim3(keys, desc, occupied, bounds, scale, pts, th, ratio):
+    f32 = np.float32
+    kf = _PyKeyFrame(keys, bounds)
+    bits = np.unpackbits(desc, axis=1)
+    matched = np.zeros(len(keys), bool) if occupied is None else np.asarray(occupied).astype(bool).copy()
+    match = np.full(len(pts), -1, np.int64)
+    nm = 0
+    for i in range(len(pts)):
+        r = _py_kf_best(kf, bits, pts[i], th, scale, skip=matched)
+        if r is None:
+            continue
+        if f32(r[0]) <= f32(f32(50) * f32(ratio)):
+            matched[r[1]] = True
+            match[i] = r[1]
+            nm += 1
+    return match, nm
+
+
+def _py_fuse(keys, desc, u_right, bounds, scale, inv_sigma2, bf, pts, th, check):
+    f32 = np.float32
+    kf = _PyKeyFrame(keys, bounds)
+    bits = np.unpackbits(desc, axis=1)
+    best = np.full(len(pts), -1, np.int64)
+    for i in range(len(pts)):
+        p = pts[i]
+        u, v = f32(p["u"]), f32(p["v"])
+        ur = f32(u - f32(f32(bf) * f32(p["invz"])))
+
+        def gate(idx, o):
+            kpx, kpy = f32(keys["x"][idx]), f32(keys["y"][idx])
+            kpr = f32(-1.0) if u_right is None else f32(u_right[idx])
+            ex, ey = f32(u - kpx), f32(v - kpy)
+            if kpr >= 0:
+                er = f32(ur - kpr)
+                e2 = f32(f32(f32(ex * ex) + f32(ey * ey)) + f32(er * er))
+                return not (float(f32(e2 * f32(inv_sigma2[o]))) > 7.8)
+            e2 = f32(f32(ex * ex) + f32(ey * ey))
+            return not (float(f32(e2 * f32(inv_sigma2[o]))) > 5.99)
+        r = _py_kf_best(kf, bits, p, th, scale, gate=gate if check else None)
+        if r is not None and r[0] <= 50:
+            best[i] = r[1]
+    return best
+
+
+def _py_search_by_sim3(k1, d1, k2, d2, b1, b2, scale, p1, p2, th):
+    kf1, kf2 = _PyKeyFrame(k1, b1), _PyKeyFrame(k2, b2)
+    bits1, bits2 = np.unpackbits(d1, axis=1), np.unpackbits(d2, axis=1)
+    vn1, vn2 = np.full(len(k1), -1, np.int64), np.full(len(k2), -1, np.int64)
+    for i1 in range(len(k1)):
+        r = _py_kf_best(kf2, bits2, p1[i1], th, scale)
+        if r is not None and r[1] >= 0 and r[0] <= 100:
+            vn1[i1] = r[1]
+    for i2 in range(len(k2)):
+        r = _py_kf_best(kf1, bits1, p2[i2], th, scale)
+        if r is not None and r[1] >= 0 and r[0] <= 100:
+            vn2[i2] = r[1]
+    m12 = np.full(len(k1), -1, np.int64)
+    for i1 in range(len(k1)):
+        if vn1[i1] >= 0 and vn2[vn1[i1]] == i1:
+            m12[i1] = vn1[i1]
+    return m12, vn1, vn2
+
+
+def kf_case(oracle, seed, npts=350, w=320, h=240, nf=500):
+    """one key frame (features of an extraction) and MapPoints projected into it (scenes.frame_points: jittered
+    re-observations, level -1 / 0 / +1, bit flips, duplicates, some not reaching the search), with a few projections placed
+    exactly on the bounds (IsInImage is >= min and < max)."""
+    img = scenes.make("texture", w, h, seed)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _, kps, desc = ex(img)
+    pts = scenes.frame_points(kps, desc, len(kps), None, None, 8, npts, seed)
+    if npts >= 8:
+        pts["u"][3], pts["v"][5], pts["u"][6], pts["v"][7] = w, h, 0.0, 0.0
+        pts["flags"][[3, 5, 6, 7]] |= 1
+    return kps, desc, ex, pts
+
+
+def test_oracle_search_by_projection_sim3_vs_python(oracle):
+    for seed, th, ratio in ((51, 10.0, 1.0), (52, 4.0, 1.6), (53, 10.0, 0.5)):
+        kps, desc, ex, pts = kf_case(oracle, 6400 + seed)
+        occupied = (scenes.rand_u32(len(kps), seed + 5) % 7 == 0).astype(np.uint8)
+        m, owner, nm = oracle.search_by_projection_sim3(kps, desc, occupied, (0, 0, 320, 240), ex.scale, pts, th, ratio)
+        ref, rnm = _py_search_sim3(kps, desc, occupied, (0, 0, 320, 240), ex.scale, pts, th, ratio)
+        np.testing.assert_array_equal(m, ref)
+        assert nm == rnm and nm > (60 if ratio >= 1.0 else 20)
+        assert m[3] == -1 and m[5] == -1                      # u == mnMaxX / v == mnMaxY are outside
+        got = m[m >= 0]
+        assert len(np.unique(got)) == len(got)                 # a taken slot is never taken again
+        assert not occupied[got].any()
+        np.testing.assert_array_equal(np.nonzero(owner >= 0)[0], np.sort(got))
+
+
+def test_oracle_fuse_vs_python(oracle):
+    for seed, th, check in ((61, 3.0, True), (62, 6.0, True), (63, 4.0, False)):
+        kps, desc, ex, pts = kf_case(oracle, 6500 + seed)
+        n = len(kps)
+        u_right = np.where(scenes.rand_u32(n, seed) % 3 == 0, -1.0, kps["x"] - 8.0).astype(np.float32)
+        inv_sigma2 = (1.0 / (ex.scale.astype(np.float32) ** 2)).astype(np.float32)
+        bi, bd, nf = oracle.fuse(kps, desc, u_right, (0, 0, 320, 240), ex.scale, inv_sigma2, 47.9, pts, th, check)
+        ref = _py_fuse(kps, desc, u_right, (0, 0, 320, 240), ex.scale, inv_sigma2, 47.9, pts, th, check)
+        np.testing.assert_array_equal(bi, ref)
+        assert nf == (ref >= 0).sum() and nf > 40
+        assert ((bd >= 0) == (bi >= 0)).all() and bd.max() <= 50
+    # the gate matters: without it more points find a feature
+    kps, desc, ex, pts = kf_case(oracle, 6561)
+    inv_sigma2 = (1.0 / (ex.scale.astype(np.float32) ** 2)).astype(np.float32)
+    a = oracle.fuse(kps, desc, None, (0, 0, 320, 240), ex.scale, inv_sigma2, 0.0, pts, 6.0, True)[0]
+    b = oracle.fuse(kps, desc, None, (0, 0, 320, 240), ex.scale, inv_sigma2, 0.0, pts, 6.0, False)[0]
+    assert (a >= 0).sum() < (b >= 0).sum()
+
+
+def sim3_case(oracle, seed, w=320, h=240, nf=400):
+    """two key frames seeing the same scene (current / previous frame); KF1's MapPoint i1 is the re-observation of a KF2
+    feature and vice versa, built with scenes.frame_points on the OTHER frame's features."""
+    cur = scenes.make("texture", w, h, seed)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _, k1, d1 = ex(cur)
+    _, k2, d2 = ex(scenes.previous_frame(cur, seed))
+    p1 = scenes.frame_points(k2, d2, len(k2), None, None, 8, len(k1), seed + 1, dup_frac=0.05)
+    p2 = scenes.frame_points(k1, d1, len(k1), None, None, 8, len(k2), seed + 2, dup_frac=0.05)
+    # make a good share of the pairs mutual: point i1 looks at feature j of KF2 and point j of KF2 looks back at i1
+    r = scenes.rand_u32(len(k1), seed + 3)
+    for i1 in range(0, len(k1), 2):
+        j = int(r[i1] % len(k2))
+        p1[i1]["u"], p1[i1]["v"], p1[i1]["level"], p1[i1]["desc"], p1[i1]["flags"] = k2["x"][j], k2["y"][j], k2["octave"][j], d2[j], 1
+        p2[j]["u"], p2[j]["v"], p2[j]["level"], p2[j]["desc"], p2[j]["flags"] = k1["x"][i1], k1["y"][i1], k1["octave"][i1], d1[i1], 1
+    return k1, d1, k2, d2, ex, p1, p2
+
+
+def test_oracle_search_by_sim3_vs_python(oracle):
+    for seed, th in ((6601, 7.5), (6602, 3.0)):
+        k1, d1, k2, d2, ex, p1, p2 = sim3_case(oracle, seed)
+        b = (0, 0, 320, 240)
+        m12, v1, v2, nf = oracle.search_by_sim3(k1, d1, k2, d2, b, b, ex.scale, p1, p2, th)
+        r12, r1, r2 = _py_search_by_sim3(k1, d1, k2, d2, b, b, ex.scale, p1, p2, th)
+        np.testing.assert_array_equal(v1, r1)
+        np.testing.assert_array_equal(v2, r2)
+        np.testing.assert_array_equal(m12, r12)
+        assert nf == (r12 >= 0).sum() and nf > 30
+        assert (v1 >= 0).sum() > nf    # some one-directional matches fail the agreement
