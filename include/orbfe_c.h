@@ -228,6 +228,36 @@ int orbfe_search_by_bow_batch(orbfe_matcher* m, const uint8_t* desc_kf, const fl
                               const int32_t* nleft_f, const int32_t* f_node_ids, const int32_t* f_node_start,
                               const int32_t* f_idx, const int32_t* f_nnodes, int cap, int node_cap, int npairs,
                               float nn_ratio, int check_orientation, int32_t* matches, int32_t* nmatches, unsigned flags);
+/* ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (ORBmatcher.cc:766-906): loop
+ * detection and relocalisation between key frames.  Feature vectors as CSR like above, for both key frames.  valid1[i] /
+ * valid2[i] = the MapPoint of feature i exists, is not bad, and (stereo-camera key frames) i < mvKeysUn.size() (:802-804,
+ * :821-823); angle1 / angle2 = mvKeysUn[i].angle.  Accepted with bestDist1 < TH_LOW (strict) and the mfNNratio test; an
+ * accepted KF2 feature enters vbMatched2.  matches12[pair*cap + i1] = idx2 (vpMatches12[i1] = vpMapPoints2[idx2]) or -1 after
+ * the rotation check; every one of the cap entries is written; nmatches[pair] = the return value. */
+int orbfe_search_by_bow_kf_batch(orbfe_matcher* m, const uint8_t* desc1, const float* angle1, const uint8_t* valid1,
+                                 const int32_t* node_ids1, const int32_t* node_start1, const int32_t* idx1,
+                                 const int32_t* nnodes1, const uint8_t* desc2, const float* angle2, const uint8_t* valid2,
+                                 const int32_t* node_ids2, const int32_t* node_start2, const int32_t* idx2,
+                                 const int32_t* nnodes2, int cap, int node_cap, int npairs, float nn_ratio, int check_orientation,
+                                 int32_t* matches12, int32_t* nmatches, unsigned flags);
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, vMatchedPairs, bOnlyStereo, bCoarse) (ORBmatcher.cc:908-1153) for key frames
+ * with one camera (mpCamera2 == NULL: Pinhole::epipolarConstrain, Pinhole.cpp:102-124) or with coarse != 0 (any camera
+ * model: the constraint is skipped, :1044).  keysN = the keypoint :973-975 / :1010-1012 picks for feature i (mvKeysUn);
+ * freeN[i] = GetMapPoint(i) == NULL && (!bOnlyStereo || mvuRight[i] >= 0); stereoN[i] (nullable = 0) = mvuRight[i] >= 0;
+ * f12[pair*9 + 3*r + c] = F12(r, c) = K1^-T [t12]x R12 K2^-1 (Pinhole.cpp:104-107; unread when coarse); epipole[pair*2 ...] =
+ * pKF2->mpCamera->project(T2w * Cw1) (:930-932); scale_factors / level_sigma2 = pKF2's mvScaleFactors / mvLevelSigma2.
+ * matches12[pair*cap + i1] = vMatches12[i1] after the rotation check (vMatchedPairs = the pairs (i1, matches12[i1]) with
+ * matches12[i1] >= 0, in i1 order); nmatches[pair] = the return value.  The KannalaBrandt8 form of the constraint (a
+ * triangulation, KannalaBrandt8.cpp:210-214) is not covered: use coarse for two-camera rigs. */
+int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1,
+                                         const uint8_t* stereo1, const int32_t* node_ids1, const int32_t* node_start1,
+                                         const int32_t* idx1, const int32_t* nnodes1, const orbfe_keypoint* keys2,
+                                         const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
+                                         const int32_t* node_ids2, const int32_t* node_start2, const int32_t* idx2,
+                                         const int32_t* nnodes2, int cap, int node_cap, int npairs, const float* f12,
+                                         const float* epipole, const float* scale_factors, const float* level_sigma2,
+                                         int nlevels, int coarse, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                         unsigned flags);
 /* ---- the per-frame tracking matcher: ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th,
  * bMono) with SearchByProjectionThread and the rotation histogram (ORBmatcher.cc:1683-1921), and
  * ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1923-2059), both with

@@ -1874,6 +1874,165 @@ int orc_search_by_bow(const uint8_t* descKF, const float* angleKF, const uint8_t
     return nmatches;
 }
 
+// ---- ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (ORBmatcher.cc:766-906) --------
+int orc_search_by_bow_kf(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, int n1, const int32_t* nodeIds1,
+                         const int32_t* nodeStart1, const int32_t* idx1v, int nodes1, const uint8_t* desc2, const float* angle2,
+                         const uint8_t* valid2, const int32_t* nodeIds2, const int32_t* nodeStart2, const int32_t* idx2v,
+                         int nodes2, float mfNNratio, int checkOrientation, int32_t* matches12) {
+    const int TH_LOW = 50, HISTO_LENGTH = 30;
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    int maxIdx2 = 0;
+    for (int t = 0; t < nodeStart2[nodes2]; t++) maxIdx2 = std::max(maxIdx2, idx2v[t] + 1);
+    std::vector<bool> vbMatched2(maxIdx2, false);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nmatches = 0;
+    int f1it = 0, f2it = 0;
+    while (f1it != nodes1 && f2it != nodes2) {
+        if (nodeIds1[f1it] == nodeIds2[f2it]) {
+            for (int i1 = nodeStart1[f1it]; i1 < nodeStart1[f1it + 1]; i1++) {
+                const size_t idx1 = (size_t)idx1v[i1];
+                if (!valid1[idx1]) continue;    // NLeft / mvKeysUn.size(), !pMP1, pMP1->isBad()
+                int bestDist1 = 256;
+                int bestIdx2 = -1;
+                int bestDist2 = 256;
+                for (int i2 = nodeStart2[f2it]; i2 < nodeStart2[f2it + 1]; i2++) {
+                    const size_t idx2 = (size_t)idx2v[i2];
+                    if (vbMatched2[idx2] || !valid2[idx2]) continue;
+                    int dist = desc_distance(desc1 + idx1 * 32, desc2 + idx2 * 32);
+                    if (dist < bestDist1) {
+                        bestDist2 = bestDist1;
+                        bestDist1 = dist;
+                        bestIdx2 = (int)idx2;
+                    } else if (dist < bestDist2) {
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist1 < TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        matches12[idx1] = bestIdx2;
+                        vbMatched2[bestIdx2] = true;
+                        if (checkOrientation) {
+                            float rot = angle1[idx1] - angle2[bestIdx2];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back((int)idx1);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            f1it++;
+            f2it++;
+        } else if (nodeIds1[f1it] < nodeIds2[f2it]) {
+            f1it = (int)(std::lower_bound(nodeIds1, nodeIds1 + nodes1, nodeIds2[f2it]) - nodeIds1);
+        } else {
+            f2it = (int)(std::lower_bound(nodeIds2, nodeIds2 + nodes2, nodeIds1[f1it]) - nodeIds2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                matches12[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
+// ---- ORBmatcher::SearchForTriangulation (ORBmatcher.cc:908-1153), one camera per key frame; Pinhole.cpp:102-124 ---------------
+namespace {
+bool pinhole_epipolar_constrain(const float* F12, const orc_keypoint& kp1, const orc_keypoint& kp2, const float unc) {
+    // F12 row-major: F12(r, c) = F12[3 * r + c].  Epipolar line in second image l = x1'F12 = [a b c]
+    const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+    const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+    const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+    const float num = a * kp2.x + b * kp2.y + c;
+    const float den = a * a + b * b;
+    if (den == 0) return false;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * unc;
+}
+}    // namespace
+
+int orc_search_for_triangulation(const orc_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1, const uint8_t* stereo1,
+                                 int n1, const int32_t* nodeIds1, const int32_t* nodeStart1, const int32_t* idx1v, int nodes1,
+                                 const orc_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
+                                 const int32_t* nodeIds2, const int32_t* nodeStart2, const int32_t* idx2v, int nodes2,
+                                 const float* F12, const float* ep, const float* mvScaleFactors, const float* mvLevelSigma2,
+                                 int bCoarse, int checkOrientation, int32_t* vMatches12) {
+    const int TH_LOW = 50, HISTO_LENGTH = 30;
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) vMatches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int f1it = 0, f2it = 0;
+    while (f1it != nodes1 && f2it != nodes2) {
+        if (nodeIds1[f1it] == nodeIds2[f2it]) {
+            for (int i1 = nodeStart1[f1it]; i1 < nodeStart1[f1it + 1]; i1++) {
+                const size_t idx1 = (size_t)idx1v[i1];
+                if (!free1[idx1]) continue;    // pMP1, or bOnlyStereo && !bStereo1
+                const bool bStereo1 = stereo1 && stereo1[idx1];
+                const orc_keypoint& kp1 = keys1[idx1];
+                int bestDist = TH_LOW;
+                int bestIdx2 = -1;
+                for (int i2 = nodeStart2[f2it]; i2 < nodeStart2[f2it + 1]; i2++) {
+                    size_t idx2 = (size_t)idx2v[i2];
+                    if (!free2[idx2]) continue;    // vbMatched2 (never set) || pMP2, or bOnlyStereo && !bStereo2
+                    const bool bStereo2 = stereo2 && stereo2[idx2];
+                    const int dist = desc_distance(desc1 + idx1 * 32, desc2 + idx2 * 32);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    const orc_keypoint& kp2 = keys2[idx2];
+                    if (!bStereo1 && !bStereo2) {    // && !pKF1->mpCamera2
+                        const float distex = ep[0] - kp2.x;
+                        const float distey = ep[1] - kp2.y;
+                        if (distex * distex + distey * distey < 100 * mvScaleFactors[kp2.octave]) continue;
+                    }
+                    if (bCoarse || pinhole_epipolar_constrain(F12, kp1, kp2, mvLevelSigma2[kp2.octave])) {
+                        bestIdx2 = (int)idx2;
+                        bestDist = dist;
+                    }
+                }
+                if (bestIdx2 >= 0) {
+                    const orc_keypoint& kp2 = keys2[bestIdx2];
+                    vMatches12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (checkOrientation) {
+                        float rot = kp1.angle - kp2.angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back((int)idx1);
+                    }
+                }
+            }
+            f1it++;
+            f2it++;
+        } else if (nodeIds1[f1it] < nodeIds2[f2it]) {
+            f1it = (int)(std::lower_bound(nodeIds1, nodeIds1 + nodes1, nodeIds2[f2it]) - nodeIds1);
+        } else {
+            f2it = (int)(std::lower_bound(nodeIds2, nodeIds2 + nodes2, nodeIds1[f1it]) - nodeIds2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                vMatches12[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 // ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764) + ComputeThreeMaxima (:2061-2102) ----------------------
 // F1 / F2 are monocular frames (Nleft == -1); the grid is F2's.  vMatchedDistance / vnMatches21 make the loop order
 // dependent (a later keypoint steals a match only with a strictly smaller distance, and matched candidates with a

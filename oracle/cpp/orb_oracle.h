@@ -186,6 +186,22 @@ int orc_search_by_bow(const uint8_t* descKF, const float* angleKF, const uint8_t
                       const float* angleF, int nF, int nleftF, const int32_t* fNodeIds, const int32_t* fNodeStart,
                       const int32_t* fIdx, int fNodes, float mfNNratio, int checkOrientation, int32_t* matches);
 
+/* ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) (ORBmatcher.cc:766-906).  validN[i] = MapPoint i exists, is not bad and
+ * (stereo-camera key frames) i < mvKeysUn.size().  matches12[n1] = idx2 or -1.  Returns nmatches. */
+int orc_search_by_bow_kf(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, int n1, const int32_t* nodeIds1,
+                         const int32_t* nodeStart1, const int32_t* idx1, int nodes1, const uint8_t* desc2, const float* angle2,
+                         const uint8_t* valid2, const int32_t* nodeIds2, const int32_t* nodeStart2, const int32_t* idx2,
+                         int nodes2, float mfNNratio, int checkOrientation, int32_t* matches12);
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, vMatchedPairs, bOnlyStereo, bCoarse) (ORBmatcher.cc:908-1153) for key frames
+ * without a second camera, Pinhole::epipolarConstrain (Pinhole.cpp:102-124) with F12 given row-major.  freeN[i] = no MapPoint
+ * (and a stereo measurement when bOnlyStereo); stereoN[i] = mvuRight[i] >= 0 (nullable).  matches12[n1] = vMatches12. */
+int orc_search_for_triangulation(const orc_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1, const uint8_t* stereo1,
+                                 int n1, const int32_t* nodeIds1, const int32_t* nodeStart1, const int32_t* idx1, int nodes1,
+                                 const orc_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
+                                 const int32_t* nodeIds2, const int32_t* nodeStart2, const int32_t* idx2, int nodes2,
+                                 const float* F12, const float* ep, const float* mvScaleFactors, const float* mvLevelSigma2,
+                                 int bCoarse, int checkOrientation, int32_t* matches12);
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) for
  * monocular frames.  prevMatchedXY: n1 (x, y) pairs, updated in place (:759-761); vnMatches12: n1 ints. Returns nmatches. */
 int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, const orc_keypoint* keys2,

@@ -391,6 +391,51 @@ def search_by_projection_keyframe(keys_un, desc, occupied, bounds, scale_factors
     return m, owner[:n], int(nm)
 
 
+def search_by_bow_kf(desc1, angle1, valid1, fv1, desc2, angle2, valid2, fv2, nn_ratio=0.75, check_orientation=True):
+    """ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) (ORBmatcher.cc:766-906).  -> (matches12 int32 (n1,), nmatches)"""
+    d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    a1, a2 = np.ascontiguousarray(angle1, np.float32), np.ascontiguousarray(angle2, np.float32)
+    v1, v2 = np.ascontiguousarray(valid1, np.uint8), np.ascontiguousarray(valid2, np.uint8)
+    a = [np.ascontiguousarray(x, np.int32) for x in fv1]
+    b = [np.ascontiguousarray(x, np.int32) for x in fv2]
+    m = np.empty(max(len(d1), 1), np.int32)
+    L = lib()
+    L.orc_search_by_bow_kf.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                       C.c_float, C.c_int, C.c_void_p]
+    L.orc_search_by_bow_kf.restype = C.c_int
+    nm = L.orc_search_by_bow_kf(_p(d1), _p(a1), _p(v1), len(d1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]), _p(d2), _p(a2), _p(v2),
+                                _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), float(nn_ratio), int(bool(check_orientation)), _p(m))
+    return m[:len(d1)].copy(), int(nm)
+
+
+def search_for_triangulation(keys1, desc1, free1, stereo1, fv1, keys2, desc2, free2, stereo2, fv2, f12, ep, scale_factors,
+                             level_sigma2, coarse=False, check_orientation=True):
+    """ORBmatcher::SearchForTriangulation (ORBmatcher.cc:908-1153), one camera per key frame.  -> (vMatches12, nmatches)"""
+    k1, k2 = np.ascontiguousarray(keys1, KP_DTYPE), np.ascontiguousarray(keys2, KP_DTYPE)
+    d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    f1, f2 = np.ascontiguousarray(free1, np.uint8), np.ascontiguousarray(free2, np.uint8)
+    s1 = None if stereo1 is None else np.ascontiguousarray(stereo1, np.uint8)
+    s2 = None if stereo2 is None else np.ascontiguousarray(stereo2, np.uint8)
+    a = [np.ascontiguousarray(x, np.int32) for x in fv1]
+    b = [np.ascontiguousarray(x, np.int32) for x in fv2]
+    F = np.ascontiguousarray(f12, np.float32).reshape(9)
+    e = np.ascontiguousarray(ep, np.float32).reshape(2)
+    sf, sg = np.ascontiguousarray(scale_factors, np.float32), np.ascontiguousarray(level_sigma2, np.float32)
+    m = np.empty(max(len(k1), 1), np.int32)
+    L = lib()
+    L.orc_search_for_triangulation.argtypes = [C.c_void_p] * 4 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 7 + \
+        [C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_int, C.c_void_p]
+    L.orc_search_for_triangulation.restype = C.c_int
+    nm = L.orc_search_for_triangulation(_p(k1), _p(d1), _p(f1), None if s1 is None else _p(s1), len(k1), _p(a[0]), _p(a[1]),
+                                        _p(a[2]), len(a[0]), _p(k2), _p(d2), _p(f2), None if s2 is None else _p(s2), _p(b[0]),
+                                        _p(b[1]), _p(b[2]), len(b[0]), _p(F), _p(e), _p(sf), _p(sg), int(bool(coarse)),
+                                        int(bool(check_orientation)), _p(m))
+    return m[:len(k1)].copy(), int(nm)
+
+
 def search_by_projection_sim3(keys_un, desc, occupied, bounds, scale_factors, pts, th=10.0, ratio_hamming=1.0):
     """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (ORBmatcher.cc:428-533, :535-647).
     -> (match, owner, nmatches)"""

@@ -36,6 +36,16 @@ int launch_search_bow(const uint8_t* descKF, const float* angleKF, const uint8_t
                       const int* nleftF, const int* fIds, const int* fStart, const int* fIdx, const int* fNodes, int cap,
                       int nodeCap, int npairs, float nnRatio, int checkOrientation, int* matches, int* nMatches,
                       cudaStream_t st);
+int launch_search_bow_kf(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, const int* ids1, const int* start1,
+                         const int* idx1, const int* nodes1, const uint8_t* desc2, const float* angle2, const uint8_t* valid2,
+                         const int* ids2, const int* start2, const int* idx2, const int* nodes2, int cap, int nodeCap, int npairs,
+                         float nnRatio, int checkOrientation, int* matches, int* nMatches, cudaStream_t st);
+int launch_search_triangulation(const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1, const uint8_t* stereo1,
+                                const int* ids1, const int* start1, const int* idx1, const int* nodes1,
+                                const orbfe_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
+                                const int* ids2, const int* start2, const int* idx2, const int* nodes2, const float* F12,
+                                const float* ep, const float* scale, const float* sigma2, int nlevels, int cap, int nodeCap,
+                                int npairs, int coarse, int checkOrientation, int* matches, int* nMatches, cudaStream_t st);
 size_t search_kf_smem_bytes(int cap);
 int launch_search_kf(const float bounds[4], const float* scale, const float* invSigma2, int nlevels, float th, float distTh,
                      float bf, int blocks, int chi2, const orbfe_keypoint* keys, const uint8_t* desc, const float* uRight,
@@ -1143,7 +1153,7 @@ struct orbfe_matcher {
     std::mutex mu;
     std::string err;
     DevBuf dQ, dT, dIdx, dDist, dNq, dNt;
-    DevBuf dS[14];    // staging of the orbfe_search_by_projection* calls
+    DevBuf dS[24];    // staging of the orbfe_search_* calls
     float lastMs = 0;
     int lastLaunches = 0;
     void* aux = nullptr;               // state of the sharded matcher (orbfe_sharded.cu), freed by auxFree at destroy
@@ -1527,6 +1537,129 @@ int orbfe_search_by_bow_batch(orbfe_matcher* m, const uint8_t* desc_kf, const fl
     m->lastLaunches = launches;
     if (!outDev) {
         if (cap) ORBFE_MCUDA(m, cudaMemcpyAsync(matches, dM, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+// host -> device staging of the nullable inputs of a matcher call into dS[0 .. count); leaves device pointers in ptrs[]
+static int stage_matcher_inputs(orbfe_matcher* m, const void** ptrs, const size_t* bytes, int count, cudaStream_t st) {
+    for (int i = 0; i < count; i++) {
+        if (!ptrs[i]) continue;
+        ORBFE_MCUDA(m, m->dS[i].reserve(std::max<size_t>(bytes[i], 16)));
+        if (bytes[i]) ORBFE_MCUDA(m, cudaMemcpyAsync(m->dS[i].p, ptrs[i], bytes[i], cudaMemcpyHostToDevice, st));
+        ptrs[i] = m->dS[i].p;
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_bow_kf_batch(orbfe_matcher* m, const uint8_t* desc1, const float* angle1, const uint8_t* valid1,
+                                 const int32_t* node_ids1, const int32_t* node_start1, const int32_t* idx1,
+                                 const int32_t* nnodes1, const uint8_t* desc2, const float* angle2, const uint8_t* valid2,
+                                 const int32_t* node_ids2, const int32_t* node_start2, const int32_t* idx2,
+                                 const int32_t* nnodes2, int cap, int node_cap, int npairs, float nn_ratio, int check_orientation,
+                                 int32_t* matches12, int32_t* nmatches, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (npairs < 0 || cap < 0 || node_cap < 0) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (npairs == 0) return ORBFE_OK;
+    if (!nnodes1 || !nnodes2 || !node_start1 || !node_start2 || (node_cap > 0 && (!node_ids1 || !node_ids2)) ||
+        (cap > 0 && (!desc1 || !angle1 || !valid1 || !idx1 || !desc2 || !angle2 || !valid2 || !idx2 || !matches12)))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (cap > 65535 || 2 * search_bow_smem_bytes(cap) > 200 * 1024) return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large", cap);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)npairs;
+    const void* dIn[14] = {desc1, angle1, valid1, node_ids1, node_start1, idx1, nnodes1,
+                           desc2, angle2, valid2, node_ids2, node_start2, idx2, nnodes2};
+    const size_t inBytes[14] = {F * cap * 32, F * cap * 4, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4,
+                                F * cap * 32, F * cap * 4, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4};
+    if (!inDev) {
+        const int rc = stage_matcher_inputs(m, dIn, inBytes, 14, st);
+        if (rc != ORBFE_OK) return rc;
+    }
+    int32_t *dM = matches12, *dCount = nmatches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dIdx.reserve(std::max<size_t>(F * cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dDist.reserve(std::max<size_t>(F * 4, 16)));
+        dM = (int32_t*)m->dIdx.p;
+        dCount = (int32_t*)m->dDist.p;
+    }
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_search_bow_kf(
+        (const uint8_t*)dIn[0], (const float*)dIn[1], (const uint8_t*)dIn[2], (const int*)dIn[3], (const int*)dIn[4],
+        (const int*)dIn[5], (const int*)dIn[6], (const uint8_t*)dIn[7], (const float*)dIn[8], (const uint8_t*)dIn[9],
+        (const int*)dIn[10], (const int*)dIn[11], (const int*)dIn[12], (const int*)dIn[13], cap, node_cap, npairs, nn_ratio,
+        check_orientation, dM, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        if (cap) ORBFE_MCUDA(m, cudaMemcpyAsync(matches12, dM, F * cap * 4, cudaMemcpyDeviceToHost, st));
+        if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1,
+                                         const uint8_t* stereo1, const int32_t* node_ids1, const int32_t* node_start1,
+                                         const int32_t* idx1, const int32_t* nnodes1, const orbfe_keypoint* keys2,
+                                         const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
+                                         const int32_t* node_ids2, const int32_t* node_start2, const int32_t* idx2,
+                                         const int32_t* nnodes2, int cap, int node_cap, int npairs, const float* f12,
+                                         const float* epipole, const float* scale_factors, const float* level_sigma2,
+                                         int nlevels, int coarse, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                         unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (npairs < 0 || cap < 0 || node_cap < 0 || nlevels < 1 || nlevels > ORBFE_MAX_LEVELS)
+        return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (npairs == 0) return ORBFE_OK;
+    if (!nnodes1 || !nnodes2 || !node_start1 || !node_start2 || !scale_factors || !level_sigma2 || !epipole ||
+        (!coarse && !f12) || (node_cap > 0 && (!node_ids1 || !node_ids2)) ||
+        (cap > 0 && (!keys1 || !desc1 || !free1 || !idx1 || !keys2 || !desc2 || !free2 || !idx2 || !matches12)))
+        return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (cap > 65535 || search_bow_smem_bytes(cap) > 200 * 1024) return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large", cap);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t F = (size_t)npairs;
+    const void* dIn[18] = {keys1, desc1, free1, stereo1, node_ids1, node_start1, idx1, nnodes1,
+                           keys2, desc2, free2, stereo2, node_ids2, node_start2, idx2, nnodes2, f12, epipole};
+    const size_t kb = F * cap * sizeof(orbfe_keypoint);
+    const size_t inBytes[18] = {kb, F * cap * 32, F * cap, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4,
+                                kb, F * cap * 32, F * cap, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4,
+                                F * 36, F * 8};
+    if (!inDev) {
+        const int rc = stage_matcher_inputs(m, dIn, inBytes, 18, st);
+        if (rc != ORBFE_OK) return rc;
+    }
+    int32_t *dM = matches12, *dCount = nmatches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dIdx.reserve(std::max<size_t>(F * cap * 4, 16)));
+        ORBFE_MCUDA(m, m->dDist.reserve(std::max<size_t>(F * 4, 16)));
+        dM = (int32_t*)m->dIdx.p;
+        dCount = (int32_t*)m->dDist.p;
+    }
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_search_triangulation(
+        (const orbfe_keypoint*)dIn[0], (const uint8_t*)dIn[1], (const uint8_t*)dIn[2], (const uint8_t*)dIn[3], (const int*)dIn[4],
+        (const int*)dIn[5], (const int*)dIn[6], (const int*)dIn[7], (const orbfe_keypoint*)dIn[8], (const uint8_t*)dIn[9],
+        (const uint8_t*)dIn[10], (const uint8_t*)dIn[11], (const int*)dIn[12], (const int*)dIn[13], (const int*)dIn[14],
+        (const int*)dIn[15], (const float*)dIn[16], (const float*)dIn[17], scale_factors, level_sigma2, nlevels, cap, node_cap,
+        npairs, coarse ? 1 : 0, check_orientation, dM, dCount, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        if (cap) ORBFE_MCUDA(m, cudaMemcpyAsync(matches12, dM, F * cap * 4, cudaMemcpyDeviceToHost, st));
         if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
     }
     ORBFE_MCUDA(m, cudaStreamSynchronize(st));

@@ -327,6 +327,73 @@ class ORBmatcher:
             ptr(desc_f), ptr(angle_f), ptr(n_f), ptr(nleft_f), ptr(f_ids), ptr(f_start), ptr(f_idx), ptr(f_nnodes), int(cap),
             int(node_cap), int(npairs), self.mfNNratio, int(self.mbCheckOrientation), ptr(matches), ptr(nmatches), int(flags)))
 
+    @staticmethod
+    def _pad(a, n, dt, fill=0):
+        a = np.asarray(a)
+        out = np.full((n,) + a.shape[1:], fill, dt)
+        out[:len(a)] = a
+        return out
+
+    def SearchByBoWKeyFrames(self, desc1, angle1, valid1, fv1, desc2, angle2, valid2, fv2):
+        """ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vpMatches12) (ORBmatcher.cc:766-906).  validN[i] = MapPoint i
+        exists, is not bad (and i < mvKeysUn.size() for stereo-camera key frames).  -> (nmatches, matches12 int32 (n1,))"""
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        n1 = len(d1)
+        cap = max(n1, len(d2), 1)
+        ncap = max(len(fv1[0]), len(fv2[0]), 1)
+        pad = self._pad
+        args = [pad(d1, cap, np.uint8), pad(angle1, cap, np.float32), pad(valid1, cap, np.uint8), pad(fv1[0], ncap, np.int32),
+                pad(fv1[1], ncap + 1, np.int32), pad(fv1[2], cap, np.int32), np.array([len(fv1[0])], np.int32),
+                pad(d2, cap, np.uint8), pad(angle2, cap, np.float32), pad(valid2, cap, np.uint8), pad(fv2[0], ncap, np.int32),
+                pad(fv2[1], ncap + 1, np.int32), pad(fv2[2], cap, np.int32), np.array([len(fv2[0])], np.int32)]
+        m, nm = np.full(cap, -1, np.int32), np.zeros(1, np.int32)
+        self.search_by_bow_kf_batch_raw(*args, cap, ncap, 1, m, nm)
+        return int(nm[0]), m[:n1]
+
+    def search_by_bow_kf_batch_raw(self, desc1, angle1, valid1, ids1, start1, idx1, nnodes1, desc2, angle2, valid2, ids2, start2,
+                                   idx2, nnodes2, cap, node_cap, npairs, matches12, nmatches, flags=0):
+        self._bf._check(_lib.lib().orbfe_search_by_bow_kf_batch(
+            self._bf._h, ptr(desc1), ptr(angle1), ptr(valid1), ptr(ids1), ptr(start1), ptr(idx1), ptr(nnodes1), ptr(desc2),
+            ptr(angle2), ptr(valid2), ptr(ids2), ptr(start2), ptr(idx2), ptr(nnodes2), int(cap), int(node_cap), int(npairs),
+            self.mfNNratio, int(self.mbCheckOrientation), ptr(matches12), ptr(nmatches), int(flags)))
+
+    def SearchForTriangulation(self, keys1, desc1, free1, fv1, keys2, desc2, free2, fv2, f12, epipole, scale_factors,
+                               level_sigma2, stereo1=None, stereo2=None, bCoarse=False):
+        """ORBmatcher::SearchForTriangulation(pKF1, pKF2, vMatchedPairs, bOnlyStereo, bCoarse) (ORBmatcher.cc:908-1153) for key
+        frames with one camera.  freeN[i] = no MapPoint yet (and a stereo measurement when bOnlyStereo); f12 = F12 (3 x 3).
+        -> (nmatches, vMatchedPairs int32 (k, 2), vMatches12 int32 (n1,))"""
+        k1, k2 = np.ascontiguousarray(keys1, KP_DTYPE), np.ascontiguousarray(keys2, KP_DTYPE)
+        n1 = len(k1)
+        cap = max(n1, len(k2), 1)
+        ncap = max(len(fv1[0]), len(fv2[0]), 1)
+        pad = self._pad
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        args = [pad(k1, cap, KP_DTYPE), pad(d1, cap, np.uint8), pad(free1, cap, np.uint8),
+                None if stereo1 is None else pad(stereo1, cap, np.uint8), pad(fv1[0], ncap, np.int32),
+                pad(fv1[1], ncap + 1, np.int32), pad(fv1[2], cap, np.int32), np.array([len(fv1[0])], np.int32),
+                pad(k2, cap, KP_DTYPE), pad(d2, cap, np.uint8), pad(free2, cap, np.uint8),
+                None if stereo2 is None else pad(stereo2, cap, np.uint8), pad(fv2[0], ncap, np.int32),
+                pad(fv2[1], ncap + 1, np.int32), pad(fv2[2], cap, np.int32), np.array([len(fv2[0])], np.int32)]
+        m, nm = np.full(cap, -1, np.int32), np.zeros(1, np.int32)
+        self.search_for_triangulation_batch_raw(*args, cap, ncap, 1, np.ascontiguousarray(f12, np.float32).reshape(1, 9),
+                                                np.ascontiguousarray(epipole, np.float32).reshape(1, 2), scale_factors,
+                                                level_sigma2, bCoarse, m, nm)
+        i1 = np.nonzero(m[:n1] >= 0)[0]
+        return int(nm[0]), np.stack([i1, m[i1]], axis=1).astype(np.int32), m[:n1]
+
+    def search_for_triangulation_batch_raw(self, keys1, desc1, free1, stereo1, ids1, start1, idx1, nnodes1, keys2, desc2, free2,
+                                           stereo2, ids2, start2, idx2, nnodes2, cap, node_cap, npairs, f12, epipole,
+                                           scale_factors, level_sigma2, coarse, matches12, nmatches, flags=0):
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        sg = np.ascontiguousarray(level_sigma2, np.float32)
+        self._bf._check(_lib.lib().orbfe_search_for_triangulation_batch(
+            self._bf._h, ptr(keys1), ptr(desc1), ptr(free1), ptr(stereo1), ptr(ids1), ptr(start1), ptr(idx1), ptr(nnodes1),
+            ptr(keys2), ptr(desc2), ptr(free2), ptr(stereo2), ptr(ids2), ptr(start2), ptr(idx2), ptr(nnodes2), int(cap),
+            int(node_cap), int(npairs), ptr(f12), ptr(epipole), ptr(sf), ptr(sg), sf.shape[0], int(bool(coarse)),
+            int(self.mbCheckOrientation), ptr(matches12), ptr(nmatches), int(flags)))
+
     def SearchForInitialization(self, keys1_un, desc1, keys2_un, desc2, bounds, vbPrevMatched, windowSize=10):
         """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) on
         monocular frames given as arrays; bounds = F2's image bounds.  vbPrevMatched: (n1, 2) float32.

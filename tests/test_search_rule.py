@@ -865,3 +865,194 @@ def test_oracle_search_by_sim3_vs_python(oracle):
         np.testing.assert_array_equal(m12, r12)
         assert nf == (r12 >= 0).sum() and nf > 30
         assert (v1 >= 0).sum() > nf    # some one-directional matches fail the agreement
+
+
+# ---- key frame <-> key frame through the vocabulary: ORBmatcher.cc:766-906 (SearchByBoW) and :908-1153 (SearchForTriangulation)
+def _merge_nodes(fv1, fv2):
+    """the std::map merge of :789-877 / :959-1121: yields (features of node in KF1, features of node in KF2) per common node."""
+    ids1, st1, ix1 = fv1
+    ids2, st2, ix2 = fv2
+    a, b = 0, 0
+    while a != len(ids1) and b != len(ids2):
+        if ids1[a] == ids2[b]:
+            yield ix1[st1[a]:st1[a + 1]], ix2[st2[b]:st2[b + 1]]
+            a += 1
+            b += 1
+        elif ids1[a] < ids2[b]:
+            a = int(np.searchsorted(ids1, ids2[b], side="left"))
+        else:
+            b = int(np.searchsorted(ids2, ids1[a], side="left"))
+
+
+def _py_three_maxima(rot_hist):
+    max1 = max2 = max3 = 0
+    ind1 = ind2 = ind3 = -1
+    for i in range(30):
+        s = len(rot_hist[i])
+        if s > max1:
+            max3, max2, max1 = max2, max1, s
+            ind3, ind2, ind1 = ind2, ind1, i
+        elif s > max2:
+            max3, max2 = max2, s
+            ind3, ind2 = ind2, i
+        elif s > max3:
+            max3, ind3 = s, i
+    if np.float32(max2) < np.float32(0.1) * np.float32(max1):
+        ind2 = ind3 = -1
+    elif np.float32(max3) < np.float32(0.1) * np.float32(max1):
+        ind3 = -1
+    return ind1, ind2, ind3
+
+
+def _py_bin(a1, a2):
+    f32 = np.float32
+    rot = f32(f32(a1) - f32(a2))
+    if rot < 0.0:
+        rot = f32(rot + f32(360.0))
+    v = float(f32(rot * (f32(1.0) / f32(30))))
+    b = int(math.floor(v + 0.5))
+    return 0 if b == 30 else b
+
+
+def _py_search_bow_kf(d1, a1, v1, fv1, d2, a2, v2, fv2, ratio, check_ori):
+    f32 = np.float32
+    bits1, bits2 = np.unpackbits(d1, axis=1), np.unpackbits(d2, axis=1)
+    m12 = np.full(len(d1), -1, np.int64)
+    matched2 = np.zeros(len(d2), bool)
+    rot_hist = [[] for _ in range(30)]
+    nm = 0
+    for n1, n2 in _merge_nodes(fv1, fv2):
+        for idx1 in n1:
+            if not v1[idx1]:
+                continue
+            best1, best_idx2, best2 = 256, -1, 256
+            for idx2 in n2:
+                if matched2[idx2] or not v2[idx2]:
+                    continue
+                d = int((bits1[idx1] != bits2[idx2]).sum())
+                if d < best1:
+                    best2, best1, best_idx2 = best1, d, idx2
+                elif d < best2:
+                    best2 = d
+            if best1 < 50 and f32(best1) < f32(f32(ratio) * f32(best2)):
+                m12[idx1] = best_idx2
+                matched2[best_idx2] = True
+                if check_ori:
+                    rot_hist[_py_bin(a1[idx1], a2[best_idx2])].append(idx1)
+                nm += 1
+    if check_ori:
+        keep = _py_three_maxima(rot_hist)
+        for i in range(30):
+            if i not in keep:
+                for idx1 in rot_hist[i]:
+                    m12[idx1] = -1
+                    nm -= 1
+    return m12, nm
+
+
+def _py_search_tri(k1, d1, free1, st1, fv1, k2, d2, free2, st2, fv2, F, ep, scale, sigma2, coarse, check_ori):
+    f32 = np.float32
+    F = np.asarray(F, f32).reshape(3, 3)
+    bits1, bits2 = np.unpackbits(d1, axis=1), np.unpackbits(d2, axis=1)
+    m12 = np.full(len(k1), -1, np.int64)
+    rot_hist = [[] for _ in range(30)]
+    nm = 0
+
+    def constrain(kp1, kp2, unc):
+        x1, y1, x2, y2 = f32(kp1["x"]), f32(kp1["y"]), f32(kp2["x"]), f32(kp2["y"])
+        a = f32(f32(f32(x1 * F[0, 0]) + f32(y1 * F[1, 0])) + F[2, 0])
+        b = f32(f32(f32(x1 * F[0, 1]) + f32(y1 * F[1, 1])) + F[2, 1])
+        c = f32(f32(f32(x1 * F[0, 2]) + f32(y1 * F[1, 2])) + F[2, 2])
+        num = f32(f32(f32(a * x2) + f32(b * y2)) + c)
+        den = f32(f32(a * a) + f32(b * b))
+        if den == 0:
+            return False
+        dsqr = f32(f32(num * num) / den)
+        return float(dsqr) < 3.84 * float(f32(unc))
+    for n1, n2 in _merge_nodes(fv1, fv2):
+        for idx1 in n1:
+            if not free1[idx1]:
+                continue
+            s1 = st1 is not None and bool(st1[idx1])
+            best_dist, best_idx2 = 50, -1
+            for idx2 in n2:
+                if not free2[idx2]:
+                    continue
+                s2 = st2 is not None and bool(st2[idx2])
+                d = int((bits1[idx1] != bits2[idx2]).sum())
+                if d > 50 or d > best_dist:
+                    continue
+                kp2 = k2[idx2]
+                if not s1 and not s2:
+                    ex, ey = f32(f32(ep[0]) - f32(kp2["x"])), f32(f32(ep[1]) - f32(kp2["y"]))
+                    if f32(f32(ex * ex) + f32(ey * ey)) < f32(f32(100) * f32(scale[kp2["octave"]])):
+                        continue
+                if coarse or constrain(k1[idx1], kp2, sigma2[kp2["octave"]]):
+                    best_idx2, best_dist = idx2, d
+            if best_idx2 >= 0:
+                m12[idx1] = best_idx2
+                nm += 1
+                if check_ori:
+                    rot_hist[_py_bin(k1["angle"][idx1], k2["angle"][best_idx2])].append(idx1)
+    if check_ori:
+        keep = _py_three_maxima(rot_hist)
+        for i in range(30):
+            if i not in keep:
+                for idx1 in rot_hist[i]:
+                    m12[idx1] = -1
+                    nm -= 1
+    return m12, nm
+
+
+def kf_pair_case(oracle, seed, w=320, h=240, nf=500):
+    """KF1 = the current frame, KF2 = the previous one (image shifted by (+3, +2)): arrays for both BoW matchers."""
+    cur = scenes.make("texture", w, h, seed)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _, k1, d1 = ex(cur)
+    _, k2, d2 = ex(scenes.previous_frame(cur, seed))
+    k1, k2 = k1.copy(), k2.copy()
+    r1, r2 = scenes.rand_u32(len(k1), seed + 3), scenes.rand_u32(len(k2), seed + 4)
+    k1["angle"] = np.where(r1 % 9 == 0, (k1["angle"] + 97.0) % 360.0, k1["angle"])    # rotation-histogram losers
+    has1, has2 = (r1 % 5 != 0), (r2 % 5 != 0)           # feature has a (good) MapPoint
+    st1, st2 = (r1 % 3 == 0).astype(np.uint8), (r2 % 3 == 1).astype(np.uint8)    # mvuRight >= 0
+    scale = ex.scale.astype(np.float32)
+    # pure image translation t = (3, 2, 0): F12 = [t]x with K = I; the epipole is put inside the image to exercise its gate
+    F = np.array([[0, 0, 2], [0, 0, -3], [-2, 3, 0]], np.float32)
+    return dict(k1=k1, d1=d1, k2=k2, d2=d2, has1=has1.astype(np.uint8), has2=has2.astype(np.uint8), st1=st1, st2=st2,
+                fv1=scenes.feature_vector(d1), fv2=scenes.feature_vector(d2), F=F, ep=np.array([w * 0.4, h * 0.45], np.float32),
+                scale=scale, sigma2=(scale * scale).astype(np.float32))
+
+
+def test_oracle_search_by_bow_kf_vs_python(oracle):
+    for seed, ratio, ori in ((6701, 0.75, True), (6702, 0.9, True), (6703, 0.6, False)):
+        c = kf_pair_case(oracle, seed)
+        a1, a2 = c["k1"]["angle"].astype(np.float32), c["k2"]["angle"].astype(np.float32)
+        m, nm = oracle.search_by_bow_kf(c["d1"], a1, c["has1"], c["fv1"], c["d2"], a2, c["has2"], c["fv2"], ratio, ori)
+        ref, rnm = _py_search_bow_kf(c["d1"], a1, c["has1"], c["fv1"], c["d2"], a2, c["has2"], c["fv2"], ratio, ori)
+        np.testing.assert_array_equal(m, ref)
+        assert nm == rnm and nm > 40
+        got = m[m >= 0]
+        assert len(np.unique(got)) == len(got) and c["has2"][got].all() and c["has1"][m >= 0].all()
+
+
+def test_oracle_search_for_triangulation_vs_python(oracle):
+    for seed, coarse, ori, stereo in ((6801, False, True, False), (6802, True, True, False), (6803, False, False, True),
+                                      (6804, False, True, True)):
+        c = kf_pair_case(oracle, seed)
+        free1, free2 = 1 - c["has1"], 1 - c["has2"]
+        free1[::2], free2[::3] = 1, 1    # most features are still without a MapPoint in local mapping
+        s1, s2 = (c["st1"], c["st2"]) if stereo else (None, None)
+        args = (c["k1"], c["d1"], free1, s1, c["fv1"], c["k2"], c["d2"], free2, s2, c["fv2"], c["F"], c["ep"], c["scale"],
+                c["sigma2"], coarse, ori)
+        m, nm = oracle.search_for_triangulation(*args)
+        ref, rnm = _py_search_tri(*args)
+        np.testing.assert_array_equal(m, ref)
+        assert nm == rnm and nm > 30
+        assert free1[m >= 0].all() and free2[m[m >= 0]].all()
+    # the constraint matters: coarse keeps more pairs
+    c = kf_pair_case(oracle, 6811)
+    free = np.ones(max(len(c["k1"]), len(c["k2"])), np.uint8)
+    base = (c["k1"], c["d1"], free, None, c["fv1"], c["k2"], c["d2"], free, None, c["fv2"], c["F"], c["ep"], c["scale"], c["sigma2"])
+    strict = oracle.search_for_triangulation(*base, False, False)[1]
+    loose = oracle.search_for_triangulation(*base, True, False)[1]
+    assert 0 < strict < loose
