@@ -258,6 +258,15 @@ int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint*
                                          const float* epipole, const float* scale_factors, const float* level_sigma2,
                                          int nlevels, int coarse, int check_orientation, int32_t* matches12, int32_t* nmatches,
                                          unsigned flags);
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:331-401) for npoints MapPoints per call.  desc = the rows that the
+ * reference gathers into vDescriptors (observations in mObservations order, left index before right index, bad key frames
+ * skipped), concatenated: point p owns rows [offsets[p], offsets[p + 1]), offsets[0] = 0, offsets[npoints] = total_rows.
+ * best_idx[p] = BestIdx (row inside the point's block: the first row with the smallest median distance, median =
+ * sorted[int(0.5 * (N - 1))] over the N distances of the row including its own 0), best_median[p] (nullable) = that median,
+ * out_desc[p*32 ...] (nullable) = the chosen row = the new mDescriptor.  A point without rows, or with more than max_n rows,
+ * gets best_idx = -1 and its out_desc row is left as it was (the reference returns before touching mDescriptor). */
+int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* offsets, int npoints, int64_t total_rows,
+                                  int max_n, int32_t* best_idx, int32_t* best_median, uint8_t* out_desc, unsigned flags);
 /* ---- the per-frame tracking matcher: ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th,
  * bMono) with SearchByProjectionThread and the rotation histogram (ORBmatcher.cc:1683-1921), and
  * ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1923-2059), both with

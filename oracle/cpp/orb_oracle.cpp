@@ -2033,6 +2033,34 @@ int orc_search_for_triangulation(const orc_keypoint* keys1, const uint8_t* desc1
     return nmatches;
 }
 
+// ---- MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:331-401), after the gathering of vDescriptors ------------------------
+int orc_distinctive_descriptor(const uint8_t* vDescriptors, int Nin, int32_t* bestMedianOut) {
+    const size_t N = (size_t)Nin;
+    std::vector<float> Distances(N * N);    // float Distances[N][N]
+    for (size_t i = 0; i < N; i++) {
+        Distances[i * N + i] = 0;
+        for (size_t j = i + 1; j < N; j++) {
+            int distij = desc_distance(vDescriptors + i * 32, vDescriptors + j * 32);
+            Distances[i * N + j] = distij;
+            Distances[j * N + i] = distij;
+        }
+    }
+    // Take the descriptor with least median distance to the rest
+    int BestMedian = INT_MAX;
+    int BestIdx = 0;
+    for (size_t i = 0; i < N; i++) {
+        std::vector<int> vDists(Distances.begin() + i * N, Distances.begin() + i * N + N);
+        std::sort(vDists.begin(), vDists.end());
+        int median = vDists[0.5 * (N - 1)];
+        if (median < BestMedian) {
+            BestMedian = median;
+            BestIdx = (int)i;
+        }
+    }
+    if (bestMedianOut) *bestMedianOut = BestMedian;
+    return BestIdx;
+}
+
 // ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:649-764) + ComputeThreeMaxima (:2061-2102) ----------------------
 // F1 / F2 are monocular frames (Nleft == -1); the grid is F2's.  vMatchedDistance / vnMatches21 make the loop order
 // dependent (a later keypoint steals a match only with a strictly smaller distance, and matched candidates with a

@@ -202,6 +202,10 @@ int orc_search_for_triangulation(const orc_keypoint* keys1, const uint8_t* desc1
                                  const float* F12, const float* ep, const float* mvScaleFactors, const float* mvLevelSigma2,
                                  int bCoarse, int checkOrientation, int32_t* matches12);
 
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:331-401) on one MapPoint's N gathered descriptors (N >= 1).
+ * Returns BestIdx; *bestMedian (nullable) = BestMedian. */
+int orc_distinctive_descriptor(const uint8_t* vDescriptors, int N, int32_t* bestMedian);
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) for
  * monocular frames.  prevMatchedXY: n1 (x, y) pairs, updated in place (:759-761); vnMatches12: n1 ints. Returns nmatches. */
 int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, const orc_keypoint* keys2,

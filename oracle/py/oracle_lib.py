@@ -436,6 +436,26 @@ def search_for_triangulation(keys1, desc1, free1, stereo1, fv1, keys2, desc2, fr
     return m[:len(k1)].copy(), int(nm)
 
 
+def distinctive_descriptors(desc, offsets):
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:331-401) per block of rows.  -> (best_idx, best_median); -1 for
+    a point without rows."""
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    off = np.asarray(offsets, np.int64)
+    L = lib()
+    L.orc_distinctive_descriptor.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    L.orc_distinctive_descriptor.restype = C.c_int
+    bi, bm = np.full(len(off) - 1, -1, np.int32), np.full(len(off) - 1, -1, np.int32)
+    med = C.c_int32(0)
+    for p in range(len(off) - 1):
+        n = int(off[p + 1] - off[p])
+        if n <= 0:
+            continue
+        blk = np.ascontiguousarray(d[off[p]:off[p + 1]])
+        bi[p] = L.orc_distinctive_descriptor(_p(blk), n, C.byref(med))
+        bm[p] = med.value
+    return bi, bm
+
+
 def search_by_projection_sim3(keys_un, desc, occupied, bounds, scale_factors, pts, th=10.0, ratio_hamming=1.0):
     """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (ORBmatcher.cc:428-533, :535-647).
     -> (match, owner, nmatches)"""

@@ -91,6 +91,7 @@ SYMBOLS = {
     "orbfe_search_by_sim3_batch": (_i, [_vp] * 7 + [_i, _vp, _vp, _vp, _i, _vp, _vp, _i, C.c_float, _vp, _vp, _vp, _vp, _u]),
     "orbfe_search_by_bow_kf_batch": (_i, [_vp] * 15 + [_i, _i, _i, C.c_float, _i, _vp, _vp, _u]),
     "orbfe_search_for_triangulation_batch": (_i, [_vp] * 17 + [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _u]),
+    "orbfe_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, C.c_int64, _i, _vp, _vp, _vp, _u]),
     "orbfe_search_for_initialization_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, C.c_float, _i, _vp,
                                                    _vp, _vp, _u]),
     "orbfe_stereo_fisheye_matches_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp,

@@ -46,6 +46,9 @@ int launch_search_triangulation(const orbfe_keypoint* keys1, const uint8_t* desc
                                 const int* ids2, const int* start2, const int* idx2, const int* nodes2, const float* F12,
                                 const float* ep, const float* scale, const float* sigma2, int nlevels, int cap, int nodeCap,
                                 int npairs, int coarse, int checkOrientation, int* matches, int* nMatches, cudaStream_t st);
+size_t distinctive_smem_bytes(int maxN);
+int launch_distinctive(const uint8_t* desc, const int* offsets, int npoints, int maxN, int* bestIdx, int* bestMedian,
+                       uint8_t* outDesc, cudaStream_t st);
 size_t search_kf_smem_bytes(int cap);
 int launch_search_kf(const float bounds[4], const float* scale, const float* invSigma2, int nlevels, float th, float distTh,
                      float bf, int blocks, int chi2, const orbfe_keypoint* keys, const uint8_t* desc, const float* uRight,
@@ -1661,6 +1664,53 @@ int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint*
     if (!outDev) {
         if (cap) ORBFE_MCUDA(m, cudaMemcpyAsync(matches12, dM, F * cap * 4, cudaMemcpyDeviceToHost, st));
         if (nmatches) ORBFE_MCUDA(m, cudaMemcpyAsync(nmatches, dCount, F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    ORBFE_MCUDA(m, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
+    return ORBFE_OK;
+}
+
+int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* offsets, int npoints, int64_t total_rows,
+                                  int max_n, int32_t* best_idx, int32_t* best_median, uint8_t* out_desc, unsigned flags) {
+    if (!m) return ORBFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (npoints < 0 || total_rows < 0 || max_n < 1) return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
+    if (npoints == 0) return ORBFE_OK;
+    if (!offsets || !best_idx || (total_rows > 0 && !desc)) return set_merr(m, ORBFE_ERR_ARG, "null pointer");
+    if (distinctive_smem_bytes(max_n) > 200 * 1024)
+        return set_merr(m, ORBFE_ERR_ARG, "max_n %d too large for the shared-memory distance strips", max_n);
+    ORBFE_MCUDA(m, cudaSetDevice(m->device));
+    const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
+    cudaStream_t st = m->stream;
+    const size_t P = (size_t)npoints;
+    const void* dIn[2] = {desc, offsets};
+    const size_t inBytes[2] = {(size_t)total_rows * 32, (P + 1) * 4};
+    if (!inDev) {
+        if (offsets[0] != 0 || offsets[npoints] != total_rows) return set_merr(m, ORBFE_ERR_ARG, "offsets do not span total_rows");
+        const int rc = stage_matcher_inputs(m, dIn, inBytes, 2, st);
+        if (rc != ORBFE_OK) return rc;
+    }
+    int32_t *dIdx = best_idx, *dMed = best_median;
+    uint8_t* dOut = out_desc;
+    if (!outDev) {
+        ORBFE_MCUDA(m, m->dS[9].reserve(P * 4));
+        ORBFE_MCUDA(m, m->dS[10].reserve(P * 4));
+        ORBFE_MCUDA(m, m->dS[11].reserve(P * 32));
+        dIdx = (int32_t*)m->dS[9].p;
+        dMed = best_median ? (int32_t*)m->dS[10].p : nullptr;
+        dOut = out_desc ? (uint8_t*)m->dS[11].p : nullptr;
+        if (dOut) ORBFE_MCUDA(m, cudaMemcpyAsync(dOut, out_desc, P * 32, cudaMemcpyHostToDevice, st));    // rows of points without
+    }                                                                                                     // observations are kept
+    cudaEventRecord(m->ev[0], st);
+    const int launches = launch_distinctive((const uint8_t*)dIn[0], (const int*)dIn[1], npoints, max_n, dIdx, dMed, dOut, st);
+    cudaEventRecord(m->ev[1], st);
+    ORBFE_MCUDA(m, cudaGetLastError());
+    g_launches += launches;
+    m->lastLaunches = launches;
+    if (!outDev) {
+        ORBFE_MCUDA(m, cudaMemcpyAsync(best_idx, dIdx, P * 4, cudaMemcpyDeviceToHost, st));
+        if (best_median) ORBFE_MCUDA(m, cudaMemcpyAsync(best_median, dMed, P * 4, cudaMemcpyDeviceToHost, st));
+        if (out_desc) ORBFE_MCUDA(m, cudaMemcpyAsync(out_desc, dOut, P * 32, cudaMemcpyDeviceToHost, st));
     }
     ORBFE_MCUDA(m, cudaStreamSynchronize(st));
     cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);

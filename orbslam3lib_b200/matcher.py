@@ -394,6 +394,21 @@ class ORBmatcher:
             int(node_cap), int(npairs), ptr(f12), ptr(epipole), ptr(sf), ptr(sg), sf.shape[0], int(bool(coarse)),
             int(self.mbCheckOrientation), ptr(matches12), ptr(nmatches), int(flags)))
 
+    def ComputeDistinctiveDescriptors(self, desc, offsets, max_n=None, out_desc=None, flags=0):
+        """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:331-401) for a batch of MapPoints: point p owns the rows
+        [offsets[p], offsets[p + 1]) of desc (its observations' descriptors in the reference's gathering order).
+        -> (best_idx int32 (npoints,), best_median int32 (npoints,), descriptors uint8 (npoints, 32))"""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        off = np.ascontiguousarray(offsets, np.int32)
+        npts = len(off) - 1
+        if max_n is None:
+            max_n = max(int(np.diff(off).max()) if npts > 0 else 1, 1)
+        bi, bm = np.full(max(npts, 1), -1, np.int32), np.full(max(npts, 1), -1, np.int32)
+        od = np.zeros((max(npts, 1), 32), np.uint8) if out_desc is None else out_desc
+        self._bf._check(_lib.lib().orbfe_distinctive_descriptors(self._bf._h, ptr(d), ptr(off), npts, len(d), int(max_n), ptr(bi),
+                                                                 ptr(bm), ptr(od), int(flags)))
+        return bi[:npts], bm[:npts], od[:npts]
+
     def SearchForInitialization(self, keys1_un, desc1, keys2_un, desc2, bounds, vbPrevMatched, windowSize=10):
         """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) on
         monocular frames given as arrays; bounds = F2's image bounds.  vbPrevMatched: (n1, 2) float32.

@@ -1056,3 +1056,55 @@ def test_oracle_search_for_triangulation_vs_python(oracle):
     strict = oracle.search_for_triangulation(*base, False, False)[1]
     loose = oracle.search_for_triangulation(*base, True, False)[1]
     assert 0 < strict < loose
+
+
+# ---- MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:331-401)
+def observation_blocks(seed, npoints=60, max_n=70):
+    """descriptor blocks of MapPoints: N observations each (1 .. max_n, a few empty), every observation = a base descriptor
+    with a different number of flipped bits, so medians differ and ties occur (several rows with the same median)."""
+    r = scenes.rand_u32(npoints * 3, seed).reshape(3, npoints)
+    counts = (r[0] % np.uint32(max_n)).astype(np.int64) + 1
+    counts[r[1] % 11 == 0] = 0
+    counts[:4] = (1, 2, 3, max_n)
+    off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    total = int(off[-1])
+    base = scenes.rand_u32(npoints * 8, seed + 1).reshape(npoints, 8).view(np.uint8).reshape(npoints, 32)
+    desc = np.repeat(base, counts, axis=0).copy()
+    nflip = (scenes.rand_u32(total, seed + 2) % np.uint32(60)).astype(np.int64)
+    pos = (scenes.rand_u32(total * 60, seed + 3) % np.uint32(256)).reshape(total, 60).astype(np.int64)
+    for k in range(60):
+        rows = np.nonzero(nflip > k)[0]
+        q = pos[rows, k]
+        desc[rows, q >> 3] ^= (1 << (q & 7)).astype(np.uint8)
+    return desc, off
+
+
+def _py_distinctive(desc, off):
+    best = np.full(len(off) - 1, -1, np.int64)
+    med = np.full(len(off) - 1, -1, np.int64)
+    for p in range(len(off) - 1):
+        blk = np.unpackbits(desc[off[p]:off[p + 1]], axis=1).astype(np.int32)
+        n = len(blk)
+        if n == 0:
+            continue
+        dist = (blk[:, None, :] != blk[None, :, :]).sum(axis=2)
+        best_median, best_idx = 2 ** 31 - 1, 0
+        for i in range(n):
+            v = sorted(int(x) for x in dist[i])
+            m = v[int(0.5 * (n - 1))]
+            if m < best_median:
+                best_median, best_idx = m, i
+        best[p], med[p] = best_idx, best_median
+    return best, med
+
+
+def test_oracle_distinctive_descriptors_vs_python(oracle):
+    desc, off = observation_blocks(6900)
+    bi, bm = oracle.distinctive_descriptors(desc, off)
+    ref_i, ref_m = _py_distinctive(desc, off)
+    np.testing.assert_array_equal(bi, ref_i)
+    np.testing.assert_array_equal(bm, ref_m)
+    n = np.diff(off)
+    assert (bi[n == 0] == -1).all() and (bi[n == 1] == 0).all() and (bm[n == 1] == 0).all()
+    assert (bi[n == 2] == 0).all() and (bm[n == 2] == 0).all()    # median of (0, d) is element int(0.5) = 0: the first row wins
+    assert len(np.unique(bi[n > 10])) > 5
