@@ -9,6 +9,7 @@
 // These kernels gather from L2 (749 B + 512 B of reads per keypoint) and are not HBM-bound.
 #include <algorithm>
 #include <cfloat>
+#include <cstdlib>
 
 #include "orb_pattern.h"
 #include "orbfe_internal.h"
@@ -19,14 +20,38 @@ __device__ char4 d_pattern[256];    // 256 x (x0,y0,x1,y1), ORBextractor_old.cc:
 
 // __device__ variables are per device.  The copy is issued on the launch stream `st` (a cudaStreamNonBlocking stream
 // does not order against the legacy default stream), so the first describe_kernel of a device cannot overtake it.
-void upload_pattern(cudaStream_t st) {
+constexpr int AG_ROWS_PER_IT = 3, AG_WORDS = 9, AG_ITERS = 11;     // 27 lanes x 11 iterations >= 31 rows x 9 words
+// IC_Angle byte weights of describe_fused_kernel: [alignment a][iteration it][lane] -> (u inside the disc, v inside the disc)
+// for the 4 bytes that lane reads in iteration it: byte j of word (lane % 9) of patch row 3 it + lane / 9 is column
+// u = 4 (lane % 9) + j - a - 15, row v = 3 it + lane / 9 - 15; zero outside the disc of ORBextractor_old.cc:449-470
+__device__ int2 d_icWeights[4 * AG_ITERS * 32];
+
+void upload_pattern(cudaStream_t st, const int* umax) {
     static std::mutex mu;
     static bool done[64] = {false};
+    static int2 hW[4 * AG_ITERS * 32];
     int dev = 0;
     cudaGetDevice(&dev);
     std::lock_guard<std::mutex> lk(mu);
     if (dev < 0 || dev >= 64 || !done[dev]) {
+        for (int i = 0; i < 4 * AG_ITERS * 32; i++) {
+            const int a = i / (AG_ITERS * 32), it = (i / 32) % AG_ITERS, ln = i & 31;
+            const int row = AG_ROWS_PER_IT * it + ln / AG_WORDS, w = ln % AG_WORDS, v = row - kHalfPatch;
+            uint32_t wu = 0, wv = 0;
+            if (ln < AG_ROWS_PER_IT * AG_WORDS && row <= 2 * kHalfPatch) {
+                const int um = umax[v < 0 ? -v : v];
+                for (int j = 0; j < 4; j++) {
+                    const int u = 4 * w + j - a - kHalfPatch;
+                    if (u >= -um && u <= um) {
+                        wu |= (uint32_t)(u & 0xff) << (8 * j);
+                        wv |= (uint32_t)(v & 0xff) << (8 * j);
+                    }
+                }
+            }
+            hW[i] = make_int2((int)wu, (int)wv);
+        }
         cudaMemcpyToSymbolAsync(d_pattern, ORBFE_BIT_PATTERN_31, 1024, 0, cudaMemcpyHostToDevice, st);
+        cudaMemcpyToSymbolAsync(d_icWeights, hW, sizeof(hW), 0, cudaMemcpyHostToDevice, st);
         if (dev >= 0 && dev < 64) done[dev] = true;
     }
 }
@@ -230,6 +255,134 @@ __global__ void __launch_bounds__(32 * DS_WARPS) describe_kernel(const __grid_co
     }    // keypoint loop
 }
 
+// ================================ describe_fused_kernel (default) =================================================================
+// Same work as describe_kernel, one warp per keypoint, restructured around what bounds it (the LSU data pipe: 210 wavefronts
+// and 841 warp instructions per keypoint in describe_kernel, profiles/r2_ncu_full_summary.md):
+//   * IC_Angle reads the 31 x 31 patch with ALIGNED 32-bit loads, 3 patch rows x 9 words per load instruction (11 loads
+//     instead of 31), and accumulates both moments with two IDP.4A per word against a shared table of signed byte weights
+//     (u inside the disc / v inside the disc, for each of the 4 alignments of the patch), then two REDUX;
+//   * the 37 x 37 window of the blurred level that the rotated pattern can reach (|coordinate| <= round(13 sqrt 2) = 18) goes
+//     to shared memory through registers, 3 rows x 10 words per load, issued BEFORE the IC loads so that both reads share
+//     one trip to L2 / HBM; the 512 byte reads of the descriptor then hit shared memory (3 wavefronts per LDS on average
+//     instead of 7.6 per global gather);
+//   * the lane's 8 test pairs live in registers as floats (no shared-memory pattern reads), the two cvRound subtractions fold
+//     into one constant of the byte address, and the 32 output bytes leave as one coalesced byte store.
+constexpr int DC_R = 18, DC_WORDS = 10, DC_ITERS = 13;            // 30 lanes x 13 iterations >= 37 rows x 10 words
+constexpr int DC_ROWS = AG_ROWS_PER_IT * DC_ITERS;                // 39 staged rows (37 used)
+
+__device__ __forceinline__ int dp4a_u8s8(uint32_t pix, int w, int acc) {    // sum pix.u8[i] * w.s8[i] + acc
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pix), "r"(w), "r"(acc));
+    return d;
+}
+
+// grid (gx, n); block 32 * DS_WARPS
+template <int MINB>
+__global__ void __launch_bounds__(32 * DS_WARPS, MINB) describe_fused_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
+                                                                             orbfe_keypoint* __restrict__ kps,
+                                                                             uint8_t* __restrict__ desc, int cap) {
+    __shared__ int2 sW[4 * AG_ITERS * 32];
+    __shared__ uint32_t sPatch[DS_WARPS][DC_ROWS * DC_WORDS];
+    for (int i = threadIdx.x; i < 4 * AG_ITERS * 32; i += 32 * DS_WARPS) sW[i] = d_icWeights[i];
+    __syncthreads();
+    const int img = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nk = b.result[img].count;
+    float px0[8], py0[8], px1[8], py1[8];    // test (8 * lane + bit): the lane's output byte
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) {
+        const char4 pt = d_pattern[8 * lane + bit];
+        px0[bit] = (float)pt.x; py0[bit] = (float)pt.y; px1[bit] = (float)pt.z; py1[bit] = (float)pt.w;
+    }
+    // lanes beyond the 27 (30) that carry data repeat the last one's address; their IC weights are zero
+    const int la = min(lane, AG_ROWS_PER_IT * AG_WORDS - 1), lb = min(lane, AG_ROWS_PER_IT * DC_WORDS - 1);
+    const int rsubA = la / AG_WORDS, wqA = la % AG_WORDS, rsubB = lb / DC_WORDS, wqB = lb % DC_WORDS;
+    uint32_t* mySlot = &sPatch[warp][rsubB * DC_WORDS + wqB];
+    const uint8_t* patch = reinterpret_cast<const uint8_t*>(&sPatch[warp][0]);
+    for (int k = blockIdx.x * DS_WARPS + warp; k < nk; k += gridDim.x * DS_WARPS) {
+        const KpWork w = b.work[(size_t)img * g.outCap + k];
+        const LevelGeom& L = g.lv[w.level];
+        const int pitch = L.pitch;
+        const size_t step = (size_t)AG_ROWS_PER_IT * pitch;
+        const size_t plane = (size_t)img * g.slabBytes + L.planeOff + kXOff;    // planes, pitches and kXOff are multiples of 4
+        const int cB = (int)w.x - DC_R, cA = (int)w.x - kHalfPatch;             // first column of the two windows
+        uint32_t st[DC_ITERS];
+        {
+            const uint8_t* p = b.blur + plane + (size_t)((int)w.y + kEdge - DC_R + rsubB) * pitch + (cB & ~3) + 4 * wqB;
+#pragma unroll
+            for (int it = 0; it < DC_ITERS; it++) {
+                st[it] = __ldg(reinterpret_cast<const uint32_t*>(p));
+                p += step;
+            }
+        }
+        // ---- IC_Angle (:78-105)
+        int m10 = 0, m01 = 0;
+        {
+            const uint8_t* p = b.pyr + plane + (size_t)((int)w.y + kEdge - kHalfPatch + rsubA) * pitch + (cA & ~3) + 4 * wqA;
+            const int2* wt = sW + (cA & 3) * (AG_ITERS * 32) + lane;
+            uint32_t pix[AG_ITERS];
+#pragma unroll
+            for (int it = 0; it < AG_ITERS; it++) {
+                pix[it] = __ldg(reinterpret_cast<const uint32_t*>(p));
+                p += step;
+            }
+#pragma unroll
+            for (int it = 0; it < AG_ITERS; it++) {
+                const int2 w2 = wt[it * 32];
+                m10 = dp4a_u8s8(pix[it], w2.x, m10);
+                m01 = dp4a_u8s8(pix[it], w2.y, m01);
+            }
+        }
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+        // ---- computeOrbDescriptor (:109-148); lane = output byte
+        const float factorPI = (float)(3.14159265358979323846 / 180.f);
+        const float rad = __fmul_rn(angle, factorPI);
+        double sd, cd;
+        sincos((double)rad, &sd, &cd);
+        const float ca = (float)cd, sb = (float)sd;
+#pragma unroll
+        for (int it = 0; it < DC_ITERS; it++) mySlot[it * (AG_ROWS_PER_IT * DC_WORDS)] = st[it];
+        __syncwarp();
+        // byte offset of test point (r, c) = (r + 18) * 40 + (c + 18) + alignment; r, c arrive as the raw bits of
+        // v + 1.5 * 2^23 (0x4B400000 + round-half-even(v)), so the two subtractions fold into one constant (uint32 wraps)
+        constexpr uint32_t M = 0x4B400000u;
+        const uint32_t K = (uint32_t)(DC_R * DC_WORDS * 4 + DC_R + (cB & 3)) - M * (uint32_t)(DC_WORDS * 4 + 1);
+        uint32_t byte = 0;
+#pragma unroll
+        for (int bit = 0; bit < 8; bit++) {
+            const uint32_t r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px0[bit], sb), __fmul_rn(py0[bit], ca)), 12582912.f));
+            const uint32_t q0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px0[bit], ca), __fmul_rn(py0[bit], sb)), 12582912.f));
+            const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px1[bit], sb), __fmul_rn(py1[bit], ca)), 12582912.f));
+            const uint32_t q1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px1[bit], ca), __fmul_rn(py1[bit], sb)), 12582912.f));
+            const uint32_t t0 = patch[r0 * (uint32_t)(DC_WORDS * 4) + q0 + K];
+            const uint32_t t1 = patch[r1 * (uint32_t)(DC_WORDS * 4) + q1 + K];
+            byte |= (uint32_t)(t0 < t1) << bit;
+        }
+        if (w.dst < cap) {
+            desc[((size_t)img * cap + w.dst) * 32 + lane] = (uint8_t)byte;
+            // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
+            if (lane < 7) {
+                float fx = (float)w.x, fy = (float)w.y;
+                if (w.level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+                uint32_t word;
+                switch (lane) {
+                    case 0: word = __float_as_uint(fx); break;
+                    case 1: word = __float_as_uint(fy); break;
+                    case 2: word = __float_as_uint((float)L.scaledPatch); break;
+                    case 3: word = __float_as_uint(angle); break;
+                    case 4: word = __float_as_uint((float)w.response); break;
+                    case 5: word = (uint32_t)w.level; break;
+                    default: word = 0xffffffffu; break;
+                }
+                reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + w.dst)[lane] = word;
+            }
+        }
+        __syncwarp();    // the next keypoint overwrites the patch
+    }
+}
+
 int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st) {
     const size_t smem = sizeof(int) * (size_t)(g.outCap + 1);
     static SmemOptIn optIn;
@@ -240,11 +393,15 @@ int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap
 
 int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
                     cudaStream_t st) {
-    upload_pattern(st);
-    // a few keypoints per warp so that the shared pattern load is amortised; small batches keep one keypoint per warp
+    upload_pattern(st, g.umax);
+    static const bool v1 = [] { const char* e = getenv("ORBFE_DESCRIBE_V1"); return e && *e == '1'; }();
+    static const int minb = [] { const char* e = getenv("ORBFE_DESCRIBE_MINB"); return e ? atoi(e) : 4; }();
+    // a few keypoints per warp so that the per-CTA setup is amortised; small batches keep one keypoint per warp
     const int full = (g.outCap + DS_WARPS - 1) / DS_WARPS;
     const int gx = n >= 64 ? std::min(full, 24) : full;
-    describe_kernel<<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
+    if (v1) describe_kernel<<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
+    else if (minb == 4) describe_fused_kernel<4><<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
+    else describe_fused_kernel<3><<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
     return 1;
 }
 
