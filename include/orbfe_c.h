@@ -151,6 +151,23 @@ int orbfe_matcher_set_stream(orbfe_matcher* m, void* cuda_stream); /* as orbfe_e
  * equal distances keep the lower train index first (OpenCV's order); missing neighbours (nt < 2) are -1. */
 int orbfe_knn2(orbfe_matcher* m, const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt, int32_t* idx,
                int32_t* dist, unsigned flags);
+/* ---- kNN without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same tcgen05 kernel as orbfe_knn2 in its train-segmented form, whose scratch memory (partial top 2 per segment + one
+ * ticket per query tile) lives in a file-scope `static __device__` array of 2 MiB + 512 B instead of coming from
+ * cudaMallocAsync; every GPU that loads the library holds that array until exit.  The call allocates nothing (no
+ * cudaMalloc / cudaFree / allocating library routine) and needs no handle: it runs on the CURRENT device, on the caller's
+ * stream (a cudaStream_t as void*, NULL = the legacy default stream), and returns after enqueueing (it does not synchronise).
+ *   q, t, idx, dist   DEVICE memory of the current device: nq x 32 and nt x 32 descriptor bytes in, 2 x int32 per query row
+ *                     out (best, second best; -1 = missing), results identical to orbfe_knn2
+ *   limits            nq <= ORBFE_KNN2_STATIC_MAX_NQ (beyond: ORBFE_ERR_CAPACITY and a message), nt < 2^31
+ *   err / err_len     optional buffer for the text of an error (there is no handle to hold it)
+ * All calls on a device share the one scratch array: calls that overlap on the GPU (two streams, two threads) RACE; serialise
+ * them on one stream.  The first call on a device resolves the array's address (cudaGetSymbolAddress) and the kernel's
+ * shared-memory opt-in: make it outside stream capture. */
+#define ORBFE_KNN2_STATIC_MAX_NQ 16384
+int orbfe_knn2_static_scratch(const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt, int32_t* idx, int32_t* dist,
+                              void* cuda_stream, char* err, size_t err_len);
 /* npairs independent problems: problem p uses rows [p*q_cap, p*q_cap + nq[p]) of q and [p*t_cap, p*t_cap + nt[p])
  * of t, and writes idx/dist rows [p*q_cap ...).  nq/nt are host arrays unless ORBFE_IN_DEVICE (then device int32). */
 int orbfe_knn2_batch(orbfe_matcher* m, const uint8_t* q, const int32_t* nq, int q_cap, const uint8_t* t,

@@ -15,6 +15,7 @@ CSRC = os.path.join(_HERE, "csrc")
 
 OK, ERR_ARG, ERR_CAPACITY, ERR_CUDA, ERR_NCCL, ERR_INTERNAL = 0, -1, -2, -3, -4, -5
 IN_DEVICE, OUT_DEVICE = 1, 2
+KNN2_STATIC_MAX_NQ = 16384    # ORBFE_KNN2_STATIC_MAX_NQ (orbfe_c.h)
 MAX_LEVELS = 16
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
@@ -92,6 +93,7 @@ SYMBOLS = {
     "orbfe_search_by_bow_kf_batch": (_i, [_vp] * 15 + [_i, _i, _i, C.c_float, _i, _vp, _vp, _u]),
     "orbfe_search_for_triangulation_batch": (_i, [_vp] * 17 + [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _u]),
     "orbfe_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, C.c_int64, _i, _vp, _vp, _vp, _u]),
+    "orbfe_knn2_static_scratch": (_i, [_vp, C.c_int64, _vp, C.c_int64, _vp, _vp, _vp, _vp, C.c_size_t]),
     "orbfe_search_for_initialization_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, C.c_float, _i, _vp,
                                                    _vp, _vp, _u]),
     "orbfe_stereo_fisheye_matches_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp,

@@ -23,6 +23,7 @@
 //     scratch array, and the last CTA of a tile to finish (atomic ticket) merges the nseg partial results in segment
 //     order -- strict "<" keeps the lowest train index on ties, as OpenCV does.
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 
@@ -399,4 +400,97 @@ int launch_knn2_tc_segments(const uint8_t* q, long long nq, long long planRows, 
     return 1;
 }
 
+// ---- orbfe_knn2_static_scratch: the segmented launch with NO allocation -------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  launch_knn2_tc above takes the scratch of
+// its segmented form (partial top 2 of every train segment + one ticket per query tile) from cudaMallocAsync; this variant
+// keeps it in a file-scope device array of a fixed, modest size instead.  Every GPU that loads the library holds the
+// array until exit; every call on a device shares it, so calls that overlap on the GPU (different streams, different
+// threads) race.  It keeps the last call's partial results (never read before they are rewritten); the tickets must start at
+// zero and are cleared by every call.
+constexpr long long KT_STATIC_MAX_NQ = ORBFE_KNN2_STATIC_MAX_NQ;     // 16384 query rows = 128 tiles
+constexpr int KT_STATIC_MAX_SEGS = 8;
+constexpr size_t KT_STATIC_PARTIAL_BYTES = (size_t)KT_STATIC_MAX_SEGS * KT_STATIC_MAX_NQ * sizeof(int4);    // 2 MiB
+constexpr size_t KT_STATIC_TICKET_BYTES = (size_t)(KT_STATIC_MAX_NQ / KT_M) * sizeof(unsigned);            // 512 B
+static_assert(KT_STATIC_MAX_NQ % KT_M == 0, "whole query tiles");
+static __device__ __align__(256) uint8_t g_knnStaticScratch[KT_STATIC_PARTIAL_BYTES + KT_STATIC_TICKET_BYTES];
+
+// In host code g_knnStaticScratch is a host-side stand-in, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int knn_static_scratch_ptr(uint8_t** out, char* err, size_t errLen) {
+    static std::mutex mu;
+    static uint8_t* ptrOf[64] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        if (err && errLen) snprintf(err, errLen, "orbfe_knn2_static_scratch: no usable current CUDA device (%s)", cudaGetErrorString(e));
+        cudaGetLastError();
+        return ORBFE_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrOf[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_knnStaticScratch);
+        if (e != cudaSuccess || !p) {
+            if (err && errLen) snprintf(err, errLen, "orbfe_knn2_static_scratch: cudaGetSymbolAddress failed on device %d (%s)", dev, cudaGetErrorString(e));
+            cudaGetLastError();
+            return ORBFE_ERR_CUDA;
+        }
+        ptrOf[dev] = static_cast<uint8_t*>(p);
+    }
+    *out = ptrOf[dev];
+    return ORBFE_OK;
+}
+
+void library_count_launches(int launches);    // orbfe_api.cu
+
 }    // namespace orbfe
+
+extern "C" int orbfe_knn2_static_scratch(const uint8_t* q, int64_t nq, const uint8_t* t, int64_t nt, int32_t* idx, int32_t* dist,
+                                         void* cuda_stream, char* err, size_t err_len) {
+    using namespace orbfe;
+    if (err && err_len) err[0] = 0;
+    auto fail = [&](int code, const char* fmt, long long a, long long b) {
+        if (err && err_len) snprintf(err, err_len, fmt, a, b);
+        return code;
+    };
+    if (nq < 0 || nt < 0) return fail(ORBFE_ERR_ARG, "orbfe_knn2_static_scratch: negative size (nq %lld, nt %lld)", nq, nt);
+    if (nq > KT_STATIC_MAX_NQ)
+        return fail(ORBFE_ERR_CAPACITY, "orbfe_knn2_static_scratch: nq %lld exceeds the static scratch maximum of %lld query rows", nq,
+                    KT_STATIC_MAX_NQ);
+    if (nt > 0x7fffffffll) return fail(ORBFE_ERR_CAPACITY, "orbfe_knn2_static_scratch: nt %lld exceeds %lld train rows", nt, 0x7fffffffll);
+    if (nq == 0) return ORBFE_OK;
+    if (!q || !idx || !dist || (nt > 0 && !t)) return fail(ORBFE_ERR_ARG, "orbfe_knn2_static_scratch: null pointer (nq %lld, nt %lld)", nq, nt);
+    uint8_t* scratch = nullptr;
+    const int rc = knn_static_scratch_ptr(&scratch, err, err_len);
+    if (rc != ORBFE_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const int resident = kt_resident_ctas();    // shared-memory opt-in + occupancy of this device (no allocation)
+    cudaGetLastError();    // an earlier, unrelated call of this thread may have left a non-sticky error behind: the check
+                           // after the launch must report THIS launch
+    const long long tiles = (nq + KT_M - 1) / KT_M;
+    // segments: as many as fill the resident CTAs (<= KT_STATIC_MAX_SEGS, >= KT_N train rows each); two at least when the
+    // train set has two tiles, so that the scratch path is the one that runs
+    int nseg = (int)std::min<long long>(KT_STATIC_MAX_SEGS, std::max<long long>(1, nt / KT_N));
+    while (nseg > 2 && tiles * (nseg - 1) >= resident) nseg--;
+    long long segLen = ((nt + nseg - 1) / nseg + KT_N - 1) / KT_N * KT_N;
+    if (segLen < KT_N) segLen = KT_N;
+    const int zTotal = (int)std::max<long long>(1, (nt + segLen - 1) / segLen);
+    if (zTotal <= 1) {
+        knn2_tc_kernel<<<dim3((unsigned)tiles, 1), KT_THREADS, KT_SMEM, st>>>(q, nullptr, nq, t, nullptr, nt, nq, nt, idx, dist, 0,
+                                                                               nullptr, nullptr, 0, 1);
+    } else {
+        const size_t partialBytes = (size_t)zTotal * tiles * KT_M * sizeof(int4);    // <= KT_STATIC_PARTIAL_BYTES by the limits above
+        cudaMemsetAsync(scratch + partialBytes, 0, (size_t)tiles * sizeof(unsigned), st);
+        knn2_tc_kernel<<<dim3((unsigned)tiles, 1, (unsigned)zTotal), KT_THREADS, KT_SMEM, st>>>(
+            q, nullptr, nq, t, nullptr, nt, nq, nt, idx, dist, segLen, reinterpret_cast<int4*>(scratch),
+            reinterpret_cast<unsigned*>(scratch + partialBytes), 0, zTotal);
+    }
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        if (err && err_len) snprintf(err, err_len, "orbfe_knn2_static_scratch: launch failed (%s)", cudaGetErrorString(e));
+        return ORBFE_ERR_CUDA;
+    }
+    library_count_launches(1);
+    return ORBFE_OK;
+}

@@ -1267,6 +1267,7 @@ void matcher_count_launches(orbfe_matcher* m, int launches) {
     g_launches += launches;
     m->lastLaunches = launches;
 }
+void library_count_launches(int launches) { g_launches += launches; }    // entry points without a handle (k_knn_tc.cu)
 }    // namespace orbfe
 
 extern "C" {
