@@ -323,6 +323,214 @@ def latency_leg(args, local):
             "keypoints": [int(counts[0]), int(counts[1])]}
 
 
+def backend_leg(args, local, dev):
+    """SURVEY.md 8(f) rank 3, the matchers of the local-mapping / loop-closing threads: the Sim3 projection
+    search, Fuse, SearchBySim3, SearchByBoW (key frame -> frame and key frame -> key frame), SearchForTriangulation and
+    MapPoint::ComputeDistinctiveDescriptors, one batch of args.search_frames key frames (pairs) per step, everything
+    resident in HBM; the CPU oracle is timed beside every one on one thread and checked on the sampled key frames."""
+    import torch
+    from orbslam3lib_b200 import ORBextractor, ORBmatcher, _lib, scenes
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+    import oracle_lib
+    oracle_lib.build()
+    nfr, npts, steps = args.search_frames, 2000, 5
+    ex = ORBextractor(NFEAT, 1.2, NLEVELS, 20, 7, device=local)
+    cap = ex.max_keypoints
+    nsc = min(nfr, 8)
+    cur = np.stack([scenes.make("texture", W, H, 7400 + k) for k in range(nsc)])
+    prev = np.stack([scenes.previous_frame(cur[k], 7400 + k) for k in range(nsc)])
+    c1, _, k1s, d1s = ex.extract_batch(cur)
+    c2, _, k2s, d2s = ex.extract_batch(prev)
+    scale = np.asarray(ex.GetScaleFactors(), np.float32)
+    sigma2 = (scale * scale).astype(np.float32)
+    inv_sigma2 = (1.0 / sigma2).astype(np.float32)
+    bounds = (0.0, 0.0, float(W), float(H))
+    FL = _lib.IN_DEVICE | _lib.OUT_DEVICE
+    S = []    # per sampled scene: everything the oracle needs
+    for k in range(nsc):
+        a, b = int(c1[k]), int(c2[k])
+        ka, da, kb, db = k1s[k, :a], d1s[k, :a], k2s[k, :b], d2s[k, :b]
+        r1, r2 = scenes.rand_u32(a, 7500 + k), scenes.rand_u32(b, 7600 + k)
+        S.append(dict(k1=ka, d1=da, k2=kb, d2=db, u1=np.where(r1 % 3 == 0, -1.0, ka["x"] - 8.0).astype(np.float32),
+                      has1=(r1 % 5 != 0).astype(np.uint8), has2=(r2 % 5 != 0).astype(np.uint8),
+                      fv1=scenes.feature_vector(da), fv2=scenes.feature_vector(db),
+                      pts=scenes.frame_points(ka, da, a, None, None, NLEVELS, npts, 7700 + k, dup_frac=0.2),
+                      p1=scenes.frame_points(kb, db, b, None, None, NLEVELS, a, 7800 + k, dup_frac=0.05),
+                      p2=scenes.frame_points(ka, da, a, None, None, NLEVELS, b, 7900 + k, dup_frac=0.05)))
+        c, rm = S[-1], scenes.rand_u32(a, 8000 + k)
+        for i1 in range(0, a, 2):    # mutual pairs: MapPoint i1 of KF1 projects onto feature j of KF2 and j's projects back
+            j = int(rm[i1] % b)
+            for pp, i, kk, dd, o in ((c["p1"], i1, kb, db, j), (c["p2"], j, ka, da, i1)):
+                pp[i]["u"], pp[i]["v"], pp[i]["level"], pp[i]["desc"], pp[i]["flags"] = kk["x"][o], kk["y"][o], kk["octave"][o], dd[o], 1
+    ncap = max(max(len(c["fv1"][0]), len(c["fv2"][0])) for c in S)
+    spec = dict(k=((nfr, cap), _lib.KP_DTYPE), d=((nfr, cap, 32), np.uint8), a=((nfr, cap), np.float32),
+                v=((nfr, cap), np.uint8), fr=((nfr, cap), np.uint8), id=((nfr, ncap), np.int32),
+                st=((nfr, ncap + 1), np.int32), ix=((nfr, cap), np.int32), nn=((nfr,), np.int32), n=((nfr,), np.int32),
+                p=((nfr, cap), scenes.FRAME_POINT_DTYPE))
+    A = {side: {key: np.zeros(shp, dt) for key, (shp, dt) in spec.items()} for side in ("1", "2")}
+    U = np.full((nfr, cap), -1, np.float32)
+    P = np.zeros((nfr, npts), scenes.FRAME_POINT_DTYPE)
+    for f in range(nfr):
+        c = S[f % nsc]
+        for side in ("1", "2"):
+            kk, dd, fv, X = c["k" + side], c["d" + side], c["fv" + side], A[side]
+            n = len(kk)
+            X["k"][f, :n], X["d"][f, :n], X["a"][f, :n], X["v"][f, :n], X["n"][f] = kk, dd, kk["angle"], c["has" + side], n
+            X["fr"][f, :n] = 1 - c["has" + side]
+            X["id"][f, :len(fv[0])], X["st"][f, :len(fv[1])], X["ix"][f, :len(fv[2])], X["nn"][f] = fv[0], fv[1], fv[2], len(fv[0])
+            X["p"][f, :n] = c["p" + side]
+        U[f, :len(c["k1"])] = c["u1"]
+        P[f] = c["pts"]
+    tt = lambda a: torch.from_numpy(a.view(np.uint8).reshape(a.shape[0], -1) if a.dtype.fields else a).to(dev)    # noqa: E731
+    T = {side: {key: tt(v) for key, v in A[side].items()} for side in ("1", "2")}
+    a, b = T["1"], T["2"]
+    dU, dP = torch.from_numpy(U).to(dev), tt(P)
+    dnp = torch.full((nfr,), npts, dtype=torch.int32, device=dev)
+    z = lambda *shp: torch.zeros(shp, dtype=torch.int32, device=dev)    # noqa: E731
+    out = {}
+
+    def timed(call):
+        ms = 0.0
+        for it in range(steps + 2):
+            mobj = call()
+            if it >= 2:
+                ms += mobj.last_ms()[0]
+        return ms / steps
+
+    def cpu(fn):
+        t0 = time.perf_counter()
+        res = [fn(c) for c in S]
+        return res, nsc / (time.perf_counter() - t0)
+
+    def entry(name, workload, ms, got, ref, cpu_rate, extra=None):
+        ok = all(bool(np.array_equal(g, r)) for g, r in zip(got, ref))
+        out[name] = {"workload": workload, "kernel_ms_per_step": ms, "key_frames_per_s": nfr / (ms * 1e-3),
+                     "cpu_oracle_key_frames_per_s_1thread": cpu_rate,
+                     "parity_sample": {"key_frames": nsc, "vs": "CPU oracle (bit-exact indices)", "ok": ok}}
+        if extra:
+            out[name].update(extra)
+
+    m75, m60 = ORBmatcher(0.75, True, device=local), ORBmatcher(0.6, True, device=local)
+    # SearchByProjection(pKF, Scw, vpPoints, vpMatched, th = 10, ratioHamming = 1) (ORBmatcher.cc:428-647)
+    d_m, d_own, d_cnt = z(nfr, npts), z(nfr, cap), z(nfr)
+
+    def run_sim3p():
+        m75.search_sim3_projection_batch_raw(a["k"], a["d"], None, a["n"], cap, bounds, scale, dP, dnp, npts, nfr, 10.0, 1.0,
+                                             d_m, d_own, d_cnt, FL)
+        return m75._bf
+    ms = timed(run_sim3p)
+    got = d_m[:nsc].cpu().numpy()
+    ref, rate = cpu(lambda c: oracle_lib.search_by_projection_sim3(c["k1"], c["d1"], None, bounds, scale, c["pts"], 10.0, 1.0)[0])
+    entry("sim3_projection", "ORBmatcher::SearchByProjection(pKF, Scw, ...), %d key frames x %d points, th = 10" % (nfr, npts),
+          ms, got, ref, rate, {"matches_per_key_frame": float(d_cnt.float().mean().item())})
+    # Fuse(pKF, vpMapPoints, th = 3) (ORBmatcher.cc:1155-1345)
+    d_bi, d_bd = z(nfr, npts), z(nfr, npts)
+
+    def run_fuse():
+        m60.fuse_batch_raw(a["k"], a["d"], dU, a["n"], cap, bounds, scale, inv_sigma2, 47.9, dP, dnp, npts, nfr, 3.0, True, d_bi,
+                           d_bd, d_cnt, FL)
+        return m60._bf
+    ms = timed(run_fuse)
+    got = d_bi[:nsc].cpu().numpy()
+    ref, rate = cpu(lambda c: oracle_lib.fuse(c["k1"], c["d1"], c["u1"], bounds, scale, inv_sigma2, 47.9, c["pts"], 3.0, True)[0])
+    entry("fuse", "ORBmatcher::Fuse(pKF, vpMapPoints, th = 3), %d key frames x %d points, chi-square gate" % (nfr, npts), ms,
+          got, ref, rate, {"candidates_per_key_frame": float(d_cnt.float().mean().item())})
+    return backend_leg_pairs(args, local, dev, S, a, b, cap, ncap, nfr, nsc, bounds, scale, sigma2, timed, cpu, entry, out, m75,
+                             m60, z, FL)
+
+
+def backend_leg_pairs(args, local, dev, S, a, b, cap, ncap, nfr, nsc, bounds, scale, sigma2, timed, cpu, entry, out, m75, m60,
+                      z, FL):
+    """second half of backend_leg: the key-frame pair matchers and the distinctive-descriptor selection."""
+    import torch
+    from orbslam3lib_b200 import scenes
+    import oracle_lib
+    d_m12, d_v1, d_v2, d_cnt = z(nfr, cap), z(nfr, cap), z(nfr, cap), z(nfr)
+    # SearchBySim3(pKF1, pKF2, vpMatches12, S12, th = 7.5) (ORBmatcher.cc:1464-1681)
+
+    def run_sim3():
+        m75.search_by_sim3_batch_raw(a["k"], a["d"], a["n"], b["k"], b["d"], b["n"], cap, bounds, bounds, scale, a["p"], b["p"],
+                                     nfr, 7.5, d_m12, d_v1, d_v2, d_cnt, FL)
+        return m75
+    ms = timed(run_sim3)
+    g = d_m12[:nsc].cpu().numpy()
+    got = [g[k, :len(S[k]["k1"])] for k in range(nsc)]
+    ref, rate = cpu(lambda c: oracle_lib.search_by_sim3(c["k1"], c["d1"], c["k2"], c["d2"], bounds, bounds, scale, c["p1"], c["p2"],
+                                                        7.5)[0])
+    entry("search_by_sim3", "ORBmatcher::SearchBySim3, %d key-frame pairs, ~%d MapPoints each way, th = 7.5"
+          % (nfr, len(S[0]["k1"])), ms, got, ref, rate, {"found_per_pair": float(d_cnt.float().mean().item())})
+    # SearchByBoW(pKF, F, vpMapPointMatches) (ORBmatcher.cc:224-425): key frame = side 2 (previous frame), frame = side 1
+
+    def run_bow():
+        m75.search_by_bow_batch_raw(b["d"], b["a"], b["v"], b["id"], b["st"], b["ix"], b["nn"], a["d"], a["a"], a["n"], None,
+                                    a["id"], a["st"], a["ix"], a["nn"], cap, ncap, nfr, d_m12, d_cnt, FL)
+        return m75
+    ms = timed(run_bow)
+    g = d_m12[:nsc].cpu().numpy()
+    got = [g[k, :len(S[k]["k1"])] for k in range(nsc)]
+    ref, rate = cpu(lambda c: oracle_lib.search_by_bow(c["d2"], c["k2"]["angle"].astype(np.float32), c["has2"], c["fv2"], c["d1"],
+                                                       c["k1"]["angle"].astype(np.float32), -1, c["fv1"], 0.75, True)[0])
+    entry("search_by_bow", "ORBmatcher::SearchByBoW(KeyFrame, Frame), %d pairs, %d vocabulary nodes" % (nfr, ncap), ms, got,
+          ref, rate, {"matches_per_pair": float(d_cnt.float().mean().item())})
+    # SearchByBoW(pKF1, pKF2, vpMatches12) (ORBmatcher.cc:766-906)
+
+    def run_bow_kf():
+        m75.search_by_bow_kf_batch_raw(a["d"], a["a"], a["v"], a["id"], a["st"], a["ix"], a["nn"], b["d"], b["a"], b["v"], b["id"],
+                                       b["st"], b["ix"], b["nn"], cap, ncap, nfr, d_m12, d_cnt, FL)
+        return m75
+    ms = timed(run_bow_kf)
+    g = d_m12[:nsc].cpu().numpy()
+    got = [g[k, :len(S[k]["k1"])] for k in range(nsc)]
+    ang = lambda c, s_: c["k" + s_]["angle"].astype(np.float32)    # noqa: E731
+    ref, rate = cpu(lambda c: oracle_lib.search_by_bow_kf(c["d1"], ang(c, "1"), c["has1"], c["fv1"], c["d2"], ang(c, "2"),
+                                                          c["has2"], c["fv2"], 0.75, True)[0])
+    entry("search_by_bow_kf", "ORBmatcher::SearchByBoW(KeyFrame, KeyFrame), %d pairs" % nfr, ms, got, ref, rate,
+          {"matches_per_pair": float(d_cnt.float().mean().item())})
+    # SearchForTriangulation (ORBmatcher.cc:908-1153): pure image translation (3, 2) between the key frames
+    F12 = np.tile(np.array([0, 0, 2, 0, 0, -3, -2, 3, 0], np.float32), (nfr, 1))
+    EP = np.tile(np.array([W * 0.4, H * 0.45], np.float32), (nfr, 1))
+    dF, dE = torch.from_numpy(F12).to(dev), torch.from_numpy(EP).to(dev)
+
+    def run_tri():
+        m60.search_for_triangulation_batch_raw(a["k"], a["d"], a["fr"], None, a["id"], a["st"], a["ix"], a["nn"], b["k"], b["d"],
+                                               b["fr"], None, b["id"], b["st"], b["ix"], b["nn"], cap, ncap, nfr, dF, dE, scale,
+                                               sigma2, False, d_m12, d_cnt, FL)
+        return m60
+    ms = timed(run_tri)
+    g = d_m12[:nsc].cpu().numpy()
+    got = [g[k, :len(S[k]["k1"])] for k in range(nsc)]
+    ref, rate = cpu(lambda c: oracle_lib.search_for_triangulation(c["k1"], c["d1"], 1 - c["has1"], None, c["fv1"], c["k2"], c["d2"],
+                                                                  1 - c["has2"], None, c["fv2"], F12[0], EP[0], scale, sigma2,
+                                                                  False, True)[0])
+    entry("search_for_triangulation", "ORBmatcher::SearchForTriangulation, %d pairs, pinhole epipolar constraint" % nfr, ms, got,
+          ref, rate, {"matches_per_pair": float(d_cnt.float().mean().item())})
+    # MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:331-401): 50k MapPoints with 2 .. 17 observations each
+    npt = 50000
+    cnts = (scenes.rand_u32(npt, 8100) % np.uint32(16)).astype(np.int64) + 2
+    off = np.concatenate([[0], np.cumsum(cnts)]).astype(np.int32)
+    rows, _ = scenes.map_descriptors(int(off[-1]), 4096, 8101)
+    d_rows, d_off = torch.from_numpy(rows).to(dev), torch.from_numpy(off).to(dev)
+    d_bi, d_bm = z(npt), z(npt)
+    d_od = torch.zeros((npt, 32), dtype=torch.uint8, device=dev)
+    from orbslam3lib_b200 import _lib
+
+    def run_dd():
+        m60._bf._check(_lib.lib().orbfe_distinctive_descriptors(m60._bf._h, _lib.ptr(d_rows), _lib.ptr(d_off), npt, len(rows), 32,
+                                                                _lib.ptr(d_bi), _lib.ptr(d_bm), _lib.ptr(d_od), FL))
+        return m60
+    ms = timed(run_dd)
+    nsam = 2000
+    t0 = time.perf_counter()
+    ri, rm = oracle_lib.distinctive_descriptors(rows[:off[nsam]], off[:nsam + 1])
+    t_cpu = time.perf_counter() - t0
+    ok = bool(np.array_equal(d_bi[:nsam].cpu().numpy(), ri) and np.array_equal(d_bm[:nsam].cpu().numpy(), rm))
+    out["distinctive_descriptors"] = {"workload": "MapPoint::ComputeDistinctiveDescriptors, %d MapPoints, %d observations"
+                                                  % (npt, len(rows)), "kernel_ms_per_step": ms,
+                                      "map_points_per_s": npt / (ms * 1e-3), "cpu_oracle_map_points_per_s_1thread": nsam / t_cpu,
+                                      "parity_sample": {"map_points": nsam, "vs": "CPU oracle (BestIdx, BestMedian)", "ok": ok}}
+    return out
+
+
 def stereo_leg(args, local, dev):
     """SURVEY.md 8(f) rank 1: the rectified-stereo front-end of Frame::Frame (two extractions) followed by
     Frame::ComputeStereoMatches (Frame.cc:827-997) on device-resident pyramids, P pairs per step
@@ -884,6 +1092,8 @@ def main():
     if args.search_frames > 0:
         torch.cuda.empty_cache()
         line["search_by_projection"] = search_leg(args, local, dev)
+        torch.cuda.empty_cache()
+        line["backend_matchers"] = backend_leg(args, local, dev)
     if not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
         import oracle_lib
