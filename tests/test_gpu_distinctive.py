@@ -38,6 +38,7 @@ def test_distinctive_capacity_and_device_buffers(oracle):
     dbm = torch.zeros(300, dtype=torch.int32, device=dev)
     dod = torch.zeros((300, 32), dtype=torch.uint8, device=dev)
     m = ORBmatcher(0.6, True)
+    torch.cuda.synchronize()    # the fills above run on torch's stream, the library on its own
     m._bf._check(_lib.lib().orbfe_distinctive_descriptors(m._bf._h, _lib.ptr(dd), _lib.ptr(doff), 300, len(desc), 50, _lib.ptr(dbi),
                                                           _lib.ptr(dbm), _lib.ptr(dod), _lib.IN_DEVICE | _lib.OUT_DEVICE))
     np.testing.assert_array_equal(dbi.cpu().numpy(), ri)

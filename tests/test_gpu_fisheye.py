@@ -134,6 +134,7 @@ def test_fisheye_batch_device_and_edges(oracle):
     o_z = torch.zeros((nfr, cap), dtype=torch.float32, device=dev)
     o_p = torch.zeros((nfr, cap, 3), dtype=torch.float32, device=dev)
     o_n = torch.zeros(nfr, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()    # the fills above run on torch's stream, the library on its own
     m.stereo_fisheye_matches_batch_raw(dKL, dKR, dn[0], dn[1], dn[2], dn[3], cap, dI, dD, cap, nfr, rig, o_ltr, o_rtl, o_z,
                                        o_p, o_st, o_n, flags=_lib.IN_DEVICE | _lib.OUT_DEVICE)
     torch.cuda.synchronize()

@@ -66,6 +66,7 @@ def test_search_by_bow_ragged_device_batch(oracle):
     T = {k: torch.from_numpy(v).to(dev) for k, v in A.items()}
     dm = torch.zeros((F, cap), dtype=torch.int32, device=dev)
     dc = torch.zeros(F, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()    # the fills above run on torch's stream, the library on its own
     ORBmatcher(0.7, True).search_by_bow_batch_raw(T["dk"], T["ak"], T["vk"], T["kid"], T["kst"], T["kix"], T["kn"], T["df"], T["af"],
                                                   T["nf"], T["nl"], T["fid"], T["fst"], T["fix"], T["fn"], cap, ncap, F, dm, dc,
                                                   flags=_lib.IN_DEVICE | _lib.OUT_DEVICE)

@@ -132,11 +132,13 @@ def test_bow_kf_matchers_ragged_device_batch(oracle):
     dm = torch.zeros((F, cap), dtype=torch.int32, device=dev)
     dc = torch.zeros(F, dtype=torch.int32, device=dev)
     a, b = T["1"], T["2"]
+    torch.cuda.synchronize()    # the fills above run on torch's stream, the library on its own
     ORBmatcher(0.75, True).search_by_bow_kf_batch_raw(a["d"], a["a"], a["v"], a["id"], a["st"], a["ix"], a["nn"], b["d"], b["a"],
                                                       b["v"], b["id"], b["st"], b["ix"], b["nn"], cap, ncap, F, dm, dc, flags)
     m, cnt = dm.cpu().numpy(), dc.cpu().numpy()
     dm2 = torch.zeros((F, cap), dtype=torch.int32, device=dev)
     dc2 = torch.zeros(F, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
     scale, sigma2 = cases[0]["scale"], cases[0]["sigma2"]
     ORBmatcher(0.6, True).search_for_triangulation_batch_raw(a["k"], a["d"], a["fr"], a["s"], a["id"], a["st"], a["ix"], a["nn"],
                                                              b["k"], b["d"], b["fr"], b["s"], b["id"], b["st"], b["ix"], b["nn"],

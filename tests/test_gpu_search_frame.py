@@ -121,6 +121,7 @@ def test_frame_search_ragged_device_batch(oracle):
     dcnt = torch.zeros(F, dtype=torch.int32, device=dev)
     m = ORBmatcher(0.9, True)
     bounds, scale = (0.0, 0.0, 640.0, 480.0), frames[0][3]
+    torch.cuda.synchronize()    # the fills above run on torch's stream, the library on its own
     m.search_frame_batch_raw(dK, dD, dU, None, dn, None, ddir, cap, bounds, scale, 47.9, dP, dnp, pcap, F, 12.0, dml, dmr,
                              down, dcnt, flags=_lib.IN_DEVICE | _lib.OUT_DEVICE)
     ml, owner, cnt = dml.cpu().numpy(), down.cpu().numpy(), dcnt.cpu().numpy()

@@ -156,8 +156,9 @@ def test_kf_searches_ragged_device_batch(oracle):
     m = ORBmatcher(0.75, True)
     flags = _lib.IN_DEVICE | _lib.OUT_DEVICE
     dm, down, dcnt = z(F, pcap), z(F, cap), z(F)
-    m.search_sim3_projection_batch_raw(dK, dD, dO, dn, cap, bounds, scale, dP, dnp, pcap, F, 8.0, 1.5, dm, down, dcnt, flags)
     dbi, dbd, dfc = z(F, pcap), z(F, pcap), z(F)
+    torch.cuda.synchronize()    # the fills above run on torch's stream, the library on its own
+    m.search_sim3_projection_batch_raw(dK, dD, dO, dn, cap, bounds, scale, dP, dnp, pcap, F, 8.0, 1.5, dm, down, dcnt, flags)
     m.fuse_batch_raw(dK, dD, dU, dn, cap, bounds, scale, inv_sigma2, 47.9, dP, dnp, pcap, F, 3.0, True, dbi, dbd, dfc, flags)
     mm, owner, cnt = dm.cpu().numpy(), down.cpu().numpy(), dcnt.cpu().numpy()
     bi, bd, fc = dbi.cpu().numpy(), dbd.cpu().numpy(), dfc.cpu().numpy()

@@ -23,6 +23,7 @@ def _existing_knn(bf, dq, nq, dt, nt):
     import torch
     idx = torch.full((nq, 2), -7, dtype=torch.int32, device=dq.device)
     dist = torch.full((nq, 2), -7, dtype=torch.int32, device=dq.device)
+    torch.cuda.synchronize()    # the fills run on torch's stream, orbfe_knn2 on the matcher's own non-blocking stream
     bf.knn2_raw(dq, nq, dt, nt, idx, dist, flags=_lib.IN_DEVICE | _lib.OUT_DEVICE)
     return idx.cpu().numpy(), dist.cpu().numpy()
 
