@@ -18,6 +18,12 @@ def num(x):
     return float(x) if x not in ("", "n/a") else 0.0
 
 
+def kname(x):
+    """plain kernel name: no arguments, namespace, `void ` of a template instance or template arguments"""
+    x = re.sub(r"\(.*", "", x).split("::")[-1].strip()
+    return re.sub(r"<.*", "", re.sub(r"^void\s+", "", x))
+
+
 def main():
     rows = list(csv.reader(open(sys.argv[1])))
     images = int(sys.argv[2])
@@ -28,7 +34,7 @@ def main():
     t_scale = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "nsecond": 1e-3, "usecond": 1.0, "msecond": 1e3, "second": 1e6}
     traffic, issue_w, time_sum = {}, {}, {}
     for r in rows[2:]:
-        name = re.sub(r"\(.*", "", r[ci["Kernel Name"]]).split("::")[-1].strip()
+        name = kname(r[ci["Kernel Name"]])
         b = 0.0
         for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
             b += num(r[ci[m]]) * scale.get(units[ci[m]], 1.0)
@@ -51,7 +57,7 @@ def main():
         for r in csv.reader(open(sys.argv[4])):
             if len(r) < 15 or r[0] == "ID":
                 continue
-            name = re.sub(r"\(.*", "", r[4]).split("::")[-1].strip()
+            name = kname(r[4])
             m = r[12].replace("sm__inst_executed_pipe_", "").replace("smsp__inst_executed", "all").replace(".sum", "")
             if m.startswith("gpu__"):
                 continue
