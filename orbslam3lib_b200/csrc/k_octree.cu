@@ -227,6 +227,90 @@ __device__ void std_sort(SortArr& a, int n) {
     }
 }
 
+// ---- the same std::sort, computed by a warp + the block --------------------------------------------------------------------
+// The serial port above costs ~40 % of the kernel (255 threads wait for lane 0).  Two observations make it parallel
+// without changing a single result:
+//  (1) __unguarded_partition is a Hoare partition whose swaps are known in advance: with A = the positions (ascending) whose
+//      key is not less than the pivot and B = the positions (descending) whose key is not greater, the k-th swap exchanges
+//      A_k and B_k as long as A_k < B_k (positions changed by earlier swaps lie behind the two scan pointers), and the
+//      returned cut is min(A_{s+1}, B_s) after s swaps (the left scan stops at the next original stopper or at the last
+//      swapped right position, which now holds a key >= pivot).  A warp builds both lists with ballots, swaps in parallel.
+//      The median-of-3 step and the (rare) heapsort at the depth limit stay literal, on lane 0.
+//  (2) __final_insertion_sort never moves an element past an equal one, so it is a STABLE sort of the array the introsort
+//      loop leaves; that array consists of unsorted runs of <= 16 elements in sorted order (heapsorted runs are sorted), so
+//      the final position of element i is i - #{j in [i-15, i): key_j > key_i} + #{j in (i, i+15]: key_j < key_i}: every
+//      thread of the block computes one.
+__device__ void warp_introsort_loop(SortArr& a, int n, int* listA, int* listB, int* stk) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t ltMask = (1u << lane) - 1u;
+    if (n <= 16) return;
+    int lg = 0;
+    for (int v = n; v > 1; v >>= 1) lg++;
+    int sp = 0;
+    if (lane == 0) { stk[0] = 0; stk[1] = n; stk[2] = 2 * lg; }
+    sp = 1;
+    __syncwarp();
+    while (sp > 0) {
+        --sp;
+        int first = stk[3 * sp], last = stk[3 * sp + 1], depth = stk[3 * sp + 2];
+        __syncwarp();
+        while (last - first > 16) {
+            if (depth == 0) {
+                if (lane == 0) std_heap_sort(a, first, last);
+                __syncwarp();
+                break;
+            }
+            --depth;
+            if (lane == 0) {    // __move_median_to_first(first, first + 1, mid, last - 1)
+                const int A = first + 1, B = first + (last - first) / 2, C = last - 1;
+                if (a.less(A, B)) {
+                    if (a.less(B, C)) a.swap(first, B);
+                    else if (a.less(A, C)) a.swap(first, C);
+                    else a.swap(first, A);
+                } else if (a.less(A, C)) a.swap(first, A);
+                else if (a.less(B, C)) a.swap(first, C);
+                else a.swap(first, B);
+            }
+            __syncwarp();
+            const unsigned long long pivot = a.k[first];
+            int cntA = 0, cntB = 0;
+            for (int base = first + 1; base < last; base += 32) {    // A: ascending positions with !(key < pivot)
+                const int p = base + lane;
+                const bool geq = p < last && !(a.k[p] < pivot);
+                const uint32_t m = __ballot_sync(0xffffffffu, geq);
+                if (geq) listA[cntA + __popc(m & ltMask)] = p;
+                cntA += __popc(m);
+            }
+            for (int base = last - 1; base > first; base -= 32) {    // B: descending positions with !(pivot < key)
+                const int p = base - lane;
+                const bool leq = p > first && !(pivot < a.k[p]);
+                const uint32_t m = __ballot_sync(0xffffffffu, leq);
+                if (leq) listB[cntB + __popc(m & ltMask)] = p;
+                cntB += __popc(m);
+            }
+            __syncwarp();
+            const int pairs = min(cntA, cntB);
+            int sw = 0;
+            for (int kb = 0; kb < pairs; kb += 32) {
+                const int k = kb + lane;
+                const bool ok = k < pairs && listA[k] < listB[k];
+                const uint32_t m = __ballot_sync(0xffffffffu, ok);
+                if (ok) a.swap(listA[k], listB[k]);
+                sw += __popc(m);
+                if (m != 0xffffffffu) break;
+            }
+            __syncwarp();
+            const int nextA = sw < cntA ? listA[sw] : 0x7fffffff, prevB = sw > 0 ? listB[sw - 1] : 0x7fffffff;
+            const int cut = min(nextA, prevB);
+            __syncwarp();    // the lists are rewritten by the next partition
+            if (lane == 0 && sp < 64) { stk[3 * sp] = cut; stk[3 * sp + 1] = last; stk[3 * sp + 2] = depth; }
+            if (sp < 64) sp++;
+            last = cut;
+        }
+        __syncwarp();
+    }
+}
+
 __device__ __forceinline__ int key_quadrant(uint32_t key, int mx, int my) {
     const int x = key & 0xfff, y = (key >> 12) & 0xfff;
     return (x < mx ? 0 : 1) | (y < my ? 0 : 2);    // 0 = n1 (UL), 1 = n2 (UR), 2 = n3 (BL), 3 = n4 (BR), :516-526
@@ -238,6 +322,7 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int wsum[2 * OT_WARPS + 2];
     __shared__ int sK, sTotal;
+    __shared__ int sortStack[3 * 64];
 
     const int level = blockIdx.x, img = blockIdx.y;
     const LevelGeom& L = g.lv[level];
@@ -380,13 +465,28 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
                 if (s.tB[i]) s.P[s.tA[i]] = i;
         } else {
             // std::sort(compareNodes) of the expandable nodes, then back to front (:700-705)
+            np = ne;
+#ifdef ORBFE_OT_SERIAL_SORT
             if (tid == 0) {
                 SortArr a{s.ekey, s.epos};
                 std_sort(a, ne);
             }
             __syncthreads();
-            np = ne;
             for (int k = tid; k < np; k += OT_THREADS) s.P[k] = s.epos[np - 1 - k];
+#else
+            if (warp == 0) {
+                SortArr a{s.ekey, s.epos};
+                warp_introsort_loop(a, ne, s.tA, s.tB, sortStack);
+            }
+            __syncthreads();
+            for (int i = tid; i < ne; i += OT_THREADS) {    // the final insertion sort as a stable rank (see above)
+                const unsigned long long ki = s.ekey[i];
+                int rank = i;
+                for (int j = max(0, i - 15); j < i; j++) rank -= s.ekey[j] > ki;
+                for (int j = i + 1; j <= min(ne - 1, i + 15); j++) rank += s.ekey[j] < ki;
+                s.P[np - 1 - rank] = s.epos[i];
+            }
+#endif
         }
         __syncthreads();
 
