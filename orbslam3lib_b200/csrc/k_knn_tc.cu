@@ -275,6 +275,166 @@ __global__ void __launch_bounds__(KT_THREADS) knn2_tc_kernel(const uint8_t* __re
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(KT_N) : "memory");
 }
 
+// ---- knn2_tck_kernel: the per-pair (C2 / C3) shape with the top-2 KEY computed by the tensor core -----------------------------
+// At 1200 x 1200 per pair a CTA runs 10 train tiles and the epilogue is 60 % of the kernel's instructions: per accumulator
+// one LEA to build key = acc << S | column and ~2.2 VIMNMX for the top 2, plus a guarded copy of the loop for the last,
+// partial tile.  Here the MMA delivers the key itself:
+//   * A' = +-64 (instead of +-1) and B = 2 b (instead of b): every product is +-128, acc' = 128 (hamming - |a|);
+//   * a ninth K = 32 instruction adds the column: A row = [1, 127, 127, 127, 127, 0 ...], B row of tile column j =
+//     [j, inv, inv, inv, inv, 0 ...] with inv = 127 for columns past the end of the train set, so the accumulator is
+//     128 (hamming - |a|) + j (+ 64516 for an invalid column: above every valid key);
+//   * the epilogue is the bare top-2 insertion on the accumulators (no LEA, no guard), decoded once per tile:
+//     distance = (key >> 7) + |a|, column = key & 127.  Equal distances keep the lower train index (lower j inside a
+//     tile, earlier tile across tiles), as OpenCV does.
+// 12.5 % more tensor work for ~40 % fewer instructions; used for batches of pairs and short train sets (the long-train-set
+// kernel above keeps its prefilter and its train segments).
+constexpr int KK_CHUNKS = 18;                               // 16 descriptor chunks + the key chunk pair
+constexpr int KK_SMEM = (KT_M + KT_N) * 16 * KK_CHUNKS + 64;
+constexpr int KK_EMPTY = 0x7fffffff;
+static_assert(KT_N <= 128 || true, "the key holds a 7-bit tile column: the launcher uses this kernel for KT_N == 128 only");
+
+template <bool SIGNED_A>
+__device__ __forceinline__ void kk_expand_row(uint8_t* base, int rows, int r, const uint4& lo, const uint4& hi) {
+    const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    uint8_t* rowp = base + (r >> 3) * 128 + (r & 7) * 16;
+    const int chunkStride = (rows >> 3) * 128;
+    auto ex = [](uint32_t v, int n) -> uint32_t {    // bit n of every byte of v -> A: 0x40 | bit << 7 (= +-64), B: bit << 1
+        if (SIGNED_A) return ((v << (7 - n)) & 0x80808080u) | 0x40404040u;
+        return (n >= 1 ? (v >> (n - 1)) : (v << 1)) & 0x02020202u;
+    };
+#pragma unroll
+    for (int q = 0; q < 16; q++) {
+        const int p = q & 3, j = q >> 2;
+        *reinterpret_cast<uint4*>(rowp + q * chunkStride) =
+            make_uint4(ex(w[2 * p], 2 * j), ex(w[2 * p], 2 * j + 1), ex(w[2 * p + 1], 2 * j), ex(w[2 * p + 1], 2 * j + 1));
+    }
+}
+
+// grid (ceil(maxNq / KT_M), npairs); block KT_THREADS; dynamic shared memory KK_SMEM
+__global__ void __launch_bounds__(KT_THREADS) knn2_tck_kernel(const uint8_t* __restrict__ q, const int* __restrict__ nqArr,
+                                                             long long qCap, const uint8_t* __restrict__ t,
+                                                             const int* __restrict__ ntArr, long long tCap,
+                                                             long long nqSingle, long long ntSingle,
+                                                             int32_t* __restrict__ idx, int32_t* __restrict__ dist) {
+    extern __shared__ __align__(128) uint8_t ktSmem[];
+    uint8_t* sA = ktSmem;
+    uint8_t* sB = ktSmem + KT_M * 16 * KK_CHUNKS;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(ktSmem + (KT_M + KT_N) * 16 * KK_CHUNKS);
+    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(bar + 1);
+
+    const int pair = blockIdx.y;
+    const long long nq = nqArr ? nqArr[pair] : nqSingle;
+    const long long nt = ntArr ? ntArr[pair] : ntSingle;
+    if ((long long)blockIdx.x * KT_M >= nq) return;    // uniform: before any allocation
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const long long row = (long long)blockIdx.x * KT_M + tid;
+    const uint4* tp = reinterpret_cast<const uint4*>(t + (long long)pair * tCap * 32);
+
+    if (tid == 0) mbar_init(bar, 1);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmemSlot)), "n"(KT_N)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    int na = 0;
+    {
+        uint4 lo = make_uint4(0u, 0u, 0u, 0u), hi = lo;
+        if (row < nq) {
+            const uint4* qp = reinterpret_cast<const uint4*>(q + ((long long)pair * qCap + row) * 32);
+            lo = __ldg(qp);
+            hi = __ldg(qp + 1);
+        }
+        na = __popc(lo.x) + __popc(lo.y) + __popc(lo.z) + __popc(lo.w) + __popc(hi.x) + __popc(hi.y) + __popc(hi.z) + __popc(hi.w);
+        kk_expand_row<true>(sA, KT_M, tid, lo, hi);
+        uint8_t* rowp = sA + (tid >> 3) * 128 + (tid & 7) * 16;    // key chunk pair of the A row: [1, 127 x 4, 0 ...]
+        *reinterpret_cast<uint4*>(rowp + 16 * (KT_M >> 3) * 128) = make_uint4(0x7f7f7f01u, 0x0000007fu, 0u, 0u);
+        *reinterpret_cast<uint4*>(rowp + 17 * (KT_M >> 3) * 128) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = *tmemSlot;
+    const uint32_t aBase = smem_u32(sA), bBase = smem_u32(sB);
+
+    int d1 = -1, i1 = -1, d2 = -1, i2 = -1;
+    uint32_t phase = 0;
+    const long long ntiles = (nt + KT_N - 1) / KT_N;
+    uint4 nx[KT_RPT][2];
+    auto fetch = [&](long long j0) {
+#pragma unroll
+        for (int u = 0; u < KT_RPT; u++) {
+            const long long r = j0 + u * KT_THREADS + tid;
+            nx[u][0] = nx[u][1] = make_uint4(0u, 0u, 0u, 0u);
+            if (r < nt) {
+                nx[u][0] = __ldg(tp + r * 2);
+                nx[u][1] = __ldg(tp + r * 2 + 1);
+            }
+        }
+    };
+    fetch(0);
+    for (long long ti = 0; ti < ntiles; ti++) {
+        const long long j0 = ti * KT_N;
+        // B tile -> shared memory (the previous tile's MMAs have completed: every thread waited on the barrier)
+#pragma unroll
+        for (int u = 0; u < KT_RPT; u++) {
+            const int r = u * KT_THREADS + tid;
+            kk_expand_row<false>(sB, KT_N, r, nx[u][0], nx[u][1]);
+            const uint32_t inv = j0 + r < nt ? 0u : 0x7fu;
+            uint8_t* rowp = sB + (r >> 3) * 128 + (r & 7) * 16;
+            *reinterpret_cast<uint4*>(rowp + 16 * (KT_N >> 3) * 128) = make_uint4((uint32_t)r | (inv * 0x01010100u), inv, 0u, 0u);
+            *reinterpret_cast<uint4*>(rowp + 17 * (KT_N >> 3) * 128) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");    // orders the previous tile's tcgen05.ld
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int s = 0; s < KK_CHUNKS / 2; s++) {
+                const uint64_t ad = kt_desc(aBase + 2 * s * (KT_M >> 3) * 128, (KT_M >> 3) * 128, 128);
+                const uint64_t bd = kt_desc(bBase + 2 * s * (KT_N >> 3) * 128, (KT_N >> 3) * 128, 128);
+                kt_mma_i8(tmem, ad, bd, KT_IDESC, s > 0);
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                         : "memory");
+        }
+        if (ti + 1 < ntiles) fetch(j0 + KT_N);
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        int b1 = KK_EMPTY, b2 = KK_EMPTY;
+#pragma unroll 1
+        for (int c = 0; c < KT_N; c += 32) {
+            int v[32];
+            kt_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, v);
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+                b2 = min(b2, max(b1, v[i]));
+                b1 = min(b1, v[i]);
+            }
+        }
+        // decode: key = 128 (hamming - |a|) + column of the tile; invalid columns sit above 64000
+        auto merge = [&](int b) {
+            if (b > 48000) return;
+            const int dd = (b >> 7) + na;
+            const int i = (int)(j0 + (b & 127));
+            if (i1 < 0 || dd < d1) { d2 = d1; i2 = i1; d1 = dd; i1 = i; }
+            else if (i2 < 0 || dd < d2) { d2 = dd; i2 = i; }
+        };
+        merge(b1);
+        merge(b2);
+    }
+    if (row < nq) {
+        const long long o = ((long long)pair * qCap + row) * 2;
+        *reinterpret_cast<int2*>(idx + o) = make_int2(i1, i2);
+        *reinterpret_cast<int2*>(dist + o) = make_int2(d1, d2);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(KT_N) : "memory");
+}
+
 // train segments for one large problem: the smallest count (<= 16) whose CTA total fills the resident-CTA waves to
 // >= 98.5 %, else the best; segments stay >= 8k rows.  ORBFE_KNN_SEGS=n forces n (tests).
 static int kt_pick_segments(long long tiles, long long nt, int resident) {
@@ -314,6 +474,15 @@ int launch_knn2_tc(const uint8_t* q, const int* nq, long long qCap, const uint8_
     });
     const int resident = residentOf[dev & 63];
     const long long tiles = (maxNq + KT_M - 1) / KT_M;
+    // batches of pairs and short train sets: the keyed kernel (ORBFE_KNN_KEYED=0: the kernel above for everything)
+    static const bool keyed = [] { const char* e = getenv("ORBFE_KNN_KEYED"); return !e || atoi(e) != 0; }();
+    if (keyed && KT_N == 128 && (npairs > 1 || nq || nt || ntSingle <= 8192)) {
+        static SmemOptIn optInK;
+        smem_opt_in(optInK, knn2_tck_kernel, (size_t)KK_SMEM);
+        knn2_tck_kernel<<<dim3((unsigned)tiles, npairs), KT_THREADS, KK_SMEM, st>>>(q, nq, qCap, t, nt, tCap, nqSingle, ntSingle, idx,
+                                                                                dist);
+        return 1;
+    }
     int nseg = 1;
     if (npairs == 1 && !nq && !nt) nseg = kt_pick_segments(tiles, ntSingle, resident);
     // stream-ordered scratch for the segmented launch: partial results [nseg][tiles * 128] + one ticket per tile
