@@ -338,8 +338,10 @@ static int set_err(orbfe_extractor* ex, int code, const char* fmt, ...) {
 #define ORBFE_CUDA(ex, call)                                                                              \
     do {                                                                                                  \
         cudaError_t e__ = (call);                                                                         \
-        if (e__ != cudaSuccess)                                                                           \
+        if (e__ != cudaSuccess) {                                                                         \
+            cudaGetLastError(); /* reported here: a later, valid call must not find it as its own launch error */ \
             return set_err(ex, ORBFE_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+        }                                                                                                 \
     } while (0)
 
 static size_t per_image_bytes(const Geom& g) {
@@ -561,6 +563,7 @@ int orbfe_extractor_create(int device, const orbfe_params* params, orbfe_extract
     ex->params = *params;
     build_tables(*params, ex->tables);
     if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ex->ownStream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();    // reported by the return code: do not leave it for the next call's launch check
         delete ex;
         return ORBFE_ERR_CUDA;
     }
@@ -1175,8 +1178,10 @@ static int set_merr(orbfe_matcher* m, int code, const char* fmt, ...) {
 #define ORBFE_MCUDA(m, call)                                                                               \
     do {                                                                                                   \
         cudaError_t e__ = (call);                                                                          \
-        if (e__ != cudaSuccess)                                                                            \
+        if (e__ != cudaSuccess) {                                                                          \
+            cudaGetLastError(); /* as in ORBFE_CUDA */                                                         \
             return set_merr(m, ORBFE_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+        }                                                                                                  \
     } while (0)
 
 static int knn_common(orbfe_matcher* m, const uint8_t* q, const int32_t* nq, long long qCap, const uint8_t* t,
@@ -1279,6 +1284,7 @@ int orbfe_matcher_create(int device, orbfe_matcher** out) {
     orbfe_matcher* m = new orbfe_matcher();
     m->device = device;
     if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&m->ownStream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();    // as in orbfe_extractor_create
         delete m;
         return ORBFE_ERR_CUDA;
     }

@@ -82,6 +82,26 @@ def test_bad_constructor_arguments():
 
 
 @pytest.mark.gpu
+def test_failed_create_does_not_poison_the_next_call(oracle):
+    """a CUDA error reported by one call (device 99 does not exist) must not come back as the launch error of the next, valid
+    call of the thread: the library clears the runtime's last-error state when it reports it."""
+    from orbslam3lib_b200._lib import OrbfeError
+    from orbslam3lib_b200 import BFMatcher, scenes
+    with pytest.raises(OrbfeError):
+        ORBextractor(500, 1.2, 8, 20, 7, device=99)
+    with pytest.raises(OrbfeError):
+        BFMatcher(device=99)
+    img = scenes.make("texture", 320, 240, 77)
+    mono, kps, desc = ORBextractor(500, 1.2, 8, 20, 7)(img)
+    rmono, rk, rd = oracle.OracleExtractor(500, 1.2, 8, 20, 7)(img)
+    np.testing.assert_array_equal(desc, rd)
+    q, t = scenes.map_descriptors(300, 700, 78)
+    idx, dist = BFMatcher().knnMatch(q, t)
+    ri, rdist = oracle.knn2_hamming(q, t)
+    np.testing.assert_array_equal(idx, ri)
+
+
+@pytest.mark.gpu
 def test_two_devices_in_one_process(oracle):
     """The opt-in for > 48 KiB of dynamic shared memory is a per-device property: extractors and matchers on
     device 0 AND device 1 of one process, with the configuration whose kernels need the opt-in (nfeatures = 5000: ~87 KiB
