@@ -264,8 +264,8 @@ int orbfe_search_by_bow_kf_batch(orbfe_matcher* m, const uint8_t* desc1, const f
  * f12[pair*9 + 3*r + c] = F12(r, c) = K1^-T [t12]x R12 K2^-1 (Pinhole.cpp:104-107; unread when coarse); epipole[pair*2 ...] =
  * pKF2->mpCamera->project(T2w * Cw1) (:930-932); scale_factors / level_sigma2 = pKF2's mvScaleFactors / mvLevelSigma2.
  * matches12[pair*cap + i1] = vMatches12[i1] after the rotation check (vMatchedPairs = the pairs (i1, matches12[i1]) with
- * matches12[i1] >= 0, in i1 order); nmatches[pair] = the return value.  The KannalaBrandt8 form of the constraint (a
- * triangulation, KannalaBrandt8.cpp:210-214) is not covered: use coarse for two-camera rigs. */
+ * matches12[i1] >= 0, in i1 order); nmatches[pair] = the return value.  Two-camera (KannalaBrandt8) key frames:
+ * orbfe_search_for_triangulation_kb8_batch below. */
 int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1,
                                          const uint8_t* stereo1, const int32_t* node_ids1, const int32_t* node_start1,
                                          const int32_t* idx1, const int32_t* nnodes1, const orbfe_keypoint* keys2,
@@ -408,6 +408,27 @@ int orbfe_stereo_fisheye_matches_batch(orbfe_matcher* m, const orbfe_keypoint* k
                                        int knn_cap, int nframes, const orbfe_fisheye_rig* rig, int32_t* left_to_right,
                                        int32_t* right_to_left, float* depth, float* points3d, int32_t* status,
                                        int32_t* nmatches, unsigned flags);
+/* ORBmatcher::SearchForTriangulation for key frames of a TWO-CAMERA rig (mpCamera2 != NULL, the Lynx fisheye pair;
+ * ORBmatcher.cc:908-1153 with the branch :1014-1043 and KannalaBrandt8::epipolarConstrain, KannalaBrandt8.cpp:210-214 =
+ * TriangulateMatches(...) > 0.0001).  Features of a key frame = its left keypoints (mvKeys, nleftN[pair] of them) followed by
+ * its right ones (mvKeysRight), descriptor rows likewise; feature vectors as CSR like orbfe_search_for_triangulation_batch;
+ * freeN[i] = GetMapPoint(i) == NULL.  rig: cam1 / cam2 = the parameters of mpCamera / mpCamera2 and precision (Rlr, tlr and
+ * the level table of the struct are not read).  t12[pair*48 + 12*c ...] = R12 (row-major, 9) and t12 (3) of the relative pose
+ * c = 0: Tll = T1w * Tw2, 1: Tlr = T1w * Twr2, 2: Trl = Tr1w * Tw2, 3: Trr = Tr1w * Twr2 (:934-940); the pair of a candidate
+ * picks c = 2 * (idx1 >= nleft1) + (idx2 >= nleft2) and the matching cameras (:1015-1042).  level_sigma2 = mvLevelSigma2 (both
+ * key frames).  No epipole gate and no mvuRight in this mode (bStereo is false when mpCamera2 is set).  coarse != 0 skips the
+ * constraint.  Results as orbfe_search_for_triangulation_batch.  The triangulation is the device code of
+ * orbfe_stereo_fisheye_matches_batch: float as the reference, null vector in double (decisions equal the reference's away
+ * from the gates). */
+int orbfe_search_for_triangulation_kb8_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1,
+                                             const uint8_t* free1, const int32_t* nleft1, const int32_t* node_ids1,
+                                             const int32_t* node_start1, const int32_t* idx1, const int32_t* nnodes1,
+                                             const orbfe_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2,
+                                             const int32_t* nleft2, const int32_t* node_ids2, const int32_t* node_start2,
+                                             const int32_t* idx2, const int32_t* nnodes2, int cap, int node_cap, int npairs,
+                                             const orbfe_fisheye_rig* rig, const float* t12, const float* level_sigma2, int nlevels,
+                                             int coarse, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                             unsigned flags);
 /* Frame::UndistortKeyPoints (Frame.cc:763-796): mvKeysUn = mvKeys with the positions passed through
  * cv::undistortPoints(pts, pts, K, mDistCoef, Mat(), mK) (OpenCV 4.x: 5 fixed-point iterations in double); K = (fx, fy,
  * cx, cy) of mK, dist_coef = k1, k2, p1, p2[, k3] (ndist 4 or 5, up to OpenCV's 14); dist_coef[0] == 0 copies the

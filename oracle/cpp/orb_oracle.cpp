@@ -2369,6 +2369,103 @@ static float kb_triangulate_matches(const orc_fisheye_rig* g, float x1, float y1
     return z1;
 }
 
+// ---- ORBmatcher::SearchForTriangulation for two-camera key frames (ORBmatcher.cc:908-1153 with :1014-1043) ------------------
+// Features = left keypoints then right keypoints; KannalaBrandt8::epipolarConstrain (KannalaBrandt8.cpp:210-214).  rig->cam1 /
+// cam2 = mpCamera / mpCamera2 parameters; T12[c] = R12 (row-major) | t12 for c = 0 Tll, 1 Tlr, 2 Trl, 3 Trr.  slack[i1]
+// (optional) = the smallest distance of any tested quantity from its gate over the candidates evaluated for feature i1.
+int orc_search_for_triangulation_kb8(const orc_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1, int n1, int nleft1,
+                                     const int32_t* nodeIds1, const int32_t* nodeStart1, const int32_t* idx1v, int nodes1,
+                                     const orc_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, int nleft2,
+                                     const int32_t* nodeIds2, const int32_t* nodeStart2, const int32_t* idx2v, int nodes2,
+                                     const orc_fisheye_rig* rig, const float* T12, const float* mvLevelSigma2, int bCoarse,
+                                     int checkOrientation, int32_t* vMatches12, float* slack) {
+    const int TH_LOW = 50, HISTO_LENGTH = 30;
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) {
+        vMatches12[i] = -1;
+        if (slack) slack[i] = 1e30f;
+    }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int f1it = 0, f2it = 0;
+    while (f1it != nodes1 && f2it != nodes2) {
+        if (nodeIds1[f1it] == nodeIds2[f2it]) {
+            for (int i1 = nodeStart1[f1it]; i1 < nodeStart1[f1it + 1]; i1++) {
+                const size_t idx1 = (size_t)idx1v[i1];
+                if (!free1[idx1]) continue;    // pMP1 (bStereo1 is false with mpCamera2: bOnlyStereo would drop everything)
+                const orc_keypoint& kp1 = keys1[idx1];    // mvKeys[idx1] or mvKeysRight[idx1 - NLeft]: concatenated here
+                const bool bRight1 = (int)idx1 >= nleft1;
+                int bestDist = TH_LOW;
+                int bestIdx2 = -1;
+                for (int i2 = nodeStart2[f2it]; i2 < nodeStart2[f2it + 1]; i2++) {
+                    size_t idx2 = (size_t)idx2v[i2];
+                    if (!free2[idx2]) continue;
+                    const int dist = desc_distance(desc1 + idx1 * 32, desc2 + idx2 * 32);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    const orc_keypoint& kp2 = keys2[idx2];
+                    const bool bRight2 = (int)idx2 >= nleft2;
+                    // :1015-1042: R12 / t12 / pCamera1 / pCamera2 by the sides of the two features
+                    const int c = (bRight1 ? 2 : 0) + (bRight2 ? 1 : 0);
+                    bool ok = bCoarse != 0;
+                    if (!ok) {
+                        orc_fisheye_rig g = *rig;
+                        std::memcpy(g.cam1, bRight1 ? rig->cam2 : rig->cam1, sizeof(g.cam1));
+                        std::memcpy(g.cam2, bRight2 ? rig->cam2 : rig->cam1, sizeof(g.cam2));
+                        std::memcpy(g.Rlr, T12 + 12 * c, 9 * sizeof(float));
+                        std::memcpy(g.tlr, T12 + 12 * c + 9, 3 * sizeof(float));
+                        float p3D[3], sl;
+                        const float z = kb_triangulate_matches(&g, kp1.x, kp1.y, kp2.x, kp2.y, mvLevelSigma2[kp1.octave],
+                                                               mvLevelSigma2[kp2.octave], p3D, &sl);
+                        if (z > 0 && std::fabs(z - 0.0001f) < sl) sl = std::fabs(z - 0.0001f);
+                        if (slack && sl < slack[idx1]) slack[idx1] = sl;
+                        ok = z > 0.0001f;    // KannalaBrandt8::epipolarConstrain
+                    }
+                    if (ok) {
+                        bestIdx2 = (int)idx2;
+                        bestDist = dist;
+                    }
+                }
+                if (bestIdx2 >= 0) {
+                    const orc_keypoint& kp2 = keys2[bestIdx2];
+                    vMatches12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (checkOrientation) {
+                        float rot = kp1.angle - kp2.angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back((int)idx1);
+                    }
+                }
+            }
+            f1it++;
+            f2it++;
+        } else if (nodeIds1[f1it] < nodeIds2[f2it]) {
+            f1it = (int)(std::lower_bound(nodeIds1, nodeIds1 + nodes1, nodeIds2[f2it]) - nodeIds1);
+        } else {
+            f2it = (int)(std::lower_bound(nodeIds2, nodeIds2 + nodes2, nodeIds1[f1it]) - nodeIds2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                vMatches12[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
+// test hook: KannalaBrandt8::TriangulateMatches for one pair (rig->cam1 / cam2 / Rlr / tlr as given)
+float orc_kb_triangulate_matches(const orc_fisheye_rig* rig, float x1, float y1, float x2, float y2, float sigmaLevel, float unc) {
+    float p3D[3], sl;
+    return kb_triangulate_matches(rig, x1, y1, x2, y2, sigmaLevel, unc, p3D, &sl);
+}
+
 int orc_stereo_fisheye_matches(const orc_keypoint* keysL, int nL, int monoL, const orc_keypoint* keysR, int nR, int monoR,
                                const int32_t* knnIdx, const int32_t* knnDist, const orc_fisheye_rig* rig,
                                int32_t* leftToRight, int32_t* rightToLeft, float* depth, float* p3d, int32_t* status, float* slack) {

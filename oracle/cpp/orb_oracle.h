@@ -234,6 +234,16 @@ int orc_stereo_fisheye_matches(const orc_keypoint* keysL, int nL, int monoL, con
                                int32_t* leftToRight, int32_t* rightToLeft, float* depth, float* p3d, int32_t* status,
                                float* slack);
 
+/* ORBmatcher::SearchForTriangulation for two-camera (KannalaBrandt8) key frames: features = left then right keypoints,
+ * rig->cam1 / cam2 = mpCamera / mpCamera2, T12[12 c ...] = R12 | t12 of Tll, Tlr, Trl, Trr; slack (optional, n1 floats). */
+int orc_search_for_triangulation_kb8(const orc_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1, int n1, int nleft1,
+                                     const int32_t* nodeIds1, const int32_t* nodeStart1, const int32_t* idx1, int nodes1,
+                                     const orc_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, int nleft2,
+                                     const int32_t* nodeIds2, const int32_t* nodeStart2, const int32_t* idx2, int nodes2,
+                                     const orc_fisheye_rig* rig, const float* T12, const float* mvLevelSigma2, int bCoarse,
+                                     int checkOrientation, int32_t* matches12, float* slack);
+float orc_kb_triangulate_matches(const orc_fisheye_rig* rig, float x1, float y1, float x2, float y2, float sigmaLevel, float unc);
+
 int orc_hardware_threads(void);
 #ifdef __cplusplus
 }

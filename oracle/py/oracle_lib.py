@@ -582,6 +582,40 @@ def stereo_fisheye_matches(keys_left, mono_left, keys_right, mono_right, knn_idx
     return ltr, rtl, depth, p3d, status, int(n), slack
 
 
+def search_for_triangulation_kb8(keys1, desc1, free1, nleft1, fv1, keys2, desc2, free2, nleft2, fv2, rig, t12, level_sigma2,
+                                 coarse=False, check_orientation=True):
+    """ORBmatcher::SearchForTriangulation for two-camera (KannalaBrandt8) key frames (ORBmatcher.cc:908-1153, :1014-1043).
+    -> (vMatches12, nmatches, slack)"""
+    k1, k2 = np.ascontiguousarray(keys1, KP_DTYPE), np.ascontiguousarray(keys2, KP_DTYPE)
+    d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    f1, f2 = np.ascontiguousarray(free1, np.uint8), np.ascontiguousarray(free2, np.uint8)
+    a = [np.ascontiguousarray(x, np.int32) for x in fv1]
+    b = [np.ascontiguousarray(x, np.int32) for x in fv2]
+    rg = np.ascontiguousarray(rig, FISHEYE_RIG_DTYPE)
+    T = np.ascontiguousarray(t12, np.float32).reshape(48)
+    sg = np.ascontiguousarray(level_sigma2, np.float32)
+    m, sl = np.empty(max(len(k1), 1), np.int32), np.empty(max(len(k1), 1), np.float32)
+    L = lib()
+    L.orc_search_for_triangulation_kb8.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_int] + [C.c_void_p] * 3 + [C.c_int] + \
+        [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    L.orc_search_for_triangulation_kb8.restype = C.c_int
+    nm = L.orc_search_for_triangulation_kb8(_p(k1), _p(d1), _p(f1), len(k1), int(nleft1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]),
+                                            _p(k2), _p(d2), _p(f2), int(nleft2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), _p(rg),
+                                            _p(T), _p(sg), int(bool(coarse)), int(bool(check_orientation)), _p(m), _p(sl))
+    return m[:len(k1)].copy(), int(nm), sl[:len(k1)].copy()
+
+
+def kb_triangulate_matches(rig, x1, y1, x2, y2, sigma_level, unc):
+    """KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:300-363) of rig.cam1 against rig.cam2 with (Rlr, tlr): z1 or
+    the negative reason."""
+    rg = np.ascontiguousarray(rig, FISHEYE_RIG_DTYPE)
+    L = lib()
+    L.orc_kb_triangulate_matches.argtypes = [C.c_void_p] + [C.c_float] * 6
+    L.orc_kb_triangulate_matches.restype = C.c_float
+    return float(L.orc_kb_triangulate_matches(_p(rg), float(x1), float(y1), float(x2), float(y2), float(sigma_level), float(unc)))
+
+
 def undistort_keypoints(kps, fx, fy, cx, cy, dist):
     """Frame::UndistortKeyPoints (Frame.cc:763-796) -> mvKeysUn."""
     k = np.ascontiguousarray(kps, KP_DTYPE)

@@ -94,6 +94,7 @@ SYMBOLS = {
     "orbfe_search_for_triangulation_batch": (_i, [_vp] * 17 + [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _u]),
     "orbfe_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, C.c_int64, _i, _vp, _vp, _vp, _u]),
     "orbfe_knn2_static_scratch": (_i, [_vp, C.c_int64, _vp, C.c_int64, _vp, _vp, _vp, _vp, C.c_size_t]),
+    "orbfe_search_for_triangulation_kb8_batch": (_i, [_vp] * 17 + [_i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _u]),
     "orbfe_search_for_initialization_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, C.c_float, _i, _vp,
                                                    _vp, _vp, _u]),
     "orbfe_stereo_fisheye_matches_batch": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp,

@@ -14,7 +14,7 @@
 // features in order, lanes stride over the frame's features of the node: 256-bit XOR + POPC, best = first minimum in
 // vector order = min (distance, position), second = second smallest distance with multiplicity, merged by shuffles.
 // Feature vectors come as CSR arrays (node ids ascending, start[nnodes + 1], indices in vector order).
-#include "orbfe_internal.h"
+#include "kb8.cuh"
 
 namespace orbfe {
 
@@ -305,6 +305,11 @@ struct TriParams {
     int cap, nodeCap;
     int coarse, checkOrientation;
     float scale[ORBFE_MAX_LEVELS], sigma2[ORBFE_MAX_LEVELS];
+    // two-camera (KannalaBrandt8) key frames (:1014-1043): mpCamera / mpCamera2 parameters; the features of a key frame are
+    // its left keypoints followed by its right ones, the constraint is KannalaBrandt8::epipolarConstrain
+    // (KannalaBrandt8.cpp:210-214: TriangulateMatches(...) > 0.0001) with the relative pose picked by the two sides
+    int kb8;
+    float camL[8], camR[8], precision;
 };
 
 __device__ __forceinline__ unsigned sb_min_u32(unsigned v) {
@@ -321,11 +326,13 @@ __global__ void __launch_bounds__(SB_THREADS) search_triangulation_kernel(
     const orbfe_keypoint* __restrict__ keys2All, const uint8_t* __restrict__ desc2All, const uint8_t* __restrict__ free2All,
     const uint8_t* __restrict__ stereo2All, const int* __restrict__ ids2All, const int* __restrict__ start2All,
     const int* __restrict__ idx2All, const int* __restrict__ nodes2, const float* __restrict__ F12All,
-    const float* __restrict__ epAll, int* __restrict__ matchesAll, int* __restrict__ nMatches) {
+    const float* __restrict__ epAll, const float* __restrict__ T12All, const int* __restrict__ nleft1Arr,
+    const int* __restrict__ nleft2Arr, int* __restrict__ matchesAll, int* __restrict__ nMatches) {
     extern __shared__ __align__(16) uint8_t binOf[];
     __shared__ int hist[32];
     __shared__ int sCount, sInd[3];
     __shared__ float sF[9], sEp[2];
+    __shared__ float sT[4][12];    // Tll, Tlr, Trl, Trr: R12 (row-major) and t12
     const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const orbfe_keypoint* keys1 = keys1All + (size_t)f * P.cap;
     const uint8_t* desc1 = desc1All + (size_t)f * P.cap * 32;
@@ -351,6 +358,8 @@ __global__ void __launch_bounds__(SB_THREADS) search_triangulation_kernel(
     if (tid < 32) hist[tid] = 0;
     if (tid < 9) sF[tid] = F12All ? F12All[(size_t)f * 9 + tid] : 0.f;
     if (tid < 2) sEp[tid] = epAll ? epAll[(size_t)f * 2 + tid] : 0.f;
+    if (tid < 48) sT[tid / 12][tid % 12] = (P.kb8 && T12All) ? T12All[(size_t)f * 48 + tid] : 0.f;
+    const int nleft1 = (P.kb8 && nleft1Arr) ? nleft1Arr[f] : 0x7fffffff, nleft2 = (P.kb8 && nleft2Arr) ? nleft2Arr[f] : 0x7fffffff;
     if (tid == 0) sCount = 0;
     __syncthreads();
 
@@ -387,11 +396,19 @@ __global__ void __launch_bounds__(SB_THREADS) search_triangulation_kernel(
                 const orbfe_keypoint kp2 = keys2[r2];
                 const int o2 = min(max(kp2.octave, 0), ORBFE_MAX_LEVELS - 1);
                 const bool bStereo2 = stereo2 && stereo2[r2];
-                if (!bStereo1 && !bStereo2) {
+                if (!P.kb8 && !bStereo1 && !bStereo2) {    // && !pKF1->mpCamera2
                     const float distex = sEp[0] - kp2.x, distey = sEp[1] - kp2.y;
                     if (distex * distex + distey * distey < 100.0f * P.scale[o2]) continue;
                 }
-                if (!P.coarse) {
+                if (!P.coarse && P.kb8) {
+                    const bool right1 = r1 >= nleft1, right2 = r2 >= nleft2;
+                    const float* T = sT[(right1 ? 2 : 0) + (right2 ? 1 : 0)];
+                    const int o1 = min(max(kp1.octave, 0), ORBFE_MAX_LEVELS - 1);
+                    float p3D[3];
+                    const float z = kb_triangulate(right1 ? P.camR : P.camL, right2 ? P.camR : P.camL, T, T + 9, P.precision, kp1.x,
+                                                   kp1.y, kp2.x, kp2.y, P.sigma2[o1], P.sigma2[o2], p3D);
+                    if (!(z > 0.0001f)) continue;
+                } else if (!P.coarse) {
                     if (den == 0) continue;
                     const float num = a * kp2.x + b * kp2.y + c;
                     const float dsqr = num * num / den;
@@ -478,9 +495,16 @@ int launch_search_triangulation(const orbfe_keypoint* keys1, const uint8_t* desc
                                 const orbfe_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
                                 const int* ids2, const int* start2, const int* idx2, const int* nodes2, const float* F12,
                                 const float* ep, const float* scale, const float* sigma2, int nlevels, int cap, int nodeCap,
-                                int npairs, int coarse, int checkOrientation, int* matches, int* nMatches, cudaStream_t st) {
+                                int npairs, int coarse, int checkOrientation, int* matches, int* nMatches, cudaStream_t st,
+                                const float* kb8Cams, const float* T12, const int* nleft1, const int* nleft2) {
     if (npairs <= 0) return 0;
     TriParams P;
+    P.kb8 = kb8Cams ? 1 : 0;    // kb8Cams: mpCamera parameters (8), mpCamera2 parameters (8), precision
+    for (int i = 0; i < 8; i++) {
+        P.camL[i] = kb8Cams ? kb8Cams[i] : 0.f;
+        P.camR[i] = kb8Cams ? kb8Cams[8 + i] : 0.f;
+    }
+    P.precision = kb8Cams ? kb8Cams[16] : 0.f;
     P.cap = cap;
     P.nodeCap = nodeCap;
     P.coarse = coarse;
@@ -494,7 +518,7 @@ int launch_search_triangulation(const orbfe_keypoint* keys1, const uint8_t* desc
     smem_opt_in(optIn, search_triangulation_kernel, smem);
     search_triangulation_kernel<<<npairs, SB_THREADS, smem, st>>>(P, keys1, desc1, free1, stereo1, ids1, start1, idx1, nodes1, keys2,
                                                                  desc2, free2, stereo2, ids2, start2, idx2, nodes2, F12, ep,
-                                                                 matches, nMatches);
+                                                                 T12, nleft1, nleft2, matches, nMatches);
     return 1;
 }
 

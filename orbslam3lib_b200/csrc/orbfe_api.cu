@@ -45,7 +45,8 @@ int launch_search_triangulation(const orbfe_keypoint* keys1, const uint8_t* desc
                                 const orbfe_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
                                 const int* ids2, const int* start2, const int* idx2, const int* nodes2, const float* F12,
                                 const float* ep, const float* scale, const float* sigma2, int nlevels, int cap, int nodeCap,
-                                int npairs, int coarse, int checkOrientation, int* matches, int* nMatches, cudaStream_t st);
+                                int npairs, int coarse, int checkOrientation, int* matches, int* nMatches, cudaStream_t st,
+                                const float* kb8Cams, const float* T12, const int* nleft1, const int* nleft2);
 size_t distinctive_smem_bytes(int maxN);
 int launch_distinctive(const uint8_t* desc, const int* offsets, int npoints, int maxN, int* bestIdx, int* bestMedian,
                        uint8_t* outDesc, cudaStream_t st);
@@ -1159,7 +1160,7 @@ struct orbfe_matcher {
     std::mutex mu;
     std::string err;
     DevBuf dQ, dT, dIdx, dDist, dNq, dNt;
-    DevBuf dS[24];    // staging of the orbfe_search_* calls
+    DevBuf dS[24];    // staging of the orbfe_search_* calls (up to 21 inputs; 9 .. 12 double as host-output staging)
     float lastMs = 0;
     int lastLaunches = 0;
     void* aux = nullptr;               // state of the sharded matcher (orbfe_sharded.cu), freed by auxFree at destroy
@@ -1617,22 +1618,22 @@ int orbfe_search_by_bow_kf_batch(orbfe_matcher* m, const uint8_t* desc1, const f
     return ORBFE_OK;
 }
 
-int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1,
-                                         const uint8_t* stereo1, const int32_t* node_ids1, const int32_t* node_start1,
-                                         const int32_t* idx1, const int32_t* nnodes1, const orbfe_keypoint* keys2,
-                                         const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
-                                         const int32_t* node_ids2, const int32_t* node_start2, const int32_t* idx2,
-                                         const int32_t* nnodes2, int cap, int node_cap, int npairs, const float* f12,
-                                         const float* epipole, const float* scale_factors, const float* level_sigma2,
-                                         int nlevels, int coarse, int check_orientation, int32_t* matches12, int32_t* nmatches,
-                                         unsigned flags) {
+static int search_tri_common(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1,
+                             const uint8_t* stereo1, const int32_t* node_ids1, const int32_t* node_start1, const int32_t* idx1,
+                             const int32_t* nnodes1, const orbfe_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2,
+                             const uint8_t* stereo2, const int32_t* node_ids2, const int32_t* node_start2, const int32_t* idx2,
+                             const int32_t* nnodes2, int cap, int node_cap, int npairs, const float* f12, const float* epipole,
+                             const float* scale_factors, const float* level_sigma2, int nlevels, int coarse,
+                             int check_orientation, int32_t* matches12, int32_t* nmatches, unsigned flags,
+                             const orbfe_fisheye_rig* rig, const float* t12, const int32_t* nleft1, const int32_t* nleft2) {
+
     if (!m) return ORBFE_ERR_ARG;
     std::lock_guard<std::mutex> lk(m->mu);
     if (npairs < 0 || cap < 0 || node_cap < 0 || nlevels < 1 || nlevels > ORBFE_MAX_LEVELS)
         return set_merr(m, ORBFE_ERR_ARG, "bad arguments");
     if (npairs == 0) return ORBFE_OK;
-    if (!nnodes1 || !nnodes2 || !node_start1 || !node_start2 || !scale_factors || !level_sigma2 || !epipole ||
-        (!coarse && !f12) || (node_cap > 0 && (!node_ids1 || !node_ids2)) ||
+    if (!nnodes1 || !nnodes2 || !node_start1 || !node_start2 || !scale_factors || !level_sigma2 || (!rig && !epipole) ||
+        (!rig && !coarse && !f12) || (rig && (!t12 || !nleft1 || !nleft2)) || (node_cap > 0 && (!node_ids1 || !node_ids2)) ||
         (cap > 0 && (!keys1 || !desc1 || !free1 || !idx1 || !keys2 || !desc2 || !free2 || !idx2 || !matches12)))
         return set_merr(m, ORBFE_ERR_ARG, "null pointer");
     if (cap > 65535 || search_bow_smem_bytes(cap) > 200 * 1024) return set_merr(m, ORBFE_ERR_ARG, "feature capacity %d too large", cap);
@@ -1640,15 +1641,25 @@ int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint*
     const bool inDev = flags & ORBFE_IN_DEVICE, outDev = flags & ORBFE_OUT_DEVICE;
     cudaStream_t st = m->stream;
     const size_t F = (size_t)npairs;
-    const void* dIn[18] = {keys1, desc1, free1, stereo1, node_ids1, node_start1, idx1, nnodes1,
-                           keys2, desc2, free2, stereo2, node_ids2, node_start2, idx2, nnodes2, f12, epipole};
+    const void* dIn[21] = {keys1, desc1, free1, stereo1, node_ids1, node_start1, idx1, nnodes1,
+                           keys2, desc2, free2, stereo2, node_ids2, node_start2, idx2, nnodes2, f12, epipole,
+                           rig ? t12 : nullptr, rig ? nleft1 : nullptr, rig ? nleft2 : nullptr};
     const size_t kb = F * cap * sizeof(orbfe_keypoint);
-    const size_t inBytes[18] = {kb, F * cap * 32, F * cap, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4,
+    const size_t inBytes[21] = {kb, F * cap * 32, F * cap, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4,
                                 kb, F * cap * 32, F * cap, F * cap, F * node_cap * 4, F * (node_cap + 1) * 4, F * cap * 4, F * 4,
-                                F * 36, F * 8};
+                                F * 36, F * 8, F * 48 * 4, F * 4, F * 4};
     if (!inDev) {
-        const int rc = stage_matcher_inputs(m, dIn, inBytes, 18, st);
+        const int rc = stage_matcher_inputs(m, dIn, inBytes, 21, st);
         if (rc != ORBFE_OK) return rc;
+    }
+    float kb8Cams[17];
+    if (rig) {
+        for (int i = 0; i < 8; i++) {
+            if (i < 2 && (rig->cam1[i] == 0.f || rig->cam2[i] == 0.f)) return set_merr(m, ORBFE_ERR_ARG, "zero focal length");
+            kb8Cams[i] = rig->cam1[i];
+            kb8Cams[8 + i] = rig->cam2[i];
+        }
+        kb8Cams[16] = rig->precision;
     }
     int32_t *dM = matches12, *dCount = nmatches;
     if (!outDev) {
@@ -1663,7 +1674,8 @@ int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint*
         (const int*)dIn[5], (const int*)dIn[6], (const int*)dIn[7], (const orbfe_keypoint*)dIn[8], (const uint8_t*)dIn[9],
         (const uint8_t*)dIn[10], (const uint8_t*)dIn[11], (const int*)dIn[12], (const int*)dIn[13], (const int*)dIn[14],
         (const int*)dIn[15], (const float*)dIn[16], (const float*)dIn[17], scale_factors, level_sigma2, nlevels, cap, node_cap,
-        npairs, coarse ? 1 : 0, check_orientation, dM, dCount, st);
+        npairs, coarse ? 1 : 0, check_orientation, dM, dCount, st, rig ? kb8Cams : nullptr, (const float*)dIn[18],
+        (const int*)dIn[19], (const int*)dIn[20]);
     cudaEventRecord(m->ev[1], st);
     ORBFE_MCUDA(m, cudaGetLastError());
     g_launches += launches;
@@ -1722,6 +1734,36 @@ int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const i
     ORBFE_MCUDA(m, cudaStreamSynchronize(st));
     cudaEventElapsedTime(&m->lastMs, m->ev[0], m->ev[1]);
     return ORBFE_OK;
+}
+
+int orbfe_search_for_triangulation_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1, const uint8_t* free1,
+                                         const uint8_t* stereo1, const int32_t* node_ids1, const int32_t* node_start1,
+                                         const int32_t* idx1, const int32_t* nnodes1, const orbfe_keypoint* keys2,
+                                         const uint8_t* desc2, const uint8_t* free2, const uint8_t* stereo2,
+                                         const int32_t* node_ids2, const int32_t* node_start2, const int32_t* idx2,
+                                         const int32_t* nnodes2, int cap, int node_cap, int npairs, const float* f12,
+                                         const float* epipole, const float* scale_factors, const float* level_sigma2,
+                                         int nlevels, int coarse, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                         unsigned flags) {
+    return search_tri_common(m, keys1, desc1, free1, stereo1, node_ids1, node_start1, idx1, nnodes1, keys2, desc2, free2, stereo2,
+                             node_ids2, node_start2, idx2, nnodes2, cap, node_cap, npairs, f12, epipole, scale_factors,
+                             level_sigma2, nlevels, coarse, check_orientation, matches12, nmatches, flags, nullptr, nullptr,
+                             nullptr, nullptr);
+}
+
+int orbfe_search_for_triangulation_kb8_batch(orbfe_matcher* m, const orbfe_keypoint* keys1, const uint8_t* desc1,
+                                             const uint8_t* free1, const int32_t* nleft1, const int32_t* node_ids1,
+                                             const int32_t* node_start1, const int32_t* idx1, const int32_t* nnodes1,
+                                             const orbfe_keypoint* keys2, const uint8_t* desc2, const uint8_t* free2,
+                                             const int32_t* nleft2, const int32_t* node_ids2, const int32_t* node_start2,
+                                             const int32_t* idx2, const int32_t* nnodes2, int cap, int node_cap, int npairs,
+                                             const orbfe_fisheye_rig* rig, const float* t12, const float* level_sigma2, int nlevels,
+                                             int coarse, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                             unsigned flags) {
+    if (!rig) return m ? set_merr(m, ORBFE_ERR_ARG, "null rig") : ORBFE_ERR_ARG;
+    return search_tri_common(m, keys1, desc1, free1, nullptr, node_ids1, node_start1, idx1, nnodes1, keys2, desc2, free2, nullptr,
+                             node_ids2, node_start2, idx2, nnodes2, cap, node_cap, npairs, nullptr, nullptr, level_sigma2,
+                             level_sigma2, nlevels, coarse, check_orientation, matches12, nmatches, flags, rig, t12, nleft1, nleft2);
 }
 
 // shared body of the two frame-to-frame searches (k_search_stereo.cu: search_frame_kernel)

@@ -409,6 +409,34 @@ class ORBmatcher:
                                                                  ptr(bm), ptr(od), int(flags)))
         return bi[:npts], bm[:npts], od[:npts]
 
+    def SearchForTriangulationKB8(self, keys1, desc1, free1, nleft1, fv1, keys2, desc2, free2, nleft2, fv2, rig, t12,
+                                  level_sigma2, bCoarse=False):
+        """ORBmatcher::SearchForTriangulation for key frames of a two-camera (KannalaBrandt8) rig (ORBmatcher.cc:908-1153 with
+        :1014-1043): keysN / descN = left then right features, nleftN = NLeft, rig.cam1 / cam2 = mpCamera / mpCamera2, t12 =
+        (4, 12): R12 | t12 of Tll, Tlr, Trl, Trr.  -> (nmatches, vMatchedPairs int32 (k, 2), vMatches12 int32 (n1,))"""
+        from .scenes import FISHEYE_RIG_DTYPE
+        k1, k2 = np.ascontiguousarray(keys1, KP_DTYPE), np.ascontiguousarray(keys2, KP_DTYPE)
+        n1 = len(k1)
+        cap = max(n1, len(k2), 1)
+        ncap = max(len(fv1[0]), len(fv2[0]), 1)
+        pad = self._pad
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        rg = np.ascontiguousarray(rig, FISHEYE_RIG_DTYPE)
+        T = np.ascontiguousarray(t12, np.float32).reshape(1, 48)
+        sg = np.ascontiguousarray(level_sigma2, np.float32)
+        m, nm = np.full(cap, -1, np.int32), np.zeros(1, np.int32)
+        self._bf._check(_lib.lib().orbfe_search_for_triangulation_kb8_batch(
+            self._bf._h, ptr(pad(k1, cap, KP_DTYPE)), ptr(pad(d1, cap, np.uint8)), ptr(pad(free1, cap, np.uint8)),
+            ptr(np.array([nleft1], np.int32)), ptr(pad(fv1[0], ncap, np.int32)), ptr(pad(fv1[1], ncap + 1, np.int32)),
+            ptr(pad(fv1[2], cap, np.int32)), ptr(np.array([len(fv1[0])], np.int32)), ptr(pad(k2, cap, KP_DTYPE)),
+            ptr(pad(d2, cap, np.uint8)), ptr(pad(free2, cap, np.uint8)), ptr(np.array([nleft2], np.int32)),
+            ptr(pad(fv2[0], ncap, np.int32)), ptr(pad(fv2[1], ncap + 1, np.int32)), ptr(pad(fv2[2], cap, np.int32)),
+            ptr(np.array([len(fv2[0])], np.int32)), cap, ncap, 1, ptr(rg), ptr(T), ptr(sg), sg.shape[0], int(bool(bCoarse)),
+            int(self.mbCheckOrientation), ptr(m), ptr(nm), 0))
+        i1 = np.nonzero(m[:n1] >= 0)[0]
+        return int(nm[0]), np.stack([i1, m[i1]], axis=1).astype(np.int32), m[:n1]
+
     def SearchForInitialization(self, keys1_un, desc1, keys2_un, desc2, bounds, vbPrevMatched, windowSize=10):
         """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:649-764) on
         monocular frames given as arrays; bounds = F2's image bounds.  vbPrevMatched: (n1, 2) float32.

@@ -374,6 +374,70 @@ def fisheye_stereo_case(kps_left, rig, seed, mono_left=0, mono_right=0, n_right=
     return kr, idx, dist
 
 
+def kb8_keyframe_pair(rig, w, h, seed, npts=900, nlevels=8):
+    """Two key frames of a two-camera KannalaBrandt8 rig that see the same 3-D points: the data of
+    ORBmatcher::SearchForTriangulation on stereo-camera key frames.  Key frame 2 is key frame 1 moved by ~0.2 m and a small
+    rotation.  Every point gets a base descriptor; each of its observations (left / right camera of either key frame, each
+    present with probability ~0.7) is the projection + up to 0.5 px of noise with a few flipped descriptor bits; a tenth of
+    the observations of key frame 2 are moved by 6 - 40 px (same descriptor, wrong geometry: the constraint must reject them).
+    -> dict(keys1, desc1, nleft1, keys2, desc2, nleft2, t12 (4, 12): R12 | t12 of Tll, Tlr, Trl, Trr)"""
+    from ._lib import KP_DTYPE
+    u = rand_u32(16 * npts, seed ^ 0x7B8).reshape(16, npts).astype(np.float64) / 2.0**32
+    c1, c2 = rig["cam1"].astype(np.float64), rig["cam2"].astype(np.float64)
+    Rlr, tlr = rig["Rlr"].astype(np.float64).reshape(3, 3), rig["tlr"].astype(np.float64)
+    Rrl, trl = Rlr.T, -Rlr.T @ tlr
+    # points in the left camera of key frame 1
+    px, py = 30 + u[0] * (w - 60), 30 + u[1] * (h - 60)
+    z = 0.5 * (16.0 ** u[2])
+    X1 = _kb_unproject64(c1, px, py) * z[:, None]
+    ax = np.array([0.01, -0.02, 0.015])    # key frame 2's left camera: x_l1 = M_R x_l2 + M_t
+    th = float(np.linalg.norm(ax))
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]]) / th
+    MR = np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * (K @ K)
+    Mt = np.array([0.18, 0.03, 0.06])
+    comp = lambda Ra, ta, Rb, tb: (Ra @ Rb, Ra @ tb + ta)    # noqa: E731  (a o b)(x) = Ra (Rb x + tb) + ta
+    Tll = (MR, Mt)
+    Tlr = comp(MR, Mt, Rlr, tlr)
+    Trl = comp(Rrl, trl, MR, Mt)
+    Trr = comp(Rrl, trl, *Tlr)
+    t12 = np.stack([np.concatenate([R.reshape(-1), t]) for R, t in (Tll, Tlr, Trl, Trr)]).astype(np.float32)
+    Xl2 = (X1 - Mt) @ MR            # MR^T (X1 - Mt)
+    cams = {"l1": (c1, X1), "r1": (c2, X1 @ Rrl.T + trl), "l2": (c1, Xl2), "r2": (c2, Xl2 @ Rrl.T + trl)}
+    base = rand_u32(npts * 8, seed + 1).reshape(npts, 8).view(np.uint8).reshape(npts, 32)
+    octave = (rand_u32(npts, seed + 2) % np.uint32(4)).astype(np.int32)
+    out = {"t12": t12}
+    for kf, sides, col in (("1", ("l1", "r1"), 3), ("2", ("l2", "r2"), 8)):
+        ks, ds = [], []
+        for si, side in enumerate(sides):
+            cam, X = cams[side]
+            uv = _kb_project64(cam, X)
+            noise = (np.stack([u[col + 2 * si], u[col + 2 * si + 1]], 1) - 0.5)
+            if kf == "2":
+                bad = u[12 + si] < 0.1
+                noise = np.where(bad[:, None], np.sign(noise) * (6 + 68 * np.abs(noise)), noise)
+            uv = uv + noise
+            vis = (u[14 + si] < 0.7) & (X[:, 2] > 0.05) & (uv[:, 0] > 5) & (uv[:, 0] < w - 5) & (uv[:, 1] > 5) & (uv[:, 1] < h - 5)
+            ids = np.nonzero(vis)[0]
+            k = np.zeros(len(ids), KP_DTYPE)
+            k["x"], k["y"] = uv[ids, 0].astype(np.float32), uv[ids, 1].astype(np.float32)
+            k["octave"] = octave[ids]
+            k["size"] = 31.0
+            k["angle"] = (rand_u32(npts, seed + 3)[ids] % np.uint32(360)).astype(np.float32) + (7.0 if kf == "2" else 0.0)
+            k["class_id"] = -1
+            d = base[ids].copy()
+            fl = rand_u32(len(ids) * 6, seed + 10 * int(kf) + si).reshape(len(ids), 6)
+            nfl = fl[:, 0] % np.uint32(6)
+            for j in range(5):
+                rows = np.nonzero(nfl > j)[0]
+                q = (fl[rows, j + 1] % np.uint32(256)).astype(np.int64)
+                d[rows, q >> 3] ^= (1 << (q & 7)).astype(np.uint8)
+            ks.append(k)
+            ds.append(d)
+        out["keys" + kf], out["desc" + kf], out["nleft" + kf] = np.concatenate(ks), np.concatenate(ds), len(ks[0])
+    out["sigma2"] = ((np.float32(1.2) ** np.arange(nlevels, dtype=np.float32)) ** 2).astype(np.float32)
+    return out
+
+
 SCENES = {"noise": noise, "checker": checker, "texture": texture, "flat_blobs": flat_blobs}
 
 

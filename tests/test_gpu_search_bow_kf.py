@@ -154,3 +154,46 @@ def test_bow_kf_matchers_ragged_device_batch(oracle):
                                                    1 - c["has2"], c["st2"], c["fv2"], c["F"], c["ep"], scale, sigma2, False, True)
         np.testing.assert_array_equal(m2[f, :n1], rm2)
         assert cnt2[f] == rn2 and (m2[f, n1:] == -1).all()
+
+
+# ---- two-camera (KannalaBrandt8) key frames: orbfe_search_for_triangulation_kb8_batch -------------------------------------------
+# Tolerance: the triangulation is floating point (tanf / atan2f differ by an ulp or two between CUDA and glibc):
+# a feature's match may differ from the oracle's only where the oracle reports that one of its gates was decided within 1e-5
+# (`slack`); everywhere else the indices are identical.
+from test_search_rule import kb8_tri_case    # noqa: E402
+
+
+@pytest.mark.parametrize("seed,coarse,ori", [(9900, False, True), (9901, False, False), (9902, True, True), (9903, False, True)])
+def test_search_for_triangulation_kb8_matches_oracle(oracle, seed, coarse, ori):
+    rig, c, fv1, fv2, free1, free2 = kb8_tri_case(seed, npts=1200)
+    rm, rn, slack = oracle.search_for_triangulation_kb8(c["keys1"], c["desc1"], free1, c["nleft1"], fv1, c["keys2"], c["desc2"],
+                                                        free2, c["nleft2"], fv2, rig, c["t12"], c["sigma2"], coarse, False)
+    nm, pairs, m = ORBmatcher(0.6, False).SearchForTriangulationKB8(c["keys1"], c["desc1"], free1, c["nleft1"], fv1, c["keys2"],
+                                                                    c["desc2"], free2, c["nleft2"], fv2, rig, c["t12"],
+                                                                    c["sigma2"], bCoarse=coarse)
+    differ = m != rm
+    assert not (differ & (slack >= 1e-5)).any(), "match differs away from a gate: features %s" % np.nonzero(differ & (slack >= 1e-5))[0][:10]
+    assert differ.sum() <= 3 and abs(nm - rn) <= 3 and nm > 400
+    if coarse:
+        assert not differ.any()
+    if ori and not differ.any():    # the rotation histogram on top (exact when the matches are)
+        rm2, rn2, _ = oracle.search_for_triangulation_kb8(c["keys1"], c["desc1"], free1, c["nleft1"], fv1, c["keys2"], c["desc2"],
+                                                          free2, c["nleft2"], fv2, rig, c["t12"], c["sigma2"], coarse, True)
+        nm2, _, m2 = ORBmatcher(0.6, True).SearchForTriangulationKB8(c["keys1"], c["desc1"], free1, c["nleft1"], fv1, c["keys2"],
+                                                                     c["desc2"], free2, c["nleft2"], fv2, rig, c["t12"],
+                                                                     c["sigma2"], bCoarse=coarse)
+        np.testing.assert_array_equal(m2, rm2)
+        assert nm2 == rn2 and nm2 <= nm
+    got = m >= 0
+    r1, r2 = np.nonzero(got)[0] >= c["nleft1"], m[got] >= c["nleft2"]
+    assert all(((r1 == a) & (r2 == b)).sum() > 20 for a in (False, True) for b in (False, True))
+
+
+def test_search_for_triangulation_kb8_errors():
+    from orbslam3lib_b200 import _lib as L
+    rig, c, fv1, fv2, free1, free2 = kb8_tri_case(9910, npts=200)
+    bad = rig.copy()
+    bad["cam1"][0] = 0
+    with pytest.raises(L.OrbfeError):
+        ORBmatcher(0.6, False).SearchForTriangulationKB8(c["keys1"], c["desc1"], free1, c["nleft1"], fv1, c["keys2"], c["desc2"],
+                                                         free2, c["nleft2"], fv2, bad, c["t12"], c["sigma2"])

@@ -1108,3 +1108,85 @@ def test_oracle_distinctive_descriptors_vs_python(oracle):
     assert (bi[n == 0] == -1).all() and (bi[n == 1] == 0).all() and (bm[n == 1] == 0).all()
     assert (bi[n == 2] == 0).all() and (bm[n == 2] == 0).all()    # median of (0, d) is element int(0.5) = 0: the first row wins
     assert len(np.unique(bi[n > 10])) > 5
+
+
+# ---- SearchForTriangulation on two-camera (KannalaBrandt8) key frames: ORBmatcher.cc:908-1153 with :1014-1043
+def _py_search_tri_kb8(oracle, c, fv1, fv2, free1, free2, rig, coarse, check_ori):
+    """literal restatement of the loop with the camera / pose selection of :1015-1042; the constraint itself
+    (KannalaBrandt8::epipolarConstrain = TriangulateMatches > 0.0001) is the oracle's Eigen-pinned function."""
+    k1, d1, k2, d2 = c["keys1"], c["desc1"], c["keys2"], c["desc2"]
+    bits1, bits2 = np.unpackbits(d1, axis=1), np.unpackbits(d2, axis=1)
+    m12 = np.full(len(k1), -1, np.int64)
+    rot_hist = [[] for _ in range(30)]
+    nm = 0
+    for n1, n2 in _merge_nodes(fv1, fv2):
+        for idx1 in n1:
+            if not free1[idx1]:
+                continue
+            right1 = idx1 >= c["nleft1"]
+            best_dist, best_idx2 = 50, -1
+            for idx2 in n2:
+                if not free2[idx2]:
+                    continue
+                d = int((bits1[idx1] != bits2[idx2]).sum())
+                if d > 50 or d > best_dist:
+                    continue
+                right2 = idx2 >= c["nleft2"]
+                ok = coarse
+                if not ok:
+                    if right1 and right2:
+                        T, cam_a, cam_b = c["t12"][3], rig["cam2"], rig["cam2"]    # Trr, mpCamera2, mpCamera2
+                    elif right1 and not right2:
+                        T, cam_a, cam_b = c["t12"][2], rig["cam2"], rig["cam1"]    # Trl
+                    elif not right1 and right2:
+                        T, cam_a, cam_b = c["t12"][1], rig["cam1"], rig["cam2"]    # Tlr
+                    else:
+                        T, cam_a, cam_b = c["t12"][0], rig["cam1"], rig["cam1"]    # Tll
+                    g = rig.copy()
+                    g["cam1"], g["cam2"], g["Rlr"], g["tlr"] = cam_a, cam_b, T[:9], T[9:]
+                    z = oracle.kb_triangulate_matches(g, k1["x"][idx1], k1["y"][idx1], k2["x"][idx2], k2["y"][idx2],
+                                                      c["sigma2"][k1["octave"][idx1]], c["sigma2"][k2["octave"][idx2]])
+                    ok = z > np.float32(0.0001)
+                if ok:
+                    best_idx2, best_dist = idx2, d
+            if best_idx2 >= 0:
+                m12[idx1] = best_idx2
+                nm += 1
+                if check_ori:
+                    rot_hist[_py_bin(k1["angle"][idx1], k2["angle"][best_idx2])].append(idx1)
+    if check_ori:
+        keep = _py_three_maxima(rot_hist)
+        for i in range(30):
+            if i not in keep:
+                for idx1 in rot_hist[i]:
+                    m12[idx1] = -1
+                    nm -= 1
+    return m12, nm
+
+
+def kb8_tri_case(seed, w=640, h=400, npts=900):
+    rig = scenes.fisheye_rig(w, h, 0.11, seed)
+    c = scenes.kb8_keyframe_pair(rig, w, h, seed, npts)
+    fv1, fv2 = scenes.feature_vector(c["desc1"]), scenes.feature_vector(c["desc2"])
+    free1 = (scenes.rand_u32(len(c["keys1"]), seed + 20) % 6 != 0).astype(np.uint8)
+    free2 = (scenes.rand_u32(len(c["keys2"]), seed + 21) % 6 != 0).astype(np.uint8)
+    return rig, c, fv1, fv2, free1, free2
+
+
+def test_oracle_search_for_triangulation_kb8_vs_python(oracle):
+    for seed, coarse, ori in ((7001, False, True), (7002, False, False), (7003, True, True)):
+        rig, c, fv1, fv2, free1, free2 = kb8_tri_case(seed, npts=500)
+        m, nm, slack = oracle.search_for_triangulation_kb8(c["keys1"], c["desc1"], free1, c["nleft1"], fv1, c["keys2"], c["desc2"],
+                                                           free2, c["nleft2"], fv2, rig, c["t12"], c["sigma2"], coarse, ori)
+        ref, rnm = _py_search_tri_kb8(oracle, c, fv1, fv2, free1, free2, rig, coarse, ori)
+        np.testing.assert_array_equal(m, ref)
+        assert nm == rnm and nm > 150
+        got = m >= 0
+        assert free1[got].all() and free2[m[got]].all()
+        # all four camera combinations occur among the matches
+        r1, r2 = np.nonzero(got)[0] >= c["nleft1"], m[got] >= c["nleft2"]
+        assert all(((r1 == a) & (r2 == b)).sum() > 5 for a in (False, True) for b in (False, True))
+    # the constraint removes the displaced observations: fewer matches than the coarse form
+    rig, c, fv1, fv2, free1, free2 = kb8_tri_case(7004, npts=500)
+    a = (c["keys1"], c["desc1"], free1, c["nleft1"], fv1, c["keys2"], c["desc2"], free2, c["nleft2"], fv2, rig, c["t12"], c["sigma2"])
+    assert oracle.search_for_triangulation_kb8(*a, False, False)[1] < oracle.search_for_triangulation_kb8(*a, True, False)[1]
