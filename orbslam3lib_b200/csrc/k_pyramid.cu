@@ -224,39 +224,37 @@ __global__ void __launch_bounds__(256) resize_tile_kernel(const uint8_t* __restr
 // lanes of a warp are on the same destination row, so everything that depends on the row only -- the byte offsets of
 // its two source rows in the window and the two vertical weights -- is ONE 16-byte record in shared memory, built once
 // per CTA (no reflect / tap decode / row-offset multiplies in the loop), and the final (t + 2) >> 2 runs on two packed
-// 16-bit pairs.  Per 4 pixels and row: 1 LDS.128, 8 IADD3 + 8 LDS.U16 + 8 IDP.2A + 8 shifts (horizontal, both source
+// 16-bit pairs.  Everything that depends on the geometry only comes from host tables in padded plane coordinates
+// (ResizeDims: the tile's staged window, the reflected taps per plane column / row, a reciprocal for the staging index).  Per 4 pixels and row: 1 LDS.128, 8 IADD3 + 8 LDS.U16 + 8 IDP.2A + 8 shifts (horizontal, both source
 // rows), 8 IMAD + ~8 ALU (vertical), 5 ALU (rounding, PRMT), one 32-bit store: 64 SASS instructions against 92.
 // Bit-exact with cv::resize(INTER_LINEAR) on CV_8UC1: same fixed-point steps in the same order.
 __global__ void __launch_bounds__(256) resize_rows_kernel(const uint8_t* __restrict__ srcPlane, int spitch,
                                                           uint8_t* __restrict__ dstPlane, int dpitch,
                                                           unsigned long long slabBytes, int dw, int dh,
-                                                          const ResizeTap* __restrict__ xtab,
-                                                          const ResizeTap* __restrict__ ytab, int SP, int SH, int rpt) {
+                                                          const ResizeTap* __restrict__ xpad,
+                                                          const ResizeTap* __restrict__ ypad,
+                                                          const ResizeTap* __restrict__ tileX,
+                                                          const ResizeTap* __restrict__ tileY, int SP, int SH, int rpt) {
     extern __shared__ __align__(16) uint8_t sm[];
     const int tid = threadIdx.x, tx = tid & 63, ty = tid >> 6;
     const int TH = 4 * rpt;
     int4* sRow = reinterpret_cast<int4*>(sm + 2 * SP * SH);    // TH records
     const int cb = RS_C0 + blockIdx.x * RS_TW;    // plane column of the tile's first byte
     const int rb = blockIdx.y * TH;               // padded row of the tile's first row
-    const int xa = max(cb - kXOff, -kEdge), xb = min(cb + RS_TW - 1 - kXOff, dw + kEdge - 1);
-    const int ya = rb - kEdge, yb = min(rb + TH - 1, dh + 2 * kEdge - 1) - kEdge;
-    if (xa > xb || ya > yb) return;
-    int xlo, xhi, ylo, yhi;
-    reflect_range(xa, xb, dw, xlo, xhi);
-    reflect_range(ya, yb, dh, ylo, yhi);
-    const int clo = xtab[xlo].s, chi = xtab[xhi].s + 1;    // source columns [clo, chi] (chi may be the first frame column)
-    const int rlo = ytab[ylo].s, rhi = ytab[yhi].s1;       // source rows [rlo, rhi]
-    const int colbase = (kXOff + clo) & ~15;
-    const int nvec = ((kXOff + chi + 1) - colbase + 15) >> 4;
-    const int nrows = rhi - rlo + 1;
+    // the tile's staged source window, from the host tables (resize_pad_tables): no reflection or range search here
+    const int2 tX = __ldg(reinterpret_cast<const int2*>(tileX + blockIdx.x));
+    const int tY = __ldg(reinterpret_cast<const int*>(tileY + blockIdx.y));
+    const int colbase = tX.x & 0xffff, nvec = tX.x >> 16;
+    const unsigned vecMagic = (unsigned)tX.y;    // 2^31 / nvec + 1: i / nvec == umulhi(2 i, vecMagic) for i < 2^31 / nvec
+    const int rlo = tY & 0xffff, nrows = tY >> 16;
     const int shift = SP * SH;    // sB[j] = sA[j + 1]
     for (int t = tid; t < TH; t += 256) {
         const int py = rb + t;
         int4 rec = make_int4(0, 0, 0, 0);
         if (py < dh + 2 * kEdge) {
-            const int2 yraw = __ldg(reinterpret_cast<const int2*>(ytab + reflect101(py - kEdge, dh)));
-            rec.x = ((int)(short)(yraw.x & 0xffff) - rlo) * SP;
-            rec.y = ((int)(short)(yraw.x >> 16) - rlo) * SP;
+            const int2 yraw = __ldg(reinterpret_cast<const int2*>(ypad + py));
+            rec.x = ((yraw.x & 0xffff) - rlo) * SP;
+            rec.y = ((int)((unsigned)yraw.x >> 16) - rlo) * SP;
             rec.z = yraw.y & 0xffff;
             rec.w = (int)((unsigned)yraw.y >> 16);
         }
@@ -264,13 +262,15 @@ __global__ void __launch_bounds__(256) resize_rows_kernel(const uint8_t* __restr
     }
     {
         const uint8_t* sp = srcPlane + (size_t)blockIdx.z * slabBytes + (size_t)(rlo + kEdge) * spitch + colbase;
+        const int lastVec = (spitch - colbase - 17) >> 4;    // vectors c <= lastVec have a byte behind them in the row
         for (int i = tid; i < nvec * nrows; i += 256) {
-            const int r = i / nvec, c = i - r * nvec;
-            const uint8_t* p = sp + (size_t)r * spitch + 16 * c;
+            const int r = (int)__umulhi(2u * (unsigned)i, vecMagic), c = i - r * nvec;
+            const uint8_t* p = sp + r * spitch + 16 * c;
             const uint4 v = *reinterpret_cast<const uint4*>(p);
-            const uint32_t nb = (colbase + 16 * c + 16 < spitch) ? p[16] : 0u;
-            *reinterpret_cast<uint4*>(sm + r * SP + 16 * c) = v;
-            *reinterpret_cast<uint4*>(sm + shift + r * SP + 16 * c) =
+            const uint32_t nb = c <= lastVec ? p[16] : 0u;
+            uint8_t* d = sm + r * SP + 16 * c;
+            *reinterpret_cast<uint4*>(d) = v;
+            *reinterpret_cast<uint4*>(d + shift) =
                 make_uint4(__funnelshift_r(v.x, v.y, 8), __funnelshift_r(v.y, v.z, 8), __funnelshift_r(v.z, v.w, 8),
                            __funnelshift_r(v.w, nb, 8));
         }
@@ -280,14 +280,12 @@ __global__ void __launch_bounds__(256) resize_rows_kernel(const uint8_t* __restr
     if (c >= kXOff + dw + kEdge) return;
     uint32_t wt[4];
     const uint8_t* ad[4];
+    {
+        const int4 q0 = __ldg(reinterpret_cast<const int4*>(xpad + c)), q1 = __ldg(reinterpret_cast<const int4*>(xpad + c + 2));
+        const int offs[4] = {q0.x & 0xffff, q0.z & 0xffff, q1.x & 0xffff, q1.z & 0xffff};
+        wt[0] = (uint32_t)q0.y; wt[1] = (uint32_t)q0.w; wt[2] = (uint32_t)q1.y; wt[3] = (uint32_t)q1.w;    // a0 | a1 << 16
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int x = c + k - kXOff;
-        const bool valid = x >= -kEdge && x < dw + kEdge;
-        const int2 raw = __ldg(reinterpret_cast<const int2*>(xtab + reflect101(valid ? x : 0, dw)));
-        const int off = kXOff + (int)(short)(raw.x & 0xffff) - colbase;
-        ad[k] = sm + (!valid ? 0 : ((off & 1) ? (shift + off - 1) : off));
-        wt[k] = valid ? (uint32_t)raw.y : 0u;    // a0 | a1 << 16
+        for (int k = 0; k < 4; k++) ad[k] = sm + ((offs[k] & 1) ? (shift + offs[k] - 1) : offs[k]);
     }
     const int r0 = ty * rpt, r1 = min(r0 + rpt, dh + 2 * kEdge - rb);
     uint8_t* dp = dstPlane + (size_t)blockIdx.z * slabBytes + (size_t)(rb + r0) * dpitch + c;
@@ -363,6 +361,54 @@ void resize_tile_dims(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int 
     *SH = shh;
 }
 
+// host: the tables resize_rows_kernel reads (ResizeDims::xpad / ypad / tileX / tileY), for `rpt` rows per thread.
+void resize_pad_counts(int dw, int dh, int rpt, int* nxpad, int* nypad, int* ntx, int* nty) {
+    *ntx = (kXOff + dw + kEdge - RS_C0 + RS_TW - 1) / RS_TW;
+    *nty = (dh + 2 * kEdge + 4 * rpt - 1) / (4 * rpt);
+    *nxpad = RS_C0 + *ntx * RS_TW;    // indexed by plane column; a multiple of 4 (four taps are loaded as two 16-byte words)
+    *nypad = dh + 2 * kEdge;
+}
+
+void resize_pad_tables(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int dh, int rpt, ResizeTap* xpad, ResizeTap* ypad,
+                       ResizeTap* tileX, ResizeTap* tileY) {
+    int nxpad, nypad, ntx, nty;
+    resize_pad_counts(dw, dh, rpt, &nxpad, &nypad, &ntx, &nty);
+    const int TH = 4 * rpt;
+    for (int i = 0; i < nxpad; i++) xpad[i] = ResizeTap{0, 0, 0, 0};    // columns outside the frame: weight 0, offset 0
+    for (int bx = 0; bx < ntx; bx++) {
+        const int cb = RS_C0 + bx * RS_TW;
+        const int xa = std::max(cb - kXOff, -kEdge), xb = std::min(cb + RS_TW - 1 - kXOff, dw + kEdge - 1);
+        int lo = 1 << 30, hi = -1;
+        for (int x = xa; x <= xb; x++) {
+            const int r = h_reflect101(x, dw);
+            lo = std::min(lo, r);
+            hi = std::max(hi, r);
+        }
+        const int clo = xtab[lo].s, chi = xtab[hi].s + 1;    // source columns [clo, chi] (chi may be the first frame column)
+        const int colbase = (kXOff + clo) & ~15;
+        const int nvec = ((kXOff + chi + 1) - colbase + 15) >> 4;
+        const unsigned magic = 0x80000000u / (unsigned)nvec + 1u;    // nvec = 1 included (2^32 / nvec + 1 would not fit)
+        tileX[bx] = ResizeTap{(short)colbase, (short)nvec, (short)(magic & 0xffffu), (short)(magic >> 16)};
+        for (int x = xa; x <= xb; x++) {
+            const ResizeTap& t = xtab[h_reflect101(x, dw)];
+            xpad[x + kXOff] = ResizeTap{(short)(kXOff + t.s - colbase), 0, t.a0, t.a1};
+        }
+    }
+    for (int by = 0; by < nty; by++) {
+        const int rb = by * TH;
+        const int ya = rb - kEdge, yb = std::min(rb + TH - 1, dh + 2 * kEdge - 1) - kEdge;
+        int lo = 1 << 30, hi = -1;
+        for (int y = ya; y <= yb; y++) {
+            const int r = h_reflect101(y, dh);
+            lo = std::min(lo, r);
+            hi = std::max(hi, r);
+        }
+        const int rlo = ytab[lo].s, rhi = ytab[hi].s1;
+        tileY[by] = ResizeTap{(short)rlo, (short)(rhi - rlo + 1), 0, 0};
+    }
+    for (int py = 0; py < nypad; py++) ypad[py] = ytab[h_reflect101(py - kEdge, dh)];
+}
+
 int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size_t imageStride, uint8_t* pyr,
                    const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims,
                    const ResizeDims* rows16, cudaStream_t st) {
@@ -397,7 +443,7 @@ int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size
                 smem_opt_in(optRows, resize_rows_kernel, (size_t)smem);
                 const dim3 grid((kXOff + L.w + kEdge - RS_C0 + RS_TW - 1) / RS_TW, (L.h + 2 * kEdge + 4 * d.rpt - 1) / (4 * d.rpt), n);
                 resize_rows_kernel<<<grid, 256, smem, st>>>(pyr + P.planeOff, P.pitch, pyr + L.planeOff, L.pitch, g.slabBytes,
-                                                            L.w, L.h, xtab[l], ytab[l], d.SP, d.SH, d.rpt);
+                                                            L.w, L.h, d.xpad, d.ypad, d.tileX, d.tileY, d.SP, d.SH, d.rpt);
                 launches++;
                 continue;
             }

@@ -389,6 +389,7 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
     // resize taps
     std::vector<ResizeTap> all;
     std::vector<size_t> xo(g.nlevels, 0), yo(g.nlevels, 0);
+    size_t padOff[2][ORBFE_MAX_LEVELS][4] = {};    // offsets of ResizeDims::xpad / ypad / tileX / tileY in `all`
     for (int l = 1; l < g.nlevels; l++) {
         std::vector<ResizeTap> tx, ty;
         build_taps(g.lv[l - 1].w, g.lv[l].w, true, tx);
@@ -406,6 +407,17 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
             }
             if (2 * d.SP * d.SH > 200 * 1024)
                 return set_err(ex, ORBFE_ERR_ARG, "scale factor too large for the resize tile (%d bytes of shared memory)", 2 * d.SP * d.SH);
+            // the kernel's tables in padded plane coordinates; xpad starts on a 32-byte boundary (two 16-byte loads per thread)
+            int nx, ny, ntx, nty;
+            resize_pad_counts(g.lv[l].w, g.lv[l].h, d.rpt, &nx, &ny, &ntx, &nty);
+            all.resize((all.size() + 3) & ~(size_t)3);
+            size_t* o = padOff[v][l];
+            o[0] = all.size();
+            o[1] = o[0] + nx;
+            o[2] = o[1] + ny;
+            o[3] = o[2] + ntx;
+            all.resize(o[3] + nty);
+            resize_pad_tables(tx.data(), ty.data(), g.lv[l].w, g.lv[l].h, d.rpt, &all[o[0]], &all[o[1]], &all[o[2]], &all[o[3]]);
         }
         xo[l] = all.size();
         all.insert(all.end(), tx.begin(), tx.end());
@@ -423,6 +435,14 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
     for (int l = 0; l < ORBFE_MAX_LEVELS; l++) {
         ex->xtab[l] = l > 0 && l < g.nlevels ? (const ResizeTap*)ex->dTaps.p + xo[l] : nullptr;
         ex->ytab[l] = l > 0 && l < g.nlevels ? (const ResizeTap*)ex->dTaps.p + yo[l] : nullptr;
+        for (int v = 0; v < 2 && l > 0 && l < g.nlevels; v++) {
+            ResizeDims& d = ex->rsDims[v][l];
+            const ResizeTap* base = (const ResizeTap*)ex->dTaps.p;
+            d.xpad = base + padOff[v][l][0];
+            d.ypad = base + padOff[v][l][1];
+            d.tileX = base + padOff[v][l][2];
+            d.tileY = base + padOff[v][l][3];
+        }
     }
     ex->geom = g;
     ex->nItems = nItems;

@@ -93,6 +93,12 @@ struct ResizeTap {
 struct ResizeDims {
     int SP, SH;    // pitch (multiple of 16) and rows of the staged source window
     int rpt;       // destination rows per thread (tile height = 4 * rpt)
+    // resize_rows_kernel: tables in padded plane coordinates, built once per extractor (resize_pad_tables), so that the
+    // kernel does no border reflection and no range search
+    const ResizeTap* xpad;     // per plane column: s = byte offset of the first tap in the tile's staged window, a0, a1
+    const ResizeTap* ypad;     // per padded plane row: the row's vertical tap (s, s1 absolute source rows)
+    const ResizeTap* tileX;    // per x tile: s = first staged plane column, s1 = 16-byte vectors per row, (a0, a1) = 2^31 / s1 + 1
+    const ResizeTap* tileY;    // per y tile: s = first staged source row, s1 = staged rows
 };
 
 // per-image results of the pack step
@@ -130,6 +136,9 @@ int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size
                    const ResizeTap* const* xtab, const ResizeTap* const* ytab, const ResizeDims* dims,
                    const ResizeDims* rows16, cudaStream_t st);
 void resize_tile_dims(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int dh, int rpt, int* SP, int* SH);
+void resize_pad_counts(int dw, int dh, int rpt, int* nxpad, int* nypad, int* ntx, int* nty);
+void resize_pad_tables(const ResizeTap* xtab, const ResizeTap* ytab, int dw, int dh, int rpt, ResizeTap* xpad, ResizeTap* ypad,
+                       ResizeTap* tileX, ResizeTap* tileY);
 int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap1, cudaStream_t st);
 int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
                     cudaStream_t st);
