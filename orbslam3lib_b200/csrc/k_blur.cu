@@ -36,6 +36,10 @@ __host__ __device__ inline void blur_strips(int w, int* nStrips, int* stripWords
     *stripWords = (words + ns - 1) / ns;
 }
 
+__device__ __forceinline__ void store_word_if(uint8_t* p, uint32_t v, int on) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q st.global.u32 [%0], %1;\n\t}" :: "l"(p), "r"(v), "r"(on) : "memory");
+}
+
 // grid (ceil(nTiles / BL_WARPS), n); block 32 * BL_WARPS; one warp per tile
 __global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_constant__ Geom g,
                                                                  const uint8_t* __restrict__ pyr,
@@ -58,14 +62,19 @@ __global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_co
     const int wi = wfirst - 1 + lane;                      // this lane's word (level x = 4 * wi)
     const int y0 = t.ty * BL_ROWS;
     const int pc = kXOff + 4 * wi;                         // plane column of the word
-    const bool inPlane = pc >= 0 && pc + 4 <= L.pitch;
+    const bool inPlane = pc >= 0 && pc + 4 <= L.pitch;    // false only for lanes right of every word an output reads
     const bool outLane = lane >= 1 && wi < wlast;
     const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff;
+    const ptrdiff_t pitch = L.pitch;
     // source row y - 3 of output row y is plane row y - 3 + kEdge
-    const uint8_t* src = pyr + planeBase + (size_t)(y0 - 3 + kEdge) * L.pitch + pc;
-    uint8_t* dst = blur + planeBase + (size_t)(y0 + kEdge) * L.pitch + pc;
-    const int planeRows = L.h + 2 * kEdge;
+    const uint8_t* src = pyr + planeBase + (y0 - 3 + kEdge) * pitch + (inPlane ? pc : 0);
+    uint8_t* dst = blur + planeBase + (y0 + kEdge) * pitch + pc;
+    asm volatile("" : "+l"(src), "+l"(dst));               // opaque: two base registers, every access = base + k * pitch
     const int rowsLeft = L.h - y0;                         // output rows available in this tile (> 0)
+    // The outputs of the tile read its source rows 0 .. rowsLeft + 5 (all inside the padded plane: the last one is plane
+    // row h + kEdge + 2).  Requests past that row are clamped onto it instead of predicated: one min per row, no
+    // compare / branch; the clamped rows only feed output rows >= rowsLeft, which are not stored.
+    const int lastRow = rowsLeft + 5;
 
     constexpr uint32_t K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24);    // lo: (18,34)  hi: (48,56)
     constexpr uint32_t K2 = 48u | (34u << 8) | (0u << 16) | (18u << 24);     // lo: (48,34)  hi: (0,18)
@@ -74,20 +83,13 @@ __global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_co
     uint32_t E[7], O[7];    // even / odd bytes of the last 7 source rows (16-bit lanes)
     uint32_t raw[BL_PF];    // loads in flight: row i + BL_PF is requested while row i is consumed
 #pragma unroll
-    for (int j = 0; j < BL_PF; j++) {
-        raw[j] = 0;
-        if (inPlane && (y0 - 3 + kEdge + j) < planeRows && j < rowsLeft + 6)
-            raw[j] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)j * L.pitch));
-    }
+    for (int j = 0; j < BL_PF; j++) raw[j] = __ldg(reinterpret_cast<const uint32_t*>(src + min(j, lastRow) * pitch));
 #pragma unroll
     for (int i = 0; i < BL_ROWS + 6; i++) {
         // source row i of the tile = plane row y0 - 3 + kEdge + i
         const uint32_t wv = raw[i % BL_PF];
-        if (i + BL_PF < BL_ROWS + 6) {
-            raw[i % BL_PF] = 0;
-            if (inPlane && (y0 - 3 + kEdge + i + BL_PF) < planeRows && i + BL_PF < rowsLeft + 6)
-                raw[i % BL_PF] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(i + BL_PF) * L.pitch));
-        }
+        if (i + BL_PF < BL_ROWS + 6)
+            raw[i % BL_PF] = __ldg(reinterpret_cast<const uint32_t*>(src + min(i + BL_PF, lastRow) * pitch));
         E[i % 7] = wv & 0x00ff00ffu;
         O[i % 7] = __byte_perm(wv, 0u, 0x4341);
         if (i >= 6) {
@@ -126,7 +128,7 @@ __global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_co
                 o3 = __dp2a_hi(RE, K2, o3);                          // v6*18
                 // byte 2 of every accumulator = (V + 32768) >> 16
                 const uint32_t out = __byte_perm(__byte_perm(o0, o1, 0x0062), __byte_perm(o2, o3, 0x0062), 0x5410);
-                if (outLane) *reinterpret_cast<uint32_t*>(dst + (size_t)r * L.pitch) = out;
+                store_word_if(dst + r * pitch, out, outLane);
             }
         }
     }

@@ -12,7 +12,7 @@ for r in rows:
     ci = {n: i for i, n in enumerate(h)}
     try:
         lines.append((cur, int(r[0]), int(r[ci["Instructions Executed"]] or 0), int(r[ci["# Samples"]] or 0),
-                      int(r[ci["L1 Wavefronts Shared Excessive"]] or 0), r[1].strip()))
+                      int(r[ci["L1 Wavefronts Shared Excessive"]] or 0) if "L1 Wavefronts Shared Excessive" in ci else 0, r[1].strip()))
     except ValueError:
         pass
 tot = sum(l[2] for l in lines) or 1
