@@ -40,42 +40,13 @@ __device__ __forceinline__ void store_word_if(uint8_t* p, uint32_t v, int on) {
     asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q st.global.u32 [%0], %1;\n\t}" :: "l"(p), "r"(v), "r"(on) : "memory");
 }
 
-// grid (ceil(nTiles / BL_WARPS), n); block 32 * BL_WARPS; one warp per tile
-__global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_constant__ Geom g,
-                                                                 const uint8_t* __restrict__ pyr,
-                                                                 uint8_t* __restrict__ blur,
-                                                                 const BlurTile* __restrict__ tiles, int nTiles,
-                                                                 const int* __restrict__ levelCount) {
-    const int lane = threadIdx.x & 31;
-    const int ti = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
-    if (ti >= nTiles) return;
-    const BlurTile t = tiles[ti];
-    const int img = blockIdx.y;
-    // ORBextractor_old.cc:1140-1141: levels without keypoints are not blurred
-    if (levelCount && levelCount[img * g.nlevels + t.level] == 0) return;
-    const LevelGeom& L = g.lv[t.level];
-    int nStrips, sw;
-    blur_strips(L.w, &nStrips, &sw);
-    const int words = (L.w + 3) >> 2;
-    const int wfirst = t.tx * sw;                          // first output word of the strip
-    const int wlast = min(wfirst + sw, words);             // one past the last output word
-    const int wi = wfirst - 1 + lane;                      // this lane's word (level x = 4 * wi)
-    const int y0 = t.ty * BL_ROWS;
-    const int pc = kXOff + 4 * wi;                         // plane column of the word
-    const bool inPlane = pc >= 0 && pc + 4 <= L.pitch;    // false only for lanes right of every word an output reads
-    const bool outLane = lane >= 1 && wi < wlast;
-    const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff;
-    const ptrdiff_t pitch = L.pitch;
-    // source row y - 3 of output row y is plane row y - 3 + kEdge
-    const uint8_t* src = pyr + planeBase + (y0 - 3 + kEdge) * pitch + (inPlane ? pc : 0);
-    uint8_t* dst = blur + planeBase + (y0 + kEdge) * pitch + pc;
-    asm volatile("" : "+l"(src), "+l"(dst));               // opaque: two base registers, every access = base + k * pitch
-    const int rowsLeft = L.h - y0;                         // output rows available in this tile (> 0)
-    // The outputs of the tile read its source rows 0 .. rowsLeft + 5 (all inside the padded plane: the last one is plane
-    // row h + kEdge + 2).  Requests past that row are clamped onto it instead of predicated: one min per row, no
-    // compare / branch; the clamped rows only feed output rows >= rowsLeft, which are not stored.
+// The row loop of one warp tile.  FULL: all BL_ROWS output rows exist (every tile but the last tile row of a level), so the
+// loop carries no row test and no clamp.  Otherwise requests past the last source row the outputs read (row rowsLeft + 5 of
+// the tile, still inside the padded plane: plane row h + kEdge + 2) are clamped onto it instead of predicated -- one min
+// per row, no compare / branch -- and the clamped rows only feed output rows >= rowsLeft, which are not computed.
+template <bool FULL>
+__device__ __forceinline__ void blur_rows(const uint8_t* src, uint8_t* dst, ptrdiff_t pitch, int rowsLeft, int outLane) {
     const int lastRow = rowsLeft + 5;
-
     constexpr uint32_t K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24);    // lo: (18,34)  hi: (48,56)
     constexpr uint32_t K2 = 48u | (34u << 8) | (0u << 16) | (18u << 24);     // lo: (48,34)  hi: (0,18)
     constexpr uint32_t K3 = 18u;                                             // lo: (18,0)
@@ -83,18 +54,18 @@ __global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_co
     uint32_t E[7], O[7];    // even / odd bytes of the last 7 source rows (16-bit lanes)
     uint32_t raw[BL_PF];    // loads in flight: row i + BL_PF is requested while row i is consumed
 #pragma unroll
-    for (int j = 0; j < BL_PF; j++) raw[j] = __ldg(reinterpret_cast<const uint32_t*>(src + min(j, lastRow) * pitch));
+    for (int j = 0; j < BL_PF; j++) raw[j] = __ldg(reinterpret_cast<const uint32_t*>(src + (FULL ? j : min(j, lastRow)) * pitch));
 #pragma unroll
     for (int i = 0; i < BL_ROWS + 6; i++) {
         // source row i of the tile = plane row y0 - 3 + kEdge + i
         const uint32_t wv = raw[i % BL_PF];
         if (i + BL_PF < BL_ROWS + 6)
-            raw[i % BL_PF] = __ldg(reinterpret_cast<const uint32_t*>(src + min(i + BL_PF, lastRow) * pitch));
+            raw[i % BL_PF] = __ldg(reinterpret_cast<const uint32_t*>(src + (FULL ? i + BL_PF : min(i + BL_PF, lastRow)) * pitch));
         E[i % 7] = wv & 0x00ff00ffu;
         O[i % 7] = __byte_perm(wv, 0u, 0x4341);
         if (i >= 6) {
             const int r = i - 6;    // output row of the tile; window rows r .. r + 6 live in slots (r + k) % 7
-            if (r < rowsLeft) {     // warp-uniform
+            if (FULL || r < rowsLeft) {     // warp-uniform
                 const uint32_t VE = (E[r % 7] + E[(r + 6) % 7]) * 18u + (E[(r + 1) % 7] + E[(r + 5) % 7]) * 34u +
                                     (E[(r + 2) % 7] + E[(r + 4) % 7]) * 48u + E[(r + 3) % 7] * 56u;    // (v0, v2)
                 const uint32_t VO = (O[r % 7] + O[(r + 6) % 7]) * 18u + (O[(r + 1) % 7] + O[(r + 5) % 7]) * 34u +
@@ -132,6 +103,41 @@ __global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_co
             }
         }
     }
+}
+
+// grid (ceil(nTiles / BL_WARPS), n); block 32 * BL_WARPS; one warp per tile
+__global__ void __launch_bounds__(32 * BL_WARPS) gauss7x7_kernel(const __grid_constant__ Geom g,
+                                                                 const uint8_t* __restrict__ pyr,
+                                                                 uint8_t* __restrict__ blur,
+                                                                 const BlurTile* __restrict__ tiles, int nTiles,
+                                                                 const int* __restrict__ levelCount) {
+    const int lane = threadIdx.x & 31;
+    const int ti = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
+    if (ti >= nTiles) return;
+    const BlurTile t = tiles[ti];
+    const int img = blockIdx.y;
+    // ORBextractor_old.cc:1140-1141: levels without keypoints are not blurred
+    if (levelCount && levelCount[img * g.nlevels + t.level] == 0) return;
+    const LevelGeom& L = g.lv[t.level];
+    int nStrips, sw;
+    blur_strips(L.w, &nStrips, &sw);
+    const int words = (L.w + 3) >> 2;
+    const int wfirst = t.tx * sw;                          // first output word of the strip
+    const int wlast = min(wfirst + sw, words);             // one past the last output word
+    const int wi = wfirst - 1 + lane;                      // this lane's word (level x = 4 * wi)
+    const int y0 = t.ty * BL_ROWS;
+    const int pc = kXOff + 4 * wi;                         // plane column of the word
+    const bool inPlane = pc >= 0 && pc + 4 <= L.pitch;    // false only for lanes right of every word an output reads
+    const bool outLane = lane >= 1 && wi < wlast;
+    const size_t planeBase = (size_t)img * g.slabBytes + L.planeOff;
+    const ptrdiff_t pitch = L.pitch;
+    // source row y - 3 of output row y is plane row y - 3 + kEdge
+    const uint8_t* src = pyr + planeBase + (y0 - 3 + kEdge) * pitch + (inPlane ? pc : 0);
+    uint8_t* dst = blur + planeBase + (y0 + kEdge) * pitch + pc;
+    asm volatile("" : "+l"(src), "+l"(dst));               // opaque: two base registers, every access = base + k * pitch
+    const int rowsLeft = L.h - y0;                         // output rows available in this tile (> 0)
+    if (rowsLeft >= BL_ROWS) blur_rows<true>(src, dst, pitch, rowsLeft, outLane);
+    else blur_rows<false>(src, dst, pitch, rowsLeft, outLane);
 }
 
 // host: tile table of one geometry (cached by the caller)
