@@ -302,29 +302,25 @@ __global__ void __launch_bounds__(32 * DS_WARPS, MINB) describe_fused_kernel(con
         const KpWork w = b.work[(size_t)img * g.outCap + k];
         const LevelGeom& L = g.lv[w.level];
         const int pitch = L.pitch;
-        const size_t step = (size_t)AG_ROWS_PER_IT * pitch;
+        const ptrdiff_t step = (ptrdiff_t)AG_ROWS_PER_IT * pitch;
         const size_t plane = (size_t)img * g.slabBytes + L.planeOff + kXOff;    // planes, pitches and kXOff are multiples of 4
         const int cB = (int)w.x - DC_R, cA = (int)w.x - kHalfPatch;             // first column of the two windows
         uint32_t st[DC_ITERS];
         {
             const uint8_t* p = b.blur + plane + (size_t)((int)w.y + kEdge - DC_R + rsubB) * pitch + (cB & ~3) + 4 * wqB;
+            asm volatile("" : "+l"(p));    // opaque: one base register, every row = p + it * step (one IMAD.WIDE per load)
 #pragma unroll
-            for (int it = 0; it < DC_ITERS; it++) {
-                st[it] = __ldg(reinterpret_cast<const uint32_t*>(p));
-                p += step;
-            }
+            for (int it = 0; it < DC_ITERS; it++) st[it] = __ldg(reinterpret_cast<const uint32_t*>(p + it * step));
         }
         // ---- IC_Angle (:78-105)
         int m10 = 0, m01 = 0;
         {
             const uint8_t* p = b.pyr + plane + (size_t)((int)w.y + kEdge - kHalfPatch + rsubA) * pitch + (cA & ~3) + 4 * wqA;
             const int2* wt = sW + (cA & 3) * (AG_ITERS * 32) + lane;
+            asm volatile("" : "+l"(p));
             uint32_t pix[AG_ITERS];
 #pragma unroll
-            for (int it = 0; it < AG_ITERS; it++) {
-                pix[it] = __ldg(reinterpret_cast<const uint32_t*>(p));
-                p += step;
-            }
+            for (int it = 0; it < AG_ITERS; it++) pix[it] = __ldg(reinterpret_cast<const uint32_t*>(p + it * step));
 #pragma unroll
             for (int it = 0; it < AG_ITERS; it++) {
                 const int2 w2 = wt[it * 32];

@@ -316,9 +316,12 @@ __device__ __forceinline__ int key_quadrant(uint32_t key, int mx, int my) {
     return (x < mx ? 0 : 1) | (y < my ? 0 : 2);    // 0 = n1 (UL), 1 = n2 (UR), 2 = n3 (BL), 3 = n4 (BR), :516-526
 }
 
-// grid (nlevels, n); block OT_THREADS; dynamic shared memory laid out by the host (octree_smem_bytes).
-__global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
-                                                            int nodeCap, int keySmem) {
+// One (image, level) list with n > 0 candidates.  KEYS_SM: the two key buffers fit the shared-memory area behind the node
+// arrays (n <= keySmem, the normal case) -- a template parameter so that every key access is an LDS / STS; with the buffer
+// chosen at run time the pointers were generic and every access a generic LD / ST.  Otherwise the keys live in the
+// per-image global scratch.
+template <bool KEYS_SM>
+__device__ __forceinline__ void octree_list(const Geom& g, const ExtractBuffers& b, int nodeCap, int keySmem, int n) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int wsum[2 * OT_WARPS + 2];
     __shared__ int sK, sTotal;
@@ -351,32 +354,17 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
     const int* cellCnt = b.cellCount + (size_t)img * g.nCells + L.cellBase;
     const uint32_t* cellSlots = b.slots + ((size_t)img * g.nCells + L.cellBase) * g.slotCap;
 
-    // ---- total number of candidates -------------------------------------------------------------------------
-    int part = 0;
-    for (int c = tid; c < nCellsL; c += OT_THREADS) part += cellCnt[c];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    if (lane == 0) wsum[warp] = part;
-    __syncthreads();
-    int n = 0;
-#pragma unroll
-    for (int w = 0; w < OT_WARPS; w++) n += wsum[w];
-    __syncthreads();
-    if (n == 0 || nCellsL == 0) {    // empty list stays empty (the loop of :624 ends at once with size == prevSize)
-        if (tid == 0) *levelCount = 0;
-        return;
-    }
-
-    uint32_t* kb[2];
-    if (n <= keySmem) {
-        kb[0] = kS;
-        kb[1] = kS + keySmem;
+    // two plain pointers and selects (not an indexed array): the address space of both survives to every access
+    uint32_t *kb0, *kb1;
+    if (KEYS_SM) {
+        kb0 = kS;
+        kb1 = kS + keySmem;
     } else {
         uint32_t* base = b.scratch + (size_t)img * b.scratchPerImage;
         unsigned long long off = 0;
         for (int l = 0; l < level; l++) off += 2ull * (unsigned long long)g.lv[l].maxCand;
-        kb[0] = base + off;
-        kb[1] = kb[0] + L.maxCand;
+        kb0 = base + off;
+        kb1 = kb0 + L.maxCand;
     }
 
     // ---- gather the candidates in the reference's insertion order (cell row, cell column, raster) --------------
@@ -391,7 +379,7 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
             for (int k = warp; k < m; k += OT_WARPS) {
                 const int cnt = cellCnt[c0 + k];
                 const uint32_t* src = cellSlots + (size_t)(c0 + k) * g.slotCap;
-                uint32_t* dst = kb[0] + running + s.tA[k];
+                uint32_t* dst = kb0 + running + s.tA[k];
                 for (int i = lane; i < cnt; i += 32) dst[i] = src[i];
             }
             running += tot;
@@ -417,13 +405,13 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
                     uint32_t key = 0;
                     bool mine = false;
                     if (i < n) {
-                        key = kb[0][i];
+                        key = kb0[i];
                         int ri = (int)(__fdiv_rn((float)(key & 0xfff), hX));
                         ri = min(ri, nIni - 1);
                         mine = ri == r;
                     }
                     const uint32_t m = __ballot_sync(0xffffffffu, mine);
-                    if (mine) kb[1][pos + __popc(m & ltMask)] = key;
+                    if (mine) kb1[pos + __popc(m & ltMask)] = key;
                     pos += __popc(m);
                 }
                 if (lane == 0) {
@@ -494,7 +482,7 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
         for (int k = warp; k < np; k += OT_WARPS) {
             const OtNode nd = s.cur[s.P[k]];
             const int mx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), my = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
-            const uint32_t* src = kb[nd.start >> 31] + (nd.start & 0x7fffffffu);
+            const uint32_t* src = ((nd.start >> 31) ? kb1 : kb0) + (nd.start & 0x7fffffffu);
             int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
             for (int i = lane; i < nd.cnt; i += 32) {
                 const int q = key_quadrant(src[i], mx, my);
@@ -538,8 +526,8 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
             const int hx = (nd.x1 - nd.x0 + 1) >> 1, hy = (nd.y1 - nd.y0 + 1) >> 1;    // ceil(float(d) / 2)
             const int mx = nd.x0 + hx, my = nd.y0 + hy;
             const unsigned sb = nd.start >> 31, st = nd.start & 0x7fffffffu;
-            const uint32_t* src = kb[sb] + st;
-            uint32_t* dst = kb[sb ^ 1] + st;
+            const uint32_t* src = (sb ? kb1 : kb0) + st;
+            uint32_t* dst = (sb ? kb0 : kb1) + st;
             const int c0 = s.c4[4 * k], c1 = s.c4[4 * k + 1], c2 = s.c4[4 * k + 2], c3 = s.c4[4 * k + 3];
             int o0 = 0, o1 = c0, o2 = c0 + c1, o3 = c0 + c1 + c2;
             for (int base = 0; base < nd.cnt; base += 32) {
@@ -621,7 +609,7 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
     // ---- keep the first key with the largest response of every node, in list order (:760-778) ----------------
     for (int i = warp; i < size; i += OT_WARPS) {
         const OtNode nd = s.cur[i];
-        const uint32_t* src = kb[nd.start >> 31] + (nd.start & 0x7fffffffu);
+        const uint32_t* src = ((nd.start >> 31) ? kb1 : kb0) + (nd.start & 0x7fffffffu);
         // maximise (response, -index): pack as response << 24 | (0xffffff - index) when the segment is short,
         // otherwise compare explicitly
         int bestR = -1, bestI = 0x7fffffff;
@@ -637,6 +625,33 @@ __global__ void __launch_bounds__(OT_THREADS) octree_kernel(const __grid_constan
         if (lane == 0) outKeys[i] = src[bestI];
     }
     if (tid == 0) *levelCount = size;
+}
+
+// grid (nlevels, n); block OT_THREADS; dynamic shared memory laid out by the host (octree_smem_bytes).
+__global__ void __launch_bounds__(OT_THREADS, 5) octree_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
+                                                            int nodeCap, int keySmem) {
+    __shared__ int wcount[OT_WARPS];
+    const int level = blockIdx.x, img = blockIdx.y;
+    const LevelGeom& L = g.lv[level];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // ---- total number of candidates -------------------------------------------------------------------------
+    const int nCellsL = L.nCols * L.nRows;
+    const int* cellCnt = b.cellCount + (size_t)img * g.nCells + L.cellBase;
+    int part = 0;
+    for (int c = tid; c < nCellsL; c += OT_THREADS) part += cellCnt[c];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (lane == 0) wcount[warp] = part;
+    __syncthreads();
+    int n = 0;
+#pragma unroll
+    for (int w = 0; w < OT_WARPS; w++) n += wcount[w];
+    if (n == 0 || nCellsL == 0) {    // empty list stays empty (the loop of :624 ends at once with size == prevSize)
+        if (tid == 0) b.levelCount[(size_t)img * g.nlevels + level] = 0;
+        return;
+    }
+    if (n <= keySmem) octree_list<true>(g, b, nodeCap, keySmem, n);    // block-uniform
+    else octree_list<false>(g, b, nodeCap, keySmem, n);
 }
 
 size_t octree_smem_bytes(int nodeCap, int keySmem) { return octree_node_bytes(nodeCap) + 8 * (size_t)keySmem; }
