@@ -298,7 +298,7 @@ struct orbfe_extractor {
     DevBuf dItems, dBlurTiles, dTaps;
     const ResizeTap* xtab[ORBFE_MAX_LEVELS] = {};
     const ResizeTap* ytab[ORBFE_MAX_LEVELS] = {};
-    ResizeDims rsDims[2][ORBFE_MAX_LEVELS] = {};    // [0] large batches (16 rows per thread), [1] small batches (4)
+    ResizeDims rsDims[2][ORBFE_MAX_LEVELS] = {};    // [0] large batches (12 rows per thread), [1] small batches (4)
 
     // workspace for `chunkCap` images
     int chunkCap = 0;
@@ -396,7 +396,7 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
         build_taps(g.lv[l - 1].h, g.lv[l].h, false, ty);
         for (int v = 0; v < 2; v++) {
             ResizeDims& d = ex->rsDims[v][l];
-            d.rpt = v == 0 ? 16 : 4;
+            d.rpt = v == 0 ? 12 : 4;    // large batches: 48-row tiles (A/B on 1024 images 752x480: 16 -> 1.19 ms, 12 -> 1.14, 8 -> 1.15, 4 -> 1.36)
             if (v == 0)
                 if (const char* e = getenv("ORBFE_RESIZE_RPT"))    // rows per thread of the large-batch resize tiles (A/B)
                     if (atoi(e) >= 1 && atoi(e) <= 64) d.rpt = atoi(e);
