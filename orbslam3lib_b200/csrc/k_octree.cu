@@ -327,7 +327,7 @@ __device__ __forceinline__ void octree_list(const Geom& g, const ExtractBuffers&
     __shared__ int sK, sTotal;
     __shared__ int sortStack[3 * 64];
 
-    const int level = blockIdx.x, img = blockIdx.y;
+    const int level = blockIdx.y, img = blockIdx.x;
     const LevelGeom& L = g.lv[level];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t ltMask = (1u << lane) - 1u;
@@ -627,11 +627,11 @@ __device__ __forceinline__ void octree_list(const Geom& g, const ExtractBuffers&
     if (tid == 0) *levelCount = size;
 }
 
-// grid (nlevels, n); block OT_THREADS; dynamic shared memory laid out by the host (octree_smem_bytes).
+// grid (n, nlevels); block OT_THREADS; dynamic shared memory laid out by the host (octree_smem_bytes).
 __global__ void __launch_bounds__(OT_THREADS, 5) octree_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
                                                             int nodeCap, int keySmem) {
     __shared__ int wcount[OT_WARPS];
-    const int level = blockIdx.x, img = blockIdx.y;
+    const int level = blockIdx.y, img = blockIdx.x;
     const LevelGeom& L = g.lv[level];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // ---- total number of candidates -------------------------------------------------------------------------
@@ -660,7 +660,9 @@ int launch_octree(const Geom& g, int n, const ExtractBuffers& b, int nodeCap, in
     const size_t smem = octree_smem_bytes(nodeCap, keySmem);
     static SmemOptIn optIn;
     smem_opt_in(optIn, octree_kernel, smem);
-    octree_kernel<<<dim3(g.nlevels, n), OT_THREADS, smem, st>>>(g, b, nodeCap, keySmem);
+    // level-major block order: the lists of level 0 (the most candidates, the longest CTAs) start first and the short
+    // lists of the top levels fill the tail of the last wave
+    octree_kernel<<<dim3(n, g.nlevels), OT_THREADS, smem, st>>>(g, b, nodeCap, keySmem);
     return 1;
 }
 
