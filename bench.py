@@ -834,6 +834,8 @@ def main():
     ap.add_argument("--map-rows", type=int, default=1000000, help="rows of the map-scale kNN leg (configs[4]); 0 = skip")
     ap.add_argument("--map-steps", type=int, default=10)
     ap.add_argument("--no-nf1000", dest="nf1000", action="store_false", help="skip the 1000-feature leg")
+    ap.add_argument("--no-two-handles", dest="two_handles", action="store_false",
+                    help="skip the e2e leg with two batches in flight (two extractor handles on two host threads)")
     ap.add_argument("--latency-iters", type=int, default=300, help="stereo pairs of the per-frame latency leg (configs[2]); 0 = skip")
     ap.add_argument("--c4-frames", type=int, default=32, help="4K frames per GPU per step of the configs[3] leg; 0 = skip")
     ap.add_argument("--search-frames", type=int, default=512, help="frames per step of the SearchByProjection leg; 0 = skip")
@@ -937,6 +939,51 @@ def main():
     for _ in range(max(1, args.warmup // 2)):
         step_e2e()
     ms_e2e, _ = timed(step_e2e, args.steps)
+    # e2e with two batches in flight: a second extractor handle (own streams, own workspace, own pinned buffers) on a
+    # second host thread; the two threads split the K steps, so the copy-in of one batch overlaps the kernel tail and
+    # the copy-out of the other (handles are independent, include/orbfe_c.h; tests/test_gpu_threads.py).  Every step is
+    # still one orbfe_extract_match_batch call with host buffers in and out.
+    e2e_pair = None
+    if args.two_handles:
+        import threading
+        ex_b = ORBextractor(NFEAT, 1.2, NLEVELS, 20, 7, device=local)
+        s_b = torch.cuda.Stream(device=dev)
+        ex_b.set_stream(s_b.cuda_stream)
+        h_pairs_b = torch.flip(h_pairs, [0]).contiguous().pin_memory()    # the same pairs in reverse order
+        b_kps, b_desc = torch.zeros_like(h_kps).pin_memory(), torch.zeros_like(h_desc).pin_memory()
+        b_counts, b_monos = torch.zeros_like(h_counts).pin_memory(), torch.zeros_like(h_monos).pin_memory()
+        b_idx, b_dist = torch.zeros_like(h_idx).pin_memory(), torch.zeros_like(h_dist).pin_memory()
+
+        def step_b():
+            ex_b.extract_match_batch_raw(h_pairs_b, P, W, H, b_kps, b_desc, cap, b_counts, b_monos, b_idx, b_dist)
+
+        def run_pair(steps):
+            errs = []
+
+            def loop(fn, k):
+                try:
+                    for _ in range(k):
+                        fn()
+                except Exception as e:    # noqa: BLE001 - re-raised in the main thread
+                    errs.append(e)
+            ts = [threading.Thread(target=loop, args=(step_e2e, (steps + 1) // 2)),
+                  threading.Thread(target=loop, args=(step_b, steps // 2))]
+            for t in ts:
+                t.start()
+            for t in ts:
+                t.join()
+            if errs:
+                raise errs[0]
+
+        run_pair(2)
+        ms_pair, _ = timed(lambda: run_pair(args.steps), 1)
+        a_cnt = h_counts.numpy().reshape(P, 2)
+        pair_same = bool(np.array_equal(b_counts.numpy().reshape(P, 2)[::-1], a_cnt) and
+                         np.array_equal(b_idx.numpy()[::-1], h_idx.numpy()))
+        e2e_pair = {"ms_per_step": ms_pair / args.steps, "equal_to_single_call": pair_same,
+                    "value": n * world * args.steps / (ms_pair * 1e-3), "unit": "frames/s",
+                    "call": "orbfe_extract_match_batch on two extractor handles from two host threads (two batches in flight)"}
+        del ex_b
     clocks = sampler.stop()
     # after the timer: the fused call returns what the two-call form returns (pair p = images p and P + p there)
     e2e_idx, e2e_cnt = h_idx.numpy().copy(), h_counts.numpy().reshape(P, 2).copy()
@@ -1065,6 +1112,7 @@ def main():
         "e2e": {"value": fps_e2e, "unit": "frames/s", "ms_per_step": ms_e2e / args.steps,
                 "call": "orbfe_extract_match_batch (one call: host images in; keypoints, descriptors, counts and k=2 matches out)",
                 "two_call_ms_per_step": ms_two / max(2, args.steps // 2), "equals_two_call_form": e2e_same,
+                "two_handles": e2e_pair,
                 "h2d_bytes_per_step": int(h_imgs.numel()),
                 "d2h_bytes_per_step": int(h_kps.numel() + h_desc.numel() + 2 * n * 4 + h_idx.numel() * 4 + h_dist.numel() * 4)},
         "gpu_launches": launches,
