@@ -304,3 +304,37 @@ def test_small_batch_cuda_graph_path(oracle):
         np.testing.assert_array_equal(idx.numpy()[0, :len(ri)], ri)
         np.testing.assert_array_equal(dist.numpy()[0, :len(ri)], rdist)
     assert min(launches) > 10    # replayed graphs still report the kernels they launch
+
+
+@pytest.mark.parametrize("scale,nl,w,h,nf", [(1.1, 8, 333, 251, 400), (1.5, 5, 752, 480, 800), (1.33, 4, 160, 150, 100),
+                                             (1.2, 3, 1000, 90, 300), (1.25, 7, 517, 389, 500)])
+def test_other_scale_factors_and_sizes_single_and_large_batch(oracle, scale, nl, w, h, nf):
+    """scaleFactor / nlevels other than the 1.2 / 8 of every shipped configuration, odd image sizes (levels narrower than one
+    resize tile, tiles whose source window is a single 16-byte vector), through the single-image kernels (4 rows per thread)
+    and the large-batch ones (>= 32 images: 48-row resize tiles): whole output and every padded pyramid plane against the
+    oracle."""
+    _compare(oracle, "texture", w, h, 8100, nf, nl)    # the same size at scale 1.2 (what _compare builds)
+    kinds = ("texture", "checker", "noise")
+    base = [scenes.make(kinds[i % 3], w, h, 8100 + i) for i in range(3)]
+    n = 35
+    imgs = np.stack([base[i % 3] for i in range(n)])
+    ex = ORBextractor(nf, scale, nl, 20, 7)
+    counts, monos, kps, desc = ex.extract_batch(imgs)
+    refs = []
+    for b in base:
+        r = oracle.OracleExtractor(nf, scale, nl, 20, 7)
+        refs.append((r, r(b)))
+    for i in (0, 1, 2, n - 2, n - 1):
+        r, (mono, rk, rd) = refs[i % 3]
+        c = int(counts[i])
+        assert c == len(rk) and int(monos[i]) == mono
+        np.testing.assert_array_equal(desc[i, :c], rd)
+        for f in ("x", "y", "size", "response", "octave"):
+            np.testing.assert_array_equal(kps[i, :c][f], rk[f])
+        for l in range(nl):
+            np.testing.assert_array_equal(ex.level_padded(l, index=i), r.level_padded(l), "image %d level %d" % (i, l))
+    single = ORBextractor(nf, scale, nl, 20, 7)
+    mono, sk, sd = single(base[1])
+    np.testing.assert_array_equal(sd, refs[1][1][2])
+    for l in range(nl):
+        np.testing.assert_array_equal(single.level_padded(l), refs[1][0].level_padded(l), "single image level %d" % l)
