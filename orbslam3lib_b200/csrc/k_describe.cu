@@ -7,9 +7,12 @@
 // Floating point (DESIGN.md "Floating point"): IEEE fp32 with explicit round-to-nearest intrinsics so that nvcc
 // cannot contract a*b+c into an FMA; cos/sin are evaluated in double and rounded to float, exactly like the oracle.
 // These kernels gather from L2 (749 B + 512 B of reads per keypoint) and are not HBM-bound.
+#include <cuda.h>
+
 #include <algorithm>
 #include <cfloat>
 #include <cstdlib>
+#include <cstring>
 
 #include "orb_pattern.h"
 #include "orbfe_internal.h"
@@ -387,6 +390,201 @@ int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap
     return 1;
 }
 
+// ---- describe_tma_kernel: describe_fused_kernel with both windows of a keypoint fetched by the TMA unit -----------------
+// describe_fused_kernel is bound by LSU wavefronts (l1tex 75 %): of ~145 per keypoint, ~85 are the 24 global row loads
+// (three plane rows = three or more cache lines per instruction) and the 13 stores that stage the descriptor window.  Here
+// one lane issues two tiled TMA loads per keypoint -- the 64 x 37 box of the blurred level and the 48 x 31 box of the level
+// around the keypoint, both starting at the 16-byte boundary below the window (a tiled box must start 16-byte aligned
+// in its innermost dimension) -- into the warp's shared-memory stage, completing on the stage's mbarrier; the loads of
+// keypoint k + 1 are issued before keypoint k is worked on (two stages per warp, the work record fetched two keypoints
+// ahead).  The LSU then only serves the 11 word reads of IC_Angle and the 16 byte gathers of the descriptor.
+// Same arithmetic as describe_fused_kernel in the same order: bit-exact.
+constexpr int DT_DW = 64, DT_DH = 2 * DC_R + 1;              // descriptor box: 64 bytes x 37 rows
+constexpr int DT_AW = 48, DT_AH = 2 * kHalfPatch + 1;        // IC_Angle box: 48 bytes x 31 rows
+constexpr int DT_DBYTES = (DT_DW * DT_DH + 127) / 128 * 128;
+constexpr int DT_ABYTES = (DT_AW * DT_AH + 127) / 128 * 128;
+constexpr int DT_STAGE = DT_DBYTES + DT_ABYTES;
+struct alignas(64) DescribeMaps {
+    unsigned char blur[ORBFE_MAX_LEVELS][128];
+    unsigned char pyr[ORBFE_MAX_LEVELS][128];
+};
+
+// parity wait with a bound: a lost transaction traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (int spin = 0; spin < (1 << 24) && !done; spin++)
+        asm volatile(
+            "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    if (!done) __trap();
+}
+
+// grid (gx, n); block 32 * DS_WARPS; dynamic shared memory DS_WARPS * 2 * DT_STAGE
+__global__ void __launch_bounds__(32 * DS_WARPS, 3) describe_tma_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
+                                                                        orbfe_keypoint* __restrict__ kps,
+                                                                        uint8_t* __restrict__ desc, int cap,
+                                                                        const __grid_constant__ DescribeMaps maps) {
+    extern __shared__ __align__(128) uint8_t smDesc[];
+    __shared__ int2 sW[4 * AG_ITERS * 32];
+    __shared__ __align__(8) uint64_t sBar[DS_WARPS][2];
+    const int img = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 4 * AG_ITERS * 32; i += 32 * DS_WARPS) sW[i] = d_icWeights[i];
+    if (lane == 0) {
+        mbar_init(&sBar[warp][0], 1);
+        mbar_init(&sBar[warp][1], 1);
+    }
+    __syncthreads();
+    const int nk = b.result[img].count;
+    float px0[8], py0[8], px1[8], py1[8];    // test (8 * lane + bit): the lane's output byte
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) {
+        const char4 pt = d_pattern[8 * lane + bit];
+        px0[bit] = (float)pt.x; py0[bit] = (float)pt.y; px1[bit] = (float)pt.z; py1[bit] = (float)pt.w;
+    }
+    const int la = min(lane, AG_ROWS_PER_IT * AG_WORDS - 1);
+    const int rsubA = la / AG_WORDS, wqA = la % AG_WORDS;
+    uint8_t* const stage0 = smDesc + warp * (2 * DT_STAGE);
+    const KpWork* work = b.work + (size_t)img * g.outCap;
+    const int stride = gridDim.x * DS_WARPS;
+    int k = blockIdx.x * DS_WARPS + warp;
+    if (k >= nk) return;
+
+    // lane 0: both boxes of keypoint w into stage s
+    auto fetch = [&](const KpWork& w, int s) {
+        if (lane == 0) {
+            uint8_t* d = stage0 + s * DT_STAGE;
+            const int xb = (kXOff + (int)w.x - DC_R) & ~15, xa = (kXOff + (int)w.x - kHalfPatch) & ~15;
+            mbar_arrive_expect_tx(&sBar[warp][s], (uint32_t)(DT_DW * DT_DH + DT_AW * DT_AH));
+            tma_load_3d(d, maps.blur[w.level], xb, (int)w.y + kEdge - DC_R, img, &sBar[warp][s]);
+            tma_load_3d(d + DT_DBYTES, maps.pyr[w.level], xa, (int)w.y + kEdge - kHalfPatch, img, &sBar[warp][s]);
+        }
+    };
+    KpWork w = work[k];
+    fetch(w, 0);
+    KpWork w1 = w;
+    if (k + stride < nk) w1 = work[k + stride];
+    for (int it = 0; k < nk; k += stride, it++) {
+        const int s = it & 1;
+        const bool more = k + stride < nk;
+        if (more) fetch(w1, s ^ 1);    // stage s ^ 1 was read in the previous iteration, which ended with __syncwarp
+        KpWork w2 = w1;
+        if (k + 2 * stride < nk) w2 = work[k + 2 * stride];
+        const LevelGeom& L = g.lv[w.level];
+        const uint8_t* patch = stage0 + s * DT_STAGE;
+        const uint8_t* win = patch + DT_DBYTES;
+        const int ob = (kXOff + (int)w.x - DC_R) & 15, oa = (kXOff + (int)w.x - kHalfPatch) & 15;
+        mbar_wait_bounded(&sBar[warp][s], (uint32_t)((it >> 1) & 1));
+        // ---- IC_Angle (:78-105): word (oa >> 2) + wqA of window row 3 it + rsubA, weights of alignment oa & 3
+        int m10 = 0, m01 = 0;
+        {
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(win) + (oa >> 2) + wqA;
+            const int2* wt = sW + (oa & 3) * (AG_ITERS * 32) + lane;
+#pragma unroll
+            for (int i = 0; i < AG_ITERS; i++) {
+                // rows 31 and 32 of the last iteration do not exist in the box: their weights are zero, read row 30
+                const int row = i == AG_ITERS - 1 ? DT_AH - 1 : AG_ROWS_PER_IT * i + rsubA;
+                const uint32_t pix = wp[row * (DT_AW / 4)];
+                const int2 w2v = wt[i * 32];
+                m10 = dp4a_u8s8(pix, w2v.x, m10);
+                m01 = dp4a_u8s8(pix, w2v.y, m01);
+            }
+        }
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+        // ---- computeOrbDescriptor (:109-148); lane = output byte
+        const float factorPI = (float)(3.14159265358979323846 / 180.f);
+        const float rad = __fmul_rn(angle, factorPI);
+        double sd, cd;
+        sincos((double)rad, &sd, &cd);
+        const float ca = (float)cd, sb = (float)sd;
+        // byte offset of test point (r, c) = (r + 18) * 64 + (c + 18) + ob; r, c arrive as the raw bits of v + 1.5 * 2^23
+        constexpr uint32_t M = 0x4B400000u;
+        const uint32_t K = (uint32_t)(DC_R * DT_DW + DC_R + ob) - M * (uint32_t)(DT_DW + 1);
+        uint32_t byte = 0;
+#pragma unroll
+        for (int bit = 0; bit < 8; bit++) {
+            const uint32_t r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px0[bit], sb), __fmul_rn(py0[bit], ca)), 12582912.f));
+            const uint32_t q0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px0[bit], ca), __fmul_rn(py0[bit], sb)), 12582912.f));
+            const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px1[bit], sb), __fmul_rn(py1[bit], ca)), 12582912.f));
+            const uint32_t q1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px1[bit], ca), __fmul_rn(py1[bit], sb)), 12582912.f));
+            const uint32_t t0 = patch[r0 * (uint32_t)DT_DW + q0 + K];
+            const uint32_t t1 = patch[r1 * (uint32_t)DT_DW + q1 + K];
+            byte |= (uint32_t)(t0 < t1) << bit;
+        }
+        if (w.dst < cap) {
+            desc[((size_t)img * cap + w.dst) * 32 + lane] = (uint8_t)byte;
+            // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
+            if (lane < 7) {
+                float fx = (float)w.x, fy = (float)w.y;
+                if (w.level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+                uint32_t word;
+                switch (lane) {
+                    case 0: word = __float_as_uint(fx); break;
+                    case 1: word = __float_as_uint(fy); break;
+                    case 2: word = __float_as_uint((float)L.scaledPatch); break;
+                    case 3: word = __float_as_uint(angle); break;
+                    case 4: word = __float_as_uint((float)w.response); break;
+                    case 5: word = (uint32_t)w.level; break;
+                    default: word = 0xffffffffu; break;
+                }
+                reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + w.dst)[lane] = word;
+            }
+        }
+        __syncwarp();    // every lane is done with stage s before the next iteration's fetch overwrites it
+        w = w1;
+        w1 = w2;
+    }
+}
+
+typedef CUresult (*DescEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                      const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                      CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through cudaGetDriverEntryPoint (liborbfe.so does not link libcuda); ORBFE_DESCRIBE_TMA=0 keeps
+// describe_fused_kernel (A/B measurements), and so does any failure to encode
+static DescEncodeTiledFn desc_encode_fn() {
+    static DescEncodeTiledFn fn = [] {
+        const char* e = getenv("ORBFE_DESCRIBE_TMA");
+        if (e && atoi(e) == 0) return (DescEncodeTiledFn) nullptr;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return (DescEncodeTiledFn) nullptr;
+        }
+        return (DescEncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+static bool desc_encode_maps(const Geom& g, const ExtractBuffers& b, int n, DescribeMaps* out) {
+    DescEncodeTiledFn enc = desc_encode_fn();
+    if (!enc) return false;
+    static_assert(sizeof(CUtensorMap) == 128, "DescribeMaps holds 128-byte tensor maps");
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& L = g.lv[l];
+        if ((L.pitch & 15) || (g.slabBytes & 15) || (L.planeOff & 15)) return false;
+        const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.h + 2 * kEdge), (cuuint64_t)n};
+        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)g.slabBytes};
+        const cuuint32_t estr[3] = {1u, 1u, 1u};
+        for (int which = 0; which < 2; which++) {
+            const cuuint32_t box[3] = {(cuuint32_t)(which ? DT_AW : DT_DW), (cuuint32_t)(which ? DT_AH : DT_DH), 1u};
+            CUtensorMap tm;
+            if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (which ? b.pyr : b.blur) + L.planeOff, dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+                return false;
+            memcpy(which ? out->pyr[l] : out->blur[l], &tm, 128);
+        }
+    }
+    return true;
+}
+
 int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoint* kps, uint8_t* desc, int cap,
                     cudaStream_t st) {
     upload_pattern(st, g.umax);
@@ -394,7 +592,32 @@ int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoin
     static const int minb = [] { const char* e = getenv("ORBFE_DESCRIBE_MINB"); return e ? atoi(e) : 4; }();
     // a few keypoints per warp so that the per-CTA setup is amortised; small batches keep one keypoint per warp
     const int full = (g.outCap + DS_WARPS - 1) / DS_WARPS;
-    const int gx = n >= 64 ? std::min(full, 24) : full;
+    static const int gxEnv = [] { const char* e = getenv("ORBFE_DESCRIBE_GX"); return e ? atoi(e) : 0; }();    // A/B
+    int gx = gxEnv > 0 ? std::min(full, gxEnv) : (n >= 64 ? std::min(full, 24) : full);
+    // tensor maps of the two slabs, cached per thread on (slab pointers, image count, geometry) like the FAST maps
+    struct MapCache {
+        const uint8_t *pyr = nullptr, *blur = nullptr;
+        int n = 0, w = 0, h = 0, nlevels = 0, ok = 0;
+        unsigned long long slab = 0;
+        DescribeMaps maps;
+    };
+    static thread_local MapCache mc;
+    if (!v1 && (mc.pyr != b.pyr || mc.blur != b.blur || mc.n != n || mc.w != g.width || mc.h != g.height || mc.nlevels != g.nlevels ||
+                mc.slab != g.slabBytes)) {
+        mc.pyr = b.pyr; mc.blur = b.blur; mc.n = n; mc.w = g.width; mc.h = g.height; mc.nlevels = g.nlevels; mc.slab = g.slabBytes;
+        memset(&mc.maps, 0, sizeof(mc.maps));
+        mc.ok = desc_encode_maps(g, b, n, &mc.maps) ? 1 : 0;
+    }
+    if (!v1 && mc.ok) {
+        // long keypoint runs per warp keep the two-stage pipeline full (1024 images, blocks per image 4 .. 10: 0.88 - 0.90 ms,
+        // 16: 0.93, 24: 0.96, 64: 1.14)
+        if (gxEnv <= 0 && n >= 64) gx = std::min(full, 8);
+        const int smem = DS_WARPS * 2 * DT_STAGE;
+        static SmemOptIn optTma;
+        smem_opt_in(optTma, describe_tma_kernel, (size_t)smem);
+        describe_tma_kernel<<<dim3(gx, n), 32 * DS_WARPS, smem, st>>>(g, b, kps, desc, cap, mc.maps);
+        return 1;
+    }
     if (v1) describe_kernel<<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
     else if (minb == 4) describe_fused_kernel<4><<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
     else describe_fused_kernel<3><<<dim3(gx, n), 32 * DS_WARPS, 0, st>>>(g, b, kps, desc, cap);
