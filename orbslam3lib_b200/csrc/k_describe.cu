@@ -396,8 +396,8 @@ int launch_pack(const Geom& g, int n, const ExtractBuffers& b, int lap0, int lap
 // one lane issues two tiled TMA loads per keypoint -- the 64 x 37 box of the blurred level and the 48 x 31 box of the level
 // around the keypoint, both starting at the 16-byte boundary below the window (a tiled box must start 16-byte aligned
 // in its innermost dimension) -- into the warp's shared-memory stage, completing on the stage's mbarrier; the loads of
-// keypoint k + 1 are issued before keypoint k is worked on (two stages per warp, the work record fetched two keypoints
-// ahead).  The LSU then only serves the 11 word reads of IC_Angle and the 16 byte gathers of the descriptor.
+// next keypoint are issued before the current one is worked on (two stages per warp and pass).  The LSU then only serves
+// the 11 word reads of IC_Angle and the 16 byte gathers of the descriptor.
 // Same arithmetic as describe_fused_kernel in the same order: bit-exact.
 constexpr int DT_DW = 64, DT_DH = 2 * DC_R + 1;              // descriptor box: 64 bytes x 37 rows
 constexpr int DT_AW = 48, DT_AH = 2 * kHalfPatch + 1;        // IC_Angle box: 48 bytes x 31 rows
@@ -422,19 +422,21 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity
 }
 
 // grid (gx, n); block 32 * DS_WARPS; dynamic shared memory DS_WARPS * 2 * DT_STAGE
+// A warp owns the keypoints k0, k0 + stride, ... of its image and works on them in groups of up to 32, in two pipelined
+// passes per group: (A) the IC_Angle moments of every keypoint of the group from its 48 x 31 box, lane j keeping those of
+// keypoint j; then ONE evaluation of fastAtan2 and of the double-precision sincos for the whole group (lane j for keypoint j
+// -- one warp per keypoint evaluated the same scalar on 32 lanes, 100 of its ~520 instructions); (B) the descriptors from
+// the 64 x 37 boxes, cos / sin / angle of keypoint j broadcast from lane j.  Each pass runs its own two-stage TMA pipeline.
 __global__ void __launch_bounds__(32 * DS_WARPS, 3) describe_tma_kernel(const __grid_constant__ Geom g, const ExtractBuffers b,
                                                                         orbfe_keypoint* __restrict__ kps,
                                                                         uint8_t* __restrict__ desc, int cap,
                                                                         const __grid_constant__ DescribeMaps maps) {
     extern __shared__ __align__(128) uint8_t smDesc[];
     __shared__ int2 sW[4 * AG_ITERS * 32];
-    __shared__ __align__(8) uint64_t sBar[DS_WARPS][2];
+    __shared__ __align__(8) uint64_t sBar[DS_WARPS][4];    // [0, 1] pass B stages, [2, 3] pass A stages
     const int img = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < 4 * AG_ITERS * 32; i += 32 * DS_WARPS) sW[i] = d_icWeights[i];
-    if (lane == 0) {
-        mbar_init(&sBar[warp][0], 1);
-        mbar_init(&sBar[warp][1], 1);
-    }
+    if (lane < 4) mbar_init(&sBar[warp][lane], 1);
     __syncthreads();
     const int nk = b.result[img].count;
     float px0[8], py0[8], px1[8], py1[8];    // test (8 * lane + bit): the lane's output byte
@@ -445,42 +447,62 @@ __global__ void __launch_bounds__(32 * DS_WARPS, 3) describe_tma_kernel(const __
     }
     const int la = min(lane, AG_ROWS_PER_IT * AG_WORDS - 1);
     const int rsubA = la / AG_WORDS, wqA = la % AG_WORDS;
-    uint8_t* const stage0 = smDesc + warp * (2 * DT_STAGE);
+    // the warp's 2 * DT_STAGE bytes: two descriptor boxes, then two IC_Angle boxes.  (Five IC_Angle boxes in flight, parked in
+    // the descriptor area while pass A runs, were slower: 0.85 vs 0.82 ms -- pass A is not waiting for the TMA.)
+    uint8_t* const bufB = smDesc + warp * (2 * DT_STAGE);
+    auto stageA = [&](int s) { return bufB + 2 * DT_DBYTES + s * DT_ABYTES; };
     const KpWork* work = b.work + (size_t)img * g.outCap;
     const int stride = gridDim.x * DS_WARPS;
-    int k = blockIdx.x * DS_WARPS + warp;
-    if (k >= nk) return;
+    const int k0 = blockIdx.x * DS_WARPS + warp;
+    if (k0 >= nk) return;
+    const int cnt = (nk - k0 + stride - 1) / stride;    // keypoints of this warp
+    uint32_t phase = 0;                                 // bit i = parity the next wait on barrier i uses
 
-    // lane 0: both boxes of keypoint w into stage s
-    auto fetch = [&](const KpWork& w, int s) {
-        if (lane == 0) {
-            uint8_t* d = stage0 + s * DT_STAGE;
-            const int xb = (kXOff + (int)w.x - DC_R) & ~15, xa = (kXOff + (int)w.x - kHalfPatch) & ~15;
-            mbar_arrive_expect_tx(&sBar[warp][s], (uint32_t)(DT_DW * DT_DH + DT_AW * DT_AH));
-            tma_load_3d(d, maps.blur[w.level], xb, (int)w.y + kEdge - DC_R, img, &sBar[warp][s]);
-            tma_load_3d(d + DT_DBYTES, maps.pyr[w.level], xa, (int)w.y + kEdge - kHalfPatch, img, &sBar[warp][s]);
+    for (int base = 0; base < cnt; base += 32) {
+        const int G = min(32, cnt - base);
+        // the lane's own keypoint of the group as two words: x | y << 16 and level | response << 8 (dst is read in pass B)
+        uint32_t myXY = 0, myLR = 0;
+        int myDst = 0;
+        if (lane < G) {
+            const KpWork w = work[k0 + (base + lane) * stride];
+            myXY = (uint32_t)w.x | ((uint32_t)w.y << 16);
+            myLR = (uint32_t)w.level | ((uint32_t)w.response << 8);
+            myDst = w.dst;
         }
-    };
-    KpWork w = work[k];
-    fetch(w, 0);
-    KpWork w1 = w;
-    if (k + stride < nk) w1 = work[k + stride];
-    for (int it = 0; k < nk; k += stride, it++) {
-        const int s = it & 1;
-        const bool more = k + stride < nk;
-        if (more) fetch(w1, s ^ 1);    // stage s ^ 1 was read in the previous iteration, which ended with __syncwarp
-        KpWork w2 = w1;
-        if (k + 2 * stride < nk) w2 = work[k + 2 * stride];
-        const LevelGeom& L = g.lv[w.level];
-        const uint8_t* patch = stage0 + s * DT_STAGE;
-        const uint8_t* win = patch + DT_DBYTES;
-        const int ob = (kXOff + (int)w.x - DC_R) & 15, oa = (kXOff + (int)w.x - kHalfPatch) & 15;
-        mbar_wait_bounded(&sBar[warp][s], (uint32_t)((it >> 1) & 1));
-        // ---- IC_Angle (:78-105): word (oa >> 2) + wqA of window row 3 it + rsubA, weights of alignment oa & 3
-        int m10 = 0, m01 = 0;
-        {
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(win) + (oa >> 2) + wqA;
+        // ---- pass A: IC_Angle moments (:78-105)
+        auto fetchA = [&](int j, int s) {
+            const uint32_t xy = __shfl_sync(0xffffffffu, myXY, j), lr = __shfl_sync(0xffffffffu, myLR, j);
+            if (lane == 0) {
+                const int x = (int)(xy & 0xffffu), y = (int)(xy >> 16);
+                mbar_arrive_expect_tx(&sBar[warp][2 + s], (uint32_t)(DT_AW * DT_AH));
+                tma_load_3d(stageA(s), maps.pyr[lr & 0xffu], (kXOff + x - kHalfPatch) & ~15, y + kEdge - kHalfPatch, img,
+                            &sBar[warp][2 + s]);
+            }
+        };
+        auto fetchB = [&](int j) {
+            const uint32_t xy = __shfl_sync(0xffffffffu, myXY, j), lr = __shfl_sync(0xffffffffu, myLR, j);
+            if (lane == 0) {
+                const int s = j & 1;
+                const int x = (int)(xy & 0xffffu), y = (int)(xy >> 16);
+                mbar_arrive_expect_tx(&sBar[warp][s], (uint32_t)(DT_DW * DT_DH));
+                tma_load_3d(bufB + s * DT_DBYTES, maps.blur[lr & 0xffu], (kXOff + x - DC_R) & ~15, y + kEdge - DC_R, img,
+                            &sBar[warp][s]);
+            }
+        };
+        fetchA(0, 0);
+        fetchB(0);    // the first descriptor box travels under pass A
+        int myM10 = 0, myM01 = 0;
+        for (int j = 0; j < G; j++) {
+            const int s = j & 1;
+            if (j + 1 < G) fetchA(j + 1, s ^ 1);    // stage s ^ 1 was read in the previous iteration, which ended with __syncwarp
+            const int x = (int)(__shfl_sync(0xffffffffu, myXY, j) & 0xffffu);
+            const int oa = (kXOff + x - kHalfPatch) & 15;
+            mbar_wait_bounded(&sBar[warp][2 + s], (phase >> (2 + s)) & 1u);
+            phase ^= 4u << s;
+            // word (oa >> 2) + wqA of box row 3 i + rsubA, weights of alignment oa & 3
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(stageA(s)) + (oa >> 2) + wqA;
             const int2* wt = sW + (oa & 3) * (AG_ITERS * 32) + lane;
+            int m10 = 0, m01 = 0;
 #pragma unroll
             for (int i = 0; i < AG_ITERS; i++) {
                 // rows 31 and 32 of the last iteration do not exist in the box: their weights are zero, read row 30
@@ -490,53 +512,71 @@ __global__ void __launch_bounds__(32 * DS_WARPS, 3) describe_tma_kernel(const __
                 m10 = dp4a_u8s8(pix, w2v.x, m10);
                 m01 = dp4a_u8s8(pix, w2v.y, m01);
             }
+            m10 = __reduce_add_sync(0xffffffffu, m10);
+            m01 = __reduce_add_sync(0xffffffffu, m01);
+            if (lane == j) { myM10 = m10; myM01 = m01; }
+            __syncwarp();
         }
-        m10 = __reduce_add_sync(0xffffffffu, m10);
-        m01 = __reduce_add_sync(0xffffffffu, m01);
-        const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-        // ---- computeOrbDescriptor (:109-148); lane = output byte
-        const float factorPI = (float)(3.14159265358979323846 / 180.f);
-        const float rad = __fmul_rn(angle, factorPI);
-        double sd, cd;
-        sincos((double)rad, &sd, &cd);
-        const float ca = (float)cd, sb = (float)sd;
-        // byte offset of test point (r, c) = (r + 18) * 64 + (c + 18) + ob; r, c arrive as the raw bits of v + 1.5 * 2^23
-        constexpr uint32_t M = 0x4B400000u;
-        const uint32_t K = (uint32_t)(DC_R * DT_DW + DC_R + ob) - M * (uint32_t)(DT_DW + 1);
-        uint32_t byte = 0;
+        // ---- one fastAtan2 + cos / sin per keypoint, lane j for keypoint j (:109-116)
+        const float myAngle = fast_atan2_deg((float)myM01, (float)myM10);
+        float myCa, mySb;
+        {
+            const float factorPI = (float)(3.14159265358979323846 / 180.f);
+            const float rad = __fmul_rn(myAngle, factorPI);
+            double sd, cd;
+            sincos((double)rad, &sd, &cd);
+            myCa = (float)cd;
+            mySb = (float)sd;
+        }
+        // ---- pass B: computeOrbDescriptor (:109-148); lane = output byte
+        for (int j = 0; j < G; j++) {
+            const int s = j & 1;
+            if (j + 1 < G) fetchB(j + 1);
+            const uint32_t xy = __shfl_sync(0xffffffffu, myXY, j), lr = __shfl_sync(0xffffffffu, myLR, j);
+            const int dst = __shfl_sync(0xffffffffu, myDst, j);
+            const float ca = __shfl_sync(0xffffffffu, myCa, j), sb = __shfl_sync(0xffffffffu, mySb, j);
+            const float angle = __shfl_sync(0xffffffffu, myAngle, j);
+            const int x = (int)(xy & 0xffffu), y = (int)(xy >> 16), level = (int)(lr & 0xffu), response = (int)(lr >> 8);
+            const int ob = (kXOff + x - DC_R) & 15;
+            const uint8_t* patch = bufB + s * DT_DBYTES;
+            mbar_wait_bounded(&sBar[warp][s], (phase >> s) & 1u);
+            phase ^= 1u << s;
+            // byte offset of test point (r, c) = (r + 18) * 64 + (c + 18) + ob; r, c arrive as the raw bits of v + 1.5 * 2^23
+            constexpr uint32_t M = 0x4B400000u;
+            const uint32_t K = (uint32_t)(DC_R * DT_DW + DC_R + ob) - M * (uint32_t)(DT_DW + 1);
+            uint32_t byte = 0;
 #pragma unroll
-        for (int bit = 0; bit < 8; bit++) {
-            const uint32_t r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px0[bit], sb), __fmul_rn(py0[bit], ca)), 12582912.f));
-            const uint32_t q0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px0[bit], ca), __fmul_rn(py0[bit], sb)), 12582912.f));
-            const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px1[bit], sb), __fmul_rn(py1[bit], ca)), 12582912.f));
-            const uint32_t q1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px1[bit], ca), __fmul_rn(py1[bit], sb)), 12582912.f));
-            const uint32_t t0 = patch[r0 * (uint32_t)DT_DW + q0 + K];
-            const uint32_t t1 = patch[r1 * (uint32_t)DT_DW + q1 + K];
-            byte |= (uint32_t)(t0 < t1) << bit;
-        }
-        if (w.dst < cap) {
-            desc[((size_t)img * cap + w.dst) * 32 + lane] = (uint8_t)byte;
-            // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
-            if (lane < 7) {
-                float fx = (float)w.x, fy = (float)w.y;
-                if (w.level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
-                uint32_t word;
-                switch (lane) {
-                    case 0: word = __float_as_uint(fx); break;
-                    case 1: word = __float_as_uint(fy); break;
-                    case 2: word = __float_as_uint((float)L.scaledPatch); break;
-                    case 3: word = __float_as_uint(angle); break;
-                    case 4: word = __float_as_uint((float)w.response); break;
-                    case 5: word = (uint32_t)w.level; break;
-                    default: word = 0xffffffffu; break;
-                }
-                reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + w.dst)[lane] = word;
+            for (int bit = 0; bit < 8; bit++) {
+                const uint32_t r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px0[bit], sb), __fmul_rn(py0[bit], ca)), 12582912.f));
+                const uint32_t q0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px0[bit], ca), __fmul_rn(py0[bit], sb)), 12582912.f));
+                const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(px1[bit], sb), __fmul_rn(py1[bit], ca)), 12582912.f));
+                const uint32_t q1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(px1[bit], ca), __fmul_rn(py1[bit], sb)), 12582912.f));
+                const uint32_t t0 = patch[r0 * (uint32_t)DT_DW + q0 + K];
+                const uint32_t t1 = patch[r1 * (uint32_t)DT_DW + q1 + K];
+                byte |= (uint32_t)(t0 < t1) << bit;
             }
+            if (dst < cap) {
+                desc[((size_t)img * cap + dst) * 32 + lane] = (uint8_t)byte;
+                // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
+                if (lane < 7) {
+                    const LevelGeom& L = g.lv[level];
+                    float fx = (float)x, fy = (float)y;
+                    if (level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+                    uint32_t word;
+                    switch (lane) {
+                        case 0: word = __float_as_uint(fx); break;
+                        case 1: word = __float_as_uint(fy); break;
+                        case 2: word = __float_as_uint((float)L.scaledPatch); break;
+                        case 3: word = __float_as_uint(angle); break;
+                        case 4: word = __float_as_uint((float)response); break;
+                        case 5: word = (uint32_t)level; break;
+                        default: word = 0xffffffffu; break;
+                    }
+                    reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + dst)[lane] = word;
+                }
+            }
+            __syncwarp();    // every lane is done with stage s before the next iteration's fetch overwrites it
         }
-        __syncwarp();    // every lane is done with stage s before the next iteration's fetch overwrites it
-        w = w1;
-        w1 = w2;
     }
 }
 
