@@ -338,3 +338,36 @@ def test_other_scale_factors_and_sizes_single_and_large_batch(oracle, scale, nl,
     np.testing.assert_array_equal(sd, refs[1][1][2])
     for l in range(nl):
         np.testing.assert_array_equal(single.level_padded(l), refs[1][0].level_padded(l), "single image level %d" % l)
+
+
+def test_random_geometries(oracle):
+    """seeded random image sizes, feature counts, level counts and scale factors (every level at least 61 px on both sides, the
+    smallest the reference's cell arithmetic accepts): the table-driven resize tiles, the FAST work items, the blur strips and
+    the TMA boxes of the descriptor stage at image borders, single image and a 33-image batch, against the oracle."""
+    rng = np.random.RandomState(20260)
+    done = 0
+    while done < 10:
+        w, h = int(rng.randint(120, 1000)), int(rng.randint(100, 720))
+        scale = float(rng.choice([1.1, 1.2, 1.2, 1.25, 1.4]))
+        nl = int(rng.randint(2, 9))
+        if min(w, h) / scale ** (nl - 1) < 61:
+            continue
+        nf = int(rng.randint(50, 1500))
+        kind = ("texture", "checker", "noise", "flat_blobs")[done % 4]
+        img = scenes.make(kind, w, h, 8200 + done)
+        ref = oracle.OracleExtractor(nf, scale, nl, 20, 7)
+        mono_r, kps_r, desc_r = ref(img, (0, 0))
+        ex = ORBextractor(nf, scale, nl, 20, 7)
+        mono_g, kps_g, desc_g = ex(img, (0, 0))
+        tag = "%s %dx%d nf=%d nl=%d scale=%g" % (kind, w, h, nf, nl, scale)
+        assert mono_g == mono_r and len(kps_g) == len(kps_r), tag
+        np.testing.assert_array_equal(desc_g, desc_r, tag)
+        for f in ("x", "y", "size", "response", "octave"):
+            np.testing.assert_array_equal(kps_g[f], kps_r[f], tag)
+        if done % 3 == 0:    # the large-batch kernels on the same geometry
+            counts, monos, kps, desc = ex.extract_batch(np.stack([img] * 33))
+            for i in (0, 16, 32):
+                c = int(counts[i])
+                assert c == len(kps_r) and int(monos[i]) == mono_r, tag
+                np.testing.assert_array_equal(desc[i, :c], desc_r, tag)
+        done += 1
