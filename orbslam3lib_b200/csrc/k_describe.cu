@@ -650,8 +650,8 @@ int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoin
     }
     if (!v1 && mc.ok) {
         // long keypoint runs per warp keep the two-stage pipeline full (1024 images, blocks per image 4 .. 10: 0.88 - 0.90 ms,
-        // 16: 0.93, 24: 0.96, 64: 1.14)
-        if (gxEnv <= 0 && n >= 64) gx = std::min(full, 8);
+        // 16: 0.93, 24: 0.96, 64: 1.14); smaller batches get enough blocks for ~4 waves of 3 CTAs per SM
+        if (gxEnv <= 0) gx = std::min(full, std::max(8, (1776 + n - 1) / n));
         const int smem = DS_WARPS * 2 * DT_STAGE;
         static SmemOptIn optTma;
         smem_opt_in(optTma, describe_tma_kernel, (size_t)smem);
