@@ -1059,7 +1059,7 @@ def main():
     stage_kernels = {"pyramid": ["pad_interior_kernel", "pad_frame_kernel", "pad_level0_kernel", "resize_rows_kernel",
                                  "resize_tile_kernel"],
                      "fast": ["fast_cells_kernel"], "blur": ["gauss7x7_kernel"], "octree": ["octree_kernel"],
-                     "describe": ["pack_kernel", "describe_kernel", "describe_fused_kernel"]}
+                     "describe": ["pack_kernel", "describe_kernel", "describe_fused_kernel", "describe_tma_kernel"]}
     for k, ks in stage_kernels.items():
         if k not in stage_report or per.get(k, 0) <= 0:
             continue
