@@ -371,3 +371,43 @@ def test_random_geometries(oracle):
                 assert c == len(kps_r) and int(monos[i]) == mono_r, tag
                 np.testing.assert_array_equal(desc[i, :c], desc_r, tag)
         done += 1
+
+
+@pytest.mark.parametrize("env", [{"ORBFE_DESCRIBE_TMA": "0"}, {"ORBFE_DESCRIBE_V1": "1"}, {"ORBFE_FAST_TMAP": "0"},
+                                 {"ORBFE_RESIZE_TILE": "1"}, {"ORBFE_KNN_KEYED": "0"}])
+def test_alternative_extractor_kernels_still_agree(env):
+    """the kernels the defaults replaced stay selectable (A/B measurements, and the fallbacks taken when a tensor map cannot
+    be encoded): describe_fused_kernel / describe_kernel instead of describe_tma_kernel, FAST strips by per-row bulk copies,
+    resize_tile_kernel, the unkeyed per-pair kNN.  Same outputs as the defaults on a 40-pair batch (large-batch kernels) and a
+    single pair; the switches are read once per process, hence the subprocesses."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import numpy as np, sys, zlib\n"
+        "from orbslam3lib_b200 import ORBextractor, scenes\n"
+        "base = [scenes.make(k, 333, 251, 8300 + i) for i, k in enumerate(('texture', 'checker', 'noise'))]\n"
+        "pairs = np.stack([np.stack([base[i % 3], scenes.stereo_right(base[i % 3], 8300 + i % 3)]) for i in range(40)])\n"
+        "ex = ORBextractor(400, 1.2, 6, 20, 7)\n"
+        "h = 0\n"
+        "for batch in (pairs, pairs[:1]):\n"
+        "    counts, monos, kps, desc, idx, dist = ex.extract_match_batch(batch)\n"
+        "    for p in range(len(batch)):\n"
+        "        for e in range(2):\n"
+        "            c = int(counts[p, e])\n"
+        "            h = zlib.crc32(desc[p, e, :c].tobytes(), h); h = zlib.crc32(kps[p, e, :c].tobytes(), h)\n"
+        "        c = int(counts[p, 0])\n"
+        "        h = zlib.crc32(idx[p, :c].tobytes(), h); h = zlib.crc32(dist[p, :c].tobytes(), h)\n"
+        "    h = zlib.crc32(counts.tobytes(), h); h = zlib.crc32(monos.tobytes(), h)\n"
+        "sys.stdout.write('%d %d' % (h, int(counts.sum())))\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for e in ({}, env):
+        full = dict(os.environ, **e)
+        for k in ("ORBFE_DESCRIBE_TMA", "ORBFE_DESCRIBE_V1", "ORBFE_FAST_TMAP", "ORBFE_RESIZE_TILE", "ORBFE_KNN_KEYED"):
+            if k not in e:
+                full.pop(k, None)
+        outs.append(subprocess.run([sys.executable, "-c", code], cwd=root, env=full, capture_output=True, text=True,
+                                   timeout=300))
+    assert outs[0].returncode == 0 and outs[1].returncode == 0, outs[1].stderr[-400:]
+    assert outs[0].stdout == outs[1].stdout and int(outs[0].stdout.split()[1]) > 100    # keypoints of the single pair
