@@ -634,21 +634,29 @@ int launch_describe(const Geom& g, int n, const ExtractBuffers& b, orbfe_keypoin
     const int full = (g.outCap + DS_WARPS - 1) / DS_WARPS;
     static const int gxEnv = [] { const char* e = getenv("ORBFE_DESCRIBE_GX"); return e ? atoi(e) : 0; }();    // A/B
     int gx = gxEnv > 0 ? std::min(full, gxEnv) : (n >= 64 ? std::min(full, 24) : full);
-    // tensor maps of the two slabs, cached per thread on (slab pointers, image count, geometry) like the FAST maps
+    // tensor maps of the two slabs, cached per thread on (slab pointers, image count, geometry); four entries, oldest replaced:
+    // the pipelined host path alternates between two workspace halves and a few stage sizes
     struct MapCache {
         const uint8_t *pyr = nullptr, *blur = nullptr;
-        int n = 0, w = 0, h = 0, nlevels = 0, ok = 0;
-        unsigned long long slab = 0;
+        int n = 0, ok = 0;
+        unsigned long long key = 0;    // geom_plane_key: level planes of the slab
         DescribeMaps maps;
     };
-    static thread_local MapCache mc;
-    if (!v1 && (mc.pyr != b.pyr || mc.blur != b.blur || mc.n != n || mc.w != g.width || mc.h != g.height || mc.nlevels != g.nlevels ||
-                mc.slab != g.slabBytes)) {
-        mc.pyr = b.pyr; mc.blur = b.blur; mc.n = n; mc.w = g.width; mc.h = g.height; mc.nlevels = g.nlevels; mc.slab = g.slabBytes;
-        memset(&mc.maps, 0, sizeof(mc.maps));
-        mc.ok = desc_encode_maps(g, b, n, &mc.maps) ? 1 : 0;
+    static thread_local MapCache cache[4];
+    static thread_local int cacheNext = 0;
+    MapCache* hit = nullptr;
+    const unsigned long long key = geom_plane_key(g);
+    for (MapCache& c : cache)
+        if (c.pyr == b.pyr && c.blur == b.blur && c.n == n && c.key == key) hit = &c;
+    if (!v1 && !hit) {
+        hit = &cache[cacheNext];
+        cacheNext = (cacheNext + 1) & 3;
+        hit->pyr = b.pyr; hit->blur = b.blur; hit->n = n; hit->key = key;
+        memset(&hit->maps, 0, sizeof(hit->maps));
+        hit->ok = desc_encode_maps(g, b, n, &hit->maps) ? 1 : 0;
     }
-    if (!v1 && mc.ok) {
+    MapCache& mc = hit ? *hit : cache[0];
+    if (!v1 && hit && mc.ok) {
         // long keypoint runs per warp keep the two-stage pipeline full (1024 images, blocks per image 4 .. 10: 0.88 - 0.90 ms,
         // 16: 0.93, 24: 0.96, 64: 1.14); smaller batches get enough blocks for ~4 waves of 3 CTAs per SM
         if (gxEnv <= 0) gx = std::min(full, std::max(8, (1776 + n - 1) / n));

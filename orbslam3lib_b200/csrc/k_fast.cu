@@ -589,24 +589,30 @@ int launch_fast(const Geom& g, const uint8_t* pyr, int n, const FastItem* items,
     const int smem = fast_smem_bytes(tileBytes, kbitsBytes, listBytes);
     static SmemOptIn optIn;    // static usage here is <= 16 KiB
     smem_opt_in(optIn, fast_cells_kernel, (size_t)smem);
-    // tensor maps of this launch, cached per thread on (slab pointer, image count, geometry)
+    // tensor maps of this launch, cached per thread on (slab pointer, image count, level planes); four entries, oldest
+    // replaced: the pipelined host path alternates between two workspace halves and a few stage sizes
     struct MapCache {
         const uint8_t* pyr = nullptr;
-        int n = 0, w = 0, h = 0, nlevels = 0, ok = 0;
-        unsigned long long slab = 0;
+        int n = 0, ok = 0;
+        unsigned long long key = 0;
         FastMaps maps;
     };
-    static thread_local MapCache mc;
-    if (mc.pyr != pyr || mc.n != n || mc.w != g.width || mc.h != g.height || mc.nlevels != g.nlevels || mc.slab != g.slabBytes) {
-        mc.pyr = pyr;
-        mc.n = n;
-        mc.w = g.width;
-        mc.h = g.height;
-        mc.nlevels = g.nlevels;
-        mc.slab = g.slabBytes;
-        memset(&mc.maps, 0, sizeof(mc.maps));
-        mc.ok = fast_encode_maps(g, pyr, n, &mc.maps) ? 1 : 0;
+    static thread_local MapCache cache[4];
+    static thread_local int cacheNext = 0;
+    const unsigned long long key = geom_plane_key(g);
+    MapCache* hit = nullptr;
+    for (MapCache& c : cache)
+        if (c.pyr == pyr && c.n == n && c.key == key) hit = &c;
+    if (!hit) {
+        hit = &cache[cacheNext];
+        cacheNext = (cacheNext + 1) & 3;
+        hit->pyr = pyr;
+        hit->n = n;
+        hit->key = key;
+        memset(&hit->maps, 0, sizeof(hit->maps));
+        hit->ok = fast_encode_maps(g, pyr, n, &hit->maps) ? 1 : 0;
     }
+    MapCache& mc = *hit;
     fast_cells_kernel<<<dim3(nItems, n), FAST_THREADS, smem, st>>>(g, pyr, items, slots, cellCount, tileBytes, kbitsBytes,
                                                                    listBytes, mc.maps, mc.ok);
     return 1;

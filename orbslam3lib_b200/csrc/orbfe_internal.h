@@ -58,6 +58,17 @@ struct Geom {
     int umax[kHalfPatch + 1];
 };
 
+// fingerprint of everything a tensor map of a level plane depends on besides the slab pointer and the image count
+inline unsigned long long geom_plane_key(const Geom& g) {
+    unsigned long long k = 1469598103934665603ull;
+    for (int l = 0; l < g.nlevels; l++) {
+        const unsigned long long v[4] = {(unsigned long long)g.lv[l].planeOff, (unsigned long long)g.lv[l].pitch,
+                                         (unsigned long long)g.lv[l].w, (unsigned long long)g.lv[l].h};
+        for (unsigned long long x : v) k = (k ^ x) * 1099511628211ull;
+    }
+    return (k ^ g.slabBytes) * 1099511628211ull;
+}
+
 // one FAST work item = a run of cells of one cell row (k_fast.cu).  Everything that depends only on the geometry is
 // worked out once on the host (fast_item_table), so a CTA starts with three 16-byte loads instead of ~130 scalar
 // instructions per thread.
