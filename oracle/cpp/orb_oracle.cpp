@@ -59,6 +59,18 @@ struct Timer {
 // imgproc/resize.cpp: coefficient setup of cv::resize + HResizeLinear<uchar,int,short,2048> +
 // VResizeLinear<uchar,int,short,FixedPtCast<int,uchar,22>>.
 void resizeLinearU8(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride) {
+    // imgproc/resize.cpp, cv::resize: "if( interpolation == INTER_LINEAR && is_area_fast && iscale_x == 2 && iscale_y == 2 )
+    // interpolation = INTER_AREA" -- an exact 2x decimation on both axes is the 2x2 box average of ResizeAreaFastVec for
+    // uchar: (s00 + s01 + s10 + s11 + 2) >> 2
+    if (sw == 2 * dw && sh == 2 * dh) {
+        for (int y = 0; y < dh; y++) {
+            const uint8_t* r0 = src + (size_t)(2 * y) * sstride;
+            const uint8_t* r1 = r0 + sstride;
+            for (int x = 0; x < dw; x++)
+                dst[(size_t)y * dstride + x] = (uint8_t)((r0[2 * x] + r0[2 * x + 1] + r1[2 * x] + r1[2 * x + 1] + 2) >> 2);
+        }
+        return;
+    }
     const double inv_x = (double)dw / sw, inv_y = (double)dh / sh;
     const double scale_x = 1. / inv_x, scale_y = 1. / inv_y;
     std::vector<int> xofs(dw), yofs(dh);

@@ -321,6 +321,33 @@ __global__ void __launch_bounds__(256) resize_rows_kernel(const uint8_t* __restr
     }
 }
 
+// ---- halve_kernel: a level that is an exact 2x decimation of the one below -----------------------------------------------
+// cv::resize(INTER_LINEAR) switches to INTER_AREA when both axes shrink by exactly 2 (imgproc/resize.cpp; scaleFactor 2.0 on
+// even sizes): the 2x2 box average (s00 + s01 + s10 + s11 + 2) >> 2 of ResizeAreaFastVec.  The REFLECT_101 frame is
+// written in the same pass by reflecting the destination coordinate first, like the bilinear kernels.  Not a hot path
+// (no shipped configuration uses scale 2): one 32-bit word of the padded destination plane per thread, byte by byte.
+// grid (ceil(words / 64), ceil(rows / 4), n); block (64, 4)
+__global__ void __launch_bounds__(256) halve_kernel(const uint8_t* __restrict__ srcPlane, int spitch,
+                                                    uint8_t* __restrict__ dstPlane, int dpitch, unsigned long long slabBytes,
+                                                    int dw, int dh) {
+    const int c0 = 4 * (blockIdx.x * 64 + threadIdx.x);    // plane column of the word
+    const int py = blockIdx.y * 4 + threadIdx.y;           // padded row
+    if (py >= dh + 2 * kEdge || c0 >= kXOff + dw + kEdge) return;
+    const int y = reflect101(py - kEdge, dh);
+    const uint8_t* r0 = srcPlane + (size_t)blockIdx.z * slabBytes + (size_t)(2 * y + kEdge) * spitch + kXOff;
+    const uint8_t* r1 = r0 + spitch;
+    uint32_t out = 0;
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+        const int x = c0 + b - kXOff;
+        if (x >= -kEdge && x < dw + kEdge) {
+            const int xr = 2 * reflect101(x, dw);
+            out |= (((uint32_t)r0[xr] + r0[xr + 1] + r1[xr] + r1[xr + 1] + 2u) >> 2) << (8 * b);
+        }
+    }
+    *reinterpret_cast<uint32_t*>(dstPlane + (size_t)blockIdx.z * slabBytes + (size_t)py * dpitch + c0) = out;
+}
+
 // host: shared-memory window (pitch SP, rows SH) needed by the tiles of one level for `rpt` rows per thread.
 // Mirrors the range computation of the kernel on the host copies of the tap tables.
 static int h_reflect101(int p, int len) {
@@ -435,6 +462,13 @@ int launch_pyramid(const Geom& g, const uint8_t* images, int n, int stride, size
             }
         } else {
             const LevelGeom& P = g.lv[l - 1];
+            if (P.w == 2 * L.w && P.h == 2 * L.h) {    // INTER_LINEAR is INTER_AREA here (see halve_kernel)
+                const int words = (kXOff + L.w + kEdge + 3) / 4, rows = L.h + 2 * kEdge;
+                halve_kernel<<<dim3((words + 63) / 64, (rows + 3) / 4, n), dim3(64, 4), 0, st>>>(pyr + P.planeOff, P.pitch, pyr + L.planeOff,
+                                                                                           L.pitch, g.slabBytes, L.w, L.h);
+                launches++;
+                continue;
+            }
             static const bool useTile = [] { const char* e = getenv("ORBFE_RESIZE_TILE"); return e && atoi(e) != 0; }();
             if (!useTile) {    // default: the stripped-down row loop on the same tiles
                 const ResizeDims& d = dims[l];

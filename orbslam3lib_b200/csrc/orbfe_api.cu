@@ -359,13 +359,8 @@ static int configure_geometry(orbfe_extractor* ex, int w, int h) {
     build_geom(ex->params, ex->tables, w, h, g);
     if (w > 4095 + 2 * kMinBorder || h > 4095 + 2 * kMinBorder)
         return set_err(ex, ORBFE_ERR_ARG, "image %dx%d too large: candidate coordinates are packed in 12 bits", w, h);
-    // cv::resize(INTER_LINEAR) silently becomes INTER_AREA (2x2 box average) when BOTH axes shrink by exactly 2
-    // (imgproc/resize.cpp: is_area_fast && iscale_x == 2 && iscale_y == 2).  Only the bilinear path exists here and in
-    // the oracle, so such a pyramid (scaleFactor 2.0 on even sizes) is refused rather than computed differently.
-    for (int l = 1; l < g.nlevels; l++)
-        if (g.lv[l - 1].w == 2 * g.lv[l].w && g.lv[l - 1].h == 2 * g.lv[l].h)
-            return set_err(ex, ORBFE_ERR_ARG, "level %d is an exact 2x decimation of level %d: cv::resize(INTER_LINEAR) switches to "
-                                              "INTER_AREA there, which this path does not implement", l, l - 1);
+    // (a level that is an exact 2x decimation of the one below -- scaleFactor 2.0 on even sizes -- takes halve_kernel:
+    // cv::resize(INTER_LINEAR) is INTER_AREA there, k_pyramid.cu)
     // FAST work items
     std::vector<FastItem> items;
     int tb = 0, sb = 0, lb = 0;

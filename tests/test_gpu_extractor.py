@@ -411,3 +411,29 @@ def test_alternative_extractor_kernels_still_agree(env):
                                    timeout=300))
     assert outs[0].returncode == 0 and outs[1].returncode == 0, outs[1].stderr[-400:]
     assert outs[0].stdout == outs[1].stdout and int(outs[0].stdout.split()[1]) > 100    # keypoints of the single pair
+
+
+@pytest.mark.parametrize("w,h,nl", [(752, 480, 3), (640, 488, 4), (333, 251, 2)])
+def test_scale_factor_two_takes_the_box_average(oracle, w, h, nl):
+    """scaleFactor 2.0: where a level is an exact 2x decimation of the one below, cv::resize(INTER_LINEAR) is INTER_AREA (2x2
+    box average, halve_kernel); odd sizes stay bilinear (333 -> 167 is not exact).  Whole output and every padded plane, single
+    image and a 33-image batch."""
+    img = scenes.make("texture", w, h, 8400)
+    ref = oracle.OracleExtractor(500, 2.0, nl, 20, 7)
+    mono_r, kps_r, desc_r = ref(img, (0, 0))
+    ex = ORBextractor(500, 2.0, nl, 20, 7)
+    mono_g, kps_g, desc_g = ex(img, (0, 0))
+    assert mono_g == mono_r and len(kps_g) == len(kps_r) and len(kps_r) > 50
+    np.testing.assert_array_equal(desc_g, desc_r)
+    for f in ("x", "y", "size", "response", "octave"):
+        np.testing.assert_array_equal(kps_g[f], kps_r[f])
+    for l in range(nl):
+        assert ex.level_size(l) == ref.level_size(l)
+        np.testing.assert_array_equal(ex.level_padded(l), ref.level_padded(l), "padded pyramid level %d" % l)
+    counts, monos, kps, desc = ex.extract_batch(np.stack([img] * 33))
+    for i in (0, 32):
+        c = int(counts[i])
+        assert c == len(kps_r)
+        np.testing.assert_array_equal(desc[i, :c], desc_r)
+        for l in range(nl):
+            np.testing.assert_array_equal(ex.level_padded(l, index=i), ref.level_padded(l), "image %d level %d" % (i, l))

@@ -39,8 +39,7 @@ def test_resize_random_pairs(oracle):
     for k in range(40):
         sw, sh = int(rng.integers(8, 300)), int(rng.integers(8, 300))
         dw, dh = max(2, int(sw / rng.uniform(1.05, 1.9))), max(2, int(sh / rng.uniform(1.05, 1.9)))
-        if sw == 2 * dw or sh == 2 * dh:
-            continue    # exact 2x switches OpenCV to INTER_AREA; never happens at scale 1.2
+        # (an exact 2x pair switches OpenCV to INTER_AREA: the oracle follows, test_resize_exact_half_is_the_box_average)
         img = scenes.make("noise" if k % 2 else "texture", sw, sh, 7100 + k)
         np.testing.assert_array_equal(oracle.resize_linear(img, dw, dh), cv2.resize(img, (dw, dh), 0, 0, cv2.INTER_LINEAR))
 
@@ -165,3 +164,12 @@ def test_undistort_keypoints_vs_cv2(oracle, dist):
     np.testing.assert_array_equal(out["y"].view(np.uint32), np.ascontiguousarray(ref[:, 1]).view(np.uint32))
     for f in ("size", "angle", "response", "octave", "class_id"):
         np.testing.assert_array_equal(out[f], kps[f])
+
+
+def test_resize_exact_half_is_the_box_average(oracle):
+    """cv::resize(INTER_LINEAR) turns into INTER_AREA when both axes shrink by exactly 2 (scaleFactor 2.0 on even sizes);
+    one axis exact and the other not stays bilinear."""
+    rng = np.random.RandomState(77)
+    for (w, h, dw, dh) in ((640, 480, 320, 240), (322, 250, 161, 125), (64, 62, 32, 31), (640, 481, 320, 240), (641, 480, 320, 240)):
+        img = rng.randint(0, 256, (h, w)).astype(np.uint8)
+        np.testing.assert_array_equal(oracle.resize_linear(img, dw, dh), cv2.resize(img, (dw, dh), 0, 0, cv2.INTER_LINEAR))
