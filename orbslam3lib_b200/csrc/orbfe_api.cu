@@ -887,6 +887,12 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             ORBFE_CUDA(ex, cudaMemcpyAsync(resHost, ex->bufs.result, (size_t)m * sizeof(ImageResult), cudaMemcpyDeviceToHost, st));
             ORBFE_CUDA(ex, cudaMemcpyAsync(errHost, ex->bufs.errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
             ORBFE_CUDA(ex, cudaMemcpy2DAsync(ex->dCounts.p, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
+            if (outDev) {
+                // counts / monos are device int32 arrays: scatter the two fields with strided 2-D copies (before the call's one
+                // synchronisation, not after it)
+                if (counts) ORBFE_CUDA(ex, cudaMemcpy2DAsync(counts + base, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
+                if (monos) ORBFE_CUDA(ex, cudaMemcpy2DAsync(monos + base, 4, &ex->bufs.result[0].mono, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
+            }
             if (!outDev && cap > 0) {
                 ORBFE_CUDA(ex, cudaMemcpyAsync(kps + (size_t)base * cap, dK, (size_t)m * cap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
                 ORBFE_CUDA(ex, cudaMemcpyAsync(desc + (size_t)base * cap * 32, dD, (size_t)m * cap * 32, cudaMemcpyDeviceToHost, st));
@@ -982,12 +988,6 @@ static int extract_batch_impl(orbfe_extractor* ex, const uint8_t* images, int n,
             if (outDev) continue;
             if (counts) counts[base + i] = res[i].count;
             if (monos) monos[base + i] = res[i].mono;
-        }
-        if (outDev) {
-            // counts / monos are device int32 arrays: scatter the two fields with strided 2-D copies
-            if (counts) ORBFE_CUDA(ex, cudaMemcpy2DAsync(counts + base, 4, &ex->bufs.result[0].count, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
-            if (monos) ORBFE_CUDA(ex, cudaMemcpy2DAsync(monos + base, 4, &ex->bufs.result[0].mono, sizeof(ImageResult), 4, m, cudaMemcpyDeviceToDevice, st));
-            ORBFE_CUDA(ex, cudaStreamSynchronize(st));
         }
     }
     if (status == ORBFE_ERR_CAPACITY) return set_err(ex, status, "keypoint capacity %d too small (need <= %d)", cap, g.outCap);
