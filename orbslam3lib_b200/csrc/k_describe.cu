@@ -434,6 +434,8 @@ __global__ void __launch_bounds__(32 * DS_WARPS, 3) describe_tma_kernel(const __
     extern __shared__ __align__(128) uint8_t smDesc[];
     __shared__ int2 sW[4 * AG_ITERS * 32];
     __shared__ __align__(8) uint64_t sBar[DS_WARPS][4];    // [0, 1] pass B stages, [2, 3] pass A stages
+    __shared__ float2 sLv[ORBFE_MAX_LEVELS];               // (scale, scaled patch size) of every level: no indexed constant loads
+    if (threadIdx.x < g.nlevels) sLv[threadIdx.x] = make_float2(g.lv[threadIdx.x].scale, (float)g.lv[threadIdx.x].scaledPatch);
     const int img = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < 4 * AG_ITERS * 32; i += 32 * DS_WARPS) sW[i] = d_icWeights[i];
     if (lane < 4) mbar_init(&sBar[warp][lane], 1);
@@ -558,22 +560,19 @@ __global__ void __launch_bounds__(32 * DS_WARPS, 3) describe_tma_kernel(const __
             if (dst < cap) {
                 desc[((size_t)img * cap + dst) * 32 + lane] = (uint8_t)byte;
                 // cv::KeyPoint: pt (scaled :1167-1169), size (:891), angle, response, octave (:890), class_id = -1
-                if (lane < 7) {
-                    const LevelGeom& L = g.lv[level];
-                    float fx = (float)x, fy = (float)y;
-                    if (level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
-                    uint32_t word;
-                    switch (lane) {
-                        case 0: word = __float_as_uint(fx); break;
-                        case 1: word = __float_as_uint(fy); break;
-                        case 2: word = __float_as_uint((float)L.scaledPatch); break;
-                        case 3: word = __float_as_uint(angle); break;
-                        case 4: word = __float_as_uint((float)response); break;
-                        case 5: word = (uint32_t)level; break;
-                        default: word = 0xffffffffu; break;
-                    }
-                    reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + dst)[lane] = word;
-                }
+                // every lane builds the same seven words and picks its own with selects (a switch on the lane was seven
+                // divergent paths: 10 % of the kernel's stall samples)
+                const float2 lv = sLv[level];
+                float fx = (float)x, fy = (float)y;
+                if (level != 0) { fx = __fmul_rn(fx, lv.x); fy = __fmul_rn(fy, lv.x); }    // warp-uniform
+                uint32_t word = 0xffffffffu;    // class_id
+                word = lane == 5 ? (uint32_t)level : word;
+                word = lane == 4 ? __float_as_uint((float)response) : word;
+                word = lane == 3 ? __float_as_uint(angle) : word;
+                word = lane == 2 ? __float_as_uint(lv.y) : word;
+                word = lane == 1 ? __float_as_uint(fy) : word;
+                word = lane == 0 ? __float_as_uint(fx) : word;
+                if (lane < 7) reinterpret_cast<uint32_t*>(kps + (size_t)img * cap + dst)[lane] = word;
             }
             __syncwarp();    // every lane is done with stage s before the next iteration's fetch overwrites it
         }
